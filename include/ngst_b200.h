@@ -1,0 +1,124 @@
+/* C ABI of libngst_b200.so: the B200-native tent-pitched Trefftz-DG wave propagator.
+ *
+ * Every entry point is what a binding of the reference's pybind11 surface for this path would call
+ * (the reference file:line each one replaces is cited per function; paths are relative to the
+ * NGSTrefftz tree, tents.* under external_dependencies/ngstents/src/). Plain pointers and sizes only.
+ * All functions return 0 on success and a negative code on failure; the message is available from
+ * ngst_last_error() (thread-local). No C++ exception crosses this boundary.
+ *
+ * Ownership: the caller owns every array passed in (it is copied during the call) and every output
+ * buffer. Handles own host tables and device buffers. A handle is not thread-safe.
+ */
+#ifndef NGST_B200_H
+#define NGST_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ngst_mesh ngst_mesh;
+typedef struct ngst_slab ngst_slab;
+typedef struct ngst_twave ngst_twave;
+
+enum {
+  NGST_OK = 0,
+  NGST_ERR_ARG = -1,     /* invalid argument / malformed input (ngcore::Exception in the reference) */
+  NGST_ERR_STATE = -2,   /* call order: not pitched, no initial data, ... */
+  NGST_ERR_CUDA = -3,    /* CUDA runtime failure, including "no device": there is no CPU fallback */
+  NGST_ERR_NUMERIC = -4, /* singular local system met during Propagate */
+  NGST_ERR_COMM = -5     /* multi-GPU exchange failure */
+};
+
+const char* ngst_last_error(void);
+const char* ngst_version(void);
+
+/* ---------------------------------------------------------------- spatial mesh
+ * Replaces the MeshAccess queries of the path (src/twavetents.cpp:113,117,380,455,472,601,616,941-952;
+ * tents.cpp:233-236,248,507,532,568). bnd_kind[i] = 1 marks a boundary element named "neumann"
+ * (src/twavetents.cpp:380), 0 anything else (Dirichlet). */
+int ngst_mesh_create(int D, int nv, const double* pts, int nel, const int* el2v, int nbnd, const int* bnd2v,
+                     const int* bnd_kind, ngst_mesh** out);
+/* structured stand-ins for netgen's SegMesh / unit_square / unit_cube meshes (test/tents.py:24,38,142) */
+int ngst_mesh_structured(int D, const int* ncells, const double* lo, const double* hi, ngst_mesh** out);
+int ngst_mesh_set_boundary_kind(ngst_mesh* m, const int* bnd_kind);
+/* counts[8] = D, nv, nel, nbnd, nedges, nfacets, 0, 0 */
+int ngst_mesh_counts(const ngst_mesh* m, int* counts);
+/* flat tables; pass NULL to skip. Sizes: pts nv*D, el2v nel*(D+1), bnd2v nbnd*D, bnd_kind nbnd,
+ * edge2v nedges*2, facet2v nfacets*D, el2facet nel*(D+1), facet2el nfacets*2, facet2bnd nfacets,
+ * el2edge nel*{1,3,6} */
+int ngst_mesh_tables(const ngst_mesh* m, double* pts, int* el2v, int* bnd2v, int* bnd_kind, int* edge2v,
+                     int* facet2v, int* el2facet, int* facet2el, int* facet2bnd, int* el2edge);
+void ngst_mesh_destroy(ngst_mesh* m);
+
+/* ---------------------------------------------------------------- tent slab
+ * TentSlab(mesh, method, heapsize) python_tents.cpp:13-29; method 2 = "edge", 1 = "vol". */
+int ngst_slab_create(const ngst_mesh* m, int method, ngst_slab** out);
+/* SetMaxWavespeed python_tents.cpp:35-43: one value per element (the CF evaluated at centroids,
+ * tents.cpp:491-500), or n == 1 for a constant. */
+int ngst_slab_set_max_wavespeed(ngst_slab* s, const double* c, int n);
+/* PitchTents python_tents.cpp:44-65 -> tents.cpp:78-359. *ok = 0 when the slab could not be completed. */
+int ngst_slab_pitch(ngst_slab* s, double dt, int local_ct, double global_ct, int* ok);
+int ngst_slab_ntents(const ngst_slab* s);    /* GetNTents  tents.hpp:217 */
+int ngst_slab_nlayers(const ngst_slab* s);   /* GetNLayers tents.hpp:218 */
+double ngst_slab_height(const ngst_slab* s); /* GetSlabHeight tents.hpp:223 */
+double ngst_slab_max_slope(const ngst_slab* s); /* MaxSlope tents.cpp:366-374 */
+/* sizes[4] = total nbv entries, total els entries, total facet entries, total dag entries */
+int ngst_slab_sizes(const ngst_slab* s, long long* sizes);
+/* Flattened struct Tent (tents.hpp:38-75, python_tents.cpp:119-128) for all tents; NULL skips.
+ * *_off arrays have ntents+1 entries. */
+int ngst_slab_export(const ngst_slab* s, int* vertex, int* level, double* tbot, double* ttop, double* maxslope,
+                     int* nb_off, int* nbv, double* nbtime, int* el_off, int* els, int* facet_off, int* facets,
+                     int* dag_off, int* dag);
+/* level sets: level_off has nlevels+1 entries, level_tents ntents entries (ascending tent id per level) */
+int ngst_slab_levels(const ngst_slab* s, int* nlevels, int* level_off, int* level_tents);
+void ngst_slab_destroy(ngst_slab* s);
+
+/* ---------------------------------------------------------------- Trefftz tent solver
+ * TWave(order, tps, wavespeedcf) src/twavetents.cpp:1194-1228 -> TWaveTents<D> (src/twavetents.hpp:168-186).
+ * c_el: wavespeed per element (the CF at element centroids, twavetents.hpp:177-185); c_vertex: the CF at the
+ * vertices (TentAdiam, twavetents.cpp:871-895) or NULL (then the first adjacent element's value).
+ * device: CUDA device ordinal. Fails with NGST_ERR_CUDA when no device is usable. */
+int ngst_twave_create(const ngst_slab* s, int order, const double* c_el, const double* c_vertex, int device,
+                      ngst_twave** out);
+/* info[8] = D, order, nbasis (LocalDofs), nip, ncomp, fosystem, nel, ntents */
+int ngst_twave_info(const ngst_twave* t, int* info);
+/* Mapped quadrature points (nel*nip*D) and weights |detJ|*w (nel*nip) of every element: what
+ * MakeWavefront (src/twavetents.cpp:734-764) samples a CoefficientFunction at. */
+int ngst_twave_quadrature(const ngst_twave* t, double* x, double* weight);
+/* SetInitial src/twavetents.hpp:195-204: wf is nel x (ncomp*nip), row = [comp][q]; ncomp == D+2 second-order
+ * input (u, grad u, dt u), ncomp == D+1 first-order input (switches to fosystem, nbasis-1). Host pointer. */
+int ngst_twave_set_initial(ngst_twave* t, const double* wf, int ncomp);
+/* Boundary datum (SetBoundaryCF src/twavetents.hpp:206-209, evaluated at src/twavetents.cpp:373-407):
+ * number of sample points and their (x, t_local) coordinates, npoints*(D+1); the datum must be evaluated at
+ * (x, t_local + timeshift). values: for each boundary face in the same order nip Dirichlet values (dt u) or
+ * D*nip Neumann values laid out [component][q]. NULL values = homogeneous datum. */
+long long ngst_twave_boundary_npoints(const ngst_twave* t);
+long long ngst_twave_boundary_nvalues(const ngst_twave* t);
+int ngst_twave_boundary_points(const ngst_twave* t, double* xt, int* kind_per_point);
+int ngst_twave_set_boundary_values(ngst_twave* t, const double* values, long long n);
+/* Propagate src/twavetents.cpp:72-175: one slab, timeshift += slab height. */
+int ngst_twave_propagate(ngst_twave* t);
+double ngst_twave_timeshift(const ngst_twave* t);
+/* device time of the last Propagate in ms (CUDA events on the solver's stream) and kernel launches in it */
+double ngst_twave_last_ms(const ngst_twave* t);
+int ngst_twave_last_launches(const ngst_twave* t);
+/* GetWavefront src/twavetents.hpp:193: copy of the nel x (ncomp*nip) state to a host buffer */
+int ngst_twave_get_wavefront(ngst_twave* t, double* out);
+/* Energy / Error / L2Error src/twavetents.cpp:766-847 on host wavefronts (nel x ncomp*nip) */
+int ngst_twave_energy(ngst_twave* t, const double* wf, double* out);
+int ngst_twave_error(ngst_twave* t, const double* wf, const double* wf_ref, double* out);
+int ngst_twave_l2error(ngst_twave* t, const double* wf, const double* wf_ref, double* out);
+/* MaxAdiam src/twavetents.cpp:906-914 */
+int ngst_twave_max_adiam(const ngst_twave* t, double* out);
+/* CSR Trefftz basis (TWaveBasis<D+1>::Basis src/trefftzfespace.cpp:611-682); sizes[3] = nbasis, npoly, nnz */
+int ngst_twave_basis(const ngst_twave* t, int* sizes, int* rowptr, int* col, double* val);
+void ngst_twave_destroy(ngst_twave* t);
+
+/* host-only helpers exposed for tests (no device needed) */
+int ngst_basis(int D, int order, int fowave, int* sizes, int* rowptr, int* col, double* val, int* expo);
+int ngst_rule(int dim, int order, int* nip, double* xi, double* w);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

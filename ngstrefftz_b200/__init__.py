@@ -1,0 +1,411 @@
+"""B200-native tent-pitched Trefftz-DG wave propagator with the Python surface of NGSTrefftz' tent path.
+
+Mirrors (reference file:line, relative to the NGSTrefftz tree):
+  TentSlab / Tent        external_dependencies/ngstents/src/python_tents.cpp:7-131
+  TWave, TrefftzTents,   src/twavetents.cpp:1157-1229
+  TWaveTents1/2/3
+  GetWave                src/__init__.py:7-53
+
+NGSolve is not available, so `CoefficientFunction`s become plain Python callables / arrays:
+  wavespeed : float | array(nel) | callable(x[n,D]) -> array(n)        (evaluated at element centroids)
+  initial   : callable(x[n,D], t) -> array(n, ncomp)  | array(nel, ncomp*nip)
+  boundary  : callable(x[n,D], t[n]) -> array(n) (Dirichlet: dt u) or array(n, D) (Neumann: grad u)
+and netgen meshes become `Mesh` objects (structured generators SegMesh / UnitSquareMesh / UnitCubeMesh,
+or explicit point/element arrays). All arithmetic of Propagate runs in libngst_b200.so on the GPU.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _capi
+from ._capi import NgstError, check, dptr, f64, i32, iptr, lib
+
+__all__ = ["Mesh", "SegMesh", "UnitSquareMesh", "UnitCubeMesh", "StructuredMesh", "TentSlab", "Tent", "TWave",
+           "TrefftzTents", "TWaveTents", "TaskManager", "SetNumThreads", "NgstError"]
+
+
+class TaskManager:
+    """No-op stand-in for `with TaskManager():` (required by the reference, paralleldepend.hpp:70)."""
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        return False
+
+
+def SetNumThreads(n):
+    """Accepted for script compatibility; tents are scheduled on the GPU."""
+
+
+class Mesh:
+    """Simplex mesh (replaces ngsolve.Mesh for this path)."""
+
+    def __init__(self, points=None, elements=None, boundary=None, boundary_names=None, _handle=None):
+        self._h = C.c_void_p()
+        if _handle is not None:
+            self._h = _handle
+        else:
+            pts = f64(points)
+            if pts.ndim == 1:
+                pts = pts.reshape(-1, 1)
+            el = i32(elements)
+            D = pts.shape[1]
+            bnd = i32(boundary if boundary is not None else np.zeros((0, D)))
+            if bnd.ndim == 1:
+                bnd = bnd.reshape(-1, 1)
+            kind = self._kinds(boundary_names, bnd.shape[0])
+            check(lib.ngst_mesh_create(D, pts.shape[0], dptr(pts), el.shape[0], iptr(el), bnd.shape[0], iptr(bnd),
+                                       iptr(kind), C.byref(self._h)))
+        cnt = np.zeros(8, dtype=np.int32)
+        check(lib.ngst_mesh_counts(self._h, iptr(cnt)))
+        self.dim, self.nv, self.ne, self.nse, self.nedge, self.nfacet = (int(x) for x in cnt[:6])
+        self._tables = None
+
+    @staticmethod
+    def _kinds(names, n):
+        if names is None:
+            return np.zeros(n, dtype=np.int32)
+        if isinstance(names, str):
+            names = [names] * n
+        return i32([1 if (nm == "neumann" or nm == 1) else 0 for nm in names])
+
+    def __del__(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib.ngst_mesh_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def SetBoundaryNames(self, names):
+        """Boundary named "neumann" selects the Neumann flux (src/twavetents.cpp:380); anything else Dirichlet."""
+        kind = self._kinds(names, self.nse)
+        check(lib.ngst_mesh_set_boundary_kind(self._h, iptr(kind)))
+        self._tables = None
+
+    def tables(self):
+        if self._tables is None:
+            D = self.dim
+            nepe = {1: 1, 2: 3, 3: 6}[D]
+            t = dict(pts=np.zeros((self.nv, D)), el2v=np.zeros((self.ne, D + 1), np.int32),
+                     bnd2v=np.zeros((self.nse, D), np.int32), bnd_kind=np.zeros(self.nse, np.int32),
+                     edge2v=np.zeros((self.nedge, 2), np.int32), facet2v=np.zeros((self.nfacet, D), np.int32),
+                     el2facet=np.zeros((self.ne, D + 1), np.int32), facet2el=np.zeros((self.nfacet, 2), np.int32),
+                     facet2bnd=np.zeros(self.nfacet, np.int32), el2edge=np.zeros((self.ne, nepe), np.int32))
+            check(lib.ngst_mesh_tables(self._h, dptr(t["pts"]), iptr(t["el2v"]), iptr(t["bnd2v"]), iptr(t["bnd_kind"]),
+                                       iptr(t["edge2v"]), iptr(t["facet2v"]), iptr(t["el2facet"]), iptr(t["facet2el"]),
+                                       iptr(t["facet2bnd"]), iptr(t["el2edge"])))
+            self._tables = t
+        return self._tables
+
+    @property
+    def points(self):
+        return self.tables()["pts"]
+
+    @property
+    def elements(self):
+        return self.tables()["el2v"]
+
+    def centroids(self):
+        t = self.tables()
+        return t["pts"][t["el2v"]].mean(axis=1)
+
+
+def StructuredMesh(ncells, lo, hi):
+    n = i32(np.atleast_1d(ncells))
+    lo = f64(np.atleast_1d(lo))
+    hi = f64(np.atleast_1d(hi))
+    h = C.c_void_p()
+    check(lib.ngst_mesh_structured(len(n), iptr(n), dptr(lo), dptr(hi), C.byref(h)))
+    return Mesh(_handle=h)
+
+
+def SegMesh(n, x0, x1):
+    """Uniform 1-D mesh, as test/tents.py:38 `SegMesh(4,0,math.pi)`."""
+    return StructuredMesh([n], [x0], [x1])
+
+
+def UnitSquareMesh(n):
+    return StructuredMesh([n, n], [0.0, 0.0], [1.0, 1.0])
+
+
+def UnitCubeMesh(n):
+    return StructuredMesh([n, n, n], [0.0, 0.0, 0.0], [1.0, 1.0, 1.0])
+
+
+class Tent:
+    """struct Tent fields exported at python_tents.cpp:119-128."""
+
+    def __init__(self, vertex, ttop, tbot, nbv, nbtime, els, level, internal_facets, maxslope):
+        self.vertex, self.ttop, self.tbot = int(vertex), float(ttop), float(tbot)
+        self.nbv, self.nbtime, self.els = nbv, nbtime, els
+        self.level, self.internal_facets, self._maxslope = int(level), internal_facets, float(maxslope)
+
+    def MaxSlope(self):
+        return self._maxslope
+
+
+class TentSlab:
+    """TentSlab(mesh, method="edge", heapsize=1000000)  (python_tents.cpp:13-29)."""
+
+    def __init__(self, mesh, method="edge", heapsize=1000000):
+        if method not in ("edge", "vol"):
+            print("Invalid method! Setting edge algorithm as default...")
+            method = "edge"
+        self.mesh = mesh
+        self._h = C.c_void_p()
+        check(lib.ngst_slab_create(mesh._h, 2 if method == "edge" else 1, C.byref(self._h)))
+        self._export = None
+
+    def __del__(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib.ngst_slab_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def SetMaxWavespeed(self, wavespeed):
+        if callable(wavespeed):
+            c = f64(wavespeed(self.mesh.centroids())).reshape(-1)
+        else:
+            c = f64(np.atleast_1d(wavespeed)).reshape(-1)
+        check(lib.ngst_slab_set_max_wavespeed(self._h, dptr(c), len(c)))
+
+    def PitchTents(self, dt, local_ct=False, global_ct=1.0):
+        ok = C.c_int(0)
+        self._export = None
+        try:
+            check(lib.ngst_slab_pitch(self._h, float(dt), int(bool(local_ct)), float(global_ct), C.byref(ok)))
+        except NgstError as e:
+            if e.code == -2:
+                raise RuntimeError("Wavespeed has not been set!") from e
+            raise
+        return bool(ok.value)
+
+    def GetNTents(self):
+        return lib.ngst_slab_ntents(self._h)
+
+    def GetNLayers(self):
+        return lib.ngst_slab_nlayers(self._h)
+
+    def GetSlabHeight(self):
+        return lib.ngst_slab_height(self._h)
+
+    def MaxSlope(self):
+        return lib.ngst_slab_max_slope(self._h)
+
+    def export(self):
+        """Flattened tents as a dict of numpy arrays (CSR offsets *_off)."""
+        if self._export is None:
+            nt = self.GetNTents()
+            sz = np.zeros(4, dtype=np.int64)
+            check(lib.ngst_slab_sizes(self._h, sz.ctypes.data_as(_capi.c_llp)))
+            e = dict(vertex=np.zeros(nt, np.int32), level=np.zeros(nt, np.int32), tbot=np.zeros(nt), ttop=np.zeros(nt),
+                     maxslope=np.zeros(nt), nb_off=np.zeros(nt + 1, np.int32), nbv=np.zeros(sz[0], np.int32),
+                     nbtime=np.zeros(sz[0]), el_off=np.zeros(nt + 1, np.int32), els=np.zeros(sz[1], np.int32),
+                     facet_off=np.zeros(nt + 1, np.int32), facets=np.zeros(sz[2], np.int32),
+                     dag_off=np.zeros(nt + 1, np.int32), dag=np.zeros(sz[3], np.int32))
+            check(lib.ngst_slab_export(self._h, iptr(e["vertex"]), iptr(e["level"]), dptr(e["tbot"]), dptr(e["ttop"]),
+                                       dptr(e["maxslope"]), iptr(e["nb_off"]), iptr(e["nbv"]), dptr(e["nbtime"]),
+                                       iptr(e["el_off"]), iptr(e["els"]), iptr(e["facet_off"]), iptr(e["facets"]),
+                                       iptr(e["dag_off"]), iptr(e["dag"])))
+            nl = C.c_int(0)
+            check(lib.ngst_slab_levels(self._h, C.byref(nl), None, None))
+            e["level_off"] = np.zeros(nl.value + 1, np.int32)
+            e["level_tents"] = np.zeros(nt, np.int32)
+            check(lib.ngst_slab_levels(self._h, C.byref(nl), iptr(e["level_off"]), iptr(e["level_tents"])))
+            self._export = e
+        return self._export
+
+    def GetTent(self, i):
+        e = self.export()
+        if not 0 <= i < len(e["vertex"]):
+            raise IndexError("tent index out of range")
+        nb = slice(e["nb_off"][i], e["nb_off"][i + 1])
+        el = slice(e["el_off"][i], e["el_off"][i + 1])
+        fc = slice(e["facet_off"][i], e["facet_off"][i + 1])
+        return Tent(e["vertex"][i], e["ttop"][i], e["tbot"][i], e["nbv"][nb].tolist(), e["nbtime"][nb].tolist(),
+                    e["els"][el].tolist(), e["level"][i], e["facets"][fc].tolist(), e["maxslope"][i])
+
+    def TentData1D(self):
+        """python_tents.cpp:87-101"""
+        ret = []
+        for i in range(self.GetNTents()):
+            t = self.GetTent(i)
+            ret.append([(t.vertex, t.ttop, t.tbot, t.level)] + list(zip(t.nbv, t.nbtime)))
+        return ret
+
+
+class TrefftzTents:
+    """Base class (src/twavetents.hpp:78-93)."""
+
+    def Propagate(self):
+        raise RuntimeError("TrefftzTents virtual!")
+
+    def SetInitial(self, init):
+        raise RuntimeError("TrefftzTents virtual!")
+
+    def SetBoundaryCF(self, bddatum):
+        raise RuntimeError("TrefftzTents virtual!")
+
+
+class TWaveTents(TrefftzTents):
+    """TWaveTents<D> (src/twavetents.hpp:95-224), state resident on one B200."""
+
+    def __init__(self, order, tps, wavespeedcf, device=0):
+        self.tps = tps
+        self.mesh = tps.mesh
+        self.order = int(order)
+        mesh = self.mesh
+        c_vertex = None
+        if callable(wavespeedcf):
+            c_el = f64(wavespeedcf(mesh.centroids())).reshape(-1)
+            c_vertex = f64(wavespeedcf(mesh.points)).reshape(-1)
+        else:
+            c = f64(np.atleast_1d(wavespeedcf)).reshape(-1)
+            c_el = np.full(mesh.ne, c[0]) if len(c) == 1 else c
+        if len(c_el) != mesh.ne:
+            raise ValueError("wavespeed: need a scalar, one value per element, or a callable")
+        self.c_el = c_el
+        self._h = C.c_void_p()
+        check(lib.ngst_twave_create(tps._h, self.order, dptr(c_el), dptr(c_vertex), int(device), C.byref(self._h)))
+        self._bddatum = None
+        self._bnd_pts = None
+        self._quad = None
+        self._refresh()
+
+    def _refresh(self):
+        info = np.zeros(8, dtype=np.int32)
+        check(lib.ngst_twave_info(self._h, iptr(info)))
+        self.D, _, self.nbasis, self.nip, self.ncomp, self.fosystem, self.nel, self.ntents = (int(x) for x in info)
+
+    def __del__(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib.ngst_twave_destroy(self._h)
+            self._h = C.c_void_p()
+
+    # ---- sampling helpers
+    def quadrature(self):
+        """(x[nel,nip,D], weight[nel,nip]) mapped points and |detJ|*w weights."""
+        if self._quad is None:
+            x = np.zeros((self.nel, self.nip, self.D))
+            w = np.zeros((self.nel, self.nip))
+            check(lib.ngst_twave_quadrature(self._h, dptr(x), dptr(w)))
+            self._quad = (x, w)
+        return self._quad
+
+    def MakeWavefront(self, cf, time=0.0):
+        """src/twavetents.cpp:734-764: sample cf at all element quadrature points at a fixed time."""
+        if not callable(cf):
+            wf = f64(cf)
+            if wf.ndim != 2 or wf.shape[0] != self.nel or wf.shape[1] % self.nip:
+                raise ValueError("wavefront array must be nel x (ncomp*nip)")
+            return wf
+        x, _ = self.quadrature()
+        vals = f64(cf(x.reshape(-1, self.D), float(time)))
+        if vals.ndim == 1:
+            vals = vals.reshape(-1, 1)
+        ncomp = vals.shape[1]
+        return np.ascontiguousarray(vals.reshape(self.nel, self.nip, ncomp).transpose(0, 2, 1)).reshape(
+            self.nel, ncomp * self.nip)
+
+    # ---- TrefftzTents interface
+    def SetInitial(self, init):
+        wf = self.MakeWavefront(init, 0.0)
+        ncomp = wf.shape[1] // self.nip
+        check(lib.ngst_twave_set_initial(self._h, dptr(wf), ncomp))
+        self._refresh()
+
+    def SetBoundaryCF(self, bddatum):
+        self._bddatum = bddatum
+
+    def _boundary_values(self):
+        npts = lib.ngst_twave_boundary_npoints(self._h)
+        if self._bddatum is None or npts == 0:
+            return None
+        if self._bnd_pts is None:
+            xt = np.zeros((npts, self.D + 1))
+            kind = np.zeros(npts, dtype=np.int32)
+            check(lib.ngst_twave_boundary_points(self._h, dptr(xt), iptr(kind)))
+            self._bnd_pts = (xt, kind)
+        xt, kind = self._bnd_pts
+        t = xt[:, self.D] + lib.ngst_twave_timeshift(self._h)
+        x = np.ascontiguousarray(xt[:, :self.D])
+        cf = self._bddatum
+        Q, D = self.nip, self.D
+        fk = kind.reshape(-1, Q)[:, 0]  # kind per boundary face
+        out = []
+        if isinstance(cf, dict):
+            vd = f64(cf["dirichlet"](x, t)).reshape(npts, -1)[:, 0] if (fk == 0).any() else None
+            vn = f64(cf["neumann"](x, t)).reshape(npts, D) if (fk == 1).any() else None
+        else:
+            v = f64(cf(x, t)).reshape(npts, -1)
+            vd = v[:, 0]
+            vn = v if v.shape[1] == D else None
+        if (fk == 0).all():
+            return np.ascontiguousarray(vd)
+        if (fk == 1).all():
+            if vn is None:
+                raise ValueError("Neumann boundary needs a D-vector datum")
+            return np.ascontiguousarray(vn.reshape(-1, Q, D).transpose(0, 2, 1)).reshape(-1)
+        for f, k in enumerate(fk):
+            sl = slice(f * Q, (f + 1) * Q)
+            out.append(vd[sl] if k == 0 else vn[sl].T.reshape(-1))
+        return np.ascontiguousarray(np.concatenate(out))
+
+    def Propagate(self):
+        vals = self._boundary_values()
+        n = 0 if vals is None else len(vals)
+        check(lib.ngst_twave_set_boundary_values(self._h, dptr(vals), n))
+        check(lib.ngst_twave_propagate(self._h))
+
+    # ---- DeclareETClass methods (src/twavetents.cpp:1160-1178)
+    def GetWavefront(self):
+        wf = np.zeros((self.nel, self.ncomp * self.nip))
+        check(lib.ngst_twave_get_wavefront(self._h, dptr(wf)))
+        return wf
+
+    def Error(self, wavefront, wavefront_corr):
+        out = C.c_double(0)
+        check(lib.ngst_twave_error(self._h, dptr(f64(wavefront)), dptr(f64(wavefront_corr)), C.byref(out)))
+        return out.value
+
+    def L2Error(self, wavefront, wavefront_corr):
+        out = C.c_double(0)
+        check(lib.ngst_twave_l2error(self._h, dptr(f64(wavefront)), dptr(f64(wavefront_corr)), C.byref(out)))
+        return out.value
+
+    def Energy(self, wavefront=None):
+        out = C.c_double(0)
+        wf = None if wavefront is None else f64(wavefront)
+        check(lib.ngst_twave_energy(self._h, dptr(wf), C.byref(out)))
+        return out.value
+
+    def MaxAdiam(self):
+        out = C.c_double(0)
+        check(lib.ngst_twave_max_adiam(self._h, C.byref(out)))
+        return out.value
+
+    def LocalDofs(self):
+        return self.nbasis
+
+    def GetOrder(self):
+        return self.order
+
+    def GetSpaceDim(self):
+        return self.D
+
+    def GetInitmesh(self):
+        return self.mesh
+
+    def timeshift(self):
+        return lib.ngst_twave_timeshift(self._h)
+
+    def last_ms(self):
+        return lib.ngst_twave_last_ms(self._h)
+
+    def last_launches(self):
+        return lib.ngst_twave_last_launches(self._h)
+
+
+def TWave(order, tps, wavespeedcf, BBcf=None, device=0):
+    """Factory of src/twavetents.cpp:1194-1228."""
+    if BBcf is not None:
+        raise NotImplementedError("quasi-Trefftz (QTWaveTents, BBcf given) is not built yet: see DESIGN.md")
+    return TWaveTents(order, tps, wavespeedcf, device=device)

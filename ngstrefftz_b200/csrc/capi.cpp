@@ -1,0 +1,311 @@
+// extern "C" boundary of libngst_b200.so (declarations and reference citations: include/ngst_b200.h).
+#include "../../include/ngst_b200.h"
+
+#include <algorithm>
+#include <cstring>
+#include <memory>
+#include <stdexcept>
+#include <string>
+
+#include "cuda/solver.hpp"
+#include "host/basis.hpp"
+#include "host/mesh.hpp"
+#include "host/pitcher.hpp"
+#include "host/quadrature.hpp"
+#include "host/stage.hpp"
+
+using namespace ngst;
+
+struct ngst_mesh { SimplexMesh m; };
+struct ngst_slab { const ngst_mesh* mesh; TentSlab s; };
+struct ngst_twave { const ngst_slab* slab; std::unique_ptr<Solver> solver; };
+
+namespace {
+thread_local std::string g_err;
+
+template <typename F>
+int guarded(F f) {
+  try {
+    f();
+    return NGST_OK;
+  } catch (const std::invalid_argument& e) {
+    g_err = e.what();
+    return NGST_ERR_ARG;
+  } catch (const std::domain_error& e) {
+    g_err = e.what();
+    return NGST_ERR_NUMERIC;
+  } catch (const std::logic_error& e) {
+    g_err = e.what();
+    return NGST_ERR_STATE;
+  } catch (const std::exception& e) {
+    g_err = e.what();
+    return g_err.rfind("CUDA:", 0) == 0 ? NGST_ERR_CUDA : NGST_ERR_ARG;
+  } catch (...) {
+    g_err = "unknown error";
+    return NGST_ERR_ARG;
+  }
+}
+template <typename T>
+void copy_out(T* dst, const std::vector<T>& src) {
+  if (dst && !src.empty()) std::memcpy(dst, src.data(), src.size() * sizeof(T));
+}
+void need(const void* p, const char* what) {
+  if (!p) throw std::invalid_argument(std::string("null argument: ") + what);
+}
+}  // namespace
+
+extern "C" {
+
+const char* ngst_last_error(void) { return g_err.c_str(); }
+const char* ngst_version(void) { return "ngst_b200 0.1 (sm_100a)"; }
+
+int ngst_mesh_create(int D, int nv, const double* pts, int nel, const int* el2v, int nbnd, const int* bnd2v,
+                     const int* bnd_kind, ngst_mesh** out) {
+  return guarded([&] {
+    need(out, "out");
+    if (D < 1 || D > 3 || nv < 2 || nel < 1 || nbnd < 0) throw std::invalid_argument("ngst_mesh_create: bad sizes");
+    need(pts, "pts");
+    need(el2v, "el2v");
+    if (nbnd) need(bnd2v, "bnd2v");
+    auto h = std::make_unique<ngst_mesh>();
+    SimplexMesh& m = h->m;
+    m.D = D; m.nv = nv; m.nel = nel; m.nse = nbnd;
+    m.pts.assign(pts, pts + (size_t)nv * D);
+    m.el2v.assign(el2v, el2v + (size_t)nel * (D + 1));
+    if (nbnd) m.se2v.assign(bnd2v, bnd2v + (size_t)nbnd * D);
+    if (bnd_kind) m.se_kind.assign(bnd_kind, bnd_kind + nbnd);
+    else m.se_kind.assign(nbnd, 0);
+    try { m.finalize(); } catch (const std::runtime_error& e) { throw std::invalid_argument(e.what()); }
+    *out = h.release();
+  });
+}
+
+int ngst_mesh_structured(int D, const int* ncells, const double* lo, const double* hi, ngst_mesh** out) {
+  return guarded([&] {
+    need(out, "out"); need(ncells, "ncells"); need(lo, "lo"); need(hi, "hi");
+    auto h = std::make_unique<ngst_mesh>();
+    try { h->m = make_structured(D, ncells, lo, hi); } catch (const std::runtime_error& e) { throw std::invalid_argument(e.what()); }
+    *out = h.release();
+  });
+}
+
+int ngst_mesh_set_boundary_kind(ngst_mesh* m, const int* bnd_kind) {
+  return guarded([&] {
+    need(m, "mesh"); need(bnd_kind, "bnd_kind");
+    m->m.se_kind.assign(bnd_kind, bnd_kind + m->m.nse);
+  });
+}
+
+int ngst_mesh_counts(const ngst_mesh* m, int* counts) {
+  return guarded([&] {
+    need(m, "mesh"); need(counts, "counts");
+    const SimplexMesh& s = m->m;
+    int c[8] = {s.D, s.nv, s.nel, s.nse, s.nedges, s.nfacets, 0, 0};
+    std::memcpy(counts, c, sizeof(c));
+  });
+}
+
+int ngst_mesh_tables(const ngst_mesh* m, double* pts, int* el2v, int* bnd2v, int* bnd_kind, int* edge2v,
+                     int* facet2v, int* el2facet, int* facet2el, int* facet2bnd, int* el2edge) {
+  return guarded([&] {
+    need(m, "mesh");
+    const SimplexMesh& s = m->m;
+    copy_out(pts, s.pts); copy_out(el2v, s.el2v); copy_out(bnd2v, s.se2v); copy_out(bnd_kind, s.se_kind);
+    copy_out(edge2v, s.edge2v); copy_out(facet2v, s.facet2v); copy_out(el2facet, s.el2facet);
+    copy_out(facet2el, s.facet2el); copy_out(facet2bnd, s.facet2se); copy_out(el2edge, s.el2edge);
+  });
+}
+
+void ngst_mesh_destroy(ngst_mesh* m) { delete m; }
+
+int ngst_slab_create(const ngst_mesh* m, int method, ngst_slab** out) {
+  return guarded([&] {
+    need(m, "mesh"); need(out, "out");
+    if (method != kEdgeGrad && method != kVolGrad) throw std::invalid_argument("ngst_slab_create: method must be 1 (vol) or 2 (edge)");
+    auto h = std::make_unique<ngst_slab>();
+    h->mesh = m;
+    h->s.mesh = &m->m;
+    h->s.method = method;
+    *out = h.release();
+  });
+}
+
+int ngst_slab_set_max_wavespeed(ngst_slab* s, const double* c, int n) {
+  return guarded([&] {
+    need(s, "slab"); need(c, "c");
+    const int nel = s->s.mesh->nel;
+    if (n == 1) s->s.cmax_el.assign(nel, c[0]);
+    else if (n == nel) s->s.cmax_el.assign(c, c + nel);
+    else throw std::invalid_argument("SetMaxWavespeed: need 1 or nel values");
+    for (double v : s->s.cmax_el)
+      if (!(v > 0)) throw std::invalid_argument("SetMaxWavespeed: wavespeed must be positive");
+  });
+}
+
+int ngst_slab_pitch(ngst_slab* s, double dt, int local_ct, double global_ct, int* ok) {
+  return guarded([&] {
+    need(s, "slab");
+    if (!(dt > 0)) throw std::invalid_argument("PitchTents: dt must be positive");
+    bool r = s->s.PitchTents(dt, local_ct != 0, global_ct);
+    if (ok) *ok = r ? 1 : 0;
+  });
+}
+
+int ngst_slab_ntents(const ngst_slab* s) { return s ? s->s.ntents : 0; }
+int ngst_slab_nlayers(const ngst_slab* s) { return s ? s->s.GetNLayers() : 0; }
+double ngst_slab_height(const ngst_slab* s) { return s ? s->s.dt : 0.0; }
+double ngst_slab_max_slope(const ngst_slab* s) { return s ? s->s.MaxSlope() : 0.0; }
+
+int ngst_slab_sizes(const ngst_slab* s, long long* sizes) {
+  return guarded([&] {
+    need(s, "slab"); need(sizes, "sizes");
+    sizes[0] = (long long)s->s.nbv.val.size();
+    sizes[1] = (long long)s->s.els.val.size();
+    sizes[2] = (long long)s->s.facets.val.size();
+    sizes[3] = (long long)s->s.dag.val.size();
+  });
+}
+
+int ngst_slab_export(const ngst_slab* s, int* vertex, int* level, double* tbot, double* ttop, double* maxslope,
+                     int* nb_off, int* nbv, double* nbtime, int* el_off, int* els, int* facet_off, int* facets,
+                     int* dag_off, int* dag) {
+  return guarded([&] {
+    need(s, "slab");
+    const TentSlab& t = s->s;
+    copy_out(vertex, t.vertex); copy_out(level, t.level); copy_out(tbot, t.tbot); copy_out(ttop, t.ttop);
+    copy_out(maxslope, t.maxslope);
+    copy_out(nb_off, t.nbv.off); copy_out(nbv, t.nbv.val); copy_out(nbtime, t.nbtime);
+    copy_out(el_off, t.els.off); copy_out(els, t.els.val);
+    copy_out(facet_off, t.facets.off); copy_out(facets, t.facets.val);
+    copy_out(dag_off, t.dag.off); copy_out(dag, t.dag.val);
+  });
+}
+
+int ngst_slab_levels(const ngst_slab* s, int* nlevels, int* level_off, int* level_tents) {
+  return guarded([&] {
+    need(s, "slab");
+    if (nlevels) *nlevels = (int)s->s.level_off.size() - 1;
+    copy_out(level_off, s->s.level_off);
+    copy_out(level_tents, s->s.level_tents);
+  });
+}
+
+void ngst_slab_destroy(ngst_slab* s) { delete s; }
+
+int ngst_twave_create(const ngst_slab* s, int order, const double* c_el, const double* c_vertex, int device,
+                      ngst_twave** out) {
+  return guarded([&] {
+    need(s, "slab"); need(out, "out"); need(c_el, "c_el");
+    const SimplexMesh& m = *s->s.mesh;
+    std::vector<double> ce(c_el, c_el + m.nel), cv;
+    if (c_vertex) cv.assign(c_vertex, c_vertex + m.nv);
+    auto h = std::make_unique<ngst_twave>();
+    h->slab = s;
+    h->solver = std::make_unique<Solver>(s->s, order, ce, cv, device);
+    *out = h.release();
+  });
+}
+
+int ngst_twave_info(const ngst_twave* t, int* info) {
+  return guarded([&] {
+    need(t, "solver"); need(info, "info");
+    const Solver& s = *t->solver;
+    int v[8] = {s.D(), s.order(), s.nbasis(), s.nip(), s.ncomp(), s.fosystem(), s.nel(), s.ntents()};
+    std::memcpy(info, v, sizeof(v));
+  });
+}
+
+int ngst_twave_quadrature(const ngst_twave* t, double* x, double* weight) {
+  return guarded([&] { need(t, "solver"); t->solver->Quadrature(x, weight); });
+}
+
+int ngst_twave_set_initial(ngst_twave* t, const double* wf, int ncomp) {
+  return guarded([&] { need(t, "solver"); need(wf, "wf"); t->solver->SetInitial(wf, ncomp); });
+}
+
+long long ngst_twave_boundary_npoints(const ngst_twave* t) { return t ? t->solver->staged().nbnd_points : 0; }
+long long ngst_twave_boundary_nvalues(const ngst_twave* t) { return t ? t->solver->staged().nbnd_values : 0; }
+
+int ngst_twave_boundary_points(const ngst_twave* t, double* xt, int* kind_per_point) {
+  return guarded([&] {
+    need(t, "solver");
+    const StagedTents& st = t->solver->staged();
+    if (xt) boundary_sample_points(st, t->solver->rule(), xt);
+    if (kind_per_point) {
+      const int Q = t->solver->nip();
+      for (int tf = 0; tf < st.ntf; tf++)
+        if (st.tf_point[tf] >= 0)
+          for (int q = 0; q < Q; q++) kind_per_point[st.tf_point[tf] + q] = st.tf_kind[tf];
+    }
+  });
+}
+
+int ngst_twave_set_boundary_values(ngst_twave* t, const double* values, long long n) {
+  return guarded([&] { need(t, "solver"); t->solver->SetBoundaryValues(values, n); });
+}
+
+int ngst_twave_propagate(ngst_twave* t) {
+  return guarded([&] { need(t, "solver"); t->solver->Propagate(); });
+}
+
+double ngst_twave_timeshift(const ngst_twave* t) { return t ? t->solver->timeshift() : 0.0; }
+double ngst_twave_last_ms(const ngst_twave* t) { return t ? t->solver->last_ms() : 0.0; }
+int ngst_twave_last_launches(const ngst_twave* t) { return t ? t->solver->last_launches() : 0; }
+
+int ngst_twave_get_wavefront(ngst_twave* t, double* out) {
+  return guarded([&] { need(t, "solver"); need(out, "out"); t->solver->GetWavefront(out); });
+}
+
+int ngst_twave_energy(ngst_twave* t, const double* wf, double* out) {
+  return guarded([&] { need(t, "solver"); need(out, "out"); *out = t->solver->Energy(wf); });
+}
+
+int ngst_twave_error(ngst_twave* t, const double* wf, const double* wf_ref, double* out) {
+  return guarded([&] {
+    need(t, "solver"); need(wf, "wf"); need(wf_ref, "wf_ref"); need(out, "out");
+    *out = t->solver->Error(wf, wf_ref, false);
+  });
+}
+
+int ngst_twave_l2error(ngst_twave* t, const double* wf, const double* wf_ref, double* out) {
+  return guarded([&] {
+    need(t, "solver"); need(wf, "wf"); need(wf_ref, "wf_ref"); need(out, "out");
+    *out = t->solver->Error(wf, wf_ref, true);
+  });
+}
+
+int ngst_twave_max_adiam(const ngst_twave* t, double* out) {
+  return guarded([&] { need(t, "solver"); need(out, "out"); *out = t->solver->MaxAdiam(); });
+}
+
+int ngst_twave_basis(const ngst_twave* t, int* sizes, int* rowptr, int* col, double* val) {
+  return guarded([&] {
+    need(t, "solver");
+    const BasisCsr& b = t->solver->basis();
+    if (sizes) { sizes[0] = b.nbasis; sizes[1] = b.npoly; sizes[2] = (int)b.val.size(); }
+    copy_out(rowptr, b.rowptr); copy_out(col, b.col); copy_out(val, b.val);
+  });
+}
+
+void ngst_twave_destroy(ngst_twave* t) { delete t; }
+
+int ngst_basis(int D, int order, int fowave, int* sizes, int* rowptr, int* col, double* val, int* expo) {
+  return guarded([&] {
+    if (D < 1 || D > 3) throw std::invalid_argument("ngst_basis: D must be 1..3");
+    BasisCsr b;
+    try { b = twave_basis(D + 1, order, fowave); } catch (const std::runtime_error& e) { throw std::invalid_argument(e.what()); }
+    if (sizes) { sizes[0] = b.nbasis; sizes[1] = b.npoly; sizes[2] = (int)b.val.size(); }
+    copy_out(rowptr, b.rowptr); copy_out(col, b.col); copy_out(val, b.val); copy_out(expo, b.expo);
+  });
+}
+
+int ngst_rule(int dim, int order, int* nip, double* xi, double* w) {
+  return guarded([&] {
+    SimplexRule r;
+    try { r = make_simplex_rule(dim, order); } catch (const std::runtime_error& e) { throw std::invalid_argument(e.what()); }
+    if (nip) *nip = r.nip;
+    copy_out(xi, r.xi); copy_out(w, r.w);
+  });
+}
+
+}  // extern "C"

@@ -1,0 +1,289 @@
+#include "solver.hpp"
+
+#include <algorithm>
+#include <cmath>
+#include <stdexcept>
+
+namespace ngst {
+
+namespace {
+struct CudaFailure : std::runtime_error {
+  using std::runtime_error::runtime_error;
+};
+inline void cuda_check(cudaError_t e, const char* what) {
+  if (e != cudaSuccess) throw CudaFailure(std::string("CUDA: ") + what + ": " + cudaGetErrorString(e));
+}
+#define CU(x) cuda_check((x), #x)
+}  // namespace
+
+template <typename T>
+T* Solver::Upload(const std::vector<T>& v) {
+  T* d = nullptr;
+  const size_t bytes = std::max<size_t>(v.size(), 1) * sizeof(T);
+  CU(cudaMalloc(&d, bytes));
+  allocs_.push_back(d);
+  if (!v.empty()) CU(cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return d;
+}
+
+Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el, const std::vector<double>& c_vertex,
+               int device)
+    : mesh_(*slab.mesh), slab_(slab), order_(order), device_(device), c_el_(c_el), c_vertex_(c_vertex) {
+  if (order < 1 || order > 12) throw std::invalid_argument("TWave: order must be in 1..12");
+  if (slab.ntents == 0) throw std::logic_error("TWave: the slab has no tents (call PitchTents first)");
+  if ((int)c_el_.size() != mesh_.nel) throw std::invalid_argument("TWave: need one wavespeed per element");
+  for (double c : c_el_)
+    if (!(c > 0)) throw std::invalid_argument("TWave: wavespeed must be positive");
+  if (c_vertex_.empty()) {
+    c_vertex_.resize(mesh_.nv);
+    for (int v = 0; v < mesh_.nv; v++) c_vertex_[v] = c_el_[mesh_.v2el.row(v)[0]];
+  }
+  const int D = mesh_.D, d1 = D + 1;
+
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    throw CudaFailure(std::string("CUDA: no usable device (") + cudaGetErrorString(e) +
+                      "); this library has no CPU fallback");
+  if (device < 0 || device >= ndev) throw CudaFailure("CUDA: device ordinal out of range");
+  CU(cudaSetDevice(device));
+  CU(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+  CU(cudaEventCreate(&ev0_));
+  CU(cudaEventCreate(&ev1_));
+
+  rule_ = make_simplex_rule(D, 2 * order);
+  basis_so_ = twave_basis(d1, order, 0);
+  basis_fo_ = twave_basis(d1, order, 1);
+  basis_ = basis_so_;
+  staged_ = stage_tents(mesh_, slab_, c_el_, c_vertex_, rule_);
+
+  const int Q = rule_.nip;
+  std::vector<double> lam((size_t)Q * d1);
+  for (int q = 0; q < Q; q++) {
+    double s = 0;
+    for (int d = 0; d < D; d++) { lam[(size_t)q * d1 + d] = rule_.xi[(size_t)q * D + d]; s += rule_.xi[(size_t)q * D + d]; }
+    lam[(size_t)q * d1 + D] = 1.0 - s;
+  }
+
+  TentKernelArgs& a = args_;
+  a.pts = Upload(mesh_.pts);
+  a.el2v = Upload(mesh_.el2v);
+  a.c_el = Upload(c_el_);
+  a.lam = Upload(lam);
+  a.w = Upload(rule_.w);
+  a.expo = Upload(basis_so_.expo);
+  for (int f = 0; f < 2; f++) {
+    const BasisCsr& b = f ? basis_fo_ : basis_so_;
+    d_rowptr_[f] = Upload(b.rowptr);
+    d_col_[f] = Upload(b.col);
+    d_val_[f] = Upload(b.val);
+  }
+  a.npoly = basis_so_.npoly;
+  a.order = order;
+  a.Q = Q;
+  a.center = Upload(staged_.center);
+  a.scale = Upload(staged_.scale);
+  a.ndom = Upload(staged_.ndom);
+  a.te_off = Upload(staged_.te_off);
+  a.tf_off = Upload(staged_.tf_off);
+  a.te_el = Upload(staged_.te_el);
+  a.te_dom = Upload(staged_.te_dom);
+  a.te_tbot = Upload(staged_.te_tbot);
+  a.te_ttop = Upload(staged_.te_ttop);
+  a.te_geo = Upload(staged_.te_geo);
+  a.tf_kind = Upload(staged_.tf_kind);
+  a.tf_dom = Upload(staged_.tf_dom);
+  a.tf_c = Upload(staged_.tf_c);
+  a.tf_verts = Upload(staged_.tf_verts);
+  a.tf_n = Upload(staged_.tf_n);
+  a.tf_area = Upload(staged_.tf_area);
+  a.tf_data = Upload(staged_.tf_data);
+  a.bnd_data = nullptr;
+  a.max_ndom = staged_.max_ndom;
+  d_level_tents_ = Upload(slab_.level_tents);
+  CU(cudaMalloc(&d_singular_, sizeof(int)));
+  allocs_.push_back(d_singular_);
+  CU(cudaMemset(d_singular_, 0, sizeof(int)));
+  a.singular = d_singular_;
+
+  // element quadrature weights |detJ| * w (GetWeight, twavetents.cpp:793,818,843)
+  {
+    std::vector<double> elw((size_t)mesh_.nel * Q);
+    Quadrature(nullptr, elw.data());
+    d_elw_ = Upload(elw);
+  }
+  CU(cudaMalloc(&d_scratch_, sizeof(double) * std::max(mesh_.nel, 1)));
+  allocs_.push_back(d_scratch_);
+}
+
+Solver::~Solver() {
+  cudaSetDevice(device_);
+  if (stream_) cudaStreamSynchronize(stream_);
+  for (void* p : allocs_) cudaFree(p);
+  if (d_wavefront_) cudaFree(d_wavefront_);
+  if (d_bnd_) cudaFree(d_bnd_);
+  if (d_tmp_a_) cudaFree(d_tmp_a_);
+  if (d_tmp_b_) cudaFree(d_tmp_b_);
+  if (ev0_) cudaEventDestroy(ev0_);
+  if (ev1_) cudaEventDestroy(ev1_);
+  if (stream_) cudaStreamDestroy(stream_);
+}
+
+void Solver::Quadrature(double* x, double* weight) const {
+  const int D = mesh_.D, d1 = D + 1, Q = rule_.nip;
+#pragma omp parallel for schedule(static)
+  for (int el = 0; el < mesh_.nel; el++) {
+    const int* ev = mesh_.elverts(el);
+    double J[9];
+    for (int i = 0; i < D; i++)
+      for (int d = 0; d < D; d++) J[d * D + i] = mesh_.point(ev[i])[d] - mesh_.point(ev[D])[d];
+    double det;
+    if (D == 1) det = J[0];
+    else if (D == 2) det = J[0] * J[3] - J[1] * J[2];
+    else det = J[0] * (J[4] * J[8] - J[5] * J[7]) - J[1] * (J[3] * J[8] - J[5] * J[6]) + J[2] * (J[3] * J[7] - J[4] * J[6]);
+    det = std::fabs(det);
+    for (int q = 0; q < Q; q++) {
+      if (weight) weight[(size_t)el * Q + q] = det * rule_.w[q];
+      if (x) {
+        double lam[4], s = 0;
+        for (int d = 0; d < D; d++) { lam[d] = rule_.xi[(size_t)q * D + d]; s += lam[d]; }
+        lam[D] = 1.0 - s;
+        for (int d = 0; d < D; d++) {
+          double v = 0;
+          for (int k = 0; k < d1; k++) v += lam[k] * mesh_.point(ev[k])[d];
+          x[((size_t)el * Q + q) * D + d] = v;
+        }
+      }
+    }
+  }
+}
+
+void Solver::SetInitial(const double* wf, int ncomp) {
+  const int D = mesh_.D;
+  if (ncomp != D + 2 && ncomp != D + 1)
+    throw std::invalid_argument("SetInitial: initial data must have D+2 (second order) or D+1 (first order) components");
+  CU(cudaSetDevice(device_));
+  fosystem_ = (ncomp == D + 1) ? 1 : 0;  // twavetents.hpp:198-203
+  ncomp_ = ncomp;
+  basis_ = fosystem_ ? basis_fo_ : basis_so_;
+  const size_t bytes = (size_t)mesh_.nel * ncomp * rule_.nip * sizeof(double);
+  if (d_wavefront_) { CU(cudaFree(d_wavefront_)); d_wavefront_ = nullptr; }
+  CU(cudaMalloc(&d_wavefront_, bytes));
+  CU(cudaMemcpyAsync(d_wavefront_, wf, bytes, cudaMemcpyHostToDevice, stream_));
+  CU(cudaStreamSynchronize(stream_));
+  have_initial_ = true;
+
+  TentKernelArgs& a = args_;
+  a.rowptr = d_rowptr_[fosystem_];
+  a.col = d_col_[fosystem_];
+  a.val = d_val_[fosystem_];
+  a.N = basis_.nbasis;
+  a.Npad = (a.N + 3) / 4 * 4;
+  a.ncomp = ncomp_;
+  a.fosystem = fosystem_;
+  a.wavefront = d_wavefront_;
+  // chunk of quadrature points staged in shared memory at a time
+  const size_t budget = 100 * 1024;
+  int qc = std::min(rule_.nip, 32);
+  for (; qc > 1; qc--) {
+    a.Qc = qc;
+    if (tent_generic_smem_bytes(D, a) <= budget) break;
+  }
+  a.Qc = qc;
+  smem_ = tent_generic_smem_bytes(D, a);
+  if (smem_ > 227 * 1024)
+    throw std::invalid_argument("TWave: local system too large for shared memory (order / number of wavespeed regions per tent)");
+  const int tiles = (a.Npad / 4) * (a.Npad / 4);
+  threads_ = tiles > 128 ? 256 : (tiles > 32 ? 128 : 64);
+}
+
+void Solver::SetBoundaryValues(const double* values, long long n) {
+  CU(cudaSetDevice(device_));
+  if (values == nullptr) { args_.bnd_data = nullptr; return; }
+  if (n != staged_.nbnd_values) throw std::invalid_argument("SetBoundaryValues: wrong number of values");
+  if (n == 0) { args_.bnd_data = nullptr; return; }
+  if (!d_bnd_) CU(cudaMalloc(&d_bnd_, sizeof(double) * n));
+  CU(cudaMemcpyAsync(d_bnd_, values, sizeof(double) * n, cudaMemcpyHostToDevice, stream_));
+  CU(cudaStreamSynchronize(stream_));
+  args_.bnd_data = d_bnd_;
+}
+
+void Solver::Propagate() {
+  if (!have_initial_) throw std::logic_error("Propagate: SetInitial has not been called");
+  CU(cudaSetDevice(device_));
+  const int nlev = (int)slab_.level_off.size() - 1;
+  int launches = 0;
+  CU(cudaEventRecord(ev0_, stream_));
+  for (int l = 0; l < nlev; l++) {
+    TentKernelArgs a = args_;
+    a.tents = d_level_tents_ + slab_.level_off[l];
+    a.ntents = slab_.level_off[l + 1] - slab_.level_off[l];
+    if (a.ntents == 0) continue;
+    CU(launch_tent_generic(mesh_.D, a, threads_, smem_, stream_));
+    launches++;
+  }
+  CU(cudaEventRecord(ev1_, stream_));
+  CU(cudaEventSynchronize(ev1_));
+  float ms = 0;
+  CU(cudaEventElapsedTime(&ms, ev0_, ev1_));
+  last_ms_ = ms;
+  last_launches_ = launches;
+  timeshift_ += slab_.dt;  // twavetents.cpp:173
+  int sing = 0;
+  CU(cudaMemcpy(&sing, d_singular_, sizeof(int), cudaMemcpyDeviceToHost));
+  if (sing) {
+    CU(cudaMemset(d_singular_, 0, sizeof(int)));
+    throw std::domain_error("Propagate: singular local system in " + std::to_string(sing) + " pivot step(s)");
+  }
+}
+
+void Solver::GetWavefront(double* out) {
+  if (!have_initial_) throw std::logic_error("GetWavefront: SetInitial has not been called");
+  CU(cudaSetDevice(device_));
+  const size_t bytes = (size_t)mesh_.nel * ncomp_ * rule_.nip * sizeof(double);
+  CU(cudaMemcpyAsync(out, d_wavefront_, bytes, cudaMemcpyDeviceToHost, stream_));
+  CU(cudaStreamSynchronize(stream_));
+}
+
+double Solver::ReduceElements(const double* a, const double* b, int mode) {
+  CU(launch_element_reduce(mode, mesh_.D, mesh_.nel, rule_.nip, ncomp_, fosystem_, d_elw_, args_.c_el, a, b,
+                           d_scratch_, stream_));
+  std::vector<double> part(mesh_.nel);
+  CU(cudaMemcpyAsync(part.data(), d_scratch_, sizeof(double) * mesh_.nel, cudaMemcpyDeviceToHost, stream_));
+  CU(cudaStreamSynchronize(stream_));
+  double s = 0;
+  for (double v : part) s += v;  // fixed element order: deterministic
+  return s;
+}
+
+double Solver::Energy(const double* wf) {
+  if (!have_initial_) throw std::logic_error("Energy: SetInitial has not been called");
+  CU(cudaSetDevice(device_));
+  const size_t bytes = (size_t)mesh_.nel * ncomp_ * rule_.nip * sizeof(double);
+  const double* src = d_wavefront_;
+  if (wf) {
+    if (!d_tmp_a_) CU(cudaMalloc(&d_tmp_a_, bytes));
+    CU(cudaMemcpyAsync(d_tmp_a_, wf, bytes, cudaMemcpyHostToDevice, stream_));
+    src = d_tmp_a_;
+  }
+  return ReduceElements(src, nullptr, 0);
+}
+
+double Solver::Error(const double* wf, const double* ref, bool l2only) {
+  if (!have_initial_) throw std::logic_error("Error: SetInitial has not been called");
+  CU(cudaSetDevice(device_));
+  const size_t bytes = (size_t)mesh_.nel * ncomp_ * rule_.nip * sizeof(double);
+  if (!d_tmp_a_) CU(cudaMalloc(&d_tmp_a_, bytes));
+  if (!d_tmp_b_) CU(cudaMalloc(&d_tmp_b_, bytes));
+  CU(cudaMemcpyAsync(d_tmp_a_, wf, bytes, cudaMemcpyHostToDevice, stream_));
+  CU(cudaMemcpyAsync(d_tmp_b_, ref, bytes, cudaMemcpyHostToDevice, stream_));
+  return std::sqrt(ReduceElements(d_tmp_a_, d_tmp_b_, l2only ? 2 : 1));
+}
+
+double Solver::MaxAdiam() const {
+  double h = 0;
+  for (double s : staged_.scale) h = std::max(h, 1.0 / s);
+  return h;
+}
+
+}  // namespace ngst

@@ -1,0 +1,95 @@
+// Host-side owner of the device state of one TWave solver (TWaveTents<D>, src/twavetents.hpp:95-224).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "../host/basis.hpp"
+#include "../host/mesh.hpp"
+#include "../host/pitcher.hpp"
+#include "../host/quadrature.hpp"
+#include "../host/stage.hpp"
+#include "tent_kernel.cuh"
+
+namespace ngst {
+
+class Solver {
+ public:
+  Solver(const TentSlab& slab, int order, const std::vector<double>& c_el, const std::vector<double>& c_vertex,
+         int device);
+  ~Solver();
+  Solver(const Solver&) = delete;
+  Solver& operator=(const Solver&) = delete;
+
+  int D() const { return mesh_.D; }
+  int order() const { return order_; }
+  int nbasis() const { return basis_.nbasis; }
+  int nip() const { return rule_.nip; }
+  int ncomp() const { return ncomp_; }
+  int fosystem() const { return fosystem_; }
+  int nel() const { return mesh_.nel; }
+  int ntents() const { return slab_.ntents; }
+  const BasisCsr& basis() const { return basis_; }
+  const StagedTents& staged() const { return staged_; }
+  const SimplexRule& rule() const { return rule_; }
+
+  void Quadrature(double* x, double* weight) const;
+  void SetInitial(const double* wf, int ncomp);
+  void SetBoundaryValues(const double* values, long long n);
+  void Propagate();
+  void GetWavefront(double* out);
+  double Energy(const double* wf);
+  double Error(const double* wf, const double* ref, bool l2only);
+  double MaxAdiam() const;
+
+  double timeshift() const { return timeshift_; }
+  double last_ms() const { return last_ms_; }
+  int last_launches() const { return last_launches_; }
+
+ private:
+  void BuildBasis();
+  template <typename T>
+  T* Upload(const std::vector<T>& v);
+  double ReduceElements(const double* d_a, const double* d_b, int mode);
+
+  const SimplexMesh& mesh_;
+  const TentSlab& slab_;
+  int order_, device_;
+  std::vector<double> c_el_, c_vertex_;
+  SimplexRule rule_;
+  BasisCsr basis_;
+  StagedTents staged_;
+  int ncomp_ = 0, fosystem_ = 0;
+  bool have_initial_ = false;
+  double timeshift_ = 0, last_ms_ = 0;
+  int last_launches_ = 0;
+
+  cudaStream_t stream_ = nullptr;
+  cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
+  std::vector<void*> allocs_;
+  TentKernelArgs args_{};
+  int* d_level_tents_ = nullptr;
+  double* d_wavefront_ = nullptr;
+  double* d_bnd_ = nullptr;
+  double* d_elw_ = nullptr;   // nel*nip weights |detJ| w
+  double* d_scratch_ = nullptr;
+  double* d_tmp_a_ = nullptr;
+  double* d_tmp_b_ = nullptr;
+  int* d_singular_ = nullptr;
+  int* d_rowptr_[2] = {nullptr, nullptr};  // [fosystem]
+  int* d_col_[2] = {nullptr, nullptr};
+  double* d_val_[2] = {nullptr, nullptr};
+  BasisCsr basis_so_, basis_fo_;
+  int threads_ = 256;
+  size_t smem_ = 0;
+};
+
+// kernels (tent_generic.cu, reduce.cu)
+size_t tent_generic_smem_bytes(int D, const TentKernelArgs& a);
+cudaError_t launch_tent_generic(int D, const TentKernelArgs& a, int threads, size_t smem, cudaStream_t stream);
+cudaError_t launch_element_reduce(int mode, int D, int nel, int Q, int ncomp, int fosystem, const double* elw,
+                                  const double* c_el, const double* a, const double* b, double* out,
+                                  cudaStream_t stream);
+
+}  // namespace ngst

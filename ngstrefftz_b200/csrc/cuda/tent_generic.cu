@@ -1,0 +1,476 @@
+// Generic per-tent Trefftz-DG kernel: one CTA per tent, any D in {1,2,3}, any order, second- or
+// first-order input, Dirichlet / Neumann boundary facets and material interfaces (macro elements).
+//
+// Implements the per-tent body of TWaveTents<D>::Propagate (src/twavetents.cpp:92-171):
+//   CalcTentBndEl (335-434), CalcTentMacroEl (436-539), CalcTentEl (177-333), Solve (64-70),
+//   CalcTentElEval (541-590), with the basis evaluation of ScalarMappedElement<D+1>::CalcShape /
+//   CalcDShape (src/scalarmappedfe.cpp:437-674) done on the fly in shared memory.
+// Shared-memory operand layout: E[(v*Qc + q)*Npad + i], v = 0 value, v = 1+d derivative in direction d.
+#include <cuda_runtime.h>
+
+#include "tent_kernel.cuh"
+
+namespace ngst {
+
+namespace {
+
+struct Smem {
+  double *A, *b, *E0, *E1, *Y, *rr, *pw, *mono, *pt;
+};
+
+template <int D>
+__device__ __forceinline__ Smem carve(double* base, const TentKernelArgs& a) {
+  constexpr int d1 = D + 1, nv = D + 2;
+  const int nmax = a.max_ndom * a.Npad;
+  const int esz = nv * a.Qc * a.Npad;
+  Smem s;
+  s.A = base;
+  s.b = s.A + (size_t)nmax * nmax;
+  s.E0 = s.b + nmax;
+  s.E1 = s.E0 + esz;
+  s.Y = s.E1 + esz;
+  s.rr = s.Y + esz;
+  s.pw = s.rr + nv * a.Qc;
+  s.mono = s.pw + a.Qc * d1 * (a.order + 1);
+  s.pt = s.mono + a.Qc * nv * a.npoly;
+  return s;
+}
+
+// Evaluate the scaled Trefftz basis (variants vlo..D+1) at the nq points in s.pt into E.
+template <int D>
+__device__ void eval_basis(const TentKernelArgs& a, const Smem& s, int nq, const double* ctr, double sc, double c,
+                           int vlo, double* E) {
+  constexpr int d1 = D + 1, nv = D + 2;
+  const int tid = threadIdx.x, nth = blockDim.x;
+  const int P1 = a.order + 1, npoly = a.npoly, Np = a.Npad, N = a.N, Qc = a.Qc;
+  for (int idx = tid; idx < nq * d1; idx += nth) {
+    const int q = idx / d1, d = idx % d1;
+    const double scale = (d == D) ? sc * c : sc;
+    const double xi = (s.pt[q * d1 + d] - ctr[d]) * scale;
+    double* p = s.pw + (q * d1 + d) * P1;
+    double v = 1.0;
+    p[0] = 1.0;
+    for (int k = 1; k < P1; k++) { v *= xi; p[k] = v; }
+  }
+  __syncthreads();
+  for (int idx = tid; idx < nq * npoly; idx += nth) {
+    const int q = idx / npoly, ii = idx % npoly;
+    const int* e = a.expo + ii * d1;
+    const double* p = s.pw + q * d1 * P1;
+    double f[d1];
+    double full = 1.0;
+#pragma unroll
+    for (int d = 0; d < d1; d++) { f[d] = p[d * P1 + e[d]]; full *= f[d]; }
+    double* mq = s.mono + (size_t)q * nv * npoly;
+    mq[ii] = full;
+#pragma unroll
+    for (int d = 0; d < d1; d++) {
+      double der = 0.0;
+      if (e[d] > 0) {
+        der = (double)e[d] * p[d * P1 + e[d] - 1];
+#pragma unroll
+        for (int dd = 0; dd < d1; dd++)
+          if (dd != d) der *= f[dd];
+      }
+      mq[(1 + d) * npoly + ii] = der;
+    }
+  }
+  __syncthreads();
+  const int tot = (nv - vlo) * nq * Np;
+  for (int idx = tid; idx < tot; idx += nth) {
+    const int i = idx % Np;
+    const int q = (idx / Np) % nq;
+    const int v = vlo + idx / (Np * nq);
+    double val = 0.0;
+    if (i < N) {
+      const double* mq = s.mono + ((size_t)q * nv + v) * npoly;
+      for (int j = a.rowptr[i]; j < a.rowptr[i + 1]; j++) val += a.val[j] * mq[a.col[j]];
+      if (v > 0) val *= (v - 1 == D) ? sc * c : sc;
+    }
+    E[(size_t)(v * Qc + q) * Np + i] = val;
+  }
+  __syncthreads();
+}
+
+// Asub[i][j] += sum_{v in [v0,v1), q < nq} L[(v*Qc+q)*Np + i] * R[(v*Qc+q)*Np + j], 4x4 register tiles.
+__device__ void gram(double* Asub, int lda, const double* L, const double* R, int v0, int v1, int nq, int Qc, int Np) {
+  const int nt = Np / 4;
+  for (int tile = threadIdx.x; tile < nt * nt; tile += blockDim.x) {
+    const int ti = tile / nt, tj = tile % nt;
+    double acc[4][4];
+#pragma unroll
+    for (int x = 0; x < 4; x++)
+#pragma unroll
+      for (int y = 0; y < 4; y++) acc[x][y] = 0.0;
+    for (int v = v0; v < v1; v++)
+      for (int q = 0; q < nq; q++) {
+        const size_t k = (size_t)(v * Qc + q) * Np;
+        const double2 l0 = *reinterpret_cast<const double2*>(L + k + 4 * ti);
+        const double2 l1 = *reinterpret_cast<const double2*>(L + k + 4 * ti + 2);
+        const double2 r0 = *reinterpret_cast<const double2*>(R + k + 4 * tj);
+        const double2 r1 = *reinterpret_cast<const double2*>(R + k + 4 * tj + 2);
+        const double l[4] = {l0.x, l0.y, l1.x, l1.y};
+        const double r[4] = {r0.x, r0.y, r1.x, r1.y};
+#pragma unroll
+        for (int x = 0; x < 4; x++)
+#pragma unroll
+          for (int y = 0; y < 4; y++) acc[x][y] = fma(l[x], r[y], acc[x][y]);
+      }
+#pragma unroll
+    for (int x = 0; x < 4; x++)
+#pragma unroll
+      for (int y = 0; y < 4; y++) Asub[(size_t)(4 * ti + x) * lda + 4 * tj + y] += acc[x][y];
+  }
+}
+
+// bsub[i] += sum_{v in [v0,v1), q<nq} E[(v*Qc+q)*Np + i] * rr[v*Qc+q]
+__device__ void gemv(double* bsub, const double* E, const double* rr, int v0, int v1, int nq, int Qc, int Np, int N) {
+  for (int i = threadIdx.x; i < N; i += blockDim.x) {
+    double acc = 0.0;
+    for (int v = v0; v < v1; v++)
+      for (int q = 0; q < nq; q++) acc = fma(E[(size_t)(v * Qc + q) * Np + i], rr[v * Qc + q], acc);
+    bsub[i] += acc;
+  }
+}
+
+template <int D>
+__global__ void tent_kernel_generic(TentKernelArgs a) {
+  constexpr int d1 = D + 1, nv = D + 2;
+  extern __shared__ double smem_raw[];
+  const Smem s = carve<D>(smem_raw, a);
+  const int tid = threadIdx.x, nth = blockDim.x;
+  const int tent = a.tents[blockIdx.x];
+  const int nd = a.ndom[tent];
+  const int N = a.N, Np = a.Npad, Qc = a.Qc, Q = a.Q;
+  const int n = nd * Np;
+  const int fo = a.fosystem;
+  const int vlo_val = fo ? 1 : 0;
+
+  double ctr[d1];
+#pragma unroll
+  for (int d = 0; d < d1; d++) ctr[d] = a.center[(size_t)tent * d1 + d];
+  const double sc = a.scale[tent];
+
+  for (int idx = tid; idx < n * n; idx += nth) s.A[idx] = 0.0;
+  for (int idx = tid; idx < n; idx += nth) s.b[idx] = 0.0;
+  __syncthreads();
+
+  // ------------------------------------------------------------------ time-like faces
+  for (int tf = a.tf_off[tent]; tf < a.tf_off[tent + 1]; tf++) {
+    const int kind = a.tf_kind[tf];
+    const double* V = a.tf_verts + (size_t)tf * d1 * d1;
+    double nrm[D];
+#pragma unroll
+    for (int d = 0; d < D; d++) nrm[d] = a.tf_n[(size_t)tf * D + d];
+    const double area = a.tf_area[tf];
+    const int din = a.tf_dom[2 * tf], dout = a.tf_dom[2 * tf + 1];
+    const double c0 = a.tf_c[2 * tf], c1 = a.tf_c[2 * tf + 1];
+    for (int q0 = 0; q0 < Q; q0 += Qc) {
+      const int nq = min(Qc, Q - q0);
+      for (int idx = tid; idx < nq * d1; idx += nth) {
+        const int q = idx / d1, r = idx % d1;
+        double x = V[r];
+        for (int m = 0; m < D; m++) x += (V[(m + 1) * d1 + r] - V[r]) * a.lam[(size_t)(q0 + q) * d1 + m];
+        s.pt[q * d1 + r] = x;
+      }
+      __syncthreads();
+      eval_basis<D>(a, s, nq, ctr, sc, c0, 1, s.E0);
+      if (kind == 2) eval_basis<D>(a, s, nq, ctr, sc, c1, 1, s.E1);
+
+      if (kind == 0) {  // Dirichlet, twavetents.cpp:404-433
+        const double alpha = 0.5, gam = 1.0 / (c0 * c0);
+        const long long off = a.tf_data[tf];
+        for (int idx = tid; idx < nq * Np; idx += nth) {
+          const int q = idx / Np, j = idx % Np;
+          const double om = a.w[q0 + q] * area;
+          double y = om * alpha * gam * s.E0[(size_t)((1 + D) * Qc + q) * Np + j];
+#pragma unroll
+          for (int d = 0; d < D; d++) y -= nrm[d] * om * s.E0[(size_t)((1 + d) * Qc + q) * Np + j];
+          s.Y[(size_t)((1 + D) * Qc + q) * Np + j] = y;
+        }
+        for (int q = tid; q < nq; q += nth) {
+          const double om = a.w[q0 + q] * area;
+          const double g = a.bnd_data ? a.bnd_data[off + q0 + q] : 0.0;
+          s.rr[(1 + D) * Qc + q] = om * alpha * gam * g;
+#pragma unroll
+          for (int d = 0; d < D; d++) s.rr[(1 + d) * Qc + q] = nrm[d] * om * g;
+        }
+        __syncthreads();
+        double* Asub = s.A + (size_t)(din * Np) * n + din * Np;
+        gram(Asub, n, s.E0, s.Y, 1 + D, 2 + D, nq, Qc, Np);
+        gemv(s.b + din * Np, s.E0, s.rr, 1, nv, nq, Qc, Np, N);
+        __syncthreads();
+      } else if (kind == 1) {  // Neumann, twavetents.cpp:380-403
+        const double beta = 0.5;
+        const long long off = a.tf_data[tf];
+        for (int idx = tid; idx < nq * Np; idx += nth) {
+          const int q = idx / Np, j = idx % Np;
+          const double om = a.w[q0 + q] * area;
+          double sum = s.E0[(size_t)((1 + D) * Qc + q) * Np + j];
+#pragma unroll
+          for (int d = 0; d < D; d++) sum += -nrm[d] * beta * s.E0[(size_t)((1 + d) * Qc + q) * Np + j];
+#pragma unroll
+          for (int r = 0; r < D; r++) s.Y[(size_t)((1 + r) * Qc + q) * Np + j] = -nrm[r] * om * sum;
+          s.Y[(size_t)((1 + D) * Qc + q) * Np + j] = 0.0;
+        }
+        for (int q = tid; q < nq; q += nth) {
+          const double om = a.w[q0 + q] * area;
+          double gn = 0.0;
+#pragma unroll
+          for (int r = 0; r < D; r++)
+            gn += -nrm[r] * (a.bnd_data ? a.bnd_data[off + (long long)r * Q + q0 + q] : 0.0);
+#pragma unroll
+          for (int d = 0; d < D; d++) s.rr[(1 + d) * Qc + q] = -nrm[d] * beta * gn * om;
+          s.rr[(1 + D) * Qc + q] = -gn * om;
+        }
+        __syncthreads();
+        double* Asub = s.A + (size_t)(din * Np) * n + din * Np;
+        gram(Asub, n, s.E0, s.Y, 1, nv, nq, Qc, Np);
+        gemv(s.b + din * Np, s.E0, s.rr, 1, nv, nq, Qc, Np, N);
+        __syncthreads();
+      } else {  // material interface, twavetents.cpp:436-539
+        for (int el = 0; el < 4; el++) {
+          const double* Lm = (el / 2 == 0) ? s.E0 : s.E1;
+          const double* Rm = (el % 2 == 0) ? s.E0 : s.E1;
+          const double sg = (el / 2 == 0) ? 1.0 : -1.0;
+          for (int idx = tid; idx < nq * Np; idx += nth) {
+            const int q = idx / Np, j = idx % Np;
+            const double om = a.w[q0 + q] * area;
+            const double rt = Rm[(size_t)((1 + D) * Qc + q) * Np + j];
+            double yt = 0.0;
+#pragma unroll
+            for (int d = 0; d < D; d++) {
+              s.Y[(size_t)((1 + d) * Qc + q) * Np + j] = -sg * 0.5 * nrm[d] * om * rt;
+              yt -= sg * 0.5 * nrm[d] * om * Rm[(size_t)((1 + d) * Qc + q) * Np + j];
+            }
+            s.Y[(size_t)((1 + D) * Qc + q) * Np + j] = yt;
+          }
+          __syncthreads();
+          const int in = (el / 2 == 0) ? din : dout;
+          const int out = (el % 2 == 0) ? din : dout;
+          gram(s.A + (size_t)(in * Np) * n + out * Np, n, Lm, s.Y, 1, nv, nq, Qc, Np);
+          __syncthreads();
+        }
+      }
+    }
+  }
+
+  // ------------------------------------------------------------------ space-like faces (CalcTentEl)
+  for (int te = a.te_off[tent]; te < a.te_off[tent + 1]; te++) {
+    const int el = a.te_el[te];
+    const int dom = a.te_dom[te];
+    const double c = a.c_el[el];
+    const double* geo = a.te_geo + (size_t)te * 2 * (d1 + 1);
+    double* Asub = s.A + (size_t)(dom * Np) * n + dom * Np;
+    double* bsub = s.b + dom * Np;
+    const double* wf = a.wavefront + (size_t)el * a.ncomp * Q;
+    double P[d1][D];
+#pragma unroll
+    for (int k = 0; k < d1; k++) {
+      const int vk = a.el2v[(size_t)el * d1 + k];
+#pragma unroll
+      for (int d = 0; d < D; d++) P[k][d] = a.pts[(size_t)vk * D + d];
+    }
+    for (int q0 = 0; q0 < Q; q0 += Qc) {
+      const int nq = min(Qc, Q - q0);
+      for (int side = 0; side < 2; side++) {
+        const double* tau = (side == 0 ? a.te_tbot : a.te_ttop) + (size_t)te * d1;
+        const double* nn = geo + side * (d1 + 1);
+        const double area = nn[d1];
+        for (int idx = tid; idx < nq * d1; idx += nth) {
+          const int q = idx / d1, r = idx % d1;
+          const double* lm = a.lam + (size_t)(q0 + q) * d1;
+          double x = 0.0;
+          if (r < D) { for (int k = 0; k < d1; k++) x += lm[k] * P[k][r]; }
+          else { for (int k = 0; k < d1; k++) x += lm[k] * tau[k]; }
+          s.pt[q * d1 + r] = x;
+        }
+        __syncthreads();
+        if (side == 0) {
+          eval_basis<D>(a, s, nq, ctr, sc, c, vlo_val, s.E0);
+          for (int q = tid; q < nq; q += nth) {
+            const double om = a.w[q0 + q] * area;
+            const double gt = wf[(size_t)((!fo) + D) * Q + q0 + q];
+            double rt = nn[D] / (c * c) * om * gt;
+#pragma unroll
+            for (int d = 0; d < D; d++) {
+              const double gx = wf[(size_t)((!fo) + d) * Q + q0 + q];
+              s.rr[(1 + d) * Qc + q] = -(nn[D] * om * gx - nn[d] * om * gt);
+              rt -= nn[d] * om * gx;
+            }
+            s.rr[(1 + D) * Qc + q] = -rt;
+            if (!fo) s.rr[q] = om * wf[q0 + q];
+          }
+          if (!fo)
+            for (int idx = tid; idx < nq * Np; idx += nth) {
+              const int q = idx / Np;
+              s.Y[idx] = a.w[q0 + q] * area * s.E0[idx];
+            }
+          __syncthreads();
+          gemv(bsub, s.E0, s.rr, vlo_val, nv, nq, Qc, Np, N);
+          if (!fo) gram(Asub, n, s.E0, s.Y, 0, 1, nq, Qc, Np);
+          __syncthreads();
+        } else {
+          eval_basis<D>(a, s, nq, ctr, sc, c, 1, s.E0);
+          for (int idx = tid; idx < nq * Np; idx += nth) {
+            const int q = idx / Np, j = idx % Np;
+            const double om = a.w[q0 + q] * area;
+            const double bt = s.E0[(size_t)((1 + D) * Qc + q) * Np + j];
+            double yt = nn[D] / (c * c) * om * bt;
+#pragma unroll
+            for (int d = 0; d < D; d++) {
+              const double bd = s.E0[(size_t)((1 + d) * Qc + q) * Np + j];
+              s.Y[(size_t)((1 + d) * Qc + q) * Np + j] = nn[D] * om * bd - nn[d] * om * bt;
+              yt -= nn[d] * om * bd;
+            }
+            s.Y[(size_t)((1 + D) * Qc + q) * Np + j] = yt;
+          }
+          __syncthreads();
+          gram(Asub, n, s.E0, s.Y, 1, nv, nq, Qc, Np);
+          __syncthreads();
+        }
+      }
+    }
+  }
+
+  // ------------------------------------------------------------------ Solve (LU with partial pivoting)
+  for (int g = 0; g < nd; g++)
+    for (int i = N + tid; i < Np; i += nth) s.A[(size_t)(g * Np + i) * n + g * Np + i] = 1.0;
+  __syncthreads();
+  __shared__ int piv_row;
+  __shared__ double piv_inv;
+  for (int k = 0; k < n; k++) {
+    if (tid < 32) {
+      double best = -1.0;
+      int brow = k;
+      for (int r = k + tid; r < n; r += 32) {
+        const double v = fabs(s.A[(size_t)r * n + k]);
+        if (v > best) { best = v; brow = r; }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const double ob = __shfl_down_sync(0xffffffffu, best, o);
+        const int orow = __shfl_down_sync(0xffffffffu, brow, o);
+        if (ob > best || (ob == best && orow < brow)) { best = ob; brow = orow; }
+      }
+      if (tid == 0) {
+        piv_row = brow;
+        if (best == 0.0) { atomicAdd(a.singular, 1); piv_inv = 0.0; }
+        else piv_inv = 1.0 / s.A[(size_t)brow * n + k];
+      }
+    }
+    __syncthreads();
+    const int p = piv_row;
+    if (p != k) {
+      for (int cidx = tid; cidx <= n; cidx += nth) {
+        if (cidx < n) {
+          const double t0 = s.A[(size_t)k * n + cidx];
+          s.A[(size_t)k * n + cidx] = s.A[(size_t)p * n + cidx];
+          s.A[(size_t)p * n + cidx] = t0;
+        } else {
+          const double t0 = s.b[k]; s.b[k] = s.b[p]; s.b[p] = t0;
+        }
+      }
+      __syncthreads();
+    }
+    const double pinv = piv_inv;
+    const int nr = n - k - 1, nc = n - k;  // columns k+1..n-1 and the right-hand side
+    for (int idx = tid; idx < nr * nc; idx += nth) {
+      const int r = k + 1 + idx / nc, cc = idx % nc;
+      const double m = s.A[(size_t)r * n + k] * pinv;
+      if (cc < nc - 1) s.A[(size_t)r * n + k + 1 + cc] -= m * s.A[(size_t)k * n + k + 1 + cc];
+      else s.b[r] -= m * s.b[k];
+    }
+    __syncthreads();
+  }
+  for (int k = n - 1; k >= 0; k--) {
+    if (tid == 0) {
+      const double d = s.A[(size_t)k * n + k];
+      s.b[k] = (d != 0.0) ? s.b[k] / d : 0.0;
+    }
+    __syncthreads();
+    const double xk = s.b[k];
+    for (int r = tid; r < k; r += nth) s.b[r] -= s.A[(size_t)r * n + k] * xk;
+    __syncthreads();
+  }
+
+  // ------------------------------------------------------------------ CalcTentElEval
+  const int lane = tid & 31, wid = tid >> 5, nw = nth >> 5;
+  for (int te = a.te_off[tent]; te < a.te_off[tent + 1]; te++) {
+    const int el = a.te_el[te];
+    const int dom = a.te_dom[te];
+    const double c = a.c_el[el];
+    const double* sol = s.b + dom * Np;
+    double* wf = a.wavefront + (size_t)el * a.ncomp * Q;
+    const double* tau = a.te_ttop + (size_t)te * d1;
+    double P[d1][D];
+#pragma unroll
+    for (int k = 0; k < d1; k++) {
+      const int vk = a.el2v[(size_t)el * d1 + k];
+#pragma unroll
+      for (int d = 0; d < D; d++) P[k][d] = a.pts[(size_t)vk * D + d];
+    }
+    for (int q0 = 0; q0 < Q; q0 += Qc) {
+      const int nq = min(Qc, Q - q0);
+      for (int idx = tid; idx < nq * d1; idx += nth) {
+        const int q = idx / d1, r = idx % d1;
+        const double* lm = a.lam + (size_t)(q0 + q) * d1;
+        double x = 0.0;
+        if (r < D) { for (int k = 0; k < d1; k++) x += lm[k] * P[k][r]; }
+        else { for (int k = 0; k < d1; k++) x += lm[k] * tau[k]; }
+        s.pt[q * d1 + r] = x;
+      }
+      __syncthreads();
+      eval_basis<D>(a, s, nq, ctr, sc, c, vlo_val, s.E0);
+      const int nk = (nv - vlo_val) * nq;
+      for (int kk = wid; kk < nk; kk += nw) {
+        const int v = vlo_val + kk / nq, q = kk % nq;
+        const double* e = s.E0 + (size_t)(v * Qc + q) * Np;
+        double acc = 0.0;
+        for (int i = lane; i < N; i += 32) acc = fma(e[i], sol[i], acc);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+        if (lane == 0) wf[(size_t)(v - fo) * Q + q0 + q] = acc;
+      }
+      __syncthreads();
+    }
+  }
+}
+
+}  // namespace
+
+size_t tent_generic_smem_bytes(int D, const TentKernelArgs& a) {
+  const int d1 = D + 1, nv = D + 2;
+  const size_t nmax = (size_t)a.max_ndom * a.Npad;
+  const size_t esz = (size_t)nv * a.Qc * a.Npad;
+  size_t doubles = nmax * nmax + nmax + 3 * esz + (size_t)nv * a.Qc + (size_t)a.Qc * d1 * (a.order + 1) +
+                   (size_t)a.Qc * nv * a.npoly + (size_t)a.Qc * d1;
+  return doubles * sizeof(double);
+}
+
+cudaError_t launch_tent_generic(int D, const TentKernelArgs& a, int threads, size_t smem, cudaStream_t stream) {
+  if (a.ntents <= 0) return cudaSuccess;
+  cudaError_t err;
+  switch (D) {
+    case 1:
+      err = cudaFuncSetAttribute(tent_kernel_generic<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (err != cudaSuccess) return err;
+      tent_kernel_generic<1><<<a.ntents, threads, smem, stream>>>(a);
+      break;
+    case 2:
+      err = cudaFuncSetAttribute(tent_kernel_generic<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (err != cudaSuccess) return err;
+      tent_kernel_generic<2><<<a.ntents, threads, smem, stream>>>(a);
+      break;
+    case 3:
+      err = cudaFuncSetAttribute(tent_kernel_generic<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (err != cudaSuccess) return err;
+      tent_kernel_generic<3><<<a.ntents, threads, smem, stream>>>(a);
+      break;
+    default:
+      return cudaErrorInvalidValue;
+  }
+  return cudaGetLastError();
+}
+
+}  // namespace ngst

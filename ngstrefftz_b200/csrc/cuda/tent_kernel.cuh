@@ -1,0 +1,47 @@
+// Device-side argument block shared by the tent kernels and the host launcher.
+#pragma once
+
+namespace ngst {
+
+struct TentKernelArgs {
+  // ---- spatial mesh (static)
+  const double* pts;    // nv * D
+  const int* el2v;      // nel * (D+1)
+  const double* c_el;   // nel
+  // ---- quadrature rule of order 2p on the D-simplex
+  const double* lam;    // Q * (D+1) barycentric coordinates (xi_0..xi_{D-1}, 1 - sum)
+  const double* w;      // Q
+  // ---- Trefftz basis (CSR, c = 1) and monomial exponents
+  const int* rowptr;    // N + 1
+  const int* col;       // nnz
+  const double* val;    // nnz
+  const int* expo;      // npoly * (D+1)
+  int N, Npad, npoly, order, Q, Qc, ncomp, fosystem;
+  // ---- tents (StagedTents, device copies)
+  const double* center;
+  const double* scale;
+  const int* ndom;
+  const int* te_off;
+  const int* tf_off;
+  const int* te_el;
+  const int* te_dom;
+  const double* te_tbot;
+  const double* te_ttop;
+  const double* te_geo;
+  const int* tf_kind;
+  const int* tf_dom;
+  const double* tf_c;
+  const double* tf_verts;
+  const double* tf_n;
+  const double* tf_area;
+  const long long* tf_data;
+  const double* bnd_data;  // boundary datum samples for this slab; nullptr = homogeneous
+  // ---- state
+  double* wavefront;       // nel * ncomp * Q, row = [comp][q]
+  const int* tents;        // tent ids of this launch (one level)
+  int ntents;
+  int max_ndom;
+  int* singular;           // incremented when a zero pivot is met
+};
+
+}  // namespace ngst

@@ -1,0 +1,38 @@
+// Trefftz basis for the wave equation: sparse coefficient matrix monomials -> wave polynomials.
+//
+// Follows src/trefftzfespace.cpp:611-682 (TWaveBasis<D+1>::Basis, basistype 0),
+// src/trefftzfespace.hpp:128-142 (PolBasis::IndexMap2), src/trefftzfespace.cpp:455-488 (TraversePol)
+// and src/scalarmappedfe.cpp:153-175 (MatToCSR). Monomials xi^alpha, |alpha| <= p, are enumerated
+// with the FIRST coordinate's exponent outermost (src/scalarmappedfe.cpp:526-531).
+#pragma once
+#include <vector>
+
+namespace ngst {
+
+inline int bincoeff(int n, int k) {
+  if (k < 0 || k > n) return 0;
+  long long r = 1;
+  for (int i = 1; i <= k; i++) r = r * (n - k + i) / i;
+  return (int)r;
+}
+
+struct BasisCsr {
+  int d1 = 0, order = 0, nbasis = 0, npoly = 0;
+  std::vector<int> rowptr, col;
+  std::vector<double> val;
+  std::vector<int> expo;  // npoly * d1 monomial exponents in evaluation order
+};
+
+// number of Trefftz functions: C(D+p,p) + C(D+p-1,p-1) (twavetents.hpp:160-161), minus 1 for fowave
+int twave_nbasis(int D, int order, int fowave);
+
+// exponents of the npoly = C(d1+p,p) monomials, first coordinate outermost
+std::vector<int> monomial_exponents(int d1, int order);
+
+// IndexMap2 (trefftzfespace.hpp:128-142)
+int index_map2(int d1, const int* index, int ord);
+
+// wave polynomials for c = 1 in d1 = D+1 space-time dimensions; fowave drops the constant (row 0)
+BasisCsr twave_basis(int d1, int order, int fowave);
+
+}  // namespace ngst

@@ -1,0 +1,521 @@
+#include "pitcher.hpp"
+
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstdio>
+#include <limits>
+#include <stdexcept>
+
+namespace ngst {
+
+namespace {
+
+// Gradients of the barycentric (P1 nodal) functions of element el: g[k*D + d] = d lambda_k / d x_d.
+// Reference elements as in NGSolve's ScalarFE<ET,1>: lambda = (xi_0, .., xi_{D-1}, 1 - sum xi),
+// x = P_D + sum_i xi_i (P_i - P_D)  (used at tents.cpp:332-352, 666, 873).
+void bary_grads(const SimplexMesh& m, int el, double* g, double* absdet) {
+  const int D = m.D;
+  const int* v = m.elverts(el);
+  double J[9], inv[9];
+  for (int i = 0; i < D; i++)
+    for (int d = 0; d < D; d++) J[d * D + i] = m.point(v[i])[d] - m.point(v[D])[d];
+  double det;
+  if (D == 1) {
+    det = J[0];
+    inv[0] = 1.0 / det;
+  } else if (D == 2) {
+    det = J[0] * J[3] - J[1] * J[2];
+    inv[0] = J[3] / det; inv[1] = -J[1] / det;
+    inv[2] = -J[2] / det; inv[3] = J[0] / det;
+  } else {
+    double c00 = J[4] * J[8] - J[5] * J[7], c01 = J[5] * J[6] - J[3] * J[8], c02 = J[3] * J[7] - J[4] * J[6];
+    det = J[0] * c00 + J[1] * c01 + J[2] * c02;
+    inv[0] = c00 / det; inv[1] = (J[2] * J[7] - J[1] * J[8]) / det; inv[2] = (J[1] * J[5] - J[2] * J[4]) / det;
+    inv[3] = c01 / det; inv[4] = (J[0] * J[8] - J[2] * J[6]) / det; inv[5] = (J[2] * J[3] - J[0] * J[5]) / det;
+    inv[6] = c02 / det; inv[7] = (J[1] * J[6] - J[0] * J[7]) / det; inv[8] = (J[0] * J[4] - J[1] * J[3]) / det;
+  }
+  // grad lambda_i = row i of J^{-1}; grad lambda_D = - sum of the others
+  for (int d = 0; d < D; d++) g[D * D + d] = 0;
+  for (int i = 0; i < D; i++)
+    for (int d = 0; d < D; d++) {
+      g[i * D + d] = inv[i * D + d];
+      g[D * D + d] -= inv[i * D + d];
+    }
+  if (absdet) *absdet = std::fabs(det);
+}
+
+inline double norm(const double* a, int D) {
+  double s = 0;
+  for (int d = 0; d < D; d++) s += a[d] * a[d];
+  return std::sqrt(s);
+}
+
+int local_index(const SimplexMesh& m, int el, int v) {
+  const int* ev = m.elverts(el);
+  for (int k = 0; k <= m.D; k++)
+    if (ev[k] == v) return k;
+  return -1;
+}
+
+// Ready list with the positional semantics of the ngcore Array used at tents.cpp:135,160-168,458-471.
+class ReadyList {
+ public:
+  ReadyList(int nv, const std::vector<int>& level) : level_(level) {
+    cap_ = 2;
+    while (cap_ < 2 * nv + 2) cap_ <<= 1;
+    slot_vertex_.assign(cap_, -1);
+    vslot_.assign(nv, -1);
+    tmin_.assign(2 * cap_, INT_MAX);
+    tcnt_.assign(2 * cap_, 0);
+  }
+  int size() const { return tcnt_[1]; }
+  bool contains(int v) const { return vslot_[v] >= 0; }
+  void append(int v) {
+    if (end_ == cap_) compact();
+    set_slot(end_++, v);
+  }
+  // first position holding the minimal level (PickNextVertexForPitching, tents.cpp:431-443)
+  int pick(int* minlevel) const {
+    int node = 1;
+    *minlevel = tmin_[1];
+    while (node < cap_) node = (tmin_[2 * node] == tmin_[node]) ? 2 * node : 2 * node + 1;
+    return node - cap_;
+  }
+  int vertex_at(int slot) const { return slot_vertex_[slot]; }
+  // Array::DeleteElement: the LAST element is moved into the freed position
+  void delete_element(int slot) {
+    int node = 1;
+    while (node < cap_) node = tcnt_[2 * node + 1] > 0 ? 2 * node + 1 : 2 * node;
+    int last = node - cap_;
+    if (last == slot) { clear_slot(slot); return; }
+    int vlast = slot_vertex_[last];
+    clear_slot(last);
+    clear_slot(slot);
+    set_slot(slot, vlast);
+  }
+  // Array::RemoveElement(Pos(v)): order-preserving erase
+  void remove(int v) {
+    if (vslot_[v] >= 0) clear_slot(vslot_[v]);
+  }
+  void level_changed(int v) {
+    if (vslot_[v] >= 0) set_key(vslot_[v], level_[v], 1);
+  }
+
+ private:
+  void set_key(int slot, int key, int cnt) {
+    int node = slot + cap_;
+    tmin_[node] = key;
+    tcnt_[node] = cnt;
+    for (node >>= 1; node >= 1; node >>= 1) {
+      tmin_[node] = std::min(tmin_[2 * node], tmin_[2 * node + 1]);
+      tcnt_[node] = tcnt_[2 * node] + tcnt_[2 * node + 1];
+    }
+  }
+  void set_slot(int slot, int v) {
+    slot_vertex_[slot] = v;
+    vslot_[v] = slot;
+    set_key(slot, level_[v], 1);
+  }
+  void clear_slot(int slot) {
+    vslot_[slot_vertex_[slot]] = -1;
+    slot_vertex_[slot] = -1;
+    set_key(slot, INT_MAX, 0);
+  }
+  void compact() {
+    std::vector<int> live;
+    for (int s = 0; s < end_; s++)
+      if (slot_vertex_[s] >= 0) live.push_back(slot_vertex_[s]);
+    std::fill(slot_vertex_.begin(), slot_vertex_.end(), -1);
+    std::fill(tmin_.begin(), tmin_.end(), INT_MAX);
+    std::fill(tcnt_.begin(), tcnt_.end(), 0);
+    end_ = (int)live.size();
+    for (int s = 0; s < end_; s++) {
+      slot_vertex_[s] = live[s];
+      vslot_[live[s]] = s;
+      tmin_[cap_ + s] = level_[live[s]];
+      tcnt_[cap_ + s] = 1;
+    }
+    for (int node = cap_ - 1; node >= 1; node--) {
+      tmin_[node] = std::min(tmin_[2 * node], tmin_[2 * node + 1]);
+      tcnt_[node] = tcnt_[2 * node] + tcnt_[2 * node + 1];
+    }
+  }
+  const std::vector<int>& level_;
+  int cap_ = 0, end_ = 0;
+  std::vector<int> slot_vertex_, vslot_, tmin_, tcnt_;
+};
+
+struct Pitcher {
+  const SimplexMesh& m;
+  int method;
+  double global_ctau = 1.0;
+  bool use_local = false;
+  std::vector<double> cmax;       // per edge (edge algo) or per element (vol algo)
+  std::vector<double> edge_len;
+  std::vector<double> vertex_refdt;
+  std::vector<double> local_ctau;  // aligned with v2e.val (edge) or v2el.val (vol)
+
+  Pitcher(const SimplexMesh& mesh, int meth) : m(mesh), method(meth) {}
+
+  // tents.cpp:476-563
+  void InitializeMeshData(const std::vector<double>& cmax_el, bool calc_local_ct, double global_ct) {
+    global_ctau = global_ct;
+    edge_len.assign(m.nedges, 0.0);
+    if (method == kEdgeGrad) cmax.assign(m.nedges, -1.0);
+    else cmax.assign(m.nel, -1.0);
+    const int nepe = m.nEdgesPerEl();
+    std::vector<char> fine(m.nedges, 0);
+    for (int el = 0; el < m.nel; el++) {
+      const double wvspd = cmax_el[el];
+      if (method == kVolGrad) cmax[el] = wvspd;
+      for (int k = 0; k < nepe; k++) {
+        int e = m.el2edge[(size_t)el * nepe + k];
+        if (!fine[e]) {
+          fine[e] = 1;
+          const double* p1 = m.point(m.edge2v[2 * e]);
+          const double* p2 = m.point(m.edge2v[2 * e + 1]);
+          double s = 0;
+          for (int d = 0; d < m.D; d++) s += (p1[d] - p2[d]) * (p1[d] - p2[d]);
+          edge_len[e] = std::sqrt(s);
+        }
+        if (method == kEdgeGrad) cmax[e] = std::max(cmax[e], wvspd);
+      }
+    }
+    use_local = calc_local_ct && m.D > 1;
+    if (use_local) {
+      if (method == kEdgeGrad) CalcLocalCTauEdge();
+      else CalcLocalCTauVol();
+    }
+  }
+
+  // EdgeGradientPitcher::CalcLocalCTau, tents.cpp:815-978
+  void CalcLocalCTauEdge() {
+    const int D = m.D;
+    local_ctau.assign(m.v2e.val.size(), 0.0);
+    std::vector<double> g((D + 1) * D);
+    for (int vi = 0; vi < m.nv; vi++)
+      for (int ie = 0; ie < m.v2e.size(vi); ie++) {
+        const int edge = m.v2e.row(vi)[ie];
+        double val = std::numeric_limits<double>::max();
+        const int v1 = m.edge2v[2 * edge], v2 = m.edge2v[2 * edge + 1];
+        for (int ii = 0; ii < m.edge2el.size(edge); ii++) {
+          const int iel = m.edge2el.row(edge)[ii];
+          bary_grads(m, iel, g.data(), nullptr);
+          const int l1 = local_index(m, iel, v1), l2 = local_index(m, iel, v2);
+          double one_over_max_grad;
+          if (D == 2) {
+            one_over_max_grad = 1.0 / std::max(norm(&g[l1 * D], D), norm(&g[l2 * D], D));
+          } else {
+            // faces of iel adjacent to the edge: those opposite the two vertices NOT on the edge.
+            // The physical face normal is parallel to the gradient of the opposite vertex' hat function.
+            double v = 1;
+            for (int k = 0; k < 4; k++) {
+              if (k == l1 || k == l2) continue;
+              double nrm[3];
+              const double ln = norm(&g[k * 3], 3);
+              for (int d = 0; d < 3; d++) nrm[d] = g[k * 3 + d] / ln;
+              auto proj = [&](int lv) {
+                const double ng = norm(&g[lv * 3], 3);
+                double u[3];
+                for (int d = 0; d < 3; d++) u[d] = g[lv * 3 + d] / ng;
+                double c[3] = {nrm[1] * u[2] - nrm[2] * u[1], nrm[2] * u[0] - nrm[0] * u[2], nrm[0] * u[1] - nrm[1] * u[0]};
+                return norm(c, 3) / ng;
+              };
+              const double val_face = std::min(proj(l1), proj(l2));
+              v = std::min(v, val_face);
+            }
+            one_over_max_grad = v;
+          }
+          const double projGrad = one_over_max_grad / edge_len[edge];
+          val = std::min(val, projGrad);
+        }
+        local_ctau[m.v2e.off[vi] + ie] = val;
+      }
+  }
+
+  // VolumeGradientPitcher::CalcLocalCTau, tents.cpp:719-794
+  void CalcLocalCTauVol() {
+    const int D = m.D;
+    local_ctau.assign(m.v2el.val.size(), 0.0);
+    for (int vi = 0; vi < m.nv; vi++)
+      for (int ie = 0; ie < m.v2el.size(vi); ie++) {
+        const int el = m.v2el.row(vi)[ie];
+        const int* ev = m.elverts(el);
+        double val = 1.0;
+        if (D == 3) {
+          for (int k = 0; k < 4; k++) {  // face k is opposite local vertex k
+            if (ev[k] == vi) continue;  // face does not contain vi
+            int fv[3], nf = 0;
+            for (int j = 0; j < 4; j++)
+              if (j != k) fv[nf++] = ev[j];
+            double opposite = -1, max_edge = 0;
+            for (int a = 0; a < 3; a++)
+              for (int b = a + 1; b < 3; b++) {
+                const double* p1 = m.point(fv[a]);
+                const double* p2 = m.point(fv[b]);
+                double s = 0;
+                for (int d = 0; d < 3; d++) s += (p1[d] - p2[d]) * (p1[d] - p2[d]);
+                const double len = std::sqrt(s);
+                if (fv[a] != vi && fv[b] != vi) opposite = len;
+                else max_edge = std::max(len, max_edge);
+              }
+            val = std::min(val, opposite / max_edge);
+          }
+        } else {
+          // 2-D: ma->GetElFaces gives the element itself as its only face
+          double opposite = -1, max_edge = 0;
+          for (int a = 0; a < 3; a++)
+            for (int b = a + 1; b < 3; b++) {
+              const double* p1 = m.point(ev[a]);
+              const double* p2 = m.point(ev[b]);
+              const double len = std::sqrt((p1[0] - p2[0]) * (p1[0] - p2[0]) + (p1[1] - p2[1]) * (p1[1] - p2[1]));
+              if (ev[a] != vi && ev[b] != vi) opposite = len;
+              else max_edge = std::max(len, max_edge);
+            }
+          val = std::min(val, opposite / max_edge);
+        }
+        val = std::min(val, 1.0);
+        local_ctau[m.v2el.off[vi] + ie] = val;
+      }
+  }
+
+  double GetPoleHeight(int vi, const std::vector<double>& tau) const {
+    return method == kEdgeGrad ? PoleHeightEdge(vi, tau) : PoleHeightVol(vi, tau);
+  }
+
+  // EdgeGradientPitcher::GetPoleHeight, tents.cpp:796-813
+  double PoleHeightEdge(int vi, const std::vector<double>& tau) const {
+    double kt = std::numeric_limits<double>::max();
+    const int n = m.v2v.size(vi);
+    const int* nbv = m.v2v.row(vi);
+    const int* nbe = m.v2e.row(vi);
+    for (int i = 0; i < n; i++) {
+      const int nb = nbv[i];
+      const int edge = nbe[i];
+      const double length = edge_len[edge];
+      const double c_max = cmax[edge];
+      const double local_ct = use_local ? local_ctau[m.v2e.off[vi] + i] : 1.0;
+      const double kt1 = tau[nb] - tau[vi] + global_ctau * local_ct * length / c_max;
+      kt = std::min(kt, kt1);
+    }
+    constexpr double num_tol = std::numeric_limits<double>::epsilon();
+    if (kt > num_tol) return kt * (1 - num_tol);
+    return 0.0;
+  }
+
+  // VolumeGradientPitcher::GetPoleHeight, tents.cpp:627-717
+  double PoleHeightVol(int vi, const std::vector<double>& tau) const {
+    const int D = m.D;
+    constexpr double init_pole_height = std::numeric_limits<double>::max();
+    constexpr double num_tol = std::numeric_limits<double>::epsilon();
+    double pole_height = init_pole_height;
+    double g[12];
+    for (int iel = 0; iel < m.v2el.size(vi); iel++) {
+      const int el = m.v2el.row(vi)[iel];
+      const double c_max_sq = cmax[el] * cmax[el];
+      const int* ev = m.elverts(el);
+      const int local_vi = local_index(m, el, vi);
+      bary_grads(m, el, g, nullptr);
+      double coeff[4];
+      for (int k = 0; k <= D; k++) coeff[k] = tau[ev[k]];
+      coeff[local_vi] = 0;
+      double alpha = 0;
+      for (int d = 0; d < D; d++) alpha += g[local_vi * D + d] * g[local_vi * D + d];
+      double tg[3] = {0, 0, 0};
+      for (int d = 0; d < D; d++)
+        for (int k = 0; k <= D; k++) tg[d] += g[k * D + d] * coeff[k];
+      double ip = 0, tt = 0;
+      for (int d = 0; d < D; d++) { ip += tg[d] * g[local_vi * D + d]; tt += tg[d] * tg[d]; }
+      const double beta = 2 * ip / alpha;
+      const double gamma = (tt - 1.0 / c_max_sq) / alpha;
+      const double delta = beta * beta - 4 * gamma;
+      double sol;
+      if (delta > num_tol * alpha) {
+        if (beta <= num_tol * alpha) sol = (std::sqrt(delta) - beta) / 2.0;
+        else sol = -(2.0 * gamma) / (beta + std::sqrt(delta));
+      } else if (delta > -num_tol * alpha) sol = -beta / 2.0;
+      else sol = init_pole_height;
+      double kbar = sol - tau[vi];
+      const double local_ct = use_local ? local_ctau[m.v2el.off[vi] + iel] : 1.0;
+      kbar *= local_ct * global_ctau;
+      pole_height = std::min(pole_height, kbar);
+    }
+    if (pole_height > 0.75 * init_pole_height) return 0.0;
+    return pole_height * (1 - num_tol);
+  }
+};
+
+}  // namespace
+
+double TentSlab::MaxSlope() const {
+  double s = 0;
+  for (double x : maxslope) s = std::max(s, x);
+  return s;
+}
+
+bool TentSlab::PitchTents(double adt, bool calc_local_ct, double global_ct) {
+  if (!mesh) throw std::runtime_error("TentSlab: no mesh");
+  if (cmax_el.empty()) throw std::logic_error("Wavespeed has not been set!");  // tents.cpp:85-88
+  const SimplexMesh& m = *mesh;
+  if ((int)cmax_el.size() != m.nel) throw std::runtime_error("TentSlab: wavespeed array size mismatch");
+  if (method != kEdgeGrad && method != kVolGrad) return false;
+  const int D = m.D, nv = m.nv;
+  dt = adt;
+  pitched = false;
+  nlayers = 0;
+  ntents = 0;
+  vertex.clear(); level.clear(); tbot.clear(); ttop.clear(); maxslope.clear();
+  nbv = Csr(); els = Csr(); facets = Csr(); dag = Csr();
+  nbv.off = {0}; els.off = {0}; facets.off = {0};
+  nbtime.clear();
+
+  Pitcher P(m, method);
+  P.InitializeMeshData(cmax_el, calc_local_ct, global_ct);
+
+  std::vector<double> tau(nv, 0.0);
+  // ComputeVerticesReferenceHeight, tents.cpp:420-429
+  P.vertex_refdt.assign(nv, std::numeric_limits<double>::max());
+  for (int i = 0; i < nv; i++) P.vertex_refdt[i] = P.GetPoleHeight(i, tau);
+  std::vector<double> ktilde = P.vertex_refdt;
+
+  std::vector<int> latest_tent(nv, -1), vertices_level(nv, 0);
+  std::vector<std::vector<int>> dependents;  // dependent_tents per tent
+  const double adv_factor = 0.5;             // reset after every GetReadyVertices (reset_adv_factor = true)
+  ReadyList ready(nv, vertices_level);
+  std::vector<char> complete(nv, 0);
+  bool slab_complete = false;
+  const double num_tol = std::numeric_limits<double>::epsilon() * dt;
+  std::vector<int> facet_mark(D == 3 ? m.nfacets : 0, -1);
+
+  while (!slab_complete) {
+    // GetReadyVertices, tents.cpp:385-418 (the list is empty on entry)
+    bool found = false;
+    double af = adv_factor;
+    for (int ia = 0; ia < 5; ia++) {
+      for (int iv = 0; iv < nv; iv++)
+        if (!complete[iv] && ktilde[iv] > af * P.vertex_refdt[iv] && !ready.contains(iv)) ready.append(iv);
+      if (ready.size()) { found = true; break; }
+      af /= 2;
+    }
+    if (!found) break;
+
+    while (ready.size()) {
+      int minlevel;
+      const int slot = ready.pick(&minlevel);
+      nlayers = std::max(minlevel, nlayers);
+      const int vi = ready.vertex_at(slot);
+      ready.delete_element(slot);
+
+      const int tid = ntents;
+      vertex.push_back(vi);
+      tbot.push_back(tau[vi]);
+      const double new_ttop = tau[vi] + ktilde[vi];
+      double tt;
+      if (dt - new_ttop > num_tol) tt = new_ttop;
+      else { tt = dt; complete[vi] = 1; }
+      ttop.push_back(tt);
+      const int lev = vertices_level[vi];
+      level.push_back(lev);
+      tau[vi] = tt;
+      ktilde[vi] = 0;
+
+      for (int i = 0; i < m.v2v.size(vi); i++) {
+        const int nb = m.v2v.row(vi)[i];
+        nbv.val.push_back(nb);
+        nbtime.push_back(tau[nb]);
+        if (vertices_level[nb] < lev + 1) {
+          vertices_level[nb] = lev + 1;
+          ready.level_changed(nb);
+        }
+        if (latest_tent[nb] != -1) dependents[latest_tent[nb]].push_back(tid);
+      }
+      nbv.off.push_back((int)nbv.val.size());
+      latest_tent[vi] = tid;
+      vertices_level[vi]++;
+      dependents.emplace_back();
+
+      // internal facets, tents.cpp:219-247
+      if (D == 1) facets.val.push_back(vi);
+      else if (D == 2)
+        for (int i = 0; i < m.v2e.size(vi); i++) facets.val.push_back(m.v2e.row(vi)[i]);
+      else
+        for (int i = 0; i < m.v2el.size(vi); i++) {
+          const int el = m.v2el.row(vi)[i];
+          for (int k = 0; k < 4; k++) {
+            const int f = m.el2facet[(size_t)el * 4 + k];
+            const int* fv = &m.facet2v[(size_t)f * 3];
+            if ((fv[0] == vi || fv[1] == vi || fv[2] == vi) && facet_mark[f] != tid) {
+              facet_mark[f] = tid;
+              facets.val.push_back(f);
+            }
+          }
+        }
+      facets.off.push_back((int)facets.val.size());
+      for (int i = 0; i < m.v2el.size(vi); i++) els.val.push_back(m.v2el.row(vi)[i]);
+      els.off.push_back((int)els.val.size());
+
+      // UpdateNeighbours, tents.cpp:445-474
+      for (int i = 0; i < m.v2v.size(vi); i++) {
+        const int nb = m.v2v.row(vi)[i];
+        if (complete[nb]) continue;
+        const double kt = P.GetPoleHeight(nb, tau);
+        ktilde[nb] = kt;
+        if (kt > adv_factor * P.vertex_refdt[nb]) {
+          if (!ready.contains(nb)) ready.append(nb);
+        } else ready.remove(nb);
+      }
+      ntents++;
+    }
+    slab_complete = true;
+    for (int i = 0; i < nv; i++)
+      if (!complete[i]) { slab_complete = false; break; }
+  }
+
+  if (!slab_complete) std::printf("Error: the algorithm could not pitch the whole slab\n");
+
+  // dependency graph, tents.cpp:313-321
+  dag.off.assign(ntents + 1, 0);
+  for (int i = 0; i < ntents; i++) dag.off[i + 1] = dag.off[i] + (int)dependents[i].size();
+  dag.val.resize(dag.off[ntents]);
+  for (int i = 0; i < ntents; i++) std::copy(dependents[i].begin(), dependents[i].end(), dag.val.begin() + dag.off[i]);
+
+  // slope of the top front per tent, tents.cpp:323-356
+  maxslope.assign(ntents, 0.0);
+#pragma omp parallel for schedule(static)
+  for (int i = 0; i < ntents; i++) {
+    double g[12];
+    for (int j = els.off[i]; j < els.off[i + 1]; j++) {
+      const int el = els.val[j];
+      const int* ev = m.elverts(el);
+      double coef[4];
+      for (int k = 0; k <= D; k++) {
+        coef[k] = ttop[i];
+        for (int q = nbv.off[i]; q < nbv.off[i + 1]; q++)
+          if (nbv.val[q] == ev[k]) { coef[k] = nbtime[q]; break; }
+      }
+      bary_grads(m, el, g, nullptr);
+      double gp[3] = {0, 0, 0};
+      for (int d = 0; d < D; d++)
+        for (int k = 0; k <= D; k++) gp[d] += g[k * D + d] * coef[k];
+      const double nrm = norm(gp, D);
+      if (nrm > maxslope[i]) maxslope[i] = nrm;
+    }
+  }
+
+  // level sets (BSP schedule replacing RunParallelDependency, paralleldepend.hpp:20-131)
+  int nl = 0;
+  for (int i = 0; i < ntents; i++) nl = std::max(nl, level[i] + 1);
+  level_off.assign(nl + 1, 0);
+  for (int i = 0; i < ntents; i++) level_off[level[i] + 1]++;
+  for (int l = 0; l < nl; l++) level_off[l + 1] += level_off[l];
+  level_tents.resize(ntents);
+  {
+    std::vector<int> pos(level_off.begin(), level_off.end() - 1);
+    for (int i = 0; i < ntents; i++) level_tents[pos[level[i]]++] = i;
+  }
+  pitched = slab_complete;
+  return pitched;
+}
+
+}  // namespace ngst

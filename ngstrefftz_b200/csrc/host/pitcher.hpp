@@ -1,0 +1,48 @@
+// Tent pitching: serial greedy advancing front, bit-exact with the reference's schedule.
+//
+// Follows external_dependencies/ngstents/src/tents.cpp:78-359 (PitchTents<DIM>),
+// 385-474 (GetReadyVertices, PickNextVertexForPitching, UpdateNeighbours),
+// 476-563 (InitializeMeshData), 796-978 (EdgeGradientPitcher), 627-794 (VolumeGradientPitcher).
+// The reference keeps the ready list in an ngcore Array and scans it linearly per tent
+// (tents.cpp:431-443); here the same list semantics (Append / DeleteElement = move-last-into-slot /
+// RemoveElement = order-preserving erase / first-position-of-minimum-level) are kept in a
+// tombstoned slot array under a min segment tree, so one tent costs O(log nv) instead of O(nv)
+// while producing the identical tent sequence (tests compare against the literal oracle).
+#pragma once
+#include <vector>
+
+#include "mesh.hpp"
+
+namespace ngst {
+
+enum PitchMethod { kVolGrad = 1, kEdgeGrad = 2 };
+
+struct TentSlab {
+  const SimplexMesh* mesh = nullptr;
+  int method = kEdgeGrad;
+  std::vector<double> cmax_el;  // per-element maximal wavespeed (SetMaxWavespeed)
+  double dt = 0;
+  bool pitched = false;
+  int nlayers = 0;  // as the reference's member: GetNLayers() == nlayers + 1
+
+  // flattened tents (struct Tent, tents.hpp:38-75)
+  int ntents = 0;
+  std::vector<int> vertex, level;
+  std::vector<double> tbot, ttop, maxslope;
+  Csr nbv;                     // neighbour vertices
+  std::vector<double> nbtime;  // aligned with nbv.val
+  Csr els;                     // vertex patch elements
+  Csr facets;                  // internal facets
+  Csr dag;                     // tent_dependency: successors of each tent
+
+  // level sets: tents of level l are level_tents[level_off[l] .. level_off[l+1]) in ascending tent index
+  std::vector<int> level_off, level_tents;
+
+  int GetNLayers() const { return nlayers + 1; }
+  double MaxSlope() const;
+
+  // returns false when the front could not reach dt (tents.cpp:265-288)
+  bool PitchTents(double dt, bool local_ct, double global_ct);
+};
+
+}  // namespace ngst

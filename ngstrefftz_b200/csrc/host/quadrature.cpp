@@ -1,0 +1,139 @@
+#include "quadrature.hpp"
+
+#include <algorithm>
+#include <cmath>
+#include <stdexcept>
+
+namespace ngst {
+
+namespace {
+// Jacobi polynomial P_n^{(a,b)}(t) by the three-term recurrence, in long double.
+long double jacobi_p(int n, int a, int b, long double t) {
+  if (n == 0) return 1.0L;
+  long double p0 = 1.0L;
+  long double p1 = 0.5L * (a - b) + 0.5L * (a + b + 2) * t;
+  for (int k = 1; k < n; k++) {
+    long double c = 2.0L * k + a + b;
+    long double a1 = 2.0L * (k + 1) * (k + a + b + 1) * c;
+    long double a2 = (c + 1) * (a * a - b * b);
+    long double a3 = c * (c + 1) * (c + 2);
+    long double a4 = 2.0L * (k + a) * (k + b) * (c + 2);
+    long double p2 = ((a2 + a3 * t) * p1 - a4 * p0) / a1;
+    p0 = p1;
+    p1 = p2;
+  }
+  return p1;
+}
+long double jacobi_dp(int n, int a, int b, long double t) {
+  if (n == 0) return 0.0L;
+  return 0.5L * (n + a + b + 1) * jacobi_p(n - 1, a + 1, b + 1, t);
+}
+
+// eigenvalues of a small dense symmetric matrix by cyclic Jacobi rotations
+std::vector<long double> sym_eigenvalues(std::vector<long double> A, int n) {
+  for (int sweep = 0; sweep < 100; sweep++) {
+    long double off = 0;
+    for (int i = 0; i < n; i++)
+      for (int j = i + 1; j < n; j++) off += A[i * n + j] * A[i * n + j];
+    if (off < 1e-40L) break;
+    for (int p = 0; p < n; p++)
+      for (int q = p + 1; q < n; q++) {
+        long double apq = A[p * n + q];
+        if (fabsl(apq) < 1e-300L) continue;
+        long double theta = (A[q * n + q] - A[p * n + p]) / (2 * apq);
+        long double t = (theta >= 0 ? 1.0L : -1.0L) / (fabsl(theta) + sqrtl(theta * theta + 1));
+        long double c = 1 / sqrtl(t * t + 1), s = t * c;
+        for (int k = 0; k < n; k++) {
+          long double akp = A[k * n + p], akq = A[k * n + q];
+          A[k * n + p] = c * akp - s * akq;
+          A[k * n + q] = s * akp + c * akq;
+        }
+        for (int k = 0; k < n; k++) {
+          long double apk = A[p * n + k], aqk = A[q * n + k];
+          A[p * n + k] = c * apk - s * aqk;
+          A[q * n + k] = s * apk + c * aqk;
+        }
+      }
+  }
+  std::vector<long double> ev(n);
+  for (int i = 0; i < n; i++) ev[i] = A[i * n + i];
+  std::sort(ev.begin(), ev.end());
+  return ev;
+}
+}  // namespace
+
+void gauss_jacobi01(int n, int alpha, std::vector<double>& x, std::vector<double>& w) {
+  if (n < 1) throw std::runtime_error("gauss_jacobi01: n < 1");
+  const int a = alpha, b = 0;
+  // Golub-Welsch start values from the Jacobi matrix of P^{(a,0)}
+  std::vector<long double> J((size_t)n * n, 0.0L);
+  for (int k = 0; k < n; k++) {
+    long double c = 2.0L * k + a + b;
+    J[k * n + k] = (k == 0) ? (long double)(b - a) / (a + b + 2) : (long double)(b * b - a * a) / (c * (c + 2));
+    if (k + 1 < n) {
+      int k1 = k + 1;
+      long double c1 = 2.0L * k1 + a + b;
+      long double num = 4.0L * k1 * (k1 + a) * (k1 + b) * (k1 + a + b);
+      long double den = c1 * c1 * (c1 + 1) * (c1 - 1);
+      long double off = sqrtl(num / den);
+      J[k * n + k1] = J[k1 * n + k] = off;
+    }
+  }
+  std::vector<long double> t = sym_eigenvalues(J, n);
+  x.resize(n);
+  w.resize(n);
+  for (int i = 0; i < n; i++) {
+    long double ti = t[i];
+    for (int it = 0; it < 50; it++) {  // Newton polish
+      long double dt = jacobi_p(n, a, b, ti) / jacobi_dp(n, a, b, ti);
+      ti -= dt;
+      if (fabsl(dt) < 1e-19L) break;
+    }
+    long double dp = jacobi_dp(n, a, b, ti);
+    // weight on [-1,1] for (1-t)^a: 2^{a+1} / ((1-t^2) P'^2); mapping to [0,1] divides by 2^{a+1}
+    long double wi = 1.0L / ((1 - ti * ti) * dp * dp);
+    x[i] = (double)(0.5L * (1 + ti));
+    w[i] = (double)wi;
+  }
+}
+
+SimplexRule make_simplex_rule(int dim, int order) {
+  if (dim < 1 || dim > 3) throw std::runtime_error("make_simplex_rule: dim must be 1..3");
+  if (order < 0) throw std::runtime_error("make_simplex_rule: negative order");
+  const int n = order / 2 + 1;
+  SimplexRule r;
+  r.dim = dim;
+  std::vector<double> x0, w0, x1, w1, x2, w2;
+  if (dim == 1) {
+    gauss_jacobi01(n, 0, x0, w0);
+    r.nip = n;
+    r.xi = x0;
+    r.w = w0;
+  } else if (dim == 2) {
+    gauss_jacobi01(n, 1, x0, w0);
+    gauss_jacobi01(n, 0, x1, w1);
+    r.nip = n * n;
+    for (int i = 0; i < n; i++)
+      for (int j = 0; j < n; j++) {
+        r.xi.push_back(x0[i]);
+        r.xi.push_back(x1[j] * (1 - x0[i]));
+        r.w.push_back(w0[i] * w1[j]);
+      }
+  } else {
+    gauss_jacobi01(n, 2, x0, w0);
+    gauss_jacobi01(n, 1, x1, w1);
+    gauss_jacobi01(n, 0, x2, w2);
+    r.nip = n * n * n;
+    for (int i = 0; i < n; i++)
+      for (int j = 0; j < n; j++)
+        for (int k = 0; k < n; k++) {
+          r.xi.push_back(x0[i]);
+          r.xi.push_back(x1[j] * (1 - x0[i]));
+          r.xi.push_back(x2[k] * (1 - x0[i]) * (1 - x1[j]));
+          r.w.push_back(w0[i] * w1[j] * w2[k]);
+        }
+  }
+  return r;
+}
+
+}  // namespace ngst
