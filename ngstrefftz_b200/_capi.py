@@ -75,6 +75,7 @@ _SIGS = {
     "ngst_twave_max_adiam": (C.c_int, [c_vp, c_dp]),
     "ngst_twave_basis": (C.c_int, [c_vp, c_ip, c_ip, c_ip, c_dp]),
     "ngst_twave_destroy": (None, [c_vp]),
+    "ngst_device_fp64_peak": (C.c_int, [C.c_int, C.c_int, c_dp]),
     "ngst_basis": (C.c_int, [C.c_int, C.c_int, C.c_int, c_ip, c_ip, c_ip, c_dp, c_ip]),
     "ngst_rule": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp, c_dp]),
 }

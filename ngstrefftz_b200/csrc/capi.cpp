@@ -289,6 +289,16 @@ int ngst_twave_basis(const ngst_twave* t, int* sizes, int* rowptr, int* col, dou
 
 void ngst_twave_destroy(ngst_twave* t) { delete t; }
 
+int ngst_device_fp64_peak(int device, int which, double* tflops) {
+  return guarded([&] {
+    need(tflops, "tflops");
+    if (which != 0 && which != 1) throw std::invalid_argument("ngst_device_fp64_peak: which must be 0 or 1");
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = measure_fp64_peak(which, 5, tflops);
+    if (e != cudaSuccess) throw std::runtime_error(std::string("CUDA: fp64 peak: ") + cudaGetErrorString(e));
+  });
+}
+
 int ngst_basis(int D, int order, int fowave, int* sizes, int* rowptr, int* col, double* val, int* expo) {
   return guarded([&] {
     if (D < 1 || D > 3) throw std::invalid_argument("ngst_basis: D must be 1..3");

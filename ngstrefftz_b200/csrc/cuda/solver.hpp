@@ -92,4 +92,7 @@ cudaError_t launch_element_reduce(int mode, int D, int nel, int Q, int ncomp, in
                                   const double* c_el, const double* a, const double* b, double* out,
                                   cudaStream_t stream);
 
+// fp64_peak.cu: which 0 = DFMA pipe, 1 = DMMA (mma.sync m8n8k4 f64); TFLOP/s on the current device
+cudaError_t measure_fp64_peak(int which, int reps, double* tflops);
+
 }  // namespace ngst

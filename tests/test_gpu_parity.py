@@ -1,0 +1,161 @@
+"""GPU parity (K6): libngst_b200.so through its C ABI vs the CPU oracle on the same tents and data.
+
+Bar: tent tables bitwise identical; wavefront and Energy within 1e-10 relative in FP64 (BASELINE.json north_star).
+"""
+import math
+
+import numpy as np
+import pytest
+
+import ngstrefftz_b200 as ng
+from _cases import dirichlet, first_order, gaussian_1d, neumann, poly_solution, standing
+from _oracle import Oracle
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+
+def both(mesh, order, c, dt, init, bnd, nslabs=1, neu=False):
+    if neu:
+        mesh.SetBoundaryNames("neumann")
+    ts = ng.TentSlab(mesh, "edge")
+    ts.SetMaxWavespeed(c)
+    assert ts.PitchTents(dt, True, 2 / 3)
+    tw = ng.TWave(order, ts, c)
+    tw.SetInitial(init)
+    tw.SetBoundaryCF(bnd)
+    o = Oracle(mesh)
+    assert o.pitch(dt, True, 2 / 3, c(o.centroids) if callable(c) else c)
+    e1, e2 = ts.export(), o.export()
+    for k in e2:
+        assert np.array_equal(e1[k], e2[k]), f"tent table {k} differs"
+    o.setup(order, c)
+    o.set_initial(init)
+    o.set_boundary_cf(bnd)
+    for _ in range(nslabs):
+        tw.Propagate()
+        o.propagate()
+    assert tw.last_launches() > 0
+    return tw, o
+
+
+def check(tw, o, tol=TOL):
+    wf, ref = tw.GetWavefront(), o.wavefront()
+    rel = np.abs(wf - ref).max() / np.abs(ref).max()
+    assert rel <= tol, rel
+    if not tw.fosystem:
+        eg, eo = tw.Energy(wf), o.energy(ref)
+        assert abs(eg - eo) <= tol * abs(eo), (eg, eo)
+        assert abs(tw.Energy() - eg) <= 1e-14 * abs(eg)  # resident state == downloaded state
+    assert abs(tw.timeshift() - o_timeshift(o)) == 0
+    return rel
+
+
+def o_timeshift(o):
+    from _oracle import lib
+    return lib.oracle_timeshift(o.h)
+
+
+CASES = {
+    # name: (mesh factory, order, c, dt, init, bnd, nslabs, neumann)
+    "cfg0_2d_p4_h025": (lambda: ng.UnitSquareMesh(4), 4, 1.0, 0.5, standing(2), dirichlet(standing(2), 2), 1, False),
+    "1d_p4_dirichlet": (lambda: ng.SegMesh(16, 0, 1), 4, 1.0, 0.5, standing(1), dirichlet(standing(1), 1), 1, False),
+    "1d_p4_neumann": (lambda: ng.SegMesh(16, 0, 1), 4, 1.0, 0.5, standing(1), neumann(standing(1), 1), 1, True),
+    "1d_p6_first_order": (lambda: ng.SegMesh(16, 0, 1), 6, 1.0, 0.5, first_order(standing(1)), dirichlet(standing(1), 1), 1, False),
+    "1d_segpi": (lambda: ng.SegMesh(4, 0, math.pi), 4, 1.0, 0.5, standing(1), dirichlet(standing(1), 1), 1, False),
+    "2d_p4_neumann": (lambda: ng.UnitSquareMesh(4), 4, 1.0, 0.5, standing(2), neumann(standing(2), 2), 1, True),
+    "2d_p4_fo_2slabs": (lambda: ng.UnitSquareMesh(6), 4, 1.0, 0.3, first_order(standing(2)), dirichlet(standing(2), 2), 2, False),
+    "2d_p5_poly": (lambda: ng.UnitSquareMesh(3), 5, 1.0, 0.3, poly_solution(2), dirichlet(poly_solution(2), 2), 1, False),
+    "2d_p2_c3": (lambda: ng.UnitSquareMesh(5), 2, 3.0, 0.1, standing(2, 3.0), dirichlet(standing(2, 3.0), 2), 3, False),
+    "3d_p3": (lambda: ng.UnitCubeMesh(3), 3, 1.0, 0.2, standing(3), dirichlet(standing(3), 3), 1, False),
+    "3d_p4": (lambda: ng.UnitCubeMesh(4), 4, 1.0, 0.2, standing(3), dirichlet(standing(3), 3), 1, False),
+    "3d_p4_neumann": (lambda: ng.UnitCubeMesh(3), 4, 1.0, 0.2, standing(3), neumann(standing(3), 3), 1, True),
+    "3d_p4_fo": (lambda: ng.UnitCubeMesh(3), 4, 1.0, 0.2, first_order(standing(3)), dirichlet(standing(3), 3), 2, False),
+    "3d_p1": (lambda: ng.UnitCubeMesh(2), 1, 1.0, 0.2, standing(3), dirichlet(standing(3), 3), 1, False),
+    "3d_box_p3": (lambda: ng.StructuredMesh([4, 2, 3], [0, 0, 0], [1, 0.6, 1.3]), 3, 1.3, 0.15, standing(3, 1.3),
+                  dirichlet(standing(3, 1.3), 3), 2, False),
+}
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_parity_constant_wavespeed(built, name):
+    mk, order, c, dt, init, bnd, nslabs, neu = CASES[name]
+    tw, o = both(mk(), order, c, dt, init, bnd, nslabs, neu)
+    check(tw, o)
+
+
+def pc1(x):
+    return np.where((np.floor(x[:, 0] * 4).astype(int) % 2) == 0, 1.0, 2.0)
+
+
+MACRO = {
+    "1d_p6_piecewise": (lambda: ng.SegMesh(32, 0, 1), 6, pc1, 0.3, gaussian_1d, lambda x, t: 0 * t, 2),
+    "2d_p3_piecewise": (lambda: ng.UnitSquareMesh(4), 3, lambda x: np.where(x[:, 0] < 0.5, 1.0, 1.5), 0.2, standing(2),
+                        dirichlet(standing(2), 2), 1),
+    "3d_p2_piecewise": (lambda: ng.UnitCubeMesh(2), 2, lambda x: np.where(x[:, 2] < 0.5, 1.0, 2.0), 0.2, standing(3),
+                        dirichlet(standing(3), 3), 1),
+}
+
+
+@pytest.mark.parametrize("name", list(MACRO))
+def test_parity_material_interfaces(built, name):
+    """CalcTentMacroEl (twavetents.cpp:436-539). The under-resolved 1-D pulse has local systems of condition ~1e9, where
+    the oracle's inverse-then-multiply (twavetents.cpp:64-70) and a pivoted LU solve differ by cond*eps: tolerance 1e-8
+    there, 1e-10 elsewhere ('Solve')."""
+    mk, order, c, dt, init, bnd, nslabs = MACRO[name]
+    tw, o = both(mk(), order, c, dt, init, bnd, nslabs)
+    check(tw, o, tol=1e-8 if name.startswith("1d") else TOL)
+
+
+def test_known_answer_on_gpu(built):
+    """K1 on the device: a cubic wave polynomial is reproduced to round-off, Error() agrees with the oracle's."""
+    f = poly_solution(3, 1.2)
+    tw, o = both(ng.UnitCubeMesh(2), 4, 1.2, 0.25, f, dirichlet(f, 3), nslabs=2)
+    wf = tw.GetWavefront()
+    exact = tw.MakeWavefront(f, 0.5)
+    assert np.abs(wf - exact).max() <= 1e-10 * np.abs(exact).max()
+    assert tw.Error(wf, exact) <= 1e-10 * math.sqrt(2 * tw.Energy(exact))
+    ref = o.wavefront()
+    assert abs(tw.L2Error(wf, 0 * wf) - o.l2error(ref, 0 * ref)) <= 1e-10 * o.l2error(ref, 0 * ref)
+    assert abs(tw.MaxAdiam() - o.max_adiam()) <= 1e-15 * o.max_adiam()
+
+
+def test_size_independent_properties_large(built):
+    """At a size the oracle does not finish in seconds: energy decay with homogeneous data and determinism
+    (two solvers on the same data give bitwise identical states)."""
+    f = standing(3)
+    mesh = ng.UnitCubeMesh(12)
+    ts = ng.TentSlab(mesh, "edge")
+    ts.SetMaxWavespeed(1.0)
+    assert ts.PitchTents(0.05, True, 2 / 3)
+    out = []
+    for _ in range(2):
+        tw = ng.TWave(4, ts, 1.0)
+        tw.SetInitial(f)
+        tw.SetBoundaryCF(lambda x, t: 0 * t)
+        en = [tw.Energy()]
+        for _ in range(2):
+            tw.Propagate()
+            en.append(tw.Energy())
+        assert en[2] <= en[1] * (1 + 1e-12) <= en[0] * (1 + 1e-12) ** 2 and en[2] > 0.9 * en[0]
+        out.append(tw.GetWavefront())
+    assert np.array_equal(out[0], out[1])
+    exact = tw.MakeWavefront(f, 0.1)
+    assert tw.Error(out[0], exact) < 2e-4
+
+
+def test_errors_on_gpu(built):
+    from ngstrefftz_b200._capi import NgstError
+    mesh = ng.UnitSquareMesh(2)
+    ts = ng.TentSlab(mesh)
+    ts.SetMaxWavespeed(1.0)
+    assert ts.PitchTents(0.1, True, 2 / 3)
+    tw = ng.TWave(2, ts, 1.0)
+    with pytest.raises(NgstError) as ei:
+        tw.Propagate()  # no initial data
+    assert ei.value.code == -2
+    with pytest.raises(NgstError):
+        tw.SetInitial(np.zeros((mesh.ne, 7 * tw.nip)))  # neither D+1 nor D+2 components
+    with pytest.raises(NgstError) as ei:
+        ng.TWave(2, ts, 1.0, device=99)
+    assert ei.value.code == -3
