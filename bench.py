@@ -1,0 +1,406 @@
+#!/usr/bin/env python
+"""Benchmark of the tent-pitched Trefftz-DG wave propagator (BASELINE.json: tents/s and DOF-updates/s,
+3+1D order-4, 1/2/4/8 B200 vs host CPU).
+
+A "step" is one Propagate() of one tent slab (TWaveTents<3>::Propagate, src/twavetents.cpp:72-175) over the
+per-GPU share of BASELINE configs[4]: unit-cube bricks of 28^3 cells x 6 tets = 131 712 tets per GPU,
+order 4, c = 1, standing-wave data, Dirichlet boundary (input 4). Weak scaling:
+1 GPU 28x28x28 cells, 2 GPUs 56x28x28, 4 GPUs 56x56x28, 8 GPUs 56x56x56.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            our arm (CUDA, libngst_b200.so through the C ABI)
+  python bench.py --impl reference [--steps K] [--warmup W]      CPU arm: the oracle restatement of the reference's
+                                                                 Propagate on all host cores (the reference itself
+                                                                 needs NGSolve and cannot be built)
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "tents/s (3+1D order-4 Trefftz-DG tent slab, one Propagate per step)"
+WEAK_GRIDS = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cells", type=int, default=28, help="cells per side of the per-GPU brick")
+    ap.add_argument("--order", type=int, default=4)
+    ap.add_argument("--dt", type=float, default=0.05, help="slab height")
+    ap.add_argument("--cpu-sample-tents", type=int, default=0, help="tents in the bounded CPU sample (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def workload(args, ngpus):
+    g = WEAK_GRIDS.get(ngpus)
+    if g is None:
+        raise SystemExit("--gpus must be 1, 2, 4 or 8")
+    cells = [args.cells * k for k in g]
+    return cells, g
+
+
+def standing3(x, t, c=1.0):
+    from _cases import standing
+    return standing(3, c)(x, t)
+
+
+# ------------------------------------------------------------------------------------------------ flop model
+def algorithmic_flops(D, p, N, npoly, nnz, Qr, nels_per_tent, ndom_per_tent):
+    """per tent-element F_el, per tent sum F_el + (2/3) n^3 + 2 n^2 (LU solve, n = ndom*N)."""
+    d1 = D + 1
+    f_el = (2 * N * N * (d1 + 1) * Qr + 2 * N * Qr * (2 * (d1 + 1) + (3 * D + 1)) +
+            2 * Qr * (d1 * (d1 * npoly + 2 * nnz) + D * npoly + 2 * nnz))
+    n = ndom_per_tent * N
+    per_tent = nels_per_tent * f_el + (2.0 / 3.0) * n ** 3 + 2.0 * n ** 2
+    return float(per_tent.sum()), f_el
+
+
+def algorithmic_bytes(D, Qr, ncomp, nels_per_tent, nnb_per_tent):
+    d1 = D + 1
+    b_el = 2 * ncomp * Qr * 8
+    per_tent = nels_per_tent * b_el + (1 + nnb_per_tent) * d1 * 8 + 4 * (nels_per_tent * d1 + nnb_per_tent)
+    return float(per_tent.sum()), b_el
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+                pw.append(float(parts[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        self.f.close()
+        os.unlink(self.f.name)
+        if sm:
+            out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                   "power_w_max": float(max(pw)), "samples": len(sm)}
+        return out
+
+
+# ------------------------------------------------------------------------------------------------ CPU arm
+def cpu_sample(args, cells, sample_tents, steps, warmup, nthreads):
+    """Times the oracle's multithreaded Propagate (restating src/twavetents.cpp:72-175 with the reference's
+    level-parallel tent loop) on a bounded sample: the first `sample_tents` tents (in level order) of the slab."""
+    import ngstrefftz_b200 as ng
+    from _cases import dirichlet, standing
+    from _oracle import Oracle
+
+    mesh = ng.StructuredMesh(cells, [0.0] * 3, [c / args.cells for c in cells])
+    o = Oracle(mesh)
+    assert o.pitch(args.dt, True, 2 / 3, 1.0)
+    f = standing(3, 1.0)
+    o.setup(args.order, 1.0)
+    o.set_initial(f)
+    o.set_boundary_cf(dirichlet(f, 3))
+    e = o.export()
+    nt = o.ntents()
+    sample_tents = min(sample_tents, nt)
+    order = np.argsort(e["level"], kind="stable")[:sample_tents]  # level order, ascending id inside a level
+    nels = np.diff(e["el_off"])[order]
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        o.propagate(nthreads=nthreads, ntents_limit=sample_tents)
+        t1 = time.perf_counter()
+        if i >= warmup:
+            times.append(t1 - t0)
+    sec = float(np.sum(times))
+    tents = sample_tents * len(times)
+    return {"tents_per_s": tents / sec, "sec_per_step": sec / max(len(times), 1), "sample_tents": int(sample_tents),
+            "slab_tents": int(nt), "nbasis": o.nbasis(), "tent_elements": int(nels.sum())}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cells, grid = workload(args, args.gpus)
+    cores = os.cpu_count() or 1
+    sample = args.cpu_sample_tents or 4000
+    r = cpu_sample(args, cells, sample, args.steps, max(args.warmup, 1), cores)
+    N = r["nbasis"]
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["tents_per_s"], "unit": "tents/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": max(args.warmup, 1), "ms_per_step": 1e3 * r["sec_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "dof_updates_per_s": r["tents_per_s"] * N,
+        "config": {"workload": f"3+1D unit-cube brick {cells[0]}x{cells[1]}x{cells[2]} cells x 6 tets, order "
+                               f"{args.order}, c=1, standing wave, Dirichlet, dt={args.dt}, edge pitching "
+                               f"local_ct global_ct=2/3", "tets": int(np.prod(cells) * 6), "order": args.order,
+                   "nbasis": N, "slab_tents": r["slab_tents"]},
+        "cpu_baseline": {"value": r["tents_per_s"], "unit": "tents/s", "cores": cores, "kind": "port",
+                         "sample": f"first {r['sample_tents']} tents (level order) of the {r['slab_tents']}-tent slab "
+                                   f"per step; oracle restatement of the reference's Propagate, OpenMP over the tents of "
+                                   f"a level; the reference itself needs NGSolve (unbuildable here)"},
+        "e2e": {"value": r["tents_per_s"], "unit": "tents/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    import ngstrefftz_b200 as ng
+    from ngstrefftz_b200 import _capi
+    from _cases import dirichlet, standing
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch N>1 with: python -m torch.distributed.run --nproc-per-node N bench.py --gpus N")
+        raise SystemExit(f"WORLD_SIZE={world} does not match --gpus {args.gpus}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    cells, grid = workload(args, world)
+    D, order = 3, args.order
+    f = standing(D, 1.0)
+    mesh = ng.StructuredMesh(cells, [0.0] * 3, [c / args.cells for c in cells])
+    ts = ng.TentSlab(mesh, "edge")
+    ts.SetMaxWavespeed(1.0)
+    t0 = time.perf_counter()
+    assert ts.PitchTents(args.dt, True, 2 / 3)
+    pitch_s = time.perf_counter() - t0
+    if world > 1:
+        tw = ng.TWave(order, ts, 1.0, device=local, partition=(rank, world, grid))
+    else:
+        tw = ng.TWave(order, ts, 1.0, device=local)
+    e = ts.export()
+    ntents_global = ts.GetNTents()
+    mine = tw.owned_tents() if world > 1 else np.arange(ntents_global)
+    nels = np.diff(e["el_off"])[mine]
+    nnb = np.diff(e["nb_off"])[mine]
+    wf0 = tw.MakeWavefront(f, 0.0)          # host, nel_local x (5*125)
+    tw.SetInitial(wf0)
+    N, Q, ncomp = tw.nbasis, tw.nip, tw.ncomp
+    ndom = np.ones_like(nels)
+    sizes = np.zeros(3, dtype=np.int32)
+    from ngstrefftz_b200._capi import check, iptr, lib
+    check(lib.ngst_twave_basis(tw._h, iptr(sizes), None, None, None))
+    npoly, nnz = int(sizes[1]), int(sizes[2])
+    flops_step, f_el = algorithmic_flops(D, order, N, npoly, nnz, Q, nels, ndom)
+    bytes_step, b_el = algorithmic_bytes(D, Q, ncomp, nels, nnb)
+
+    # boundary datum pre-sampled per slab on the host (it depends on timeshift, src/twavetents.cpp:373-374)
+    bd = dirichlet(f, D)
+    tw.SetBoundaryCF(bd)
+    nsteps_total = args.warmup + args.steps
+    bvals = []
+    h = ts.GetSlabHeight()
+    for i in range(2 * nsteps_total + 2):
+        bvals.append(tw.sample_boundary(i * h))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------- resident arm: state stays in HBM, boundary samples uploaded before the timed Propagate
+    step = 0
+    for _ in range(args.warmup):
+        tw.propagate_with_values(bvals[step]); step += 1
+    barrier()
+    clk = ClockSampler(local)
+    dev_ms, launches = [], 0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        tw.propagate_with_values(bvals[step]); step += 1
+        dev_ms.append(tw.last_ms())
+        launches += tw.last_launches()
+    barrier()
+    wall_s = time.perf_counter() - t0
+    clocks = clk.stop()
+    dev_s = float(np.sum(dev_ms)) * 1e-3
+    energy = tw.Energy()
+
+    # ---------------- e2e arm: the plugin call sequence with HOST buffers inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        nbytes = wf0.nbytes
+        pin_in = torch.empty(wf0.size, dtype=torch.float64, pin_memory=True)
+        pin_out = torch.empty(wf0.size, dtype=torch.float64, pin_memory=True)
+        pin_in.numpy()[:] = wf0.reshape(-1)
+        bpin = [torch.from_numpy(b).pin_memory() if b is not None else None for b in bvals[:1]]
+        b0 = bpin[0]
+        in_ptr = _capi.C.cast(pin_in.data_ptr(), _capi.c_dp)
+        out_ptr = _capi.C.cast(pin_out.data_ptr(), _capi.c_dp)
+        b_ptr = _capi.C.cast(b0.data_ptr(), _capi.c_dp) if b0 is not None else None
+        nb = 0 if b0 is None else b0.numel()
+
+        def e2e_step():
+            tw.reset_time()
+            check(lib.ngst_twave_set_initial(tw._h, in_ptr, ncomp))               # H2D: state rows
+            check(lib.ngst_twave_set_boundary_values(tw._h, b_ptr, nb))            # H2D: boundary samples
+            check(lib.ngst_twave_propagate(tw._h))
+            check(lib.ngst_twave_get_wavefront(tw._h, out_ptr))                    # D2H: state rows
+
+        for _ in range(args.warmup):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        barrier()
+        e2e_s = time.perf_counter() - t0
+        e2e = {"sec": e2e_s, "h2d": int(nbytes + nb * 8), "d2h": int(nbytes)}
+
+    # ---------------- reduce over ranks (max time, sum units)
+    ntents_local = len(mine)
+    stats = torch.tensor([dev_s, wall_s, e2e["sec"] if e2e else 0.0, float(ntents_local), flops_step, bytes_step,
+                          float(launches), float(nels.sum())], dtype=torch.float64, device="cuda")
+    if world > 1:
+        mx = stats.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = stats.clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+    else:
+        mx, sm = stats, stats
+    mx, sm = mx.cpu().numpy(), sm.cpu().numpy()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    dev_s, wall_s, e2e_s = mx[0], mx[1], mx[2]
+    tents_step = sm[3]
+    value = tents_step * args.steps / dev_s
+
+    # ---------------- roofline of the dominant kernel (the per-level tent kernel; every launch in the step is it)
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            peaks = json.load(fh)
+    except OSError:
+        pass
+    hbm_peak, hbm_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    dfma = _capi.C.c_double(0)
+    dmma = _capi.C.c_double(0)
+    check(lib.ngst_device_fp64_peak(local, 0, _capi.C.byref(dfma)))
+    check(lib.ngst_device_fp64_peak(local, 1, _capi.C.byref(dmma)))
+    fp64_peak = max(dfma.value, dmma.value)
+    flops_rank0 = flops_step * args.steps
+    ach_tf = flops_rank0 / (float(np.sum(dev_ms)) * 1e-3) * 1e-12
+    ach_gbs = bytes_step * args.steps / (float(np.sum(dev_ms)) * 1e-3) * 1e-9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        try:
+            with open(tpath) as fh:
+                # ncu --set full capture (profiles/): DRAM bytes per tent x the tents of an average launch of this run
+                traffic = json.load(fh).get("dram_bytes_per_tent") * tents_step * args.steps / max(sm[6], 1)
+        except (OSError, ValueError):
+            traffic = None
+    roofline = {"bound": "fp64", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach_tf / fp64_peak,
+                "traffic": traffic, "kernel": tw.kernel_name(),
+                "peak_source": f"measured live on this GPU: DFMA {dfma.value:.2f} / DMMA m8n8k4 {dmma.value:.2f} TFLOP/s "
+                               f"(ngst_device_fp64_peak); MEASURED_PEAKS.json holds no FP64 figure",
+                "flops_per_tent_element": f_el, "launches_per_step": launches / max(args.steps, 1),
+                "hbm": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s",
+                        "frac": ach_gbs / hbm_peak, "peak_source": hbm_src, "bytes_per_tent_element": b_el}}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": "tents/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "dof_updates_per_s": value * N,
+        "config": {"workload": f"3+1D unit-cube brick {cells[0]}x{cells[1]}x{cells[2]} cells x 6 tets, order {order}, "
+                               f"c=1, standing wave, Dirichlet, dt={args.dt}, edge pitching local_ct global_ct=2/3",
+                   "tets": int(np.prod(cells) * 6), "order": order, "nbasis": N, "nip": Q,
+                   "slab_tents": int(ntents_global), "levels": ts.GetNLayers(), "tent_elements": int(sm[7]),
+                   "parallelism": f"spatial partition {grid[0]}x{grid[1]}x{grid[2]}" if world > 1 else "single GPU",
+                   "l2": f"state {wf0.nbytes * world / 1e6:.0f} MB per slab > 126 MB L2 (no flush needed)",
+                   "pitch_s": pitch_s},
+        "wall_ms_per_step": 1e3 * wall_s / args.steps,
+        "gpu_launches": int(sm[6]),
+        "clocks": clocks,
+        "roofline": roofline,
+        "energy_after": energy,
+    }
+    if e2e:
+        line["e2e"] = {"value": tents_step * args.steps / e2e_s, "unit": "tents/s",
+                       "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"],
+                       "ms_per_step": 1e3 * e2e_s / args.steps,
+                       "path": "ngst_twave_set_initial + set_boundary_values + propagate + get_wavefront on pinned host buffers"}
+    if not args.no_cpu_baseline and world >= 1:
+        cores = os.cpu_count() or 1
+        sample = args.cpu_sample_tents or 4000
+        r = cpu_sample(args, [args.cells] * 3, sample, 1, 1, cores)
+        line["cpu_baseline"] = {"value": r["tents_per_s"], "unit": "tents/s", "cores": cores, "kind": "port",
+                                "sample": f"first {r['sample_tents']} tents (level order) of the N=1 slab "
+                                          f"({r['slab_tents']} tents), 1 warm-up + 1 timed pass, oracle restatement of "
+                                          f"the reference's Propagate with OpenMP over the tents of a level"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -99,6 +99,11 @@ int ngst_twave_set_boundary_values(ngst_twave* t, const double* values, long lon
 /* Propagate src/twavetents.cpp:72-175: one slab, timeshift += slab height. */
 int ngst_twave_propagate(ngst_twave* t);
 double ngst_twave_timeshift(const ngst_twave* t);
+/* Rewind / set the accumulated time (the reference's `timeshift` member, src/twavetents.hpp:106, is only ever
+ * advanced by Propagate; re-running a slab from the same initial data needs it reset). */
+int ngst_twave_set_timeshift(ngst_twave* t, double timeshift);
+/* name of the CUDA kernel variant Propagate launches for this solver (diagnostics / bench.py) */
+const char* ngst_twave_kernel_name(const ngst_twave* t);
 /* device time of the last Propagate in ms (CUDA events on the solver's stream) and kernel launches in it */
 double ngst_twave_last_ms(const ngst_twave* t);
 int ngst_twave_last_launches(const ngst_twave* t);

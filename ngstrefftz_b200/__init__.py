@@ -315,7 +315,7 @@ class TWaveTents(TrefftzTents):
     def SetBoundaryCF(self, bddatum):
         self._bddatum = bddatum
 
-    def _boundary_values(self):
+    def _boundary_values(self, timeshift=None):
         npts = lib.ngst_twave_boundary_npoints(self._h)
         if self._bddatum is None or npts == 0:
             return None
@@ -325,7 +325,7 @@ class TWaveTents(TrefftzTents):
             check(lib.ngst_twave_boundary_points(self._h, dptr(xt), iptr(kind)))
             self._bnd_pts = (xt, kind)
         xt, kind = self._bnd_pts
-        t = xt[:, self.D] + lib.ngst_twave_timeshift(self._h)
+        t = xt[:, self.D] + (lib.ngst_twave_timeshift(self._h) if timeshift is None else float(timeshift))
         x = np.ascontiguousarray(xt[:, :self.D])
         cf = self._bddatum
         Q, D = self.nip, self.D
@@ -350,10 +350,23 @@ class TWaveTents(TrefftzTents):
         return np.ascontiguousarray(np.concatenate(out))
 
     def Propagate(self):
-        vals = self._boundary_values()
+        self.propagate_with_values(self._boundary_values())
+
+    def sample_boundary(self, timeshift):
+        """Boundary datum sampled for the slab that starts at `timeshift` (src/twavetents.cpp:373-374)."""
+        return self._boundary_values(timeshift)
+
+    def propagate_with_values(self, vals):
+        """Propagate with pre-sampled boundary values (the array ngst_twave_set_boundary_values takes)."""
         n = 0 if vals is None else len(vals)
         check(lib.ngst_twave_set_boundary_values(self._h, dptr(vals), n))
         check(lib.ngst_twave_propagate(self._h))
+
+    def reset_time(self, timeshift=0.0):
+        check(lib.ngst_twave_set_timeshift(self._h, float(timeshift)))
+
+    def kernel_name(self):
+        return lib.ngst_twave_kernel_name(self._h).decode()
 
     # ---- DeclareETClass methods (src/twavetents.cpp:1160-1178)
     def GetWavefront(self):

@@ -249,6 +249,10 @@ int ngst_twave_propagate(ngst_twave* t) {
 }
 
 double ngst_twave_timeshift(const ngst_twave* t) { return t ? t->solver->timeshift() : 0.0; }
+int ngst_twave_set_timeshift(ngst_twave* t, double timeshift) {
+  return guarded([&] { need(t, "solver"); t->solver->set_timeshift(timeshift); });
+}
+const char* ngst_twave_kernel_name(const ngst_twave* t) { return t ? t->solver->kernel_name() : ""; }
 double ngst_twave_last_ms(const ngst_twave* t) { return t ? t->solver->last_ms() : 0.0; }
 int ngst_twave_last_launches(const ngst_twave* t) { return t ? t->solver->last_launches() : 0; }
 

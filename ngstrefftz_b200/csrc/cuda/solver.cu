@@ -167,8 +167,8 @@ void Solver::SetInitial(const double* wf, int ncomp) {
   ncomp_ = ncomp;
   basis_ = fosystem_ ? basis_fo_ : basis_so_;
   const size_t bytes = (size_t)mesh_.nel * ncomp * rule_.nip * sizeof(double);
-  if (d_wavefront_) { CU(cudaFree(d_wavefront_)); d_wavefront_ = nullptr; }
-  CU(cudaMalloc(&d_wavefront_, bytes));
+  if (d_wavefront_ && wavefront_bytes_ != bytes) { CU(cudaFree(d_wavefront_)); d_wavefront_ = nullptr; }
+  if (!d_wavefront_) { CU(cudaMalloc(&d_wavefront_, bytes)); wavefront_bytes_ = bytes; }
   CU(cudaMemcpyAsync(d_wavefront_, wf, bytes, cudaMemcpyHostToDevice, stream_));
   CU(cudaStreamSynchronize(stream_));
   have_initial_ = true;

@@ -44,6 +44,8 @@ class Solver {
   double MaxAdiam() const;
 
   double timeshift() const { return timeshift_; }
+  void set_timeshift(double t) { timeshift_ = t; }
+  const char* kernel_name() const { return kernel_name_; }
   double last_ms() const { return last_ms_; }
   int last_launches() const { return last_launches_; }
 
@@ -81,6 +83,8 @@ class Solver {
   int* d_col_[2] = {nullptr, nullptr};
   double* d_val_[2] = {nullptr, nullptr};
   BasisCsr basis_so_, basis_fo_;
+  const char* kernel_name_ = "tent_kernel_generic";
+  size_t wavefront_bytes_ = 0;
   int threads_ = 256;
   size_t smem_ = 0;
 };

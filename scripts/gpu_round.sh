@@ -1,0 +1,17 @@
+#!/bin/bash
+# One GPU-box visit: parity tests, smoke, bench, then ncu launch list + one full capture of the tent kernel.
+set -u
+mkdir -p gpurun_out
+nvidia-smi -L; nproc
+python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/smoke.log
+python bench.py --steps 3 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; cat gpurun_out/bench.json; tail -3 gpurun_out/bench.err
+python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"; cat gpurun_out/bench_ref.json
+SMALL="python bench.py --cells 12 --steps 2 --warmup 3 --no-cpu-baseline --no-e2e"
+$SMALL > gpurun_out/plain_small.log 2>&1 && \
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $SMALL > gpurun_out/ncu_launches.log 2>&1
+echo "ncu launches rc=$?"
+$SMALL > gpurun_out/plain_small2.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:tent_kernel -s 60 -c 3 -f -o gpurun_out/prof_tent $SMALL > gpurun_out/ncu_full.log 2>&1
+echo "ncu full rc=$?"
+ls -la gpurun_out
