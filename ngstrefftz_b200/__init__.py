@@ -368,6 +368,13 @@ class TWaveTents(TrefftzTents):
     def kernel_name(self):
         return lib.ngst_twave_kernel_name(self._h).decode()
 
+    def set_kernel_mode(self, mode):
+        """0 = automatic routing (DMMA kernel for single-wavespeed tents), 1 = generic DFMA kernel for every tent."""
+        check(lib.ngst_twave_set_kernel_mode(self._h, int(mode)))
+
+    def ntents_fast(self):
+        return lib.ngst_twave_ntents_fast(self._h)
+
     # ---- DeclareETClass methods (src/twavetents.cpp:1160-1178)
     def GetWavefront(self):
         wf = np.zeros((self.nel, self.ncomp * self.nip))

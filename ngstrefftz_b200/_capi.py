@@ -68,6 +68,8 @@ _SIGS = {
     "ngst_twave_timeshift": (C.c_double, [c_vp]),
     "ngst_twave_set_timeshift": (C.c_int, [c_vp, C.c_double]),
     "ngst_twave_kernel_name": (C.c_char_p, [c_vp]),
+    "ngst_twave_set_kernel_mode": (C.c_int, [c_vp, C.c_int]),
+    "ngst_twave_ntents_fast": (C.c_int, [c_vp]),
     "ngst_twave_last_ms": (C.c_double, [c_vp]),
     "ngst_twave_last_launches": (C.c_int, [c_vp]),
     "ngst_twave_get_wavefront": (C.c_int, [c_vp, c_dp]),

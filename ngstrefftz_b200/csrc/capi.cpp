@@ -253,6 +253,14 @@ int ngst_twave_set_timeshift(ngst_twave* t, double timeshift) {
   return guarded([&] { need(t, "solver"); t->solver->set_timeshift(timeshift); });
 }
 const char* ngst_twave_kernel_name(const ngst_twave* t) { return t ? t->solver->kernel_name() : ""; }
+int ngst_twave_set_kernel_mode(ngst_twave* t, int mode) {
+  return guarded([&] {
+    need(t, "solver");
+    if (mode < 0 || mode > 1) throw std::invalid_argument("ngst_twave_set_kernel_mode: mode must be 0 or 1");
+    t->solver->set_kernel_mode(mode);
+  });
+}
+int ngst_twave_ntents_fast(const ngst_twave* t) { return t ? t->solver->ntents_fast() : 0; }
 double ngst_twave_last_ms(const ngst_twave* t) { return t ? t->solver->last_ms() : 0.0; }
 int ngst_twave_last_launches(const ngst_twave* t) { return t ? t->solver->last_launches() : 0; }
 

@@ -100,7 +100,44 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
   a.tf_data = Upload(staged_.tf_data);
   a.bnd_data = nullptr;
   a.max_ndom = staged_.max_ndom;
-  d_level_tents_ = Upload(slab_.level_tents);
+  // ---- kernel routing: single-wavespeed tents run on the fast DMMA kernel when a variant exists for (D, order)
+  fast_ = tent_fast_available(D, order);
+  if (fast_) {
+    fstage_ = stage_fast(mesh_, slab_, staged_, c_el_, rule_, basis_so_, basis_fo_, fast_fe_stride(D), fast_ff_stride(D));
+    fargs_.fe = Upload(fstage_.fe);
+    fargs_.ff = Upload(fstage_.ff);
+    fargs_.sqrtw = Upload(fstage_.sqrtw);
+    fargs_.dmap = Upload(fstage_.dmap);
+    fargs_.dfac = Upload(fstage_.dfac);
+    for (int f = 0; f < 2; f++) {
+      d_cptr_[f] = Upload(fstage_.cptr[f]);
+      d_crow_[f] = Upload(fstage_.crow[f]);
+      d_cval_[f] = Upload(fstage_.cval[f]);
+    }
+  }
+  {
+    const int nlev = (int)slab_.level_off.size() - 1;
+    std::vector<int> gen, fast;
+    gen_off_.assign(1, 0);
+    fast_off_.assign(1, 0);
+    for (int l = 0; l < nlev; l++) {
+      const size_t f0 = fast.size();
+      for (int i = slab_.level_off[l]; i < slab_.level_off[l + 1]; i++) {
+        const int t = slab_.level_tents[i];
+        if (fast_ && fstage_.ok[t]) fast.push_back(t);
+        else gen.push_back(t);
+      }
+      // most expensive tents first (the order inside a level is free: tents of a level share no element)
+      std::stable_sort(fast.begin() + f0, fast.end(), [&](int x, int y) {
+        return staged_.te_off[x + 1] - staged_.te_off[x] > staged_.te_off[y + 1] - staged_.te_off[y];
+      });
+      gen_off_.push_back((int)gen.size());
+      fast_off_.push_back((int)fast.size());
+    }
+    d_level_tents_ = Upload(gen);
+    d_level_all_ = Upload(slab_.level_tents);
+    d_level_fast_ = Upload(fast);
+  }
   CU(cudaMalloc(&d_singular_, sizeof(int)));
   allocs_.push_back(d_singular_);
   CU(cudaMemset(d_singular_, 0, sizeof(int)));
@@ -182,6 +219,9 @@ void Solver::SetInitial(const double* wf, int ncomp) {
   a.ncomp = ncomp_;
   a.fosystem = fosystem_;
   a.wavefront = d_wavefront_;
+  fargs_.cptr = d_cptr_[fosystem_];
+  fargs_.crow = d_crow_[fosystem_];
+  fargs_.cval = d_cval_[fosystem_];
   // chunk of quadrature points staged in shared memory at a time
   const size_t budget = 100 * 1024;
   int qc = std::min(rule_.nip, 32);
@@ -214,13 +254,28 @@ void Solver::Propagate() {
   const int nlev = (int)slab_.level_off.size() - 1;
   int launches = 0;
   CU(cudaEventRecord(ev0_, stream_));
-  for (int l = 0; l < nlev; l++) {
+  for (int l = 0; l < nlev && force_generic_; l++) {
     TentKernelArgs a = args_;
-    a.tents = d_level_tents_ + slab_.level_off[l];
+    a.tents = d_level_all_ + slab_.level_off[l];
     a.ntents = slab_.level_off[l + 1] - slab_.level_off[l];
     if (a.ntents == 0) continue;
     CU(launch_tent_generic(mesh_.D, a, threads_, smem_, stream_));
     launches++;
+  }
+  for (int l = 0; l < nlev && !force_generic_; l++) {
+    TentKernelArgs a = args_;
+    a.tents = d_level_fast_ + fast_off_[l];
+    a.ntents = fast_off_[l + 1] - fast_off_[l];
+    if (a.ntents > 0) {
+      CU(launch_tent_fast(mesh_.D, order_, fosystem_, a, fargs_, stream_));
+      launches++;
+    }
+    a.tents = d_level_tents_ + gen_off_[l];
+    a.ntents = gen_off_[l + 1] - gen_off_[l];
+    if (a.ntents > 0) {
+      CU(launch_tent_generic(mesh_.D, a, threads_, smem_, stream_));
+      launches++;
+    }
   }
   CU(cudaEventRecord(ev1_, stream_));
   CU(cudaEventSynchronize(ev1_));

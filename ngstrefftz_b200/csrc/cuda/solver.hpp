@@ -10,6 +10,7 @@
 #include "../host/pitcher.hpp"
 #include "../host/quadrature.hpp"
 #include "../host/stage.hpp"
+#include "tent_fast.cuh"
 #include "tent_kernel.cuh"
 
 namespace ngst {
@@ -45,7 +46,10 @@ class Solver {
 
   double timeshift() const { return timeshift_; }
   void set_timeshift(double t) { timeshift_ = t; }
-  const char* kernel_name() const { return kernel_name_; }
+  const char* kernel_name() const { return (fast_ && !force_generic_) ? "tent_kernel_fast" : "tent_kernel_generic"; }
+  int ntents_fast() const { return fast_ ? fast_off_.back() : 0; }
+  // 0 = automatic routing (fast kernel where possible), 1 = every tent on the generic DFMA kernel (A/B evidence)
+  void set_kernel_mode(int mode) { force_generic_ = mode == 1; }
   double last_ms() const { return last_ms_; }
   int last_launches() const { return last_launches_; }
 
@@ -71,7 +75,16 @@ class Solver {
   cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
   std::vector<void*> allocs_;
   TentKernelArgs args_{};
-  int* d_level_tents_ = nullptr;
+  int* d_level_tents_ = nullptr;   // per level: generic-kernel tents (material interfaces or no fast variant)
+  int* d_level_fast_ = nullptr;    // per level: fast-kernel tents, most elements first
+  std::vector<int> gen_off_, fast_off_;  // nlevels + 1 offsets into the two lists
+  bool fast_ = false, force_generic_ = false;
+  int* d_level_all_ = nullptr;     // per level: all tents (slab order), for force_generic_
+  FastStage fstage_;
+  FastArgs fargs_{};
+  int* d_cptr_[2] = {nullptr, nullptr};
+  int* d_crow_[2] = {nullptr, nullptr};
+  double* d_cval_[2] = {nullptr, nullptr};
   double* d_wavefront_ = nullptr;
   double* d_bnd_ = nullptr;
   double* d_elw_ = nullptr;   // nel*nip weights |detJ| w
@@ -83,7 +96,6 @@ class Solver {
   int* d_col_[2] = {nullptr, nullptr};
   double* d_val_[2] = {nullptr, nullptr};
   BasisCsr basis_so_, basis_fo_;
-  const char* kernel_name_ = "tent_kernel_generic";
   size_t wavefront_bytes_ = 0;
   int threads_ = 256;
   size_t smem_ = 0;

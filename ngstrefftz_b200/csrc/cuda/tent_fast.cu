@@ -1,0 +1,552 @@
+// Fast per-tent Trefftz-DG kernel for single-wavespeed tents (ndomains == 1), sm_100a.
+//
+// Same mathematics as tent_generic.cu / TWaveTents<D>::Propagate's per-tent body (src/twavetents.cpp:92-171:
+// CalcTentEl 177-333, CalcTentBndEl 335-434, Solve 64-70, CalcTentElEval 541-590), re-organised for the B200:
+//   * one CTA of 4 warps per tent, two CTAs per SM;
+//   * the flat list of (element, quadrature point) pairs of the tent is processed in chunks of 32 points:
+//     lane = point, warp = one quarter of the basis functions. Each warp evaluates its functions with the
+//     generated straight-line evaluators (basis_eval_gen.cuh; the reference evaluates the same polynomials through
+//     CSR tables, src/scalarmappedfe.cpp:437-674) and writes the weighted operand Z[function][k-row] to shared memory;
+//   * the Gram contractions elmat += B W B^T (top faces, src/twavetents.cpp:293-312) and elmat += S diag(w) S^T
+//     (bottom faces, 255-262) run on the FP64 tensor path (mma.sync m8n8k4 f64, "DMMA"). W is symmetric positive
+//     definite on a causal face, so with W = L L^T and Z = B L the update is the symmetric rank-k product Z Z^T:
+//     only the upper-triangular 8x8 tiles are accumulated, in registers, split over the 4 warps as
+//     (tile half) x (k-step parity);
+//   * right-hand sides are accumulated per lane in registers and reduced once per tent;
+//   * boundary faces (Dirichlet / Neumann) are rank-1 per point, A += l r^T, and use the same DMMA machinery on all
+//     tiles; pivoted LU in shared memory; the top-face evaluation runs in the monomial basis (one thread per point).
+// Tents with material interfaces (ndomains > 1) are routed to the generic kernel by the host.
+#include <cuda_runtime.h>
+
+#include "basis_eval_gen.cuh"
+#include "tent_fast.cuh"
+#include "tent_kernel.cuh"
+
+namespace ngst {
+
+namespace {
+
+constexpr int kChunk = 32;   // quadrature points per chunk (one per lane)
+constexpr int kThreads = 128;
+constexpr int kBS = 36;      // row stride of the boundary-pass operands (== 4 mod 16)
+
+__device__ __forceinline__ void dmma_m8n8k4(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+               : "+d"(c0), "+d"(c1)
+               : "d"(a), "d"(b));
+}
+
+constexpr int ipow(int b, int e) { return e == 0 ? 1 : b * ipow(b, e - 1); }
+constexpr int cbinom(int n, int k) { return (k < 0 || k > n) ? 0 : (k == 0 ? 1 : cbinom(n - 1, k - 1) * n / k); }
+
+template <int D, int P, int FO>
+struct Cfg {
+  static constexpr int d1 = D + 1;
+  static constexpr int N = gen::BasisInfo<D, P, FO>::N;
+  static constexpr int npoly = gen::BasisInfo<D, P, FO>::npoly;
+  static constexpr int npm1 = cbinom(d1 + P - 1, P - 1);  // monomials of degree <= P-1
+  static constexpr int NT = (N + 7) / 8;          // 8x8 tiles per dimension
+  static constexpr int NP = NT * 8;               // padded system size
+  static constexpr int G = NP / 4;                // functions per evaluation group (function i -> group i % 4)
+  static constexpr int Q = (D == 1) ? (P + 1) : ipow(P + 1, D);  // points of the order-2P rule (quadrature.cpp)
+  static constexpr int ZS = kChunk * d1 + 4;      // row stride of Z: == 4 (mod 16) -> conflict-free fragment loads
+  static constexpr int LDA = NP + 1;
+  static constexpr int NSYM = NT * (NT + 1) / 2;  // upper-triangular tiles
+  static constexpr int NACC = (NSYM + 1) / 2;     // accumulator tiles per warp (>= ceil(NT*NT/4) for NT >= 2)
+  static constexpr int FE = fast_fe_stride(D);
+  static constexpr int FF = fast_ff_stride(D);
+  // shared memory (doubles)
+  static constexpr int oA = 0;
+  static constexpr int oB = oA + NP * LDA;
+  static constexpr int oZ = (oB + NP + 1) / 2 * 2;
+  static constexpr int oCM = oZ + NP * ZS;
+  static constexpr int oCMD = oCM + npoly;
+  static constexpr int nsmem = oCMD + d1 * npm1;
+  static_assert(2 * kBS <= ZS, "boundary operands must fit in the Z buffer");
+  static_assert(NT >= 2 && (NT * NT + 3) / 4 <= NACC, "accumulator budget");
+};
+
+// Symmetric rank-k update of this warp's upper-triangular tiles from the operand rows Z[function][k-row]:
+// tile L (row-major over ti <= tj) belongs to tile half L & 1; k-steps ks = kh, kh+2, .. < nks.
+template <int NT, int NACC, int TH>
+__device__ __forceinline__ void dmma_sym(double (&acc)[NACC][2], const double* __restrict__ Z, int ZS, int nks, int kh,
+                                         int g, int k) {
+  for (int ks = kh; ks < nks; ks += 2) {
+    double fr[NT];
+#pragma unroll
+    for (int t = 0; t < NT; t++) fr[t] = Z[(8 * t + g) * ZS + 4 * ks + k];
+    int L = 0;
+#pragma unroll
+    for (int ti = 0; ti < NT; ti++)
+#pragma unroll
+      for (int tj = ti; tj < NT; tj++) {
+        if ((L & 1) == TH) dmma_m8n8k4(acc[L >> 1][0], acc[L >> 1][1], fr[ti], fr[tj]);
+        L++;
+      }
+  }
+}
+
+// acc -> A (upper-triangular tiles of this warp's half); add = false stores, true accumulates.
+template <int NT, int NACC, int TH>
+__device__ __forceinline__ void flush_sym(const double (&acc)[NACC][2], double* A, int LDA, bool add, int g, int k) {
+  int L = 0;
+#pragma unroll
+  for (int ti = 0; ti < NT; ti++)
+#pragma unroll
+    for (int tj = ti; tj < NT; tj++) {
+      if ((L & 1) == TH) {
+        double* p = A + (8 * ti + g) * LDA + 8 * tj + 2 * k;
+        if (add) { p[0] += acc[L >> 1][0]; p[1] += acc[L >> 1][1]; }
+        else { p[0] = acc[L >> 1][0]; p[1] = acc[L >> 1][1]; }
+      }
+      L++;
+    }
+}
+
+// General (non-symmetric) update A += ZL ZR^T over 8 k-steps; tile L = ti*NT + tj belongs to warp L & 3 (= W).
+template <int NT, int NACC, int W>
+__device__ __forceinline__ void dmma_full(double (&acc)[NACC][2], const double* __restrict__ ZL,
+                                          const double* __restrict__ ZR, int g, int k) {
+  for (int ks = 0; ks < kChunk / 4; ks++) {
+    double fl[NT], fr[NT];
+#pragma unroll
+    for (int t = 0; t < NT; t++) {
+      fl[t] = ZL[(8 * t + g) * kBS + 4 * ks + k];
+      fr[t] = ZR[(8 * t + g) * kBS + 4 * ks + k];
+    }
+    int L = 0;
+#pragma unroll
+    for (int ti = 0; ti < NT; ti++)
+#pragma unroll
+      for (int tj = 0; tj < NT; tj++) {
+        if ((L & 3) == W) dmma_m8n8k4(acc[L >> 2][0], acc[L >> 2][1], fl[ti], fr[tj]);
+        L++;
+      }
+  }
+}
+
+template <int NT, int NACC, int W>
+__device__ __forceinline__ void flush_full(const double (&acc)[NACC][2], double* A, int LDA, int g, int k) {
+  int L = 0;
+#pragma unroll
+  for (int ti = 0; ti < NT; ti++)
+#pragma unroll
+    for (int tj = 0; tj < NT; tj++) {
+      if ((L & 3) == W) {
+        double* p = A + (8 * ti + g) * LDA + 8 * tj + 2 * k;
+        p[0] += acc[L >> 2][0];
+        p[1] += acc[L >> 2][1];
+      }
+      L++;
+    }
+}
+
+// group dispatch: warp w evaluates the functions i with i % 4 == w
+template <int D, int P, int FO, class F>
+__device__ __forceinline__ void eval_group(int w, const double* xi, F&& f) {
+  switch (w) {
+    case 0: gen::BasisGroup<D, P, FO, 0>::eval(xi, f); break;
+    case 1: gen::BasisGroup<D, P, FO, 1>::eval(xi, f); break;
+    case 2: gen::BasisGroup<D, P, FO, 2>::eval(xi, f); break;
+    default: gen::BasisGroup<D, P, FO, 3>::eval(xi, f); break;
+  }
+}
+
+template <int D, int P, int FO>
+__global__ void __launch_bounds__(kThreads, 2) tent_kernel_fast(TentKernelArgs a, FastArgs f) {
+  using C = Cfg<D, P, FO>;
+  constexpr int d1 = C::d1, N = C::N, NT = C::NT, NP = C::NP, G = C::G, Q = C::Q, ZS = C::ZS, LDA = C::LDA;
+  constexpr int NACC = C::NACC, FE = C::FE, FF = C::FF, npoly = C::npoly, npm1 = C::npm1;
+  extern __shared__ double sm[];
+  double* const A = sm + C::oA;
+  double* const bv = sm + C::oB;
+  double* const Z = sm + C::oZ;
+  double* const cm = sm + C::oCM;
+  double* const cmd = sm + C::oCMD;
+
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int g = lane >> 2, k = lane & 3;  // DMMA fragment coordinates
+  const int th = w >> 1, kh = w & 1;      // tile half / k-step parity of this warp in the symmetric passes
+  const int tent = a.tents[blockIdx.x];
+  const int te0 = a.te_off[tent], nel = a.te_off[tent + 1] - te0;
+  const int tf0 = a.tf_off[tent], nfc = a.tf_off[tent + 1] - tf0;
+  const int npts = nel * Q;
+
+  for (int i = tid; i < NP * ZS; i += kThreads) Z[i] = 0.0;  // rows of the padding functions stay zero
+  double acc[NACC][2];
+#pragma unroll
+  for (int i = 0; i < NACC; i++) acc[i][0] = acc[i][1] = 0.0;
+  double bpart[G];
+#pragma unroll
+  for (int j = 0; j < G; j++) bpart[j] = 0.0;
+  __syncthreads();
+
+  // ------------------------------------------------------------------ top faces: A += B W B^T  (twavetents.cpp:270-313)
+  for (int c0 = 0; c0 < npts; c0 += kChunk) {
+    const int idx = c0 + lane;
+    const bool valid = idx < npts;
+    const int idc = valid ? idx : npts - 1;
+    const int te = te0 + idc / Q, q = idc % Q;
+    const double* __restrict__ rec = f.fe + (size_t)te * FE;
+    const double* __restrict__ lm = a.lam + q * d1;
+    double xi[d1];
+#pragma unroll
+    for (int u = 0; u < d1; u++) xi[u] = 0.0;
+#pragma unroll
+    for (int kk = 0; kk < d1; kk++) {
+      const double l = lm[kk];
+#pragma unroll
+      for (int u = 0; u < D; u++) xi[u] = fma(l, rec[fast_fe_xv(D) + kk * D + u], xi[u]);
+      xi[D] = fma(l, rec[fast_fe_tt(D) + kk], xi[D]);
+    }
+    const double sq = valid ? f.sqrtw[q] : 0.0;
+    const double k0 = sq * rec[fast_fe_top(D)];
+    double kd[D];
+#pragma unroll
+    for (int u = 0; u < D; u++) kd[u] = sq * rec[fast_fe_top(D) + 1 + u];
+    const double kt = sq * rec[fast_fe_top(D) + 1 + D];
+    double* const zl = Z + lane;
+    eval_group<D, P, FO>(w, xi, [&](auto ic, double, double e0, double e1, double e2, double e3) {
+      constexpr int i = decltype(ic)::value;
+      const double dv[4] = {e0, e1, e2, e3};
+      double* z = zl + i * ZS;
+#pragma unroll
+      for (int u = 0; u < D; u++) z[u * kChunk] = k0 * dv[u] - kd[u] * dv[D];
+      z[D * kChunk] = kt * dv[D];
+    });
+    __syncthreads();
+    if (th == 0) dmma_sym<NT, NACC, 0>(acc, Z, ZS, d1 * (kChunk / 4), kh, g, k);
+    else dmma_sym<NT, NACC, 1>(acc, Z, ZS, d1 * (kChunk / 4), kh, g, k);
+    __syncthreads();
+  }
+
+  // ------------------------------------------------------------------ bottom faces: rhs (+ stabilisation Gram)  (209-267)
+  for (int c0 = 0; c0 < npts; c0 += kChunk) {
+    const int idx = c0 + lane;
+    const bool valid = idx < npts;
+    const int idc = valid ? idx : npts - 1;
+    const int te = te0 + idc / Q, q = idc % Q;
+    const double* __restrict__ rec = f.fe + (size_t)te * FE;
+    const double* __restrict__ lm = a.lam + q * d1;
+    double xi[d1];
+#pragma unroll
+    for (int u = 0; u < d1; u++) xi[u] = 0.0;
+#pragma unroll
+    for (int kk = 0; kk < d1; kk++) {
+      const double l = lm[kk];
+#pragma unroll
+      for (int u = 0; u < D; u++) xi[u] = fma(l, rec[fast_fe_xv(D) + kk * D + u], xi[u]);
+      xi[D] = fma(l, rec[fast_fe_tb(D) + kk], xi[D]);
+    }
+    const double* __restrict__ wf = a.wavefront + (size_t)a.te_el[te] * ((FO ? d1 : d1 + 1) * Q);
+    const double area = rec[fast_fe_bot(D)];
+    const double* __restrict__ nn = rec + fast_fe_bot(D) + 2;
+    const double s = rec[fast_fe_sc(D)], sc = rec[fast_fe_sc(D) + 1], ic2 = rec[fast_fe_sc(D) + 2];
+    const double om = valid ? a.w[q] * area : 0.0;
+    const double gt = wf[((FO ? 0 : 1) + D) * Q + q];
+    double rho[d1];
+    double ndg = 0.0;
+#pragma unroll
+    for (int u = 0; u < D; u++) {
+      const double gx = wf[((FO ? 0 : 1) + u) * Q + q];
+      rho[u] = -om * s * (nn[D] * gx - nn[u] * gt);
+      ndg = fma(nn[u], gx, ndg);
+    }
+    rho[D] = -om * sc * (nn[D] * ic2 * gt - ndg);
+    const double rho_u = FO ? 0.0 : om * wf[q];
+    const double sqo = valid ? f.sqrtw[q] * rec[fast_fe_bot(D) + 1] : 0.0;
+    double* const zl = Z + lane;
+    eval_group<D, P, FO>(w, xi, [&](auto ic, double v, double e0, double e1, double e2, double e3) {
+      constexpr int i = decltype(ic)::value;
+      const double dv[4] = {e0, e1, e2, e3};
+      double r = FO ? 0.0 : v * rho_u;
+#pragma unroll
+      for (int u = 0; u < d1; u++) r = fma(dv[u], rho[u], r);
+      bpart[i >> 2] += r;
+      if (!FO) zl[i * ZS] = sqo * v;
+    });
+    if (!FO) {
+      __syncthreads();
+      if (th == 0) dmma_sym<NT, NACC, 0>(acc, Z, ZS, kChunk / 4, kh, g, k);
+      else dmma_sym<NT, NACC, 1>(acc, Z, ZS, kChunk / 4, kh, g, k);
+      __syncthreads();
+    }
+  }
+
+  // ------------------------------------------------------------------ accumulators -> A (fixed order: deterministic)
+  if (kh == 0) {
+    if (th == 0) flush_sym<NT, NACC, 0>(acc, A, LDA, false, g, k);
+    else flush_sym<NT, NACC, 1>(acc, A, LDA, false, g, k);
+  }
+  __syncthreads();
+  if (kh == 1) {
+    if (th == 0) flush_sym<NT, NACC, 0>(acc, A, LDA, true, g, k);
+    else flush_sym<NT, NACC, 1>(acc, A, LDA, true, g, k);
+  }
+  __syncthreads();
+  for (int idx = tid; idx < NP * NP; idx += kThreads) {
+    const int i = idx / NP, j = idx % NP;
+    if (j < i && (j >> 3) != (i >> 3)) A[i * LDA + j] = A[j * LDA + i];  // diagonal tiles were computed in full
+  }
+  __syncthreads();
+
+  // ------------------------------------------------------------------ boundary faces (CalcTentBndEl, 335-434)
+  // Dirichlet (404-433): A += sum_q p (om (alpha gamma p - nn))^T, b += om g (alpha gamma p + nn)
+  // Neumann   (380-403): A += sum_q (-nn) (om (p - beta nn))^T,    b += om (n.g) (beta nn + p)
+  // with p = d_t phi, nn = n . grad_x phi (physical derivatives), alpha = beta = 1/2, gamma = 1/c^2.
+  if (nfc > 0) {
+#pragma unroll
+    for (int i = 0; i < NACC; i++) acc[i][0] = acc[i][1] = 0.0;
+    double* const ZL = Z;
+    double* const ZR = Z + NP * kBS;
+    for (int i = tid; i < 2 * NP * kBS; i += kThreads) Z[i] = 0.0;
+    __syncthreads();
+    const int nbp = nfc * Q;
+    for (int c0 = 0; c0 < nbp; c0 += kChunk) {
+      const int idx = c0 + lane;
+      const bool valid = idx < nbp;
+      const int idc = valid ? idx : nbp - 1;
+      const int tf = tf0 + idc / Q, q = idc % Q;
+      const double* __restrict__ rec = f.ff + (size_t)tf * FF;
+      const double* __restrict__ lm = a.lam + q * d1;
+      double xi[d1];
+#pragma unroll
+      for (int u = 0; u < d1; u++) xi[u] = rec[fast_ff_v0(D) + u];
+#pragma unroll
+      for (int m = 0; m < D; m++) {
+        const double l = lm[m];
+#pragma unroll
+        for (int u = 0; u < d1; u++) xi[u] = fma(l, rec[fast_ff_e(D) + m * d1 + u], xi[u]);
+      }
+      double nrm[D];
+#pragma unroll
+      for (int u = 0; u < D; u++) nrm[u] = rec[fast_ff_n(D) + u];
+      const double area = rec[fast_ff_misc(D)], s = rec[fast_ff_misc(D) + 1], sc = rec[fast_ff_misc(D) + 2];
+      const double ic2 = rec[fast_ff_misc(D) + 3];
+      const bool neumann = rec[fast_ff_misc(D) + 4] != 0.0;
+      const double om = valid ? a.w[q] * area : 0.0;
+      double gdat = 0.0;
+      if (a.bnd_data) {
+        const long long off = a.tf_data[tf];
+        if (neumann) {
+#pragma unroll
+          for (int r = 0; r < D; r++) gdat = fma(nrm[r], a.bnd_data[off + (long long)r * Q + q], gdat);
+        } else {
+          gdat = a.bnd_data[off + q];
+        }
+      }
+      const double og = om * gdat;
+      double* const zl = ZL + lane;
+      double* const zr = ZR + lane;
+      eval_group<D, P, FO>(w, xi, [&](auto ic, double, double e0, double e1, double e2, double e3) {
+        constexpr int i = decltype(ic)::value;
+        const double dv[4] = {e0, e1, e2, e3};
+        const double p = sc * dv[D];
+        double nd = 0.0;
+#pragma unroll
+        for (int u = 0; u < D; u++) nd = fma(nrm[u], dv[u], nd);
+        nd *= s;
+        double lv, rv, bc;
+        if (neumann) { lv = -nd; rv = om * (p - 0.5 * nd); bc = og * (0.5 * nd + p); }
+        else { lv = p; rv = om * (0.5 * ic2 * p - nd); bc = og * (0.5 * ic2 * p + nd); }
+        zl[i * kBS] = lv;
+        zr[i * kBS] = rv;
+        bpart[i >> 2] += bc;
+      });
+      __syncthreads();
+      switch (w) {
+        case 0: dmma_full<NT, NACC, 0>(acc, ZL, ZR, g, k); break;
+        case 1: dmma_full<NT, NACC, 1>(acc, ZL, ZR, g, k); break;
+        case 2: dmma_full<NT, NACC, 2>(acc, ZL, ZR, g, k); break;
+        default: dmma_full<NT, NACC, 3>(acc, ZL, ZR, g, k); break;
+      }
+      __syncthreads();
+    }
+    switch (w) {
+      case 0: flush_full<NT, NACC, 0>(acc, A, LDA, g, k); break;
+      case 1: flush_full<NT, NACC, 1>(acc, A, LDA, g, k); break;
+      case 2: flush_full<NT, NACC, 2>(acc, A, LDA, g, k); break;
+      default: flush_full<NT, NACC, 3>(acc, A, LDA, g, k); break;
+    }
+  }
+
+  // ------------------------------------------------------------------ right-hand side: reduce the per-lane partial sums
+#pragma unroll
+  for (int j = 0; j < G; j++) {
+    double v = bpart[j];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) bv[4 * j + w] = v;
+  }
+  __syncthreads();
+  for (int i = N + tid; i < NP; i += kThreads) A[i * LDA + i] = 1.0;  // padding rows: identity
+  __syncthreads();
+
+  // ------------------------------------------------------------------ Solve (LU with partial pivoting; 64-70 forms the inverse)
+  __shared__ int piv_row;
+  __shared__ double piv_inv;
+  for (int kk = 0; kk < NP; kk++) {
+    if (tid < 32) {
+      double best = -1.0;
+      int brow = kk;
+      for (int r = kk + tid; r < NP; r += 32) {
+        const double v = fabs(A[r * LDA + kk]);
+        if (v > best) { best = v; brow = r; }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const double ob = __shfl_down_sync(0xffffffffu, best, o);
+        const int orow = __shfl_down_sync(0xffffffffu, brow, o);
+        if (ob > best || (ob == best && orow < brow)) { best = ob; brow = orow; }
+      }
+      if (tid == 0) {
+        piv_row = brow;
+        if (best == 0.0) { atomicAdd(a.singular, 1); piv_inv = 0.0; }
+        else piv_inv = 1.0 / A[brow * LDA + kk];
+      }
+    }
+    __syncthreads();
+    const int p = piv_row;
+    if (p != kk) {
+      for (int cidx = tid; cidx <= NP; cidx += kThreads) {
+        if (cidx < NP) {
+          const double t0 = A[kk * LDA + cidx];
+          A[kk * LDA + cidx] = A[p * LDA + cidx];
+          A[p * LDA + cidx] = t0;
+        } else {
+          const double t0 = bv[kk]; bv[kk] = bv[p]; bv[p] = t0;
+        }
+      }
+      __syncthreads();
+    }
+    const double pinv = piv_inv;
+    const int nr = NP - kk - 1, nc = NP - kk;  // columns kk+1..NP-1 and the right-hand side
+    for (int idx = tid; idx < nr * nc; idx += kThreads) {
+      const int r = kk + 1 + idx / nc, cc = idx % nc;
+      const double m = A[r * LDA + kk] * pinv;
+      if (cc < nc - 1) A[r * LDA + kk + 1 + cc] -= m * A[kk * LDA + kk + 1 + cc];
+      else bv[r] -= m * bv[kk];
+    }
+    __syncthreads();
+  }
+  for (int kk = NP - 1; kk >= 0; kk--) {
+    if (tid == 0) {
+      const double d = A[kk * LDA + kk];
+      bv[kk] = (d != 0.0) ? bv[kk] / d : 0.0;
+    }
+    __syncthreads();
+    const double xk = bv[kk];
+    for (int r = tid; r < kk; r += kThreads) bv[r] -= A[r * LDA + kk] * xk;
+    __syncthreads();
+  }
+
+  // ------------------------------------------------------------------ CalcTentElEval (541-590) in the monomial basis
+  // u = sum_i sol_i phi_i = sum_j cm_j xi^alpha_j with cm = M^T sol; derivative coefficients in the degree <= P-1 basis.
+  for (int j = tid; j < npoly; j += kThreads) {
+    double v = 0.0;
+    for (int p = f.cptr[j]; p < f.cptr[j + 1]; p++) v = fma(f.cval[p], bv[f.crow[p]], v);
+    cm[j] = v;
+  }
+  __syncthreads();
+  for (int t = tid; t < d1 * npm1; t += kThreads) cmd[t] = cm[f.dmap[t]] * f.dfac[t];
+  __syncthreads();
+  for (int idx = tid; idx < npts; idx += kThreads) {
+    const int te = te0 + idx / Q, q = idx % Q;
+    const double* __restrict__ rec = f.fe + (size_t)te * FE;
+    const double* __restrict__ lm = a.lam + q * d1;
+    double xi[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+    for (int kk = 0; kk < d1; kk++) {
+      const double l = lm[kk];
+#pragma unroll
+      for (int u = 0; u < D; u++) xi[u] = fma(l, rec[fast_fe_xv(D) + kk * D + u], xi[u]);
+      xi[D] = fma(l, rec[fast_fe_tt(D) + kk], xi[D]);
+    }
+    double pw[4][P + 1];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      pw[u][0] = 1.0;
+#pragma unroll
+      for (int e = 1; e <= P; e++) pw[u][e] = pw[u][e - 1] * xi[u];
+    }
+    double val = 0.0, dv[4] = {0.0, 0.0, 0.0, 0.0};
+    int j = 0, j1 = 0;
+    // monomial order: first coordinate's exponent outermost (src/scalarmappedfe.cpp:526-531); unused coordinates fixed at 0
+#pragma unroll
+    for (int e0 = 0; e0 <= P; e0++) {
+      const double m0 = pw[0][e0];
+#pragma unroll
+      for (int e1 = 0; e1 <= P - e0; e1++) {
+        const double m1 = m0 * pw[1][e1];
+#pragma unroll
+        for (int e2 = 0; e2 <= ((d1 > 2) ? P - e0 - e1 : 0); e2++) {
+          const double m2 = (d1 > 2) ? m1 * pw[2][e2] : m1;
+#pragma unroll
+          for (int e3 = 0; e3 <= ((d1 > 3) ? P - e0 - e1 - e2 : 0); e3++) {
+            const double m = (d1 > 3) ? m2 * pw[3][e3] : m2;
+            if (!FO) val = fma(cm[j], m, val);
+            if (e0 + e1 + e2 + e3 <= P - 1) {
+#pragma unroll
+              for (int u = 0; u < d1; u++) dv[u] = fma(cmd[u * npm1 + j1], m, dv[u]);
+              j1++;
+            }
+            j++;
+          }
+        }
+      }
+    }
+    const double s = rec[fast_fe_sc(D)], sc = rec[fast_fe_sc(D) + 1];
+    double* __restrict__ wf = a.wavefront + (size_t)a.te_el[te] * ((FO ? d1 : d1 + 1) * Q);
+    if (!FO) wf[q] = val;
+#pragma unroll
+    for (int u = 0; u < D; u++) wf[((FO ? 0 : 1) + u) * Q + q] = s * dv[u];
+    wf[((FO ? 0 : 1) + D) * Q + q] = sc * dv[D];
+  }
+}
+
+template <int D, int P, int FO>
+cudaError_t launch_cfg(const TentKernelArgs& a, const FastArgs& f, cudaStream_t stream) {
+  using C = Cfg<D, P, FO>;
+  if (a.Q != C::Q || a.N != C::N || a.npoly != C::npoly) return cudaErrorInvalidValue;
+  const size_t smem = sizeof(double) * C::nsmem;
+  static bool configured = false;  // per instantiation
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(tent_kernel_fast<D, P, FO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  tent_kernel_fast<D, P, FO><<<a.ntents, kThreads, smem, stream>>>(a, f);
+  return cudaGetLastError();
+}
+
+template <int D, int P, int FO>
+constexpr size_t smem_cfg() { return sizeof(double) * Cfg<D, P, FO>::nsmem; }
+
+}  // namespace
+
+#define NGST_FAST_CONFIGS(X) X(3, 4) X(3, 3) X(3, 2) X(2, 4) X(2, 5) X(2, 3) X(2, 6)
+
+bool tent_fast_available(int D, int order) {
+#define X(d, p) if (D == d && order == p) return true;
+  NGST_FAST_CONFIGS(X)
+#undef X
+  return false;
+}
+
+size_t tent_fast_smem_bytes(int D, int order, int fosystem) {
+#define X(d, p) if (D == d && order == p) return fosystem ? smem_cfg<d, p, 1>() : smem_cfg<d, p, 0>();
+  NGST_FAST_CONFIGS(X)
+#undef X
+  return 0;
+}
+
+cudaError_t launch_tent_fast(int D, int order, int fosystem, const TentKernelArgs& a, const FastArgs& f,
+                             cudaStream_t stream) {
+  if (a.ntents <= 0) return cudaSuccess;
+#define X(d, p) if (D == d && order == p) return fosystem ? launch_cfg<d, p, 1>(a, f, stream) : launch_cfg<d, p, 0>(a, f, stream);
+  NGST_FAST_CONFIGS(X)
+#undef X
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace ngst

@@ -1,0 +1,52 @@
+// Host/device contract of the fast single-wavespeed tent kernel (tent_fast.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "tent_kernel.cuh"
+
+namespace ngst {
+
+// ---- per tent-element record (doubles), staged once per slab by stage_fast():
+//   XV  : d1*D  element vertices in scaled tent coordinates, vertex k at [k*D .. k*D+D): (P_k - x_v) * s
+//   TB  : d1    bottom-face vertex times, scaled: (tau_k - t0) * s * c
+//   TT  : d1    top-face vertex times, scaled
+//   TOP : D+2   k0, kd[D], kt: Cholesky factor of the top-face flux matrix (src/twavetents.cpp:293-309) times
+//               sqrt(area) and the derivative scalings s / s*c
+//   BOT : d1+2  area, sqrt(area), n[d1] of the bottom face
+//   SC  : 3     s, s*c, 1/c^2
+constexpr int fast_fe_xv(int) { return 0; }
+constexpr int fast_fe_tb(int D) { return (D + 1) * D; }
+constexpr int fast_fe_tt(int D) { return fast_fe_tb(D) + D + 1; }
+constexpr int fast_fe_top(int D) { return fast_fe_tt(D) + D + 1; }
+constexpr int fast_fe_bot(int D) { return fast_fe_top(D) + D + 2; }
+constexpr int fast_fe_sc(int D) { return fast_fe_bot(D) + D + 3; }
+constexpr int fast_fe_stride(int D) { return (fast_fe_sc(D) + 3 + 3) / 4 * 4; }
+
+// ---- per boundary-face record (doubles):
+//   V0 : d1     tent vertex at tbot, scaled;  E : D*d1 edge vectors V_{m+1} - V_0, scaled, edge m at [m*d1 ..)
+//   N  : D      outward spatial unit normal;  then area, s, s*c, 1/c^2, kind (0 Dirichlet, 1 Neumann)
+constexpr int fast_ff_v0(int) { return 0; }
+constexpr int fast_ff_e(int D) { return D + 1; }
+constexpr int fast_ff_n(int D) { return fast_ff_e(D) + D * (D + 1); }
+constexpr int fast_ff_misc(int D) { return fast_ff_n(D) + D; }
+constexpr int fast_ff_stride(int D) { return (fast_ff_misc(D) + 5 + 3) / 4 * 4; }
+
+struct FastArgs {
+  const double* fe;     // nte * fast_fe_stride(D)
+  const double* ff;     // ntf * fast_ff_stride(D)
+  const double* sqrtw;  // Q: sqrt of the rule weights
+  // column-compressed basis matrix (monomial j -> functions), for sol -> monomial coefficients
+  const int* cptr;      // npoly + 1
+  const int* crow;      // nnz
+  const double* cval;   // nnz
+  // derivative maps: coefficient u*npm1 + j' of d/dxi_u in the degree <= p-1 monomial basis = cm[dmap] * dfac
+  const int* dmap;      // d1 * npm1
+  const double* dfac;   // d1 * npm1
+};
+
+bool tent_fast_available(int D, int order);
+size_t tent_fast_smem_bytes(int D, int order, int fosystem);
+cudaError_t launch_tent_fast(int D, int order, int fosystem, const TentKernelArgs& a, const FastArgs& f,
+                             cudaStream_t stream);
+
+}  // namespace ngst

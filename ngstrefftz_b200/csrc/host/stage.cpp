@@ -306,4 +306,125 @@ void boundary_sample_points(const StagedTents& st, const SimplexRule& rule, doub
   }
 }
 
+// Record layouts: cuda/tent_fast.cuh (the offsets are recomputed here from D; solver.cu static_asserts the strides).
+FastStage stage_fast(const SimplexMesh& m, const TentSlab& slab, const StagedTents& st, const std::vector<double>& c_el,
+                     const SimplexRule& rule, const BasisCsr& basis_so, const BasisCsr& basis_fo, int fe_stride,
+                     int ff_stride) {
+  const int D = st.D, d1 = st.d1, nt = st.ntents;
+  FastStage fs;
+  fs.fe_stride = fe_stride;
+  fs.ff_stride = ff_stride;
+  fs.fe.assign((size_t)st.nte * fe_stride, 0.0);
+  fs.ff.assign((size_t)std::max(st.ntf, 1) * ff_stride, 0.0);
+  fs.ok.assign(nt, 1);
+  fs.sqrtw.resize(rule.nip);
+  for (int q = 0; q < rule.nip; q++) {
+    if (!(rule.w[q] > 0)) throw std::runtime_error("stage_fast: quadrature weights must be positive");
+    fs.sqrtw[q] = std::sqrt(rule.w[q]);
+  }
+  const int o_xv = 0, o_tb = d1 * D, o_tt = o_tb + d1, o_top = o_tt + d1, o_bot = o_top + D + 2, o_sc = o_bot + D + 3;
+  const int f_v0 = 0, f_e = d1, f_n = f_e + D * d1, f_misc = f_n + D;
+  if (o_sc + 3 > fe_stride || f_misc + 5 > ff_stride) throw std::runtime_error("stage_fast: record stride too small");
+#pragma omp parallel for schedule(dynamic, 256)
+  for (int t = 0; t < nt; t++) {
+    const double* x0 = &st.center[(size_t)t * d1];
+    const double t0 = x0[D], s = st.scale[t];
+    bool ok = st.ndom[t] == 1;
+    for (int te = st.te_off[t]; te < st.te_off[t + 1]; te++) {
+      const int el = st.te_el[te];
+      const double c = c_el[el];
+      const int* ev = m.elverts(el);
+      double* r = &fs.fe[(size_t)te * fe_stride];
+      for (int k = 0; k < d1; k++) {
+        for (int u = 0; u < D; u++) r[o_xv + k * D + u] = (m.point(ev[k])[u] - x0[u]) * s;
+        r[o_tb + k] = (st.te_tbot[(size_t)te * d1 + k] - t0) * s * c;
+        r[o_tt + k] = (st.te_ttop[(size_t)te * d1 + k] - t0) * s * c;
+      }
+      const double* g = &st.te_geo[(size_t)te * 2 * (d1 + 1)];
+      const double* nb = g;
+      const double area_b = g[d1];
+      const double* ntp = g + d1 + 1;
+      const double area_t = g[2 * d1 + 1];
+      // W_top / omega = [[n_t I, -n_x], [-n_x^T, n_t / c^2]] = L L^T (twavetents.cpp:293-309)
+      const double n_t = ntp[D];
+      double nx2 = 0;
+      for (int u = 0; u < D; u++) nx2 += ntp[u] * ntp[u];
+      const double schur = n_t / (c * c) - (n_t > 0 ? nx2 / n_t : 0.0);
+      if (!(n_t > 0) || !(schur > 0) || !(area_t >= 0)) { ok = false; continue; }
+      const double sa = std::sqrt(area_t), snt = std::sqrt(n_t);
+      r[o_top] = sa * snt * s;
+      for (int u = 0; u < D; u++) r[o_top + 1 + u] = sa * (ntp[u] / snt) * s * c;
+      r[o_top + 1 + D] = sa * std::sqrt(schur) * s * c;
+      r[o_bot] = area_b;
+      r[o_bot + 1] = std::sqrt(area_b);
+      for (int u = 0; u < d1; u++) r[o_bot + 2 + u] = nb[u];
+      r[o_sc] = s;
+      r[o_sc + 1] = s * c;
+      r[o_sc + 2] = 1.0 / (c * c);
+    }
+    for (int tf = st.tf_off[t]; tf < st.tf_off[t + 1]; tf++) {
+      if (st.tf_kind[tf] == kInterface) { ok = false; continue; }
+      const double c = st.tf_c[2 * tf];
+      const double* V = &st.tf_verts[(size_t)tf * d1 * d1];
+      double* r = &fs.ff[(size_t)tf * ff_stride];
+      for (int u = 0; u < D; u++) r[f_v0 + u] = (V[u] - x0[u]) * s;
+      r[f_v0 + D] = (V[D] - t0) * s * c;
+      for (int k = 0; k < D; k++) {
+        for (int u = 0; u < D; u++) r[f_e + k * d1 + u] = (V[(k + 1) * d1 + u] - V[u]) * s;
+        r[f_e + k * d1 + D] = (V[(k + 1) * d1 + D] - V[D]) * s * c;
+      }
+      for (int u = 0; u < D; u++) r[f_n + u] = st.tf_n[(size_t)tf * D + u];
+      r[f_misc] = st.tf_area[tf];
+      r[f_misc + 1] = s;
+      r[f_misc + 2] = s * c;
+      r[f_misc + 3] = 1.0 / (c * c);
+      r[f_misc + 4] = st.tf_kind[tf] == kNeumann ? 1.0 : 0.0;
+    }
+    fs.ok[t] = ok ? 1 : 0;
+  }
+  (void)slab;
+  // column-compressed basis: monomial j -> (function, coefficient), functions ascending (fixed summation order)
+  for (int fo = 0; fo < 2; fo++) {
+    const BasisCsr& b = fo ? basis_fo : basis_so;
+    std::vector<int>& cp = fs.cptr[fo];
+    cp.assign(b.npoly + 1, 0);
+    for (int j : b.col) cp[j + 1]++;
+    for (int j = 0; j < b.npoly; j++) cp[j + 1] += cp[j];
+    fs.crow[fo].resize(b.col.size());
+    fs.cval[fo].resize(b.col.size());
+    std::vector<int> fill(cp.begin(), cp.end() - 1);
+    for (int i = 0; i < b.nbasis; i++)
+      for (int p = b.rowptr[i]; p < b.rowptr[i + 1]; p++) {
+        const int j = b.col[p];
+        fs.crow[fo][fill[j]] = i;
+        fs.cval[fo][fill[j]] = b.val[p];
+        fill[j]++;
+      }
+  }
+  // d/dxi_u of sum_j cm_j xi^alpha_j = sum_j' (cm[index(alpha' + e_u)] * (alpha'_u + 1)) xi^alpha', |alpha'| <= p-1
+  {
+    const int order = basis_so.order;
+    const std::vector<int> lo = monomial_exponents(d1, order - 1);
+    const int npm1 = (int)lo.size() / d1, npoly = basis_so.npoly;
+    fs.dmap.resize((size_t)d1 * npm1);
+    fs.dfac.resize((size_t)d1 * npm1);
+    for (int u = 0; u < d1; u++)
+      for (int j1 = 0; j1 < npm1; j1++) {
+        int e[4] = {0, 0, 0, 0};
+        for (int k = 0; k < d1; k++) e[k] = lo[(size_t)j1 * d1 + k];
+        e[u]++;
+        int found = -1;
+        for (int j = 0; j < npoly && found < 0; j++) {
+          bool same = true;
+          for (int k = 0; k < d1; k++) same = same && basis_so.expo[(size_t)j * d1 + k] == e[k];
+          if (same) found = j;
+        }
+        if (found < 0) throw std::runtime_error("stage_fast: monomial not found");
+        fs.dmap[(size_t)u * npm1 + j1] = found;
+        fs.dfac[(size_t)u * npm1 + j1] = (double)e[u];
+      }
+  }
+  return fs;
+}
+
 }  // namespace ngst

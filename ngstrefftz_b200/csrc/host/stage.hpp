@@ -49,6 +49,26 @@ struct StagedTents {
 StagedTents stage_tents(const SimplexMesh& m, const TentSlab& slab, const std::vector<double>& c_el,
                         const std::vector<double>& c_vertex, const SimplexRule& rule);
 
+// Operands of the fast single-wavespeed kernel (cuda/tent_fast.cu; record layouts in cuda/tent_fast.cuh): everything
+// per tent-element / boundary face that does not depend on the wave state, in scaled tent coordinates.
+struct FastStage {
+  int fe_stride = 0, ff_stride = 0;
+  std::vector<double> fe;          // nte * fe_stride
+  std::vector<double> ff;          // ntf * ff_stride (interface faces: zeros, never read by the fast kernel)
+  std::vector<double> sqrtw;       // nip
+  std::vector<unsigned char> ok;   // ntents: 1 = tent can run on the fast kernel (one wavespeed region, causal top faces)
+  // column-compressed basis [fosystem]
+  std::vector<int> cptr[2], crow[2];
+  std::vector<double> cval[2];
+  // derivative maps of the monomial basis (degree <= p-1 enumeration, first coordinate outermost)
+  std::vector<int> dmap;           // d1 * npm1
+  std::vector<double> dfac;        // d1 * npm1
+};
+
+FastStage stage_fast(const SimplexMesh& m, const TentSlab& slab, const StagedTents& st, const std::vector<double>& c_el,
+                     const SimplexRule& rule, const BasisCsr& basis_so, const BasisCsr& basis_fo, int fe_stride,
+                     int ff_stride);
+
 // Geometry helpers restating twavetents.cpp:633-732; vert holds d1 vertices of d1 coordinates each
 // (vertex k at vert[k*d1 .. k*d1+d1), i.e. the reference's Mat column k).
 double tent_face_area(int D, const double* vert);
