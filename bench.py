@@ -337,6 +337,8 @@ def run_ours(args):
     dmma = _capi.C.c_double(0)
     check(lib.ngst_device_fp64_peak(local, 0, _capi.C.byref(dfma)))
     check(lib.ngst_device_fp64_peak(local, 1, _capi.C.byref(dmma)))
+    mixed = _capi.C.c_double(0)
+    check(lib.ngst_device_fp64_peak(local, 2, _capi.C.byref(mixed)))
     fp64_peak = max(dfma.value, dmma.value)
     flops_rank0 = flops_step * args.steps
     ach_tf = flops_rank0 / (float(np.sum(dev_ms)) * 1e-3) * 1e-12
@@ -350,11 +352,20 @@ def run_ours(args):
                 traffic = json.load(fh).get("dram_bytes_per_tent") * tents_step * args.steps / max(sm[6], 1)
         except (OSError, ValueError):
             traffic = None
+    # executed tensor-path work of tent_kernel_fast: symmetric rank-k updates touch only the NT(NT+1)/2 upper-triangular
+    # 8x8 tiles; (D+1) k-rows per top-face point, 1 per bottom-face point (second-order form), 4 k-rows per DMMA
+    nt_tiles = (N + 7) // 8
+    dmma_el = (Q * (D + 1) / 4.0 + (0 if tw.fosystem else Q / 4.0)) * (nt_tiles * (nt_tiles + 1) / 2) * 512.0
+    dmma_tf = dmma_el * float(nels.sum()) * args.steps / (float(np.sum(dev_ms)) * 1e-3) * 1e-12
     roofline = {"bound": "fp64", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach_tf / fp64_peak,
                 "traffic": traffic, "kernel": tw.kernel_name(),
                 "peak_source": f"measured live on this GPU: DFMA {dfma.value:.2f} / DMMA m8n8k4 {dmma.value:.2f} TFLOP/s "
-                               f"(ngst_device_fp64_peak); MEASURED_PEAKS.json holds no FP64 figure",
-                "flops_per_tent_element": f_el, "launches_per_step": launches / max(args.steps, 1),
+                               f"(ngst_device_fp64_peak), DMMA+DFMA interleaved 4:1 {mixed.value:.2f}; MEASURED_PEAKS.json holds no FP64 figure",
+                "flops_per_tent_element": f_el,
+                "note": "achieved = algorithmic flops of SURVEY.md 8.4 (full N x N Gram) / device time; the kernel exploits "
+                        "the symmetry of W (Z Z^T) and executes about half of them, so frac can exceed 1",
+                "executed_dmma": {"flops_per_tent_element": dmma_el, "achieved": dmma_tf, "peak": dmma.value,
+                                  "unit": "TFLOP/s", "frac": dmma_tf / dmma.value if dmma.value else None}, "launches_per_step": launches / max(args.steps, 1),
                 "hbm": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s",
                         "frac": ach_gbs / hbm_peak, "peak_source": hbm_src, "bytes_per_tent_element": b_el}}
 

@@ -124,7 +124,8 @@ int ngst_twave_max_adiam(const ngst_twave* t, double* out);
 int ngst_twave_basis(const ngst_twave* t, int* sizes, int* rowptr, int* col, double* val);
 void ngst_twave_destroy(ngst_twave* t);
 
-/* Measured FP64 roofline denominator of `device` in TFLOP/s: which 0 = DFMA pipe, 1 = DMMA (mma.sync m8n8k4 f64).
+/* Measured FP64 roofline denominator of `device` in TFLOP/s: which 0 = DFMA pipe, 1 = DMMA (mma.sync m8n8k4 f64),
+ * 2 = both interleaved in one instruction stream (4:1 flops; shows whether the two datapaths overlap).
  * No reference counterpart (the reference is CPU-only); used by bench.py for roofline.peak. */
 int ngst_device_fp64_peak(int device, int which, double* tflops);
 

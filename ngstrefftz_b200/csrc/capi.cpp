@@ -304,7 +304,7 @@ void ngst_twave_destroy(ngst_twave* t) { delete t; }
 int ngst_device_fp64_peak(int device, int which, double* tflops) {
   return guarded([&] {
     need(tflops, "tflops");
-    if (which != 0 && which != 1) throw std::invalid_argument("ngst_device_fp64_peak: which must be 0 or 1");
+    if (which < 0 || which > 2) throw std::invalid_argument("ngst_device_fp64_peak: which must be 0, 1 or 2");
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = measure_fp64_peak(which, 5, tflops);
     if (e != cudaSuccess) throw std::runtime_error(std::string("CUDA: fp64 peak: ") + cudaGetErrorString(e));

@@ -47,9 +47,33 @@ __global__ void __launch_bounds__(256) dmma_peak_kernel(double* out, int iters, 
   if (s == 123.456) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// DMMA and DFMA issued from the same warps, 8 DMMAs (4096 flops/warp) to 16 DFMAs (1024 flops/warp): tells whether
+// the two share one FP64 datapath (total stays at the DMMA peak) or can overlap (total exceeds it).
+__global__ void __launch_bounds__(256) mixed_peak_kernel(double* out, int iters, double a, double b) {
+  double c[kChains][2];
+  double x[kChains];
+#pragma unroll
+  for (int k = 0; k < kChains; k++) { c[k][0] = threadIdx.x * 1e-3; c[k][1] = k * 1e-3; x[k] = (threadIdx.x + k) * 1e-3; }
+  for (int it = 0; it < iters; it++) {
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+#pragma unroll
+      for (int k = 0; k < kChains; k++) {
+        dmma_m8n8k4(c[k][0], c[k][1], a, b);
+        x[k] = fma(x[k], a, b);
+        x[(k + 4) % kChains] = fma(x[(k + 4) % kChains], a, b);
+      }
+    }
+  }
+  double s = 0;
+#pragma unroll
+  for (int k = 0; k < kChains; k++) s += c[k][0] + c[k][1] + x[k];
+  if (s == 123.456) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 }  // namespace
 
-// which: 0 = DFMA, 1 = DMMA m8n8k4. Returns TFLOP/s (2 flops per FMA), best of `reps` timed launches.
+// which: 0 = DFMA, 1 = DMMA m8n8k4, 2 = both interleaved (4:1 flops). Returns TFLOP/s (2 flops per FMA), best of `reps` timed launches.
 cudaError_t measure_fp64_peak(int which, int reps, double* tflops) {
   cudaError_t e;
   int dev = 0, nsm = 0;
@@ -65,14 +89,16 @@ cudaError_t measure_fp64_peak(int which, int reps, double* tflops) {
   for (int r = 0; r < reps + 1; r++) {
     cudaEventRecord(e0);
     if (which == 0) dfma_peak_kernel<<<blocks, threads>>>(d_out, iters, 0.999999, 1e-9);
-    else dmma_peak_kernel<<<blocks, threads>>>(d_out, iters, 0.999999, 1e-9);
+    else if (which == 1) dmma_peak_kernel<<<blocks, threads>>>(d_out, iters, 0.999999, 1e-9);
+    else mixed_peak_kernel<<<blocks, threads>>>(d_out, iters, 0.999999, 1e-9);
     cudaEventRecord(e1);
     if ((e = cudaEventSynchronize(e1)) != cudaSuccess) break;
     float ms = 0;
     cudaEventElapsedTime(&ms, e0, e1);
     double fma_count;
     if (which == 0) fma_count = (double)blocks * threads * iters * 8.0 * kChains;
-    else fma_count = (double)blocks * (threads / 32) * iters * 4.0 * kChains * 256.0;  // 8x8x4 FMAs per warp MMA
+    else if (which == 1) fma_count = (double)blocks * (threads / 32) * iters * 4.0 * kChains * 256.0;  // 8x8x4 FMAs per warp MMA
+    else fma_count = (double)blocks * (threads / 32) * iters * 4.0 * kChains * (256.0 + 2 * 32.0);
     const double tf = 2.0 * fma_count / (ms * 1e-3) * 1e-12;
     if (r > 0 && tf > best) best = tf;  // first launch is the warm-up
   }

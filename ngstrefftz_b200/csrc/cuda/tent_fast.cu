@@ -69,20 +69,36 @@ struct Cfg {
 // Symmetric rank-k update of this warp's upper-triangular tiles from the operand rows Z[function][k-row]:
 // tile L (row-major over ti <= tj) belongs to tile half L & 1; k-steps ks = kh, kh+2, .. < nks.
 template <int NT, int NACC, int TH>
+__device__ __forceinline__ void mma_sym_step(double (&acc)[NACC][2], const double (&fr)[NT]) {
+  int L = 0;
+#pragma unroll
+  for (int ti = 0; ti < NT; ti++)
+#pragma unroll
+    for (int tj = ti; tj < NT; tj++) {
+      if ((L & 1) == TH) dmma_m8n8k4(acc[L >> 1][0], acc[L >> 1][1], fr[ti], fr[tj]);
+      L++;
+    }
+}
+
+// nks / 2 (the k-steps of one warp) must be even: fragments are double-buffered so that the shared-memory loads of
+// the next k-step are in flight while the DMMAs of the current one issue.
+template <int NT, int NACC, int TH>
 __device__ __forceinline__ void dmma_sym(double (&acc)[NACC][2], const double* __restrict__ Z, int ZS, int nks, int kh,
                                          int g, int k) {
-  for (int ks = kh; ks < nks; ks += 2) {
-    double fr[NT];
+  const double* __restrict__ zp = Z + g * ZS + k + 4 * kh;
+  double fa[NT], fb[NT];
 #pragma unroll
-    for (int t = 0; t < NT; t++) fr[t] = Z[(8 * t + g) * ZS + 4 * ks + k];
-    int L = 0;
+  for (int t = 0; t < NT; t++) fa[t] = zp[8 * t * ZS];
+  for (int ks = kh; ks < nks; ks += 4) {
 #pragma unroll
-    for (int ti = 0; ti < NT; ti++)
+    for (int t = 0; t < NT; t++) fb[t] = zp[8 * t * ZS + 8];
+    mma_sym_step<NT, NACC, TH>(acc, fa);
+    zp += 16;
+    if (ks + 4 < nks) {
 #pragma unroll
-      for (int tj = ti; tj < NT; tj++) {
-        if ((L & 1) == TH) dmma_m8n8k4(acc[L >> 1][0], acc[L >> 1][1], fr[ti], fr[tj]);
-        L++;
-      }
+      for (int t = 0; t < NT; t++) fa[t] = zp[8 * t * ZS];
+    }
+    mma_sym_step<NT, NACC, TH>(acc, fb);
   }
 }
 
@@ -221,11 +237,29 @@ __global__ void __launch_bounds__(kThreads, 2) tent_kernel_fast(TentKernelArgs a
   }
 
   // ------------------------------------------------------------------ bottom faces: rhs (+ stabilisation Gram)  (209-267)
+  // the state values of the next chunk are loaded one iteration ahead (HBM/L2 latency hidden behind the evaluation)
+  constexpr int NC = FO ? d1 : d1 + 1;
+  double gnext[NC];
+  {
+    const int idc = min(lane, npts - 1);
+    const double* __restrict__ wf = a.wavefront + (size_t)a.te_el[te0 + idc / Q] * (NC * Q) + idc % Q;
+#pragma unroll
+    for (int cc = 0; cc < NC; cc++) gnext[cc] = wf[cc * Q];
+  }
   for (int c0 = 0; c0 < npts; c0 += kChunk) {
     const int idx = c0 + lane;
     const bool valid = idx < npts;
     const int idc = valid ? idx : npts - 1;
     const int te = te0 + idc / Q, q = idc % Q;
+    double gcur[NC];
+#pragma unroll
+    for (int cc = 0; cc < NC; cc++) gcur[cc] = gnext[cc];
+    if (c0 + kChunk < npts) {
+      const int idn = min(idx + kChunk, npts - 1);
+      const double* __restrict__ wf = a.wavefront + (size_t)a.te_el[te0 + idn / Q] * (NC * Q) + idn % Q;
+#pragma unroll
+      for (int cc = 0; cc < NC; cc++) gnext[cc] = wf[cc * Q];
+    }
     const double* __restrict__ rec = f.fe + (size_t)te * FE;
     const double* __restrict__ lm = a.lam + q * d1;
     double xi[d1];
@@ -238,22 +272,21 @@ __global__ void __launch_bounds__(kThreads, 2) tent_kernel_fast(TentKernelArgs a
       for (int u = 0; u < D; u++) xi[u] = fma(l, rec[fast_fe_xv(D) + kk * D + u], xi[u]);
       xi[D] = fma(l, rec[fast_fe_tb(D) + kk], xi[D]);
     }
-    const double* __restrict__ wf = a.wavefront + (size_t)a.te_el[te] * ((FO ? d1 : d1 + 1) * Q);
     const double area = rec[fast_fe_bot(D)];
     const double* __restrict__ nn = rec + fast_fe_bot(D) + 2;
     const double s = rec[fast_fe_sc(D)], sc = rec[fast_fe_sc(D) + 1], ic2 = rec[fast_fe_sc(D) + 2];
     const double om = valid ? a.w[q] * area : 0.0;
-    const double gt = wf[((FO ? 0 : 1) + D) * Q + q];
+    const double gt = gcur[(FO ? 0 : 1) + D];
     double rho[d1];
     double ndg = 0.0;
 #pragma unroll
     for (int u = 0; u < D; u++) {
-      const double gx = wf[((FO ? 0 : 1) + u) * Q + q];
+      const double gx = gcur[(FO ? 0 : 1) + u];
       rho[u] = -om * s * (nn[D] * gx - nn[u] * gt);
       ndg = fma(nn[u], gx, ndg);
     }
     rho[D] = -om * sc * (nn[D] * ic2 * gt - ndg);
-    const double rho_u = FO ? 0.0 : om * wf[q];
+    const double rho_u = FO ? 0.0 : om * gcur[0];
     const double sqo = valid ? f.sqrtw[q] * rec[fast_fe_bot(D) + 1] : 0.0;
     double* const zl = Z + lane;
     eval_group<D, P, FO>(w, xi, [&](auto ic, double v, double e0, double e1, double e2, double e3) {
@@ -379,66 +412,65 @@ __global__ void __launch_bounds__(kThreads, 2) tent_kernel_fast(TentKernelArgs a
     if (lane == 0) bv[4 * j + w] = v;
   }
   __syncthreads();
-  for (int i = N + tid; i < NP; i += kThreads) A[i * LDA + i] = 1.0;  // padding rows: identity
+  // ------------------------------------------------------------------ Solve (64-70 forms the inverse with LAPACK)
+  // LU with partial pivoting on the N x N system, right-hand side carried as column N. Pivoting is implicit (rows are
+  // never swapped; every thread tracks the used rows in a bit mask), the pivot search is done redundantly by every
+  // warp, so one barrier per elimination step suffices.
+  for (int i = tid; i < N; i += kThreads) A[i * LDA + N] = bv[i];
+  __shared__ int perm[64];
+  static_assert(N <= 64, "row mask is 64 bits wide");
   __syncthreads();
-
-  // ------------------------------------------------------------------ Solve (LU with partial pivoting; 64-70 forms the inverse)
-  __shared__ int piv_row;
-  __shared__ double piv_inv;
-  for (int kk = 0; kk < NP; kk++) {
-    if (tid < 32) {
+  {
+    unsigned long long done = 0ull;
+    for (int kk = 0; kk < N; kk++) {
       double best = -1.0;
-      int brow = kk;
-      for (int r = kk + tid; r < NP; r += 32) {
+      int brow = 0x7fffffff;
+      for (int r = lane; r < N; r += 32) {
+        if ((done >> r) & 1ull) continue;
         const double v = fabs(A[r * LDA + kk]);
         if (v > best) { best = v; brow = r; }
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
-        const double ob = __shfl_down_sync(0xffffffffu, best, o);
-        const int orow = __shfl_down_sync(0xffffffffu, brow, o);
+        const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int orow = __shfl_xor_sync(0xffffffffu, brow, o);
         if (ob > best || (ob == best && orow < brow)) { best = ob; brow = orow; }
       }
+      const int p = brow;
+      done |= 1ull << p;
+      double pinv = 0.0;
+      if (best > 0.0) pinv = 1.0 / A[p * LDA + kk];
       if (tid == 0) {
-        piv_row = brow;
-        if (best == 0.0) { atomicAdd(a.singular, 1); piv_inv = 0.0; }
-        else piv_inv = 1.0 / A[brow * LDA + kk];
+        perm[kk] = p;
+        if (!(best > 0.0)) atomicAdd(a.singular, 1);
       }
-    }
-    __syncthreads();
-    const int p = piv_row;
-    if (p != kk) {
-      for (int cidx = tid; cidx <= NP; cidx += kThreads) {
-        if (cidx < NP) {
-          const double t0 = A[kk * LDA + cidx];
-          A[kk * LDA + cidx] = A[p * LDA + cidx];
-          A[p * LDA + cidx] = t0;
-        } else {
-          const double t0 = bv[kk]; bv[kk] = bv[p]; bv[p] = t0;
-        }
+      const int c0 = kk + 1 + lane, c1 = c0 + 32;  // columns kk+1 .. N (N = right-hand side)
+      const double pr0 = (c0 <= N) ? A[p * LDA + c0] : 0.0;
+      const double pr1 = (c1 <= N) ? A[p * LDA + c1] : 0.0;
+      for (int r = w; r < N; r += 4) {
+        if ((done >> r) & 1ull) continue;
+        const double m = A[r * LDA + kk] * pinv;
+        if (c0 <= N) A[r * LDA + c0] -= m * pr0;
+        if (c1 <= N) A[r * LDA + c1] -= m * pr1;
       }
       __syncthreads();
     }
-    const double pinv = piv_inv;
-    const int nr = NP - kk - 1, nc = NP - kk;  // columns kk+1..NP-1 and the right-hand side
-    for (int idx = tid; idx < nr * nc; idx += kThreads) {
-      const int r = kk + 1 + idx / nc, cc = idx % nc;
-      const double m = A[r * LDA + kk] * pinv;
-      if (cc < nc - 1) A[r * LDA + kk + 1 + cc] -= m * A[kk * LDA + kk + 1 + cc];
-      else bv[r] -= m * bv[kk];
-    }
-    __syncthreads();
   }
-  for (int kk = NP - 1; kk >= 0; kk--) {
-    if (tid == 0) {
-      const double d = A[kk * LDA + kk];
-      bv[kk] = (d != 0.0) ? bv[kk] / d : 0.0;
+  // back substitution by warp 0: lane l carries the right-hand sides of rows l and l + 32
+  if (w == 0) {
+    double r0 = (lane < N) ? A[lane * LDA + N] : 0.0;
+    double r1 = (lane + 32 < N) ? A[(lane + 32) * LDA + N] : 0.0;
+    for (int kk = N - 1; kk >= 0; kk--) {
+      const int p = perm[kk];
+      const double d = A[p * LDA + kk];
+      const double rp = __shfl_sync(0xffffffffu, (p < 32) ? r0 : r1, p & 31);
+      const double xk = (d != 0.0) ? rp / d : 0.0;
+      if (lane == 0) bv[kk] = xk;
+      if (lane < N) r0 -= A[lane * LDA + kk] * xk;
+      if (lane + 32 < N) r1 -= A[(lane + 32) * LDA + kk] * xk;
     }
-    __syncthreads();
-    const double xk = bv[kk];
-    for (int r = tid; r < kk; r += kThreads) bv[r] -= A[r * LDA + kk] * xk;
-    __syncthreads();
   }
+  __syncthreads();
 
   // ------------------------------------------------------------------ CalcTentElEval (541-590) in the monomial basis
   // u = sum_i sol_i phi_i = sum_j cm_j xi^alpha_j with cm = M^T sol; derivative coefficients in the degree <= P-1 basis.
@@ -494,6 +526,7 @@ __global__ void __launch_bounds__(kThreads, 2) tent_kernel_fast(TentKernelArgs a
           }
         }
       }
+      asm volatile("" ::: "memory");  // keeps the coefficient loads of later e0 slices from being hoisted (register pressure)
     }
     const double s = rec[fast_fe_sc(D)], sc = rec[fast_fe_sc(D) + 1];
     double* __restrict__ wf = a.wavefront + (size_t)a.te_el[te] * ((FO ? d1 : d1 + 1) * Q);
