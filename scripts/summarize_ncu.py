@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Turns the ncu outputs a gpurun visit leaves in gpurun_out/ into small text summaries under profiles/.
 
-usage: summarize_ncu.py <tag>   (reads gpurun_out/launches.csv and gpurun_out/prof_tent.ncu-rep)
+usage: summarize_ncu.py <tag>   (reads gpurun_out/<tag>_launches.csv and gpurun_out/<tag>_prof_tent.ncu-rep)
 """
 import csv
 import io
@@ -35,7 +35,7 @@ KEYS = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "la
         "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio"]
 
-lc = os.path.join(ROOT, "gpurun_out", "launches.csv")
+lc = os.path.join(ROOT, "gpurun_out", f"{tag}_launches.csv")
 if os.path.exists(lc):
     rows = [r for r in csv.reader(l for l in open(lc) if l.startswith('"'))]
     hdr = rows[0]
@@ -55,7 +55,7 @@ if os.path.exists(lc):
         f.write("\n# per launch\n" + "\n".join(lines) + "\n")
     print(open(os.path.join(out, f"{tag}_launches.txt")).read()[:1500])
 
-rep = os.path.join(ROOT, "gpurun_out", "prof_tent.ncu-rep")
+rep = os.path.join(ROOT, "gpurun_out", f"{tag}_prof_tent.ncu-rep")
 if os.path.exists(rep):
     txt = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(txt)))
