@@ -80,7 +80,26 @@ void ngst_slab_destroy(ngst_slab* s);
  * device: CUDA device ordinal. Fails with NGST_ERR_CUDA when no device is usable. */
 int ngst_twave_create(const ngst_slab* s, int order, const double* c_el, const double* c_vertex, int device,
                       ngst_twave** out);
-/* info[8] = D, order, nbasis (LocalDofs), nip, ncomp, fosystem, nel, ntents */
+/* ---- multi-GPU (one process per GPU; the reference has no distributed Propagate).
+ * The spatial mesh is partitioned by vertex ownership: vertex_owner[v] in [0, nranks). A tent runs on the owner of its
+ * vertex; an element is LOCAL to every rank owning one of its vertices. Every rank pitches the same global slab and
+ * passes the same owner array. For a partitioned solver every element-indexed array of this interface (wavefronts,
+ * quadrature) has one row per LOCAL element, in ascending global element order (loc2glob).
+ * ngst_partition_plan (host only, no device): counts[5] = own tents, local elements, total send rows, total recv rows,
+ * levels; arrays may be NULL. send_off/recv_off have levels*nranks+1 entries (index level*nranks+peer); *_el are local
+ * element ids; owned[i] = 1 when this rank counts local element i in Energy/Error. */
+int ngst_partition_plan(const ngst_slab* s, const int* vertex_owner, int nranks, int rank, int* counts, int* own_tents,
+                        int* loc2glob, int* owned, int* send_off, int* send_el, int* recv_off, int* recv_el);
+int ngst_twave_create_partitioned(const ngst_slab* s, int order, const double* c_el, const double* c_vertex, int device,
+                                  const int* vertex_owner, int nranks, int rank, ngst_twave** out);
+/* NCCL bootstrap: one rank creates the 128-byte id, the caller distributes it (MPI / torch.distributed broadcast), every
+ * rank calls ngst_twave_comm_init. Afterwards Propagate exchanges the updated ghost rows after every tent level with
+ * grouped ncclSend/ncclRecv, and Energy / Error / L2Error return the all-reduced global value. */
+int ngst_comm_unique_id(void* out128);
+int ngst_twave_comm_init(ngst_twave* t, const void* id128);
+/* own_tents: info[7] global tent ids; loc2glob / owned: info[6] entries; NULL skips */
+int ngst_twave_partition(const ngst_twave* t, int* own_tents, int* loc2glob, int* owned);
+/* info[8] = D, order, nbasis (LocalDofs), nip, ncomp, fosystem, nel (local), ntents (of this rank) */
 int ngst_twave_info(const ngst_twave* t, int* info);
 /* Mapped quadrature points (nel*nip*D) and weights |detJ|*w (nel*nip) of every element: what
  * MakeWavefront (src/twavetents.cpp:734-764) samples a CoefficientFunction at. */

@@ -248,7 +248,10 @@ class TrefftzTents:
 class TWaveTents(TrefftzTents):
     """TWaveTents<D> (src/twavetents.hpp:95-224), state resident on one B200."""
 
-    def __init__(self, order, tps, wavespeedcf, device=0):
+    def __init__(self, order, tps, wavespeedcf, device=0, partition=None, comm_id=None):
+        """partition: None (one GPU) or (rank, nranks, owner) with owner either an int array (one rank per mesh vertex)
+        or a tuple (gx, gy, ..) = brick grid over the mesh's bounding box. comm_id: 128-byte NCCL id shared by all ranks
+        (default: created on rank 0 and broadcast with torch.distributed, which must be initialised)."""
         self.tps = tps
         self.mesh = tps.mesh
         self.order = int(order)
@@ -264,11 +267,49 @@ class TWaveTents(TrefftzTents):
             raise ValueError("wavespeed: need a scalar, one value per element, or a callable")
         self.c_el = c_el
         self._h = C.c_void_p()
-        check(lib.ngst_twave_create(tps._h, self.order, dptr(c_el), dptr(c_vertex), int(device), C.byref(self._h)))
+        self.partition = None
+        if partition is None:
+            check(lib.ngst_twave_create(tps._h, self.order, dptr(c_el), dptr(c_vertex), int(device), C.byref(self._h)))
+        else:
+            rank, nranks, owner = partition
+            owner = brick_vertex_owner(mesh, owner) if isinstance(owner, tuple) else i32(owner)
+            if len(owner) != mesh.nv:
+                raise ValueError("partition: need one owner per mesh vertex")
+            check(lib.ngst_twave_create_partitioned(tps._h, self.order, dptr(c_el), dptr(c_vertex), int(device),
+                                                    iptr(owner), int(nranks), int(rank), C.byref(self._h)))
+            self.partition = (int(rank), int(nranks), owner)
         self._bddatum = None
         self._bnd_pts = None
         self._quad = None
         self._refresh()
+        if self.partition is not None:
+            self._own = np.zeros(self.ntents, dtype=np.int32)
+            self.loc2glob = np.zeros(self.nel, dtype=np.int32)
+            self.owned = np.zeros(self.nel, dtype=np.int32)
+            check(lib.ngst_twave_partition(self._h, iptr(self._own), iptr(self.loc2glob), iptr(self.owned)))
+            if self.partition[1] > 1 and comm_id is not False:
+                self.init_comm(comm_id)
+
+    def init_comm(self, comm_id=None):
+        """NCCL bootstrap (ngst_comm_unique_id / ngst_twave_comm_init)."""
+        rank = self.partition[0]
+        if comm_id is None:
+            import torch
+            import torch.distributed as dist
+            buf = np.zeros(128, dtype=np.uint8)
+            if rank == 0:
+                check(lib.ngst_comm_unique_id(buf.ctypes.data_as(C.c_void_p)))
+            t = torch.from_numpy(buf)
+            if dist.get_backend() == "nccl":
+                t = t.cuda()
+            dist.broadcast(t, src=0)
+            comm_id = t.cpu().numpy().tobytes()
+        idbuf = C.create_string_buffer(bytes(comm_id), 128)
+        check(lib.ngst_twave_comm_init(self._h, C.cast(idbuf, C.c_void_p)))
+
+    def owned_tents(self):
+        """Global ids of the tents this rank solves (all tents without a partition)."""
+        return self._own if self.partition is not None else np.arange(self.ntents)
 
     def _refresh(self):
         info = np.zeros(8, dtype=np.int32)
@@ -424,8 +465,42 @@ class TWaveTents(TrefftzTents):
         return lib.ngst_twave_last_launches(self._h)
 
 
-def TWave(order, tps, wavespeedcf, BBcf=None, device=0):
-    """Factory of src/twavetents.cpp:1194-1228."""
+def brick_vertex_owner(mesh, grid):
+    """Vertex owners for a brick partition: the bounding box is cut into grid[0] x grid[1] x .. equal bricks, a vertex
+    belongs to the brick that contains it (upper brick on a cut plane); rank = bx + gx * (by + gy * bz)."""
+    pts = mesh.points
+    lo, hi = pts.min(axis=0), pts.max(axis=0)
+    owner = np.zeros(len(pts), dtype=np.int64)
+    stride = 1
+    for d, g in enumerate(grid):
+        if d >= pts.shape[1]:
+            if g != 1:
+                raise ValueError("partition grid has more directions than the mesh")
+            continue
+        b = np.floor((pts[:, d] - lo[d]) / (hi[d] - lo[d]) * g + 1e-9).astype(np.int64)
+        owner += np.clip(b, 0, g - 1) * stride
+        stride *= g
+    return i32(owner)
+
+
+def partition_plan(tps, owner, nranks, rank):
+    """Host-only view of a rank's partition plan (ngst_partition_plan): dict of numpy arrays."""
+    owner = i32(owner)
+    counts = np.zeros(5, dtype=np.int32)
+    check(lib.ngst_partition_plan(tps._h, iptr(owner), nranks, rank, iptr(counts), None, None, None, None, None, None, None))
+    nown, nloc, nsend, nrecv, nlev = (int(x) for x in counts)
+    out = {"own_tents": np.zeros(nown, np.int32), "loc2glob": np.zeros(nloc, np.int32), "owned": np.zeros(nloc, np.int32),
+           "send_off": np.zeros(nlev * nranks + 1, np.int32), "send_el": np.zeros(nsend, np.int32),
+           "recv_off": np.zeros(nlev * nranks + 1, np.int32), "recv_el": np.zeros(nrecv, np.int32)}
+    check(lib.ngst_partition_plan(tps._h, iptr(owner), nranks, rank, iptr(counts), iptr(out["own_tents"]),
+                                  iptr(out["loc2glob"]), iptr(out["owned"]), iptr(out["send_off"]), iptr(out["send_el"]),
+                                  iptr(out["recv_off"]), iptr(out["recv_el"])))
+    out["nlev"] = nlev
+    return out
+
+
+def TWave(order, tps, wavespeedcf, BBcf=None, device=0, partition=None, comm_id=None):
+    """Factory of src/twavetents.cpp:1194-1228. partition / comm_id: multi-GPU (see TWaveTents)."""
     if BBcf is not None:
         raise NotImplementedError("quasi-Trefftz (QTWaveTents, BBcf given) is not built yet: see DESIGN.md")
-    return TWaveTents(order, tps, wavespeedcf, device=device)
+    return TWaveTents(order, tps, wavespeedcf, device=device, partition=partition, comm_id=comm_id)

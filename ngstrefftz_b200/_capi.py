@@ -57,6 +57,12 @@ _SIGS = {
     "ngst_slab_levels": (C.c_int, [c_vp, c_ip, c_ip, c_ip]),
     "ngst_slab_destroy": (None, [c_vp]),
     "ngst_twave_create": (C.c_int, [c_vp, C.c_int, c_dp, c_dp, C.c_int, C.POINTER(c_vp)]),
+    "ngst_partition_plan": (C.c_int, [c_vp, c_ip, C.c_int, C.c_int, c_ip, c_ip, c_ip, c_ip, c_ip, c_ip, c_ip, c_ip]),
+    "ngst_twave_create_partitioned": (C.c_int, [c_vp, C.c_int, c_dp, c_dp, C.c_int, c_ip, C.c_int, C.c_int,
+                                                C.POINTER(c_vp)]),
+    "ngst_comm_unique_id": (C.c_int, [c_vp]),
+    "ngst_twave_comm_init": (C.c_int, [c_vp, c_vp]),
+    "ngst_twave_partition": (C.c_int, [c_vp, c_ip, c_ip, c_ip]),
     "ngst_twave_info": (C.c_int, [c_vp, c_ip]),
     "ngst_twave_quadrature": (C.c_int, [c_vp, c_dp, c_dp]),
     "ngst_twave_set_initial": (C.c_int, [c_vp, c_dp, C.c_int]),

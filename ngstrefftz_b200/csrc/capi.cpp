@@ -10,6 +10,7 @@
 #include "cuda/solver.hpp"
 #include "host/basis.hpp"
 #include "host/mesh.hpp"
+#include "host/partition.hpp"
 #include "host/pitcher.hpp"
 #include "host/quadrature.hpp"
 #include "host/stage.hpp"
@@ -18,7 +19,13 @@ using namespace ngst;
 
 struct ngst_mesh { SimplexMesh m; };
 struct ngst_slab { const ngst_mesh* mesh; TentSlab s; };
-struct ngst_twave { const ngst_slab* slab; std::unique_ptr<Solver> solver; };
+struct ngst_twave {
+  const ngst_slab* slab;
+  // multi-GPU: this rank's partition plan and its restricted slab (must outlive the solver, which keeps references)
+  std::unique_ptr<PartitionPlan> plan;
+  std::unique_ptr<TentSlab> sub;
+  std::unique_ptr<Solver> solver;
+};
 
 namespace {
 thread_local std::string g_err;
@@ -39,6 +46,7 @@ int guarded(F f) {
     return NGST_ERR_STATE;
   } catch (const std::exception& e) {
     g_err = e.what();
+    if (g_err.rfind("COMM:", 0) == 0) return NGST_ERR_COMM;
     return g_err.rfind("CUDA:", 0) == 0 ? NGST_ERR_CUDA : NGST_ERR_ARG;
   } catch (...) {
     g_err = "unknown error";
@@ -203,6 +211,65 @@ int ngst_twave_create(const ngst_slab* s, int order, const double* c_el, const d
     h->slab = s;
     h->solver = std::make_unique<Solver>(s->s, order, ce, cv, device);
     *out = h.release();
+  });
+}
+
+int ngst_partition_plan(const ngst_slab* s, const int* vertex_owner, int nranks, int rank, int* counts, int* own_tents,
+                        int* loc2glob, int* owned, int* send_off, int* send_el, int* recv_off, int* recv_el) {
+  return guarded([&] {
+    need(s, "slab"); need(vertex_owner, "vertex_owner"); need(counts, "counts");
+    const SimplexMesh& m = *s->s.mesh;
+    const std::vector<int> vo(vertex_owner, vertex_owner + m.nv);
+    const PartitionPlan p = make_partition_plan(m, s->s, vo, nranks, rank);
+    counts[0] = (int)p.own_tents.size();
+    counts[1] = (int)p.loc2glob.size();
+    counts[2] = (int)p.send_el.size();
+    counts[3] = (int)p.recv_el.size();
+    counts[4] = p.nlev;
+    copy_out(own_tents, p.own_tents);
+    copy_out(loc2glob, p.loc2glob);
+    if (owned) for (size_t i = 0; i < p.owned.size(); i++) owned[i] = p.owned[i];
+    copy_out(send_off, p.send_off);
+    copy_out(send_el, p.send_el);
+    copy_out(recv_off, p.recv_off);
+    copy_out(recv_el, p.recv_el);
+  });
+}
+
+int ngst_twave_create_partitioned(const ngst_slab* s, int order, const double* c_el, const double* c_vertex, int device,
+                                  const int* vertex_owner, int nranks, int rank, ngst_twave** out) {
+  return guarded([&] {
+    need(s, "slab"); need(out, "out"); need(c_el, "c_el"); need(vertex_owner, "vertex_owner");
+    const SimplexMesh& m = *s->s.mesh;
+    std::vector<double> ce(c_el, c_el + m.nel), cv;
+    if (c_vertex) cv.assign(c_vertex, c_vertex + m.nv);
+    const std::vector<int> vo(vertex_owner, vertex_owner + m.nv);
+    auto h = std::make_unique<ngst_twave>();
+    h->slab = s;
+    h->plan = std::make_unique<PartitionPlan>(make_partition_plan(m, s->s, vo, nranks, rank));
+    h->sub = std::make_unique<TentSlab>(restrict_slab(s->s, h->plan->own_tents));
+    h->solver = std::make_unique<Solver>(*h->sub, order, ce, cv, device, h->plan.get());
+    *out = h.release();
+  });
+}
+
+int ngst_comm_unique_id(void* out128) {
+  const int rc = guarded([&] { need(out128, "out128"); halo_unique_id(out128); });
+  return rc == NGST_OK ? rc : NGST_ERR_COMM;
+}
+
+int ngst_twave_comm_init(ngst_twave* t, const void* id128) {
+  const int rc = guarded([&] { need(t, "solver"); need(id128, "id128"); t->solver->InitComm(id128); });
+  return (rc == NGST_OK || rc == NGST_ERR_STATE || rc == NGST_ERR_CUDA) ? rc : NGST_ERR_COMM;
+}
+
+int ngst_twave_partition(const ngst_twave* t, int* own_tents, int* loc2glob, int* owned) {
+  return guarded([&] {
+    need(t, "solver");
+    if (!t->plan) throw std::logic_error("ngst_twave_partition: the solver was not created with a partition");
+    copy_out(own_tents, t->plan->own_tents);
+    copy_out(loc2glob, t->plan->loc2glob);
+    if (owned) for (size_t i = 0; i < t->plan->owned.size(); i++) owned[i] = t->plan->owned[i];
   });
 }
 

@@ -27,10 +27,10 @@ T* Solver::Upload(const std::vector<T>& v) {
 }
 
 Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el, const std::vector<double>& c_vertex,
-               int device)
-    : mesh_(*slab.mesh), slab_(slab), order_(order), device_(device), c_el_(c_el), c_vertex_(c_vertex) {
+               int device, const PartitionPlan* plan)
+    : mesh_(*slab.mesh), slab_(slab), plan_(plan), order_(order), device_(device), c_el_(c_el), c_vertex_(c_vertex) {
   if (order < 1 || order > 12) throw std::invalid_argument("TWave: order must be in 1..12");
-  if (slab.ntents == 0) throw std::logic_error("TWave: the slab has no tents (call PitchTents first)");
+  if (slab.ntents == 0 && !plan) throw std::logic_error("TWave: the slab has no tents (call PitchTents first)");
   if ((int)c_el_.size() != mesh_.nel) throw std::invalid_argument("TWave: need one wavespeed per element");
   for (double c : c_el_)
     if (!(c > 0)) throw std::invalid_argument("TWave: wavespeed must be positive");
@@ -39,6 +39,9 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
     for (int v = 0; v < mesh_.nv; v++) c_vertex_[v] = c_el_[mesh_.v2el.row(v)[0]];
   }
   const int D = mesh_.D, d1 = D + 1;
+  if (plan_) loc2glob_ = plan_->loc2glob;
+  else { loc2glob_.resize(mesh_.nel); for (int e = 0; e < mesh_.nel; e++) loc2glob_[e] = e; }
+  nel_ = (int)loc2glob_.size();
 
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -67,8 +70,16 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
 
   TentKernelArgs& a = args_;
   a.pts = Upload(mesh_.pts);
-  a.el2v = Upload(mesh_.el2v);
-  a.c_el = Upload(c_el_);
+  {
+    std::vector<int> el2v_loc((size_t)nel_ * d1);
+    std::vector<double> c_loc(nel_);
+    for (int e = 0; e < nel_; e++) {
+      for (int k = 0; k < d1; k++) el2v_loc[(size_t)e * d1 + k] = mesh_.el2v[(size_t)loc2glob_[e] * d1 + k];
+      c_loc[e] = c_el_[loc2glob_[e]];
+    }
+    a.el2v = Upload(el2v_loc);
+    a.c_el = Upload(c_loc);
+  }
   a.lam = Upload(lam);
   a.w = Upload(rule_.w);
   a.expo = Upload(basis_so_.expo);
@@ -86,7 +97,12 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
   a.ndom = Upload(staged_.ndom);
   a.te_off = Upload(staged_.te_off);
   a.tf_off = Upload(staged_.tf_off);
-  a.te_el = Upload(staged_.te_el);
+  {
+    std::vector<int> te_el_loc(staged_.te_el);  // staged_ keeps global element ids; the device sees local ones
+    if (plan_)
+      for (int& e : te_el_loc) e = plan_->glob2loc[e];
+    a.te_el = Upload(te_el_loc);
+  }
   a.te_dom = Upload(staged_.te_dom);
   a.te_tbot = Upload(staged_.te_tbot);
   a.te_ttop = Upload(staged_.te_ttop);
@@ -145,11 +161,11 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
 
   // element quadrature weights |detJ| * w (GetWeight, twavetents.cpp:793,818,843)
   {
-    std::vector<double> elw((size_t)mesh_.nel * Q);
+    std::vector<double> elw((size_t)nel_ * Q);
     Quadrature(nullptr, elw.data());
     d_elw_ = Upload(elw);
   }
-  CU(cudaMalloc(&d_scratch_, sizeof(double) * std::max(mesh_.nel, 1)));
+  CU(cudaMalloc(&d_scratch_, sizeof(double) * std::max(nel_, 1)));
   allocs_.push_back(d_scratch_);
 }
 
@@ -161,6 +177,9 @@ Solver::~Solver() {
   if (d_bnd_) cudaFree(d_bnd_);
   if (d_tmp_a_) cudaFree(d_tmp_a_);
   if (d_tmp_b_) cudaFree(d_tmp_b_);
+  if (d_sendbuf_) cudaFree(d_sendbuf_);
+  if (d_recvbuf_) cudaFree(d_recvbuf_);
+  comm_.reset();
   if (ev0_) cudaEventDestroy(ev0_);
   if (ev1_) cudaEventDestroy(ev1_);
   if (stream_) cudaStreamDestroy(stream_);
@@ -169,8 +188,8 @@ Solver::~Solver() {
 void Solver::Quadrature(double* x, double* weight) const {
   const int D = mesh_.D, d1 = D + 1, Q = rule_.nip;
 #pragma omp parallel for schedule(static)
-  for (int el = 0; el < mesh_.nel; el++) {
-    const int* ev = mesh_.elverts(el);
+  for (int el = 0; el < nel_; el++) {
+    const int* ev = mesh_.elverts(loc2glob_[el]);
     double J[9];
     for (int i = 0; i < D; i++)
       for (int d = 0; d < D; d++) J[d * D + i] = mesh_.point(ev[i])[d] - mesh_.point(ev[D])[d];
@@ -203,7 +222,7 @@ void Solver::SetInitial(const double* wf, int ncomp) {
   fosystem_ = (ncomp == D + 1) ? 1 : 0;  // twavetents.hpp:198-203
   ncomp_ = ncomp;
   basis_ = fosystem_ ? basis_fo_ : basis_so_;
-  const size_t bytes = (size_t)mesh_.nel * ncomp * rule_.nip * sizeof(double);
+  const size_t bytes = (size_t)nel_ * ncomp * rule_.nip * sizeof(double);
   if (d_wavefront_ && wavefront_bytes_ != bytes) { CU(cudaFree(d_wavefront_)); d_wavefront_ = nullptr; }
   if (!d_wavefront_) { CU(cudaMalloc(&d_wavefront_, bytes)); wavefront_bytes_ = bytes; }
   CU(cudaMemcpyAsync(d_wavefront_, wf, bytes, cudaMemcpyHostToDevice, stream_));
@@ -258,9 +277,11 @@ void Solver::Propagate() {
     TentKernelArgs a = args_;
     a.tents = d_level_all_ + slab_.level_off[l];
     a.ntents = slab_.level_off[l + 1] - slab_.level_off[l];
-    if (a.ntents == 0) continue;
-    CU(launch_tent_generic(mesh_.D, a, threads_, smem_, stream_));
-    launches++;
+    if (a.ntents > 0) {
+      CU(launch_tent_generic(mesh_.D, a, threads_, smem_, stream_));
+      launches++;
+    }
+    if (comm_) launches += ExchangeLevel(l);
   }
   for (int l = 0; l < nlev && !force_generic_; l++) {
     TentKernelArgs a = args_;
@@ -276,6 +297,7 @@ void Solver::Propagate() {
       CU(launch_tent_generic(mesh_.D, a, threads_, smem_, stream_));
       launches++;
     }
+    if (comm_) launches += ExchangeLevel(l);
   }
   CU(cudaEventRecord(ev1_, stream_));
   CU(cudaEventSynchronize(ev1_));
@@ -292,29 +314,73 @@ void Solver::Propagate() {
   }
 }
 
+// rows updated in level l that other ranks hold -> peers; rows peers updated that this rank holds <- peers
+int Solver::ExchangeLevel(int l) {
+  const PartitionPlan& p = *plan_;
+  const int nr = p.nranks, rowlen = ncomp_ * rule_.nip;
+  std::vector<int> sc(nr), rc(nr);
+  int ns = 0, nrv = 0;
+  for (int q = 0; q < nr; q++) {
+    sc[q] = p.send_off[(size_t)l * nr + q + 1] - p.send_off[(size_t)l * nr + q];
+    rc[q] = p.recv_off[(size_t)l * nr + q + 1] - p.recv_off[(size_t)l * nr + q];
+    ns += sc[q];
+    nrv += rc[q];
+  }
+  if (ns == 0 && nrv == 0) return 0;
+  const size_t need = (size_t)p.max_rows_per_level() * rowlen * sizeof(double);
+  if (halo_bytes_ < need) {
+    if (d_sendbuf_) CU(cudaFree(d_sendbuf_));
+    if (d_recvbuf_) CU(cudaFree(d_recvbuf_));
+    CU(cudaMalloc(&d_sendbuf_, need));
+    CU(cudaMalloc(&d_recvbuf_, need));
+    halo_bytes_ = need;
+  }
+  comm_->Exchange(d_wavefront_, rowlen, d_send_el_ + p.send_off[(size_t)l * nr], sc.data(),
+                  d_recv_el_ + p.recv_off[(size_t)l * nr], rc.data(), d_sendbuf_, d_recvbuf_, stream_);
+  return (ns > 0) + (nrv > 0);
+}
+
 void Solver::GetWavefront(double* out) {
   if (!have_initial_) throw std::logic_error("GetWavefront: SetInitial has not been called");
   CU(cudaSetDevice(device_));
-  const size_t bytes = (size_t)mesh_.nel * ncomp_ * rule_.nip * sizeof(double);
+  const size_t bytes = (size_t)nel_ * ncomp_ * rule_.nip * sizeof(double);
   CU(cudaMemcpyAsync(out, d_wavefront_, bytes, cudaMemcpyDeviceToHost, stream_));
   CU(cudaStreamSynchronize(stream_));
 }
 
 double Solver::ReduceElements(const double* a, const double* b, int mode) {
-  CU(launch_element_reduce(mode, mesh_.D, mesh_.nel, rule_.nip, ncomp_, fosystem_, d_elw_, args_.c_el, a, b,
+  CU(launch_element_reduce(mode, mesh_.D, nel_, rule_.nip, ncomp_, fosystem_, d_elw_, args_.c_el, a, b,
                            d_scratch_, stream_));
-  std::vector<double> part(mesh_.nel);
-  CU(cudaMemcpyAsync(part.data(), d_scratch_, sizeof(double) * mesh_.nel, cudaMemcpyDeviceToHost, stream_));
+  std::vector<double> part(nel_);
+  CU(cudaMemcpyAsync(part.data(), d_scratch_, sizeof(double) * nel_, cudaMemcpyDeviceToHost, stream_));
   CU(cudaStreamSynchronize(stream_));
   double s = 0;
-  for (double v : part) s += v;  // fixed element order: deterministic
+  if (plan_) {
+    for (int e = 0; e < nel_; e++)
+      if (plan_->owned[e]) s += part[e];  // every element is counted by exactly one rank
+    if (comm_) s = comm_->AllReduceSum(s, d_scalar_, stream_);
+  } else {
+    for (double v : part) s += v;  // fixed element order: deterministic
+  }
   return s;
+}
+
+void Solver::InitComm(const void* id128) {
+  if (!plan_) throw std::logic_error("InitComm: the solver was not created with a partition");
+  CU(cudaSetDevice(device_));
+  comm_ = std::make_unique<HaloComm>(plan_->rank, plan_->nranks, id128);
+  if (!d_send_el_) {
+    d_send_el_ = Upload(plan_->send_el);
+    d_recv_el_ = Upload(plan_->recv_el);
+    CU(cudaMalloc(&d_scalar_, sizeof(double)));
+    allocs_.push_back(d_scalar_);
+  }
 }
 
 double Solver::Energy(const double* wf) {
   if (!have_initial_) throw std::logic_error("Energy: SetInitial has not been called");
   CU(cudaSetDevice(device_));
-  const size_t bytes = (size_t)mesh_.nel * ncomp_ * rule_.nip * sizeof(double);
+  const size_t bytes = (size_t)nel_ * ncomp_ * rule_.nip * sizeof(double);
   const double* src = d_wavefront_;
   if (wf) {
     if (!d_tmp_a_) CU(cudaMalloc(&d_tmp_a_, bytes));
@@ -327,7 +393,7 @@ double Solver::Energy(const double* wf) {
 double Solver::Error(const double* wf, const double* ref, bool l2only) {
   if (!have_initial_) throw std::logic_error("Error: SetInitial has not been called");
   CU(cudaSetDevice(device_));
-  const size_t bytes = (size_t)mesh_.nel * ncomp_ * rule_.nip * sizeof(double);
+  const size_t bytes = (size_t)nel_ * ncomp_ * rule_.nip * sizeof(double);
   if (!d_tmp_a_) CU(cudaMalloc(&d_tmp_a_, bytes));
   if (!d_tmp_b_) CU(cudaMalloc(&d_tmp_b_, bytes));
   CU(cudaMemcpyAsync(d_tmp_a_, wf, bytes, cudaMemcpyHostToDevice, stream_));

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -9,7 +10,9 @@
 #include "../host/mesh.hpp"
 #include "../host/pitcher.hpp"
 #include "../host/quadrature.hpp"
+#include "../host/partition.hpp"
 #include "../host/stage.hpp"
+#include "halo.hpp"
 #include "tent_fast.cuh"
 #include "tent_kernel.cuh"
 
@@ -17,8 +20,11 @@ namespace ngst {
 
 class Solver {
  public:
+  // plan == nullptr: the whole slab on one GPU. Otherwise `slab` is the rank's restricted slab (restrict_slab) and
+  // plan its partition plan; c_el / c_vertex stay GLOBAL arrays; every element-indexed array of the public interface
+  // (wavefronts, quadrature) is then indexed by LOCAL element (plan->loc2glob).
   Solver(const TentSlab& slab, int order, const std::vector<double>& c_el, const std::vector<double>& c_vertex,
-         int device);
+         int device, const PartitionPlan* plan = nullptr);
   ~Solver();
   Solver(const Solver&) = delete;
   Solver& operator=(const Solver&) = delete;
@@ -29,7 +35,9 @@ class Solver {
   int nip() const { return rule_.nip; }
   int ncomp() const { return ncomp_; }
   int fosystem() const { return fosystem_; }
-  int nel() const { return mesh_.nel; }
+  int nel() const { return nel_; }
+  const PartitionPlan* plan() const { return plan_; }
+  void InitComm(const void* id128);
   int ntents() const { return slab_.ntents; }
   const BasisCsr& basis() const { return basis_; }
   const StagedTents& staged() const { return staged_; }
@@ -58,9 +66,20 @@ class Solver {
   template <typename T>
   T* Upload(const std::vector<T>& v);
   double ReduceElements(const double* d_a, const double* d_b, int mode);
+  int ExchangeLevel(int level);
+  size_t halo_bytes_ = 0;
 
   const SimplexMesh& mesh_;
   const TentSlab& slab_;
+  const PartitionPlan* plan_ = nullptr;
+  int nel_ = 0;                      // local elements (== mesh_.nel without a partition)
+  std::vector<int> loc2glob_;        // local -> global element
+  std::unique_ptr<HaloComm> comm_;
+  int* d_send_el_ = nullptr;
+  int* d_recv_el_ = nullptr;
+  double* d_sendbuf_ = nullptr;
+  double* d_recvbuf_ = nullptr;
+  double* d_scalar_ = nullptr;
   int order_, device_;
   std::vector<double> c_el_, c_vertex_;
   SimplexRule rule_;
