@@ -392,7 +392,7 @@ def run_ours(args):
                        "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"],
                        "ms_per_step": 1e3 * e2e_s / args.steps,
                        "path": "ngst_twave_set_initial + set_boundary_values + propagate + get_wavefront on pinned host buffers"}
-    if not args.no_cpu_baseline and world >= 1:
+    if not args.no_cpu_baseline and world == 1:
         cores = os.cpu_count() or 1
         sample = args.cpu_sample_tents or 4000
         r = cpu_sample(args, [args.cells] * 3, sample, 1, 1, cores)

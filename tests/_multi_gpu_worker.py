@@ -1,0 +1,53 @@
+"""Worker of tests/test_gpu_multi.py: one process per GPU (NCCL), partitioned Propagate, results written per rank."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+sys.path.insert(0, HERE)
+import ngstrefftz_b200 as ng  # noqa: E402
+from _cases import dirichlet, standing  # noqa: E402
+
+CASES = {
+    # name: (mesh factory, grid by world size, order, dt, nslabs)
+    "cube_p4": (lambda: ng.UnitCubeMesh(6), {2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}, 4, 0.1, 2),
+    "cube_p3": (lambda: ng.StructuredMesh([8, 4, 4], [0, 0, 0], [2, 1, 1]), {2: (2, 1, 1), 4: (4, 1, 1), 8: (4, 2, 1)}, 3, 0.1, 2),
+    "square_p4": (lambda: ng.UnitSquareMesh(12), {2: (2, 1), 4: (2, 2), 8: (4, 2)}, 4, 0.1, 3),
+}
+
+
+def main():
+    case, outdir = sys.argv[1], sys.argv[2]
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rank, world = dist.get_rank(), dist.get_world_size()
+    mk, grids, order, dt, nslabs = CASES[case]
+    mesh = mk()
+    D = mesh.dim
+    f = standing(D, 1.0)
+    ts = ng.TentSlab(mesh, "edge")
+    ts.SetMaxWavespeed(1.0)
+    assert ts.PitchTents(dt, True, 2 / 3)
+    tw = ng.TWave(order, ts, 1.0, device=local, partition=(rank, world, grids[world]))
+    tw.SetInitial(f)
+    tw.SetBoundaryCF(dirichlet(f, D))
+    e0 = tw.Energy()
+    for _ in range(nslabs):
+        tw.Propagate()
+    wf = tw.GetWavefront()
+    en = tw.Energy()
+    err = tw.Error(wf, tw.MakeWavefront(f, nslabs * dt))
+    np.savez(os.path.join(outdir, f"rank{rank}.npz"), wf=wf, loc2glob=tw.loc2glob, owned=tw.owned, energy0=e0, energy=en,
+             error=err, own_tents=tw.owned_tents(), launches=tw.last_launches(), ms=tw.last_ms())
+    dist.barrier()
+    dist.destroy_process_group()
+    print("MULTI_OK", rank)
+
+
+if __name__ == "__main__":
+    main()
