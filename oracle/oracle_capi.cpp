@@ -5,6 +5,7 @@
 #include <string>
 
 #include "oracle_twave.cpp"
+#include "oracle_qt.cpp"
 
 using namespace oracle;
 
@@ -113,6 +114,55 @@ int oracle_twave_setup(void* hp, int order, const double* c_el, const double* c_
     t.IndexBoundary();
   });
 }
+// quasi-Trefftz solver (QTWaveTents): wavespeed polynomial c(x) of degree cdeg (coefficients in first-coordinate-outermost
+// monomial order), Taylor tables of 1/c^2 (degree <= order-2) and B (degree <= order-1) at the mesh vertices, and the
+// (D+1)-simplex rule of order 2*order for the volume terms
+int oracle_qt_setup(void* hp, int order, const double* c_el, const double* c_vertex, int nip, const double* xi,
+                    const double* w, int cdeg, const double* ccoef, const double* aa_taylor, const double* bb_taylor,
+                    int vnip, const double* vxi, const double* vw) {
+  auto* h = (OracleHandle*)hp;
+  return guarded([&] {
+    const int D = h->ma.D;
+    if (D > 2) throw std::runtime_error("oracle: QTWaveTents exists for D = 1, 2 only (twavetents.cpp:1150-1151)");
+    auto* q = new QTWaveTents(D, order, &h->ma, &h->slab, c_el, c_vertex);
+    h->tw.reset(q);
+    q->snip = nip;
+    q->ir_points = Matrix(nip, D);
+    std::memcpy(q->ir_points.d.data(), xi, sizeof(double) * nip * D);
+    q->ir_w.assign(w, w + nip);
+    q->cpoly.init(D, cdeg, ccoef);
+    q->aa_taylor.assign(aa_taylor, aa_taylor + (size_t)h->ma.nv * q->nA);
+    q->bb_taylor.assign(bb_taylor, bb_taylor + (size_t)h->ma.nv * q->nB);
+    q->vir_points = Matrix(vnip, D + 1);
+    std::memcpy(q->vir_points.d.data(), vxi, sizeof(double) * vnip * (D + 1));
+    q->vir_w.assign(vw, vw + vnip);
+    q->IndexBoundary();
+  });
+}
+// wavespeed at every (element, quadrature point) for Energy / Error (nel * nip values); NULL restores the element values
+void oracle_set_point_wavespeed(void* hp, const double* c) {
+  auto* h = (OracleHandle*)hp;
+  if (!c) { h->tw->c_point.clear(); return; }
+  h->tw->c_point.assign(c, c + (size_t)h->ma.nel * h->tw->snip);
+}
+// CSR quasi-Trefftz basis of one tent for tests: Taylor tables already scaled by elsize^|alpha|; returns nnz
+int oracle_qt_basis(int D, int order, const double* aa_scaled, const double* bb_scaled, int* rowptr, int* col, double* val) {
+  const int d1 = D + 1;
+  PolIndex pix(d1, order), pixA(D, std::max(order - 2, 0)), pixB(D, order - 1);
+  Matrix BB(order, (order - 1) * (d1 == 3) + 1), AA(order - 1, (order - 2) * (d1 == 3) + 1);
+  for (size_t j = 0; j < pixB.expo.size(); j++) {
+    const std::vector<int>& e = pixB.expo[j];
+    const int nx = e[0], ny = D > 1 ? e[1] : 0;
+    BB(nx, ny) = bb_scaled[j];
+    if (nx + ny < order - 1) AA(nx, ny) = aa_scaled[pixA(e)];
+  }
+  CSR b = QTWaveBasisMat(d1, order, AA, BB, pix);
+  if (rowptr) std::memcpy(rowptr, b.rowptr.data(), sizeof(int) * b.rowptr.size());
+  if (col) std::memcpy(col, b.col.data(), sizeof(int) * b.col.size());
+  if (val) std::memcpy(val, b.val.data(), sizeof(double) * b.val.size());
+  return (int)b.val.size();
+}
+
 int oracle_nbasis(void* hp) { return ((OracleHandle*)hp)->tw->nbasis; }
 
 int oracle_set_initial(void* hp, const double* wf, int ncomp) {

@@ -266,6 +266,11 @@ struct TWaveTents {
   double timeshift = 0;
   PolIndex pix;
   int singular = 0;
+  // wavespeed per (element, quadrature point) for Energy / Error (the reference evaluates the CF at every point,
+  // twavetents.cpp:785-793, 835-843); empty = the element value
+  std::vector<double> c_point;
+  double CAt(int elnr, int imip) const { return c_point.empty() ? wavespeed[elnr] : c_point[(size_t)elnr * snip + imip]; }
+  virtual ~TWaveTents() {}
 
   TWaveTents(int aD, int aorder, const OMesh* ama, const OSlab* atps, const double* c_el, const double* c_vert)
       : D(aD), order(aorder), ma(ama), tps(atps), pix(aD + 1, aorder) {
@@ -438,8 +443,10 @@ struct TWaveTents {
   void SetWavespeed(MappedElement& tel, double c) const { tel.scale[D] = tel.scale[0] * c; }
 
   // ---- per-tent pieces ------------------------------------------------------------------------------
+  // cpt: wavespeed per quadrature point (the reference's LocalWavespeed(imip) functor, twavetents.cpp:181, 1005-1015);
+  // nullptr = the element's constant c
   void CalcTentEl(int elnr, const OTent& tent, MappedElement& tel, double c, double* elmat, int ld, double* elvec,
-                  Matrix& topdshapes) const {
+                  Matrix& topdshapes, const double* cpt = nullptr) const {
     const int d1 = D + 1;
     Matrix pts(snip, d1);
     Vert vert = TentFaceVerts(tent, elnr, -1);
@@ -450,7 +457,7 @@ struct TWaveTents {
     const int off = !fosystem;
     for (int imip = 0; imip < snip; imip++) {
       const double weight = ir_w[imip] * area;
-      bdbvec[D * snip + imip] += n[D] * std::pow(c, -2) * weight * wavefront(elnr, (off + D) * snip + imip);
+      bdbvec[D * snip + imip] += n[D] * std::pow(cpt ? cpt[imip] : c, -2) * weight * wavefront(elnr, (off + D) * snip + imip);
       for (int d = 0; d < D; d++) {
         bdbvec[d * snip + imip] += n[D] * weight * wavefront(elnr, (off + d) * snip + imip);
         bdbvec[d * snip + imip] -= n[d] * weight * wavefront(elnr, (off + D) * snip + imip);
@@ -489,7 +496,7 @@ struct TWaveTents {
     for (int imip = 0; imip < snip; imip++) {
       const double weight = ir_w[imip] * area;
       for (int j = 0; j < nbasis; j++) {
-        bdbmat(D * snip + imip, j) += n[D] * std::pow(c, -2) * weight * bbmat(j, D * snip + imip);
+        bdbmat(D * snip + imip, j) += n[D] * std::pow(cpt ? cpt[imip] : c, -2) * weight * bbmat(j, D * snip + imip);
         for (int d = 0; d < D; d++) {
           bdbmat(d * snip + imip, j) += n[D] * weight * bbmat(j, d * snip + imip);
           bdbmat(d * snip + imip, j) -= n[d] * weight * bbmat(j, D * snip + imip);
@@ -501,8 +508,9 @@ struct TWaveTents {
     topdshapes = bbmat;
   }
 
+  // invc2: 1/c^2 per boundary point (the reference evaluates the wavespeed CF there, twavetents.cpp:409-412); nullptr = 1/cadj^2
   void CalcTentBndEl(int surfel, const OTent& tent, MappedElement& tel, const double* bd, double cadj, double* elmat,
-                     int ld, double* elvec) const {
+                     int ld, double* elvec, const double* invc2 = nullptr) const {
     const int d1 = D + 1;
     const int* sel_verts = &ma->se2v[(size_t)surfel * D];
     Vert vert = TentFaceVertsBnd(tent, sel_verts);
@@ -529,8 +537,8 @@ struct TWaveTents {
       AddAv(bbmat, bdbvec, elvec, 1.0);
     } else {  // dirichlet
       const double alpha = 0.5;
-      const double ws = 1.0 / (cadj * cadj);
       for (int imip = 0; imip < snip; imip++) {
+        const double ws = invc2 ? invc2[imip] : 1.0 / (cadj * cadj);
         const double weight = area * ir_w[imip];
         const double g = bd ? bd[imip] : 0.0;
         for (int j = 0; j < nbasis; j++) bdbmat(D * snip + imip, j) += weight * alpha * ws * bbmat(j, D * snip + imip);
@@ -707,6 +715,8 @@ struct TWaveTents {
     }
   }
 
+  virtual void PropagateTentQT(int) { throw std::runtime_error("oracle: not a quasi-Trefftz solver"); }
+  bool qt = false;
   void Propagate(int nthreads, int first_tent, int ntents_limit) {
     CSR basismat = TWaveBasis(D + 1, order, fosystem, pix);
     const int nt = (int)tps->tents.size();
@@ -721,7 +731,10 @@ struct TWaveTents {
       int cnt = (int)lt.size();
       if (ntents_limit > 0 && done + cnt > ntents_limit) cnt = (int)std::max<long long>(0, ntents_limit - done);
 #pragma omp parallel for schedule(dynamic, 1) num_threads(nthreads)
-      for (int k = 0; k < cnt; k++) PropagateTent(lt[k], basismat);
+      for (int k = 0; k < cnt; k++) {
+        if (qt) PropagateTentQT(lt[k]);
+        else PropagateTent(lt[k], basismat);
+      }
       done += cnt;
       if (ntents_limit > 0 && done >= ntents_limit) break;
     }
@@ -746,7 +759,7 @@ struct TWaveTents {
     for (int elnr = 0; elnr < ma->nel; elnr++)
       for (int imip = 0; imip < snip; imip++)
         for (int d = 0; d < D + 1; d++)
-          energy += 0.5 * (std::pow(wavespeed[elnr], -2 * (d == D)) * std::pow(wf[(size_t)elnr * w + base + d * snip + imip], 2) *
+          energy += 0.5 * (std::pow(CAt(elnr, imip), -2 * (d == D)) * std::pow(wf[(size_t)elnr * w + base + d * snip + imip], 2) *
                            ElWeight(elnr, imip));
     return energy;
   }
@@ -756,7 +769,7 @@ struct TWaveTents {
     for (int elnr = 0; elnr < ma->nel; elnr++)
       for (int imip = 0; imip < snip; imip++)
         for (int d = 0; d < D + 1; d++)
-          error += std::pow(wavespeed[elnr], -2 * (d == D)) *
+          error += std::pow(CAt(elnr, imip), -2 * (d == D)) *
                    std::pow(a[(size_t)elnr * w + (off + d) * snip + imip] - b[(size_t)elnr * w + (off + d) * snip + imip], 2) *
                    ElWeight(elnr, imip);
     return std::sqrt(error);

@@ -64,6 +64,10 @@ def _load():
         getattr(lib, f).restype = C.c_double
         getattr(lib, f).argtypes = [C.c_void_p, c_dp, c_dp, C.c_int]
     lib.oracle_basis.argtypes = [C.c_int, C.c_int, C.c_int, c_ip, c_ip, c_dp]
+    lib.oracle_qt_setup.argtypes = [C.c_void_p, C.c_int, c_dp, c_dp, C.c_int, c_dp, c_dp, C.c_int, c_dp, c_dp, c_dp, C.c_int,
+                                    c_dp, c_dp]
+    lib.oracle_set_point_wavespeed.argtypes = [C.c_void_p, c_dp]
+    lib.oracle_qt_basis.argtypes = [C.c_int, C.c_int, c_dp, c_dp, c_ip, c_ip, c_dp]
     return lib
 
 
@@ -171,6 +175,35 @@ class Oracle:
         rc = lib.oracle_twave_setup(self.h, order, _dp(c_el), _dp(c_v), len(w), _dp(xi), _dp(w))
         if rc:
             raise RuntimeError(lib.oracle_last_error().decode())
+
+    def setup_qt(self, order, cpoly, bpoly=None):
+        """QTWaveTents (src/twavetents.hpp:225-252): wavespeed polynomial cpoly, optional coefficient B (default 1)."""
+        from ngstrefftz_b200._poly import PolynomialCF
+        D = self.D
+        pts = self._keep["pts"]
+        bpoly = bpoly or PolynomialCF.constant(D, 1.0)
+        c_el = np.ascontiguousarray(cpoly(self.centroids))
+        c_v = np.ascontiguousarray(cpoly(pts))
+        xi, w = reference_rule(D, 2 * order)
+        vxi, vw = reference_rule(D + 1, 2 * order)
+        xi, w, vxi, vw = (np.ascontiguousarray(a, dtype=np.float64) for a in (xi, w, vxi, vw))
+        aa = cpoly.taylor_inverse_square(pts, max(order - 2, 0))
+        bb = bpoly.taylor(pts, order - 1)
+        cc = np.ascontiguousarray(cpoly.coef_array())
+        self.order, self.nip, self.xi, self.w, self.c_el = order, len(w), xi, w, c_el
+        rc = lib.oracle_qt_setup(self.h, order, _dp(c_el), _dp(c_v), len(w), _dp(xi), _dp(w), cpoly.deg, _dp(cc), _dp(aa),
+                                 _dp(bb), len(vw), _dp(vxi), _dp(vw))
+        if rc:
+            raise RuntimeError(lib.oracle_last_error().decode())
+        self.set_point_wavespeed(cpoly)
+
+    def set_point_wavespeed(self, cf):
+        """Energy / Error with the wavespeed evaluated at every quadrature point (src/twavetents.cpp:785-793, 835-843)."""
+        if cf is None:
+            lib.oracle_set_point_wavespeed(self.h, None)
+            return
+        c = np.ascontiguousarray(cf(self.quadrature_points().reshape(-1, self.D)), dtype=np.float64)
+        lib.oracle_set_point_wavespeed(self.h, _dp(c))
 
     def quadrature_points(self):
         t = self._keep
