@@ -80,6 +80,21 @@ void ngst_slab_destroy(ngst_slab* s);
  * device: CUDA device ordinal. Fails with NGST_ERR_CUDA when no device is usable. */
 int ngst_twave_create(const ngst_slab* s, int order, const double* c_el, const double* c_vertex, int device,
                       ngst_twave** out);
+/* Quasi-Trefftz solver: TWave(order, tps, wavespeedcf, BBcf) -> QTWaveTents<D>, D = 1, 2 (src/twavetents.cpp:1201-1216,
+ * src/twavetents.hpp:225-252; Propagate src/twavetents.cpp:967-1144). NGSolve CoefficientFunctions are replaced by
+ *  - the wavespeed as a polynomial c(x) of total degree cdeg in the D space coordinates, coefficients in
+ *    first-coordinate-outermost monomial order (evaluated on the device wherever the reference evaluates the CF:
+ *    src/twavetents.cpp:1008, 1071, 1099; 409-412);
+ *  - Taylor tables at the mesh vertices, aa_taylor[v][j] = d^alpha_j (1/c^2)(x_v) / alpha_j!, |alpha| <= order-2, and
+ *    bb_taylor[v][j] = d^alpha_j B(x_v) / alpha_j!, |alpha| <= order-1 (what ComputeDerivs + Evaluate produce in
+ *    src/trefftzfespace.hpp:59-126, src/trefftzfespace.cpp:1076-1089), same monomial order.
+ * c_el / c_vertex as in ngst_twave_create (used for MaxAdiam only). All other ngst_twave_* calls apply. */
+int ngst_qtwave_create(const ngst_slab* s, int order, const double* c_el, const double* c_vertex, int device, int cdeg,
+                       const double* ccoef, const double* aa_taylor, const double* bb_taylor, ngst_twave** out);
+/* Energy / Error with the wavespeed evaluated at every quadrature point, as the reference does with its CF
+ * (src/twavetents.cpp:785-793, 835-843), instead of one value per element; ccoef == NULL restores the element values. */
+int ngst_twave_set_wavespeed_poly(ngst_twave* t, int cdeg, const double* ccoef);
+
 /* ---- multi-GPU (one process per GPU; the reference has no distributed Propagate).
  * The spatial mesh is partitioned by vertex ownership: vertex_owner[v] in [0, nranks). A tent runs on the owner of its
  * vertex; an element is LOCAL to every rank owning one of its vertices. Every rank pitches the same global slab and

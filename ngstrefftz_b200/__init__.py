@@ -19,9 +19,10 @@ import numpy as np
 
 from . import _capi
 from ._capi import NgstError, check, dptr, f64, i32, iptr, lib
+from ._poly import PolynomialCF
 
 __all__ = ["Mesh", "SegMesh", "UnitSquareMesh", "UnitCubeMesh", "StructuredMesh", "TentSlab", "Tent", "TWave",
-           "TrefftzTents", "TWaveTents", "TaskManager", "SetNumThreads", "NgstError"]
+           "TrefftzTents", "TWaveTents", "TaskManager", "SetNumThreads", "NgstError", "PolynomialCF"]
 
 
 class TaskManager:
@@ -248,7 +249,7 @@ class TrefftzTents:
 class TWaveTents(TrefftzTents):
     """TWaveTents<D> (src/twavetents.hpp:95-224), state resident on one B200."""
 
-    def __init__(self, order, tps, wavespeedcf, device=0, partition=None, comm_id=None):
+    def __init__(self, order, tps, wavespeedcf, device=0, partition=None, comm_id=None, BBcf=None):
         """partition: None (one GPU) or (rank, nranks, owner) with owner either an int array (one rank per mesh vertex)
         or a tuple (gx, gy, ..) = brick grid over the mesh's bounding box. comm_id: 128-byte NCCL id shared by all ranks
         (default: created on rank 0 and broadcast with torch.distributed, which must be initialised)."""
@@ -268,7 +269,21 @@ class TWaveTents(TrefftzTents):
         self.c_el = c_el
         self._h = C.c_void_p()
         self.partition = None
-        if partition is None:
+        self.qt = BBcf is not None
+        if self.qt:
+            # TWave(order, tps, wavespeedcf, BBcf) -> QTWaveTents (src/twavetents.cpp:1201-1216)
+            if not isinstance(wavespeedcf, PolynomialCF):
+                raise TypeError("quasi-Trefftz: the wavespeed must be a ngstrefftz_b200.PolynomialCF (polynomial in x)")
+            if partition is not None:
+                raise NotImplementedError("quasi-Trefftz: multi-GPU partition is not supported yet")
+            if not isinstance(BBcf, PolynomialCF):
+                BBcf = PolynomialCF.constant(mesh.dim, float(BBcf))
+            aa = f64(wavespeedcf.taylor_inverse_square(mesh.points, max(self.order - 2, 0)))
+            bb = f64(BBcf.taylor(mesh.points, self.order - 1))
+            cc = f64(wavespeedcf.coef_array())
+            check(lib.ngst_qtwave_create(tps._h, self.order, dptr(c_el), dptr(c_vertex), int(device), wavespeedcf.deg,
+                                         dptr(cc), dptr(aa), dptr(bb), C.byref(self._h)))
+        elif partition is None:
             check(lib.ngst_twave_create(tps._h, self.order, dptr(c_el), dptr(c_vertex), int(device), C.byref(self._h)))
         else:
             rank, nranks, owner = partition
@@ -409,6 +424,14 @@ class TWaveTents(TrefftzTents):
     def kernel_name(self):
         return lib.ngst_twave_kernel_name(self._h).decode()
 
+    def set_point_wavespeed(self, cf):
+        """Energy / Error with the wavespeed polynomial evaluated at every quadrature point (src/twavetents.cpp:785-793)."""
+        if cf is None:
+            check(lib.ngst_twave_set_wavespeed_poly(self._h, 0, None))
+        else:
+            cc = f64(cf.coef_array())
+            check(lib.ngst_twave_set_wavespeed_poly(self._h, cf.deg, dptr(cc)))
+
     def set_kernel_mode(self, mode):
         """0 = automatic routing (DMMA kernel for single-wavespeed tents), 1 = generic DFMA kernel for every tent."""
         check(lib.ngst_twave_set_kernel_mode(self._h, int(mode)))
@@ -501,6 +524,4 @@ def partition_plan(tps, owner, nranks, rank):
 
 def TWave(order, tps, wavespeedcf, BBcf=None, device=0, partition=None, comm_id=None):
     """Factory of src/twavetents.cpp:1194-1228. partition / comm_id: multi-GPU (see TWaveTents)."""
-    if BBcf is not None:
-        raise NotImplementedError("quasi-Trefftz (QTWaveTents, BBcf given) is not built yet: see DESIGN.md")
-    return TWaveTents(order, tps, wavespeedcf, device=device, partition=partition, comm_id=comm_id)
+    return TWaveTents(order, tps, wavespeedcf, device=device, partition=partition, comm_id=comm_id, BBcf=BBcf)

@@ -253,6 +253,37 @@ int ngst_twave_create_partitioned(const ngst_slab* s, int order, const double* c
   });
 }
 
+int ngst_qtwave_create(const ngst_slab* s, int order, const double* c_el, const double* c_vertex, int device, int cdeg,
+                       const double* ccoef, const double* aa_taylor, const double* bb_taylor, ngst_twave** out) {
+  return guarded([&] {
+    need(s, "slab"); need(out, "out"); need(c_el, "c_el"); need(ccoef, "ccoef"); need(aa_taylor, "aa_taylor");
+    need(bb_taylor, "bb_taylor");
+    const SimplexMesh& m = *s->s.mesh;
+    if (order < 2 || cdeg < 0 || cdeg > 8) throw std::invalid_argument("ngst_qtwave_create: order >= 2 and 0 <= cdeg <= 8 required");
+    std::vector<double> ce(c_el, c_el + m.nel), cv;
+    if (c_vertex) cv.assign(c_vertex, c_vertex + m.nv);
+    QtHostData q;
+    q.cdeg = cdeg;
+    q.ccoef.assign(ccoef, ccoef + monomial_exponents(m.D, cdeg).size() / m.D);
+    const size_t nA = monomial_exponents(m.D, order - 2).size() / m.D, nB = monomial_exponents(m.D, order - 1).size() / m.D;
+    q.aa.assign(aa_taylor, aa_taylor + (size_t)m.nv * nA);
+    q.bb.assign(bb_taylor, bb_taylor + (size_t)m.nv * nB);
+    auto h = std::make_unique<ngst_twave>();
+    h->slab = s;
+    h->solver = std::make_unique<Solver>(s->s, order, ce, cv, device, nullptr, &q);
+    *out = h.release();
+  });
+}
+
+int ngst_twave_set_wavespeed_poly(ngst_twave* t, int cdeg, const double* ccoef) {
+  return guarded([&] {
+    need(t, "solver");
+    if (ccoef && (cdeg < 0 || cdeg > 8)) throw std::invalid_argument("ngst_twave_set_wavespeed_poly: 0 <= cdeg <= 8 required");
+    if (t->solver->is_qt() && !ccoef) throw std::logic_error("ngst_twave_set_wavespeed_poly: the quasi-Trefftz solver needs its wavespeed polynomial");
+    t->solver->SetWavespeedPoly(cdeg, ccoef);
+  });
+}
+
 int ngst_comm_unique_id(void* out128) {
   const int rc = guarded([&] { need(out128, "out128"); halo_unique_id(out128); });
   return rc == NGST_OK ? rc : NGST_ERR_COMM;

@@ -27,8 +27,11 @@ T* Solver::Upload(const std::vector<T>& v) {
 }
 
 Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el, const std::vector<double>& c_vertex,
-               int device, const PartitionPlan* plan)
+               int device, const PartitionPlan* plan, const QtHostData* qt)
     : mesh_(*slab.mesh), slab_(slab), plan_(plan), order_(order), device_(device), c_el_(c_el), c_vertex_(c_vertex) {
+  qt_ = qt != nullptr;
+  if (qt_ && (mesh_.D > 2 || order < 2))
+    throw std::invalid_argument("TWave: the quasi-Trefftz solver exists for D = 1, 2 (twavetents.cpp:1150-1151) and order >= 2");
   if (order < 1 || order > 12) throw std::invalid_argument("TWave: order must be in 1..12");
   if (slab.ntents == 0 && !plan) throw std::logic_error("TWave: the slab has no tents (call PitchTents first)");
   if ((int)c_el_.size() != mesh_.nel) throw std::invalid_argument("TWave: need one wavespeed per element");
@@ -58,7 +61,7 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
   basis_so_ = twave_basis(d1, order, 0);
   basis_fo_ = twave_basis(d1, order, 1);
   basis_ = basis_so_;
-  staged_ = stage_tents(mesh_, slab_, c_el_, c_vertex_, rule_);
+  staged_ = stage_tents(mesh_, slab_, c_el_, c_vertex_, rule_, qt_);
 
   const int Q = rule_.nip;
   std::vector<double> lam((size_t)Q * d1);
@@ -117,7 +120,7 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
   a.bnd_data = nullptr;
   a.max_ndom = staged_.max_ndom;
   // ---- kernel routing: single-wavespeed tents run on the fast DMMA kernel when a variant exists for (D, order)
-  fast_ = tent_fast_available(D, order);
+  fast_ = !qt_ && tent_fast_available(D, order);
   if (fast_) {
     fstage_ = stage_fast(mesh_, slab_, staged_, c_el_, rule_, basis_so_, basis_fo_, fast_fe_stride(D), fast_ff_stride(D));
     fargs_.fe = Upload(fstage_.fe);
@@ -159,6 +162,70 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
   CU(cudaMemset(d_singular_, 0, sizeof(int)));
   a.singular = d_singular_;
 
+  if (qt_) {
+    const int nv = mesh_.nv;
+    const std::vector<int> eA = monomial_exponents(D, order - 2), eB = monomial_exponents(D, order - 1);
+    const int nA = (int)eA.size() / D, nB = (int)eB.size() / D;
+    if ((int)qt->aa.size() != nv * nA || (int)qt->bb.size() != nv * nB)
+      throw std::invalid_argument("TWave: Taylor tables must hold nv x (#monomials of degree <= order-2 / order-1) values");
+    auto find = [&](const std::vector<int>& ex, int dim, const int* e) {
+      for (int j = 0; j < (int)ex.size() / dim; j++) {
+        bool same = true;
+        for (int k = 0; k < dim; k++) same = same && ex[(size_t)j * dim + k] == e[k];
+        if (same) return j;
+      }
+      return -1;
+    };
+    const int P = order, P1 = P + 1;
+    std::vector<int> idxA((size_t)(P - 1) * (P - 1), -1), idxB((size_t)P * P, -1), idx3((size_t)P1 * P1 * P1, -1);
+    for (int nx = 0; nx < P; nx++)
+      for (int ny = 0; ny < P; ny++) {
+        if (D == 1 && ny > 0) continue;
+        const int e[2] = {nx, ny};
+        if (nx + ny <= P - 1) idxB[(size_t)nx * P + ny] = find(eB, D, e);
+        if (nx < P - 1 && ny < P - 1 && nx + ny <= P - 2) idxA[(size_t)nx * (P - 1) + ny] = find(eA, D, e);
+      }
+    for (int x = 0; x <= P; x++)
+      for (int y = 0; y <= P; y++)
+        for (int t = 0; t <= P; t++) {
+          if (x + y + t > P || (D == 1 && y > 0)) continue;
+          const int e3[3] = {x, y, t}, e2[2] = {x, t};
+          idx3[((size_t)x * P1 + y) * P1 + t] = find(basis_so_.expo, d1, D == 1 ? e2 : e3);
+        }
+    // wavespeed polynomial: non-zero terms only
+    const std::vector<int> eC = monomial_exponents(D, qt->cdeg);
+    if ((int)qt->ccoef.size() != (int)eC.size() / D) throw std::invalid_argument("TWave: wavespeed polynomial has the wrong number of coefficients");
+    std::vector<double> cc;
+    std::vector<int> ce;
+    for (size_t j = 0; j < qt->ccoef.size(); j++)
+      if (qt->ccoef[j] != 0.0) {
+        cc.push_back(qt->ccoef[j]);
+        for (int k = 0; k < D; k++) ce.push_back(eC[j * D + k]);
+      }
+    if (cc.empty()) throw std::invalid_argument("TWave: the wavespeed polynomial is zero");
+    const SimplexRule vrule = make_simplex_rule(d1, 2 * order);
+    std::vector<double> tsize(slab_.ntents);
+    for (int t = 0; t < slab_.ntents; t++) tsize[t] = 1.0 / staged_.scale[t];
+    QtArgs& q = qargs_;
+    q.ccoef = Upload(cc);
+    q.cexpo = Upload(ce);
+    q.ncterm = (int)cc.size();
+    q.aa = Upload(qt->aa);
+    q.bb = Upload(qt->bb);
+    q.nA = nA;
+    q.nB = nB;
+    q.idxA = Upload(idxA);
+    q.idxB = Upload(idxB);
+    q.idx3 = Upload(idx3);
+    q.tent_vertex = Upload(slab_.vertex);
+    q.tentsize = Upload(tsize);
+    q.vxi = Upload(vrule.xi);
+    q.vw = Upload(vrule.w);
+    q.Qv = vrule.nip;
+    SetWavespeedPoly(qt->cdeg, qt->ccoef.data());
+    q.c_point = d_cpoint_;
+  }
+
   // element quadrature weights |detJ| * w (GetWeight, twavetents.cpp:793,818,843)
   {
     std::vector<double> elw((size_t)nel_ * Q);
@@ -183,6 +250,29 @@ Solver::~Solver() {
   if (ev0_) cudaEventDestroy(ev0_);
   if (ev1_) cudaEventDestroy(ev1_);
   if (stream_) cudaStreamDestroy(stream_);
+}
+
+void Solver::SetWavespeedPoly(int deg, const double* coef) {
+  CU(cudaSetDevice(device_));
+  if (!coef) { d_cpoint_ = nullptr; return; }
+  const int D = mesh_.D, Q = rule_.nip;
+  const std::vector<int> ex = monomial_exponents(D, deg);
+  const int nt = (int)ex.size() / D;
+  std::vector<double> x((size_t)nel_ * Q * D), cp((size_t)nel_ * Q);
+  Quadrature(x.data(), nullptr);
+#pragma omp parallel for schedule(static)
+  for (long long i = 0; i < (long long)nel_ * Q; i++) {
+    double s = 0;
+    for (int j = 0; j < nt; j++) {
+      double m = coef[j];
+      if (m == 0.0) continue;
+      for (int d = 0; d < D; d++)
+        for (int k = 0; k < ex[(size_t)j * D + d]; k++) m *= x[(size_t)i * D + d];
+      s += m;
+    }
+    cp[i] = s;
+  }
+  d_cpoint_ = Upload(cp);
 }
 
 void Solver::Quadrature(double* x, double* weight) const {
@@ -241,6 +331,21 @@ void Solver::SetInitial(const double* wf, int ncomp) {
   fargs_.cptr = d_cptr_[fosystem_];
   fargs_.crow = d_crow_[fosystem_];
   fargs_.cval = d_cval_[fosystem_];
+  if (qt_) {
+    if (fosystem_) throw std::invalid_argument("SetInitial: the quasi-Trefftz solver takes second-order initial data (D+2 components)");
+    a.rowptr = nullptr; a.col = nullptr; a.val = nullptr;
+    const size_t budget = 150 * 1024;
+    int qc = std::min(std::max(rule_.nip, qargs_.Qv), 16);
+    for (; qc > 1; qc--) {
+      a.Qc = qc;
+      if (tent_qt_smem_bytes(D, a, qargs_) <= budget) break;
+    }
+    a.Qc = qc;
+    smem_ = tent_qt_smem_bytes(D, a, qargs_);
+    if (smem_ > 227 * 1024 || a.N > 64)
+      throw std::invalid_argument("TWave: quasi-Trefftz local system too large for shared memory");
+    return;
+  }
   // chunk of quadrature points staged in shared memory at a time
   const size_t budget = 100 * 1024;
   int qc = std::min(rule_.nip, 32);
@@ -273,7 +378,17 @@ void Solver::Propagate() {
   const int nlev = (int)slab_.level_off.size() - 1;
   int launches = 0;
   CU(cudaEventRecord(ev0_, stream_));
-  for (int l = 0; l < nlev && force_generic_; l++) {
+  for (int l = 0; l < nlev && qt_; l++) {
+    TentKernelArgs a = args_;
+    a.tents = d_level_all_ + slab_.level_off[l];
+    a.ntents = slab_.level_off[l + 1] - slab_.level_off[l];
+    if (a.ntents > 0) {
+      CU(launch_tent_qt(mesh_.D, a, qargs_, smem_, stream_));
+      launches++;
+    }
+    if (comm_) launches += ExchangeLevel(l);
+  }
+  for (int l = 0; l < nlev && force_generic_ && !qt_; l++) {
     TentKernelArgs a = args_;
     a.tents = d_level_all_ + slab_.level_off[l];
     a.ntents = slab_.level_off[l + 1] - slab_.level_off[l];
@@ -283,7 +398,7 @@ void Solver::Propagate() {
     }
     if (comm_) launches += ExchangeLevel(l);
   }
-  for (int l = 0; l < nlev && !force_generic_; l++) {
+  for (int l = 0; l < nlev && !force_generic_ && !qt_; l++) {
     TentKernelArgs a = args_;
     a.tents = d_level_fast_ + fast_off_[l];
     a.ntents = fast_off_[l + 1] - fast_off_[l];
@@ -349,7 +464,7 @@ void Solver::GetWavefront(double* out) {
 }
 
 double Solver::ReduceElements(const double* a, const double* b, int mode) {
-  CU(launch_element_reduce(mode, mesh_.D, nel_, rule_.nip, ncomp_, fosystem_, d_elw_, args_.c_el, a, b,
+  CU(launch_element_reduce(mode, mesh_.D, nel_, rule_.nip, ncomp_, fosystem_, d_elw_, args_.c_el, d_cpoint_, a, b,
                            d_scratch_, stream_));
   std::vector<double> part(nel_);
   CU(cudaMemcpyAsync(part.data(), d_scratch_, sizeof(double) * nel_, cudaMemcpyDeviceToHost, stream_));

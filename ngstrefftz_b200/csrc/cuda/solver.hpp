@@ -15,8 +15,18 @@
 #include "halo.hpp"
 #include "tent_fast.cuh"
 #include "tent_kernel.cuh"
+#include "tent_qt.cuh"
 
 namespace ngst {
+
+// Inputs of the quasi-Trefftz solver (QTWaveTents, src/twavetents.hpp:225-252) that NGSolve CoefficientFunctions provide in
+// the reference: the wavespeed as a polynomial in x and the Taylor tables of 1/c^2 and B at the mesh vertices.
+struct QtHostData {
+  int cdeg = 0;
+  std::vector<double> ccoef;  // monomial_exponents(D, cdeg) order
+  std::vector<double> aa;     // nv * nA, nA = #monomials of degree <= order-2
+  std::vector<double> bb;     // nv * nB, nB = #monomials of degree <= order-1
+};
 
 class Solver {
  public:
@@ -24,7 +34,10 @@ class Solver {
   // plan its partition plan; c_el / c_vertex stay GLOBAL arrays; every element-indexed array of the public interface
   // (wavefronts, quadrature) is then indexed by LOCAL element (plan->loc2glob).
   Solver(const TentSlab& slab, int order, const std::vector<double>& c_el, const std::vector<double>& c_vertex,
-         int device, const PartitionPlan* plan = nullptr);
+         int device, const PartitionPlan* plan = nullptr, const QtHostData* qt = nullptr);
+  // wavespeed polynomial for Energy / Error with c evaluated at every quadrature point (twavetents.cpp:785-793, 835-843)
+  void SetWavespeedPoly(int deg, const double* coef);
+  bool is_qt() const { return qt_; }
   ~Solver();
   Solver(const Solver&) = delete;
   Solver& operator=(const Solver&) = delete;
@@ -54,7 +67,7 @@ class Solver {
 
   double timeshift() const { return timeshift_; }
   void set_timeshift(double t) { timeshift_ = t; }
-  const char* kernel_name() const { return (fast_ && !force_generic_) ? "tent_kernel_fast" : "tent_kernel_generic"; }
+  const char* kernel_name() const { return qt_ ? "tent_kernel_qt" : ((fast_ && !force_generic_) ? "tent_kernel_fast" : "tent_kernel_generic"); }
   int ntents_fast() const { return fast_ ? fast_off_.back() : 0; }
   // 0 = automatic routing (fast kernel where possible), 1 = every tent on the generic DFMA kernel (A/B evidence)
   void set_kernel_mode(int mode) { force_generic_ = mode == 1; }
@@ -97,7 +110,9 @@ class Solver {
   int* d_level_tents_ = nullptr;   // per level: generic-kernel tents (material interfaces or no fast variant)
   int* d_level_fast_ = nullptr;    // per level: fast-kernel tents, most elements first
   std::vector<int> gen_off_, fast_off_;  // nlevels + 1 offsets into the two lists
-  bool fast_ = false, force_generic_ = false;
+  bool fast_ = false, force_generic_ = false, qt_ = false;
+  QtArgs qargs_{};
+  double* d_cpoint_ = nullptr;     // nel * nip wavespeed per quadrature point (QT; optional for reductions)
   int* d_level_all_ = nullptr;     // per level: all tents (slab order), for force_generic_
   FastStage fstage_;
   FastArgs fargs_{};
@@ -124,8 +139,8 @@ class Solver {
 size_t tent_generic_smem_bytes(int D, const TentKernelArgs& a);
 cudaError_t launch_tent_generic(int D, const TentKernelArgs& a, int threads, size_t smem, cudaStream_t stream);
 cudaError_t launch_element_reduce(int mode, int D, int nel, int Q, int ncomp, int fosystem, const double* elw,
-                                  const double* c_el, const double* a, const double* b, double* out,
-                                  cudaStream_t stream);
+                                  const double* c_el, const double* c_point, const double* a, const double* b,
+                                  double* out, cudaStream_t stream);
 
 // fp64_peak.cu: which 0 = DFMA pipe, 1 = DMMA (mma.sync m8n8k4 f64); TFLOP/s on the current device
 cudaError_t measure_fp64_peak(int which, int reps, double* tflops);

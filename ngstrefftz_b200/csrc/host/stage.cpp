@@ -76,7 +76,7 @@ void tent_face_normal(int D, const double* ve, int top, double* n) {
 }
 
 StagedTents stage_tents(const SimplexMesh& m, const TentSlab& slab, const std::vector<double>& c_el,
-                        const std::vector<double>& c_vertex, const SimplexRule& rule) {
+                        const std::vector<double>& c_vertex, const SimplexRule& rule, bool qt) {
   if ((int)c_el.size() != m.nel) throw std::runtime_error("stage_tents: c_el size mismatch");
   if ((int)c_vertex.size() != m.nv) throw std::runtime_error("stage_tents: c_vertex size mismatch");
   const int D = m.D, d1 = D + 1, nt = slab.ntents, Q = rule.nip;
@@ -98,6 +98,10 @@ StagedTents stage_tents(const SimplexMesh& m, const TentSlab& slab, const std::v
       int j = 0;
       while (c_el[slab.els.val[e0 + i]] != c_el[slab.els.val[e0 + j]]) j++;
       dom_of[e0 + i] = (j == i) ? nd++ : dom_of[e0 + j];
+    }
+    if (qt) {
+      nd = 1;
+      for (int i = 0; i < ne; i++) dom_of[e0 + i] = 0;
     }
     st.ndom[t] = nd;
     st.max_ndom = std::max(st.max_ndom, nd);
@@ -167,6 +171,20 @@ StagedTents stage_tents(const SimplexMesh& m, const TentSlab& slab, const std::v
         }
       }
       st.scale[t] = 1.0 / adiam;
+    }
+    if (qt) {  // TentXdiam, twavetents.cpp:1125-1144
+      double diam = 0;
+      auto dist = [&](const double* p, const double* q) {
+        double l2 = 0;
+        for (int d = 0; d < D; d++) l2 += (p[d] - q[d]) * (p[d] - q[d]);
+        return std::sqrt(l2);
+      };
+      for (int k = 0; k < nnb; k++) {
+        const double* v1 = m.point(nbv[k]);
+        diam = std::max(diam, dist(v1, m.point(vtx)));
+        for (int j = k; j < nnb; j++) diam = std::max(diam, dist(v1, m.point(nbv[j])));
+      }
+      st.scale[t] = 1.0 / diam;
     }
 
     const int e0 = slab.els.off[t], ne = slab.els.size(t);

@@ -46,8 +46,10 @@ struct StagedTents {
 };
 
 // c_vertex: wavespeed "evaluated at the vertices" for TentAdiam (twavetents.cpp:871-895).
+// qt = true stages for QTWaveTents (src/twavetents.cpp:967-1144): one domain per tent (no macro elements, 992-993), no
+// interface faces, isotropic scale 1 / TentXdiam (984-990, 1125-1144).
 StagedTents stage_tents(const SimplexMesh& m, const TentSlab& slab, const std::vector<double>& c_el,
-                        const std::vector<double>& c_vertex, const SimplexRule& rule);
+                        const std::vector<double>& c_vertex, const SimplexRule& rule, bool qt = false);
 
 // Operands of the fast single-wavespeed kernel (cuda/tent_fast.cu; record layouts in cuda/tent_fast.cuh): everything
 // per tent-element / boundary face that does not depend on the wave state, in scaled tent coordinates.

@@ -159,3 +159,77 @@ def test_errors_on_gpu(built):
     with pytest.raises(NgstError) as ei:
         ng.TWave(2, ts, 1.0, device=99)
     assert ei.value.code == -3
+
+
+# ---------------------------------------------------------------------------------------------- quasi-Trefftz (QTWaveTents)
+def qt_both(mesh, order, dt, nslabs=1, cpoly=None, bpoly=None):
+    from test_oracle_qt import qt_exact
+    D = mesh.dim
+    c = cpoly or ng.PolynomialCF.affine([1.0] * D, 1.0)
+    f = qt_exact(D)
+    bnd = lambda x, t: f(x, t)[:, D + 1]  # noqa: E731
+    ts = ng.TentSlab(mesh, "edge")
+    ts.SetMaxWavespeed(c)
+    assert ts.PitchTents(dt, True, 2 / 3)
+    tw = ng.TWave(order, ts, c, BBcf=bpoly if bpoly is not None else 1)
+    tw.SetInitial(f)
+    tw.SetBoundaryCF(bnd)
+    o = Oracle(mesh)
+    assert o.pitch(dt, True, 2 / 3, c(o.centroids))
+    e1, e2 = ts.export(), o.export()
+    for k in e2:
+        assert np.array_equal(e1[k], e2[k]), f"tent table {k} differs"
+    o.setup_qt(order, c, bpoly)
+    o.set_initial(f)
+    o.set_boundary_cf(bnd)
+    for _ in range(nslabs):
+        tw.Propagate()
+        o.propagate()
+    assert tw.kernel_name() == "tent_kernel_qt" and tw.last_launches() > 0
+    return tw, o, f
+
+
+QT_CASES = {
+    "1d_p4_h8": (lambda: ng.SegMesh(8, 0, math.pi), 4, 1.0, 1, None),
+    "1d_p3_2slabs": (lambda: ng.SegMesh(16, 0, 1), 3, 0.2, 2, None),
+    "2d_p4": (lambda: ng.UnitSquareMesh(4), 4, 0.25, 1, None),
+    "2d_p5": (lambda: ng.UnitSquareMesh(3), 5, 0.2, 1, None),
+    "2d_p3_varB": (lambda: ng.UnitSquareMesh(4), 3, 0.2, 2, "B"),
+}
+
+
+@pytest.mark.parametrize("name", list(QT_CASES))
+def test_parity_quasi_trefftz(built, name):
+    """QTWaveTents (twavetents.cpp:967-1144): per-tent basis recursion, per-point wavespeed, cone volume terms."""
+    mk, order, dt, nslabs, var = QT_CASES[name]
+    mesh = mk()
+    bpoly = ng.PolynomialCF(mesh.dim, {(0, 0): 1.0, (1, 0): 0.2, (0, 1): 0.1}) if var == "B" else None
+    tw, o, f = qt_both(mesh, order, dt, nslabs, bpoly=bpoly)
+    wf, ref = tw.GetWavefront(), o.wavefront()
+    rel = np.abs(wf - ref).max() / np.abs(ref).max()
+    assert rel <= 1e-9, rel
+    exact = tw.MakeWavefront(f, nslabs * dt)
+    eg, eo = tw.Error(wf, exact), o.error(ref, o.make_wavefront(f, nslabs * dt))
+    assert abs(eg - eo) <= 1e-6 * eo + 1e-12, (eg, eo)  # Error with the wavespeed evaluated at every point
+    assert abs(tw.Energy(wf) - o.energy(ref)) <= 1e-9 * o.energy(ref)
+
+
+def test_reference_doctest_digit_qt_on_gpu(built):
+    """test/tents.py:133-141, second entry (h = 8): 0.001..."""
+    tw, o, f = qt_both(ng.SegMesh(8, 0, math.pi), 4, 1.0)
+    err = tw.Error(tw.GetWavefront(), tw.MakeWavefront(f, 1.0))
+    assert repr(err).startswith("0.001"), err
+
+
+def test_pointwise_wavespeed_in_error_plain_trefftz(built):
+    """Plain Trefftz with a varying wavespeed (TestQTrefftz(..., None), test/tents.py:150-157): Error evaluates c per point."""
+    from test_oracle_qt import qt_exact
+    c = ng.PolynomialCF.affine([1.0], 1.0)
+    f = qt_exact(1)
+    tw, o = both(ng.SegMesh(16, 0, math.pi), 4, c, 1.0, f, lambda x, t: f(x, t)[:, 2])
+    tw.set_point_wavespeed(c)
+    o.set_point_wavespeed(c)
+    wf = tw.GetWavefront()
+    err = tw.Error(wf, tw.MakeWavefront(f, 1.0))
+    assert repr(err).startswith("0.01"), err
+    assert abs(err - o.error(o.wavefront(), o.make_wavefront(f, 1.0))) <= 1e-9 * err
