@@ -28,6 +28,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
+_RESULT = []  # the JSON line, printed by main() on the real stdout
 METRIC = "tents/s (3+1D order-4 Trefftz-DG tent slab, one Propagate per step)"
 WEAK_GRIDS = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}
 
@@ -186,7 +187,7 @@ def run_reference(args):
         "e2e": {"value": r["tents_per_s"], "unit": "tents/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    _RESULT.append(json.dumps(line))
 
 
 # ------------------------------------------------------------------------------------------------ our arm
@@ -400,17 +401,28 @@ def run_ours(args):
                                 "sample": f"first {r['sample_tents']} tents (level order) of the N=1 slab "
                                           f"({r['slab_tents']} tents), 1 warm-up + 1 timed pass, oracle restatement of "
                                           f"the reference's Propagate with OpenMP over the tents of a level"}
-    print(json.dumps(line), flush=True)
+    _RESULT.append(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
 
 def main():
     args = parse()
-    if args.impl == "reference":
-        run_reference(args)
-    else:
-        run_ours(args)
+    # stdout carries exactly ONE JSON line: anything libraries print on fd 1 meanwhile (e.g. "NCCL version ...") goes to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        if args.impl == "reference":
+            run_reference(args)
+        else:
+            run_ours(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+    if _RESULT:
+        print(_RESULT[0], flush=True)
 
 
 if __name__ == "__main__":
