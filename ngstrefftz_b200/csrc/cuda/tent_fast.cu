@@ -2,7 +2,7 @@
 //
 // Same mathematics as tent_generic.cu / TWaveTents<D>::Propagate's per-tent body (src/twavetents.cpp:92-171:
 // CalcTentEl 177-333, CalcTentBndEl 335-434, Solve 64-70, CalcTentElEval 541-590), re-organised for the B200:
-//   * one CTA of 4 warps per tent, two CTAs per SM;
+//   * one CTA of 4 warps per tent, three CTAs per SM (168 registers, 61 KB shared memory at D = 3, p = 4);
 //   * the flat list of (element, quadrature point) pairs of the tent is processed in chunks of 32 points:
 //     lane = point, warp = one quarter of the basis functions. Each warp evaluates its functions with the
 //     generated straight-line evaluators (basis_eval_gen.cuh; the reference evaluates the same polynomials through
@@ -55,11 +55,14 @@ struct Cfg {
   static constexpr int NACC = (NSYM + 1) / 2;     // accumulator tiles per warp (>= ceil(NT*NT/4) for NT >= 2)
   static constexpr int FE = fast_fe_stride(D);
   static constexpr int FF = fast_ff_stride(D);
-  // shared memory (doubles)
-  static constexpr int oA = 0;
-  static constexpr int oB = oA + NP * LDA;
-  static constexpr int oZ = (oB + NP + 1) / 2 * 2;
-  static constexpr int oCM = oZ + NP * ZS;
+  // shared memory (doubles). The system matrix A is only needed once the Gram passes are over, so where it fits it
+  // aliases the tail of the operand buffer Z (behind the two boundary-pass operands): 61 KB per CTA at D = 3, p = 4,
+  // three CTAs per SM.
+  static constexpr bool aliasA = 2 * kBS + LDA <= ZS;
+  static constexpr int oZ = 0;
+  static constexpr int oA = aliasA ? oZ + 2 * NP * kBS : oZ + NP * ZS;
+  static constexpr int oB = aliasA ? oZ + NP * ZS : oA + NP * LDA;
+  static constexpr int oCM = (oB + NP + 1) / 2 * 2;
   static constexpr int oCMD = oCM + npoly;
   static constexpr int nsmem = oCMD + d1 * npm1;
   static_assert(2 * kBS <= ZS, "boundary operands must fit in the Z buffer");
@@ -169,7 +172,7 @@ __device__ __forceinline__ void eval_group(int w, const double* xi, F&& f) {
 }
 
 template <int D, int P, int FO>
-__global__ void __launch_bounds__(kThreads, 2) tent_kernel_fast(TentKernelArgs a, FastArgs f) {
+__global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a, FastArgs f) {
   using C = Cfg<D, P, FO>;
   constexpr int d1 = C::d1, N = C::N, NT = C::NT, NP = C::NP, G = C::G, Q = C::Q, ZS = C::ZS, LDA = C::LDA;
   constexpr int NACC = C::NACC, FE = C::FE, FF = C::FF, npoly = C::npoly, npm1 = C::npm1;
@@ -413,45 +416,69 @@ __global__ void __launch_bounds__(kThreads, 2) tent_kernel_fast(TentKernelArgs a
   }
   __syncthreads();
   // ------------------------------------------------------------------ Solve (64-70 forms the inverse with LAPACK)
-  // LU with partial pivoting on the N x N system, right-hand side carried as column N. Pivoting is implicit (rows are
-  // never swapped; every thread tracks the used rows in a bit mask), the pivot search is done redundantly by every
-  // warp, so one barrier per elimination step suffices.
+  // LU on the N x N system, right-hand side carried as column N. Interior tents (no boundary face) have a symmetric
+  // positive definite matrix (Z Z^T + stabilisation): elimination in natural order needs no pivot search. Tents with
+  // boundary faces are unsymmetric: partial pivoting, implicit (rows are never swapped; every thread tracks the used rows
+  // in a bit mask, the search is done redundantly by every warp). One barrier per elimination step either way.
   for (int i = tid; i < N; i += kThreads) A[i * LDA + N] = bv[i];
   __shared__ int perm[64];
   static_assert(N <= 64, "row mask is 64 bits wide");
   __syncthreads();
   {
+    const bool spd = nfc == 0;
     unsigned long long done = 0ull;
     for (int kk = 0; kk < N; kk++) {
-      double best = -1.0;
-      int brow = 0x7fffffff;
-      for (int r = lane; r < N; r += 32) {
-        if ((done >> r) & 1ull) continue;
-        const double v = fabs(A[r * LDA + kk]);
-        if (v > best) { best = v; brow = r; }
-      }
+      int p = kk;
+      double piv;
+      if (spd) {
+        piv = A[kk * LDA + kk];
+      } else {
+        double best = -1.0;
+        int brow = 0x7fffffff;
+        for (int r = lane; r < N; r += 32) {
+          if ((done >> r) & 1ull) continue;
+          const double v = fabs(A[r * LDA + kk]);
+          if (v > best) { best = v; brow = r; }
+        }
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const double ob = __shfl_xor_sync(0xffffffffu, best, o);
-        const int orow = __shfl_xor_sync(0xffffffffu, brow, o);
-        if (ob > best || (ob == best && orow < brow)) { best = ob; brow = orow; }
+        for (int o = 16; o > 0; o >>= 1) {
+          const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+          const int orow = __shfl_xor_sync(0xffffffffu, brow, o);
+          if (ob > best || (ob == best && orow < brow)) { best = ob; brow = orow; }
+        }
+        p = brow;
+        piv = A[p * LDA + kk];
       }
-      const int p = brow;
       done |= 1ull << p;
-      double pinv = 0.0;
-      if (best > 0.0) pinv = 1.0 / A[p * LDA + kk];
+      const bool ok = spd ? (piv > 0.0) : (piv != 0.0);
+      const double pinv = ok ? 1.0 / piv : 0.0;
       if (tid == 0) {
         perm[kk] = p;
-        if (!(best > 0.0)) atomicAdd(a.singular, 1);
+        if (!ok) atomicAdd(a.singular, 1);
       }
       const int c0 = kk + 1 + lane, c1 = c0 + 32;  // columns kk+1 .. N (N = right-hand side)
-      const double pr0 = (c0 <= N) ? A[p * LDA + c0] : 0.0;
-      const double pr1 = (c1 <= N) ? A[p * LDA + c1] : 0.0;
-      for (int r = w; r < N; r += 4) {
-        if ((done >> r) & 1ull) continue;
-        const double m = A[r * LDA + kk] * pinv;
-        if (c0 <= N) A[r * LDA + c0] -= m * pr0;
-        if (c1 <= N) A[r * LDA + c1] -= m * pr1;
+      const bool h0 = c0 <= N, h1 = c1 <= N;
+      const double pr0 = h0 ? A[p * LDA + c0] : 0.0;
+      const double pr1 = h1 ? A[p * LDA + c1] : 0.0;
+      // rows r = w, w+4, ..: four at a time, loads first
+      for (int r0 = w; r0 < N; r0 += 16) {
+        double m[4], x0[4], x1[4];
+        bool act[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const int r = r0 + 4 * u;
+          act[u] = r < N && !((done >> r) & 1ull);
+          m[u] = act[u] ? A[r * LDA + kk] : 0.0;
+          x0[u] = (act[u] && h0) ? A[r * LDA + c0] : 0.0;
+          x1[u] = (act[u] && h1) ? A[r * LDA + c1] : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const int r = r0 + 4 * u;
+          const double mm = m[u] * pinv;
+          if (act[u] && h0) A[r * LDA + c0] = x0[u] - mm * pr0;
+          if (act[u] && h1) A[r * LDA + c1] = x1[u] - mm * pr1;
+        }
       }
       __syncthreads();
     }
