@@ -354,9 +354,11 @@ def run_ours(args):
         except (OSError, ValueError):
             traffic = None
     # executed tensor-path work of tent_kernel_fast: symmetric rank-k updates touch only the NT(NT+1)/2 upper-triangular
-    # 8x8 tiles; (D+1) k-rows per top-face point, 1 per bottom-face point (second-order form), 4 k-rows per DMMA
+    # 8x8 tiles; (D+1) k-rows per top-face point, 1 per bottom-face point (second-order form), 4 k-rows per DMMA. The
+    # top-face Gram runs on the rule of order 2p-2 (Qt = p^D points, exact for its integrand; tent_fast.cu Cfg::QT)
     nt_tiles = (N + 7) // 8
-    dmma_el = (Q * (D + 1) / 4.0 + (0 if tw.fosystem else Q / 4.0)) * (nt_tiles * (nt_tiles + 1) / 2) * 512.0
+    Qt = order ** D
+    dmma_el = (Qt * (D + 1) / 4.0 + (0 if tw.fosystem else Q / 4.0)) * (nt_tiles * (nt_tiles + 1) / 2) * 512.0
     dmma_tf = dmma_el * float(nels.sum()) * args.steps / (float(np.sum(dev_ms)) * 1e-3) * 1e-12
     roofline = {"bound": "fp64", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach_tf / fp64_peak,
                 "traffic": traffic, "kernel": tw.kernel_name(),
@@ -364,7 +366,8 @@ def run_ours(args):
                                f"(ngst_device_fp64_peak), DMMA+DFMA interleaved 4:1 {mixed.value:.2f}; MEASURED_PEAKS.json holds no FP64 figure",
                 "flops_per_tent_element": f_el,
                 "note": "achieved = algorithmic flops of SURVEY.md 8.4 (full N x N Gram) / device time; the kernel exploits "
-                        "the symmetry of W (Z Z^T) and executes about half of them, so frac can exceed 1",
+                        "the symmetry of W (Z Z^T) and integrates the degree-(2p-2) top-face Gram with the order-(2p-2) rule, so it "
+                        "executes fewer flops and frac can exceed 1",
                 "executed_dmma": {"flops_per_tent_element": dmma_el, "achieved": dmma_tf, "peak": dmma.value,
                                   "unit": "TFLOP/s", "frac": dmma_tf / dmma.value if dmma.value else None}, "launches_per_step": launches / max(args.steps, 1),
                 "hbm": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s",

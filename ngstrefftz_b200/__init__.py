@@ -506,6 +506,41 @@ def brick_vertex_owner(mesh, grid):
     return i32(owner)
 
 
+def balanced_vertex_owner(tps, grid):
+    """Vertex owners for a cost-balanced brick partition: recursive coordinate bisection into grid[0] x grid[1] x ..
+    parts, each cut placed where the accumulated tent cost (tent-elements of the tents pitched at a vertex) splits evenly.
+    Vertices are ordered lexicographically (cut direction first), so a cut may run through a vertex layer -- with 2k+1
+    layers the plain brick cut leaves one side a whole layer heavier. rank = bx + gx * (by + gy * bz)."""
+    mesh = tps.mesh
+    pts = mesh.points
+    D = pts.shape[1]
+    e = tps.export()
+    cost = np.zeros(len(pts))
+    np.add.at(cost, e["vertex"], np.diff(e["el_off"]).astype(float))
+    cost += 1e-9
+    owner = np.zeros(len(pts), dtype=np.int64)
+
+    def split(idx, d, stride):
+        if d >= len(grid):
+            return
+        g = grid[d]
+        if d >= D:
+            if g != 1:
+                raise ValueError("partition grid has more directions than the mesh")
+            return split(idx, d + 1, stride)
+        keys = [pts[idx, (d + k) % D] for k in range(D)]
+        order = np.lexsort(keys[::-1])  # primary key: coordinate d
+        idx = idx[order]
+        cum = np.cumsum(cost[idx])
+        cuts = np.searchsorted(cum, cum[-1] * np.arange(1, g) / g, side="left")
+        for b, part in enumerate(np.split(idx, cuts)):
+            owner[part] += b * stride
+            split(part, d + 1, stride * g)
+
+    split(np.arange(len(pts)), 0, 1)
+    return i32(owner)
+
+
 def partition_plan(tps, owner, nranks, rank):
     """Host-only view of a rank's partition plan (ngst_partition_plan): dict of numpy arrays."""
     owner = i32(owner)

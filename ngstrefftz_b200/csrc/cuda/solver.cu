@@ -126,6 +126,20 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
     fargs_.fe = Upload(fstage_.fe);
     fargs_.ff = Upload(fstage_.ff);
     fargs_.sqrtw = Upload(fstage_.sqrtw);
+    {
+      // top-face Gram: rule of order 2p-2 (exact for the degree-(2p-2) integrand, tent_fast.cu Cfg::QT)
+      const SimplexRule rt = make_simplex_rule(D, 2 * order - 2);
+      std::vector<double> lt((size_t)rt.nip * d1), sw(rt.nip);
+      for (int q = 0; q < rt.nip; q++) {
+        double s = 0;
+        for (int d = 0; d < D; d++) { lt[(size_t)q * d1 + d] = rt.xi[(size_t)q * D + d]; s += rt.xi[(size_t)q * D + d]; }
+        lt[(size_t)q * d1 + D] = 1.0 - s;
+        sw[q] = std::sqrt(rt.w[q]);
+      }
+      fargs_.lam_top = Upload(lt);
+      fargs_.sqrtw_top = Upload(sw);
+      fargs_.Qt = rt.nip;
+    }
     fargs_.dmap = Upload(fstage_.dmap);
     fargs_.dfac = Upload(fstage_.dfac);
     for (int f = 0; f < 2; f++) {

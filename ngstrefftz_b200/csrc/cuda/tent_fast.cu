@@ -49,6 +49,9 @@ struct Cfg {
   static constexpr int NP = NT * 8;               // padded system size
   static constexpr int G = NP / 4;                // functions per evaluation group (function i -> group i % 4)
   static constexpr int Q = (D == 1) ? (P + 1) : ipow(P + 1, D);  // points of the order-2P rule (quadrature.cpp)
+  // The top-face Gram integrand (B L)(B L)^T is a polynomial of degree 2P-2 on the (affine) face: the rule of order
+  // 2P-2 (P points per direction) integrates it exactly, i.e. gives the order-2P rule's matrix up to round-off.
+  static constexpr int QT = (D == 1) ? P : ipow(P, D);
   static constexpr int ZS = kChunk * d1 + 4;      // row stride of Z: == 4 (mod 16) -> conflict-free fragment loads
   static constexpr int LDA = NP + 1;
   static constexpr int NSYM = NT * (NT + 1) / 2;  // upper-triangular tiles
@@ -174,7 +177,7 @@ __device__ __forceinline__ void eval_group(int w, const double* xi, F&& f) {
 template <int D, int P, int FO>
 __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a, FastArgs f) {
   using C = Cfg<D, P, FO>;
-  constexpr int d1 = C::d1, N = C::N, NT = C::NT, NP = C::NP, G = C::G, Q = C::Q, ZS = C::ZS, LDA = C::LDA;
+  constexpr int d1 = C::d1, N = C::N, NT = C::NT, NP = C::NP, G = C::G, Q = C::Q, QT = C::QT, ZS = C::ZS, LDA = C::LDA;
   constexpr int NACC = C::NACC, FE = C::FE, FF = C::FF, npoly = C::npoly, npm1 = C::npm1;
   extern __shared__ double sm[];
   double* const A = sm + C::oA;
@@ -190,6 +193,7 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
   const int te0 = a.te_off[tent], nel = a.te_off[tent + 1] - te0;
   const int tf0 = a.tf_off[tent], nfc = a.tf_off[tent + 1] - tf0;
   const int npts = nel * Q;
+  const int nptt = nel * QT;
 
   for (int i = tid; i < NP * ZS; i += kThreads) Z[i] = 0.0;  // rows of the padding functions stay zero
   double acc[NACC][2];
@@ -201,13 +205,13 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
   __syncthreads();
 
   // ------------------------------------------------------------------ top faces: A += B W B^T  (twavetents.cpp:270-313)
-  for (int c0 = 0; c0 < npts; c0 += kChunk) {
+  for (int c0 = 0; c0 < nptt; c0 += kChunk) {
     const int idx = c0 + lane;
-    const bool valid = idx < npts;
-    const int idc = valid ? idx : npts - 1;
-    const int te = te0 + idc / Q, q = idc % Q;
+    const bool valid = idx < nptt;
+    const int idc = valid ? idx : nptt - 1;
+    const int te = te0 + idc / QT, q = idc % QT;
     const double* __restrict__ rec = f.fe + (size_t)te * FE;
-    const double* __restrict__ lm = a.lam + q * d1;
+    const double* __restrict__ lm = f.lam_top + q * d1;
     double xi[d1];
 #pragma unroll
     for (int u = 0; u < d1; u++) xi[u] = 0.0;
@@ -218,7 +222,7 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
       for (int u = 0; u < D; u++) xi[u] = fma(l, rec[fast_fe_xv(D) + kk * D + u], xi[u]);
       xi[D] = fma(l, rec[fast_fe_tt(D) + kk], xi[D]);
     }
-    const double sq = valid ? f.sqrtw[q] : 0.0;
+    const double sq = valid ? f.sqrtw_top[q] : 0.0;
     const double k0 = sq * rec[fast_fe_top(D)];
     double kd[D];
 #pragma unroll
@@ -416,85 +420,128 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
   }
   __syncthreads();
   // ------------------------------------------------------------------ Solve (64-70 forms the inverse with LAPACK)
-  // LU on the N x N system, right-hand side carried as column N. Interior tents (no boundary face) have a symmetric
-  // positive definite matrix (Z Z^T + stabilisation): elimination in natural order needs no pivot search. Tents with
-  // boundary faces are unsymmetric: partial pivoting, implicit (rows are never swapped; every thread tracks the used rows
-  // in a bit mask, the search is done redundantly by every warp). One barrier per elimination step either way.
-  for (int i = tid; i < N; i += kThreads) A[i * LDA + N] = bv[i];
-  __shared__ int perm[64];
-  static_assert(N <= 64, "row mask is 64 bits wide");
-  __syncthreads();
+  // Gauss-Jordan elimination with the whole augmented system [A | b] held in REGISTERS: thread (ty, tx) of an 8 x 16
+  // grid owns the rows ty + 8 i and the columns tx + 16 j (NR x NCB doubles). Per step the owners publish the pivot row
+  // and the pivot column through (double-buffered) shared memory, then every thread updates its block with NR * NCB
+  // FMAs and no further memory traffic; eliminating above the diagonal as well costs nothing extra in this layout and
+  // removes the serial back substitution. Interior tents (no boundary face) have a symmetric positive definite matrix
+  // (Z Z^T + stabilisation): natural order, one barrier per step. Tents with boundary faces are unsymmetric: partial
+  // pivoting with an implicit row permutation (the search is done redundantly by every warp), two barriers per step.
   {
+    constexpr int NR = NT, NCB = (N + 1 + 15) / 16;
+    static_assert(N <= 64, "row mask is 64 bits wide");
+    __shared__ double prow[2][16 * NCB];
+    __shared__ double pcol[2][NP];
+    __shared__ double pinv_s[2];
+    __shared__ double pinv_row[NP];
+    __shared__ int rowstep[NP];
+    const int ty = tid >> 4, tx = tid & 15;
+    double Ar[NR][NCB];
+#pragma unroll
+    for (int i = 0; i < NR; i++)
+#pragma unroll
+      for (int j = 0; j < NCB; j++) {
+        const int r = ty + 8 * i, c = tx + 16 * j;
+        Ar[i][j] = (r < N && c < N) ? A[r * LDA + c] : ((r < N && c == N) ? bv[r] : 0.0);
+      }
     const bool spd = nfc == 0;
     unsigned long long done = 0ull;
-    for (int kk = 0; kk < N; kk++) {
-      int p = kk;
-      double piv;
-      if (spd) {
-        piv = A[kk * LDA + kk];
-      } else {
-        double best = -1.0;
-        int brow = 0x7fffffff;
-        for (int r = lane; r < N; r += 32) {
-          if ((done >> r) & 1ull) continue;
-          const double v = fabs(A[r * LDA + kk]);
-          if (v > best) { best = v; brow = r; }
+#pragma unroll
+    for (int i0 = 0; i0 < NR; i0++) {
+      constexpr int dummy = 0;
+      (void)dummy;
+      const int j0 = i0 >> 1;  // column block of the steps kk = 8 i0 + k8
+      for (int k8 = 0; k8 < 8; k8++) {
+        const int kk = 8 * i0 + k8;
+        if (kk >= N) break;
+        const int buf = kk & 1;
+        int p = kk;
+        if (spd) {
+          if (ty == k8) {
+#pragma unroll
+            for (int j = 0; j < NCB; j++) prow[buf][tx + 16 * j] = Ar[i0][j];
+            if (tx == (kk & 15)) {
+              const double piv = Ar[i0][j0];
+              const bool ok = piv > 0.0;
+              pinv_s[buf] = ok ? 1.0 / piv : 0.0;
+              pinv_row[kk] = ok ? 1.0 / piv : 0.0;
+              rowstep[kk] = kk;
+              if (!ok) atomicAdd(a.singular, 1);
+            }
+          }
+          if (tx == (kk & 15)) {
+#pragma unroll
+            for (int i = 0; i < NR; i++) pcol[buf][ty + 8 * i] = Ar[i][j0];
+          }
+          __syncthreads();
+        } else {
+          if (tx == (kk & 15)) {
+#pragma unroll
+            for (int i = 0; i < NR; i++) pcol[buf][ty + 8 * i] = Ar[i][j0];
+          }
+          __syncthreads();
+          double best = -1.0;
+          int brow = 0x7fffffff;
+          for (int r = lane; r < N; r += 32) {
+            if ((done >> r) & 1ull) continue;
+            const double v = fabs(pcol[buf][r]);
+            if (v > best) { best = v; brow = r; }
+          }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const int orow = __shfl_xor_sync(0xffffffffu, brow, o);
+            if (ob > best || (ob == best && orow < brow)) { best = ob; brow = orow; }
+          }
+          p = brow;
+          done |= 1ull << p;
+          if (ty == (p & 7)) {
+            const int ip = p >> 3;
+            double tmp[NCB];
+#pragma unroll
+            for (int j = 0; j < NCB; j++) tmp[j] = 0.0;
+#pragma unroll
+            for (int i = 0; i < NR; i++)
+              if (i == ip) {
+#pragma unroll
+                for (int j = 0; j < NCB; j++) tmp[j] = Ar[i][j];
+              }
+#pragma unroll
+            for (int j = 0; j < NCB; j++) prow[buf][tx + 16 * j] = tmp[j];
+            if (tx == (kk & 15)) {
+              const double piv = tmp[j0];
+              const bool ok = piv != 0.0;
+              pinv_s[buf] = ok ? 1.0 / piv : 0.0;
+              pinv_row[p] = ok ? 1.0 / piv : 0.0;
+              rowstep[p] = kk;
+              if (!ok) atomicAdd(a.singular, 1);
+            }
+          }
+          __syncthreads();
+        }
+        const double pinv = pinv_s[buf];
+        double m[NR], pr[NCB];
+#pragma unroll
+        for (int i = 0; i < NR; i++) {
+          const double v = pcol[buf][ty + 8 * i];
+          m[i] = (ty + 8 * i == p) ? 0.0 : -v * pinv;
         }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-          const double ob = __shfl_xor_sync(0xffffffffu, best, o);
-          const int orow = __shfl_xor_sync(0xffffffffu, brow, o);
-          if (ob > best || (ob == best && orow < brow)) { best = ob; brow = orow; }
-        }
-        p = brow;
-        piv = A[p * LDA + kk];
-      }
-      done |= 1ull << p;
-      const bool ok = spd ? (piv > 0.0) : (piv != 0.0);
-      const double pinv = ok ? 1.0 / piv : 0.0;
-      if (tid == 0) {
-        perm[kk] = p;
-        if (!ok) atomicAdd(a.singular, 1);
-      }
-      const int c0 = kk + 1 + lane, c1 = c0 + 32;  // columns kk+1 .. N (N = right-hand side)
-      const bool h0 = c0 <= N, h1 = c1 <= N;
-      const double pr0 = h0 ? A[p * LDA + c0] : 0.0;
-      const double pr1 = h1 ? A[p * LDA + c1] : 0.0;
-      // rows r = w, w+4, ..: four at a time, loads first
-      for (int r0 = w; r0 < N; r0 += 16) {
-        double m[4], x0[4], x1[4];
-        bool act[4];
+        for (int j = 0; j < NCB; j++) pr[j] = prow[buf][tx + 16 * j];
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
-          const int r = r0 + 4 * u;
-          act[u] = r < N && !((done >> r) & 1ull);
-          m[u] = act[u] ? A[r * LDA + kk] : 0.0;
-          x0[u] = (act[u] && h0) ? A[r * LDA + c0] : 0.0;
-          x1[u] = (act[u] && h1) ? A[r * LDA + c1] : 0.0;
-        }
+        for (int i = 0; i < NR; i++)
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
-          const int r = r0 + 4 * u;
-          const double mm = m[u] * pinv;
-          if (act[u] && h0) A[r * LDA + c0] = x0[u] - mm * pr0;
-          if (act[u] && h1) A[r * LDA + c1] = x1[u] - mm * pr1;
-        }
+          for (int j = 0; j < NCB; j++) Ar[i][j] = fma(m[i], pr[j], Ar[i][j]);
       }
-      __syncthreads();
     }
-  }
-  // back substitution by warp 0: lane l carries the right-hand sides of rows l and l + 32
-  if (w == 0) {
-    double r0 = (lane < N) ? A[lane * LDA + N] : 0.0;
-    double r1 = (lane + 32 < N) ? A[(lane + 32) * LDA + N] : 0.0;
-    for (int kk = N - 1; kk >= 0; kk--) {
-      const int p = perm[kk];
-      const double d = A[p * LDA + kk];
-      const double rp = __shfl_sync(0xffffffffu, (p < 32) ? r0 : r1, p & 31);
-      const double xk = (d != 0.0) ? rp / d : 0.0;
-      if (lane == 0) bv[kk] = xk;
-      if (lane < N) r0 -= A[lane * LDA + kk] * xk;
-      if (lane + 32 < N) r1 -= A[(lane + 32) * LDA + kk] * xk;
+    __syncthreads();
+    // row r was the pivot row of step rowstep[r]: x[rowstep[r]] = [A | b][r][N] / pivot
+    if (tx == (N & 15)) {
+#pragma unroll
+      for (int i = 0; i < NR; i++) {
+        const int r = ty + 8 * i;
+        if (r < N) bv[rowstep[r]] = Ar[i][N >> 4] * pinv_row[r];
+      }
     }
   }
   __syncthreads();
@@ -567,7 +614,7 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
 template <int D, int P, int FO>
 cudaError_t launch_cfg(const TentKernelArgs& a, const FastArgs& f, cudaStream_t stream) {
   using C = Cfg<D, P, FO>;
-  if (a.Q != C::Q || a.N != C::N || a.npoly != C::npoly) return cudaErrorInvalidValue;
+  if (a.Q != C::Q || f.Qt != C::QT || a.N != C::N || a.npoly != C::npoly) return cudaErrorInvalidValue;
   const size_t smem = sizeof(double) * C::nsmem;
   static bool configured = false;  // per instantiation
   if (!configured) {

@@ -35,6 +35,10 @@ struct FastArgs {
   const double* fe;     // nte * fast_fe_stride(D)
   const double* ff;     // ntf * fast_ff_stride(D)
   const double* sqrtw;  // Q: sqrt of the rule weights
+  // rule of order 2p-2 for the top-face Gram (exact for its degree-(2p-2) integrand)
+  const double* lam_top;    // Qt * (D+1) barycentric coordinates
+  const double* sqrtw_top;  // Qt
+  int Qt;
   // column-compressed basis matrix (monomial j -> functions), for sol -> monomial coefficients
   const int* cptr;      // npoly + 1
   const int* crow;      // nnz
