@@ -45,6 +45,9 @@ def parse():
     ap.add_argument("--cpu-sample-tents", type=int, default=0, help="tents in the bounded CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--partition", default="balanced", choices=["balanced", "brick"],
+                    help="N>1: cost-balanced recursive bisection (default) or plain brick cut of the bounding box")
+    ap.add_argument("--no-overlap", action="store_true", help="N>1: exchange after each level instead of overlapped")
     return ap.parse_args()
 
 
@@ -223,7 +226,10 @@ def run_ours(args):
     assert ts.PitchTents(args.dt, True, 2 / 3)
     pitch_s = time.perf_counter() - t0
     if world > 1:
-        tw = ng.TWave(order, ts, 1.0, device=local, partition=(rank, world, grid))
+        owner = ng.balanced_vertex_owner(ts, grid) if args.partition == "balanced" else ng.brick_vertex_owner(mesh, grid)
+        tw = ng.TWave(order, ts, 1.0, device=local, partition=(rank, world, owner))
+        if args.no_overlap:
+            tw.set_kernel_mode(2)
     else:
         tw = ng.TWave(order, ts, 1.0, device=local)
     e = ts.export()
@@ -382,7 +388,8 @@ def run_ours(args):
                                f"c=1, standing wave, Dirichlet, dt={args.dt}, edge pitching local_ct global_ct=2/3",
                    "tets": int(np.prod(cells) * 6), "order": order, "nbasis": N, "nip": Q,
                    "slab_tents": int(ntents_global), "levels": ts.GetNLayers(), "tent_elements": int(sm[7]),
-                   "parallelism": f"spatial partition {grid[0]}x{grid[1]}x{grid[2]}" if world > 1 else "single GPU",
+                   "parallelism": (f"spatial partition {grid[0]}x{grid[1]}x{grid[2]} ({args.partition} vertex ownership), per-level halo exchange "
+                                   f"{'after' if args.no_overlap else 'overlapped with'} the interior tents") if world > 1 else "single GPU",
                    "l2": f"state {wf0.nbytes * world / 1e6:.0f} MB per slab > 126 MB L2 (no flush needed)",
                    "pitch_s": pitch_s},
         "wall_ms_per_step": 1e3 * wall_s / args.steps,

@@ -140,7 +140,9 @@ int ngst_twave_set_timeshift(ngst_twave* t, double timeshift);
 const char* ngst_twave_kernel_name(const ngst_twave* t);
 /* Kernel routing (diagnostics; no reference counterpart): mode 0 = automatic (single-wavespeed tents on the DMMA
  * kernel tent_kernel_fast, tents with material interfaces on tent_kernel_generic), 1 = every tent on the generic
- * DFMA kernel. ngst_twave_ntents_fast: tents of the slab routed to the fast kernel in mode 0. */
+ * DFMA kernel, 2 = as 0 but, on several GPUs, the halo exchange of a level runs after all tents of the level instead
+ * of overlapping the interior tents (A/B measurements; results are bitwise identical in every mode 0/2).
+ * ngst_twave_ntents_fast: tents of the slab routed to the fast kernel in mode 0. */
 int ngst_twave_set_kernel_mode(ngst_twave* t, int mode);
 int ngst_twave_ntents_fast(const ngst_twave* t);
 /* device time of the last Propagate in ms (CUDA events on the solver's stream) and kernel launches in it */

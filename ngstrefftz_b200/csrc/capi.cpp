@@ -354,7 +354,7 @@ const char* ngst_twave_kernel_name(const ngst_twave* t) { return t ? t->solver->
 int ngst_twave_set_kernel_mode(ngst_twave* t, int mode) {
   return guarded([&] {
     need(t, "solver");
-    if (mode < 0 || mode > 1) throw std::invalid_argument("ngst_twave_set_kernel_mode: mode must be 0 or 1");
+    if (mode < 0 || mode > 2) throw std::invalid_argument("ngst_twave_set_kernel_mode: mode must be 0, 1 or 2");
     t->solver->set_kernel_mode(mode);
   });
 }

@@ -153,17 +153,46 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
     std::vector<int> gen, fast;
     gen_off_.assign(1, 0);
     fast_off_.assign(1, 0);
+    fast_nhalo_.assign(nlev, 0);
+    gen_nhalo_.assign(nlev, 0);
+    std::vector<char> sent(nel_, 0);
     for (int l = 0; l < nlev; l++) {
-      const size_t f0 = fast.size();
+      const size_t f0 = fast.size(), g0 = gen.size();
+      // halo tents (multi-GPU): the tents of this level that write a row another rank holds. They run first, on their own
+      // stream, so that the exchange of the level overlaps the interior tents (Propagate()).
+      int s0 = 0, s1 = 0;
+      if (plan_ && plan_->nranks > 1) {
+        s0 = plan_->send_off[(size_t)l * plan_->nranks];
+        s1 = plan_->send_off[(size_t)(l + 1) * plan_->nranks];
+        for (int i = s0; i < s1; i++) sent[plan_->send_el[i]] = 1;
+      }
+      auto is_halo = [&](int t) {
+        if (s1 == s0) return false;
+        for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++)
+          if (sent[plan_->glob2loc[staged_.te_el[te]]]) return true;
+        return false;
+      };
+      std::vector<int> fh, fi, gh, gi;
       for (int i = slab_.level_off[l]; i < slab_.level_off[l + 1]; i++) {
         const int t = slab_.level_tents[i];
-        if (fast_ && fstage_.ok[t]) fast.push_back(t);
-        else gen.push_back(t);
+        const bool h = is_halo(t);
+        if (fast_ && fstage_.ok[t]) (h ? fh : fi).push_back(t);
+        else (h ? gh : gi).push_back(t);
       }
+      for (int i = s0; i < s1; i++) sent[plan_->send_el[i]] = 0;
       // most expensive tents first (the order inside a level is free: tents of a level share no element)
-      std::stable_sort(fast.begin() + f0, fast.end(), [&](int x, int y) {
+      auto by_cost = [&](int x, int y) {
         return staged_.te_off[x + 1] - staged_.te_off[x] > staged_.te_off[y + 1] - staged_.te_off[y];
-      });
+      };
+      std::stable_sort(fh.begin(), fh.end(), by_cost);
+      std::stable_sort(fi.begin(), fi.end(), by_cost);
+      fast.insert(fast.end(), fh.begin(), fh.end());
+      fast.insert(fast.end(), fi.begin(), fi.end());
+      gen.insert(gen.end(), gh.begin(), gh.end());
+      gen.insert(gen.end(), gi.begin(), gi.end());
+      fast_nhalo_[l] = (int)fh.size();
+      gen_nhalo_[l] = (int)gh.size();
+      (void)f0; (void)g0;
       gen_off_.push_back((int)gen.size());
       fast_off_.push_back((int)fast.size());
     }
@@ -252,6 +281,7 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
 
 Solver::~Solver() {
   cudaSetDevice(device_);
+  if (stream_halo_) cudaStreamSynchronize(stream_halo_);
   if (stream_) cudaStreamSynchronize(stream_);
   for (void* p : allocs_) cudaFree(p);
   if (d_wavefront_) cudaFree(d_wavefront_);
@@ -263,6 +293,9 @@ Solver::~Solver() {
   comm_.reset();
   if (ev0_) cudaEventDestroy(ev0_);
   if (ev1_) cudaEventDestroy(ev1_);
+  if (ev_halo_) cudaEventDestroy(ev_halo_);
+  if (ev_int_) cudaEventDestroy(ev_int_);
+  if (stream_halo_) cudaStreamDestroy(stream_halo_);
   if (stream_) cudaStreamDestroy(stream_);
 }
 
@@ -400,7 +433,7 @@ void Solver::Propagate() {
       CU(launch_tent_qt(mesh_.D, a, qargs_, smem_, stream_));
       launches++;
     }
-    if (comm_) launches += ExchangeLevel(l);
+    if (comm_) launches += ExchangeLevel(l, stream_);
   }
   for (int l = 0; l < nlev && force_generic_ && !qt_; l++) {
     TentKernelArgs a = args_;
@@ -410,24 +443,53 @@ void Solver::Propagate() {
       CU(launch_tent_generic(mesh_.D, a, threads_, smem_, stream_));
       launches++;
     }
-    if (comm_) launches += ExchangeLevel(l);
+    if (comm_) launches += ExchangeLevel(l, stream_);
   }
+  const bool overlap = comm_ && !force_generic_ && !qt_ && overlap_;
+  if (overlap && !stream_halo_) {
+    int lo = 0, hi = 0;
+    CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CU(cudaStreamCreateWithPriority(&stream_halo_, cudaStreamNonBlocking, hi));
+    CU(cudaEventCreateWithFlags(&ev_halo_, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&ev_int_, cudaEventDisableTiming));
+  }
+  if (overlap) CU(cudaEventRecord(ev_int_, stream_));
   for (int l = 0; l < nlev && !force_generic_ && !qt_; l++) {
+    // level l: [halo tents | interior tents] of the fast and of the generic list. Single GPU: one launch per list.
+    // Multi-GPU: halo tents + exchange on the high-priority stream, interior tents concurrently on the main stream;
+    // level l+1 starts when both are done (tents of a level touch disjoint rows, received rows belong to no local tent
+    // of the level).
+    const int fh = overlap ? fast_nhalo_[l] : 0, gh = overlap ? gen_nhalo_[l] : 0;
+    if (overlap) {
+      CU(cudaStreamWaitEvent(stream_halo_, ev_int_, 0));
+      if (l > 0) CU(cudaStreamWaitEvent(stream_, ev_halo_, 0));
+      TentKernelArgs h = args_;
+      h.tents = d_level_fast_ + fast_off_[l];
+      h.ntents = fh;
+      if (h.ntents > 0) { CU(launch_tent_fast(mesh_.D, order_, fosystem_, h, fargs_, stream_halo_)); launches++; }
+      h.tents = d_level_tents_ + gen_off_[l];
+      h.ntents = gh;
+      if (h.ntents > 0) { CU(launch_tent_generic(mesh_.D, h, threads_, smem_, stream_halo_)); launches++; }
+      launches += ExchangeLevel(l, stream_halo_);
+      CU(cudaEventRecord(ev_halo_, stream_halo_));
+    }
     TentKernelArgs a = args_;
-    a.tents = d_level_fast_ + fast_off_[l];
-    a.ntents = fast_off_[l + 1] - fast_off_[l];
+    a.tents = d_level_fast_ + fast_off_[l] + fh;
+    a.ntents = fast_off_[l + 1] - fast_off_[l] - fh;
     if (a.ntents > 0) {
       CU(launch_tent_fast(mesh_.D, order_, fosystem_, a, fargs_, stream_));
       launches++;
     }
-    a.tents = d_level_tents_ + gen_off_[l];
-    a.ntents = gen_off_[l + 1] - gen_off_[l];
+    a.tents = d_level_tents_ + gen_off_[l] + gh;
+    a.ntents = gen_off_[l + 1] - gen_off_[l] - gh;
     if (a.ntents > 0) {
       CU(launch_tent_generic(mesh_.D, a, threads_, smem_, stream_));
       launches++;
     }
-    if (comm_) launches += ExchangeLevel(l);
+    if (overlap) CU(cudaEventRecord(ev_int_, stream_));
+    else if (comm_) launches += ExchangeLevel(l, stream_);
   }
+  if (overlap) CU(cudaStreamWaitEvent(stream_, ev_halo_, 0));
   CU(cudaEventRecord(ev1_, stream_));
   CU(cudaEventSynchronize(ev1_));
   float ms = 0;
@@ -444,7 +506,7 @@ void Solver::Propagate() {
 }
 
 // rows updated in level l that other ranks hold -> peers; rows peers updated that this rank holds <- peers
-int Solver::ExchangeLevel(int l) {
+int Solver::ExchangeLevel(int l, cudaStream_t stream) {
   const PartitionPlan& p = *plan_;
   const int nr = p.nranks, rowlen = ncomp_ * rule_.nip;
   std::vector<int> sc(nr), rc(nr);
@@ -465,7 +527,7 @@ int Solver::ExchangeLevel(int l) {
     halo_bytes_ = need;
   }
   comm_->Exchange(d_wavefront_, rowlen, d_send_el_ + p.send_off[(size_t)l * nr], sc.data(),
-                  d_recv_el_ + p.recv_off[(size_t)l * nr], rc.data(), d_sendbuf_, d_recvbuf_, stream_);
+                  d_recv_el_ + p.recv_off[(size_t)l * nr], rc.data(), d_sendbuf_, d_recvbuf_, stream);
   return (ns > 0) + (nrv > 0);
 }
 

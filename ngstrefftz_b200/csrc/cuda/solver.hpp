@@ -70,7 +70,8 @@ class Solver {
   const char* kernel_name() const { return qt_ ? "tent_kernel_qt" : ((fast_ && !force_generic_) ? "tent_kernel_fast" : "tent_kernel_generic"); }
   int ntents_fast() const { return fast_ ? fast_off_.back() : 0; }
   // 0 = automatic routing (fast kernel where possible), 1 = every tent on the generic DFMA kernel (A/B evidence)
-  void set_kernel_mode(int mode) { force_generic_ = mode == 1; }
+  // 0: fast kernel where available (default), 1: generic kernel everywhere, 2: fast kernel, multi-GPU exchange not overlapped
+  void set_kernel_mode(int mode) { force_generic_ = mode == 1; overlap_ = mode != 2; }
   double last_ms() const { return last_ms_; }
   int last_launches() const { return last_launches_; }
 
@@ -79,7 +80,7 @@ class Solver {
   template <typename T>
   T* Upload(const std::vector<T>& v);
   double ReduceElements(const double* d_a, const double* d_b, int mode);
-  int ExchangeLevel(int level);
+  int ExchangeLevel(int level, cudaStream_t stream);
   size_t halo_bytes_ = 0;
 
   const SimplexMesh& mesh_;
@@ -105,6 +106,11 @@ class Solver {
 
   cudaStream_t stream_ = nullptr;
   cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
+  // multi-GPU overlap: halo tents + exchange of a level run on a high-priority stream beside the interior tents
+  cudaStream_t stream_halo_ = nullptr;
+  cudaEvent_t ev_halo_ = nullptr, ev_int_ = nullptr;
+  bool overlap_ = true;
+  std::vector<int> fast_nhalo_, gen_nhalo_;  // per level: leading halo tents of the fast / generic list
   std::vector<void*> allocs_;
   TentKernelArgs args_{};
   int* d_level_tents_ = nullptr;   // per level: generic-kernel tents (material interfaces or no fast variant)

@@ -19,6 +19,8 @@
 #include <cuda_runtime.h>
 
 #include "basis_eval_gen.cuh"
+#include "dmma_tiles.cuh"
+#include "tent_solve.cuh"
 #include "tent_fast.cuh"
 #include "tent_kernel.cuh"
 
@@ -26,18 +28,7 @@ namespace ngst {
 
 namespace {
 
-constexpr int kChunk = 32;   // quadrature points per chunk (one per lane)
-constexpr int kThreads = 128;
-constexpr int kBS = 36;      // row stride of the boundary-pass operands (== 4 mod 16)
-
-__device__ __forceinline__ void dmma_m8n8k4(double& c0, double& c1, double a, double b) {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
-               : "+d"(c0), "+d"(c1)
-               : "d"(a), "d"(b));
-}
-
-constexpr int ipow(int b, int e) { return e == 0 ? 1 : b * ipow(b, e - 1); }
-constexpr int cbinom(int n, int k) { return (k < 0 || k > n) ? 0 : (k == 0 ? 1 : cbinom(n - 1, k - 1) * n / k); }
+using namespace tiles;
 
 template <int D, int P, int FO>
 struct Cfg {
@@ -71,97 +62,6 @@ struct Cfg {
   static_assert(2 * kBS <= ZS, "boundary operands must fit in the Z buffer");
   static_assert(NT >= 2 && (NT * NT + 3) / 4 <= NACC, "accumulator budget");
 };
-
-// Symmetric rank-k update of this warp's upper-triangular tiles from the operand rows Z[function][k-row]:
-// tile L (row-major over ti <= tj) belongs to tile half L & 1; k-steps ks = kh, kh+2, .. < nks.
-template <int NT, int NACC, int TH>
-__device__ __forceinline__ void mma_sym_step(double (&acc)[NACC][2], const double (&fr)[NT]) {
-  int L = 0;
-#pragma unroll
-  for (int ti = 0; ti < NT; ti++)
-#pragma unroll
-    for (int tj = ti; tj < NT; tj++) {
-      if ((L & 1) == TH) dmma_m8n8k4(acc[L >> 1][0], acc[L >> 1][1], fr[ti], fr[tj]);
-      L++;
-    }
-}
-
-// nks / 2 (the k-steps of one warp) must be even: fragments are double-buffered so that the shared-memory loads of
-// the next k-step are in flight while the DMMAs of the current one issue.
-template <int NT, int NACC, int TH>
-__device__ __forceinline__ void dmma_sym(double (&acc)[NACC][2], const double* __restrict__ Z, int ZS, int nks, int kh,
-                                         int g, int k) {
-  const double* __restrict__ zp = Z + g * ZS + k + 4 * kh;
-  double fa[NT], fb[NT];
-#pragma unroll
-  for (int t = 0; t < NT; t++) fa[t] = zp[8 * t * ZS];
-  for (int ks = kh; ks < nks; ks += 4) {
-#pragma unroll
-    for (int t = 0; t < NT; t++) fb[t] = zp[8 * t * ZS + 8];
-    mma_sym_step<NT, NACC, TH>(acc, fa);
-    zp += 16;
-    if (ks + 4 < nks) {
-#pragma unroll
-      for (int t = 0; t < NT; t++) fa[t] = zp[8 * t * ZS];
-    }
-    mma_sym_step<NT, NACC, TH>(acc, fb);
-  }
-}
-
-// acc -> A (upper-triangular tiles of this warp's half); add = false stores, true accumulates.
-template <int NT, int NACC, int TH>
-__device__ __forceinline__ void flush_sym(const double (&acc)[NACC][2], double* A, int LDA, bool add, int g, int k) {
-  int L = 0;
-#pragma unroll
-  for (int ti = 0; ti < NT; ti++)
-#pragma unroll
-    for (int tj = ti; tj < NT; tj++) {
-      if ((L & 1) == TH) {
-        double* p = A + (8 * ti + g) * LDA + 8 * tj + 2 * k;
-        if (add) { p[0] += acc[L >> 1][0]; p[1] += acc[L >> 1][1]; }
-        else { p[0] = acc[L >> 1][0]; p[1] = acc[L >> 1][1]; }
-      }
-      L++;
-    }
-}
-
-// General (non-symmetric) update A += ZL ZR^T over 8 k-steps; tile L = ti*NT + tj belongs to warp L & 3 (= W).
-template <int NT, int NACC, int W>
-__device__ __forceinline__ void dmma_full(double (&acc)[NACC][2], const double* __restrict__ ZL,
-                                          const double* __restrict__ ZR, int g, int k) {
-  for (int ks = 0; ks < kChunk / 4; ks++) {
-    double fl[NT], fr[NT];
-#pragma unroll
-    for (int t = 0; t < NT; t++) {
-      fl[t] = ZL[(8 * t + g) * kBS + 4 * ks + k];
-      fr[t] = ZR[(8 * t + g) * kBS + 4 * ks + k];
-    }
-    int L = 0;
-#pragma unroll
-    for (int ti = 0; ti < NT; ti++)
-#pragma unroll
-      for (int tj = 0; tj < NT; tj++) {
-        if ((L & 3) == W) dmma_m8n8k4(acc[L >> 2][0], acc[L >> 2][1], fl[ti], fr[tj]);
-        L++;
-      }
-  }
-}
-
-template <int NT, int NACC, int W>
-__device__ __forceinline__ void flush_full(const double (&acc)[NACC][2], double* A, int LDA, int g, int k) {
-  int L = 0;
-#pragma unroll
-  for (int ti = 0; ti < NT; ti++)
-#pragma unroll
-    for (int tj = 0; tj < NT; tj++) {
-      if ((L & 3) == W) {
-        double* p = A + (8 * ti + g) * LDA + 8 * tj + 2 * k;
-        p[0] += acc[L >> 2][0];
-        p[1] += acc[L >> 2][1];
-      }
-      L++;
-    }
-}
 
 // group dispatch: warp w evaluates the functions i with i % 4 == w
 template <int D, int P, int FO, class F>
@@ -420,130 +320,8 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
   }
   __syncthreads();
   // ------------------------------------------------------------------ Solve (64-70 forms the inverse with LAPACK)
-  // Gauss-Jordan elimination with the whole augmented system [A | b] held in REGISTERS: thread (ty, tx) of an 8 x 16
-  // grid owns the rows ty + 8 i and the columns tx + 16 j (NR x NCB doubles). Per step the owners publish the pivot row
-  // and the pivot column through (double-buffered) shared memory, then every thread updates its block with NR * NCB
-  // FMAs and no further memory traffic; eliminating above the diagonal as well costs nothing extra in this layout and
-  // removes the serial back substitution. Interior tents (no boundary face) have a symmetric positive definite matrix
-  // (Z Z^T + stabilisation): natural order, one barrier per step. Tents with boundary faces are unsymmetric: partial
-  // pivoting with an implicit row permutation (the search is done redundantly by every warp), two barriers per step.
-  {
-    constexpr int NR = NT, NCB = (N + 1 + 15) / 16;
-    static_assert(N <= 64, "row mask is 64 bits wide");
-    __shared__ double prow[2][16 * NCB];
-    __shared__ double pcol[2][NP];
-    __shared__ double pinv_s[2];
-    __shared__ double pinv_row[NP];
-    __shared__ int rowstep[NP];
-    const int ty = tid >> 4, tx = tid & 15;
-    double Ar[NR][NCB];
-#pragma unroll
-    for (int i = 0; i < NR; i++)
-#pragma unroll
-      for (int j = 0; j < NCB; j++) {
-        const int r = ty + 8 * i, c = tx + 16 * j;
-        Ar[i][j] = (r < N && c < N) ? A[r * LDA + c] : ((r < N && c == N) ? bv[r] : 0.0);
-      }
-    const bool spd = nfc == 0;
-    unsigned long long done = 0ull;
-#pragma unroll
-    for (int i0 = 0; i0 < NR; i0++) {
-      constexpr int dummy = 0;
-      (void)dummy;
-      const int j0 = i0 >> 1;  // column block of the steps kk = 8 i0 + k8
-      for (int k8 = 0; k8 < 8; k8++) {
-        const int kk = 8 * i0 + k8;
-        if (kk >= N) break;
-        const int buf = kk & 1;
-        int p = kk;
-        if (spd) {
-          if (ty == k8) {
-#pragma unroll
-            for (int j = 0; j < NCB; j++) prow[buf][tx + 16 * j] = Ar[i0][j];
-            if (tx == (kk & 15)) {
-              const double piv = Ar[i0][j0];
-              const bool ok = piv > 0.0;
-              pinv_s[buf] = ok ? 1.0 / piv : 0.0;
-              pinv_row[kk] = ok ? 1.0 / piv : 0.0;
-              rowstep[kk] = kk;
-              if (!ok) atomicAdd(a.singular, 1);
-            }
-          }
-          if (tx == (kk & 15)) {
-#pragma unroll
-            for (int i = 0; i < NR; i++) pcol[buf][ty + 8 * i] = Ar[i][j0];
-          }
-          __syncthreads();
-        } else {
-          if (tx == (kk & 15)) {
-#pragma unroll
-            for (int i = 0; i < NR; i++) pcol[buf][ty + 8 * i] = Ar[i][j0];
-          }
-          __syncthreads();
-          double best = -1.0;
-          int brow = 0x7fffffff;
-          for (int r = lane; r < N; r += 32) {
-            if ((done >> r) & 1ull) continue;
-            const double v = fabs(pcol[buf][r]);
-            if (v > best) { best = v; brow = r; }
-          }
-#pragma unroll
-          for (int o = 16; o > 0; o >>= 1) {
-            const double ob = __shfl_xor_sync(0xffffffffu, best, o);
-            const int orow = __shfl_xor_sync(0xffffffffu, brow, o);
-            if (ob > best || (ob == best && orow < brow)) { best = ob; brow = orow; }
-          }
-          p = brow;
-          done |= 1ull << p;
-          if (ty == (p & 7)) {
-            const int ip = p >> 3;
-            double tmp[NCB];
-#pragma unroll
-            for (int j = 0; j < NCB; j++) tmp[j] = 0.0;
-#pragma unroll
-            for (int i = 0; i < NR; i++)
-              if (i == ip) {
-#pragma unroll
-                for (int j = 0; j < NCB; j++) tmp[j] = Ar[i][j];
-              }
-#pragma unroll
-            for (int j = 0; j < NCB; j++) prow[buf][tx + 16 * j] = tmp[j];
-            if (tx == (kk & 15)) {
-              const double piv = tmp[j0];
-              const bool ok = piv != 0.0;
-              pinv_s[buf] = ok ? 1.0 / piv : 0.0;
-              pinv_row[p] = ok ? 1.0 / piv : 0.0;
-              rowstep[p] = kk;
-              if (!ok) atomicAdd(a.singular, 1);
-            }
-          }
-          __syncthreads();
-        }
-        const double pinv = pinv_s[buf];
-        double m[NR], pr[NCB];
-#pragma unroll
-        for (int i = 0; i < NR; i++) {
-          const double v = pcol[buf][ty + 8 * i];
-          m[i] = (ty + 8 * i == p) ? 0.0 : -v * pinv;
-        }
-#pragma unroll
-        for (int j = 0; j < NCB; j++) pr[j] = prow[buf][tx + 16 * j];
-#pragma unroll
-        for (int i = 0; i < NR; i++)
-#pragma unroll
-          for (int j = 0; j < NCB; j++) Ar[i][j] = fma(m[i], pr[j], Ar[i][j]);
-      }
-    }
-    __syncthreads();
-    // row r was the pivot row of step rowstep[r]: x[rowstep[r]] = [A | b][r][N] / pivot
-    if (tx == (N & 15)) {
-#pragma unroll
-      for (int i = 0; i < NR; i++) {
-        const int r = ty + 8 * i;
-        if (r < N) bv[rowstep[r]] = Ar[i][N >> 4] * pinv_row[r];
-      }
-    }
-  }
+  // Interior tents (no boundary face) have a symmetric positive definite matrix (Z Z^T + stabilisation): no pivoting.
+  gauss_jordan_solve<N, NP, kThreads>(A, LDA, bv, nfc == 0, a.singular);
   __syncthreads();
 
   // ------------------------------------------------------------------ CalcTentElEval (541-590) in the monomial basis

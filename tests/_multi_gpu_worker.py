@@ -33,7 +33,12 @@ def main():
     ts = ng.TentSlab(mesh, "edge")
     ts.SetMaxWavespeed(1.0)
     assert ts.PitchTents(dt, True, 2 / 3)
-    tw = ng.TWave(order, ts, 1.0, device=local, partition=(rank, world, grids[world]))
+    # argv[3]: "brick" (default) or "balanced" vertex ownership; argv[4]: kernel mode (2 = exchange not overlapped)
+    how = sys.argv[3] if len(sys.argv) > 3 else "brick"
+    owner = ng.balanced_vertex_owner(ts, grids[world]) if how == "balanced" else grids[world]
+    tw = ng.TWave(order, ts, 1.0, device=local, partition=(rank, world, owner))
+    if len(sys.argv) > 4:
+        tw.set_kernel_mode(int(sys.argv[4]))
     tw.SetInitial(f)
     tw.SetBoundaryCF(dirichlet(f, D))
     e0 = tw.Energy()

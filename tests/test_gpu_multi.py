@@ -30,8 +30,10 @@ def _free_port():
     return p
 
 
-@pytest.mark.parametrize("case,world", [("cube_p4", 2), ("square_p4", 2), ("cube_p3", 2), ("cube_p4", 4), ("cube_p3", 8)])
-def test_partitioned_matches_single_gpu(built, case, world):
+@pytest.mark.parametrize("case,world,how", [("cube_p4", 2, "brick"), ("square_p4", 2, "brick"), ("cube_p3", 2, "balanced"),
+                                            ("cube_p4", 2, "balanced"), ("cube_p4", 2, "brick-nooverlap"),
+                                            ("cube_p4", 4, "balanced"), ("cube_p3", 8, "brick"), ("cube_p4", 8, "balanced")])
+def test_partitioned_matches_single_gpu(built, case, world, how):
     if ngpus() < world:
         pytest.skip(f"needs {world} GPUs")
     sys.path.insert(0, HERE)
@@ -39,7 +41,8 @@ def test_partitioned_matches_single_gpu(built, case, world):
     mk, grids, order, dt, nslabs = CASES[case]
     with tempfile.TemporaryDirectory() as out:
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr",
-               "127.0.0.1", "--master-port", str(_free_port()), os.path.join(HERE, "_multi_gpu_worker.py"), case, out]
+               "127.0.0.1", "--master-port", str(_free_port()), os.path.join(HERE, "_multi_gpu_worker.py"), case, out] + \
+              (["brick", "2"] if how == "brick-nooverlap" else [how])
         r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
         assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
         ranks = [np.load(os.path.join(out, f"rank{k}.npz")) for k in range(world)]

@@ -23,11 +23,12 @@ def pitched(mesh, dt=0.15):
 @pytest.mark.parametrize("mk,grid", [(lambda: ng.UnitCubeMesh(4), (2, 1, 1)), (lambda: ng.UnitCubeMesh(4), (2, 2, 1)),
                                      (lambda: ng.UnitSquareMesh(6), (2, 2)), (lambda: ng.SegMesh(16, 0, 1), (4,)),
                                      (lambda: ng.StructuredMesh([4, 2, 2], [0, 0, 0], [2, 1, 1]), (2, 2, 2))])
-def test_plan_is_consistent(built, mk, grid):
+@pytest.mark.parametrize("how", ["brick", "balanced"])
+def test_plan_is_consistent(built, mk, grid, how):
     mesh = mk()
     ts = pitched(mesh)
     nranks = int(np.prod(grid))
-    owner = ng.brick_vertex_owner(mesh, grid)
+    owner = ng.brick_vertex_owner(mesh, grid) if how == "brick" else ng.balanced_vertex_owner(ts, grid)
     assert set(owner) == set(range(nranks))
     e = ts.export()
     el2v = mesh.elements
@@ -59,6 +60,22 @@ def test_plan_is_consistent(built, mk, grid):
                 assert np.array_equal(s, v)
                 if r == q:
                     assert len(s) == 0
+
+
+def test_balanced_owner_balances_cost(built):
+    """An even number of cells per direction has an odd number of vertex layers: the brick cut leaves the upper bricks a
+    whole layer heavier, the cost-balanced bisection cuts through the middle layer."""
+    mesh = ng.UnitCubeMesh(8)
+    ts = pitched(mesh, 0.1)
+    e = ts.export()
+    cost = np.zeros(mesh.nv)
+    np.add.at(cost, e["vertex"], np.diff(e["el_off"]).astype(float))
+
+    def imbalance(owner):
+        w = np.array([cost[owner == r].sum() for r in range(8)])
+        return w.max() / w.mean()
+
+    assert imbalance(ng.balanced_vertex_owner(ts, (2, 2, 2))) < 1.03 < imbalance(ng.brick_vertex_owner(mesh, (2, 2, 2)))
 
 
 def test_plan_argument_errors(built):
