@@ -148,58 +148,6 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
       d_cval_[f] = Upload(fstage_.cval[f]);
     }
   }
-  {
-    const int nlev = (int)slab_.level_off.size() - 1;
-    std::vector<int> gen, fast;
-    gen_off_.assign(1, 0);
-    fast_off_.assign(1, 0);
-    fast_nhalo_.assign(nlev, 0);
-    gen_nhalo_.assign(nlev, 0);
-    std::vector<char> sent(nel_, 0);
-    for (int l = 0; l < nlev; l++) {
-      const size_t f0 = fast.size(), g0 = gen.size();
-      // halo tents (multi-GPU): the tents of this level that write a row another rank holds. They run first, on their own
-      // stream, so that the exchange of the level overlaps the interior tents (Propagate()).
-      int s0 = 0, s1 = 0;
-      if (plan_ && plan_->nranks > 1) {
-        s0 = plan_->send_off[(size_t)l * plan_->nranks];
-        s1 = plan_->send_off[(size_t)(l + 1) * plan_->nranks];
-        for (int i = s0; i < s1; i++) sent[plan_->send_el[i]] = 1;
-      }
-      auto is_halo = [&](int t) {
-        if (s1 == s0) return false;
-        for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++)
-          if (sent[plan_->glob2loc[staged_.te_el[te]]]) return true;
-        return false;
-      };
-      std::vector<int> fh, fi, gh, gi;
-      for (int i = slab_.level_off[l]; i < slab_.level_off[l + 1]; i++) {
-        const int t = slab_.level_tents[i];
-        const bool h = is_halo(t);
-        if (fast_ && fstage_.ok[t]) (h ? fh : fi).push_back(t);
-        else (h ? gh : gi).push_back(t);
-      }
-      for (int i = s0; i < s1; i++) sent[plan_->send_el[i]] = 0;
-      // most expensive tents first (the order inside a level is free: tents of a level share no element)
-      auto by_cost = [&](int x, int y) {
-        return staged_.te_off[x + 1] - staged_.te_off[x] > staged_.te_off[y + 1] - staged_.te_off[y];
-      };
-      std::stable_sort(fh.begin(), fh.end(), by_cost);
-      std::stable_sort(fi.begin(), fi.end(), by_cost);
-      fast.insert(fast.end(), fh.begin(), fh.end());
-      fast.insert(fast.end(), fi.begin(), fi.end());
-      gen.insert(gen.end(), gh.begin(), gh.end());
-      gen.insert(gen.end(), gi.begin(), gi.end());
-      fast_nhalo_[l] = (int)fh.size();
-      gen_nhalo_[l] = (int)gh.size();
-      (void)f0; (void)g0;
-      gen_off_.push_back((int)gen.size());
-      fast_off_.push_back((int)fast.size());
-    }
-    d_level_tents_ = Upload(gen);
-    d_level_all_ = Upload(slab_.level_tents);
-    d_level_fast_ = Upload(fast);
-  }
   CU(cudaMalloc(&d_singular_, sizeof(int)));
   allocs_.push_back(d_singular_);
   CU(cudaMemset(d_singular_, 0, sizeof(int)));
@@ -267,6 +215,79 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
     q.Qv = vrule.nip;
     SetWavespeedPoly(qt->cdeg, qt->ccoef.data());
     q.c_point = d_cpoint_;
+  }
+  if (qt_ && tent_qt_fast_available(D, order)) {
+    // fast quasi-Trefftz kernel: per-slab records and routing flags computed on the device (tent_qt_fast.cu)
+    double *fe = nullptr, *cone = nullptr, *ff = nullptr;
+    int* ok = nullptr;
+    CU(cudaMalloc(&fe, sizeof(double) * std::max<size_t>((size_t)staged_.nte * qt_fast_fe_stride(), 1)));
+    allocs_.push_back(fe);
+    CU(cudaMalloc(&cone, sizeof(double) * std::max<size_t>((size_t)staged_.nte * 2 * qt_fast_cone_stride(), 1)));
+    allocs_.push_back(cone);
+    CU(cudaMalloc(&ff, sizeof(double) * std::max<size_t>((size_t)staged_.ntf * qt_fast_ff_stride(), 1)));
+    allocs_.push_back(ff);
+    CU(cudaMalloc(&ok, sizeof(int) * std::max(slab_.ntents, 1)));
+    allocs_.push_back(ok);
+    CU(launch_qt_fast_stage(args_, qargs_, slab_.ntents, fe, cone, ff, ok, stream_));
+    qt_ok_.assign(slab_.ntents, 0);
+    CU(cudaMemcpyAsync(qt_ok_.data(), ok, sizeof(int) * slab_.ntents, cudaMemcpyDeviceToHost, stream_));
+    CU(cudaStreamSynchronize(stream_));
+    qfargs_.fe = fe;
+    qfargs_.cone = cone;
+    qfargs_.ff = ff;
+    qtfast_ = true;
+  }
+  {
+    const int nlev = (int)slab_.level_off.size() - 1;
+    std::vector<int> gen, fast;
+    gen_off_.assign(1, 0);
+    fast_off_.assign(1, 0);
+    fast_nhalo_.assign(nlev, 0);
+    gen_nhalo_.assign(nlev, 0);
+    std::vector<char> sent(nel_, 0);
+    for (int l = 0; l < nlev; l++) {
+      const size_t f0 = fast.size(), g0 = gen.size();
+      // halo tents (multi-GPU): the tents of this level that write a row another rank holds. They run first, on their own
+      // stream, so that the exchange of the level overlaps the interior tents (Propagate()).
+      int s0 = 0, s1 = 0;
+      if (plan_ && plan_->nranks > 1) {
+        s0 = plan_->send_off[(size_t)l * plan_->nranks];
+        s1 = plan_->send_off[(size_t)(l + 1) * plan_->nranks];
+        for (int i = s0; i < s1; i++) sent[plan_->send_el[i]] = 1;
+      }
+      auto is_halo = [&](int t) {
+        if (s1 == s0) return false;
+        for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++)
+          if (sent[plan_->glob2loc[staged_.te_el[te]]]) return true;
+        return false;
+      };
+      std::vector<int> fh, fi, gh, gi;
+      for (int i = slab_.level_off[l]; i < slab_.level_off[l + 1]; i++) {
+        const int t = slab_.level_tents[i];
+        const bool h = is_halo(t);
+        if ((fast_ && fstage_.ok[t]) || (qtfast_ && qt_ok_[t])) (h ? fh : fi).push_back(t);
+        else (h ? gh : gi).push_back(t);
+      }
+      for (int i = s0; i < s1; i++) sent[plan_->send_el[i]] = 0;
+      // most expensive tents first (the order inside a level is free: tents of a level share no element)
+      auto by_cost = [&](int x, int y) {
+        return staged_.te_off[x + 1] - staged_.te_off[x] > staged_.te_off[y + 1] - staged_.te_off[y];
+      };
+      std::stable_sort(fh.begin(), fh.end(), by_cost);
+      std::stable_sort(fi.begin(), fi.end(), by_cost);
+      fast.insert(fast.end(), fh.begin(), fh.end());
+      fast.insert(fast.end(), fi.begin(), fi.end());
+      gen.insert(gen.end(), gh.begin(), gh.end());
+      gen.insert(gen.end(), gi.begin(), gi.end());
+      fast_nhalo_[l] = (int)fh.size();
+      gen_nhalo_[l] = (int)gh.size();
+      (void)f0; (void)g0;
+      gen_off_.push_back((int)gen.size());
+      fast_off_.push_back((int)fast.size());
+    }
+    d_level_tents_ = Upload(gen);
+    d_level_all_ = Upload(slab_.level_tents);
+    d_level_fast_ = Upload(fast);
   }
 
   // element quadrature weights |detJ| * w (GetWeight, twavetents.cpp:793,818,843)
@@ -426,9 +447,23 @@ void Solver::Propagate() {
   int launches = 0;
   CU(cudaEventRecord(ev0_, stream_));
   for (int l = 0; l < nlev && qt_; l++) {
+    // quasi-Trefftz: fast monomial-space DMMA kernel where a variant exists (second-order form, causal top faces),
+    // generic kernel otherwise
+    const bool usefast = qtfast_ && !force_generic_ && !fosystem_;
     TentKernelArgs a = args_;
-    a.tents = d_level_all_ + slab_.level_off[l];
-    a.ntents = slab_.level_off[l + 1] - slab_.level_off[l];
+    if (usefast) {
+      a.tents = d_level_fast_ + fast_off_[l];
+      a.ntents = fast_off_[l + 1] - fast_off_[l];
+      if (a.ntents > 0) {
+        CU(launch_tent_qt_fast(order_, a, qargs_, qfargs_, stream_));
+        launches++;
+      }
+      a.tents = d_level_tents_ + gen_off_[l];
+      a.ntents = gen_off_[l + 1] - gen_off_[l];
+    } else {
+      a.tents = d_level_all_ + slab_.level_off[l];
+      a.ntents = slab_.level_off[l + 1] - slab_.level_off[l];
+    }
     if (a.ntents > 0) {
       CU(launch_tent_qt(mesh_.D, a, qargs_, smem_, stream_));
       launches++;

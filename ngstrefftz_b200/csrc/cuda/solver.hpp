@@ -67,8 +67,8 @@ class Solver {
 
   double timeshift() const { return timeshift_; }
   void set_timeshift(double t) { timeshift_ = t; }
-  const char* kernel_name() const { return qt_ ? "tent_kernel_qt" : ((fast_ && !force_generic_) ? "tent_kernel_fast" : "tent_kernel_generic"); }
-  int ntents_fast() const { return fast_ ? fast_off_.back() : 0; }
+  const char* kernel_name() const { return qt_ ? ((qtfast_ && !force_generic_ && !fosystem_) ? "tent_kernel_qt_fast" : "tent_kernel_qt") : ((fast_ && !force_generic_) ? "tent_kernel_fast" : "tent_kernel_generic"); }
+  int ntents_fast() const { return (fast_ || qtfast_) ? fast_off_.back() : 0; }
   // 0 = automatic routing (fast kernel where possible), 1 = every tent on the generic DFMA kernel (A/B evidence)
   // 0: fast kernel where available (default), 1: generic kernel everywhere, 2: fast kernel, multi-GPU exchange not overlapped
   void set_kernel_mode(int mode) { force_generic_ = mode == 1; overlap_ = mode != 2; }
@@ -118,6 +118,9 @@ class Solver {
   std::vector<int> gen_off_, fast_off_;  // nlevels + 1 offsets into the two lists
   bool fast_ = false, force_generic_ = false, qt_ = false;
   QtArgs qargs_{};
+  QtFastArgs qfargs_{};
+  bool qtfast_ = false;            // quasi-Trefftz tents with qt_ok_ run on tent_kernel_qt_fast
+  std::vector<int> qt_ok_;
   double* d_cpoint_ = nullptr;     // nel * nip wavespeed per quadrature point (QT; optional for reductions)
   int* d_level_all_ = nullptr;     // per level: all tents (slab order), for force_generic_
   FastStage fstage_;

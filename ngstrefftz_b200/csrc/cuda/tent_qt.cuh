@@ -29,6 +29,22 @@ struct QtArgs {
   int Qv;
 };
 
+// Fast quasi-Trefftz kernel (tent_qt_fast.cu; D = 2): state-independent records computed once per slab on the device
+struct QtFastArgs {
+  const double* fe;    // nte * qt_fast_fe_stride(): scaled element vertices, face vertex times, normals, areas
+  const double* cone;  // nte * 2 * qt_fast_cone_stride(): cone maps, volume, h / max(1/c^2)
+  const double* ff;    // ntf * qt_fast_ff_stride(): boundary faces
+};
+bool tent_qt_fast_available(int D, int order);
+int qt_fast_fe_stride();
+int qt_fast_cone_stride();
+int qt_fast_ff_stride();
+// fills the three record arrays and ok[tent] (1 = the tent can run on the fast kernel)
+cudaError_t launch_qt_fast_stage(const TentKernelArgs& a, const QtArgs& qa, int ntents, double* fe, double* cone, double* ff,
+                                 int* ok, cudaStream_t stream);
+cudaError_t launch_tent_qt_fast(int order, const TentKernelArgs& a, const QtArgs& qa, const QtFastArgs& f,
+                                cudaStream_t stream);
+
 size_t tent_qt_smem_bytes(int D, const TentKernelArgs& a, const QtArgs& q);
 cudaError_t launch_tent_qt(int D, const TentKernelArgs& a, const QtArgs& q, size_t smem, cudaStream_t stream);
 
