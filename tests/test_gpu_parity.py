@@ -162,7 +162,7 @@ def test_errors_on_gpu(built):
 
 
 # ---------------------------------------------------------------------------------------------- quasi-Trefftz (QTWaveTents)
-def qt_both(mesh, order, dt, nslabs=1, cpoly=None, bpoly=None):
+def qt_both(mesh, order, dt, nslabs=1, cpoly=None, bpoly=None, generic=False):
     from test_oracle_qt import qt_exact
     D = mesh.dim
     c = cpoly or ng.PolynomialCF.affine([1.0] * D, 1.0)
@@ -172,6 +172,8 @@ def qt_both(mesh, order, dt, nslabs=1, cpoly=None, bpoly=None):
     ts.SetMaxWavespeed(c)
     assert ts.PitchTents(dt, True, 2 / 3)
     tw = ng.TWave(order, ts, c, BBcf=bpoly if bpoly is not None else 1)
+    if generic:
+        tw.set_kernel_mode(1)
     tw.SetInitial(f)
     tw.SetBoundaryCF(bnd)
     o = Oracle(mesh)
@@ -185,7 +187,9 @@ def qt_both(mesh, order, dt, nslabs=1, cpoly=None, bpoly=None):
     for _ in range(nslabs):
         tw.Propagate()
         o.propagate()
-    assert tw.kernel_name() == "tent_kernel_qt" and tw.last_launches() > 0
+    # D = 2, orders 3-5 run on the monomial-space DMMA kernel, everything else on the generic quasi-Trefftz kernel
+    want = "tent_kernel_qt_fast" if (D == 2 and 3 <= order <= 5 and not generic) else "tent_kernel_qt"
+    assert tw.kernel_name() == want and tw.last_launches() > 0
     return tw, o, f
 
 
@@ -195,6 +199,10 @@ QT_CASES = {
     "2d_p4": (lambda: ng.UnitSquareMesh(4), 4, 0.25, 1, None),
     "2d_p5": (lambda: ng.UnitSquareMesh(3), 5, 0.2, 1, None),
     "2d_p3_varB": (lambda: ng.UnitSquareMesh(4), 3, 0.2, 2, "B"),
+    "2d_p5_varB_3slabs": (lambda: ng.UnitSquareMesh(5), 5, 0.15, 3, "B"),
+    "2d_p2": (lambda: ng.UnitSquareMesh(4), 2, 0.2, 1, None),
+    "2d_p4_generic": (lambda: ng.UnitSquareMesh(4), 4, 0.25, 1, "generic"),
+    "2d_p5_generic": (lambda: ng.UnitSquareMesh(3), 5, 0.2, 1, "generic"),
 }
 
 
@@ -204,7 +212,7 @@ def test_parity_quasi_trefftz(built, name):
     mk, order, dt, nslabs, var = QT_CASES[name]
     mesh = mk()
     bpoly = ng.PolynomialCF(mesh.dim, {(0, 0): 1.0, (1, 0): 0.2, (0, 1): 0.1}) if var == "B" else None
-    tw, o, f = qt_both(mesh, order, dt, nslabs, bpoly=bpoly)
+    tw, o, f = qt_both(mesh, order, dt, nslabs, bpoly=bpoly, generic=(var == "generic"))
     wf, ref = tw.GetWavefront(), o.wavefront()
     rel = np.abs(wf - ref).max() / np.abs(ref).max()
     assert rel <= 1e-9, rel
