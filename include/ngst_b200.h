@@ -140,8 +140,10 @@ int ngst_twave_set_timeshift(ngst_twave* t, double timeshift);
 const char* ngst_twave_kernel_name(const ngst_twave* t);
 /* Kernel routing (diagnostics; no reference counterpart): mode 0 = automatic (single-wavespeed tents on the DMMA
  * kernel tent_kernel_fast, tents with material interfaces on tent_kernel_generic), 1 = every tent on the generic
- * DFMA kernel, 2 = as 0 but, on several GPUs, the halo exchange of a level runs after all tents of the level instead
- * of overlapping the interior tents (A/B measurements; results are bitwise identical in every mode 0/2).
+ * DFMA kernel, 2 = as 0 but strictly level by level: on one GPU one launch per level instead of the dependency-driven
+ * single launch per slab, on several GPUs the halo exchange of a level runs after all tents of the level instead of
+ * overlapping the interior tents; 3 = as 0 with the dependency-driven single launch forced (mode 0 uses it only for
+ * slabs with small levels). Results are bitwise identical in modes 0, 2 and 3.
  * ngst_twave_ntents_fast: tents of the slab routed to the fast kernel in mode 0. */
 int ngst_twave_set_kernel_mode(ngst_twave* t, int mode);
 int ngst_twave_ntents_fast(const ngst_twave* t);
@@ -150,6 +152,13 @@ double ngst_twave_last_ms(const ngst_twave* t);
 int ngst_twave_last_launches(const ngst_twave* t);
 /* GetWavefront src/twavetents.hpp:193: copy of the nel x (ncomp*nip) state to a host buffer */
 int ngst_twave_get_wavefront(ngst_twave* t, double* out);
+/* GetWave src/__init__.py:7-43 (per-element L2 projection of the quadrature-point state, IntegrationPointFunction
+ * src/specialcoefficientfunction.cpp:48-172): second-order state -> u onto polynomials of degree p (1 component),
+ * first-order state -> (grad u, d_t u) onto degree p-1 (D+1 components). The basis is orthonormal on the reference
+ * simplex (monomials, first coordinate outermost, Gram-Schmidt in that order); NGSolve's L2 dof numbering is not part of
+ * the reference sources. sizes[3] = {components, ndof, degree}; coef: nel x components x ndof; psi_at_points: nip x ndof;
+ * mono_coef: ndof x ndof (psi_k = sum_j mono_coef[k*ndof+j] xi^expo_j); expo: ndof x D. Null outputs are skipped. */
+int ngst_twave_get_wave(ngst_twave* t, int* sizes, double* coef, double* psi_at_points, double* mono_coef, int* expo);
 /* Energy / Error / L2Error src/twavetents.cpp:766-847 on host wavefronts (nel x ncomp*nip) */
 int ngst_twave_energy(ngst_twave* t, const double* wf, double* out);
 int ngst_twave_error(ngst_twave* t, const double* wf, const double* wf_ref, double* out);

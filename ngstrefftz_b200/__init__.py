@@ -233,6 +233,25 @@ class TentSlab:
         return ret
 
 
+class L2Wave:
+    """Result of GetWave: coef[el, component, k] in the basis psi_k = sum_j mono[k, j] xi^expo[j] (orthonormal on the
+    reference simplex; xi = reference coordinates, x = sum_i lambda_i P_i with lambda = (xi, 1 - sum xi))."""
+
+    def __init__(self, coef, order, psi_at_points, mono, expo):
+        self.coef, self.order, self.psi_at_points, self.mono, self.expo = coef, order, psi_at_points, mono, expo
+
+    def at_quadrature(self):
+        """values[el, component, q] of the projected field at the rule points of every element"""
+        return np.einsum("eck,qk->ecq", self.coef, self.psi_at_points)
+
+    def __call__(self, el, xi):
+        """values[component, point] on element(s) el at reference points xi (npts x D)"""
+        xi = np.atleast_2d(np.asarray(xi, dtype=float))
+        m = np.prod(xi[:, None, :] ** self.expo[None, :, :], axis=2)  # npts x ndof monomials
+        psi = m @ self.mono.T
+        return self.coef[el] @ psi.T
+
+
 class TrefftzTents:
     """Base class (src/twavetents.hpp:78-93)."""
 
@@ -444,6 +463,23 @@ class TWaveTents(TrefftzTents):
         wf = np.zeros((self.nel, self.ncomp * self.nip))
         check(lib.ngst_twave_get_wavefront(self._h, dptr(wf)))
         return wf
+
+    def GetWave(self, U=None):
+        """GetWave (src/__init__.py:7-43): element-wise L2 projection of the current state onto polynomials -- u onto
+        degree p for a second-order state (the reference's U.dim == 1 branch), (grad u, d_t u) onto degree p-1 for a
+        first-order state. Returns an L2Wave (modal coefficients in a basis orthonormal on the reference simplex); when U
+        is given (any object with a writable `.vec` numpy array of the right size) the coefficients are also stored there."""
+        sizes = np.zeros(3, dtype=np.int32)
+        check(lib.ngst_twave_get_wave(self._h, iptr(sizes), None, None, None, None))
+        comps, ndof, deg = (int(x) for x in sizes)
+        coef = np.zeros((self.nel, comps, ndof))
+        psi = np.zeros((self.nip, ndof))
+        mono = np.zeros((ndof, ndof))
+        expo = np.zeros((ndof, self.D), dtype=np.int32)
+        check(lib.ngst_twave_get_wave(self._h, iptr(sizes), dptr(coef), dptr(psi), dptr(mono), iptr(expo)))
+        if U is not None:
+            np.asarray(U.vec).reshape(-1)[:] = coef.reshape(-1)
+        return L2Wave(coef, deg, psi, mono, expo)
 
     def Error(self, wavefront, wavefront_corr):
         out = C.c_double(0)

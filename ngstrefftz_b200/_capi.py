@@ -81,6 +81,7 @@ _SIGS = {
     "ngst_twave_last_ms": (C.c_double, [c_vp]),
     "ngst_twave_last_launches": (C.c_int, [c_vp]),
     "ngst_twave_get_wavefront": (C.c_int, [c_vp, c_dp]),
+    "ngst_twave_get_wave": (C.c_int, [c_vp, c_ip, c_dp, c_dp, c_dp, c_ip]),
     "ngst_twave_energy": (C.c_int, [c_vp, c_dp, c_dp]),
     "ngst_twave_error": (C.c_int, [c_vp, c_dp, c_dp, c_dp]),
     "ngst_twave_l2error": (C.c_int, [c_vp, c_dp, c_dp, c_dp]),

@@ -354,7 +354,7 @@ const char* ngst_twave_kernel_name(const ngst_twave* t) { return t ? t->solver->
 int ngst_twave_set_kernel_mode(ngst_twave* t, int mode) {
   return guarded([&] {
     need(t, "solver");
-    if (mode < 0 || mode > 2) throw std::invalid_argument("ngst_twave_set_kernel_mode: mode must be 0, 1 or 2");
+    if (mode < 0 || mode > 3) throw std::invalid_argument("ngst_twave_set_kernel_mode: mode must be 0, 1, 2 or 3");
     t->solver->set_kernel_mode(mode);
   });
 }
@@ -364,6 +364,10 @@ int ngst_twave_last_launches(const ngst_twave* t) { return t ? t->solver->last_l
 
 int ngst_twave_get_wavefront(ngst_twave* t, double* out) {
   return guarded([&] { need(t, "solver"); need(out, "out"); t->solver->GetWavefront(out); });
+}
+
+int ngst_twave_get_wave(ngst_twave* t, int* sizes, double* coef, double* psi_at_points, double* mono_coef, int* expo) {
+  return guarded([&] { need(t, "solver"); t->solver->GetWave(sizes, coef, psi_at_points, mono_coef, expo); });
 }
 
 int ngst_twave_energy(ngst_twave* t, const double* wf, double* out) {

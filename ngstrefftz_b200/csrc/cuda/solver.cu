@@ -288,6 +288,40 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
     d_level_tents_ = Upload(gen);
     d_level_all_ = Upload(slab_.level_tents);
     d_level_fast_ = Upload(fast);
+    // Dependency-driven scheduling (single GPU, every tent on the fast kernel): tent t must wait for the last earlier tent
+    // (pitching order = the reference's serial order) that touched each of its elements -- exactly the read/write
+    // hazards of the state rows. One launch per slab then replaces the per-level launches and their tails.
+    if (fast_ && !qt_ && !plan_ && gen.empty() && slab_.ntents > 0) {
+      const int nt = slab_.ntents;
+      std::vector<int> last(mesh_.nel, -1), indeg(nt, 0), soff(nt + 1, 0);
+      std::vector<std::vector<int>> pred(nt);
+      for (int t = 0; t < nt; t++) {
+        for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++) {
+          const int e = staged_.te_el[te];
+          if (last[e] >= 0) pred[t].push_back(last[e]);
+          last[e] = t;
+        }
+        std::sort(pred[t].begin(), pred[t].end());
+        pred[t].erase(std::unique(pred[t].begin(), pred[t].end()), pred[t].end());
+        indeg[t] = (int)pred[t].size();
+        for (int p : pred[t]) {
+          if (slab_.level[p] >= slab_.level[t]) throw std::logic_error("tent levels do not respect the element hazards");
+          soff[p + 1]++;
+        }
+      }
+      for (int t = 0; t < nt; t++) soff[t + 1] += soff[t];
+      std::vector<int> succ(soff[nt]), fill(soff.begin(), soff.end() - 1);
+      for (int t = 0; t < nt; t++)
+        for (int p : pred[t]) succ[fill[p]++] = t;
+      d_indeg_ = Upload(indeg);
+      d_succ_off_ = Upload(soff);
+      d_succ_ = Upload(succ);
+      CU(cudaMalloc(&d_remaining_, sizeof(int) * nt));
+      allocs_.push_back(d_remaining_);
+      CU(cudaMalloc(&d_ticket_, sizeof(int)));
+      allocs_.push_back(d_ticket_);
+      dag_ = true;
+    }
   }
 
   // element quadrature weights |detJ| * w (GetWeight, twavetents.cpp:793,818,843)
@@ -480,6 +514,23 @@ void Solver::Propagate() {
     }
     if (comm_) launches += ExchangeLevel(l, stream_);
   }
+  // Measured on B200 (profiles/r01o): with ~2700 tents per level (config 4) the single launch is 3 % slower than one launch
+  // per level (waiting CTAs hold SM slots and poll), with small levels it removes the launch gaps and tails.
+  const bool small_levels = slab_.ntents < 2 * 444 * nlev;
+  const bool dag = dag_ && (dag_mode_ == 2 || (dag_mode_ == 1 && small_levels)) && !force_generic_ && !comm_;
+  if (dag) {
+    CU(cudaMemcpyAsync(d_remaining_, d_indeg_, sizeof(int) * slab_.ntents, cudaMemcpyDeviceToDevice, stream_));
+    CU(cudaMemsetAsync(d_ticket_, 0, sizeof(int), stream_));
+    TentKernelArgs a = args_;
+    a.tents = d_level_fast_;  // level after level, most expensive tents first inside a level
+    a.ntents = fast_off_.back();
+    a.ticket = d_ticket_;
+    a.remaining = d_remaining_;
+    a.succ_off = d_succ_off_;
+    a.succ = d_succ_;
+    CU(launch_tent_fast(mesh_.D, order_, fosystem_, a, fargs_, stream_));
+    launches++;
+  }
   const bool overlap = comm_ && !force_generic_ && !qt_ && overlap_;
   if (overlap && !stream_halo_) {
     int lo = 0, hi = 0;
@@ -489,7 +540,7 @@ void Solver::Propagate() {
     CU(cudaEventCreateWithFlags(&ev_int_, cudaEventDisableTiming));
   }
   if (overlap) CU(cudaEventRecord(ev_int_, stream_));
-  for (int l = 0; l < nlev && !force_generic_ && !qt_; l++) {
+  for (int l = 0; l < nlev && !force_generic_ && !qt_ && !dag; l++) {
     // level l: [halo tents | interior tents] of the fast and of the generic list. Single GPU: one launch per list.
     // Multi-GPU: halo tents + exchange on the high-priority stream, interior tents concurrently on the main stream;
     // level l+1 starts when both are done (tents of a level touch disjoint rows, received rows belong to no local tent
@@ -589,6 +640,78 @@ double Solver::ReduceElements(const double* a, const double* b, int mode) {
     for (double v : part) s += v;  // fixed element order: deterministic
   }
   return s;
+}
+
+void Solver::GetWave(int* sizes, double* coef, double* psi_at_points, double* mono_coef, int* expo) {
+  if (!have_initial_) throw std::logic_error("GetWave: SetInitial has not been called");
+  CU(cudaSetDevice(device_));
+  const int D = mesh_.D, Q = rule_.nip;
+  const int deg = fosystem_ ? order_ - 1 : order_;
+  const int comps = fosystem_ ? D + 1 : 1;
+  if (proj_deg_ != deg) {
+    // orthonormal basis on the reference simplex: the monomials xi^alpha, |alpha| <= deg (first coordinate's exponent
+    // outermost), orthonormalised in that order by modified Gram-Schmidt (twice) in the inner product of the order-2p
+    // rule, which is exact for these products. NGSolve's own L2 dof numbering is not part of the reference sources.
+    const std::vector<int> ex = monomial_exponents(D, deg);
+    const int nd = (int)ex.size() / D;
+    std::vector<double> V((size_t)Q * nd), R((size_t)nd * nd, 0.0);  // V[q*nd + k] -> orthonormal columns; mono = psi R
+    for (int q = 0; q < Q; q++)
+      for (int k = 0; k < nd; k++) {
+        double m = 1.0;
+        for (int d = 0; d < D; d++) m *= std::pow(rule_.xi[(size_t)q * D + d], ex[(size_t)k * D + d]);
+        V[(size_t)q * nd + k] = m;
+      }
+    auto dot = [&](int a, int b) {
+      double s = 0;
+      for (int q = 0; q < Q; q++) s += rule_.w[q] * V[(size_t)q * nd + a] * V[(size_t)q * nd + b];
+      return s;
+    };
+    for (int k = 0; k < nd; k++) {
+      for (int pass = 0; pass < 2; pass++)
+        for (int j = 0; j < k; j++) {
+          const double r = dot(j, k);
+          R[(size_t)j * nd + k] += r;
+          for (int q = 0; q < Q; q++) V[(size_t)q * nd + k] -= r * V[(size_t)q * nd + j];
+        }
+      const double nrm = std::sqrt(dot(k, k));
+      if (!(nrm > 0)) throw std::domain_error("GetWave: the quadrature rule does not resolve the polynomial space");
+      R[(size_t)k * nd + k] = nrm;
+      for (int q = 0; q < Q; q++) V[(size_t)q * nd + k] /= nrm;
+    }
+    // psi = mono R^-1: coefficient of monomial j in psi_k is (R^-1)[j][k]
+    std::vector<double> Rinv((size_t)nd * nd, 0.0);
+    for (int c = 0; c < nd; c++) {
+      Rinv[(size_t)c * nd + c] = 1.0 / R[(size_t)c * nd + c];
+      for (int r = c - 1; r >= 0; r--) {
+        double s = 0;
+        for (int j = r + 1; j <= c; j++) s += R[(size_t)r * nd + j] * Rinv[(size_t)j * nd + c];
+        Rinv[(size_t)r * nd + c] = -s / R[(size_t)r * nd + r];
+      }
+    }
+    proj_mono_.assign((size_t)nd * nd, 0.0);
+    for (int k = 0; k < nd; k++)
+      for (int j = 0; j < nd; j++) proj_mono_[(size_t)k * nd + j] = Rinv[(size_t)j * nd + k];
+    proj_psi_ = V;
+    proj_expo_ = ex;
+    std::vector<double> P((size_t)nd * Q);
+    for (int k = 0; k < nd; k++)
+      for (int q = 0; q < Q; q++) P[(size_t)k * Q + q] = rule_.w[q] * V[(size_t)q * nd + k];
+    d_proj_ = Upload(P);
+    CU(cudaMalloc(&d_proj_out_, sizeof(double) * std::max<size_t>((size_t)nel_ * (D + 1) * nd, 1)));
+    allocs_.push_back(d_proj_out_);
+    proj_deg_ = deg;
+    proj_ndof_ = nd;
+  }
+  const int nd = proj_ndof_;
+  if (sizes) { sizes[0] = comps; sizes[1] = nd; sizes[2] = deg; }
+  if (psi_at_points) std::copy(proj_psi_.begin(), proj_psi_.end(), psi_at_points);
+  if (mono_coef) std::copy(proj_mono_.begin(), proj_mono_.end(), mono_coef);
+  if (expo) std::copy(proj_expo_.begin(), proj_expo_.end(), expo);
+  if (coef) {
+    CU(launch_project_rows(nel_, Q, nd, 0, comps, ncomp_ * Q, d_proj_, d_wavefront_, d_proj_out_, stream_));
+    CU(cudaMemcpyAsync(coef, d_proj_out_, sizeof(double) * (size_t)nel_ * comps * nd, cudaMemcpyDeviceToHost, stream_));
+    CU(cudaStreamSynchronize(stream_));
+  }
 }
 
 void Solver::InitComm(const void* id128) {

@@ -64,14 +64,22 @@ class Solver {
   double Energy(const double* wf);
   double Error(const double* wf, const double* ref, bool l2only);
   double MaxAdiam() const;
+  // GetWave (src/__init__.py:7-43): L2 projection of the state onto polynomials, element by element. Second-order state:
+  // u onto degree p (1 component); first-order state: (grad u, d_t u) onto degree p-1 (D+1 components).
+  // sizes[3] = {components, ndof per component, degree}. Null pointers are skipped. coef: nel x comps x ndof;
+  // psi_at_points: nip x ndof values of the orthonormal reference basis at the rule points; mono_coef: ndof x ndof,
+  // psi_k = sum_j mono_coef[k*ndof + j] xi^expo_j; expo: ndof x D.
+  void GetWave(int* sizes, double* coef, double* psi_at_points, double* mono_coef, int* expo);
 
   double timeshift() const { return timeshift_; }
   void set_timeshift(double t) { timeshift_ = t; }
   const char* kernel_name() const { return qt_ ? ((qtfast_ && !force_generic_ && !fosystem_) ? "tent_kernel_qt_fast" : "tent_kernel_qt") : ((fast_ && !force_generic_) ? "tent_kernel_fast" : "tent_kernel_generic"); }
   int ntents_fast() const { return (fast_ || qtfast_) ? fast_off_.back() : 0; }
   // 0 = automatic routing (fast kernel where possible), 1 = every tent on the generic DFMA kernel (A/B evidence)
-  // 0: fast kernel where available (default), 1: generic kernel everywhere, 2: fast kernel, multi-GPU exchange not overlapped
-  void set_kernel_mode(int mode) { force_generic_ = mode == 1; overlap_ = mode != 2; }
+  // 0: fast kernel where available (default), 1: generic kernel everywhere, 2: fast kernel with one launch per level
+  // (no dependency-driven scheduling on one GPU, exchange not overlapped on several), 3: as 0 with the dependency-driven
+  // single launch forced (default: only for slabs with small levels, where launches and level tails dominate)
+  void set_kernel_mode(int mode) { force_generic_ = mode == 1; overlap_ = mode != 2; dag_mode_ = mode == 2 ? 0 : (mode == 3 ? 2 : 1); }
   double last_ms() const { return last_ms_; }
   int last_launches() const { return last_launches_; }
 
@@ -110,6 +118,10 @@ class Solver {
   cudaStream_t stream_halo_ = nullptr;
   cudaEvent_t ev_halo_ = nullptr, ev_int_ = nullptr;
   bool overlap_ = true;
+  // single GPU: dependency-driven scheduling of the fast kernel (one launch per slab)
+  bool dag_ = false;
+  int dag_mode_ = 1;  // 0 never, 1 automatic (average level smaller than two waves of CTAs), 2 always
+  int *d_indeg_ = nullptr, *d_remaining_ = nullptr, *d_ticket_ = nullptr, *d_succ_off_ = nullptr, *d_succ_ = nullptr;
   std::vector<int> fast_nhalo_, gen_nhalo_;  // per level: leading halo tents of the fast / generic list
   std::vector<void*> allocs_;
   TentKernelArgs args_{};
@@ -134,6 +146,11 @@ class Solver {
   double* d_scratch_ = nullptr;
   double* d_tmp_a_ = nullptr;
   double* d_tmp_b_ = nullptr;
+  double* d_proj_ = nullptr;       // projection matrix of GetWave (ndof x nip), built on first use
+  double* d_proj_out_ = nullptr;
+  int proj_deg_ = -1, proj_ndof_ = 0;
+  std::vector<double> proj_psi_, proj_mono_;
+  std::vector<int> proj_expo_;
   int* d_singular_ = nullptr;
   int* d_rowptr_[2] = {nullptr, nullptr};  // [fosystem]
   int* d_col_[2] = {nullptr, nullptr};
@@ -147,6 +164,8 @@ class Solver {
 // kernels (tent_generic.cu, reduce.cu)
 size_t tent_generic_smem_bytes(int D, const TentKernelArgs& a);
 cudaError_t launch_tent_generic(int D, const TentKernelArgs& a, int threads, size_t smem, cudaStream_t stream);
+cudaError_t launch_project_rows(int nel, int Q, int ndof, int comp0, int ncomp_used, int rowlen, const double* P,
+                                const double* wf, double* out, cudaStream_t stream);
 cudaError_t launch_element_reduce(int mode, int D, int nel, int Q, int ncomp, int fosystem, const double* elw,
                                   const double* c_el, const double* c_point, const double* a, const double* b,
                                   double* out, cudaStream_t stream);

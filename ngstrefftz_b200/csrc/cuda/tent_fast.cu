@@ -89,7 +89,27 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const int g = lane >> 2, k = lane & 3;  // DMMA fragment coordinates
   const int th = w >> 1, kh = w & 1;      // tile half / k-step parity of this warp in the symmetric passes
-  const int tent = a.tents[blockIdx.x];
+  int tent;
+  if (a.ticket) {
+    // dependency-driven order (replaces the reference's RunParallelDependency, ngstents paralleldepend.hpp:20-131): tickets
+    // are handed out in level order, so every predecessor holds an earlier ticket and is running or done -- no deadlock.
+    __shared__ int s_tent;
+    if (tid == 0) {
+      const int t = a.tents[atomicAdd(a.ticket, 1)];
+      volatile int* r = a.remaining + t;
+      long long spins = 0;
+      while (*r > 0) {
+        __nanosleep(64);
+        if (++spins > (1ll << 26)) { atomicAdd(a.singular, 1 << 20); break; }  // never hang the device: flag and go on
+      }
+      __threadfence();
+      s_tent = t;
+    }
+    __syncthreads();
+    tent = s_tent;
+  } else {
+    tent = a.tents[blockIdx.x];
+  }
   const int te0 = a.te_off[tent], nel = a.te_off[tent + 1] - te0;
   const int tf0 = a.tf_off[tent], nfc = a.tf_off[tent + 1] - tf0;
   const int npts = nel * Q;
@@ -151,7 +171,7 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
     const int idc = min(lane, npts - 1);
     const double* __restrict__ wf = a.wavefront + (size_t)a.te_el[te0 + idc / Q] * (NC * Q) + idc % Q;
 #pragma unroll
-    for (int cc = 0; cc < NC; cc++) gnext[cc] = wf[cc * Q];
+    for (int cc = 0; cc < NC; cc++) gnext[cc] = __ldcg(wf + cc * Q);  // L2: rows written by other SMs
   }
   for (int c0 = 0; c0 < npts; c0 += kChunk) {
     const int idx = c0 + lane;
@@ -165,7 +185,7 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
       const int idn = min(idx + kChunk, npts - 1);
       const double* __restrict__ wf = a.wavefront + (size_t)a.te_el[te0 + idn / Q] * (NC * Q) + idn % Q;
 #pragma unroll
-      for (int cc = 0; cc < NC; cc++) gnext[cc] = wf[cc * Q];
+      for (int cc = 0; cc < NC; cc++) gnext[cc] = __ldcg(wf + cc * Q);  // L2: rows written by other SMs
     }
     const double* __restrict__ rec = f.fe + (size_t)te * FE;
     const double* __restrict__ lm = a.lam + q * d1;
@@ -386,6 +406,11 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
 #pragma unroll
     for (int u = 0; u < D; u++) wf[((FO ? 0 : 1) + u) * Q + q] = s * dv[u];
     wf[((FO ? 0 : 1) + D) * Q + q] = sc * dv[D];
+  }
+  if (a.ticket) {
+    __threadfence();  // this thread's state rows are visible device-wide before the successors are released
+    __syncthreads();
+    for (int s = a.succ_off[tent] + tid; s < a.succ_off[tent + 1]; s += kThreads) atomicSub(a.remaining + a.succ[s], 1);
   }
 }
 

@@ -42,6 +42,13 @@ struct TentKernelArgs {
   int ntents;
   int max_ndom;
   int* singular;           // incremented when a zero pivot is met
+  // ---- dependency-driven scheduling (tent_fast.cu, single GPU): one launch per slab; CTAs draw tents from `tents` in
+  // order through `ticket` and wait until remaining[tent] (unfinished predecessors) is zero; a finished tent decrements
+  // the counters of its successors. ticket == nullptr: `tents` is one level, CTA b solves tents[b].
+  int* ticket;
+  int* remaining;
+  const int* succ_off;
+  const int* succ;
 };
 
 }  // namespace ngst

@@ -19,3 +19,9 @@ $SMALL > gpurun_out/${TAG}_plain_small2.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:tent_kernel -s 60 -c 3 -f -o gpurun_out/${TAG}_prof_tent $SMALL > gpurun_out/${TAG}_ncu_full.log 2>&1
 echo "ncu full rc=$?"
 ls -la gpurun_out
+if [ "${QT:-0}" = "1" ]; then
+QTS="python scripts/bench_configs.py --config 3 --scale 16 --slabs 1"
+$QTS > gpurun_out/${TAG}_qt_small.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:tent_kernel_qt_fast -s 4 -c 2 -f -o gpurun_out/${TAG}_prof_qt $QTS > gpurun_out/${TAG}_ncu_qt.log 2>&1
+echo "ncu qt rc=$?"
+fi

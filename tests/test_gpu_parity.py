@@ -144,6 +144,70 @@ def test_size_independent_properties_large(built):
     assert tw.Error(out[0], exact) < 2e-4
 
 
+def test_dependency_driven_launch_matches_level_launches(built):
+    """One GPU, every tent on the fast kernel: Propagate is ONE launch per slab whose CTAs draw tents in level order and wait
+    on per-tent hazard counters (replacing RunParallelDependency, paralleldepend.hpp:20-131). Mode 2 keeps one launch per
+    level. Same tents, same arithmetic per tent: the states must be bitwise identical."""
+    f = standing(3)
+    mesh = ng.UnitCubeMesh(10)
+    ts = ng.TentSlab(mesh, "edge")
+    ts.SetMaxWavespeed(1.0)
+    assert ts.PitchTents(0.08, True, 2 / 3)
+    out, launches = [], []
+    for mode in (3, 2):
+        tw = ng.TWave(4, ts, 1.0)
+        tw.set_kernel_mode(mode)
+        tw.SetInitial(f)
+        tw.SetBoundaryCF(dirichlet(f, 3))
+        for _ in range(3):
+            tw.Propagate()
+        out.append(tw.GetWavefront())
+        launches.append(tw.last_launches())
+    assert launches[0] == 1 and launches[1] == ts.GetNLayers()
+    assert np.array_equal(out[0], out[1])
+
+
+@pytest.mark.parametrize("D,fo", [(1, False), (2, False), (3, False), (2, True), (3, True)])
+def test_get_wave_projection(built, D, fo):
+    """GetWave (src/__init__.py:7-43): the element-wise L2 projection reproduces a polynomial state exactly (degree p for
+    u, p-1 for the first-order components), its basis is orthonormal in the rule, and it equals the numpy least-squares
+    projection for a non-polynomial state."""
+    order = 3
+    mesh = {1: lambda: ng.SegMesh(6, 0, 1), 2: lambda: ng.UnitSquareMesh(3), 3: lambda: ng.UnitCubeMesh(2)}[D]()
+    ts = ng.TentSlab(mesh, "edge")
+    ts.SetMaxWavespeed(1.0)
+    assert ts.PitchTents(0.1, True, 2 / 3)
+    tw = ng.TWave(order, ts, 1.0)
+    pf = poly_solution(D, 1.0)  # cubic u, quadratic derivatives
+    init = first_order(pf) if fo else pf
+    tw.SetInitial(init)
+    w = tw.GetWave()
+    assert w.order == (order - 1 if fo else order)
+    assert w.coef.shape[:2] == (mesh.ne, D + 1 if fo else 1)
+    wf = tw.GetWavefront().reshape(mesh.ne, -1, tw.nip)
+    got = w.at_quadrature()
+    want = wf[:, :got.shape[1], :]
+    assert np.abs(got - want).max() <= 1e-12 * np.abs(want).max()
+    rule_w = tw.quadrature()[1][0] / tw.quadrature()[1][0].sum() / math.factorial(D)
+    gram = w.psi_at_points.T @ (rule_w[:, None] * w.psi_at_points)
+    assert np.abs(gram - np.eye(gram.shape[0])).max() < 1e-12
+    # monomial form of the basis agrees with its point values (evaluation off the rule points goes through it)
+    xq = np.zeros((tw.nip, D))
+    x, _ = tw.quadrature()
+    P = mesh.points[mesh.elements[0]]
+    lam = np.linalg.lstsq(np.vstack([P.T, np.ones(D + 1)]), np.vstack([x[0].T, np.ones(tw.nip)]), rcond=None)[0]
+    xq = lam[:D].T
+    assert np.abs(w(0, xq) - got[0]).max() <= 1e-10 * np.abs(got[0]).max()
+    # non-polynomial state: compare with a weighted least-squares projection done in numpy
+    f = standing(D)
+    tw.SetInitial(first_order(f) if fo else f)
+    w2 = tw.GetWave()
+    wf2 = tw.GetWavefront().reshape(mesh.ne, -1, tw.nip)[:, :w2.coef.shape[1], :]
+    sw = np.sqrt(rule_w)
+    ref = np.linalg.lstsq(sw[:, None] * w2.psi_at_points, (sw * wf2).reshape(-1, tw.nip).T, rcond=None)[0]
+    assert np.abs(w2.coef.reshape(-1, ref.shape[0]).T - ref).max() <= 1e-12 * np.abs(ref).max()
+
+
 def test_errors_on_gpu(built):
     from ngstrefftz_b200._capi import NgstError
     mesh = ng.UnitSquareMesh(2)
