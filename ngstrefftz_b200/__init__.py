@@ -214,6 +214,95 @@ class TentSlab:
             self._export = e
         return self._export
 
+    def DrawPitchedTentsVTK(self, filename="output"):
+        """Headless writer of TentPitchedSlab::DrawPitchedTentsVTK (ngstents/src/tents.cpp:982-1058): 2-D meshes, one
+        tetrahedron per (tent, element), point data tentlevel / tentnumber. Writes <filename>.vtk (legacy ASCII)."""
+        mesh = self.mesh
+        if mesh.dim != 2:
+            raise ValueError("DrawPitchedTentsVTK: 2-D meshes only (as the reference)")
+        e = self.export()
+        pts, el2v = mesh.points, mesh.elements
+        P, cells, level, tentnr = [], [], [], []
+        for i in range(len(e["vertex"])):
+            v = int(e["vertex"][i])
+            first = len(P)
+            P.append((pts[v, 0], pts[v, 1], e["tbot"][i]))
+            P.append((pts[v, 0], pts[v, 1], e["ttop"][i]))
+            nb = {int(n): float(t) for n, t in zip(e["nbv"][e["nb_off"][i]:e["nb_off"][i + 1]],
+                                                   e["nbtime"][e["nb_off"][i]:e["nb_off"][i + 1]])}
+            for el in e["els"][e["el_off"][i]:e["el_off"][i + 1]]:
+                tet = [first, first + 1]
+                for w in el2v[el]:
+                    if int(w) != v:
+                        tet.append(len(P))
+                        P.append((pts[w, 0], pts[w, 1], nb[int(w)]))
+                cells.append(tet)
+            n = len(P) - first
+            level += [int(e["level"][i])] * n
+            tentnr += [i] * n
+        with open(filename + ".vtk", "w") as out:
+            out.write("# vtk DataFile Version 3.0\nvtk output\nASCII\nDATASET UNSTRUCTURED_GRID\n")
+            out.write(f"POINTS {len(P)} float\n")
+            out.writelines(f"{x:.9g} {y:.9g} {t:.9g}\n" for x, y, t in P)
+            out.write(f"CELLS {len(cells)} {5 * len(cells)}\n")
+            out.writelines("4 " + " ".join(str(k) for k in c) + "\n" for c in cells)
+            out.write(f"CELL_TYPES {len(cells)}\n" + "10 \n" * len(cells))
+            out.write(f"CELL_DATA {len(cells)}\nPOINT_DATA {len(P)}\nFIELD FieldData 2\n")
+            out.write(f"tentlevel 1 {len(level)} float\n" + " ".join(str(k) for k in level) + " \n")
+            out.write(f"tentnumber 1 {len(tentnr)} float\n" + " ".join(str(k) for k in tentnr) + " \n")
+        return len(P), len(cells)
+
+    # ---- exchange of tent lists with a real NGSTrefftz / ngstents install (SURVEY.md section 8.6 row 1)
+    def save_tents(self, path):
+        """All flattened tent tables (export()) as one .npz; dump_reference_tents() writes the same keys from ngstents."""
+        np.savez_compressed(path, **self.export())
+
+    @staticmethod
+    def dump_reference_tents(ref_slab, path):
+        """Run inside a real ngstents session: ref_slab is ngstents.TentSlab after PitchTents. Flattens
+        GetTent(i).{vertex, ttop, tbot, nbv, nbtime, els, level, internal_facets} (python_tents.cpp:119-128) to the .npz
+        layout of save_tents (no dag / maxslope / level sets: they are derived)."""
+        cols = {k: [] for k in ("vertex", "level", "tbot", "ttop", "nbv", "nbtime", "els", "facets")}
+        off = {"nb_off": [0], "el_off": [0], "facet_off": [0]}
+        for i in range(ref_slab.GetNTents()):
+            t = ref_slab.GetTent(i)
+            cols["vertex"].append(t.vertex)
+            cols["level"].append(t.level)
+            cols["tbot"].append(t.tbot)
+            cols["ttop"].append(t.ttop)
+            cols["nbv"] += list(t.nbv)
+            cols["nbtime"] += list(t.nbtime)
+            cols["els"] += list(t.els)
+            cols["facets"] += list(t.internal_facets)
+            off["nb_off"].append(len(cols["nbv"]))
+            off["el_off"].append(len(cols["els"]))
+            off["facet_off"].append(len(cols["facets"]))
+        out = {k: np.asarray(v, dtype=np.float64 if k in ("tbot", "ttop", "nbtime") else np.int32) for k, v in cols.items()}
+        out.update({k: np.asarray(v, dtype=np.int32) for k, v in off.items()})
+        np.savez_compressed(path, **out)
+
+    def compare_tents(self, path, same_numbering=True):
+        """Compare this slab with a tent dump (save_tents / dump_reference_tents). same_numbering=True: bitwise equality of
+        every shared table (needs identical vertex / element / facet numbering). False: numbering-free invariants only --
+        tent count, level histogram, sorted (tbot, ttop) per level -- for meshes numbered by another program.
+        Returns the list of differing items (empty = match)."""
+        ref = np.load(path)
+        mine = self.export()
+        diffs = []
+        if same_numbering:
+            return [k for k in ref.files if k in mine and not np.array_equal(ref[k], mine[k])]
+        if len(ref["vertex"]) != len(mine["vertex"]):
+            diffs.append("ntents")
+        if not np.array_equal(np.bincount(ref["level"]), np.bincount(mine["level"])):
+            diffs.append("level histogram")
+        else:
+            for name in ("tbot", "ttop"):
+                a = np.lexsort((ref[name], ref["level"]))
+                b = np.lexsort((mine[name], mine["level"]))
+                if not np.allclose(ref[name][a], mine[name][b], rtol=1e-13, atol=1e-15):
+                    diffs.append(name)
+        return diffs
+
     def GetTent(self, i):
         e = self.export()
         if not 0 <= i < len(e["vertex"]):
@@ -459,6 +548,18 @@ class TWaveTents(TrefftzTents):
         return lib.ngst_twave_ntents_fast(self._h)
 
     # ---- DeclareETClass methods (src/twavetents.cpp:1160-1178)
+    def import_reference_wavefront(self, wf, simd_width=None):
+        """A GetWavefront() matrix of the real reference has ncomp * snip columns with snip = nip rounded up to the SIMD
+        width (zero-weight pad points, src/twavetents.cpp:192): drop the pad columns of every component block so that it can
+        be compared with / loaded into this solver (SetInitial). Point ORDER inside a block is NGSolve's."""
+        wf = np.asarray(wf, dtype=float)
+        for ncomp in (self.D + 2, self.D + 1):
+            if wf.shape[1] % ncomp == 0:
+                snip = wf.shape[1] // ncomp
+                if snip >= self.nip and (simd_width is None or snip == -(-self.nip // simd_width) * simd_width):
+                    return np.ascontiguousarray(wf.reshape(len(wf), ncomp, snip)[:, :, :self.nip].reshape(len(wf), -1))
+        raise ValueError("wavefront width does not match (D+1 or D+2) component blocks of >= nip points")
+
     def GetWavefront(self):
         wf = np.zeros((self.nel, self.ncomp * self.nip))
         check(lib.ngst_twave_get_wavefront(self._h, dptr(wf)))

@@ -208,6 +208,24 @@ def test_get_wave_projection(built, D, fo):
     assert np.abs(w2.coef.reshape(-1, ref.shape[0]).T - ref).max() <= 1e-12 * np.abs(ref).max()
 
 
+def test_import_reference_wavefront_drops_simd_padding(built):
+    """The reference's wavefront has snip = nip rounded up to the SIMD width columns per component (twavetents.cpp:192, 741)."""
+    mesh = ng.UnitCubeMesh(2)
+    ts = ng.TentSlab(mesh, "edge")
+    ts.SetMaxWavespeed(1.0)
+    assert ts.PitchTents(0.1, True, 2 / 3)
+    tw = ng.TWave(4, ts, 1.0)
+    tw.SetInitial(standing(3))
+    wf = tw.GetWavefront()
+    assert tw.nip == 125
+    padded = np.zeros((mesh.ne, 5, 128))
+    padded[:, :, :125] = wf.reshape(mesh.ne, 5, 125)
+    padded[:, :, 125:] = padded[:, :, 124:125]  # pad = last point repeated
+    assert np.array_equal(tw.import_reference_wavefront(padded.reshape(mesh.ne, -1), simd_width=4), wf)
+    with pytest.raises(ValueError):
+        tw.import_reference_wavefront(np.zeros((mesh.ne, 7 * 100)))
+
+
 def test_errors_on_gpu(built):
     from ngstrefftz_b200._capi import NgstError
     mesh = ng.UnitSquareMesh(2)
