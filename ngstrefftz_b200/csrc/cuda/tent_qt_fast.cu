@@ -61,7 +61,9 @@ struct QCfg {
   static constexpr int oCm = oBv + NB;
   static constexpr int oAA = oCm + NP;
   static constexpr int oBB = oAA + (P - 1) * (P - 1);
-  static constexpr int nsmem = (oBB + P * P + 1) / 2 * 2;
+  // per-point setup of the volume pass for one super-chunk of 128 points (thread = point): xi[3], 1/c^2, L and R weights
+  static constexpr int oSP = (oBB + P * P + 1) / 2 * 2;
+  static constexpr int nsmem = oSP + 6 * 4 * kChunk;
   static_assert(2 * kBS <= ZS, "general operands must fit in the Z buffer");
   static_assert(NP * LDM + NM * NB <= NP * ZS, "At and T must fit in the Z buffer");
   static_assert(N * LDA <= NP * LDM, "A must fit where At was");
@@ -278,6 +280,7 @@ __global__ void __launch_bounds__(kThreads, P >= 5 ? 2 : 3) tent_kernel_qt_fast(
 #define QB(j) Mq[(size_t)(j) * NB + b]
 #define AAF(x, y) AAs[(x) * (P - 1) + (y)]
 #define BBF(x, y) BBs[(x) * P + (y)]
+    // seeds: function b <-> the b-th monomial (t-exponent 0 or 1) in TraversePol order (t outermost)
     for (int b = tid; b < N; b += kThreads) {
       int cnt = 0;
       for (int t = 0; t < 2; t++)
@@ -286,24 +289,36 @@ __global__ void __launch_bounds__(kThreads, P >= 5 ? 2 : 3) tent_kernel_qt_fast(
             if (cnt == b) QB(IDX3(x, y, t)) = 1.0;
             cnt++;
           }
+    }
+    __syncthreads();
+    // recursion over the total degree ell of (x, y, t): the coefficient of (x, y, t + 2) needs coefficients of lower ell
+    // and, at the same ell, those with t-exponent t (computed from t - 2). Rows t = tp, tp + 1 of one ell are therefore
+    // independent of each other: one thread per (function, t, x) item, a barrier per row pair.
+    {
       const double A0 = AAF(0, 0);
       for (int ell = 0; ell < P - 1; ell++)
-        for (int t = 0; t <= ell; t++)
-          for (int x = 0; x <= ell - t; x++) {
-            const int y = ell - t - x;
-            const double den = (double)((t + 2) * (t + 1)) * A0;
-            double nc = 0.0;
-            for (int bx = 0; bx <= x; bx++)
-              for (int by = 0; by <= y; by++) {
-                nc += (double)((bx + 2) * (bx + 1)) / den * BBF(x - bx, y - by) * QB(IDX3(bx + 2, by, t)) +
-                      (double)((x - bx + 1) * (bx + 1)) / den * BBF(x - bx + 1, y - by) * QB(IDX3(bx + 1, by, t));
-                nc += (double)((by + 2) * (by + 1)) / den * BBF(x - bx, y - by) * QB(IDX3(bx, by + 2, t)) +
-                      (double)((y - by + 1) * (by + 1)) / den * BBF(x - bx, y - by + 1) * QB(IDX3(bx, by + 1, t));
-                if (bx + by == x + y) continue;
-                nc -= AAF(x - bx, y - by) * QB(IDX3(bx, by, t + 2)) / A0;
-              }
-            QB(IDX3(x, y, t + 2)) = nc;
-          }
+        for (int tp = 0; tp <= ell; tp += 2) {
+        const int n0 = ell - tp + 1, n1 = (tp + 1 <= ell) ? ell - tp : 0;
+        for (int it = tid; it < N * (n0 + n1); it += kThreads) {
+          const int b = it % N;
+          const int r = it / N;
+          const int t = tp + (r >= n0 ? 1 : 0);
+          const int x = r - (r >= n0 ? n0 : 0), y = ell - t - x;
+          const double den = (double)((t + 2) * (t + 1)) * A0;
+          double nc = 0.0;
+          for (int bx = 0; bx <= x; bx++)
+            for (int by = 0; by <= y; by++) {
+              nc += (double)((bx + 2) * (bx + 1)) / den * BBF(x - bx, y - by) * QB(IDX3(bx + 2, by, t)) +
+                    (double)((x - bx + 1) * (bx + 1)) / den * BBF(x - bx + 1, y - by) * QB(IDX3(bx + 1, by, t));
+              nc += (double)((by + 2) * (by + 1)) / den * BBF(x - bx, y - by) * QB(IDX3(bx, by + 2, t)) +
+                    (double)((y - by + 1) * (by + 1)) / den * BBF(x - bx, y - by + 1) * QB(IDX3(bx, by + 1, t));
+              if (bx + by == x + y) continue;
+              nc -= AAF(x - bx, y - by) * QB(IDX3(bx, by, t + 2)) / A0;
+            }
+          QB(IDX3(x, y, t + 2)) = nc;
+        }
+        __syncthreads();
+      }
     }
 #undef IDX3
 #undef QB
@@ -409,42 +424,53 @@ __global__ void __launch_bounds__(kThreads, P >= 5 ? 2 : 3) tent_kernel_qt_fast(
   __syncthreads();
   {
     const int Qv = qa.Qv, nvp = nel * 2 * Qv;
-    for (int c0 = 0; c0 < nvp; c0 += kChunk) {
-      const int idx = c0 + lane;
-      const bool valid = idx < nvp;
-      const int idc = valid ? idx : nvp - 1;
-      const int cn = idc / Qv, q = idc % Qv;
-      const double* __restrict__ rec = f.cone + ((size_t)te0 * 2 + cn) * kCS;
-      const double* __restrict__ vx = qa.vxi + (size_t)q * d1;
-      const double v0 = vx[0], v1 = vx[1], v2 = vx[2];
-      double xi[d1], x[D];
+    constexpr int kSuper = 4 * kChunk;
+    double* const sp = sm + C::oSP;
+    for (int s0 = 0; s0 < nvp; s0 += kSuper) {
+      {  // setup, thread = point: the wavespeed polynomial, two divisions and the cone map are evaluated once per point
+        const int idx = s0 + tid;
+        const bool valid = idx < nvp;
+        const int idc = valid ? idx : nvp - 1;
+        const int cn = idc / Qv, q = idc % Qv;
+        const double* __restrict__ rec = f.cone + ((size_t)te0 * 2 + cn) * kCS;
+        const double* __restrict__ vx = qa.vxi + (size_t)q * d1;
+        const double v0 = vx[0], v1 = vx[1], v2 = vx[2];
+        double x[D];
 #pragma unroll
-      for (int r = 0; r < d1; r++) xi[r] = rec[r * d1] * v0 + rec[r * d1 + 1] * v1 + rec[r * d1 + 2] * v2;
+        for (int r = 0; r < d1; r++) sp[r * kSuper + tid] = rec[r * d1] * v0 + rec[r * d1 + 1] * v1 + rec[r * d1 + 2] * v2;
 #pragma unroll
-      for (int d = 0; d < D; d++) x[d] = rec[17 + d] + rec[9 + d * d1] * v0 + rec[9 + d * d1 + 1] * v1 + rec[9 + d * d1 + 2] * v2;
-      const double cc = qt_poly_eval(qa, x);
-      const double inv = 1.0 / (cc * cc);
-      const double lw = valid ? rec[15] * qa.vw[q] * sc * sc : 0.0;
-      const double mu = rec[16] / inv * sc * sc;
-      Pw<P> pw;
-      pw.set(xi);
-      double* const zl = ZL + lane;
-      double* const zr = ZR + lane;
-      mono_rows_w<P>(w, [&](auto jc) {
-        constexpr int j = decltype(jc)::value;
-        double dt, box;
-        mono_box<P, j>(pw, inv, dt, box);
-        zl[j * kBS] = lw * box;
-        zr[j * kBS] = fma(mu, box, sc * dt);
-      });
-      __syncthreads();
-      switch (w) {
-        case 0: dmma_full<NT, NACC, 0>(accf, ZL, ZR, g, k); break;
-        case 1: dmma_full<NT, NACC, 1>(accf, ZL, ZR, g, k); break;
-        case 2: dmma_full<NT, NACC, 2>(accf, ZL, ZR, g, k); break;
-        default: dmma_full<NT, NACC, 3>(accf, ZL, ZR, g, k); break;
+        for (int d = 0; d < D; d++) x[d] = rec[17 + d] + rec[9 + d * d1] * v0 + rec[9 + d * d1 + 1] * v1 + rec[9 + d * d1 + 2] * v2;
+        const double cc = qt_poly_eval(qa, x);
+        const double inv = 1.0 / (cc * cc);
+        sp[3 * kSuper + tid] = inv;
+        sp[4 * kSuper + tid] = valid ? rec[15] * qa.vw[q] * sc * sc : 0.0;
+        sp[5 * kSuper + tid] = rec[16] / inv * sc * sc;
       }
       __syncthreads();
+      for (int sub = 0; sub < kSuper / kChunk && s0 + sub * kChunk < nvp; sub++) {
+        const double* __restrict__ spl = sp + sub * kChunk + lane;
+        const double xi[d1] = {spl[0], spl[kSuper], spl[2 * kSuper]};
+        const double inv = spl[3 * kSuper], lw = spl[4 * kSuper], mu = spl[5 * kSuper];
+        Pw<P> pw;
+        pw.set(xi);
+        double* const zl = ZL + lane;
+        double* const zr = ZR + lane;
+        mono_rows_w<P>(w, [&](auto jc) {
+          constexpr int j = decltype(jc)::value;
+          double dt, box;
+          mono_box<P, j>(pw, inv, dt, box);
+          zl[j * kBS] = lw * box;
+          zr[j * kBS] = fma(mu, box, sc * dt);
+        });
+        __syncthreads();
+        switch (w) {
+          case 0: dmma_full<NT, NACC, 0>(accf, ZL, ZR, g, k); break;
+          case 1: dmma_full<NT, NACC, 1>(accf, ZL, ZR, g, k); break;
+          case 2: dmma_full<NT, NACC, 2>(accf, ZL, ZR, g, k); break;
+          default: dmma_full<NT, NACC, 3>(accf, ZL, ZR, g, k); break;
+        }
+        __syncthreads();
+      }
     }
   }
 
