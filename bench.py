@@ -365,9 +365,9 @@ def run_ours(args):
             traffic = None
     # executed tensor-path work of tent_kernel_fast: symmetric rank-k updates touch only the NT(NT+1)/2 upper-triangular
     # 8x8 tiles; (D+1) k-rows per top-face point, 1 per bottom-face point (second-order form), 4 k-rows per DMMA. The
-    # top-face Gram runs on the rule of order 2p-2 (Qt = p^D points, exact for its integrand; tent_fast.cu Cfg::QT)
+    # top-face Gram runs on a compact rule exact to degree 2p-2 (24 points at D=3, p=4; tent_fast.cu Cfg::QT)
     nt_tiles = (N + 7) // 8
-    Qt = order ** D
+    Qt = {(3, 4): 24, (3, 3): 14, (3, 2): 4}.get((D, order), order ** D)  # compact rule exact to degree 2p-2 (quadrature.hpp)
     dmma_el = (Qt * (D + 1) / 4.0 + (0 if tw.fosystem else Q / 4.0)) * (nt_tiles * (nt_tiles + 1) / 2) * 512.0
     dmma_tf = dmma_el * float(nels.sum()) * args.steps / (float(np.sum(dev_ms)) * 1e-3) * 1e-12
     roofline = {"bound": "fp64", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach_tf / fp64_peak,

@@ -177,6 +177,9 @@ int ngst_device_fp64_peak(int device, int which, double* tflops);
 /* host-only helpers exposed for tests (no device needed) */
 int ngst_basis(int D, int order, int fowave, int* sizes, int* rowptr, int* col, double* val, int* expo);
 int ngst_rule(int dim, int order, int* nip, double* xi, double* w);
+/* compact fully symmetric rule exact to `degree` (top-face Gram of the fast kernel; no reference counterpart); falls back
+ * to ngst_rule(dim, degree) where no table exists */
+int ngst_compact_rule(int dim, int degree, int* nip, double* xi, double* w);
 
 #ifdef __cplusplus
 }

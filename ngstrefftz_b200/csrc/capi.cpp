@@ -432,4 +432,13 @@ int ngst_rule(int dim, int order, int* nip, double* xi, double* w) {
   });
 }
 
+int ngst_compact_rule(int dim, int degree, int* nip, double* xi, double* w) {
+  return guarded([&] {
+    SimplexRule r;
+    try { r = make_compact_rule(dim, degree); } catch (const std::runtime_error& e) { throw std::invalid_argument(e.what()); }
+    if (nip) *nip = r.nip;
+    copy_out(xi, r.xi); copy_out(w, r.w);
+  });
+}
+
 }  // extern "C"

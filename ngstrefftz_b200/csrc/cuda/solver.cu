@@ -127,8 +127,8 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
     fargs_.ff = Upload(fstage_.ff);
     fargs_.sqrtw = Upload(fstage_.sqrtw);
     {
-      // top-face Gram: rule of order 2p-2 (exact for the degree-(2p-2) integrand, tent_fast.cu Cfg::QT)
-      const SimplexRule rt = make_simplex_rule(D, 2 * order - 2);
+      // top-face Gram: compact rule exact to degree 2p-2 (the degree of the integrand, tent_fast.cu Cfg::QT)
+      const SimplexRule rt = make_compact_rule(D, 2 * order - 2);
       std::vector<double> lt((size_t)rt.nip * d1), sw(rt.nip);
       for (int q = 0; q < rt.nip; q++) {
         double s = 0;

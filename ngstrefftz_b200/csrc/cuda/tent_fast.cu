@@ -18,6 +18,7 @@
 // Tents with material interfaces (ndomains > 1) are routed to the generic kernel by the host.
 #include <cuda_runtime.h>
 
+#include "../host/quadrature.hpp"
 #include "basis_eval_gen.cuh"
 #include "dmma_tiles.cuh"
 #include "tent_solve.cuh"
@@ -40,9 +41,11 @@ struct Cfg {
   static constexpr int NP = NT * 8;               // padded system size
   static constexpr int G = NP / 4;                // functions per evaluation group (function i -> group i % 4)
   static constexpr int Q = (D == 1) ? (P + 1) : ipow(P + 1, D);  // points of the order-2P rule (quadrature.cpp)
-  // The top-face Gram integrand (B L)(B L)^T is a polynomial of degree 2P-2 on the (affine) face: the rule of order
-  // 2P-2 (P points per direction) integrates it exactly, i.e. gives the order-2P rule's matrix up to round-off.
-  static constexpr int QT = (D == 1) ? P : ipow(P, D);
+  // The top-face Gram integrand (B L)(B L)^T is a polynomial of degree 2P-2 on the (affine) face: any rule exact to that
+  // degree gives the order-2P rule's matrix up to round-off. Compact symmetric rule where the table has one (24 points
+  // at D = 3, P = 4 instead of the 64 of the Duffy rule of order 2P-2 and the 125 of order 2P), else the Duffy rule.
+  static constexpr int QTD = (D == 1) ? P : ipow(P, D);
+  static constexpr int QT = compact_rule_points(D, 2 * P - 2) > 0 ? compact_rule_points(D, 2 * P - 2) : QTD;
   static constexpr int ZS = kChunk * d1 + 4;      // row stride of Z: == 4 (mod 16) -> conflict-free fragment loads
   static constexpr int LDA = NP + 1;
   static constexpr int NSYM = NT * (NT + 1) / 2;  // upper-triangular tiles

@@ -136,4 +136,34 @@ SimplexRule make_simplex_rule(int dim, int order) {
   return r;
 }
 
+namespace {
+struct CompactRuleTable {
+  int dim, degree, n;
+  std::vector<double> bary;  // n * (dim + 1)
+  std::vector<double> w;     // n
+};
+const std::vector<CompactRuleTable>& compact_tables() {
+  static const std::vector<CompactRuleTable> t = {
+#include "compact_rules.inc"
+  };
+  return t;
+}
+}  // namespace
+
+SimplexRule make_compact_rule(int dim, int degree) {
+  for (const CompactRuleTable& t : compact_tables())
+    if (t.dim == dim && t.degree == degree) {
+      if (t.n != compact_rule_points(dim, degree) || (int)t.w.size() != t.n || (int)t.bary.size() != t.n * (dim + 1))
+        throw std::runtime_error("make_compact_rule: table does not match compact_rule_points");
+      SimplexRule r;
+      r.dim = dim;
+      r.nip = t.n;
+      r.w = t.w;
+      for (int q = 0; q < t.n; q++)
+        for (int d = 0; d < dim; d++) r.xi.push_back(t.bary[(size_t)q * (dim + 1) + d]);
+      return r;
+    }
+  return make_simplex_rule(dim, degree);
+}
+
 }  // namespace ngst

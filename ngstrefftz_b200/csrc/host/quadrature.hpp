@@ -25,4 +25,19 @@ void gauss_jacobi01(int n, int alpha, std::vector<double>& x, std::vector<double
 
 SimplexRule make_simplex_rule(int dim, int order);
 
+// Points of the compact rule make_compact_rule(dim, degree) returns, or 0 when the table has none (then the Duffy rule of
+// that order is used). constexpr: the fast tent kernel sizes its top-face pass with it at compile time.
+constexpr int compact_rule_points(int dim, int degree) {
+  if (dim == 2) return degree == 4 ? 6 : degree == 6 ? 12 : degree == 8 ? 16 : degree == 10 ? 25 : 0;
+  if (dim == 3) return degree == 2 ? 4 : degree == 4 ? 14 : degree == 6 ? 24 : 0;
+  return 0;
+}
+
+// Fully symmetric interior rule with positive weights that integrates polynomials of total degree <= `degree` exactly with
+// (near-)minimal point count (tables generated and verified by scripts/gen_compact_rules.py: 24 points for degree 6 on the
+// tetrahedron where the Duffy rule has 64). Not a reference rule: used only where the integrand is a polynomial of known
+// degree (top-face Gram of the fast kernel), so the result equals the reference's up to round-off. Falls back to
+// make_simplex_rule(dim, degree) when the table has no entry.
+SimplexRule make_compact_rule(int dim, int degree);
+
 }  // namespace ngst

@@ -92,3 +92,26 @@ def test_rule_matches_scipy_and_integrates_exactly(built, dim, order):
         exact = math.prod(math.factorial(k) for k in e) / math.factorial(dim + sum(e))
         got = (w * np.prod(xi ** np.array(e), axis=1)).sum()
         assert abs(got - exact) < 1e-14, (e, got, exact)
+
+
+@pytest.mark.parametrize("dim,degree,npts", [(2, 4, 6), (2, 6, 12), (2, 8, 16), (2, 10, 25), (3, 2, 4), (3, 4, 14), (3, 6, 24)])
+def test_compact_rules_are_exact_positive_and_interior(built, dim, degree, npts):
+    """Compact symmetric rules of the fast kernel's top-face Gram (scripts/gen_compact_rules.py): exact for every monomial
+    of total degree <= degree (integral of lambda^alpha = alpha! / (|alpha| + dim)!), positive weights, interior points."""
+    import itertools
+    import math
+    from ngstrefftz_b200._capi import C, check, dptr, lib
+    n = C.c_int(0)
+    check(lib.ngst_compact_rule(dim, degree, C.byref(n), None, None))
+    assert n.value == npts
+    xi, w = np.zeros((npts, dim)), np.zeros(npts)
+    check(lib.ngst_compact_rule(dim, degree, C.byref(n), dptr(xi), dptr(w)))
+    lam = np.hstack([xi, 1 - xi.sum(axis=1, keepdims=True)])
+    assert w.min() > 0 and lam.min() > 1e-3
+    for alpha in itertools.product(range(degree + 1), repeat=dim + 1):
+        if sum(alpha) <= degree:
+            exact = math.prod(math.factorial(a) for a in alpha) / math.factorial(sum(alpha) + dim)
+            assert abs(np.sum(w * np.prod(lam ** np.array(alpha), axis=1)) - exact) <= 1e-13 * exact
+    # no table: falls back to the Duffy rule of that order
+    check(lib.ngst_compact_rule(3, 8, C.byref(n), None, None))
+    assert n.value == 125
