@@ -140,6 +140,20 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
       fargs_.sqrtw_top = Upload(sw);
       fargs_.Qt = rt.nip;
     }
+    if (compact_rule_points(D, 2 * order) > 0) {
+      // stabilisation Gram of the bottom faces (degree 2p): compact rule in a pass of its own (tent_fast.cu Cfg::QS)
+      const SimplexRule rs = make_compact_rule(D, 2 * order);
+      std::vector<double> ls((size_t)rs.nip * d1), sw(rs.nip);
+      for (int q = 0; q < rs.nip; q++) {
+        double s = 0;
+        for (int d = 0; d < D; d++) { ls[(size_t)q * d1 + d] = rs.xi[(size_t)q * D + d]; s += rs.xi[(size_t)q * D + d]; }
+        ls[(size_t)q * d1 + D] = 1.0 - s;
+        sw[q] = std::sqrt(rs.w[q]);
+      }
+      fargs_.lam_stab = Upload(ls);
+      fargs_.sqrtw_stab = Upload(sw);
+      fargs_.Qs = rs.nip;
+    }
     fargs_.dmap = Upload(fstage_.dmap);
     fargs_.dfac = Upload(fstage_.dfac);
     for (int f = 0; f < 2; f++) {

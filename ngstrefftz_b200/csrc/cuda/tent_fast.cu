@@ -46,6 +46,10 @@ struct Cfg {
   // at D = 3, P = 4 instead of the 64 of the Duffy rule of order 2P-2 and the 125 of order 2P), else the Duffy rule.
   static constexpr int QTD = (D == 1) ? P : ipow(P, D);
   static constexpr int QT = compact_rule_points(D, 2 * P - 2) > 0 ? compact_rule_points(D, 2 * P - 2) : QTD;
+  // Likewise the bottom-face stabilisation Gram S diag(w) S^T (degree 2P): compact rule of degree 2P in a pass of its
+  // own where the table has one (the right-hand side keeps the order-2P rule: it contains the sampled state)
+  static constexpr int QS = compact_rule_points(D, 2 * P);
+  static constexpr bool splitStab = !FO && QS > 0 && QS < Q;
   static constexpr int ZS = kChunk * d1 + 4;      // row stride of Z: == 4 (mod 16) -> conflict-free fragment loads
   static constexpr int LDA = NP + 1;
   static constexpr int NSYM = NT * (NT + 1) / 2;  // upper-triangular tiles
@@ -226,9 +230,43 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
 #pragma unroll
       for (int u = 0; u < d1; u++) r = fma(dv[u], rho[u], r);
       bpart[i >> 2] += r;
-      if (!FO) zl[i * ZS] = sqo * v;
+      if (!FO && !C::splitStab) zl[i * ZS] = sqo * v;
     });
-    if (!FO) {
+    if (!FO && !C::splitStab) {
+      __syncthreads();
+      if (th == 0) dmma_sym<NT, NACC, 0>(acc, Z, ZS, kChunk / 4, kh, g, k);
+      else dmma_sym<NT, NACC, 1>(acc, Z, ZS, kChunk / 4, kh, g, k);
+      __syncthreads();
+    }
+  }
+  if (C::splitStab) {
+    // ---------------------------------------------------------------- stabilisation Gram on the compact degree-2P rule
+    constexpr int QS = C::QS;
+    const int npss = nel * QS;
+    __syncthreads();  // the top-face pass has released Z; the right-hand-side pass above does not touch it
+    for (int c0 = 0; c0 < npss; c0 += kChunk) {
+      const int idx = c0 + lane;
+      const bool valid = idx < npss;
+      const int idc = valid ? idx : npss - 1;
+      const int te = te0 + idc / QS, q = idc % QS;
+      const double* __restrict__ rec = f.fe + (size_t)te * FE;
+      const double* __restrict__ lm = f.lam_stab + q * d1;
+      double xi[d1];
+#pragma unroll
+      for (int u = 0; u < d1; u++) xi[u] = 0.0;
+#pragma unroll
+      for (int kk = 0; kk < d1; kk++) {
+        const double l = lm[kk];
+#pragma unroll
+        for (int u = 0; u < D; u++) xi[u] = fma(l, rec[fast_fe_xv(D) + kk * D + u], xi[u]);
+        xi[D] = fma(l, rec[fast_fe_tb(D) + kk], xi[D]);
+      }
+      const double sqo = valid ? f.sqrtw_stab[q] * rec[fast_fe_bot(D) + 1] : 0.0;
+      double* const zl = Z + lane;
+      eval_group<D, P, FO>(w, xi, [&](auto ic, double v, double, double, double, double) {
+        constexpr int i = decltype(ic)::value;
+        zl[i * ZS] = sqo * v;
+      });
       __syncthreads();
       if (th == 0) dmma_sym<NT, NACC, 0>(acc, Z, ZS, kChunk / 4, kh, g, k);
       else dmma_sym<NT, NACC, 1>(acc, Z, ZS, kChunk / 4, kh, g, k);
@@ -421,6 +459,7 @@ template <int D, int P, int FO>
 cudaError_t launch_cfg(const TentKernelArgs& a, const FastArgs& f, cudaStream_t stream) {
   using C = Cfg<D, P, FO>;
   if (a.Q != C::Q || f.Qt != C::QT || a.N != C::N || a.npoly != C::npoly) return cudaErrorInvalidValue;
+  if (C::splitStab && f.Qs != C::QS) return cudaErrorInvalidValue;
   const size_t smem = sizeof(double) * C::nsmem;
   static bool configured = false;  // per instantiation
   if (!configured) {

@@ -39,6 +39,10 @@ struct FastArgs {
   const double* lam_top;    // Qt * (D+1) barycentric coordinates
   const double* sqrtw_top;  // Qt
   int Qt;
+  // compact rule exact to degree 2p for the bottom-face stabilisation Gram (second-order form), when the table has one
+  const double* lam_stab;   // Qs * (D+1)
+  const double* sqrtw_stab; // Qs
+  int Qs;
   // column-compressed basis matrix (monomial j -> functions), for sol -> monomial coefficients
   const int* cptr;      // npoly + 1
   const int* crow;      // nnz
