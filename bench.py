@@ -367,8 +367,12 @@ def run_ours(args):
     # 8x8 tiles; (D+1) k-rows per top-face point, 1 per bottom-face point (second-order form), 4 k-rows per DMMA. The
     # top-face Gram runs on a compact rule exact to degree 2p-2 (24 points at D=3, p=4; tent_fast.cu Cfg::QT)
     nt_tiles = (N + 7) // 8
-    Qt = {(3, 4): 24, (3, 3): 14, (3, 2): 4}.get((D, order), order ** D)  # compact rule exact to degree 2p-2 (quadrature.hpp)
-    dmma_el = (Qt * (D + 1) / 4.0 + (0 if tw.fosystem else Q / 4.0)) * (nt_tiles * (nt_tiles + 1) / 2) * 512.0
+    n_rule = _capi.C.c_int(0)
+    check(lib.ngst_compact_rule(D, 2 * order - 2, _capi.C.byref(n_rule), None, None))
+    Qt = n_rule.value   # top-face Gram: compact rule exact to degree 2p-2 (24 points at D=3, p=4; tent_fast.cu Cfg::QT)
+    check(lib.ngst_compact_rule(D, 2 * order, _capi.C.byref(n_rule), None, None))
+    Qs = n_rule.value   # stabilisation Gram: compact rule exact to degree 2p where the table has one, else the order-2p rule
+    dmma_el = (Qt * (D + 1) / 4.0 + (0 if tw.fosystem else Qs / 4.0)) * (nt_tiles * (nt_tiles + 1) / 2) * 512.0
     dmma_tf = dmma_el * float(nels.sum()) * args.steps / (float(np.sum(dev_ms)) * 1e-3) * 1e-12
     roofline = {"bound": "fp64", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach_tf / fp64_peak,
                 "traffic": traffic, "kernel": tw.kernel_name(),
