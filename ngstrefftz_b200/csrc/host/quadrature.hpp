@@ -29,7 +29,7 @@ SimplexRule make_simplex_rule(int dim, int order);
 // that order is used). constexpr: the fast tent kernel sizes its top-face pass with it at compile time.
 constexpr int compact_rule_points(int dim, int degree) {
   if (dim == 2) return degree == 4 ? 6 : degree == 6 ? 12 : degree == 8 ? 16 : degree == 10 ? 25 : 0;
-  if (dim == 3) return degree == 2 ? 4 : degree == 4 ? 14 : degree == 6 ? 24 : 0;
+  if (dim == 3) return degree == 2 ? 4 : degree == 4 ? 14 : degree == 6 ? 24 : degree == 8 ? 46 : 0;
   return 0;
 }
 

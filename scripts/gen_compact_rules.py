@@ -129,6 +129,70 @@ def solve(dim, degree, orbits, seed=0, tries=400):
     return best[1], best[2]
 
 
+def duffy_rule(dim, n):
+    """dense positive reference rule (Duffy-collapsed Gauss-Jacobi, n points per direction) used only to orthonormalise"""
+    from scipy.special import roots_jacobi
+    pts, wts = [np.zeros(0)], np.ones(1)
+    pts = np.zeros((1, 0))
+    scale = np.ones(1)
+    for k in range(dim):
+        x, w = roots_jacobi(n, dim - 1 - k, 0)
+        x, w = (x + 1) / 2, w / 2 ** (dim - k)
+        newp = np.concatenate([np.repeat(pts, n, axis=0), (np.tile(x, len(pts)) * np.repeat(scale, n))[:, None]], axis=1)
+        wts = np.repeat(wts, n) * np.tile(w, len(pts))
+        scale = np.repeat(scale, n) * (1 - np.tile(x, len(pts)))
+        pts = newp
+    return np.hstack([pts, 1 - pts.sum(axis=1, keepdims=True)]), wts
+
+
+def solve_conditioned(dim, degree, orbits, seed=0, tries=400):
+    """As solve(), for larger systems: the invariant polynomials are orthonormalised in the inner product of a dense exact
+    rule (well-conditioned moment equations), the unknowns are box-constrained to interior points / positive weights, and
+    the result is polished by minimum-norm Gauss-Newton steps."""
+    inv = invariants(dim, degree)
+
+    def invmat(pts):
+        es = elem_sym(pts)
+        return np.stack([np.prod([es[k] ** e for k, e in enumerate(ex)], axis=0) for ex in inv], axis=1)
+
+    lam, w = duffy_rule(dim, degree)
+    R = np.linalg.qr(np.sqrt(w)[:, None] * invmat(lam))[1]
+    Rinv = np.linalg.inv(R)
+    tgt = (w @ invmat(lam)) @ Rinv
+
+    def resid(x):
+        pts, wts = build(dim, orbits, x)
+        return (wts @ invmat(pts)) @ Rinv - tgt
+
+    lo, hi = [], []
+    for kind in orbits:
+        lo += {"c": [], "a": [0.01], "aabb": [0.01], "ab": [0.01, 0.01]}[kind] + [1e-6]
+        hi += {"c": [], "a": [1.0 / dim - 0.003], "aabb": [0.49], "ab": [0.49, 0.97]}[kind] + [0.1]
+    lo, hi = np.array(lo), np.array(hi)
+    rng = np.random.default_rng(seed)
+    npts = sum(len(orbit_points(dim, k, [0.1, 0.23][:NPAR[k]])) for k in orbits)
+    for _ in range(tries):
+        x0 = rng.uniform(lo, hi)
+        r = least_squares(resid, x0, bounds=(lo, hi), xtol=1e-15, ftol=1e-15, gtol=1e-15, max_nfev=300)
+        if np.abs(r.fun).max() > 1e-11:
+            continue
+        x = r.x
+        for _it in range(6):
+            r0 = resid(x)
+            J = np.zeros((len(r0), len(x)))
+            for k in range(len(x)):
+                h = 1e-6 * max(abs(x[k]), 1e-3)
+                xp, xm = x.copy(), x.copy()
+                xp[k] += h
+                xm[k] -= h
+                J[:, k] = (resid(xp) - resid(xm)) / (2 * h)
+            x = x - np.linalg.lstsq(J, r0, rcond=None)[0]
+        pts, wts = build(dim, orbits, x)
+        if wts.min() > 0 and pts.min() > 5e-3 and len(np.unique(np.round(pts, 8), axis=0)) == npts == len(pts):
+            return pts, wts
+    raise RuntimeError(f"no rule found for dim {dim} degree {degree} orbits {orbits}")
+
+
 def verify(dim, degree, pts, wts):
     worst = 0.0
     for alpha in itertools.product(range(degree + 1), repeat=dim + 1):
@@ -148,12 +212,13 @@ RULES = [  # (dim, degree, orbits)
     (3, 2, ["a"]),                                     # 4
     (3, 4, ["a", "a", "aabb"]),                        # 14 (exact to degree 5)
     (3, 6, ["a", "a", "a", "ab"]),                     # 24
+    (3, 8, ["a", "a", "a", "a", "aabb", "ab", "ab"]),  # 46 (one free parameter; solve_conditioned)
 ]
 
 if __name__ == "__main__":
     print("// generated by scripts/gen_compact_rules.py -- do not edit. {dim, degree, npoints, barycentric points..., weights...}")
     for dim, degree, orbits in RULES:
-        pts, wts = solve(dim, degree, orbits)
+        pts, wts = solve_conditioned(dim, degree, orbits) if (dim, degree) == (3, 8) else solve(dim, degree, orbits)
         err = verify(dim, degree, pts, wts)
         assert err < 5e-14, (dim, degree, err)
         print(f"// dim {dim} degree {degree}: {len(wts)} points, orbits {'+'.join(orbits)}, max rel. moment error {err:.1e}, "

@@ -94,7 +94,7 @@ def test_rule_matches_scipy_and_integrates_exactly(built, dim, order):
         assert abs(got - exact) < 1e-14, (e, got, exact)
 
 
-@pytest.mark.parametrize("dim,degree,npts", [(2, 4, 6), (2, 6, 12), (2, 8, 16), (2, 10, 25), (3, 2, 4), (3, 4, 14), (3, 6, 24)])
+@pytest.mark.parametrize("dim,degree,npts", [(2, 4, 6), (2, 6, 12), (2, 8, 16), (2, 10, 25), (3, 2, 4), (3, 4, 14), (3, 6, 24), (3, 8, 46)])
 def test_compact_rules_are_exact_positive_and_interior(built, dim, degree, npts):
     """Compact symmetric rules of the fast kernel's top-face Gram (scripts/gen_compact_rules.py): exact for every monomial
     of total degree <= degree (integral of lambda^alpha = alpha! / (|alpha| + dim)!), positive weights, interior points."""
@@ -113,5 +113,5 @@ def test_compact_rules_are_exact_positive_and_interior(built, dim, degree, npts)
             exact = math.prod(math.factorial(a) for a in alpha) / math.factorial(sum(alpha) + dim)
             assert abs(np.sum(w * np.prod(lam ** np.array(alpha), axis=1)) - exact) <= 1e-13 * exact
     # no table: falls back to the Duffy rule of that order
-    check(lib.ngst_compact_rule(3, 8, C.byref(n), None, None))
-    assert n.value == 125
+    check(lib.ngst_compact_rule(3, 10, C.byref(n), None, None))
+    assert n.value == 216
