@@ -65,7 +65,10 @@ struct Cfg {
   static constexpr int oB = aliasA ? oZ + NP * ZS : oA + NP * LDA;
   static constexpr int oCM = (oB + NP + 1) / 2 * 2;
   static constexpr int oCMD = oCM + npoly;
-  static constexpr int nsmem = oCMD + d1 * npm1;
+  // right-hand side of the bottom faces when it is computed in a pass of its own (rhsFirst)
+  static constexpr bool rhsFirst = FO || splitStab;
+  static constexpr int oRHS = (oCMD + d1 * npm1 + 1) / 2 * 2;
+  static constexpr int nsmem = oRHS + (rhsFirst ? NP : 0);
   static_assert(2 * kBS <= ZS, "boundary operands must fit in the Z buffer");
   static_assert(NT >= 2 && (NT * NT + 3) / 4 <= NACC, "accumulator budget");
 };
@@ -122,6 +125,108 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
   const int npts = nel * Q;
   const int nptt = nel * QT;
 
+  if (C::rhsFirst) {
+    // ---------------------------------------------------------------- bottom faces: right-hand side  (twavetents.cpp:209-267)
+    // No Gram is fused into this pass (first-order form, or the stabilisation Gram runs on its compact rule), so it needs
+    // no operand buffer and no barrier: warp w takes the chunks w, w + 4, .. and evaluates ALL functions at its 32 points
+    // (per-point setup and shared monomials once per point instead of once per warp). It runs first: the Gram
+    // accumulators are not live yet, the partial sums of all N functions fit in registers.
+    constexpr int NC = FO ? d1 : d1 + 1;
+    // H = 2 (larger bases): a warp evaluates one half of the functions (groups 2h, 2h + 1) on every second chunk, which
+    // keeps the partial sums and the live monomials within the 168-register budget of three CTAs per SM
+    constexpr int H = (NP > 32) ? 2 : 1;
+    constexpr int NS = 4 / H;          // chunk streams
+    constexpr int NB = NP / H;         // partial sums per lane
+    const int part = w % H, cs = w / H;
+    double bp[NB];
+#pragma unroll
+    for (int i = 0; i < NB; i++) bp[i] = 0.0;
+    double gnext[NC];
+    {
+      const int idc = min(cs * kChunk + lane, npts - 1);
+      const double* __restrict__ wf = a.wavefront + (size_t)a.te_el[te0 + idc / Q] * (NC * Q) + idc % Q;
+#pragma unroll
+      for (int cc = 0; cc < NC; cc++) gnext[cc] = __ldcg(wf + cc * Q);  // L2: rows written by other SMs
+    }
+    for (int c0 = cs * kChunk; c0 < npts; c0 += NS * kChunk) {
+      const int idx = c0 + lane;
+      const bool valid = idx < npts;
+      const int idc = valid ? idx : npts - 1;
+      const int te = te0 + idc / Q, q = idc % Q;
+      double gcur[NC];
+#pragma unroll
+      for (int cc = 0; cc < NC; cc++) gcur[cc] = gnext[cc];
+      if (c0 + NS * kChunk < npts) {
+        const int idn = min(idx + NS * kChunk, npts - 1);
+        const double* __restrict__ wf = a.wavefront + (size_t)a.te_el[te0 + idn / Q] * (NC * Q) + idn % Q;
+#pragma unroll
+        for (int cc = 0; cc < NC; cc++) gnext[cc] = __ldcg(wf + cc * Q);
+      }
+      const double* __restrict__ rec = f.fe + (size_t)te * FE;
+      const double* __restrict__ lm = a.lam + q * d1;
+      double xi[d1];
+#pragma unroll
+      for (int u = 0; u < d1; u++) xi[u] = 0.0;
+#pragma unroll
+      for (int kk = 0; kk < d1; kk++) {
+        const double l = lm[kk];
+#pragma unroll
+        for (int u = 0; u < D; u++) xi[u] = fma(l, rec[fast_fe_xv(D) + kk * D + u], xi[u]);
+        xi[D] = fma(l, rec[fast_fe_tb(D) + kk], xi[D]);
+      }
+      const double area = rec[fast_fe_bot(D)];
+      const double* __restrict__ nn = rec + fast_fe_bot(D) + 2;
+      const double s = rec[fast_fe_sc(D)], sc = rec[fast_fe_sc(D) + 1], ic2 = rec[fast_fe_sc(D) + 2];
+      const double om = valid ? a.w[q] * area : 0.0;
+      const double gt = gcur[(FO ? 0 : 1) + D];
+      double rho[d1];
+      double ndg = 0.0;
+#pragma unroll
+      for (int u = 0; u < D; u++) {
+        const double gx = gcur[(FO ? 0 : 1) + u];
+        rho[u] = -om * s * (nn[D] * gx - nn[u] * gt);
+        ndg = fma(nn[u], gx, ndg);
+      }
+      rho[D] = -om * sc * (nn[D] * ic2 * gt - ndg);
+      const double rho_u = FO ? 0.0 : om * gcur[0];
+      auto fn = [&](auto ic, double v, double e0, double e1, double e2, double e3) {
+        constexpr int i = decltype(ic)::value;
+        const double dv[4] = {e0, e1, e2, e3};
+        double r = FO ? 0.0 : v * rho_u;
+#pragma unroll
+        for (int u = 0; u < d1; u++) r = fma(dv[u], rho[u], r);
+        bp[H == 1 ? i : ((i >> 2) * 2 + (i & 1))] += r;   // H == 2: function i = 4 m + 2 part + b -> slot 2 m + b
+      };
+      if (H == 1) {
+        gen::BasisGroup<D, P, FO, 0>::eval(xi, fn);
+        gen::BasisGroup<D, P, FO, 1>::eval(xi, fn);
+        gen::BasisGroup<D, P, FO, 2>::eval(xi, fn);
+        gen::BasisGroup<D, P, FO, 3>::eval(xi, fn);
+      } else if (part == 0) {
+        gen::BasisGroup<D, P, FO, 0>::eval(xi, fn);
+        gen::BasisGroup<D, P, FO, 1>::eval(xi, fn);
+      } else {
+        gen::BasisGroup<D, P, FO, 2>::eval(xi, fn);
+        gen::BasisGroup<D, P, FO, 3>::eval(xi, fn);
+      }
+    }
+#pragma unroll
+    for (int sl = 0; sl < NB; sl++) {
+      double v = bp[sl];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      const int i = (H == 1) ? sl : ((sl >> 1) * 4 + 2 * part + (sl & 1));
+      if (lane == 0) Z[cs * NP + i] = v;
+    }
+    __syncthreads();
+    for (int i = tid; i < NP; i += kThreads) {
+      double v = 0.0;
+#pragma unroll
+      for (int c = 0; c < NS; c++) v += Z[c * NP + i];
+      sm[C::oRHS + i] = v;
+    }
+    __syncthreads();
+  }
   for (int i = tid; i < NP * ZS; i += kThreads) Z[i] = 0.0;  // rows of the padding functions stay zero
   double acc[NACC][2];
 #pragma unroll
@@ -174,13 +279,13 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
   // the state values of the next chunk are loaded one iteration ahead (HBM/L2 latency hidden behind the evaluation)
   constexpr int NC = FO ? d1 : d1 + 1;
   double gnext[NC];
-  {
+  if (!C::rhsFirst) {
     const int idc = min(lane, npts - 1);
     const double* __restrict__ wf = a.wavefront + (size_t)a.te_el[te0 + idc / Q] * (NC * Q) + idc % Q;
 #pragma unroll
     for (int cc = 0; cc < NC; cc++) gnext[cc] = __ldcg(wf + cc * Q);  // L2: rows written by other SMs
   }
-  for (int c0 = 0; c0 < npts; c0 += kChunk) {
+  for (int c0 = 0; c0 < npts && !C::rhsFirst; c0 += kChunk) {
     const int idx = c0 + lane;
     const bool valid = idx < npts;
     const int idc = valid ? idx : npts - 1;
@@ -377,7 +482,7 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
     double v = bpart[j];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0) bv[4 * j + w] = v;
+    if (lane == 0) bv[4 * j + w] = C::rhsFirst ? v + sm[C::oRHS + 4 * j + w] : v;
   }
   __syncthreads();
   // ------------------------------------------------------------------ Solve (64-70 forms the inverse with LAPACK)
