@@ -48,6 +48,8 @@ def parse():
     ap.add_argument("--partition", default="balanced", choices=["balanced", "brick"],
                     help="N>1: cost-balanced recursive bisection (default) or plain brick cut of the bounding box")
     ap.add_argument("--no-overlap", action="store_true", help="N>1: exchange after each level instead of overlapped")
+    ap.add_argument("--level-launches", action="store_true",
+                    help="N=1: always one launch per tent level (profiling; default: automatic, see DESIGN.md section 4.5)")
     ap.add_argument("--single-launch", action="store_true",
                     help="N=1: dependency-driven single launch per slab instead of one launch per tent level (A/B)")
     return ap.parse_args()
@@ -236,6 +238,8 @@ def run_ours(args):
         tw = ng.TWave(order, ts, 1.0, device=local)
         if args.single_launch:
             tw.set_kernel_mode(3)
+        if args.level_launches:
+            tw.set_kernel_mode(2)
     e = ts.export()
     ntents_global = ts.GetNTents()
     mine = tw.owned_tents() if world > 1 else np.arange(ntents_global)

@@ -84,6 +84,23 @@ __device__ __forceinline__ void eval_group(int w, const double* xi, F&& f) {
   }
 }
 
+// all functions (H == 1) or the half of them in groups 2 part, 2 part + 1 (H == 2)
+template <int D, int P, int FO, int H, class F>
+__device__ __forceinline__ void eval_part(int part, const double* xi, F&& f) {
+  if (H == 1) {
+    gen::BasisGroup<D, P, FO, 0>::eval(xi, f);
+    gen::BasisGroup<D, P, FO, 1>::eval(xi, f);
+    gen::BasisGroup<D, P, FO, 2>::eval(xi, f);
+    gen::BasisGroup<D, P, FO, 3>::eval(xi, f);
+  } else if (part == 0) {
+    gen::BasisGroup<D, P, FO, 0>::eval(xi, f);
+    gen::BasisGroup<D, P, FO, 1>::eval(xi, f);
+  } else {
+    gen::BasisGroup<D, P, FO, 2>::eval(xi, f);
+    gen::BasisGroup<D, P, FO, 3>::eval(xi, f);
+  }
+}
+
 template <int D, int P, int FO>
 __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a, FastArgs f) {
   using C = Cfg<D, P, FO>;
@@ -197,17 +214,56 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
         for (int u = 0; u < d1; u++) r = fma(dv[u], rho[u], r);
         bp[H == 1 ? i : ((i >> 2) * 2 + (i & 1))] += r;   // H == 2: function i = 4 m + 2 part + b -> slot 2 m + b
       };
-      if (H == 1) {
-        gen::BasisGroup<D, P, FO, 0>::eval(xi, fn);
-        gen::BasisGroup<D, P, FO, 1>::eval(xi, fn);
-        gen::BasisGroup<D, P, FO, 2>::eval(xi, fn);
-        gen::BasisGroup<D, P, FO, 3>::eval(xi, fn);
-      } else if (part == 0) {
-        gen::BasisGroup<D, P, FO, 0>::eval(xi, fn);
-        gen::BasisGroup<D, P, FO, 1>::eval(xi, fn);
-      } else {
-        gen::BasisGroup<D, P, FO, 2>::eval(xi, fn);
-        gen::BasisGroup<D, P, FO, 3>::eval(xi, fn);
+      eval_part<D, P, FO, H>(part, xi, fn);
+    }
+    // boundary faces, right-hand side only (CalcTentBndEl, 404-433 / 380-403): b += om g (alpha gamma p + nn) (Dirichlet),
+    // b += om (n.g) (beta nn + p) (Neumann); the datum is sampled at the points of the order-2P rule (twavetents.cpp:373-374)
+    if (nfc > 0) {
+      const int nbp = nfc * Q;
+      for (int c0 = cs * kChunk; c0 < nbp; c0 += NS * kChunk) {
+        const int idx = c0 + lane;
+        const bool valid = idx < nbp;
+        const int idc = valid ? idx : nbp - 1;
+        const int tf = tf0 + idc / Q, q = idc % Q;
+        const double* __restrict__ rec = f.ff + (size_t)tf * FF;
+        const double* __restrict__ lm = a.lam + q * d1;
+        double xi[d1];
+#pragma unroll
+        for (int u = 0; u < d1; u++) xi[u] = rec[fast_ff_v0(D) + u];
+#pragma unroll
+        for (int m = 0; m < D; m++) {
+          const double l = lm[m];
+#pragma unroll
+          for (int u = 0; u < d1; u++) xi[u] = fma(l, rec[fast_ff_e(D) + m * d1 + u], xi[u]);
+        }
+        double nrm[D];
+#pragma unroll
+        for (int u = 0; u < D; u++) nrm[u] = rec[fast_ff_n(D) + u];
+        const double area = rec[fast_ff_misc(D)], s = rec[fast_ff_misc(D) + 1], sc = rec[fast_ff_misc(D) + 2];
+        const double ic2 = rec[fast_ff_misc(D) + 3];
+        const bool neumann = rec[fast_ff_misc(D) + 4] != 0.0;
+        double gdat = 0.0;
+        if (a.bnd_data) {
+          const long long off = a.tf_data[tf];
+          if (neumann) {
+#pragma unroll
+            for (int r = 0; r < D; r++) gdat = fma(nrm[r], a.bnd_data[off + (long long)r * Q + q], gdat);
+          } else {
+            gdat = a.bnd_data[off + q];
+          }
+        }
+        const double og = valid ? a.w[q] * area * gdat : 0.0;
+        // bc = og (cp p + cn nd): Dirichlet cp = gamma / 2, cn = 1; Neumann cp = 1, cn = 1 / 2
+        const double cp = og * sc * (neumann ? 1.0 : 0.5 * ic2), cn = og * s * (neumann ? 0.5 : 1.0);
+        auto fnb = [&](auto ic, double, double e0, double e1, double e2, double e3) {
+          constexpr int i = decltype(ic)::value;
+          const double dv[4] = {e0, e1, e2, e3};
+          double nd = 0.0;
+#pragma unroll
+          for (int u = 0; u < D; u++) nd = fma(nrm[u], dv[u], nd);
+          bp[H == 1 ? i : ((i >> 2) * 2 + (i & 1))] += fma(cp, dv[D], cn * nd);
+        };
+        eval_part<D, P, FO, H>(part, xi, fnb);
       }
     }
 #pragma unroll
@@ -407,14 +463,17 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
     double* const ZR = Z + NP * kBS;
     for (int i = tid; i < 2 * NP * kBS; i += kThreads) Z[i] = 0.0;
     __syncthreads();
-    const int nbp = nfc * Q;
+    // rhsFirst: the right-hand side was done in the first pass; the matrix integrand is a polynomial of degree 2P-2 on the
+    // (affine) time-like face -> compact rule of the top-face Gram (a D-simplex rule as well)
+    constexpr int QB = C::rhsFirst ? QT : Q;
+    const int nbp = nfc * QB;
     for (int c0 = 0; c0 < nbp; c0 += kChunk) {
       const int idx = c0 + lane;
       const bool valid = idx < nbp;
       const int idc = valid ? idx : nbp - 1;
-      const int tf = tf0 + idc / Q, q = idc % Q;
+      const int tf = tf0 + idc / QB, q = idc % QB;
       const double* __restrict__ rec = f.ff + (size_t)tf * FF;
-      const double* __restrict__ lm = a.lam + q * d1;
+      const double* __restrict__ lm = (C::rhsFirst ? f.lam_top : a.lam) + q * d1;
       double xi[d1];
 #pragma unroll
       for (int u = 0; u < d1; u++) xi[u] = rec[fast_ff_v0(D) + u];
@@ -430,9 +489,10 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
       const double area = rec[fast_ff_misc(D)], s = rec[fast_ff_misc(D) + 1], sc = rec[fast_ff_misc(D) + 2];
       const double ic2 = rec[fast_ff_misc(D) + 3];
       const bool neumann = rec[fast_ff_misc(D) + 4] != 0.0;
-      const double om = valid ? a.w[q] * area : 0.0;
+      const double wq = C::rhsFirst ? f.sqrtw_top[q] * f.sqrtw_top[q] : a.w[q];
+      const double om = valid ? wq * area : 0.0;
       double gdat = 0.0;
-      if (a.bnd_data) {
+      if (!C::rhsFirst && a.bnd_data) {
         const long long off = a.tf_data[tf];
         if (neumann) {
 #pragma unroll
@@ -457,7 +517,7 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
         else { lv = p; rv = om * (0.5 * ic2 * p - nd); bc = og * (0.5 * ic2 * p + nd); }
         zl[i * kBS] = lv;
         zr[i * kBS] = rv;
-        bpart[i >> 2] += bc;
+        if (!C::rhsFirst) bpart[i >> 2] += bc;
       });
       __syncthreads();
       switch (w) {
@@ -476,13 +536,17 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
     }
   }
 
-  // ------------------------------------------------------------------ right-hand side: reduce the per-lane partial sums
+  // ------------------------------------------------------------------ right-hand side
+  if (C::rhsFirst) {
+    for (int i = tid; i < NP; i += kThreads) bv[i] = sm[C::oRHS + i];
+  } else {
 #pragma unroll
-  for (int j = 0; j < G; j++) {
-    double v = bpart[j];
+    for (int j = 0; j < G; j++) {
+      double v = bpart[j];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0) bv[4 * j + w] = C::rhsFirst ? v + sm[C::oRHS + 4 * j + w] : v;
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) bv[4 * j + w] = v;
+    }
   }
   __syncthreads();
   // ------------------------------------------------------------------ Solve (64-70 forms the inverse with LAPACK)

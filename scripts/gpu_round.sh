@@ -11,7 +11,7 @@ python bench.py --steps 3 --warmup 3 > gpurun_out/${TAG}_bench.json 2> gpurun_ou
 if [ "${REF:-1}" = "1" ]; then
 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${TAG}_bench_ref.json 2> gpurun_out/${TAG}_bench_ref.err; echo "ref rc=$?"; cat gpurun_out/${TAG}_bench_ref.json
 fi
-SMALL="python bench.py --cells 12 --steps 2 --warmup 3 --no-cpu-baseline --no-e2e"
+SMALL="python bench.py --cells 12 --steps 2 --warmup 3 --no-cpu-baseline --no-e2e --level-launches"
 $SMALL > gpurun_out/${TAG}_plain_small.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/${TAG}_launches.csv $SMALL > gpurun_out/${TAG}_ncu_launches.log 2>&1
 echo "ncu launches rc=$?"
