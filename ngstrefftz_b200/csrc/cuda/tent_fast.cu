@@ -147,7 +147,8 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
     // No Gram is fused into this pass (first-order form, or the stabilisation Gram runs on its compact rule), so it needs
     // no operand buffer and no barrier: warp w takes the chunks w, w + 4, .. and evaluates ALL functions at its 32 points
     // (per-point setup and shared monomials once per point instead of once per warp). It runs first: the Gram
-    // accumulators are not live yet, the partial sums of all N functions fit in registers.
+    // accumulators are not live yet, the partial sums of all N functions fit in registers. The state rows are loaded at the
+    // top of an iteration and consumed after the coordinate setup (a register prefetch one chunk ahead costs spills).
     constexpr int NC = FO ? d1 : d1 + 1;
     // H = 2 (larger bases): a warp evaluates one half of the functions (groups 2h, 2h + 1) on every second chunk, which
     // keeps the partial sums and the live monomials within the 168-register budget of three CTAs per SM
@@ -158,26 +159,16 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
     double bp[NB];
 #pragma unroll
     for (int i = 0; i < NB; i++) bp[i] = 0.0;
-    double gnext[NC];
-    {
-      const int idc = min(cs * kChunk + lane, npts - 1);
-      const double* __restrict__ wf = a.wavefront + (size_t)a.te_el[te0 + idc / Q] * (NC * Q) + idc % Q;
-#pragma unroll
-      for (int cc = 0; cc < NC; cc++) gnext[cc] = __ldcg(wf + cc * Q);  // L2: rows written by other SMs
-    }
     for (int c0 = cs * kChunk; c0 < npts; c0 += NS * kChunk) {
       const int idx = c0 + lane;
       const bool valid = idx < npts;
       const int idc = valid ? idx : npts - 1;
       const int te = te0 + idc / Q, q = idc % Q;
       double gcur[NC];
+      {
+        const double* __restrict__ wf = a.wavefront + (size_t)a.te_el[te] * (NC * Q) + q;
 #pragma unroll
-      for (int cc = 0; cc < NC; cc++) gcur[cc] = gnext[cc];
-      if (c0 + NS * kChunk < npts) {
-        const int idn = min(idx + NS * kChunk, npts - 1);
-        const double* __restrict__ wf = a.wavefront + (size_t)a.te_el[te0 + idn / Q] * (NC * Q) + idn % Q;
-#pragma unroll
-        for (int cc = 0; cc < NC; cc++) gnext[cc] = __ldcg(wf + cc * Q);
+        for (int cc = 0; cc < NC; cc++) gcur[cc] = __ldcg(wf + cc * Q);  // L2: rows written by other SMs
       }
       const double* __restrict__ rec = f.fe + (size_t)te * FE;
       const double* __restrict__ lm = a.lam + q * d1;
