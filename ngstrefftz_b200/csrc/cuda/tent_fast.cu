@@ -621,11 +621,15 @@ cudaError_t launch_cfg(const TentKernelArgs& a, const FastArgs& f, cudaStream_t 
   if (a.Q != C::Q || f.Qt != C::QT || a.N != C::N || a.npoly != C::npoly) return cudaErrorInvalidValue;
   if (C::splitStab && f.Qs != C::QS) return cudaErrorInvalidValue;
   const size_t smem = sizeof(double) * C::nsmem;
-  static bool configured = false;  // per instantiation
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(tent_kernel_fast<D, P, FO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  // the attribute is per device: one flag per device ordinal, not per process (a process may hold solvers on several GPUs)
+  static bool configured[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
+    e = cudaFuncSetAttribute(tent_kernel_fast<D, P, FO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    configured = true;
+    if (dev >= 0 && dev < 64) configured[dev] = true;
   }
   tent_kernel_fast<D, P, FO><<<a.ntents, kThreads, smem, stream>>>(a, f);
   return cudaGetLastError();

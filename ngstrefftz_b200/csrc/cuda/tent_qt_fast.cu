@@ -653,11 +653,15 @@ cudaError_t launch_p(const TentKernelArgs& a, const QtArgs& qa, const QtFastArgs
   using C = QCfg<P>;
   if (a.Q != C::Q || a.N != C::N || a.npoly != C::NM || qa.Qv != (P + 1) * (P + 1) * (P + 1)) return cudaErrorInvalidValue;
   const size_t smem = sizeof(double) * C::nsmem;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(tent_kernel_qt_fast<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  // the attribute is per device: one flag per device ordinal, not per process (a process may hold solvers on several GPUs)
+  static bool configured[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
+    e = cudaFuncSetAttribute(tent_kernel_qt_fast<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    configured = true;
+    if (dev >= 0 && dev < 64) configured[dev] = true;
   }
   tent_kernel_qt_fast<P><<<a.ntents, kThreads, smem, stream>>>(a, qa, f);
   return cudaGetLastError();
