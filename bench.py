@@ -378,7 +378,7 @@ def run_ours(args):
     Qs = n_rule.value   # stabilisation Gram: compact rule exact to degree 2p where the table has one, else the order-2p rule
     dmma_el = (Qt * (D + 1) / 4.0 + (0 if tw.fosystem else Qs / 4.0)) * (nt_tiles * (nt_tiles + 1) / 2) * 512.0
     dmma_tf = dmma_el * float(nels.sum()) * args.steps / (float(np.sum(dev_ms)) * 1e-3) * 1e-12
-    roofline = {"bound": "fp64", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach_tf / fp64_peak,
+    roofline = {"bound": "tensor", "pipe": "FP64: DMMA m8n8k4 tensor path and DFMA share one datapath (DESIGN.md 4.1)", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach_tf / fp64_peak,
                 "traffic": traffic, "kernel": tw.kernel_name(),
                 "peak_source": f"measured live on this GPU: DFMA {dfma.value:.2f} / DMMA m8n8k4 {dmma.value:.2f} TFLOP/s "
                                f"(ngst_device_fp64_peak), DMMA+DFMA interleaved 4:1 {mixed.value:.2f}; MEASURED_PEAKS.json holds no FP64 figure",
