@@ -322,6 +322,57 @@ class TentSlab:
         return ret
 
 
+def Mesh1dTents(tps):
+    """Headless form of Mesh1dTents / NgsTP1dmesh (src/mesh1dtents.cpp:46-174): the 1+1-D tent slab as a 2-D space-time
+    mesh -- one triangle (boundary tent) or quadrilateral per tent, unique points (x, t), boundary segments labelled
+    "inflow" (t = 0), "outflow" (t = dt) and "dirichlet" (spatial boundary). The reference builds a netgen Mesh; here the
+    same entities come back as arrays: dict(points[n,2], trigs[m,3], quads[k,4], segments[s,2], segment_bc[s] in
+    {1: inflow, 2: outflow, 3: dirichlet}). Degenerate tents (ttop < tbot + 1e-5) are skipped as in the reference."""
+    mesh = tps.mesh
+    if mesh.dim != 1:
+        raise ValueError("Mesh1dTents: 1-D meshes only")
+    dt_eps = 0.00001
+    dt = tps.GetSlabHeight()
+    x = mesh.points[:, 0]
+    bd = [float(x[v]) for v in np.unique(mesh.tables()["bnd2v"])] if "bnd2v" in mesh.tables() else [float(x.min()), float(x.max())]
+    pim, pts, trigs, quads, segs, bcs = {}, [], [], [], [], []
+
+    def add(px, pt):
+        key = (px, pt)
+        if key not in pim:
+            pim[key] = len(pts)
+            pts.append(key)
+        return pim[key]
+
+    e = tps.export()
+    for i in range(len(e["vertex"])):
+        v, tbot, ttop = int(e["vertex"][i]), float(e["tbot"][i]), float(e["ttop"][i])
+        if ttop < tbot + dt_eps:
+            continue
+        nbv = e["nbv"][e["nb_off"][i]:e["nb_off"][i + 1]]
+        nbt = e["nbtime"][e["nb_off"][i]:e["nb_off"][i + 1]]
+        vert = [None] * (len(nbv) + 2)
+        ibot, itop = (0, 2) if nbv[0] > v else (2, 0)
+        vert[ibot] = add(float(x[v]), tbot)
+        vert[itop] = add(float(x[v]), ttop)
+        for k in range(len(nbv)):
+            vert[2 * k + 1] = add(float(x[nbv[k]]), float(nbt[k]))
+        (trigs if len(nbv) == 1 else quads).append(vert[:3] if len(nbv) == 1 else vert[:4])
+        for k in range(len(nbv)):
+            if tbot < dt_eps and nbt[k] < dt_eps:
+                segs.append((vert[ibot], vert[2 * k + 1]) if v < nbv[k] else (vert[2 * k + 1], vert[ibot]))
+                bcs.append(1)
+            if ttop > dt - dt_eps and nbt[k] > dt - dt_eps:
+                segs.append((vert[2 * k + 1], vert[itop]) if v < nbv[k] else (vert[itop], vert[2 * k + 1]))
+                bcs.append(2)
+            if float(x[v]) in bd:
+                segs.append((vert[2], vert[0]))
+                bcs.append(3)
+    return {"points": np.array(pts, dtype=float).reshape(-1, 2), "trigs": np.array(trigs, dtype=np.int32).reshape(-1, 3),
+            "quads": np.array(quads, dtype=np.int32).reshape(-1, 4), "segments": np.array(segs, dtype=np.int32).reshape(-1, 2),
+            "segment_bc": np.array(bcs, dtype=np.int32)}
+
+
 class L2Wave:
     """Result of GetWave: coef[el, component, k] in the basis psi_k = sum_j mono[k, j] xi^expo[j] (orthonormal on the
     reference simplex; xi = reference coordinates, x = sum_i lambda_i P_i with lambda = (xi, 1 - sum xi))."""

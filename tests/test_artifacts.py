@@ -46,3 +46,34 @@ def test_tent_dump_round_trip_and_reference_dump(built, tmp_path):
     # a different slab height must be detected, with and without a common numbering
     _, other = pitched(4, 0.25)
     assert other.compare_tents(ref) != [] and other.compare_tents(ref, same_numbering=False) != []
+
+
+def test_mesh1dtents_space_time_mesh(built):
+    """Mesh1dTents (src/mesh1dtents.cpp:46-174): one triangle / quadrilateral per tent, unique points, the elements tile
+    [x0, x1] x [0, dt] exactly, labelled boundary segments cover the four sides."""
+    m = ng.SegMesh(8, 0.0, 2.0)
+    ts = ng.TentSlab(m)
+    ts.SetMaxWavespeed(1.0)
+    dt = 0.3
+    assert ts.PitchTents(dt, True, 2 / 3)
+    out = ng.Mesh1dTents(ts)
+    P = out["points"]
+    assert len(np.unique(P, axis=0)) == len(P)
+    assert len(out["trigs"]) + len(out["quads"]) == ts.GetNTents()
+
+    def area(poly):
+        xy = P[poly]
+        return 0.5 * abs(np.sum(xy[:, 0] * np.roll(xy[:, 1], -1) - np.roll(xy[:, 0], -1) * xy[:, 1]))
+
+    total = sum(area(t) for t in out["trigs"]) + sum(area(q) for q in out["quads"])
+    assert abs(total - 2.0 * dt) < 1e-12
+    seg, bc = out["segments"], out["segment_bc"]
+
+    def length(mask):
+        d = P[seg[mask, 0]] - P[seg[mask, 1]]
+        return np.sqrt((d ** 2).sum(axis=1)).sum()
+
+    assert abs(length(bc == 1) - 2.0) < 1e-12 and abs(length(bc == 2) - 2.0) < 1e-12   # inflow t = 0, outflow t = dt
+    assert np.all(P[seg[bc == 1]][:, :, 1] < 1e-5) and np.all(P[seg[bc == 2]][:, :, 1] > dt - 1e-5)
+    db = seg[bc == 3]
+    assert np.all(np.isin(P[db][:, :, 0], [0.0, 2.0]))
