@@ -169,6 +169,12 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
         const double* __restrict__ wf = a.wavefront + (size_t)a.te_el[te] * (NC * Q) + q;
 #pragma unroll
         for (int cc = 0; cc < NC; cc++) gcur[cc] = __ldcg(wf + cc * Q);  // L2: rows written by other SMs
+        if (c0 + NS * kChunk < npts) {  // next chunk of this warp: HBM -> L2 now (costs no registers)
+          const int idn = min(idx + NS * kChunk, npts - 1);
+          const double* __restrict__ wn = a.wavefront + (size_t)a.te_el[te0 + idn / Q] * (NC * Q) + idn % Q;
+#pragma unroll
+          for (int cc = 0; cc < NC; cc++) asm volatile("prefetch.global.L2 [%0];" ::"l"(wn + cc * Q));
+        }
       }
       const double* __restrict__ rec = f.fe + (size_t)te * FE;
       const double* __restrict__ lm = a.lam + q * d1;
