@@ -399,7 +399,7 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
   }
   if (C::splitStab) {
     // ---------------------------------------------------------------- stabilisation Gram on the compact degree-2P rule
-    constexpr int QS = C::QS;
+    constexpr int QS = C::QS > 0 ? C::QS : 1;  // (no compact rule: branch not taken)
     const int npss = nel * QS;
     __syncthreads();  // the top-face pass has released Z; the right-hand-side pass above does not touch it
     for (int c0 = 0; c0 < npss; c0 += kChunk) {

@@ -41,7 +41,7 @@ constexpr int kFF = 20;  // per boundary-face record: V0s[3] Es[6] (scaled), x0[
 
 template <int P>
 struct QCfg {
-  static constexpr int D = 2, d1 = 3;
+  static constexpr int d1 = 3;
   static constexpr int NM = (P + 1) * (P + 2) * (P + 3) / 6;  // monomials of degree <= P in (x, y, t)
   static constexpr int N = (P + 1) * (P + 1);                 // quasi-Trefftz functions (second-order form)
   static constexpr int NT = (NM + 7) / 8, NP = NT * 8;        // 8x8 tiles / padded monomial count
