@@ -155,6 +155,17 @@ struct Pitcher {
   std::vector<double> edge_len;
   std::vector<double> vertex_refdt;
   std::vector<double> local_ctau;  // aligned with v2e.val (edge) or v2el.val (vol)
+  std::vector<double> edge_term;   // edge algo: global_ctau * local_ct * length / c_max per (vertex, edge), aligned with v2e.val
+  std::vector<double> elgrads;     // barycentric gradients of every element, (D+1)*D doubles each (computed once, in parallel)
+
+  const double* grads(int el) const { return &elgrads[(size_t)el * (m.D + 1) * m.D]; }
+  void CacheGradients() {
+    if (!elgrads.empty()) return;
+    const int stride = (m.D + 1) * m.D;
+    elgrads.resize((size_t)m.nel * stride);
+#pragma omp parallel for schedule(static)
+    for (int el = 0; el < m.nel; el++) bary_grads(m, el, &elgrads[(size_t)el * stride], nullptr);
+  }
 
   Pitcher(const SimplexMesh& mesh, int meth) : m(mesh), method(meth) {}
 
@@ -187,51 +198,66 @@ struct Pitcher {
       if (method == kEdgeGrad) CalcLocalCTauEdge();
       else CalcLocalCTauVol();
     }
+    if (method == kEdgeGrad) {
+      // The tau-independent summand of GetPoleHeight (tents.cpp:806-808), evaluated once per (vertex, edge) in the
+      // reference's operation order, so that the pole height below is bit-identical to recomputing it every time.
+      edge_term.resize(m.v2e.val.size());
+#pragma omp parallel for schedule(static)
+      for (int vi = 0; vi < m.nv; vi++)
+        for (int i = 0; i < m.v2e.size(vi); i++) {
+          const int edge = m.v2e.row(vi)[i];
+          const double local_ct = use_local ? local_ctau[m.v2e.off[vi] + i] : 1.0;
+          edge_term[m.v2e.off[vi] + i] = global_ctau * local_ct * edge_len[edge] / cmax[edge];
+        }
+    }
   }
 
-  // EdgeGradientPitcher::CalcLocalCTau, tents.cpp:815-978
+  // EdgeGradientPitcher::CalcLocalCTau, tents.cpp:815-978. The value the reference computes for (vertex, edge) depends on
+  // the edge only (both end points enter symmetrically), so it is computed once per edge, in parallel, and copied.
   void CalcLocalCTauEdge() {
     const int D = m.D;
-    local_ctau.assign(m.v2e.val.size(), 0.0);
-    std::vector<double> g((D + 1) * D);
-    for (int vi = 0; vi < m.nv; vi++)
-      for (int ie = 0; ie < m.v2e.size(vi); ie++) {
-        const int edge = m.v2e.row(vi)[ie];
-        double val = std::numeric_limits<double>::max();
-        const int v1 = m.edge2v[2 * edge], v2 = m.edge2v[2 * edge + 1];
-        for (int ii = 0; ii < m.edge2el.size(edge); ii++) {
-          const int iel = m.edge2el.row(edge)[ii];
-          bary_grads(m, iel, g.data(), nullptr);
-          const int l1 = local_index(m, iel, v1), l2 = local_index(m, iel, v2);
-          double one_over_max_grad;
-          if (D == 2) {
-            one_over_max_grad = 1.0 / std::max(norm(&g[l1 * D], D), norm(&g[l2 * D], D));
-          } else {
-            // faces of iel adjacent to the edge: those opposite the two vertices NOT on the edge.
-            // The physical face normal is parallel to the gradient of the opposite vertex' hat function.
-            double v = 1;
-            for (int k = 0; k < 4; k++) {
-              if (k == l1 || k == l2) continue;
-              double nrm[3];
-              const double ln = norm(&g[k * 3], 3);
-              for (int d = 0; d < 3; d++) nrm[d] = g[k * 3 + d] / ln;
-              auto proj = [&](int lv) {
-                const double ng = norm(&g[lv * 3], 3);
-                double u[3];
-                for (int d = 0; d < 3; d++) u[d] = g[lv * 3 + d] / ng;
-                double c[3] = {nrm[1] * u[2] - nrm[2] * u[1], nrm[2] * u[0] - nrm[0] * u[2], nrm[0] * u[1] - nrm[1] * u[0]};
-                return norm(c, 3) / ng;
-              };
-              const double val_face = std::min(proj(l1), proj(l2));
-              v = std::min(v, val_face);
-            }
-            one_over_max_grad = v;
+    CacheGradients();
+    std::vector<double> edge_val(m.nedges);
+#pragma omp parallel for schedule(dynamic, 1024)
+    for (int edge = 0; edge < m.nedges; edge++) {
+      double val = std::numeric_limits<double>::max();
+      const int v1 = m.edge2v[2 * edge], v2 = m.edge2v[2 * edge + 1];
+      for (int ii = 0; ii < m.edge2el.size(edge); ii++) {
+        const int iel = m.edge2el.row(edge)[ii];
+        const double* g = grads(iel);
+        const int l1 = local_index(m, iel, v1), l2 = local_index(m, iel, v2);
+        double one_over_max_grad;
+        if (D == 2) {
+          one_over_max_grad = 1.0 / std::max(norm(&g[l1 * D], D), norm(&g[l2 * D], D));
+        } else {
+          // faces of iel adjacent to the edge: those opposite the two vertices NOT on the edge.
+          // The physical face normal is parallel to the gradient of the opposite vertex' hat function.
+          double v = 1;
+          for (int k = 0; k < 4; k++) {
+            if (k == l1 || k == l2) continue;
+            double nrm[3];
+            const double ln = norm(&g[k * 3], 3);
+            for (int d = 0; d < 3; d++) nrm[d] = g[k * 3 + d] / ln;
+            auto proj = [&](int lv) {
+              const double ng = norm(&g[lv * 3], 3);
+              double u[3];
+              for (int d = 0; d < 3; d++) u[d] = g[lv * 3 + d] / ng;
+              double c[3] = {nrm[1] * u[2] - nrm[2] * u[1], nrm[2] * u[0] - nrm[0] * u[2], nrm[0] * u[1] - nrm[1] * u[0]};
+              return norm(c, 3) / ng;
+            };
+            const double val_face = std::min(proj(l1), proj(l2));
+            v = std::min(v, val_face);
           }
-          const double projGrad = one_over_max_grad / edge_len[edge];
-          val = std::min(val, projGrad);
+          one_over_max_grad = v;
         }
-        local_ctau[m.v2e.off[vi] + ie] = val;
+        const double projGrad = one_over_max_grad / edge_len[edge];
+        val = std::min(val, projGrad);
       }
+      edge_val[edge] = val;
+    }
+    local_ctau.resize(m.v2e.val.size());
+#pragma omp parallel for schedule(static)
+    for (size_t k = 0; k < m.v2e.val.size(); k++) local_ctau[k] = edge_val[m.v2e.val[k]];
   }
 
   // VolumeGradientPitcher::CalcLocalCTau, tents.cpp:719-794
@@ -289,14 +315,10 @@ struct Pitcher {
     double kt = std::numeric_limits<double>::max();
     const int n = m.v2v.size(vi);
     const int* nbv = m.v2v.row(vi);
-    const int* nbe = m.v2e.row(vi);
+    const double* term = &edge_term[m.v2e.off[vi]];  // v2v and v2e rows are aligned (neighbour i is across edge i)
+    const double tv = tau[vi];
     for (int i = 0; i < n; i++) {
-      const int nb = nbv[i];
-      const int edge = nbe[i];
-      const double length = edge_len[edge];
-      const double c_max = cmax[edge];
-      const double local_ct = use_local ? local_ctau[m.v2e.off[vi] + i] : 1.0;
-      const double kt1 = tau[nb] - tau[vi] + global_ctau * local_ct * length / c_max;
+      const double kt1 = tau[nbv[i]] - tv + term[i];
       kt = std::min(kt, kt1);
     }
     constexpr double num_tol = std::numeric_limits<double>::epsilon();
@@ -310,13 +332,12 @@ struct Pitcher {
     constexpr double init_pole_height = std::numeric_limits<double>::max();
     constexpr double num_tol = std::numeric_limits<double>::epsilon();
     double pole_height = init_pole_height;
-    double g[12];
     for (int iel = 0; iel < m.v2el.size(vi); iel++) {
       const int el = m.v2el.row(vi)[iel];
       const double c_max_sq = cmax[el] * cmax[el];
       const int* ev = m.elverts(el);
       const int local_vi = local_index(m, el, vi);
-      bary_grads(m, el, g, nullptr);
+      const double* g = grads(el);
       double coeff[4];
       for (int k = 0; k <= D; k++) coeff[k] = tau[ev[k]];
       coeff[local_vi] = 0;
@@ -370,7 +391,13 @@ bool TentSlab::PitchTents(double adt, bool calc_local_ct, double global_ct) {
   nbv.off = {0}; els.off = {0}; facets.off = {0};
   nbtime.clear();
 
+  {
+    // a first guess of the slab's size (the vectors grow as needed)
+    const size_t guess = (size_t)nv * 4;
+    vertex.reserve(guess); level.reserve(guess); tbot.reserve(guess); ttop.reserve(guess);
+  }
   Pitcher P(m, method);
+  P.CacheGradients();
   P.InitializeMeshData(cmax_el, calc_local_ct, global_ct);
 
   std::vector<double> tau(nv, 0.0);
@@ -380,13 +407,34 @@ bool TentSlab::PitchTents(double adt, bool calc_local_ct, double global_ct) {
   std::vector<double> ktilde = P.vertex_refdt;
 
   std::vector<int> latest_tent(nv, -1), vertices_level(nv, 0);
-  std::vector<std::vector<int>> dependents;  // dependent_tents per tent
+  std::vector<int> dep_src, dep_dst;  // dependent_tents (tents.cpp:206) as (tent, dependent) pairs in creation order
   const double adv_factor = 0.5;             // reset after every GetReadyVertices (reset_adv_factor = true)
   ReadyList ready(nv, vertices_level);
   std::vector<char> complete(nv, 0);
   bool slab_complete = false;
   const double num_tol = std::numeric_limits<double>::epsilon() * dt;
-  std::vector<int> facet_mark(D == 3 ? m.nfacets : 0, -1);
+  // D = 3: the internal-facet list of a tent (tents.cpp:219-247) depends on its vertex only: the facets of the patch
+  // elements that contain the vertex, in order of first occurrence. Built once per vertex instead of once per tent.
+  Csr v2f;
+  if (D == 3) {
+    v2f.off.assign(nv + 1, 0);
+    std::vector<std::vector<int>> rows(nv);
+#pragma omp parallel for schedule(dynamic, 256)
+    for (int vi = 0; vi < nv; vi++) {
+      std::vector<int>& r = rows[vi];
+      for (int i = 0; i < m.v2el.size(vi); i++) {
+        const int el = m.v2el.row(vi)[i];
+        for (int k = 0; k < 4; k++) {
+          const int f = m.el2facet[(size_t)el * 4 + k];
+          const int* fv = &m.facet2v[(size_t)f * 3];
+          if ((fv[0] == vi || fv[1] == vi || fv[2] == vi) && std::find(r.begin(), r.end(), f) == r.end()) r.push_back(f);
+        }
+      }
+    }
+    for (int vi = 0; vi < nv; vi++) v2f.off[vi + 1] = v2f.off[vi] + (int)rows[vi].size();
+    v2f.val.resize(v2f.off[nv]);
+    for (int vi = 0; vi < nv; vi++) std::copy(rows[vi].begin(), rows[vi].end(), v2f.val.begin() + v2f.off[vi]);
+  }
 
   while (!slab_complete) {
     // GetReadyVertices, tents.cpp:385-418 (the list is empty on entry)
@@ -428,29 +476,18 @@ bool TentSlab::PitchTents(double adt, bool calc_local_ct, double global_ct) {
           vertices_level[nb] = lev + 1;
           ready.level_changed(nb);
         }
-        if (latest_tent[nb] != -1) dependents[latest_tent[nb]].push_back(tid);
+        if (latest_tent[nb] != -1) { dep_src.push_back(latest_tent[nb]); dep_dst.push_back(tid); }
       }
       nbv.off.push_back((int)nbv.val.size());
       latest_tent[vi] = tid;
       vertices_level[vi]++;
-      dependents.emplace_back();
 
       // internal facets, tents.cpp:219-247
       if (D == 1) facets.val.push_back(vi);
       else if (D == 2)
         for (int i = 0; i < m.v2e.size(vi); i++) facets.val.push_back(m.v2e.row(vi)[i]);
       else
-        for (int i = 0; i < m.v2el.size(vi); i++) {
-          const int el = m.v2el.row(vi)[i];
-          for (int k = 0; k < 4; k++) {
-            const int f = m.el2facet[(size_t)el * 4 + k];
-            const int* fv = &m.facet2v[(size_t)f * 3];
-            if ((fv[0] == vi || fv[1] == vi || fv[2] == vi) && facet_mark[f] != tid) {
-              facet_mark[f] = tid;
-              facets.val.push_back(f);
-            }
-          }
-        }
+        facets.val.insert(facets.val.end(), v2f.row(vi), v2f.row(vi) + v2f.size(vi));
       facets.off.push_back((int)facets.val.size());
       for (int i = 0; i < m.v2el.size(vi); i++) els.val.push_back(m.v2el.row(vi)[i]);
       els.off.push_back((int)els.val.size());
@@ -475,31 +512,38 @@ bool TentSlab::PitchTents(double adt, bool calc_local_ct, double global_ct) {
   if (!slab_complete) std::printf("Error: the algorithm could not pitch the whole slab\n");
 
   // dependency graph, tents.cpp:313-321
+  // (stable counting sort by source tent: every row keeps the order in which its dependents were appended)
   dag.off.assign(ntents + 1, 0);
-  for (int i = 0; i < ntents; i++) dag.off[i + 1] = dag.off[i] + (int)dependents[i].size();
-  dag.val.resize(dag.off[ntents]);
-  for (int i = 0; i < ntents; i++) std::copy(dependents[i].begin(), dependents[i].end(), dag.val.begin() + dag.off[i]);
+  for (int s : dep_src) dag.off[s + 1]++;
+  for (int i = 0; i < ntents; i++) dag.off[i + 1] += dag.off[i];
+  dag.val.resize(dep_src.size());
+  {
+    std::vector<int> pos(dag.off.begin(), dag.off.end() - 1);
+    for (size_t k = 0; k < dep_src.size(); k++) dag.val[pos[dep_src[k]]++] = dep_dst[k];
+  }
 
   // slope of the top front per tent, tents.cpp:323-356
   maxslope.assign(ntents, 0.0);
-#pragma omp parallel for schedule(static)
-  for (int i = 0; i < ntents; i++) {
-    double g[12];
-    for (int j = els.off[i]; j < els.off[i + 1]; j++) {
-      const int el = els.val[j];
-      const int* ev = m.elverts(el);
-      double coef[4];
-      for (int k = 0; k <= D; k++) {
-        coef[k] = ttop[i];
-        for (int q = nbv.off[i]; q < nbv.off[i + 1]; q++)
-          if (nbv.val[q] == ev[k]) { coef[k] = nbtime[q]; break; }
+#pragma omp parallel
+  {
+    // front height of the patch vertices of the current tent (every vertex of a patch element is the tent vertex or one of nbv)
+    std::vector<double> vt(nv, 0.0);
+#pragma omp for schedule(static)
+    for (int i = 0; i < ntents; i++) {
+      vt[vertex[i]] = ttop[i];
+      for (int q = nbv.off[i]; q < nbv.off[i + 1]; q++) vt[nbv.val[q]] = nbtime[q];
+      double ms = 0.0;
+      for (int j = els.off[i]; j < els.off[i + 1]; j++) {
+        const int el = els.val[j];
+        const int* ev = m.elverts(el);
+        const double* g = P.grads(el);
+        double gp[3] = {0, 0, 0};
+        for (int d = 0; d < D; d++)
+          for (int k = 0; k <= D; k++) gp[d] += g[k * D + d] * vt[ev[k]];
+        const double nrm = norm(gp, D);
+        if (nrm > ms) ms = nrm;
       }
-      bary_grads(m, el, g, nullptr);
-      double gp[3] = {0, 0, 0};
-      for (int d = 0; d < D; d++)
-        for (int k = 0; k <= D; k++) gp[d] += g[k * D + d] * coef[k];
-      const double nrm = norm(gp, D);
-      if (nrm > maxslope[i]) maxslope[i] = nrm;
+      maxslope[i] = ms;
     }
   }
 
