@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--cpu-sample-tents", type=int, default=0, help="tents in the bounded CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-device-data", action="store_true", help="skip the informational device-sampled-data arm")
     ap.add_argument("--partition", default="balanced", choices=["balanced", "brick"],
                     help="N>1: cost-balanced recursive bisection (default) or plain brick cut of the bounding box")
     ap.add_argument("--no-overlap", action="store_true", help="N>1: exchange after each level instead of overlapped")
@@ -320,6 +321,38 @@ def run_ours(args):
         e2e_s = time.perf_counter() - t0
         e2e = {"sec": e2e_s, "h2d": int(nbytes + nb * 8), "d2h": int(nbytes)}
 
+    # ---------------- informational: the same call sequence with initial and boundary data sampled ON THE DEVICE
+    # (ngst_twave_*_analytic): no H2D of samples, same D2H. Not the e2e figure (that one copies
+    # host inputs every step); reported beside it, with the difference of the resulting state to the host-data run.
+    device_data = None
+    if e2e is not None and world == 1 and not args.no_device_data:
+        try:
+            data = ng.StandingWave(D, 1.0)
+            host_out = pin_out.numpy().copy()
+
+            def dd_step():
+                tw.reset_time()
+                tw.SetInitial(data)
+                tw.SetBoundaryCF(data)
+                check(lib.ngst_twave_propagate(tw._h))
+                check(lib.ngst_twave_get_wavefront(tw._h, out_ptr))
+
+            for _ in range(args.warmup):
+                dd_step()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                dd_step()
+            barrier()
+            dd_s = time.perf_counter() - t0
+            diff = float(np.abs(pin_out.numpy() - host_out).max() / np.abs(host_out).max())
+            device_data = {"value": len(mine) * args.steps / dd_s, "unit": "tents/s", "ms_per_step": dd_s / args.steps * 1e3,
+                           "h2d_bytes_per_step": 0, "d2h_bytes_per_step": int(nbytes),
+                           "max_rel_diff_vs_host_data": diff,
+                           "path": "ngst_twave_set_initial_analytic + set_boundary_analytic + propagate + get_wavefront"}
+        except Exception as ex:  # informational arm: never takes the bench line down
+            device_data = {"error": repr(ex)}
+
     # ---------------- reduce over ranks (max time, sum units)
     ntents_local = len(mine)
     stats = torch.tensor([dev_s, wall_s, e2e["sec"] if e2e else 0.0, float(ntents_local), flops_step, bytes_step,
@@ -415,6 +448,8 @@ def run_ours(args):
                        "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"],
                        "ms_per_step": 1e3 * e2e_s / args.steps,
                        "path": "ngst_twave_set_initial + set_boundary_values + propagate + get_wavefront on pinned host buffers"}
+    if device_data:
+        line["device_data"] = device_data
     if not args.no_cpu_baseline and world == 1:
         cores = os.cpu_count() or 1
         sample = args.cpu_sample_tents or 4000

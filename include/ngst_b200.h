@@ -130,6 +130,19 @@ long long ngst_twave_boundary_npoints(const ngst_twave* t);
 long long ngst_twave_boundary_nvalues(const ngst_twave* t);
 int ngst_twave_boundary_points(const ngst_twave* t, double* xt, int* kind_per_point);
 int ngst_twave_set_boundary_values(ngst_twave* t, const double* values, long long n);
+/* Analytic data sampled on the device instead of a host-evaluated CoefficientFunction:
+ * SetInitial / MakeWavefront (src/twavetents.cpp:734-764) and the boundary datum (src/twavetents.cpp:373-374, 386,
+ * 407-411), which every later Propagate re-samples at (x, t_local + timeshift) until ngst_twave_set_boundary_values
+ * replaces it. family / params (doubles), data = (u, grad u, d_t u):
+ *   0 standing wave  [c]                          u = prod_d sin(pi x_d) sin(pi sqrt(D) c t) / (sqrt(D) pi)
+ *   1 plane pulse    [c, a, s0, k_0..k_{D-1}]     u = exp(-a (k.x - c t - s0)^2), |k| = 1
+ *   2 polynomial     [nterms, (coef, e_0..e_{D-1}, e_t) per term]   u = sum coef x^e t^e_t
+ * first_order != 0: rows hold (grad u, d_t u) only (switches the solver to the first-order system like
+ * ngst_twave_set_initial with ncomp == D+1). out: host buffer, nel x (ncomp*nip). */
+int ngst_twave_set_initial_analytic(ngst_twave* t, int family, const double* params, int nparams, int first_order);
+int ngst_twave_make_wavefront_analytic(ngst_twave* t, int family, const double* params, int nparams, double time,
+                                       int first_order, double* out);
+int ngst_twave_set_boundary_analytic(ngst_twave* t, int family, const double* params, int nparams);
 /* Propagate src/twavetents.cpp:72-175: one slab, timeshift += slab height. */
 int ngst_twave_propagate(ngst_twave* t);
 double ngst_twave_timeshift(const ngst_twave* t);

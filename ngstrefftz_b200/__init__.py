@@ -10,6 +10,8 @@ NGSolve is not available, so `CoefficientFunction`s become plain Python callable
   wavespeed : float | array(nel) | callable(x[n,D]) -> array(n)        (evaluated at element centroids)
   initial   : callable(x[n,D], t) -> array(n, ncomp)  | array(nel, ncomp*nip)
   boundary  : callable(x[n,D], t[n]) -> array(n) (Dirichlet: dt u) or array(n, D) (Neumann: grad u)
+  initial / boundary may also be an AnalyticData object (StandingWave, PlanePulse, PolynomialWave): those are sampled
+  on the device (cuda/sample.cu), with no host evaluation and no H2D copy of samples
 and netgen meshes become `Mesh` objects (structured generators SegMesh / UnitSquareMesh / UnitCubeMesh,
 or explicit point/element arrays). All arithmetic of Propagate runs in libngst_b200.so on the GPU.
 """
@@ -20,9 +22,11 @@ import numpy as np
 from . import _capi
 from ._capi import NgstError, check, dptr, f64, i32, iptr, lib
 from ._poly import PolynomialCF
+from ._analytic import AnalyticData, PlanePulse, PolynomialWave, StandingWave
 
 __all__ = ["Mesh", "SegMesh", "UnitSquareMesh", "UnitCubeMesh", "StructuredMesh", "TentSlab", "Tent", "TWave",
-           "TrefftzTents", "TWaveTents", "TaskManager", "SetNumThreads", "NgstError", "PolynomialCF"]
+           "TrefftzTents", "TWaveTents", "TaskManager", "SetNumThreads", "NgstError", "PolynomialCF",
+           "AnalyticData", "StandingWave", "PlanePulse", "PolynomialWave"]
 
 
 class TaskManager:
@@ -453,6 +457,8 @@ class TWaveTents(TrefftzTents):
                                                     iptr(owner), int(nranks), int(rank), C.byref(self._h)))
             self.partition = (int(rank), int(nranks), owner)
         self._bddatum = None
+        self._bnd_on_device = False
+        self._bnd_dirty = False
         self._bnd_pts = None
         self._quad = None
         self._refresh()
@@ -507,6 +513,13 @@ class TWaveTents(TrefftzTents):
 
     def MakeWavefront(self, cf, time=0.0):
         """src/twavetents.cpp:734-764: sample cf at all element quadrature points at a fixed time."""
+        if isinstance(cf, AnalyticData):  # sampled on the device (cuda/sample.cu)
+            self._check_data(cf)
+            ncomp = self.D + (1 if cf.first_order else 2)
+            wf = np.zeros((self.nel, ncomp * self.nip))
+            check(lib.ngst_twave_make_wavefront_analytic(self._h, cf.family, dptr(cf.params), len(cf.params), float(time),
+                                                         int(cf.first_order), dptr(wf)))
+            return wf
         if not callable(cf):
             wf = f64(cf)
             if wf.ndim != 2 or wf.shape[0] != self.nel or wf.shape[1] % self.nip:
@@ -521,14 +534,31 @@ class TWaveTents(TrefftzTents):
             self.nel, ncomp * self.nip)
 
     # ---- TrefftzTents interface
+    def _check_data(self, data):
+        if data.D != self.D:
+            raise ValueError(f"analytic data is {data.D}-dimensional, the solver {self.D}-dimensional")
+
     def SetInitial(self, init):
+        if isinstance(init, AnalyticData):
+            self._check_data(init)
+            check(lib.ngst_twave_set_initial_analytic(self._h, init.family, dptr(init.params), len(init.params),
+                                                      int(init.first_order)))
+            self._refresh()
+            return
         wf = self.MakeWavefront(init, 0.0)
         ncomp = wf.shape[1] // self.nip
         check(lib.ngst_twave_set_initial(self._h, dptr(wf), ncomp))
         self._refresh()
 
     def SetBoundaryCF(self, bddatum):
+        """An AnalyticData datum is sampled on the device by every Propagate (Dirichlet faces take d_t u, Neumann faces
+        grad u); any other callable is evaluated on the host per slab as before."""
         self._bddatum = bddatum
+        self._bnd_on_device = isinstance(bddatum, AnalyticData)
+        self._bnd_dirty = False
+        if self._bnd_on_device:
+            self._check_data(bddatum)
+            check(lib.ngst_twave_set_boundary_analytic(self._h, bddatum.family, dptr(bddatum.params), len(bddatum.params)))
 
     def _boundary_values(self, timeshift=None):
         npts = lib.ngst_twave_boundary_npoints(self._h)
@@ -565,6 +595,11 @@ class TWaveTents(TrefftzTents):
         return np.ascontiguousarray(np.concatenate(out))
 
     def Propagate(self):
+        if getattr(self, "_bnd_on_device", False):
+            if self._bnd_dirty:  # propagate_with_values replaced the device-side datum in between
+                self.SetBoundaryCF(self._bddatum)
+            check(lib.ngst_twave_propagate(self._h))
+            return
         self.propagate_with_values(self._boundary_values())
 
     def sample_boundary(self, timeshift):
@@ -574,6 +609,7 @@ class TWaveTents(TrefftzTents):
     def propagate_with_values(self, vals):
         """Propagate with pre-sampled boundary values (the array ngst_twave_set_boundary_values takes)."""
         n = 0 if vals is None else len(vals)
+        self._bnd_dirty = True
         check(lib.ngst_twave_set_boundary_values(self._h, dptr(vals), n))
         check(lib.ngst_twave_propagate(self._h))
 

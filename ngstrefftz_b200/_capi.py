@@ -72,6 +72,9 @@ _SIGS = {
     "ngst_twave_boundary_nvalues": (C.c_longlong, [c_vp]),
     "ngst_twave_boundary_points": (C.c_int, [c_vp, c_dp, c_ip]),
     "ngst_twave_set_boundary_values": (C.c_int, [c_vp, c_dp, C.c_longlong]),
+    "ngst_twave_set_initial_analytic": (C.c_int, [c_vp, C.c_int, c_dp, C.c_int, C.c_int]),
+    "ngst_twave_make_wavefront_analytic": (C.c_int, [c_vp, C.c_int, c_dp, C.c_int, C.c_double, C.c_int, c_dp]),
+    "ngst_twave_set_boundary_analytic": (C.c_int, [c_vp, C.c_int, c_dp, C.c_int]),
     "ngst_twave_propagate": (C.c_int, [c_vp]),
     "ngst_twave_timeshift": (C.c_double, [c_vp]),
     "ngst_twave_set_timeshift": (C.c_int, [c_vp, C.c_double]),

@@ -342,6 +342,22 @@ int ngst_twave_set_boundary_values(ngst_twave* t, const double* values, long lon
   return guarded([&] { need(t, "solver"); t->solver->SetBoundaryValues(values, n); });
 }
 
+int ngst_twave_set_initial_analytic(ngst_twave* t, int family, const double* params, int nparams, int first_order) {
+  return guarded([&] { need(t, "solver"); t->solver->SetInitialAnalytic(family, params, nparams, first_order); });
+}
+
+int ngst_twave_make_wavefront_analytic(ngst_twave* t, int family, const double* params, int nparams, double time,
+                                       int first_order, double* out) {
+  return guarded([&] {
+    need(t, "solver");
+    t->solver->MakeWavefrontAnalytic(family, params, nparams, time, first_order, out);
+  });
+}
+
+int ngst_twave_set_boundary_analytic(ngst_twave* t, int family, const double* params, int nparams) {
+  return guarded([&] { need(t, "solver"); t->solver->SetBoundaryAnalytic(family, params, nparams); });
+}
+
 int ngst_twave_propagate(ngst_twave* t) {
   return guarded([&] { need(t, "solver"); t->solver->Propagate(); });
 }

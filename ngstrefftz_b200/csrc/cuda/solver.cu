@@ -1,4 +1,5 @@
 #include "solver.hpp"
+#include "sample.hpp"
 
 #include <algorithm>
 #include <cmath>
@@ -355,6 +356,8 @@ Solver::~Solver() {
   for (void* p : allocs_) cudaFree(p);
   if (d_wavefront_) cudaFree(d_wavefront_);
   if (d_bnd_) cudaFree(d_bnd_);
+  if (d_bnd_params_) cudaFree(d_bnd_params_);
+  if (d_tmp_params_) cudaFree(d_tmp_params_);
   if (d_tmp_a_) cudaFree(d_tmp_a_);
   if (d_tmp_b_) cudaFree(d_tmp_b_);
   if (d_sendbuf_) cudaFree(d_sendbuf_);
@@ -431,8 +434,10 @@ void Solver::SetInitial(const double* wf, int ncomp) {
   const size_t bytes = (size_t)nel_ * ncomp * rule_.nip * sizeof(double);
   if (d_wavefront_ && wavefront_bytes_ != bytes) { CU(cudaFree(d_wavefront_)); d_wavefront_ = nullptr; }
   if (!d_wavefront_) { CU(cudaMalloc(&d_wavefront_, bytes)); wavefront_bytes_ = bytes; }
-  CU(cudaMemcpyAsync(d_wavefront_, wf, bytes, cudaMemcpyHostToDevice, stream_));
-  CU(cudaStreamSynchronize(stream_));
+  if (wf) {
+    CU(cudaMemcpyAsync(d_wavefront_, wf, bytes, cudaMemcpyHostToDevice, stream_));
+    CU(cudaStreamSynchronize(stream_));
+  }
   have_initial_ = true;
 
   TentKernelArgs& a = args_;
@@ -477,8 +482,80 @@ void Solver::SetInitial(const double* wf, int ncomp) {
   threads_ = tiles > 128 ? 256 : (tiles > 32 ? 128 : 64);
 }
 
+namespace {
+void check_family(int D, int family, const double* params, int nparams) {
+  if (!params) throw std::invalid_argument("analytic data: params is null");
+  if (family == kStandingWave) {
+    if (nparams != 1) throw std::invalid_argument("analytic data: the standing wave takes 1 parameter (c)");
+  } else if (family == kPlaneGauss) {
+    if (nparams != 3 + D) throw std::invalid_argument("analytic data: the plane pulse takes 3 + D parameters (c, a, s0, k)");
+  } else if (family == kPolynomial) {
+    if (nparams < 1 || params[0] < 0 || nparams != 1 + (int)params[0] * (D + 2))
+      throw std::invalid_argument("analytic data: the polynomial takes 1 + nterms * (D + 2) parameters");
+    for (int m = 0; m < (int)params[0]; m++)
+      for (int d = 0; d <= D; d++) {
+        const double e = params[1 + m * (D + 2) + 1 + d];
+        if (e < 0 || e > 64 || e != std::floor(e)) throw std::invalid_argument("analytic data: exponents must be integers in [0, 64]");
+      }
+  } else {
+    throw std::invalid_argument("analytic data: unknown family");
+  }
+}
+}  // namespace
+
+double* Solver::UploadParams(const double* params, int nparams, double** slot) {
+  if (*slot) { CU(cudaFree(*slot)); *slot = nullptr; }
+  CU(cudaMalloc(slot, sizeof(double) * nparams));
+  CU(cudaMemcpyAsync(*slot, params, sizeof(double) * nparams, cudaMemcpyHostToDevice, stream_));
+  CU(cudaStreamSynchronize(stream_));
+  return *slot;
+}
+
+void Solver::SetInitialAnalytic(int family, const double* params, int nparams, int first_order) {
+  const int D = mesh_.D;
+  check_family(D, family, params, nparams);
+  SetInitial(nullptr, first_order ? D + 1 : D + 2);  // allocates the state and configures the kernels
+  double* d_p = UploadParams(params, nparams, &d_tmp_params_);
+  CU(launch_sample_wavefront(D, family, d_p, nel_, rule_.nip, first_order ? 1 : 0, 0.0, args_.pts, args_.el2v, args_.lam,
+                             d_wavefront_, stream_));
+  CU(cudaStreamSynchronize(stream_));
+}
+
+void Solver::MakeWavefrontAnalytic(int family, const double* params, int nparams, double time, int first_order,
+                                   double* out) {
+  const int D = mesh_.D;
+  check_family(D, family, params, nparams);
+  if (!out) throw std::invalid_argument("MakeWavefrontAnalytic: out is null");
+  CU(cudaSetDevice(device_));
+  const int ncomp = first_order ? D + 1 : D + 2;
+  const size_t bytes = (size_t)nel_ * ncomp * rule_.nip * sizeof(double);
+  double* d_out = nullptr;
+  CU(cudaMalloc(&d_out, bytes));
+  try {
+    double* d_p = UploadParams(params, nparams, &d_tmp_params_);
+    CU(launch_sample_wavefront(D, family, d_p, nel_, rule_.nip, first_order ? 1 : 0, time, args_.pts, args_.el2v,
+                               args_.lam, d_out, stream_));
+    CU(cudaMemcpyAsync(out, d_out, bytes, cudaMemcpyDeviceToHost, stream_));
+    CU(cudaStreamSynchronize(stream_));
+  } catch (...) {
+    cudaFree(d_out);
+    throw;
+  }
+  CU(cudaFree(d_out));
+}
+
+void Solver::SetBoundaryAnalytic(int family, const double* params, int nparams) {
+  check_family(mesh_.D, family, params, nparams);
+  CU(cudaSetDevice(device_));
+  UploadParams(params, nparams, &d_bnd_params_);
+  bnd_family_ = family;
+  if (staged_.nbnd_values > 0 && !d_bnd_) CU(cudaMalloc(&d_bnd_, sizeof(double) * staged_.nbnd_values));
+  args_.bnd_data = staged_.nbnd_values > 0 ? d_bnd_ : nullptr;
+}
+
 void Solver::SetBoundaryValues(const double* values, long long n) {
   CU(cudaSetDevice(device_));
+  bnd_family_ = -1;  // host-sampled values replace an analytic datum
   if (values == nullptr) { args_.bnd_data = nullptr; return; }
   if (n != staged_.nbnd_values) throw std::invalid_argument("SetBoundaryValues: wrong number of values");
   if (n == 0) { args_.bnd_data = nullptr; return; }
@@ -494,6 +571,12 @@ void Solver::Propagate() {
   const int nlev = (int)slab_.level_off.size() - 1;
   int launches = 0;
   CU(cudaEventRecord(ev0_, stream_));
+  if (bnd_family_ >= 0 && staged_.nbnd_values > 0) {
+    // analytic boundary datum: sampled for this slab at t_local + timeshift (twavetents.cpp:373-374) ahead of the tents
+    CU(launch_sample_boundary(mesh_.D, bnd_family_, d_bnd_params_, staged_.ntf, rule_.nip, timeshift_, args_.tf_kind,
+                              args_.tf_verts, args_.tf_data, args_.lam, kNeumann, d_bnd_, stream_));
+    launches++;
+  }
   for (int l = 0; l < nlev && qt_; l++) {
     // quasi-Trefftz: fast monomial-space DMMA kernel where a variant exists (second-order form, causal top faces),
     // generic kernel otherwise

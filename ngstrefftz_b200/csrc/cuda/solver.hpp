@@ -59,6 +59,12 @@ class Solver {
   void Quadrature(double* x, double* weight) const;
   void SetInitial(const double* wf, int ncomp);
   void SetBoundaryValues(const double* values, long long n);
+  // Analytic data sampled on the device (cuda/sample.hpp): SetInitial / MakeWavefront
+  // (twavetents.cpp:734-764) and the boundary datum, re-sampled by every Propagate at t_local + timeshift
+  // (twavetents.cpp:373-374), without a host evaluation or an H2D copy of samples.
+  void SetInitialAnalytic(int family, const double* params, int nparams, int first_order);
+  void MakeWavefrontAnalytic(int family, const double* params, int nparams, double time, int first_order, double* out);
+  void SetBoundaryAnalytic(int family, const double* params, int nparams);
   void Propagate();
   void GetWavefront(double* out);
   double Energy(const double* wf);
@@ -142,6 +148,10 @@ class Solver {
   double* d_cval_[2] = {nullptr, nullptr};
   double* d_wavefront_ = nullptr;
   double* d_bnd_ = nullptr;
+  int bnd_family_ = -1;            // >= 0: analytic boundary datum (AnalyticFamily), sampled on the device per slab
+  double* d_bnd_params_ = nullptr;
+  double* d_tmp_params_ = nullptr;
+  double* UploadParams(const double* params, int nparams, double** slot);
   double* d_elw_ = nullptr;   // nel*nip weights |detJ| w
   double* d_scratch_ = nullptr;
   double* d_tmp_a_ = nullptr;
