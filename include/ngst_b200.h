@@ -143,6 +143,10 @@ int ngst_twave_set_initial_analytic(ngst_twave* t, int family, const double* par
 int ngst_twave_make_wavefront_analytic(ngst_twave* t, int family, const double* params, int nparams, double time,
                                        int first_order, double* out);
 int ngst_twave_set_boundary_analytic(ngst_twave* t, int family, const double* params, int nparams);
+/* Error (l2only == 0) / L2Error (l2only != 0) src/twavetents.cpp:766-822 of the state RESIDENT on the device against
+ * the analytic data sampled on the device at `time`: no wavefront crosses PCIe. */
+int ngst_twave_error_analytic(ngst_twave* t, int family, const double* params, int nparams, double time, int l2only,
+                              double* out);
 /* Propagate src/twavetents.cpp:72-175: one slab, timeshift += slab height. */
 int ngst_twave_propagate(ngst_twave* t);
 double ngst_twave_timeshift(const ngst_twave* t);

@@ -669,15 +669,31 @@ class TWaveTents(TrefftzTents):
             np.asarray(U.vec).reshape(-1)[:] = coef.reshape(-1)
         return L2Wave(coef, deg, psi, mono, expo)
 
-    def Error(self, wavefront, wavefront_corr):
+    def _error(self, wavefront, wavefront_corr, time, l2only):
         out = C.c_double(0)
-        check(lib.ngst_twave_error(self._h, dptr(f64(wavefront)), dptr(f64(wavefront_corr)), C.byref(out)))
+        if isinstance(wavefront_corr, AnalyticData):
+            self._check_data(wavefront_corr)
+            time = self.timeshift() if time is None else float(time)
+            if wavefront is None:  # resident state against device-sampled data: nothing crosses PCIe
+                check(lib.ngst_twave_error_analytic(self._h, wavefront_corr.family, dptr(wavefront_corr.params),
+                                                    len(wavefront_corr.params), time, int(l2only), C.byref(out)))
+                return out.value
+            d = wavefront_corr.FirstOrder() if self.fosystem else wavefront_corr
+            wavefront_corr = self.MakeWavefront(d, time)
+        if wavefront is None:
+            wavefront = self.GetWavefront()
+        fn = lib.ngst_twave_l2error if l2only else lib.ngst_twave_error
+        check(fn(self._h, dptr(f64(wavefront)), dptr(f64(wavefront_corr)), C.byref(out)))
         return out.value
 
-    def L2Error(self, wavefront, wavefront_corr):
-        out = C.c_double(0)
-        check(lib.ngst_twave_l2error(self._h, dptr(f64(wavefront)), dptr(f64(wavefront_corr)), C.byref(out)))
-        return out.value
+    def Error(self, wavefront, wavefront_corr, time=None):
+        """src/twavetents.cpp:766-800. wavefront None = the state resident on the device; wavefront_corr may be an
+        AnalyticData object, evaluated on the device at `time` (default: the solver's current time)."""
+        return self._error(wavefront, wavefront_corr, time, False)
+
+    def L2Error(self, wavefront, wavefront_corr, time=None):
+        """src/twavetents.cpp:802-822, same conventions as Error."""
+        return self._error(wavefront, wavefront_corr, time, True)
 
     def Energy(self, wavefront=None):
         out = C.c_double(0)

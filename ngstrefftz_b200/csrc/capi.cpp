@@ -397,6 +397,14 @@ int ngst_twave_error(ngst_twave* t, const double* wf, const double* wf_ref, doub
   });
 }
 
+int ngst_twave_error_analytic(ngst_twave* t, int family, const double* params, int nparams, double time, int l2only,
+                              double* out) {
+  return guarded([&] {
+    need(t, "solver"); need(out, "out");
+    *out = t->solver->ErrorAnalytic(family, params, nparams, time, l2only != 0);
+  });
+}
+
 int ngst_twave_l2error(ngst_twave* t, const double* wf, const double* wf_ref, double* out) {
   return guarded([&] {
     need(t, "solver"); need(wf, "wf"); need(wf_ref, "wf_ref"); need(out, "out");

@@ -847,6 +847,21 @@ double Solver::Error(const double* wf, const double* ref, bool l2only) {
   return std::sqrt(ReduceElements(d_tmp_a_, d_tmp_b_, l2only ? 2 : 1));
 }
 
+// Error / L2Error (twavetents.cpp:766-822) of the RESIDENT state against analytic data sampled on the device at `time`:
+// neither the state nor the exact solution crosses PCIe.
+double Solver::ErrorAnalytic(int family, const double* params, int nparams, double time, bool l2only) {
+  if (!have_initial_) throw std::logic_error("Error: SetInitial has not been called");
+  check_family(mesh_.D, family, params, nparams);
+  if (l2only && fosystem_) throw std::invalid_argument("L2Error: the first-order state has no u component");
+  CU(cudaSetDevice(device_));
+  const size_t bytes = (size_t)nel_ * ncomp_ * rule_.nip * sizeof(double);
+  if (!d_tmp_b_) CU(cudaMalloc(&d_tmp_b_, bytes));
+  double* d_p = UploadParams(params, nparams, &d_tmp_params_);
+  CU(launch_sample_wavefront(mesh_.D, family, d_p, nel_, rule_.nip, fosystem_, time, args_.pts, args_.el2v, args_.lam,
+                             d_tmp_b_, stream_));
+  return std::sqrt(ReduceElements(d_wavefront_, d_tmp_b_, l2only ? 2 : 1));
+}
+
 double Solver::MaxAdiam() const {
   double h = 0;
   for (double s : staged_.scale) h = std::max(h, 1.0 / s);

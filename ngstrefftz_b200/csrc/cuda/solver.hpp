@@ -65,6 +65,7 @@ class Solver {
   void SetInitialAnalytic(int family, const double* params, int nparams, int first_order);
   void MakeWavefrontAnalytic(int family, const double* params, int nparams, double time, int first_order, double* out);
   void SetBoundaryAnalytic(int family, const double* params, int nparams);
+  double ErrorAnalytic(int family, const double* params, int nparams, double time, bool l2only);
   void Propagate();
   void GetWavefront(double* out);
   double Energy(const double* wf);

@@ -100,6 +100,32 @@ def test_polynomial_is_reproduced_exactly():
     assert tw.Error(wf, exact) <= 1e-10 * np.sqrt(2 * tw.Energy(exact))
 
 
+@pytest.mark.parametrize("name", ["standing1", "standing2", "pulse3", "poly2"])
+@pytest.mark.parametrize("fo", [False, True])
+def test_error_against_device_sampled_exact_solution(name, fo):
+    """Error / L2Error of the resident state vs analytic data, all on the device, equal the host-array route."""
+    mesh, data, c = DATA[name]()
+    _, tw = solver(mesh, 4, c, 0.2)
+    tw.SetInitial(data.FirstOrder() if fo else data)
+    tw.SetBoundaryCF(data)
+    tw.Propagate()
+    d = data.FirstOrder() if fo else data
+    wf = tw.GetWavefront()
+    exact = tw.MakeWavefront(lambda x, t: d(x, t), tw.timeshift())
+    want = tw.Error(wf, exact)
+    got = tw.Error(None, data)
+    scale = np.sqrt(np.sum(exact ** 2)) + 1.0
+    assert abs(got - want) <= 1e-12 * scale, (got, want)
+    assert abs(tw.Error(wf, data) - want) <= 1e-12 * scale
+    if not fo:
+        assert abs(tw.L2Error(None, data) - tw.L2Error(wf, exact)) <= 1e-12 * scale
+    else:
+        with pytest.raises(ng.NgstError):
+            tw.L2Error(None, data)
+    # at another time the error is the distance of the two exact samples (triangle inequality, loose check)
+    assert tw.Error(None, data, time=0.0) > 0 or name.startswith("poly")
+
+
 def test_values_then_analytic_again():
     """propagate_with_values replaces the device-side datum for one slab; the next Propagate samples it again."""
     mesh, data, c = DATA["standing2"]()
