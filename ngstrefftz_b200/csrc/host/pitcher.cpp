@@ -108,8 +108,11 @@ class ReadyList {
     tmin_[node] = key;
     tcnt_[node] = cnt;
     for (node >>= 1; node >= 1; node >>= 1) {
-      tmin_[node] = std::min(tmin_[2 * node], tmin_[2 * node + 1]);
-      tcnt_[node] = tcnt_[2 * node] + tcnt_[2 * node + 1];
+      const int mn = std::min(tmin_[2 * node], tmin_[2 * node + 1]);
+      const int cn = tcnt_[2 * node] + tcnt_[2 * node + 1];
+      if (mn == tmin_[node] && cn == tcnt_[node]) break;  // nothing changes further up
+      tmin_[node] = mn;
+      tcnt_[node] = cn;
     }
   }
   void set_slot(int slot, int v) {
