@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--cpu-sample-tents", type=int, default=0, help="tents in the bounded CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-mirror", action="store_true", help="e2e arm: explicit get_wavefront copy instead of the output mirror")
     ap.add_argument("--no-device-data", action="store_true", help="skip the informational device-sampled-data arm")
     ap.add_argument("--partition", default="balanced", choices=["balanced", "brick"],
                     help="N>1: cost-balanced recursive bisection (default) or plain brick cut of the bounding box")
@@ -304,13 +305,27 @@ def run_ours(args):
         b_ptr = _capi.C.cast(b0.data_ptr(), _capi.c_dp) if b0 is not None else None
         nb = 0 if b0 is None else b0.numel()
 
-        def e2e_step():
+        # N=1: the result rows reach the host buffer through the output mirror (ngst_twave_set_output_mirror): each row is
+        # written to pin_out during Propagate as soon as it is final, so most of the D2H overlaps the remaining tents.
+        use_mirror = world == 1 and not args.no_mirror
+
+        def e2e_step(mirror=use_mirror):
             tw.reset_time()
             check(lib.ngst_twave_set_initial(tw._h, in_ptr, ncomp))               # H2D: state rows
             check(lib.ngst_twave_set_boundary_values(tw._h, b_ptr, nb))            # H2D: boundary samples
-            check(lib.ngst_twave_propagate(tw._h))
-            check(lib.ngst_twave_get_wavefront(tw._h, out_ptr))                    # D2H: state rows
+            check(lib.ngst_twave_propagate(tw._h))                                 # (+ D2H of final rows with the mirror)
+            if not mirror:
+                check(lib.ngst_twave_get_wavefront(tw._h, out_ptr))                # D2H: state rows
 
+        if use_mirror:
+            e2e_step(False)                      # reference result through the explicit copy
+            want = pin_out.numpy().copy()
+            pin_out.zero_()
+            check(lib.ngst_twave_set_output_mirror(tw._h, out_ptr))
+            e2e_step(True)
+            if not np.array_equal(pin_out.numpy(), want):
+                raise SystemExit("bench.py: output mirror differs from ngst_twave_get_wavefront")
+            del want
         for _ in range(args.warmup):
             e2e_step()
         barrier()
@@ -319,7 +334,9 @@ def run_ours(args):
             e2e_step()
         barrier()
         e2e_s = time.perf_counter() - t0
-        e2e = {"sec": e2e_s, "h2d": int(nbytes + nb * 8), "d2h": int(nbytes)}
+        e2e = {"sec": e2e_s, "h2d": int(nbytes + nb * 8), "d2h": int(nbytes), "mirror": use_mirror}
+        if use_mirror:
+            check(lib.ngst_twave_set_output_mirror(tw._h, None))
 
     # ---------------- informational: the same call sequence with initial and boundary data sampled ON THE DEVICE
     # (ngst_twave_*_analytic): no H2D of samples, same D2H. Not the e2e figure (that one copies
@@ -335,8 +352,12 @@ def run_ours(args):
                 tw.SetInitial(data)
                 tw.SetBoundaryCF(data)
                 check(lib.ngst_twave_propagate(tw._h))
-                check(lib.ngst_twave_get_wavefront(tw._h, out_ptr))
+                if not use_mirror:
+                    check(lib.ngst_twave_get_wavefront(tw._h, out_ptr))
 
+            if use_mirror:
+                tw.SetInitial(data)
+                check(lib.ngst_twave_set_output_mirror(tw._h, out_ptr))
             for _ in range(args.warmup):
                 dd_step()
             barrier()
@@ -349,9 +370,13 @@ def run_ours(args):
             device_data = {"value": len(mine) * args.steps / dd_s, "unit": "tents/s", "ms_per_step": dd_s / args.steps * 1e3,
                            "h2d_bytes_per_step": 0, "d2h_bytes_per_step": int(nbytes),
                            "max_rel_diff_vs_host_data": diff,
-                           "path": "ngst_twave_set_initial_analytic + set_boundary_analytic + propagate + get_wavefront"}
+                           "path": "ngst_twave_set_initial_analytic + set_boundary_analytic + propagate + "
+                                   + ("output mirror" if use_mirror else "get_wavefront")}
         except Exception as ex:  # informational arm: never takes the bench line down
             device_data = {"error": repr(ex)}
+        finally:
+            if use_mirror:
+                lib.ngst_twave_set_output_mirror(tw._h, None)
 
     # ---------------- reduce over ranks (max time, sum units)
     ntents_local = len(mine)
@@ -447,7 +472,10 @@ def run_ours(args):
         line["e2e"] = {"value": tents_step * args.steps / e2e_s, "unit": "tents/s",
                        "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"],
                        "ms_per_step": 1e3 * e2e_s / args.steps,
-                       "path": "ngst_twave_set_initial + set_boundary_values + propagate + get_wavefront on pinned host buffers"}
+                       "path": ("ngst_twave_set_initial + set_boundary_values + propagate on pinned host buffers, result rows "
+                                "streamed into the host buffer during propagate (ngst_twave_set_output_mirror; checked bitwise "
+                                "against ngst_twave_get_wavefront before timing)") if e2e.get("mirror") else
+                               "ngst_twave_set_initial + set_boundary_values + propagate + get_wavefront on pinned host buffers"}
     if device_data:
         line["device_data"] = device_data
     if not args.no_cpu_baseline and world == 1:

@@ -169,6 +169,13 @@ double ngst_twave_last_ms(const ngst_twave* t);
 int ngst_twave_last_launches(const ngst_twave* t);
 /* GetWavefront src/twavetents.hpp:193: copy of the nel x (ncomp*nip) state to a host buffer */
 int ngst_twave_get_wavefront(ngst_twave* t, double* out);
+/* Output mirror (no reference counterpart; the fused form of Propagate + GetWavefront src/twavetents.hpp:193): `host`
+ * (nel x ncomp*nip doubles; page-locked and mapped by the call if it is plain pageable memory) receives every state row
+ * during ngst_twave_propagate as soon as the last tent that contains its element has run, over PCIe while the remaining
+ * tents are solved; when ngst_twave_propagate returns it holds exactly what ngst_twave_get_wavefront would copy. The
+ * buffer must stay valid until the mirror is switched off (host == NULL), ngst_twave_set_initial changes the row length,
+ * or the solver is destroyed. Call after ngst_twave_set_initial. Single-GPU solvers only. */
+int ngst_twave_set_output_mirror(ngst_twave* t, double* host);
 /* GetWave src/__init__.py:7-43 (per-element L2 projection of the quadrature-point state, IntegrationPointFunction
  * src/specialcoefficientfunction.cpp:48-172): second-order state -> u onto polynomials of degree p (1 component),
  * first-order state -> (grad u, d_t u) onto degree p-1 (D+1 components). The basis is orthonormal on the reference

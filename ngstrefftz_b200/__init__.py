@@ -647,6 +647,20 @@ class TWaveTents(TrefftzTents):
                     return np.ascontiguousarray(wf.reshape(len(wf), ncomp, snip)[:, :, :self.nip].reshape(len(wf), -1))
         raise ValueError("wavefront width does not match (D+1 or D+2) component blocks of >= nip points")
 
+    def SetOutputMirror(self, out):
+        """Stream the state rows into the host array `out` (C-contiguous float64, nel x ncomp*nip) during Propagate, each
+        row as soon as it is final (cuda/mirror.cu): after Propagate `out` equals GetWavefront() without a separate
+        device-to-host copy. None switches the mirror off. Call after SetInitial."""
+        if out is None:
+            check(lib.ngst_twave_set_output_mirror(self._h, None))
+            self._mirror = None
+            return
+        if not (isinstance(out, np.ndarray) and out.dtype == np.float64 and out.flags.c_contiguous and out.flags.writeable
+                and out.size == self.nel * self.ncomp * self.nip):
+            raise ValueError("SetOutputMirror: need a writeable C-contiguous float64 array of nel * ncomp * nip entries")
+        check(lib.ngst_twave_set_output_mirror(self._h, dptr(out)))
+        self._mirror = out  # keeps the page-locked buffer alive as long as the solver writes to it
+
     def GetWavefront(self):
         wf = np.zeros((self.nel, self.ncomp * self.nip))
         check(lib.ngst_twave_get_wavefront(self._h, dptr(wf)))

@@ -386,6 +386,10 @@ int ngst_twave_get_wave(ngst_twave* t, int* sizes, double* coef, double* psi_at_
   return guarded([&] { need(t, "solver"); t->solver->GetWave(sizes, coef, psi_at_points, mono_coef, expo); });
 }
 
+int ngst_twave_set_output_mirror(ngst_twave* t, double* host) {
+  return guarded([&] { need(t, "solver"); t->solver->SetOutputMirror(host); });
+}
+
 int ngst_twave_energy(ngst_twave* t, const double* wf, double* out) {
   return guarded([&] { need(t, "solver"); need(out, "out"); *out = t->solver->Energy(wf); });
 }

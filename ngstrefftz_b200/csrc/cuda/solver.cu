@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <stdexcept>
 
 namespace ngst {
@@ -356,6 +357,10 @@ Solver::~Solver() {
   for (void* p : allocs_) cudaFree(p);
   if (d_wavefront_) cudaFree(d_wavefront_);
   if (d_bnd_) cudaFree(d_bnd_);
+  ReleaseMirror();
+  if (stream_mirror_) cudaStreamDestroy(stream_mirror_);
+  if (ev_level_) cudaEventDestroy(ev_level_);
+  if (ev_mirror_) cudaEventDestroy(ev_mirror_);
   if (d_bnd_params_) cudaFree(d_bnd_params_);
   if (d_tmp_params_) cudaFree(d_tmp_params_);
   if (d_tmp_a_) cudaFree(d_tmp_a_);
@@ -432,6 +437,7 @@ void Solver::SetInitial(const double* wf, int ncomp) {
   ncomp_ = ncomp;
   basis_ = fosystem_ ? basis_fo_ : basis_so_;
   const size_t bytes = (size_t)nel_ * ncomp * rule_.nip * sizeof(double);
+  if (wavefront_bytes_ != bytes) ReleaseMirror();  // the mirror buffer was sized for the previous row length
   if (d_wavefront_ && wavefront_bytes_ != bytes) { CU(cudaFree(d_wavefront_)); d_wavefront_ = nullptr; }
   if (!d_wavefront_) { CU(cudaMalloc(&d_wavefront_, bytes)); wavefront_bytes_ = bytes; }
   if (wf) {
@@ -577,6 +583,7 @@ void Solver::Propagate() {
                               args_.tf_verts, args_.tf_data, args_.lam, kNeumann, d_bnd_, stream_));
     launches++;
   }
+  if (mirror_dev_) MirrorRows(-1, -1, launches);  // rows no tent touches are final from the start
   for (int l = 0; l < nlev && qt_; l++) {
     // quasi-Trefftz: fast monomial-space DMMA kernel where a variant exists (second-order form, causal top faces),
     // generic kernel otherwise
@@ -600,6 +607,7 @@ void Solver::Propagate() {
       launches++;
     }
     if (comm_) launches += ExchangeLevel(l, stream_);
+    if (mirror_dev_) MirrorRows(l, l, launches);
   }
   for (int l = 0; l < nlev && force_generic_ && !qt_; l++) {
     TentKernelArgs a = args_;
@@ -610,6 +618,7 @@ void Solver::Propagate() {
       launches++;
     }
     if (comm_) launches += ExchangeLevel(l, stream_);
+    if (mirror_dev_) MirrorRows(l, l, launches);
   }
   // Measured on B200 (profiles/r01o): with ~2700 tents per level (config 4) the single launch is 3 % slower than one launch
   // per level (waiting CTAs hold SM slots and poll), with small levels it removes the launch gaps and tails.
@@ -627,6 +636,7 @@ void Solver::Propagate() {
     a.succ = d_succ_;
     CU(launch_tent_fast(mesh_.D, order_, fosystem_, a, fargs_, stream_));
     launches++;
+    if (mirror_dev_) MirrorRows(0, nlev - 1, launches);  // single launch per slab: nothing to overlap with
   }
   const bool overlap = comm_ && !force_generic_ && !qt_ && overlap_;
   if (overlap && !stream_halo_) {
@@ -671,8 +681,13 @@ void Solver::Propagate() {
     }
     if (overlap) CU(cudaEventRecord(ev_int_, stream_));
     else if (comm_) launches += ExchangeLevel(l, stream_);
+    if (mirror_dev_) MirrorRows(l, l, launches);
   }
   if (overlap) CU(cudaStreamWaitEvent(stream_, ev_halo_, 0));
+  if (mirror_dev_) {  // the slab is done when the last rows have reached the host buffer
+    CU(cudaEventRecord(ev_mirror_, stream_mirror_));
+    CU(cudaStreamWaitEvent(stream_, ev_mirror_, 0));
+  }
   CU(cudaEventRecord(ev1_, stream_));
   CU(cudaEventSynchronize(ev1_));
   float ms = 0;
@@ -712,6 +727,85 @@ int Solver::ExchangeLevel(int l, cudaStream_t stream) {
   comm_->Exchange(d_wavefront_, rowlen, d_send_el_ + p.send_off[(size_t)l * nr], sc.data(),
                   d_recv_el_ + p.recv_off[(size_t)l * nr], rc.data(), d_sendbuf_, d_recvbuf_, stream);
   return (ns > 0) + (nrv > 0);
+}
+
+void Solver::ReleaseMirror() {
+  if (mirror_host_) {
+    cudaSetDevice(device_);
+    if (stream_mirror_) cudaStreamSynchronize(stream_mirror_);
+    if (mirror_registered_) cudaHostUnregister(mirror_host_);
+  }
+  mirror_host_ = nullptr;
+  mirror_dev_ = nullptr;
+  mirror_registered_ = false;
+  mirror_bytes_ = 0;
+}
+
+void Solver::SetOutputMirror(double* host) {
+  CU(cudaSetDevice(device_));
+  ReleaseMirror();
+  if (!host) return;
+  if (plan_) throw std::invalid_argument("SetOutputMirror: partitioned (multi-GPU) solvers are not supported");
+  if (!have_initial_) throw std::logic_error("SetOutputMirror: SetInitial has not been called (row length unknown)");
+  const size_t bytes = (size_t)nel_ * ncomp_ * rule_.nip * sizeof(double);
+  cudaPointerAttributes attr{};
+  if (cudaPointerGetAttributes(&attr, host) != cudaSuccess) {
+    cudaGetLastError();
+    attr.type = cudaMemoryTypeUnregistered;
+  }
+  if (attr.type == cudaMemoryTypeUnregistered) {
+    CU(cudaHostRegister(host, bytes, cudaHostRegisterMapped));  // pageable memory of the caller: page-lock and map it
+    mirror_registered_ = true;
+  } else if (attr.type != cudaMemoryTypeHost) {
+    throw std::invalid_argument("SetOutputMirror: the buffer must be host memory");
+  }
+  mirror_host_ = host;
+  mirror_bytes_ = bytes;
+  void* dev = nullptr;
+  cudaError_t e = cudaHostGetDevicePointer(&dev, host, 0);
+  if (e != cudaSuccess) {
+    ReleaseMirror();
+    cuda_check(e, "cudaHostGetDevicePointer (is the buffer mapped, page-locked memory?)");
+  }
+  mirror_dev_ = static_cast<double*>(dev);
+  if (!stream_mirror_) {
+    int lo = 0, hi = 0;
+    CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CU(cudaStreamCreateWithPriority(&stream_mirror_, cudaStreamNonBlocking, hi));
+    CU(cudaEventCreateWithFlags(&ev_level_, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&ev_mirror_, cudaEventDisableTiming));
+  }
+  if (!d_final_rows_) {
+    // level of the last tent that contains each element (the tents of one level touch disjoint elements)
+    const int nlev = (int)slab_.level_off.size() - 1;
+    std::vector<int> last(nel_, -1);
+    for (int t = 0; t < staged_.ntents; t++)
+      for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++) {
+        int& l = last[staged_.te_el[te]];
+        l = std::max(l, slab_.level[t]);
+      }
+    final_off_.assign(nlev + 2, 0);
+    for (int el = 0; el < nel_; el++) final_off_[last[el] + 2]++;
+    for (int i = 0; i < nlev + 1; i++) final_off_[i + 1] += final_off_[i];
+    std::vector<int> rows(nel_), pos(final_off_.begin(), final_off_.end() - 1);
+    for (int el = 0; el < nel_; el++) rows[pos[last[el] + 1]++] = el;
+    d_final_rows_ = Upload(rows);
+  }
+}
+
+void Solver::MirrorRows(int first_level, int last_level, int& launches) {
+  const int b = final_off_[first_level + 1], e = final_off_[last_level + 2];
+  if (e <= b) return;
+  CU(cudaEventRecord(ev_level_, stream_));
+  CU(cudaStreamWaitEvent(stream_mirror_, ev_level_, 0));
+  // a few CTAs keep PCIe busy (16 KB in flight each); each takes the place of one tent CTA (of 3 per SM) while it runs
+  static const int ctas = [] {
+    const char* s = std::getenv("NGST_MIRROR_CTAS");  // tuning knob (profiles/r03c)
+    const int v = s ? std::atoi(s) : 0;
+    return v > 0 ? v : 24;
+  }();
+  CU(launch_mirror_rows(d_final_rows_ + b, e - b, ncomp_ * rule_.nip, d_wavefront_, mirror_dev_, ctas, stream_mirror_));
+  launches++;
 }
 
 void Solver::GetWavefront(double* out) {

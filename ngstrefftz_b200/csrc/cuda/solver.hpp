@@ -68,6 +68,10 @@ class Solver {
   double ErrorAnalytic(int family, const double* params, int nparams, double time, bool l2only);
   void Propagate();
   void GetWavefront(double* out);
+  // Output mirror (cuda/mirror.cu): `host` (nel x ncomp*nip doubles; page-locked here if it is not already) receives every
+  // state row as soon as it is final during Propagate, overlapped with the remaining tents; when Propagate returns it
+  // holds what GetWavefront would copy. nullptr switches the mirror off. Single-GPU solvers only.
+  void SetOutputMirror(double* host);
   double Energy(const double* wf);
   double Error(const double* wf, const double* ref, bool l2only);
   double MaxAdiam() const;
@@ -149,6 +153,16 @@ class Solver {
   double* d_cval_[2] = {nullptr, nullptr};
   double* d_wavefront_ = nullptr;
   double* d_bnd_ = nullptr;
+  double* mirror_host_ = nullptr;   // caller's buffer, its device alias, and whether this solver page-locked it
+  double* mirror_dev_ = nullptr;
+  bool mirror_registered_ = false;
+  size_t mirror_bytes_ = 0;
+  int* d_final_rows_ = nullptr;     // local elements ordered by the level of the last tent that contains them
+  std::vector<int> final_off_;      // nlevels + 2 offsets: [0] rows no tent touches, [l + 1] rows final after level l
+  cudaStream_t stream_mirror_ = nullptr;
+  cudaEvent_t ev_level_ = nullptr, ev_mirror_ = nullptr;
+  void ReleaseMirror();
+  void MirrorRows(int first_level, int last_level, int& launches);  // rows final after levels first..last (-1 = untouched)
   int bnd_family_ = -1;            // >= 0: analytic boundary datum (AnalyticFamily), sampled on the device per slab
   double* d_bnd_params_ = nullptr;
   double* d_tmp_params_ = nullptr;
@@ -177,6 +191,8 @@ size_t tent_generic_smem_bytes(int D, const TentKernelArgs& a);
 cudaError_t launch_tent_generic(int D, const TentKernelArgs& a, int threads, size_t smem, cudaStream_t stream);
 cudaError_t launch_project_rows(int nel, int Q, int ndof, int comp0, int ncomp_used, int rowlen, const double* P,
                                 const double* wf, double* out, cudaStream_t stream);
+cudaError_t launch_mirror_rows(const int* rows, int nrows, int rowlen, const double* wf, double* host_alias, int ctas,
+                               cudaStream_t stream);
 cudaError_t launch_element_reduce(int mode, int D, int nel, int Q, int ncomp, int fosystem, const double* elw,
                                   const double* c_el, const double* c_point, const double* a, const double* b,
                                   double* out, cudaStream_t stream);
