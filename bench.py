@@ -309,7 +309,8 @@ def run_ours(args):
         # written to pin_out during Propagate as soon as it is final, so most of the D2H overlaps the remaining tents.
         use_mirror = world == 1 and not args.no_mirror
 
-        def e2e_step(mirror=use_mirror):
+        def e2e_step(mirror=None):
+            mirror = use_mirror if mirror is None else mirror
             tw.reset_time()
             check(lib.ngst_twave_set_initial(tw._h, in_ptr, ncomp))               # H2D: state rows
             check(lib.ngst_twave_set_boundary_values(tw._h, b_ptr, nb))            # H2D: boundary samples
@@ -324,7 +325,11 @@ def run_ours(args):
             check(lib.ngst_twave_set_output_mirror(tw._h, out_ptr))
             e2e_step(True)
             if not np.array_equal(pin_out.numpy(), want):
-                raise SystemExit("bench.py: output mirror differs from ngst_twave_get_wavefront")
+                # never observed; do not time a path whose result is wrong: go back to the explicit copy and say so
+                print("bench.py: output mirror differs from ngst_twave_get_wavefront; timing the explicit copy",
+                      file=sys.stderr)
+                check(lib.ngst_twave_set_output_mirror(tw._h, None))
+                use_mirror = False
             del want
         for _ in range(args.warmup):
             e2e_step()
