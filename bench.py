@@ -160,6 +160,8 @@ def cpu_sample(args, cells, sample_tents, steps, warmup, nthreads):
     nels = np.diff(e["el_off"])[order]
     times = []
     for i in range(warmup + steps):
+        if i == warmup:
+            o.phase_timing(True)  # per-phase thread-seconds of the timed passes (reference Timer names)
         t0 = time.perf_counter()
         o.propagate(nthreads=nthreads, ntents_limit=sample_tents)
         t1 = time.perf_counter()
@@ -167,8 +169,11 @@ def cpu_sample(args, cells, sample_tents, steps, warmup, nthreads):
             times.append(t1 - t0)
     sec = float(np.sum(times))
     tents = sample_tents * len(times)
+    ph = o.phase_times()
+    total = ph["tent"] or 1.0
+    phases = {k: {"thread_s": round(v, 4), "share_of_tent": round(v / total, 4)} for k, v in ph.items()}
     return {"tents_per_s": tents / sec, "sec_per_step": sec / max(len(times), 1), "sample_tents": int(sample_tents),
-            "slab_tents": int(nt), "nbasis": o.nbasis(), "tent_elements": int(nels.sum())}
+            "slab_tents": int(nt), "nbasis": o.nbasis(), "tent_elements": int(nels.sum()), "phases": phases}
 
 
 def run_reference(args):
@@ -192,7 +197,8 @@ def run_reference(args):
         "cpu_baseline": {"value": r["tents_per_s"], "unit": "tents/s", "cores": cores, "kind": "port",
                          "sample": f"first {r['sample_tents']} tents (level order) of the {r['slab_tents']}-tent slab "
                                    f"per step; oracle restatement of the reference's Propagate, OpenMP over the tents of "
-                                   f"a level; the reference itself needs NGSolve (unbuildable here)"},
+                                   f"a level; the reference itself needs NGSolve (unbuildable here)",
+                         "phases": r["phases"]},
         "e2e": {"value": r["tents_per_s"], "unit": "tents/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -490,7 +496,8 @@ def run_ours(args):
         line["cpu_baseline"] = {"value": r["tents_per_s"], "unit": "tents/s", "cores": cores, "kind": "port",
                                 "sample": f"first {r['sample_tents']} tents (level order) of the N=1 slab "
                                           f"({r['slab_tents']} tents), 1 warm-up + 1 timed pass, oracle restatement of "
-                                          f"the reference's Propagate with OpenMP over the tents of a level"}
+                                          f"the reference's Propagate with OpenMP over the tents of a level",
+                                "phases": r["phases"]}
     _RESULT.append(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

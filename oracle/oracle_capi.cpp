@@ -216,6 +216,19 @@ int oracle_propagate(void* hp, int nthreads, int ntents_limit) {
   h->tw->singular = 0;
   return s ? -2 : 0;
 }
+// Per-phase timers of the plain Trefftz path (names of twavetents.cpp:84-88, 186-188): on != 0 switches them on and
+// clears them; out[7] = thread-seconds {calcshape, AAt, bilinearform, tentel, solve, tenteval, tent} since then.
+void oracle_set_phase_timing(void* hp, int on) {
+  auto* tw = ((OracleHandle*)hp)->tw.get();
+  if (!tw) return;
+  tw->phase_timing = on != 0;
+  for (double& v : tw->phase_sec) v = 0.0;
+}
+void oracle_get_phase_times(void* hp, double* out) {
+  auto* tw = ((OracleHandle*)hp)->tw.get();
+  for (int k = 0; k < 7; k++) out[k] = tw ? tw->phase_sec[k] : 0.0;
+}
+
 void oracle_get_wavefront(void* hp, double* out) {
   auto* h = (OracleHandle*)hp;
   std::memcpy(out, h->tw->wavefront.d.data(), sizeof(double) * h->tw->wavefront.d.size());

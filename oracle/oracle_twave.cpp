@@ -13,6 +13,7 @@
 // (pad points carry zero weight in the reference and contribute nothing to elmat / elvec).
 // Tents are run level by level with OpenMP over the tents of a level; the reference's RunParallelDependency
 // (paralleldepend.hpp:20-131) yields the same result because concurrently running tents never share elements.
+#include <chrono>
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -264,6 +265,18 @@ struct TWaveTents {
   std::vector<long long> bd_offset;  // per tent: offset into bddata of its first boundary facet
   bool have_bd = false;
   double timeshift = 0;
+  // Per-phase thread-seconds with the reference's timer names (twavetents.cpp:84-88, 186-188): [0] "tent top calcshape",
+  // [1] "tent top AAt", [2] "tent top bilinearform", [3] "tentel" (all of CalcTentEl), [4] solve, [5] "tenteval",
+  // [6] "tent" (whole tent). Filled only when phase_timing is set; bench.py reports them beside the CPU baseline.
+  bool phase_timing = false;
+  mutable double phase_sec[7] = {0, 0, 0, 0, 0, 0, 0};
+  static double Now() {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+  }
+  void AddPhase(int k, double sec) const {
+#pragma omp atomic
+    phase_sec[k] += sec;
+  }
   PolIndex pix;
   int singular = 0;
   // wavespeed per (element, quadrature point) for Energy / Error (the reference evaluates the CF at every point,
@@ -448,6 +461,7 @@ struct TWaveTents {
   void CalcTentEl(int elnr, const OTent& tent, MappedElement& tel, double c, double* elmat, int ld, double* elvec,
                   Matrix& topdshapes, const double* cpt = nullptr) const {
     const int d1 = D + 1;
+    const double t_el = phase_timing ? Now() : 0.0;
     Matrix pts(snip, d1);
     Vert vert = TentFaceVerts(tent, elnr, -1);
     ElementPoints(elnr, vert, pts);
@@ -489,7 +503,9 @@ struct TWaveTents {
 
     vert = TentFaceVerts(tent, elnr, 1);
     ElementPoints(elnr, vert, pts);
+    const double t1 = phase_timing ? Now() : 0.0;
     tel.CalcDShape(pts, bbmat);
+    const double t2 = phase_timing ? Now() : 0.0;
     area = TentFaceArea(vert);
     n = TentFaceNormal(vert, 1);
     Matrix bdbmat(d1 * snip, nbasis);
@@ -504,8 +520,16 @@ struct TWaveTents {
         }
       }
     }
+    const double t3 = phase_timing ? Now() : 0.0;
     AddAB(bbmat, bdbmat, elmat, ld);
+    const double t4 = phase_timing ? Now() : 0.0;
     topdshapes = bbmat;
+    if (phase_timing) {
+      AddPhase(0, t2 - t1);
+      AddPhase(1, t3 - t2);
+      AddPhase(2, t4 - t3);
+      AddPhase(3, Now() - t_el);
+    }
   }
 
   // invc2: 1/c^2 per boundary point (the reference evaluates the wavespeed CF there, twavetents.cpp:409-412); nullptr = 1/cadj^2
@@ -658,6 +682,7 @@ struct TWaveTents {
   void PropagateTent(int tentnr, const CSR& basismat) {
     const OTent& tent = tps->tents[tentnr];
     const int d1 = D + 1;
+    const double t_tent = phase_timing ? Now() : 0.0;
     MappedElement tel;
     tel.d1 = d1; tel.ndof = nbasis; tel.order = order; tel.npoly = BinCoeff(d1 + order, order);
     tel.localmat = &basismat; tel.pix = &pix;
@@ -698,6 +723,7 @@ struct TWaveTents {
     }
 
     // Solve: inverse, then multiply (twavetents.cpp:64-70)
+    const double t_solve = phase_timing ? Now() : 0.0;
     if (!CalcInverseLapack(elmat.data(), n)) {
 #pragma omp atomic
       singular++;
@@ -708,10 +734,17 @@ struct TWaveTents {
       for (int j = 0; j < n; j++) s += elmat[(size_t)i * n + j] * elvec[j];
       sol[i] = s;
     }
+    const double t_eval = phase_timing ? Now() : 0.0;
     for (size_t elnr = 0; elnr < tent.els.size(); elnr++) {
       SetWavespeed(tel, wavespeed[tent.els[elnr]]);
       const int eli = ndomains > 1 ? macroel[tent.els[elnr]] : 0;
       CalcTentElEval(tent.els[elnr], tent, tel, &sol[eli * nbasis], topdshapes[elnr]);
+    }
+    if (phase_timing) {
+      const double t_end = Now();
+      AddPhase(4, t_eval - t_solve);
+      AddPhase(5, t_end - t_eval);
+      AddPhase(6, t_end - t_tent);
     }
   }
 

@@ -55,6 +55,8 @@ def _load():
     lib.oracle_set_boundary_values.argtypes = [C.c_void_p, c_dp, C.c_longlong]
     lib.oracle_propagate.argtypes = [C.c_void_p, C.c_int, C.c_int]
     lib.oracle_get_wavefront.argtypes = [C.c_void_p, c_dp]
+    lib.oracle_set_phase_timing.argtypes = [C.c_void_p, C.c_int]
+    lib.oracle_get_phase_times.argtypes = [C.c_void_p, c_dp]
     for f in ("oracle_timeshift", "oracle_max_adiam"):
         getattr(lib, f).restype = C.c_double
         getattr(lib, f).argtypes = [C.c_void_p]
@@ -270,6 +272,18 @@ class Oracle:
             raise ArithmeticError("oracle: singular local system")
         if rc:
             raise RuntimeError(lib.oracle_last_error().decode())
+
+    PHASES = ("tent top calcshape", "tent top AAt", "tent top bilinearform", "tentel", "solve", "tenteval", "tent")
+
+    def phase_timing(self, on=True):
+        """Switch the per-phase timers (the reference's Timer names, src/twavetents.cpp:84-88, 186-188) on / off and clear them."""
+        lib.oracle_set_phase_timing(self.h, int(bool(on)))
+
+    def phase_times(self):
+        """Thread-seconds per phase since phase_timing(True)."""
+        out = np.zeros(7)
+        lib.oracle_get_phase_times(self.h, _dp(out))
+        return dict(zip(self.PHASES, out.tolist()))
 
     def wavefront(self):
         out = np.zeros((self.nel, self.ncomp * self.nip))
