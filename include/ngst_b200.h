@@ -201,6 +201,14 @@ int ngst_device_fp64_peak(int device, int which, double* tflops);
 /* host-only helpers exposed for tests (no device needed) */
 int ngst_basis(int D, int order, int fowave, int* sizes, int* rowptr, int* col, double* val, int* expo);
 int ngst_rule(int dim, int order, int* nip, double* xi, double* w);
+/* Install a rule table dumped from a real NGSolve install (IntegrationRule(eltyp, order) points and weights, without the
+ * zero-weight SIMD pad points) in place of the restated rule of (dim, order): every solver
+ * created afterwards samples, stores and exchanges its state at these points in this order, so that wavefront matrices
+ * correspond column for column to the reference's (src/twavetents.cpp:77, 739). The table must have as many points as the
+ * built-in rule (the kernels are sized for it), positive weights, and integrate all monomials of total degree <= order
+ * exactly (checked to 1e-11 relative); otherwise NGST_ERR_ARG. nip == 0 removes the override. ngst_rule returns the rule in
+ * force. */
+int ngst_rule_override(int dim, int order, int nip, const double* xi, const double* w);
 /* compact fully symmetric rule exact to `degree` (top-face Gram of the fast kernel; no reference counterpart); falls back
  * to ngst_rule(dim, degree) where no table exists */
 int ngst_compact_rule(int dim, int degree, int* nip, double* xi, double* w);

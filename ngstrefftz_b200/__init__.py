@@ -26,7 +26,8 @@ from ._analytic import AnalyticData, PlanePulse, PolynomialWave, StandingWave
 
 __all__ = ["Mesh", "SegMesh", "UnitSquareMesh", "UnitCubeMesh", "StructuredMesh", "TentSlab", "Tent", "TWave",
            "TrefftzTents", "TWaveTents", "TaskManager", "SetNumThreads", "NgstError", "PolynomialCF",
-           "AnalyticData", "StandingWave", "PlanePulse", "PolynomialWave"]
+           "AnalyticData", "StandingWave", "PlanePulse", "PolynomialWave",
+           "GetIntegrationRule", "SetIntegrationRule"]
 
 
 class TaskManager:
@@ -740,6 +741,34 @@ class TWaveTents(TrefftzTents):
 
     def last_launches(self):
         return lib.ngst_twave_last_launches(self._h)
+
+
+def GetIntegrationRule(dim, order):
+    """(points[nip, dim], weights[nip]) of the rule in force for the reference simplex of dimension `dim` and the given
+    order (the solver of polynomial order p samples its state at the rule of order 2p)."""
+    nip = C.c_int(0)
+    check(lib.ngst_rule(int(dim), int(order), C.byref(nip), None, None))
+    xi, w = np.zeros((nip.value, int(dim))), np.zeros(nip.value)
+    check(lib.ngst_rule(int(dim), int(order), C.byref(nip), dptr(xi), dptr(w)))
+    return xi, w
+
+
+def SetIntegrationRule(dim, order, points=None, weights=None):
+    """Install a rule table dumped from a real NGSolve install, e.g.
+        ir = IntegrationRule(TET, 8); points = [list(p.point) for p in ir]; weights = [p.weight for p in ir]
+    for every solver created afterwards (ngst_rule_override): wavefront matrices then correspond
+    column for column to the reference's. points=None restores the built-in rule. The table is validated (point count of
+    the built-in rule, positive weights, exact to `order`); a rejected table raises NgstError."""
+    if int(dim) not in (1, 2, 3):
+        raise ValueError("SetIntegrationRule: dim must be 1, 2 or 3")
+    if points is None:
+        check(lib.ngst_rule_override(int(dim), int(order), 0, None, None))
+        return
+    xi = np.ascontiguousarray(f64(points).reshape(-1, int(dim)))
+    w = f64(weights).reshape(-1)
+    if len(w) != len(xi):
+        raise ValueError("SetIntegrationRule: as many weights as points")
+    check(lib.ngst_rule_override(int(dim), int(order), len(w), dptr(xi), dptr(w)))
 
 
 def brick_vertex_owner(mesh, grid):

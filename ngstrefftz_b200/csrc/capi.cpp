@@ -460,6 +460,14 @@ int ngst_rule(int dim, int order, int* nip, double* xi, double* w) {
   });
 }
 
+int ngst_rule_override(int dim, int order, int nip, const double* xi, const double* w) {
+  return guarded([&] {
+    try { set_simplex_rule_override(dim, order, nip, xi, w); }
+    catch (const std::invalid_argument&) { throw; }
+    catch (const std::runtime_error& e) { throw std::invalid_argument(e.what()); }
+  });
+}
+
 int ngst_compact_rule(int dim, int degree, int* nip, double* xi, double* w) {
   return guarded([&] {
     SimplexRule r;

@@ -2,7 +2,11 @@
 
 #include <algorithm>
 #include <cmath>
+#include <map>
+#include <mutex>
 #include <stdexcept>
+#include <string>
+#include <utility>
 
 namespace ngst {
 
@@ -97,7 +101,67 @@ void gauss_jacobi01(int n, int alpha, std::vector<double>& x, std::vector<double
   }
 }
 
+namespace {
+std::mutex g_override_mutex;
+std::map<std::pair<int, int>, SimplexRule> g_override;
+}  // namespace
+
 SimplexRule make_simplex_rule(int dim, int order) {
+  {
+    std::lock_guard<std::mutex> lock(g_override_mutex);
+    auto it = g_override.find({dim, order});
+    if (it != g_override.end()) return it->second;
+  }
+  return default_simplex_rule(dim, order);
+}
+
+void set_simplex_rule_override(int dim, int order, int nip, const double* xi, const double* w) {
+  const SimplexRule def = default_simplex_rule(dim, order);  // validates dim / order
+  std::lock_guard<std::mutex> lock(g_override_mutex);
+  if (nip == 0) {
+    g_override.erase({dim, order});
+    return;
+  }
+  if (nip != def.nip)
+    throw std::invalid_argument("rule override: the table must have " + std::to_string(def.nip) + " points (the default rule's)");
+  if (!xi || !w) throw std::invalid_argument("rule override: null table");
+  SimplexRule r;
+  r.dim = dim;
+  r.nip = nip;
+  r.xi.assign(xi, xi + (size_t)nip * dim);
+  r.w.assign(w, w + nip);
+  for (int q = 0; q < nip; q++) {
+    if (!(r.w[q] > 0)) throw std::invalid_argument("rule override: weights must be positive");
+    double s = 0;
+    for (int d = 0; d < dim; d++) {
+      const double x = r.xi[(size_t)q * dim + d];
+      if (!(x >= 0 && x <= 1)) throw std::invalid_argument("rule override: point outside the reference simplex");
+      s += x;
+    }
+    if (s > 1 + 1e-14) throw std::invalid_argument("rule override: point outside the reference simplex");
+  }
+  // exactness: integral of x^a over the reference simplex = prod a_i! / (dim + |a|)!
+  auto fact = [](int n) { double f = 1; for (int i = 2; i <= n; i++) f *= i; return f; };
+  int a[3] = {0, 0, 0};
+  for (a[0] = 0; a[0] <= order; a[0]++)
+    for (a[1] = 0; a[1] <= (dim > 1 ? order - a[0] : 0); a[1]++)
+      for (a[2] = 0; a[2] <= (dim > 2 ? order - a[0] - a[1] : 0); a[2]++) {
+        const int deg = a[0] + a[1] + a[2];
+        double exact = 1.0 / fact(dim + deg);
+        for (int d = 0; d < dim; d++) exact *= fact(a[d]);
+        double sum = 0;
+        for (int q = 0; q < nip; q++) {
+          double v = r.w[q];
+          for (int d = 0; d < dim; d++) v *= std::pow(r.xi[(size_t)q * dim + d], a[d]);
+          sum += v;
+        }
+        if (std::fabs(sum - exact) > 1e-11 * exact)
+          throw std::invalid_argument("rule override: the table does not integrate degree " + std::to_string(deg) + " exactly");
+      }
+  g_override[{dim, order}] = std::move(r);
+}
+
+SimplexRule default_simplex_rule(int dim, int order) {
   if (dim < 1 || dim > 3) throw std::runtime_error("make_simplex_rule: dim must be 1..3");
   if (order < 0) throw std::runtime_error("make_simplex_rule: negative order");
   const int n = order / 2 + 1;
@@ -163,7 +227,7 @@ SimplexRule make_compact_rule(int dim, int degree) {
         for (int d = 0; d < dim; d++) r.xi.push_back(t.bary[(size_t)q * (dim + 1) + d]);
       return r;
     }
-  return make_simplex_rule(dim, degree);
+  return default_simplex_rule(dim, degree);
 }
 
 }  // namespace ngst

@@ -23,7 +23,17 @@ struct SimplexRule {
 // n-point Gauss-Jacobi rule for weight (1-x)^alpha on [0,1] (alpha = 0: Gauss-Legendre).
 void gauss_jacobi01(int n, int alpha, std::vector<double>& x, std::vector<double>& w);
 
+// The rule the solver samples the state at: an installed override (below) if there is one, else default_simplex_rule.
 SimplexRule make_simplex_rule(int dim, int order);
+// The restated NGSolve convention described above, never overridden.
+SimplexRule default_simplex_rule(int dim, int order);
+
+// Rule tables dumped from a real NGSolve install: replaces the rule of (dim, order) for every solver
+// created afterwards, so that wavefront columns correspond point for point to the reference's. The table must have the
+// default rule's number of points (the kernels are sized for it), positive weights, and integrate every monomial of
+// total degree <= order exactly (checked to 1e-11 relative; throws std::invalid_argument otherwise). nip == 0 removes
+// the override.
+void set_simplex_rule_override(int dim, int order, int nip, const double* xi, const double* w);
 
 // Points of the compact rule make_compact_rule(dim, degree) returns, or 0 when the table has none (then the Duffy rule of
 // that order is used). constexpr: the fast tent kernel sizes its top-face pass with it at compile time.
