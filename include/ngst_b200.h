@@ -209,6 +209,12 @@ int ngst_rule(int dim, int order, int* nip, double* xi, double* w);
  * exactly (checked to 1e-11 relative); otherwise NGST_ERR_ARG. nip == 0 removes the override. ngst_rule returns the rule in
  * force. */
 int ngst_rule_override(int dim, int order, int nip, const double* xi, const double* w);
+/* Point-value transfer from the state rule (ngst_rule(dim, order_from)) to the compact rule (ngst_compact_rule(dim,
+ * degree_to)) through the polynomials of total degree <= poly_degree: sizes[2] = {rows = compact points, cols = state
+ * points}, M row-major. With both rules exact to 2*poly_degree, sum_q w_q phi(x_q) g_q = sum_r v_r phi(y_r) (M g)_r for every
+ * g and every polynomial phi of degree <= poly_degree, and M g = g at the compact points for polynomial g: the identity
+ * behind integrating a tent's right-hand side (src/twavetents.cpp:230-267) on the compact rule. */
+int ngst_rule_transfer(int dim, int order_from, int degree_to, int poly_degree, int* sizes, double* M);
 /* compact fully symmetric rule exact to `degree` (top-face Gram of the fast kernel; no reference counterpart); falls back
  * to ngst_rule(dim, degree) where no table exists */
 int ngst_compact_rule(int dim, int degree, int* nip, double* xi, double* w);

@@ -96,6 +96,7 @@ _SIGS = {
     "ngst_device_fp64_peak": (C.c_int, [C.c_int, C.c_int, c_dp]),
     "ngst_basis": (C.c_int, [C.c_int, C.c_int, C.c_int, c_ip, c_ip, c_ip, c_dp, c_ip]),
     "ngst_rule": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp, c_dp]),
+    "ngst_rule_transfer": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, c_ip, c_dp]),
     "ngst_rule_override": (C.c_int, [C.c_int, C.c_int, C.c_int, c_dp, c_dp]),
     "ngst_compact_rule": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp, c_dp]),
 }

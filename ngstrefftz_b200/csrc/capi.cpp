@@ -468,6 +468,18 @@ int ngst_rule_override(int dim, int order, int nip, const double* xi, const doub
   });
 }
 
+int ngst_rule_transfer(int dim, int order_from, int degree_to, int poly_degree, int* sizes, double* M) {
+  return guarded([&] {
+    try {
+      const SimplexRule A = make_simplex_rule(dim, order_from), B = make_compact_rule(dim, degree_to);
+      if (sizes) { sizes[0] = B.nip; sizes[1] = A.nip; }
+      if (M) copy_out(M, rule_transfer_matrix(A, B, poly_degree));
+    } catch (const std::invalid_argument&) { throw; }
+    catch (const std::domain_error&) { throw; }
+    catch (const std::runtime_error& e) { throw std::invalid_argument(e.what()); }
+  });
+}
+
 int ngst_compact_rule(int dim, int degree, int* nip, double* xi, double* w) {
   return guarded([&] {
     SimplexRule r;

@@ -230,4 +230,55 @@ SimplexRule make_compact_rule(int dim, int degree) {
   return default_simplex_rule(dim, degree);
 }
 
+std::vector<double> rule_transfer_matrix(const SimplexRule& A, const SimplexRule& B, int deg) {
+  if (A.dim != B.dim || A.dim < 1 || A.dim > 3 || deg < 0) throw std::invalid_argument("rule_transfer_matrix: bad arguments");
+  const int D = A.dim, nA = A.nip, nB = B.nip;
+  std::vector<int> ex;  // exponents of the monomials of total degree <= deg, first coordinate outermost
+  int e[3] = {0, 0, 0};
+  for (e[0] = 0; e[0] <= deg; e[0]++)
+    for (e[1] = 0; e[1] <= (D > 1 ? deg - e[0] : 0); e[1]++)
+      for (e[2] = 0; e[2] <= (D > 2 ? deg - e[0] - e[1] : 0); e[2]++)
+        for (int d = 0; d < D; d++) ex.push_back(e[d]);
+  const int nd = (int)ex.size() / D;
+  auto mono = [&](const SimplexRule& r, std::vector<double>& V) {
+    V.assign((size_t)r.nip * nd, 0.0);
+    for (int q = 0; q < r.nip; q++)
+      for (int k = 0; k < nd; k++) {
+        double m = 1.0;
+        for (int d = 0; d < D; d++) m *= std::pow(r.xi[(size_t)q * D + d], ex[(size_t)k * D + d]);
+        V[(size_t)q * nd + k] = m;
+      }
+  };
+  std::vector<double> VA, VB;
+  mono(A, VA);
+  mono(B, VB);
+  // modified Gram-Schmidt (twice) on the columns of VA in A's inner product; the same column operations on VB evaluate
+  // the orthonormal functions at B's points
+  auto dot = [&](int a, int b) {
+    double s = 0;
+    for (int q = 0; q < nA; q++) s += A.w[q] * VA[(size_t)q * nd + a] * VA[(size_t)q * nd + b];
+    return s;
+  };
+  for (int k = 0; k < nd; k++) {
+    for (int pass = 0; pass < 2; pass++)
+      for (int j = 0; j < k; j++) {
+        const double r = dot(j, k);
+        for (int q = 0; q < nA; q++) VA[(size_t)q * nd + k] -= r * VA[(size_t)q * nd + j];
+        for (int q = 0; q < nB; q++) VB[(size_t)q * nd + k] -= r * VB[(size_t)q * nd + j];
+      }
+    const double nrm = std::sqrt(dot(k, k));
+    if (!(nrm > 0)) throw std::domain_error("rule_transfer_matrix: rule A does not resolve the polynomial space");
+    for (int q = 0; q < nA; q++) VA[(size_t)q * nd + k] /= nrm;
+    for (int q = 0; q < nB; q++) VB[(size_t)q * nd + k] /= nrm;
+  }
+  std::vector<double> M((size_t)nB * nA, 0.0);
+  for (int r = 0; r < nB; r++)
+    for (int q = 0; q < nA; q++) {
+      double s = 0;
+      for (int k = 0; k < nd; k++) s += VB[(size_t)r * nd + k] * VA[(size_t)q * nd + k];
+      M[(size_t)r * nA + q] = s * A.w[q];
+    }
+  return M;
+}
+
 }  // namespace ngst

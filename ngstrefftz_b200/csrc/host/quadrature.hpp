@@ -50,4 +50,14 @@ constexpr int compact_rule_points(int dim, int degree) {
 // make_simplex_rule(dim, degree) when the table has no entry.
 SimplexRule make_compact_rule(int dim, int degree);
 
+// Transfer of point values from rule A to rule B through the polynomials of total degree <= deg: the nB x nA matrix
+//   M = Psi(B) Psi(A)^T diag(w_A),   Psi = basis of P_deg orthonormal in A's inner product,
+// i.e. (M g)(y_r) = (Pi g)(y_r) with Pi the projection onto P_deg that is orthogonal in A's inner product. If A and B are
+// exact to degree 2 deg, then for EVERY g (polynomial or not) and every phi in P_deg
+//   sum_q wA_q phi(x_q) g_q = sum_r wB_r phi(y_r) (M g)_r,
+// and M g = g restricted to B's points when g is itself in P_deg. This is what lets the right-hand side of a tent
+// (test functions of degree <= p against the state row, src/twavetents.cpp:230-267) be integrated on the compact rule
+// (DESIGN.md section 9). Row-major M[r * nA + q].
+std::vector<double> rule_transfer_matrix(const SimplexRule& A, const SimplexRule& B, int deg);
+
 }  // namespace ngst
