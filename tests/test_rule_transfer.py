@@ -60,3 +60,29 @@ def test_transfer_size_query_and_errors(built):
         check(lib.ngst_rule_transfer(5, 8, 8, 4, iptr(sizes), None))
     with pytest.raises(NgstError):   # 220 polynomials of degree <= 9 cannot be orthonormalised on the 8-point rule
         check(lib.ngst_rule_transfer(3, 2, 2, 9, iptr(sizes), np.zeros(4 * 8).ctypes.data_as(C.POINTER(C.c_double))))
+
+
+def test_rows_written_by_tents_are_polynomials_of_degree_p(built):
+    """Fact (ii) of DESIGN.md section 9: after a slab every state row is a polynomial of degree <= p on its element (one tent
+    writes all points of a row), so projecting it onto P_p in the rule's inner product changes nothing -- checked on the
+    oracle's Propagate; the sampled initial rows (a standing wave) are NOT polynomials."""
+    import ngstrefftz_b200 as ng
+    from _cases import dirichlet, standing
+    from _oracle import Oracle
+    for D, mesh, p, dt in ((2, ng.UnitSquareMesh(4), 4, 0.3), (3, ng.UnitCubeMesh(2), 3, 0.2)):
+        o = Oracle(mesh)
+        assert o.pitch(dt, True, 2 / 3, 1.0)
+        o.setup(p, 1.0)
+        o.set_initial(standing(D))
+        o.set_boundary_cf(dirichlet(standing(D), D))
+        xa, wa = rule(lib.ngst_rule, D, 2 * p)
+        expo = [e for e in product(range(p + 1), repeat=D) if sum(e) <= p]
+        V = np.stack([np.prod(xa ** np.array(e), axis=1) for e in expo], axis=1)
+        # W-orthogonal projector onto P_p at the rule points
+        G = V.T @ (wa[:, None] * V)
+        P = V @ np.linalg.solve(G, V.T * wa[None, :])
+        init = o.wavefront().reshape(o.nel, -1, len(wa))
+        assert np.abs(init - init @ P.T).max() > 1e-6 * np.abs(init).max()
+        o.propagate()
+        rows = o.wavefront().reshape(o.nel, -1, len(wa))
+        assert np.abs(rows - rows @ P.T).max() <= 1e-11 * np.abs(rows).max()
