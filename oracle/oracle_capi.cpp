@@ -229,6 +229,24 @@ void oracle_get_phase_times(void* hp, double* out) {
   for (int k = 0; k < 7; k++) out[k] = tw ? tw->phase_sec[k] : 0.0;
 }
 
+// EXPERIMENT: bottom-face terms on a compact rule (cnip points xi, weights w) with the state row
+// transferred by M (cnip x nip, ngst_rule_transfer). cnip == 0 switches back to the restated reference algorithm.
+int oracle_set_compact_rhs(void* hp, int cnip, const double* xi, const double* w, const double* M) {
+  auto* h = (OracleHandle*)hp;
+  return guarded([&] {
+    TWaveTents* t = h->tw.get();
+    if (!t) throw std::runtime_error("oracle: setup has not been called");
+    t->cnip = 0;
+    if (cnip <= 0) return;
+    t->c_points = Matrix(cnip, h->ma.D);
+    std::memcpy(t->c_points.d.data(), xi, sizeof(double) * cnip * h->ma.D);
+    t->c_w.assign(w, w + cnip);
+    t->c_M = Matrix(cnip, t->snip);
+    std::memcpy(t->c_M.d.data(), M, sizeof(double) * (size_t)cnip * t->snip);
+    t->cnip = cnip;
+  });
+}
+
 void oracle_get_wavefront(void* hp, double* out) {
   auto* h = (OracleHandle*)hp;
   std::memcpy(out, h->tw->wavefront.d.data(), sizeof(double) * h->tw->wavefront.d.size());

@@ -265,6 +265,13 @@ struct TWaveTents {
   std::vector<long long> bd_offset;  // per tent: offset into bddata of its first boundary facet
   bool have_bd = false;
   double timeshift = 0;
+  // EXPERIMENT (off by default; not part of the restatement): bottom-face terms of CalcTentEl integrated on a compact rule
+  // B after transferring the state row with M (cnip x snip, ngst_rule_transfer). Proves on the CPU that the fast kernel's
+  // planned compact state reproduces the reference's Propagate up to round-off.
+  int cnip = 0;
+  Matrix c_points;             // cnip x D
+  std::vector<double> c_w;     // cnip
+  Matrix c_M;                  // cnip x snip
   // Per-phase thread-seconds with the reference's timer names (twavetents.cpp:84-88, 186-188): [0] "tent top calcshape",
   // [1] "tent top AAt", [2] "tent top bilinearform", [3] "tentel" (all of CalcTentEl), [4] solve, [5] "tenteval",
   // [6] "tent" (whole tent). Filled only when phase_timing is set; bench.py reports them beside the CPU baseline.
@@ -429,11 +436,12 @@ struct TWaveTents {
   }
 
   // mapped points of the spatial rule on element elnr, time from the linear face function
-  void ElementPoints(int elnr, const Vert& vert, Matrix& pts) const {
+  void ElementPoints(int elnr, const Vert& vert, Matrix& pts) const { ElementPointsAt(elnr, vert, ir_points, pts); }
+  void ElementPointsAt(int elnr, const Vert& vert, const Matrix& ref, Matrix& pts) const {
     const int* ev = ma->elverts(elnr);
-    for (int q = 0; q < snip; q++) {
+    for (int q = 0; q < ref.h; q++) {
       double lam[4], s = 0;
-      for (int d = 0; d < D; d++) { lam[d] = ir_points(q, d); s += lam[d]; }
+      for (int d = 0; d < D; d++) { lam[d] = ref(q, d); s += lam[d]; }
       lam[D] = 1.0 - s;
       for (int d = 0; d < D; d++) {
         double x = 0;
@@ -464,12 +472,55 @@ struct TWaveTents {
     const double t_el = phase_timing ? Now() : 0.0;
     Matrix pts(snip, d1);
     Vert vert = TentFaceVerts(tent, elnr, -1);
-    ElementPoints(elnr, vert, pts);
     double area = TentFaceArea(vert);
     std::vector<double> n = TentFaceNormal(vert, -1);
-    std::vector<double> bdbvec((size_t)d1 * snip, 0.0);
     const int off = !fosystem;
-    for (int imip = 0; imip < snip; imip++) {
+    if (cnip > 0) {
+      // experiment: the same bottom-face terms on the compact rule, state row transferred with M
+      if (cpt) throw std::runtime_error("oracle: compact right-hand side needs a constant wavespeed per element");
+      const int nc = off + d1;
+      Matrix g(nc, cnip);
+      for (int cc = 0; cc < nc; cc++)
+        for (int r = 0; r < cnip; r++) {
+          double sacc = 0;
+          for (int q = 0; q < snip; q++) sacc += c_M(r, q) * wavefront(elnr, cc * snip + q);
+          g(cc, r) = sacc;
+        }
+      Matrix cpts(cnip, d1);
+      ElementPointsAt(elnr, vert, c_points, cpts);
+      std::vector<double> cvec((size_t)d1 * cnip, 0.0);
+      for (int r = 0; r < cnip; r++) {
+        const double weight = c_w[r] * area;
+        cvec[D * cnip + r] += n[D] * std::pow(c, -2) * weight * g(off + D, r);
+        for (int d = 0; d < D; d++) {
+          cvec[d * cnip + r] += n[D] * weight * g(off + d, r);
+          cvec[d * cnip + r] -= n[d] * weight * g(off + D, r);
+          cvec[D * cnip + r] -= n[d] * weight * g(off + d, r);
+        }
+      }
+      Matrix cbb(nbasis, d1 * cnip);
+      tel.CalcDShape(cpts, cbb);
+      AddAv(cbb, cvec, elvec, -1.0);
+      if (!fosystem) {
+        Matrix cs(nbasis, cnip);
+        tel.CalcShape(cpts, cs);
+        Matrix ws(nbasis, cnip), wst(cnip, nbasis), ws2(nbasis, cnip);
+        std::vector<double> wu(cnip);
+        for (int r = 0; r < cnip; r++) wu[r] = g(0, r);
+        for (int i = 0; i < nbasis; i++)
+          for (int r = 0; r < cnip; r++) {
+            const double sq = std::sqrt(area * c_w[r]);
+            ws(i, r) = cs(i, r) * sq;
+            wst(r, i) = ws(i, r);
+            ws2(i, r) = ws(i, r) * sq;
+          }
+        AddAB(ws, wst, elmat, ld);
+        AddAv(ws2, wu, elvec, 1.0);
+      }
+    }
+    ElementPoints(elnr, vert, pts);
+    std::vector<double> bdbvec((size_t)d1 * snip, 0.0);
+    for (int imip = 0; imip < snip && cnip == 0; imip++) {
       const double weight = ir_w[imip] * area;
       bdbvec[D * snip + imip] += n[D] * std::pow(cpt ? cpt[imip] : c, -2) * weight * wavefront(elnr, (off + D) * snip + imip);
       for (int d = 0; d < D; d++) {
@@ -482,7 +533,7 @@ struct TWaveTents {
     tel.CalcDShape(pts, bbmat);
     AddAv(bbmat, bdbvec, elvec, -1.0);
 
-    if (!fosystem) {  // stabilization to recover the second-order solution
+    if (!fosystem && cnip == 0) {  // stabilization to recover the second-order solution
       Matrix shapes(nbasis, snip);
       tel.CalcShape(pts, shapes);
       Matrix ws(nbasis, snip), wst(snip, nbasis);

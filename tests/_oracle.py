@@ -56,6 +56,7 @@ def _load():
     lib.oracle_propagate.argtypes = [C.c_void_p, C.c_int, C.c_int]
     lib.oracle_get_wavefront.argtypes = [C.c_void_p, c_dp]
     lib.oracle_set_phase_timing.argtypes = [C.c_void_p, C.c_int]
+    lib.oracle_set_compact_rhs.argtypes = [C.c_void_p, C.c_int, c_dp, c_dp, c_dp]
     lib.oracle_get_phase_times.argtypes = [C.c_void_p, c_dp]
     for f in ("oracle_timeshift", "oracle_max_adiam"):
         getattr(lib, f).restype = C.c_double
@@ -270,6 +271,18 @@ class Oracle:
         rc = lib.oracle_propagate(self.h, int(nthreads), int(ntents_limit))
         if rc == -2:
             raise ArithmeticError("oracle: singular local system")
+        if rc:
+            raise RuntimeError(lib.oracle_last_error().decode())
+
+    def set_compact_rhs(self, xi=None, w=None, M=None):
+        """EXPERIMENT: integrate the bottom-face terms on the compact rule (xi, w) after transferring
+        the state row with M (ngst_rule_transfer); no arguments = the restated reference algorithm."""
+        if xi is None:
+            rc = lib.oracle_set_compact_rhs(self.h, 0, None, None, None)
+        else:
+            xi, w, M = (np.ascontiguousarray(a, dtype=np.float64) for a in (xi, w, M))
+            assert M.shape == (len(w), self.nip)
+            rc = lib.oracle_set_compact_rhs(self.h, len(w), _dp(xi), _dp(w), _dp(M))
         if rc:
             raise RuntimeError(lib.oracle_last_error().decode())
 
