@@ -147,8 +147,14 @@ int ngst_twave_set_boundary_analytic(ngst_twave* t, int family, const double* pa
  * the analytic data sampled on the device at `time`: no wavefront crosses PCIe. */
 int ngst_twave_error_analytic(ngst_twave* t, int family, const double* params, int nparams, double time, int l2only,
                               double* out);
-/* Propagate src/twavetents.cpp:72-175: one slab, timeshift += slab height. */
+/* Propagate src/twavetents.cpp:72-175: one slab, timeshift += slab height. Fails with NGST_ERR_STATE when the slab was
+ * re-pitched after the solver was created (the device tables are staged once; the reference re-reads its slab on every
+ * call): create a new solver for the new tents. */
 int ngst_twave_propagate(ngst_twave* t);
+/* Diagnostics (no reference counterpart): the tents of the first `nlevels` tent levels only, one launch per level,
+ * timeshift unchanged -- the state the reference's loop over the tents (src/twavetents.cpp:90-171) holds once these
+ * tents are done. Lets the parity tests compare slabs of the benchmark's size with the CPU oracle level by level. */
+int ngst_twave_propagate_levels(ngst_twave* t, int nlevels);
 double ngst_twave_timeshift(const ngst_twave* t);
 /* Rewind / set the accumulated time (the reference's `timeshift` member, src/twavetents.hpp:106, is only ever
  * advanced by Propagate; re-running a slab from the same initial data needs it reset). */
@@ -176,6 +182,8 @@ int ngst_twave_get_wavefront(ngst_twave* t, double* out);
  * buffer must stay valid until the mirror is switched off (host == NULL), ngst_twave_set_initial changes the row length,
  * or the solver is destroyed. Call after ngst_twave_set_initial. Single-GPU solvers only. */
 int ngst_twave_set_output_mirror(ngst_twave* t, double* host);
+/* number of copy CTAs the output mirror keeps in flight (default 24, the best of 12 / 24 / 48 measured on B200) */
+int ngst_twave_set_mirror_ctas(ngst_twave* t, int ctas);
 /* GetWave src/__init__.py:7-43 (per-element L2 projection of the quadrature-point state, IntegrationPointFunction
  * src/specialcoefficientfunction.cpp:48-172): second-order state -> u onto polynomials of degree p (1 component),
  * first-order state -> (grad u, d_t u) onto degree p-1 (D+1 components). The basis is orthonormal on the reference

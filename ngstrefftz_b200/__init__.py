@@ -614,6 +614,16 @@ class TWaveTents(TrefftzTents):
         check(lib.ngst_twave_set_boundary_values(self._h, dptr(vals), n))
         check(lib.ngst_twave_propagate(self._h))
 
+    def propagate_levels(self, nlevels, vals="auto"):
+        """Diagnostics: run only the tents of the first `nlevels` tent levels (timeshift unchanged), with the boundary
+        datum of the current slab; see ngst_twave_propagate_levels."""
+        if not getattr(self, "_bnd_on_device", False):
+            if isinstance(vals, str):
+                vals = self._boundary_values()
+            n = 0 if vals is None else len(vals)
+            check(lib.ngst_twave_set_boundary_values(self._h, dptr(vals), n))
+        check(lib.ngst_twave_propagate_levels(self._h, int(nlevels)))
+
     def reset_time(self, timeshift=0.0):
         check(lib.ngst_twave_set_timeshift(self._h, float(timeshift)))
 
@@ -661,6 +671,10 @@ class TWaveTents(TrefftzTents):
             raise ValueError("SetOutputMirror: need a writeable C-contiguous float64 array of nel * ncomp * nip entries")
         check(lib.ngst_twave_set_output_mirror(self._h, dptr(out)))
         self._mirror = out  # keeps the page-locked buffer alive as long as the solver writes to it
+
+    def set_mirror_ctas(self, ctas):
+        """Copy CTAs the output mirror keeps in flight (default 24)."""
+        check(lib.ngst_twave_set_mirror_ctas(self._h, int(ctas)))
 
     def GetWavefront(self):
         wf = np.zeros((self.nel, self.ncomp * self.nip))

@@ -21,6 +21,7 @@ struct ngst_mesh { SimplexMesh m; };
 struct ngst_slab { const ngst_mesh* mesh; TentSlab s; };
 struct ngst_twave {
   const ngst_slab* slab;
+  int slab_generation = 0;  // generation of *slab the device tables were staged from
   // multi-GPU: this rank's partition plan and its restricted slab (must outlive the solver, which keeps references)
   std::unique_ptr<PartitionPlan> plan;
   std::unique_ptr<TentSlab> sub;
@@ -59,6 +60,14 @@ void copy_out(T* dst, const std::vector<T>& src) {
 }
 void need(const void* p, const char* what) {
   if (!p) throw std::invalid_argument(std::string("null argument: ") + what);
+}
+// The device tables of a solver are staged once, at creation. The reference re-reads its TentPitchedSlab on every
+// Propagate (src/twavetents.cpp:72-90), so re-pitching under a live TWave is legal there; here it is refused instead of
+// running the old tables against the new slab.
+void need_current(const ngst_twave* t) {
+  need(t, "solver");
+  if (t->slab->s.generation != t->slab_generation)
+    throw std::logic_error("the tent slab was re-pitched after this TWave was created: create a new TWave for the new tents");
 }
 }  // namespace
 
@@ -209,6 +218,7 @@ int ngst_twave_create(const ngst_slab* s, int order, const double* c_el, const d
     if (c_vertex) cv.assign(c_vertex, c_vertex + m.nv);
     auto h = std::make_unique<ngst_twave>();
     h->slab = s;
+    h->slab_generation = s->s.generation;
     h->solver = std::make_unique<Solver>(s->s, order, ce, cv, device);
     *out = h.release();
   });
@@ -246,6 +256,7 @@ int ngst_twave_create_partitioned(const ngst_slab* s, int order, const double* c
     const std::vector<int> vo(vertex_owner, vertex_owner + m.nv);
     auto h = std::make_unique<ngst_twave>();
     h->slab = s;
+    h->slab_generation = s->s.generation;
     h->plan = std::make_unique<PartitionPlan>(make_partition_plan(m, s->s, vo, nranks, rank));
     h->sub = std::make_unique<TentSlab>(restrict_slab(s->s, h->plan->own_tents));
     h->solver = std::make_unique<Solver>(*h->sub, order, ce, cv, device, h->plan.get());
@@ -270,6 +281,7 @@ int ngst_qtwave_create(const ngst_slab* s, int order, const double* c_el, const 
     q.bb.assign(bb_taylor, bb_taylor + (size_t)m.nv * nB);
     auto h = std::make_unique<ngst_twave>();
     h->slab = s;
+    h->slab_generation = s->s.generation;
     h->solver = std::make_unique<Solver>(s->s, order, ce, cv, device, nullptr, &q);
     *out = h.release();
   });
@@ -359,7 +371,15 @@ int ngst_twave_set_boundary_analytic(ngst_twave* t, int family, const double* pa
 }
 
 int ngst_twave_propagate(ngst_twave* t) {
-  return guarded([&] { need(t, "solver"); t->solver->Propagate(); });
+  return guarded([&] { need_current(t); t->solver->Propagate(); });
+}
+
+int ngst_twave_propagate_levels(ngst_twave* t, int nlevels) {
+  return guarded([&] {
+    need_current(t);
+    if (nlevels < 0) throw std::invalid_argument("ngst_twave_propagate_levels: nlevels must be >= 0");
+    t->solver->Propagate(nlevels);
+  });
 }
 
 double ngst_twave_timeshift(const ngst_twave* t) { return t ? t->solver->timeshift() : 0.0; }
@@ -387,7 +407,15 @@ int ngst_twave_get_wave(ngst_twave* t, int* sizes, double* coef, double* psi_at_
 }
 
 int ngst_twave_set_output_mirror(ngst_twave* t, double* host) {
-  return guarded([&] { need(t, "solver"); t->solver->SetOutputMirror(host); });
+  return guarded([&] { need_current(t); t->solver->SetOutputMirror(host); });
+}
+
+int ngst_twave_set_mirror_ctas(ngst_twave* t, int ctas) {
+  return guarded([&] {
+    need(t, "solver");
+    if (ctas < 1 || ctas > 1024) throw std::invalid_argument("ngst_twave_set_mirror_ctas: ctas must be in 1..1024");
+    t->solver->set_mirror_ctas(ctas);
+  });
 }
 
 int ngst_twave_energy(ngst_twave* t, const double* wf, double* out) {

@@ -3,7 +3,6 @@
 
 #include <algorithm>
 #include <cmath>
-#include <cstdlib>
 #include <stdexcept>
 
 namespace ngst {
@@ -58,6 +57,7 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
   CU(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
   CU(cudaEventCreate(&ev0_));
   CU(cudaEventCreate(&ev1_));
+  CU(cudaEventCreateWithFlags(&ev_done_, cudaEventDisableTiming));
 
   rule_ = make_simplex_rule(D, 2 * order);
   basis_so_ = twave_basis(d1, order, 0);
@@ -164,10 +164,15 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
       d_cval_[f] = Upload(fstage_.cval[f]);
     }
   }
-  CU(cudaMalloc(&d_singular_, sizeof(int)));
+  // [0] singular pivots, [1] dependency time-outs of the single-launch mode; copied into page-locked host words by
+  // an asynchronous 8-byte copy at the end of every Propagate (no extra synchronisation)
+  CU(cudaMalloc(&d_singular_, 2 * sizeof(int)));
   allocs_.push_back(d_singular_);
-  CU(cudaMemset(d_singular_, 0, sizeof(int)));
+  CU(cudaMemset(d_singular_, 0, 2 * sizeof(int)));
+  CU(cudaHostAlloc(&h_flags_, 2 * sizeof(int), cudaHostAllocDefault));
+  h_flags_[0] = h_flags_[1] = 0;
   a.singular = d_singular_;
+  a.stuck = d_singular_ + 1;
 
   if (qt_) {
     const int nv = mesh_.nv;
@@ -365,11 +370,13 @@ Solver::~Solver() {
   if (d_tmp_params_) cudaFree(d_tmp_params_);
   if (d_tmp_a_) cudaFree(d_tmp_a_);
   if (d_tmp_b_) cudaFree(d_tmp_b_);
+  if (h_flags_) cudaFreeHost(h_flags_);
   if (d_sendbuf_) cudaFree(d_sendbuf_);
   if (d_recvbuf_) cudaFree(d_recvbuf_);
   comm_.reset();
   if (ev0_) cudaEventDestroy(ev0_);
   if (ev1_) cudaEventDestroy(ev1_);
+  if (ev_done_) cudaEventDestroy(ev_done_);
   if (ev_halo_) cudaEventDestroy(ev_halo_);
   if (ev_int_) cudaEventDestroy(ev_int_);
   if (stream_halo_) cudaStreamDestroy(stream_halo_);
@@ -432,12 +439,18 @@ void Solver::SetInitial(const double* wf, int ncomp) {
   const int D = mesh_.D;
   if (ncomp != D + 2 && ncomp != D + 1)
     throw std::invalid_argument("SetInitial: initial data must have D+2 (second order) or D+1 (first order) components");
+  if (qt_ && ncomp == D + 1)  // checked before any member changes: a failed call leaves the solver as it was
+    throw std::invalid_argument("SetInitial: the quasi-Trefftz solver takes second-order initial data (D+2 components)");
   CU(cudaSetDevice(device_));
   fosystem_ = (ncomp == D + 1) ? 1 : 0;  // twavetents.hpp:198-203
   ncomp_ = ncomp;
   basis_ = fosystem_ ? basis_fo_ : basis_so_;
   const size_t bytes = (size_t)nel_ * ncomp * rule_.nip * sizeof(double);
-  if (wavefront_bytes_ != bytes) ReleaseMirror();  // the mirror buffer was sized for the previous row length
+  if (wavefront_bytes_ != bytes) {
+    ReleaseMirror();  // the mirror buffer and the scratch wavefronts of Energy / Error were sized for the previous row length
+    if (d_tmp_a_) { CU(cudaFree(d_tmp_a_)); d_tmp_a_ = nullptr; }
+    if (d_tmp_b_) { CU(cudaFree(d_tmp_b_)); d_tmp_b_ = nullptr; }
+  }
   if (d_wavefront_ && wavefront_bytes_ != bytes) { CU(cudaFree(d_wavefront_)); d_wavefront_ = nullptr; }
   if (!d_wavefront_) { CU(cudaMalloc(&d_wavefront_, bytes)); wavefront_bytes_ = bytes; }
   if (wf) {
@@ -459,7 +472,6 @@ void Solver::SetInitial(const double* wf, int ncomp) {
   fargs_.crow = d_crow_[fosystem_];
   fargs_.cval = d_cval_[fosystem_];
   if (qt_) {
-    if (fosystem_) throw std::invalid_argument("SetInitial: the quasi-Trefftz solver takes second-order initial data (D+2 components)");
     a.rowptr = nullptr; a.col = nullptr; a.val = nullptr;
     const size_t budget = 150 * 1024;
     int qc = std::min(std::max(rule_.nip, qargs_.Qv), 16);
@@ -571,10 +583,14 @@ void Solver::SetBoundaryValues(const double* values, long long n) {
   args_.bnd_data = d_bnd_;
 }
 
-void Solver::Propagate() {
+void Solver::Propagate(int level_limit) {
   if (!have_initial_) throw std::logic_error("Propagate: SetInitial has not been called");
   CU(cudaSetDevice(device_));
-  const int nlev = (int)slab_.level_off.size() - 1;
+  const int nlev_all = (int)slab_.level_off.size() - 1;
+  // level_limit >= 0 (diagnostics, ngst_twave_propagate_levels): only the tents of the first level_limit levels, one
+  // launch per level, no advance of timeshift -- the state the reference's serial loop holds once these tents are done
+  const bool partial = level_limit >= 0 && level_limit < nlev_all;
+  const int nlev = partial ? level_limit : nlev_all;
   int launches = 0;
   CU(cudaEventRecord(ev0_, stream_));
   if (bnd_family_ >= 0 && staged_.nbnd_values > 0) {
@@ -623,7 +639,7 @@ void Solver::Propagate() {
   // Measured on B200 (profiles/r01o): with ~2700 tents per level (config 4) the single launch is 3 % slower than one launch
   // per level (waiting CTAs hold SM slots and poll), with small levels it removes the launch gaps and tails.
   const bool small_levels = slab_.ntents < 2 * 444 * nlev;
-  const bool dag = dag_ && (dag_mode_ == 2 || (dag_mode_ == 1 && small_levels)) && !force_generic_ && !comm_;
+  const bool dag = dag_ && (dag_mode_ == 2 || (dag_mode_ == 1 && small_levels)) && !force_generic_ && !comm_ && !partial;
   if (dag) {
     CU(cudaMemcpyAsync(d_remaining_, d_indeg_, sizeof(int) * slab_.ntents, cudaMemcpyDeviceToDevice, stream_));
     CU(cudaMemsetAsync(d_ticket_, 0, sizeof(int), stream_));
@@ -689,18 +705,22 @@ void Solver::Propagate() {
     CU(cudaStreamWaitEvent(stream_, ev_mirror_, 0));
   }
   CU(cudaEventRecord(ev1_, stream_));
-  CU(cudaEventSynchronize(ev1_));
+  CU(cudaMemcpyAsync(h_flags_, d_singular_, 2 * sizeof(int), cudaMemcpyDeviceToHost, stream_));
+  CU(cudaEventRecord(ev_done_, stream_));
+  CU(cudaEventSynchronize(ev_done_));
   float ms = 0;
   CU(cudaEventElapsedTime(&ms, ev0_, ev1_));
   last_ms_ = ms;
   last_launches_ = launches;
-  timeshift_ += slab_.dt;  // twavetents.cpp:173
-  int sing = 0;
-  CU(cudaMemcpy(&sing, d_singular_, sizeof(int), cudaMemcpyDeviceToHost));
-  if (sing) {
-    CU(cudaMemset(d_singular_, 0, sizeof(int)));
+  const int sing = h_flags_[0], stuck = h_flags_[1];
+  if (sing || stuck) {
+    CU(cudaMemsetAsync(d_singular_, 0, 2 * sizeof(int), stream_));
+    if (stuck)
+      throw std::logic_error("Propagate: " + std::to_string(stuck) + " tent(s) gave up waiting for their predecessors in "
+                             "the dependency-driven launch (scheduling failure, not a numerical one); the state is invalid");
     throw std::domain_error("Propagate: singular local system in " + std::to_string(sing) + " pivot step(s)");
   }
+  if (!partial) timeshift_ += slab_.dt;  // twavetents.cpp:173
 }
 
 // rows updated in level l that other ranks hold -> peers; rows peers updated that this rank holds <- peers
@@ -798,13 +818,9 @@ void Solver::MirrorRows(int first_level, int last_level, int& launches) {
   if (e <= b) return;
   CU(cudaEventRecord(ev_level_, stream_));
   CU(cudaStreamWaitEvent(stream_mirror_, ev_level_, 0));
-  // a few CTAs keep PCIe busy (16 KB in flight each); each takes the place of one tent CTA (of 3 per SM) while it runs
-  static const int ctas = [] {
-    const char* s = std::getenv("NGST_MIRROR_CTAS");  // tuning knob (profiles/r03c)
-    const int v = s ? std::atoi(s) : 0;
-    return v > 0 ? v : 24;
-  }();
-  CU(launch_mirror_rows(d_final_rows_ + b, e - b, ncomp_ * rule_.nip, d_wavefront_, mirror_dev_, ctas, stream_mirror_));
+  // a few CTAs keep PCIe busy (16 KB in flight each); each takes the place of one tent CTA (of 3 per SM) while it runs.
+  // 24 measured best of 12 / 24 / 48 on B200 (profiles/r03c); ngst_twave_set_mirror_ctas changes it
+  CU(launch_mirror_rows(d_final_rows_ + b, e - b, ncomp_ * rule_.nip, d_wavefront_, mirror_dev_, mirror_ctas_, stream_mirror_));
   launches++;
 }
 

@@ -66,7 +66,7 @@ class Solver {
   void MakeWavefrontAnalytic(int family, const double* params, int nparams, double time, int first_order, double* out);
   void SetBoundaryAnalytic(int family, const double* params, int nparams);
   double ErrorAnalytic(int family, const double* params, int nparams, double time, bool l2only);
-  void Propagate();
+  void Propagate(int level_limit = -1);
   void GetWavefront(double* out);
   // Output mirror (cuda/mirror.cu): `host` (nel x ncomp*nip doubles; page-locked here if it is not already) receives every
   // state row as soon as it is final during Propagate, overlapped with the remaining tents; when Propagate returns it
@@ -91,6 +91,7 @@ class Solver {
   // (no dependency-driven scheduling on one GPU, exchange not overlapped on several), 3: as 0 with the dependency-driven
   // single launch forced (default: only for slabs with small levels, where launches and level tails dominate)
   void set_kernel_mode(int mode) { force_generic_ = mode == 1; overlap_ = mode != 2; dag_mode_ = mode == 2 ? 0 : (mode == 3 ? 2 : 1); }
+  void set_mirror_ctas(int n) { mirror_ctas_ = n; }
   double last_ms() const { return last_ms_; }
   int last_launches() const { return last_launches_; }
 
@@ -124,7 +125,7 @@ class Solver {
   int last_launches_ = 0;
 
   cudaStream_t stream_ = nullptr;
-  cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
+  cudaEvent_t ev0_ = nullptr, ev1_ = nullptr, ev_done_ = nullptr;
   // multi-GPU overlap: halo tents + exchange of a level run on a high-priority stream beside the interior tents
   cudaStream_t stream_halo_ = nullptr;
   cudaEvent_t ev_halo_ = nullptr, ev_int_ = nullptr;
@@ -176,7 +177,9 @@ class Solver {
   int proj_deg_ = -1, proj_ndof_ = 0;
   std::vector<double> proj_psi_, proj_mono_;
   std::vector<int> proj_expo_;
-  int* d_singular_ = nullptr;
+  int* d_singular_ = nullptr;      // device words: [0] singular pivot steps, [1] dependency time-outs
+  int* h_flags_ = nullptr;         // their page-locked host copy, refreshed by every Propagate
+  int mirror_ctas_ = 24;
   int* d_rowptr_[2] = {nullptr, nullptr};  // [fosystem]
   int* d_col_[2] = {nullptr, nullptr};
   double* d_val_[2] = {nullptr, nullptr};

@@ -120,20 +120,28 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
   if (a.ticket) {
     // dependency-driven order (replaces the reference's RunParallelDependency, ngstents paralleldepend.hpp:20-131): tickets
     // are handed out in level order, so every predecessor holds an earlier ticket and is running or done -- no deadlock.
-    __shared__ int s_tent;
+    __shared__ int s_tent, s_stuck;
     if (tid == 0) {
       const int t = a.tents[atomicAdd(a.ticket, 1)];
       volatile int* r = a.remaining + t;
       long long spins = 0;
+      int stuck = 0;
       while (*r > 0) {
         __nanosleep(64);
-        if (++spins > (1ll << 26)) { atomicAdd(a.singular, 1 << 20); break; }  // never hang the device: flag and go on
+        // never hang the device: a tent that gives up is counted in its own flag (Propagate reports a scheduling failure,
+        // not a singular system), skips its work and still releases its successors so that the launch drains quickly
+        if (++spins > (1ll << 26)) { atomicAdd(a.stuck, 1); stuck = 1; break; }
       }
       __threadfence();
       s_tent = t;
+      s_stuck = stuck;
     }
     __syncthreads();
     tent = s_tent;
+    if (s_stuck) {
+      for (int s = a.succ_off[tent] + tid; s < a.succ_off[tent + 1]; s += kThreads) atomicSub(a.remaining + a.succ[s], 1);
+      return;
+    }
   } else {
     tent = a.tents[blockIdx.x];
   }

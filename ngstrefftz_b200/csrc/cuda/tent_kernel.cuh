@@ -42,6 +42,7 @@ struct TentKernelArgs {
   int ntents;
   int max_ndom;
   int* singular;           // incremented when a zero pivot is met
+  int* stuck;              // incremented when a tent of the dependency-driven launch gives up waiting (its writes are skipped)
   // ---- dependency-driven scheduling (tent_fast.cu, single GPU): one launch per slab; CTAs draw tents from `tents` in
   // order through `ticket` and wait until remaining[tent] (unfinished predecessors) is zero; a finished tent decrements
   // the counters of its successors. ticket == nullptr: `tents` is one level, CTA b solves tents[b].

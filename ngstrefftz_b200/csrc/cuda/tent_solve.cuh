@@ -52,7 +52,7 @@ __device__ __forceinline__ void gauss_jordan_solve(const double* A, int LDA, dou
             for (int j = 0; j < NCB; j++) prow[buf][tx + 16 * j] = Ar[i0][j];
             if (tx == (kk & 15)) {
               const double piv = Ar[i0][j0];
-              const bool ok = piv > 0.0;
+              const bool ok = piv > 0.0 && isfinite(piv);
               pinv_s[buf] = ok ? 1.0 / piv : 0.0;
               pinv_row[kk] = ok ? 1.0 / piv : 0.0;
               rowstep[kk] = kk;
@@ -83,6 +83,9 @@ __device__ __forceinline__ void gauss_jordan_solve(const double* A, int LDA, dou
             const int orow = __shfl_xor_sync(0xffffffffu, brow, o);
             if (ob > best || (ob == best && orow < brow)) { best = ob; brow = orow; }
           }
+          // every remaining entry NaN (degenerate geometry): no candidate was selected. Take the first row not yet used
+          // so that the indices stay in range; the non-finite pivot is counted as singular below.
+          if (brow >= N) brow = __ffsll((long long)~done) - 1;
           p = brow;
           done |= 1ull << p;
           if (ty == (p & 7)) {
@@ -100,7 +103,7 @@ __device__ __forceinline__ void gauss_jordan_solve(const double* A, int LDA, dou
             for (int j = 0; j < NCB; j++) prow[buf][tx + 16 * j] = tmp[j];
             if (tx == (kk & 15)) {
               const double piv = tmp[j0];
-              const bool ok = piv != 0.0;
+              const bool ok = piv != 0.0 && isfinite(piv);
               pinv_s[buf] = ok ? 1.0 / piv : 0.0;
               pinv_row[p] = ok ? 1.0 / piv : 0.0;
               rowstep[p] = kk;

@@ -1,9 +1,9 @@
 // Trefftz basis for the wave equation: sparse coefficient matrix monomials -> wave polynomials.
 //
-// Follows src/trefftzfespace.cpp:611-682 (TWaveBasis<D+1>::Basis, basistype 0),
-// src/trefftzfespace.hpp:128-142 (PolBasis::IndexMap2), src/trefftzfespace.cpp:455-488 (TraversePol)
-// and src/scalarmappedfe.cpp:153-175 (MatToCSR). Monomials xi^alpha, |alpha| <= p, are enumerated
-// with the FIRST coordinate's exponent outermost (src/scalarmappedfe.cpp:526-531).
+// Produces the table of src/trefftzfespace.cpp:611-682 (TWaveBasis<D+1>::Basis, basistype 0) in the CSR form of
+// src/scalarmappedfe.cpp:153-175 (MatToCSR) -- same rows, columns and values -- from the Cauchy-Kovalevskaya series of
+// each seed monomial (basis.cpp). Monomials xi^alpha, |alpha| <= p, are enumerated with the FIRST coordinate's
+// exponent outermost (src/scalarmappedfe.cpp:526-531).
 #pragma once
 #include <vector>
 
@@ -29,8 +29,8 @@ int twave_nbasis(int D, int order, int fowave);
 // exponents of the npoly = C(d1+p,p) monomials, first coordinate outermost
 std::vector<int> monomial_exponents(int d1, int order);
 
-// IndexMap2 (trefftzfespace.hpp:128-142)
-int index_map2(int d1, const int* index, int ord);
+// position of the monomial xi^expo in monomial_exponents(d1, order)
+int monomial_rank(int d1, const int* expo, int order);
 
 // wave polynomials for c = 1 in d1 = D+1 space-time dimensions; fowave drops the constant (row 0)
 BasisCsr twave_basis(int d1, int order, int fowave);

@@ -379,6 +379,7 @@ double TentSlab::MaxSlope() const {
 }
 
 bool TentSlab::PitchTents(double adt, bool calc_local_ct, double global_ct) {
+  generation++;
   if (!mesh) throw std::runtime_error("TentSlab: no mesh");
   if (cmax_el.empty()) throw std::logic_error("Wavespeed has not been set!");  // tents.cpp:85-88
   const SimplexMesh& m = *mesh;

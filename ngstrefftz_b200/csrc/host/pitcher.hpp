@@ -23,6 +23,7 @@ struct TentSlab {
   std::vector<double> cmax_el;  // per-element maximal wavespeed (SetMaxWavespeed)
   double dt = 0;
   bool pitched = false;
+  int generation = 0;  // bumped by every PitchTents / import: solvers staged from an older generation refuse to run
   int nlayers = 0;  // as the reference's member: GetNLayers() == nlayers + 1
 
   // flattened tents (struct Tent, tents.hpp:38-75)

@@ -216,6 +216,18 @@ int oracle_propagate(void* hp, int nthreads, int ntents_limit) {
   h->tw->singular = 0;
   return s ? -2 : 0;
 }
+// bench.py's CPU baseline: the listed tents only, dependencies ignored (timing; see PropagateSample)
+int oracle_propagate_sample(void* hp, int nthreads, const int* tents, int n) {
+  auto* h = (OracleHandle*)hp;
+  int rc = guarded([&] {
+    const int nt = (int)h->tw->tps->tents.size();
+    for (int i = 0; i < n; i++)
+      if (tents[i] < 0 || tents[i] >= nt) throw std::runtime_error("oracle_propagate_sample: tent id out of range");
+    h->tw->PropagateSample(nthreads, tents, n);
+  });
+  h->tw->singular = 0;
+  return rc;
+}
 // Per-phase timers of the plain Trefftz path (names of twavetents.cpp:84-88, 186-188): on != 0 switches them on and
 // clears them; out[7] = thread-seconds {calcshape, AAt, bilinearform, tentel, solve, tenteval, tent} since then.
 void oracle_set_phase_timing(void* hp, int on) {

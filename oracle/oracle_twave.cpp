@@ -825,6 +825,32 @@ struct TWaveTents {
     if (ntents_limit <= 0) timeshift += tps->dt;
   }
 
+  // Timing aid of bench.py's CPU baseline: the listed tents, in parallel, WITHOUT regard to their dependencies -- the cost of
+  // a tent does not depend on the values in its state rows, so a sample spread over all levels of a slab can be timed
+  // without running the whole slab. The state afterwards is meaningless; timeshift is not advanced.
+  void PropagateSample(int nthreads, const int* tents, int n) {
+    CSR basismat = TWaveBasis(D + 1, order, fosystem, pix);
+    // tents of one chunk must not share elements (they write rows concurrently): greedy colouring into conflict-free rounds
+    std::vector<int> rest(tents, tents + n);
+    std::vector<char> used(ma->nel, 0);
+    while (!rest.empty()) {
+      std::vector<int> round, later;
+      for (int t : rest) {
+        bool free_ = true;
+        for (int el : tps->tents[t].els) free_ = free_ && !used[el];
+        if (free_) { round.push_back(t); for (int el : tps->tents[t].els) used[el] = 1; }
+        else later.push_back(t);
+      }
+      for (int t : round) for (int el : tps->tents[t].els) used[el] = 0;
+#pragma omp parallel for schedule(dynamic, 1) num_threads(nthreads)
+      for (int k = 0; k < (int)round.size(); k++) {
+        if (qt) PropagateTentQT(round[k]);
+        else PropagateTent(round[k], basismat);
+      }
+      rest.swap(later);
+    }
+  }
+
   double ElWeight(int elnr, int q) const {
     const int* ev = ma->elverts(elnr);
     double J[9];

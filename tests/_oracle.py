@@ -54,6 +54,7 @@ def _load():
     lib.oracle_boundary_points.argtypes = [C.c_void_p, c_dp, c_ip]
     lib.oracle_set_boundary_values.argtypes = [C.c_void_p, c_dp, C.c_longlong]
     lib.oracle_propagate.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    lib.oracle_propagate_sample.argtypes = [C.c_void_p, C.c_int, c_ip, C.c_int]
     lib.oracle_get_wavefront.argtypes = [C.c_void_p, c_dp]
     lib.oracle_set_phase_timing.argtypes = [C.c_void_p, C.c_int]
     lib.oracle_set_compact_rhs.argtypes = [C.c_void_p, C.c_int, c_dp, c_dp, c_dp]
@@ -264,8 +265,21 @@ class Oracle:
             out.append(vd[sl] if k == 0 else vn[sl].T.reshape(-1))
         return np.ascontiguousarray(np.concatenate(out))
 
-    def propagate(self, nthreads=0, ntents_limit=0):
-        vals = self._boundary_values()
+    def set_boundary_values(self, vals):
+        """Pre-sampled boundary values (what _boundary_values() returns for the current timeshift)."""
+        lib.oracle_set_boundary_values(self.h, _dp(vals), 0 if vals is None else len(vals))
+
+    def propagate_sample(self, tents, nthreads=0):
+        """TIMING ONLY (bench.py CPU baseline): the listed tents with the boundary values already set, dependencies
+        between tents ignored -- the state afterwards is meaningless."""
+        tents = np.ascontiguousarray(tents, dtype=np.int32)
+        rc = lib.oracle_propagate_sample(self.h, int(nthreads or os.cpu_count() or 1), _ip(tents), len(tents))
+        if rc:
+            raise RuntimeError(lib.oracle_last_error().decode())
+
+    def propagate(self, nthreads=0, ntents_limit=0, vals="sample"):
+        if isinstance(vals, str):
+            vals = self._boundary_values()
         lib.oracle_set_boundary_values(self.h, _dp(vals), 0 if vals is None else len(vals))
         nthreads = nthreads or os.cpu_count() or 1
         rc = lib.oracle_propagate(self.h, int(nthreads), int(ntents_limit))
