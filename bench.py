@@ -270,6 +270,8 @@ def run_ours(args):
             tw.set_kernel_mode(2)
     else:
         tw = ng.TWave(order, ts, 1.0, device=local)
+        if args.mirror_ctas:
+            tw.set_mirror_ctas(args.mirror_ctas)
         if args.single_launch:
             tw.set_kernel_mode(3)
         if args.level_launches:
@@ -415,6 +417,71 @@ def run_ours(args):
             if use_mirror:
                 lib.ngst_twave_set_output_mirror(tw._h, None)
 
+    # ---------------- N>1: the partitioned run must equal a single-GPU run of the SAME slab bit for bit (same tents, same
+    # arithmetic per tent). Both runs take initial and boundary data sampled on the device (bitwise reproducible per
+    # point); rank 0 runs the whole slab on its GPU and broadcasts one checksum pair per global row.
+    parity = None
+    if world > 1 and not args.no_parity_check:
+        try:
+            nslabs = 2
+            data = ng.StandingWave(D, 1.0)
+            local_err = None
+            try:  # collectives below must be reached by every rank
+                tw.reset_time()
+                tw.SetInitial(data)
+                tw.SetBoundaryCF(data)
+                for _ in range(nslabs):
+                    tw.Propagate()
+                mine_rows = tw.GetWavefront().view(np.uint64)
+            except Exception as ex:
+                local_err = repr(ex)
+            okf = torch.tensor([0.0 if local_err else 1.0], dtype=torch.float64, device="cuda")
+            dist.all_reduce(okf, op=dist.ReduceOp.MIN)
+            if float(okf[0]) != 1.0:
+                raise RuntimeError(f"partitioned run with device-sampled data failed on some rank (this rank: {local_err})")
+            en_part = tw.Energy()
+            nel_glob = int(mesh.ne)
+            ref = torch.zeros((2, nel_glob), dtype=torch.int64, device="cuda")
+            en_ref = torch.zeros(2, dtype=torch.float64, device="cuda")  # [energy, 1 = the single-GPU run succeeded]
+            t_ref, ref_err = 0.0, None
+            if rank == 0:
+                try:  # every rank must reach the broadcasts below, whatever happens here
+                    t0 = time.perf_counter()
+                    one = ng.TWave(order, ts, 1.0, device=local)
+                    one.SetInitial(data)
+                    one.SetBoundaryCF(data)
+                    for _ in range(nslabs):
+                        one.Propagate()
+                    rows = one.GetWavefront().view(np.uint64)
+                    en_ref[0] = one.Energy()
+                    ref[0] = torch.from_numpy(rows.sum(axis=1, dtype=np.uint64).view(np.int64)).cuda()
+                    ref[1] = torch.from_numpy(np.bitwise_xor.reduce(rows, axis=1).view(np.int64)).cuda()
+                    en_ref[1] = 1.0
+                    del one, rows
+                    t_ref = time.perf_counter() - t0
+                except Exception as ex:
+                    ref_err = repr(ex)
+            dist.broadcast(ref, 0)
+            dist.broadcast(en_ref, 0)
+            if float(en_ref[1]) != 1.0:
+                raise RuntimeError(f"single-GPU reference run on rank 0 failed: {ref_err}")
+            refh = ref.cpu().numpy().view(np.uint64)
+            l2g = tw.loc2glob
+            bad = int(np.count_nonzero((mine_rows.sum(axis=1, dtype=np.uint64) != refh[0][l2g]) |
+                                       (np.bitwise_xor.reduce(mine_rows, axis=1) != refh[1][l2g])))
+            cnt = torch.tensor([bad, len(l2g)], dtype=torch.int64, device="cuda")
+            dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+            e1 = float(en_ref[0])
+            parity = {"ok": bool(int(cnt[0]) == 0 and abs(en_part - e1) <= 1e-12 * abs(e1)),
+                      "kind": "bitwise: every local row (owned and ghost) of every rank vs a single-GPU run of the same "
+                              "slab on rank 0 (64-bit sum and xor of each row's bit patterns)",
+                      "slabs": nslabs, "rows_compared": int(cnt[1]), "rows_differing": int(cnt[0]),
+                      "global_rows": nel_glob, "energy_partitioned": en_part, "energy_single_gpu": e1,
+                      "single_gpu_run_s": t_ref, "data": "standing wave sampled on the device (initial + Dirichlet datum)"}
+            del mine_rows
+        except Exception as ex:  # a failed check is reported, never hidden
+            parity = {"ok": False, "error": repr(ex)}
+
     # ---------------- reduce over ranks (max time, sum units)
     ntents_local = len(mine)
     stats = torch.tensor([dev_s, wall_s, e2e["sec"] if e2e else 0.0, float(ntents_local), flops_step, bytes_step,
@@ -453,42 +520,59 @@ def run_ours(args):
     flops_rank0 = flops_step * args.steps
     ach_tf = flops_rank0 / (float(np.sum(dev_ms)) * 1e-3) * 1e-12
     ach_gbs = bytes_step * args.steps / (float(np.sum(dev_ms)) * 1e-3) * 1e-9
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tpath):
-        try:
-            with open(tpath) as fh:
-                # ncu --set full capture (profiles/): DRAM bytes per tent x the tents of an average launch of this run
-                traffic = json.load(fh).get("dram_bytes_per_tent") * tents_step * args.steps / max(sm[6], 1)
-        except (OSError, ValueError):
-            traffic = None
-    # executed tensor-path work of tent_kernel_fast: symmetric rank-k updates touch only the NT(NT+1)/2 upper-triangular
-    # 8x8 tiles; (D+1) k-rows per top-face point, 1 per bottom-face point (second-order form), 4 k-rows per DMMA. The
-    # top-face Gram runs on a compact rule exact to degree 2p-2 (24 points at D=3, p=4; tent_fast.cu Cfg::QT)
+    dev_sec0 = float(np.sum(dev_ms)) * 1e-3          # rank 0's device time of the timed steps
+    te_rank0 = float(nels.sum()) * args.steps         # tent-elements rank 0 processed in them
+    launches_rank0 = max(launches, 1)
+    # Executed FP64 work per tent-element of the kernel variant, from ncu counters of ONE capture of this workload
+    # (profiles/executed_flops.json, written by scripts/summarize_ncu.py: DMMA warp instructions x 512 + 2 x DFMA + DMUL +
+    # DADD thread instructions, divided by the tent-elements of the captured launches), and the DRAM bytes of the same
+    # capture. Falls back to the tile-count model of the DMMA work alone when the file does not describe this variant.
     nt_tiles = (N + 7) // 8
     n_rule = _capi.C.c_int(0)
     check(lib.ngst_compact_rule(D, 2 * order - 2, _capi.C.byref(n_rule), None, None))
     Qt = n_rule.value   # top-face Gram: compact rule exact to degree 2p-2 (24 points at D=3, p=4; tent_fast.cu Cfg::QT)
     check(lib.ngst_compact_rule(D, 2 * order, _capi.C.byref(n_rule), None, None))
-    Qs = n_rule.value   # stabilisation Gram: compact rule exact to degree 2p where the table has one, else the order-2p rule
-    dmma_el = (Qt * (D + 1) / 4.0 + (0 if tw.fosystem else Qs / 4.0)) * (nt_tiles * (nt_tiles + 1) / 2) * 512.0
-    dmma_tf = dmma_el * float(nels.sum()) * args.steps / (float(np.sum(dev_ms)) * 1e-3) * 1e-12
-    roofline = {"bound": "tensor", "pipe": "FP64: DMMA m8n8k4 tensor path and DFMA share one datapath (DESIGN.md 4.1)", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach_tf / fp64_peak,
-                "traffic": traffic, "kernel": tw.kernel_name(),
-                "peak_source": f"measured live on this GPU: DFMA {dfma.value:.2f} / DMMA m8n8k4 {dmma.value:.2f} TFLOP/s "
-                               f"(ngst_device_fp64_peak), DMMA+DFMA interleaved 4:1 {mixed.value:.2f}; MEASURED_PEAKS.json holds no FP64 figure",
-                "flops_per_tent_element": f_el,
-                "note": "achieved = algorithmic flops of SURVEY.md 8.4 (full N x N Gram) / device time; the kernel exploits "
-                        "the symmetry of W (Z Z^T) and integrates the degree-(2p-2) top-face Gram with the order-(2p-2) rule, so it "
-                        "executes fewer flops and frac can exceed 1",
-                "executed_dmma": {"flops_per_tent_element": dmma_el, "achieved": dmma_tf, "peak": dmma.value,
-                                  "unit": "TFLOP/s", "frac": dmma_tf / dmma.value if dmma.value else None}, "launches_per_step": launches / max(args.steps, 1),
-                "hbm": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s",
-                        "frac": ach_gbs / hbm_peak, "peak_source": hbm_src, "bytes_per_tent_element": b_el}}
+    Qs = n_rule.value   # stabilisation Gram: compact rule exact to degree 2p where the table has one
+    dmma_model = (Qt * (D + 1) / 4.0 + (0 if tw.fosystem else Qs / 4.0)) * (nt_tiles * (nt_tiles + 1) / 2) * 512.0
+    exe, exe_src, traffic, ncu = None, None, None, None
+    try:
+        with open(os.path.join(ROOT, "profiles", "executed_flops.json")) as fh:
+            rec = json.load(fh)
+        if rec.get("kernel") == tw.kernel_name() and rec.get("D") == D and rec.get("order") == order:
+            exe = rec["flops_per_tent_element"]
+            exe_src = f"ncu counters, {rec.get('tag')}: {rec.get('formula')}"
+            traffic = rec.get("dram_bytes_per_tent_element")
+            ncu = {k: rec.get(k) for k in ("pipe_shared_pct", "dmma_pipe_pct", "fp64_pipe_pct", "dmma_flops_per_tent_element",
+                                           "dfma_flops_per_tent_element", "captured_grid_sizes", "tag")}
+    except (OSError, ValueError, KeyError):
+        exe = None
+    if exe is None:
+        exe, exe_src = dmma_model, "model: DMMA tiles only (no ncu capture of this kernel variant under profiles/)"
+    exe_tf = exe * te_rank0 / dev_sec0 * 1e-12
+    te_per_launch = te_rank0 / launches_rank0
+    roofline = {
+        "bound": "tensor", "unit": "TFLOP/s", "achieved": exe_tf, "peak": fp64_peak, "frac": exe_tf / fp64_peak,
+        "kernel": tw.kernel_name(),
+        "pipe": "FP64: DMMA m8n8k4 (tensor path) and DFMA/DMUL/DADD share one datapath per SM (sm__pipe_shared)",
+        "achieved_definition": "EXECUTED FP64 flops per tent-element x tent-elements of the timed steps / CUDA-event time",
+        "executed_flops_per_tent_element": exe, "executed_source": exe_src,
+        "executed_dmma_model_flops_per_tent_element": dmma_model,
+        "peak_source": f"measured live on this GPU (ngst_device_fp64_peak): DFMA {dfma.value:.2f} / DMMA m8n8k4 {dmma.value:.2f} "
+                       f"TFLOP/s, interleaved 4:1 {mixed.value:.2f}; MEASURED_PEAKS.json holds no FP64 figure",
+        "traffic": None if traffic is None else traffic * te_per_launch,
+        "algorithmic_bytes_per_launch": bytes_step * args.steps / launches_rank0,
+        "ncu": ncu, "launches_per_step": launches / max(args.steps, 1),
+        # SURVEY 8.4's count (order-2p rule everywhere, full N x N Grams) over the same time: how much faster the kernel is
+        # than executing the reference's algorithm at the FP64 peak would be -- the gain of symmetry and compact rules
+        "algorithmic": {"flops_per_tent_element": f_el, "achieved": ach_tf, "unit": "TFLOP/s",
+                        "algorithmic_speedup": ach_tf / fp64_peak},
+        "hbm": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
+                "peak_source": hbm_src, "bytes_per_tent_element": b_el},
+    }
 
     line = {
         "metric": METRIC, "value": value, "unit": "tents/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True, "scaling": args.scaling,
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "dof_updates_per_s": value * N,
         "config": {"workload": f"3+1D unit-cube brick {cells[0]}x{cells[1]}x{cells[2]} cells x 6 tets, order {order}, "
@@ -515,6 +599,8 @@ def run_ours(args):
                                "ngst_twave_set_initial + set_boundary_values + propagate + get_wavefront on pinned host buffers"}
     if device_data:
         line["device_data"] = device_data
+    if parity is not None:
+        line["parity_check"] = parity
     if not args.no_cpu_baseline and world == 1:
         cores = os.cpu_count() or 1
         sample = args.cpu_sample_tents or 4000
