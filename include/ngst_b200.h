@@ -58,6 +58,17 @@ int ngst_slab_create(const ngst_mesh* m, int method, ngst_slab** out);
 int ngst_slab_set_max_wavespeed(ngst_slab* s, const double* c, int n);
 /* PitchTents python_tents.cpp:44-65 -> tents.cpp:78-359. *ok = 0 when the slab could not be completed. */
 int ngst_slab_pitch(ngst_slab* s, double dt, int local_ct, double global_ct, int* ok);
+/* A slab from tents pitched elsewhere, e.g. by the reference's own ngstents (what TWave(order, tps, ...) is handed,
+ * src/twavetents.cpp:1194-1228): the Tent fields of python_tents.cpp:119-128 -- vertex, level, tbot, ttop, nbv, nbtime,
+ * els, internal_facets -- flattened with CSR offsets (*_off: ntents+1 entries), in the slab's tent order. They are taken
+ * as they are (so tent ids, list order and times are the caller's, bit for bit); dependency table, slopes and level
+ * sets are derived as after ngst_slab_pitch. level == NULL: replayed as the greedy loop assigns levels (tents.cpp:199-217);
+ * facet_off == facets == NULL: internal facets from the mesh. NGST_ERR_ARG for lists that do not fit the mesh or whose
+ * levels do not order the tents sharing an element. Replaces ngst_slab_pitch for this slab (solvers created before
+ * must be re-created). */
+int ngst_slab_import_tents(ngst_slab* s, int ntents, double dt, const int* vertex, const int* level, const double* tbot,
+                           const double* ttop, const int* nb_off, const int* nbv, const double* nbtime, const int* el_off,
+                           const int* els, const int* facet_off, const int* facets);
 int ngst_slab_ntents(const ngst_slab* s);    /* GetNTents  tents.hpp:217 */
 int ngst_slab_nlayers(const ngst_slab* s);   /* GetNLayers tents.hpp:218 */
 double ngst_slab_height(const ngst_slab* s); /* GetSlabHeight tents.hpp:223 */
@@ -169,6 +180,15 @@ const char* ngst_twave_kernel_name(const ngst_twave* t);
  * slabs with small levels). Results are bitwise identical in modes 0, 2 and 3.
  * ngst_twave_ntents_fast: tents of the slab routed to the fast kernel in mode 0. */
 int ngst_twave_set_kernel_mode(ngst_twave* t, int mode);
+/* Compact state (no reference counterpart; default on). Where every tent of the slab runs on the fast kernel, the solver
+ * keeps a second copy of the state at the points of the compact rule exact to degree 2p (46 instead of 125 points at
+ * D = 3, p = 4), which the tents read and write; a row written by a tent is a polynomial of degree <= p on its element
+ * (src/twavetents.cpp:541-590), so nothing is lost, and the bottom-face integrals of src/twavetents.cpp:230-267 agree for
+ * sampled initial rows as well (ngst_rule_transfer). The public rows (ngst_twave_get_wavefront, Energy, Error, mirror) are
+ * written by the last tent of the slab that contains the element. on == 0: the tents work on the public rows (A/B).
+ * ngst_twave_compact_state: 1 when the next Propagate will use it. */
+int ngst_twave_set_compact_state(ngst_twave* t, int on);
+int ngst_twave_compact_state(const ngst_twave* t);
 int ngst_twave_ntents_fast(const ngst_twave* t);
 /* device time of the last Propagate in ms (CUDA events on the solver's stream) and kernel launches in it */
 double ngst_twave_last_ms(const ngst_twave* t);

@@ -286,6 +286,36 @@ class TentSlab:
         out.update({k: np.asarray(v, dtype=np.int32) for k, v in off.items()})
         np.savez_compressed(path, **out)
 
+    def import_tents(self, tents, dt=None):
+        """Take the tents of another pitcher instead of pitching: `tents` is a dict (or .npz path) with the keys of
+        save_tents / dump_reference_tents -- vertex, tbot, ttop, nb_off, nbv, nbtime, el_off, els and optionally level,
+        facet_off, facets (ngst_slab_import_tents). dt defaults to the largest ttop."""
+        if isinstance(tents, (str, bytes)) or hasattr(tents, "__fspath__"):
+            with np.load(tents) as z:
+                tents = {k: z[k] for k in z.files}
+        g = lambda k, conv: conv(tents[k]) if k in tents and tents[k] is not None else None  # noqa: E731
+        vertex, level = i32(tents["vertex"]), g("level", i32)
+        tbot, ttop, nbtime = f64(tents["tbot"]), f64(tents["ttop"]), f64(tents["nbtime"])
+        nb_off, nbv, el_off, els = i32(tents["nb_off"]), i32(tents["nbv"]), i32(tents["el_off"]), i32(tents["els"])
+        facet_off, facets = g("facet_off", i32), g("facets", i32)
+        n = len(vertex)
+        if not (len(tbot) == len(ttop) == n and len(nb_off) == len(el_off) == n + 1 and len(nbv) == len(nbtime)
+                and (level is None or len(level) == n) and (facet_off is None or len(facet_off) == n + 1)
+                and (n == 0 or (len(nbv) == nb_off[-1] and len(els) == el_off[-1]))
+                and (facet_off is None or facets is not None and len(facets) == facet_off[-1])):
+            raise ValueError("import_tents: array lengths do not fit together")
+        dt = float(ttop.max()) if dt is None else float(dt)
+        self._export = None
+        check(lib.ngst_slab_import_tents(self._h, n, dt, iptr(vertex), iptr(level), dptr(tbot), dptr(ttop), iptr(nb_off),
+                                         iptr(nbv), dptr(nbtime), iptr(el_off), iptr(els), iptr(facet_off), iptr(facets)))
+        return self
+
+    @classmethod
+    def from_reference(cls, mesh, tents, dt=None, method="edge"):
+        """TentSlab over `mesh` holding the tents of a dump written by dump_reference_tents inside a real ngstents session
+        (or by save_tents): the counterpart of handing the reference's TentPitchedSlab to TWave."""
+        return cls(mesh, method).import_tents(tents, dt)
+
     def compare_tents(self, path, same_numbering=True):
         """Compare this slab with a tent dump (save_tents / dump_reference_tents). same_numbering=True: bitwise equality of
         every shared table (needs identical vertex / element / facet numbering). False: numbering-free invariants only --
@@ -641,6 +671,13 @@ class TWaveTents(TrefftzTents):
     def set_kernel_mode(self, mode):
         """0 = automatic routing (DMMA kernel for single-wavespeed tents), 1 = generic DFMA kernel for every tent."""
         check(lib.ngst_twave_set_kernel_mode(self._h, int(mode)))
+
+    def set_compact_state(self, on=True):
+        """Tents read / write the internal compact-rule copy of the state (default) or the public rows (A/B)."""
+        check(lib.ngst_twave_set_compact_state(self._h, int(bool(on))))
+
+    def compact_state(self):
+        return bool(lib.ngst_twave_compact_state(self._h))
 
     def ntents_fast(self):
         return lib.ngst_twave_ntents_fast(self._h)

@@ -47,6 +47,8 @@ _SIGS = {
     "ngst_slab_create": (C.c_int, [c_vp, C.c_int, C.POINTER(c_vp)]),
     "ngst_slab_set_max_wavespeed": (C.c_int, [c_vp, c_dp, C.c_int]),
     "ngst_slab_pitch": (C.c_int, [c_vp, C.c_double, C.c_int, C.c_double, c_ip]),
+    "ngst_slab_import_tents": (C.c_int, [c_vp, C.c_int, C.c_double, c_ip, c_ip, c_dp, c_dp, c_ip, c_ip, c_dp, c_ip, c_ip,
+                                         c_ip, c_ip]),
     "ngst_slab_ntents": (C.c_int, [c_vp]),
     "ngst_slab_nlayers": (C.c_int, [c_vp]),
     "ngst_slab_height": (C.c_double, [c_vp]),
@@ -85,6 +87,8 @@ _SIGS = {
     "ngst_twave_kernel_name": (C.c_char_p, [c_vp]),
     "ngst_twave_set_kernel_mode": (C.c_int, [c_vp, C.c_int]),
     "ngst_twave_ntents_fast": (C.c_int, [c_vp]),
+    "ngst_twave_set_compact_state": (C.c_int, [c_vp, C.c_int]),
+    "ngst_twave_compact_state": (C.c_int, [c_vp]),
     "ngst_twave_last_ms": (C.c_double, [c_vp]),
     "ngst_twave_last_launches": (C.c_int, [c_vp]),
     "ngst_twave_get_wavefront": (C.c_int, [c_vp, c_dp]),

@@ -168,6 +168,15 @@ int ngst_slab_pitch(ngst_slab* s, double dt, int local_ct, double global_ct, int
   });
 }
 
+int ngst_slab_import_tents(ngst_slab* s, int ntents, double dt, const int* vertex, const int* level, const double* tbot,
+                           const double* ttop, const int* nb_off, const int* nbv, const double* nbtime, const int* el_off,
+                           const int* els, const int* facet_off, const int* facets) {
+  return guarded([&] {
+    need(s, "slab");
+    s->s.ImportTents(ntents, dt, vertex, level, tbot, ttop, nb_off, nbv, nbtime, el_off, els, facet_off, facets);
+  });
+}
+
 int ngst_slab_ntents(const ngst_slab* s) { return s ? s->s.ntents : 0; }
 int ngst_slab_nlayers(const ngst_slab* s) { return s ? s->s.GetNLayers() : 0; }
 double ngst_slab_height(const ngst_slab* s) { return s ? s->s.dt : 0.0; }
@@ -409,6 +418,11 @@ int ngst_twave_get_wave(ngst_twave* t, int* sizes, double* coef, double* psi_at_
 int ngst_twave_set_output_mirror(ngst_twave* t, double* host) {
   return guarded([&] { need_current(t); t->solver->SetOutputMirror(host); });
 }
+
+int ngst_twave_set_compact_state(ngst_twave* t, int on) {
+  return guarded([&] { need(t, "solver"); t->solver->set_compact_state(on != 0); });
+}
+int ngst_twave_compact_state(const ngst_twave* t) { return t && t->solver->compact_state_active() ? 1 : 0; }
 
 int ngst_twave_set_mirror_ctas(ngst_twave* t, int ctas) {
   return guarded([&] {

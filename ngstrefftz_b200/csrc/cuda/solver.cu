@@ -154,6 +154,7 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
       }
       fargs_.lam_stab = Upload(ls);
       fargs_.sqrtw_stab = Upload(sw);
+      fargs_.w_stab = Upload(rs.w);
       fargs_.Qs = rs.nip;
     }
     fargs_.dmap = Upload(fstage_.dmap);
@@ -345,6 +346,22 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
     }
   }
 
+  // ---- compact state (tent_fast.cu, CS = 1): which tent is the last one of the slab to contain each element
+  compact_possible_ = fast_ && !qt_ && slab_.ntents > 0 && gen_off_.back() == 0;
+  if (compact_possible_) {
+    if (plan_) {
+      el_final_level_ = plan_->final_level;
+    } else {
+      el_final_level_.assign(nel_, -1);
+      for (int t = 0; t < staged_.ntents; t++)
+        for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++) {
+          int& l = el_final_level_[staged_.te_el[te]];
+          l = std::max(l, slab_.level[t]);
+        }
+    }
+    d_te_final_ = const_cast<unsigned char*>(FinalFlags(-1));
+  }
+
   // element quadrature weights |detJ| * w (GetWeight, twavetents.cpp:793,818,843)
   {
     std::vector<double> elw((size_t)nel_ * Q);
@@ -370,6 +387,7 @@ Solver::~Solver() {
   if (d_tmp_params_) cudaFree(d_tmp_params_);
   if (d_tmp_a_) cudaFree(d_tmp_a_);
   if (d_tmp_b_) cudaFree(d_tmp_b_);
+  if (d_cstate_) cudaFree(d_cstate_);
   if (h_flags_) cudaFreeHost(h_flags_);
   if (d_sendbuf_) cudaFree(d_sendbuf_);
   if (d_recvbuf_) cudaFree(d_recvbuf_);
@@ -435,6 +453,53 @@ void Solver::Quadrature(double* x, double* weight) const {
   }
 }
 
+// te_final flags (device) for a full slab (level_limit < 0, built once) or for the first level_limit levels
+const unsigned char* Solver::FinalFlags(int level_limit) {
+  if (level_limit < 0 && d_te_final_) return d_te_final_;
+  if (level_limit >= 0 && level_limit == partial_levels_ && d_te_final_partial_) return d_te_final_partial_;
+  std::vector<int> last(el_final_level_);
+  if (level_limit >= 0) {
+    // last tent among the levels < level_limit. Multi-GPU: a rank only sees its own tents, so the restriction is exact for
+    // single-GPU solvers only (partial runs of partitioned solvers are refused in Propagate).
+    std::fill(last.begin(), last.end(), -1);
+    for (int t = 0; t < staged_.ntents; t++)
+      if (slab_.level[t] < level_limit)
+        for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++) {
+          const int el = plan_ ? plan_->glob2loc[staged_.te_el[te]] : staged_.te_el[te];
+          last[el] = std::max(last[el], slab_.level[t]);
+        }
+  }
+  std::vector<unsigned char> fin((size_t)std::max(staged_.nte, 1), 0);
+  for (int t = 0; t < staged_.ntents; t++)
+    for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++) {
+      const int el = plan_ ? plan_->glob2loc[staged_.te_el[te]] : staged_.te_el[te];
+      fin[te] = last[el] == slab_.level[t];
+    }
+  if (level_limit < 0) return Upload(fin);
+  if (!d_te_final_partial_) {
+    CU(cudaMalloc(&d_te_final_partial_, fin.size()));
+    allocs_.push_back(d_te_final_partial_);
+  }
+  CU(cudaMemcpyAsync(d_te_final_partial_, fin.data(), fin.size(), cudaMemcpyHostToDevice, stream_));
+  CU(cudaStreamSynchronize(stream_));  // `fin` is a local
+  partial_levels_ = level_limit;
+  return d_te_final_partial_;
+}
+
+// compact state <- public state: every row through the degree-p polynomials onto the compact rule (exact for rows the
+// tents have written; for sampled initial rows it is the projection under which the bottom-face integrals agree)
+void Solver::ProjectCompact() {
+  const int Q = rule_.nip;
+  if (transfer_points_ != cs_points_) {
+    const SimplexRule rs = make_compact_rule(mesh_.D, 2 * order_);
+    if (rs.nip != cs_points_) throw std::logic_error("compact state: rule table and kernel disagree on the point count");
+    d_transfer_ = Upload(rule_transfer_matrix(rule_, rs, order_));
+    transfer_points_ = cs_points_;
+  }
+  CU(launch_project_rows(nel_, Q, cs_points_, 0, ncomp_, ncomp_ * Q, d_transfer_, d_wavefront_, d_cstate_, stream_));
+  cstate_valid_ = true;
+}
+
 void Solver::SetInitial(const double* wf, int ncomp) {
   const int D = mesh_.D;
   if (ncomp != D + 2 && ncomp != D + 1)
@@ -453,8 +518,16 @@ void Solver::SetInitial(const double* wf, int ncomp) {
   }
   if (d_wavefront_ && wavefront_bytes_ != bytes) { CU(cudaFree(d_wavefront_)); d_wavefront_ = nullptr; }
   if (!d_wavefront_) { CU(cudaMalloc(&d_wavefront_, bytes)); wavefront_bytes_ = bytes; }
+  cs_points_ = compact_possible_ ? tent_fast_compact_points(D, order_, fosystem_) : 0;
+  cstate_valid_ = false;
+  if (cs_points_ > 0) {
+    const size_t cb = (size_t)nel_ * ncomp * cs_points_ * sizeof(double);
+    if (d_cstate_ && cstate_bytes_ != cb) { CU(cudaFree(d_cstate_)); d_cstate_ = nullptr; }
+    if (!d_cstate_) { CU(cudaMalloc(&d_cstate_, cb)); cstate_bytes_ = cb; }
+  }
   if (wf) {
     CU(cudaMemcpyAsync(d_wavefront_, wf, bytes, cudaMemcpyHostToDevice, stream_));
+    if (cs_points_ > 0 && compact_enabled_) ProjectCompact();
     CU(cudaStreamSynchronize(stream_));
   }
   have_initial_ = true;
@@ -536,6 +609,7 @@ void Solver::SetInitialAnalytic(int family, const double* params, int nparams, i
   double* d_p = UploadParams(params, nparams, &d_tmp_params_);
   CU(launch_sample_wavefront(D, family, d_p, nel_, rule_.nip, first_order ? 1 : 0, 0.0, args_.pts, args_.el2v, args_.lam,
                              d_wavefront_, stream_));
+  if (cs_points_ > 0 && compact_enabled_) ProjectCompact();
   CU(cudaStreamSynchronize(stream_));
 }
 
@@ -591,6 +665,17 @@ void Solver::Propagate(int level_limit) {
   // launch per level, no advance of timeshift -- the state the reference's serial loop holds once these tents are done
   const bool partial = level_limit >= 0 && level_limit < nlev_all;
   const int nlev = partial ? level_limit : nlev_all;
+  if (partial && plan_) throw std::logic_error("Propagate: partial slabs (propagate_levels) are for single-GPU solvers");
+  // compact state: the fast kernel reads / writes d_cstate_ and writes the public rows of final elements only
+  const bool compact = UseCompact() && !qt_;
+  FastArgs fa = fargs_;
+  fa.cstate = nullptr;
+  fa.te_final = nullptr;
+  if (compact) {
+    if (!cstate_valid_) ProjectCompact();
+    fa.cstate = d_cstate_;
+    fa.te_final = FinalFlags(partial ? level_limit : -1);
+  }
   int launches = 0;
   CU(cudaEventRecord(ev0_, stream_));
   if (bnd_family_ >= 0 && staged_.nbnd_values > 0) {
@@ -650,7 +735,7 @@ void Solver::Propagate(int level_limit) {
     a.remaining = d_remaining_;
     a.succ_off = d_succ_off_;
     a.succ = d_succ_;
-    CU(launch_tent_fast(mesh_.D, order_, fosystem_, a, fargs_, stream_));
+    CU(launch_tent_fast(mesh_.D, order_, fosystem_, a, fa, stream_));
     launches++;
     if (mirror_dev_) MirrorRows(0, nlev - 1, launches);  // single launch per slab: nothing to overlap with
   }
@@ -675,7 +760,7 @@ void Solver::Propagate(int level_limit) {
       TentKernelArgs h = args_;
       h.tents = d_level_fast_ + fast_off_[l];
       h.ntents = fh;
-      if (h.ntents > 0) { CU(launch_tent_fast(mesh_.D, order_, fosystem_, h, fargs_, stream_halo_)); launches++; }
+      if (h.ntents > 0) { CU(launch_tent_fast(mesh_.D, order_, fosystem_, h, fa, stream_halo_)); launches++; }
       h.tents = d_level_tents_ + gen_off_[l];
       h.ntents = gh;
       if (h.ntents > 0) { CU(launch_tent_generic(mesh_.D, h, threads_, smem_, stream_halo_)); launches++; }
@@ -686,7 +771,7 @@ void Solver::Propagate(int level_limit) {
     a.tents = d_level_fast_ + fast_off_[l] + fh;
     a.ntents = fast_off_[l + 1] - fast_off_[l] - fh;
     if (a.ntents > 0) {
-      CU(launch_tent_fast(mesh_.D, order_, fosystem_, a, fargs_, stream_));
+      CU(launch_tent_fast(mesh_.D, order_, fosystem_, a, fa, stream_));
       launches++;
     }
     a.tents = d_level_tents_ + gen_off_[l] + gh;
@@ -720,6 +805,7 @@ void Solver::Propagate(int level_limit) {
                              "the dependency-driven launch (scheduling failure, not a numerical one); the state is invalid");
     throw std::domain_error("Propagate: singular local system in " + std::to_string(sing) + " pivot step(s)");
   }
+  if (!compact) cstate_valid_ = false;   // the public rows moved on without the compact copy
   if (!partial) timeshift_ += slab_.dt;  // twavetents.cpp:173
 }
 
@@ -744,9 +830,31 @@ int Solver::ExchangeLevel(int l, cudaStream_t stream) {
     CU(cudaMalloc(&d_recvbuf_, need));
     halo_bytes_ = need;
   }
-  comm_->Exchange(d_wavefront_, rowlen, d_send_el_ + p.send_off[(size_t)l * nr], sc.data(),
-                  d_recv_el_ + p.recv_off[(size_t)l * nr], rc.data(), d_sendbuf_, d_recvbuf_, stream);
-  return (ns > 0) + (nrv > 0);
+  const bool compact = UseCompact() && !qt_;
+  int extra = 0;
+  if (!compact) {
+    comm_->Exchange(d_wavefront_, rowlen, d_send_el_ + p.send_off[(size_t)l * nr], sc.data(),
+                    d_recv_el_ + p.recv_off[(size_t)l * nr], rc.data(), d_sendbuf_, d_recvbuf_, stream);
+  } else {
+    // compact rows of everything the level updated (what the peers' later tents read) ...
+    comm_->Exchange(d_cstate_, ncomp_ * cs_points_, d_send_el_ + p.send_off[(size_t)l * nr], sc.data(),
+                    d_recv_el_ + p.recv_off[(size_t)l * nr], rc.data(), d_sendbuf_, d_recvbuf_, stream);
+    // ... and the public rows of the elements that became final in this level
+    std::vector<int> sf(nr), rf(nr);
+    int nsf = 0, nrf = 0;
+    for (int q = 0; q < nr; q++) {
+      sf[q] = sendf_off_[(size_t)l * nr + q + 1] - sendf_off_[(size_t)l * nr + q];
+      rf[q] = recvf_off_[(size_t)l * nr + q + 1] - recvf_off_[(size_t)l * nr + q];
+      nsf += sf[q];
+      nrf += rf[q];
+    }
+    if (nsf > 0 || nrf > 0) {
+      comm_->Exchange(d_wavefront_, rowlen, d_sendf_el_ + sendf_off_[(size_t)l * nr], sf.data(),
+                      d_recvf_el_ + recvf_off_[(size_t)l * nr], rf.data(), d_sendbuf_, d_recvbuf_, stream);
+      extra = (nsf > 0) + (nrf > 0);
+    }
+  }
+  return (ns > 0) + (nrv > 0) + extra;
 }
 
 void Solver::ReleaseMirror() {
@@ -928,6 +1036,22 @@ void Solver::InitComm(const void* id128) {
   if (!d_send_el_) {
     d_send_el_ = Upload(plan_->send_el);
     d_recv_el_ = Upload(plan_->recv_el);
+    if (compact_possible_) {
+      // the exchanged rows whose element becomes final in the level of the exchange (same order on both sides)
+      auto filter = [&](const std::vector<int>& off, const std::vector<int>& el, std::vector<int>& foff, int** d_out) {
+        std::vector<int> fel;
+        foff.assign(1, 0);
+        for (int l = 0; l < plan_->nlev; l++)
+          for (int q = 0; q < plan_->nranks; q++) {
+            for (int i = off[(size_t)l * plan_->nranks + q]; i < off[(size_t)l * plan_->nranks + q + 1]; i++)
+              if (el_final_level_[el[i]] == l) fel.push_back(el[i]);
+            foff.push_back((int)fel.size());
+          }
+        *d_out = Upload(fel);
+      };
+      filter(plan_->send_off, plan_->send_el, sendf_off_, &d_sendf_el_);
+      filter(plan_->recv_off, plan_->recv_el, recvf_off_, &d_recvf_el_);
+    }
     CU(cudaMalloc(&d_scalar_, sizeof(double)));
     allocs_.push_back(d_scalar_);
   }

@@ -92,6 +92,10 @@ class Solver {
   // single launch forced (default: only for slabs with small levels, where launches and level tails dominate)
   void set_kernel_mode(int mode) { force_generic_ = mode == 1; overlap_ = mode != 2; dag_mode_ = mode == 2 ? 0 : (mode == 3 ? 2 : 1); }
   void set_mirror_ctas(int n) { mirror_ctas_ = n; }
+  // Compact state (tent_fast.cu, CS = 1; default on): slabs whose tents all run on the fast kernel keep an internal copy of
+  // the state on the compact degree-2p rule that the tents read and write; off = the tents work on the public rows (A/B).
+  void set_compact_state(bool on) { compact_enabled_ = on; }
+  bool compact_state_active() const { return UseCompact(); }
   double last_ms() const { return last_ms_; }
   int last_launches() const { return last_launches_; }
 
@@ -177,6 +181,25 @@ class Solver {
   int proj_deg_ = -1, proj_ndof_ = 0;
   std::vector<double> proj_psi_, proj_mono_;
   std::vector<int> proj_expo_;
+  // ---- compact state
+  bool compact_enabled_ = true;
+  bool compact_possible_ = false;     // every tent of the slab runs on the fast kernel
+  int cs_points_ = 0;                 // points of the compact rule for the current system, 0 = no compact variant
+  double* d_cstate_ = nullptr;        // nel * ncomp * cs_points_
+  size_t cstate_bytes_ = 0;
+  bool cstate_valid_ = false;         // d_cstate_ corresponds to d_wavefront_
+  double* d_transfer_ = nullptr;      // cs_points_ x nip: order-2p points -> compact points through degree-p polynomials
+  int transfer_points_ = 0;
+  std::vector<int> el_final_level_;   // per local element: level of the last tent (of the global slab) containing it
+  unsigned char* d_te_final_ = nullptr;          // per staged tent-element: its tent is that last tent
+  unsigned char* d_te_final_partial_ = nullptr;  // the same for a partial run (propagate_levels)
+  int partial_levels_ = -1;
+  // multi-GPU: per (level, peer) the exchanged rows whose element becomes final in that level (public rows follow)
+  std::vector<int> sendf_off_, recvf_off_;
+  int *d_sendf_el_ = nullptr, *d_recvf_el_ = nullptr;
+  bool UseCompact() const { return cs_points_ > 0 && compact_enabled_ && !force_generic_; }
+  void ProjectCompact();
+  const unsigned char* FinalFlags(int level_limit);
   int* d_singular_ = nullptr;      // device words: [0] singular pivot steps, [1] dependency time-outs
   int* h_flags_ = nullptr;         // their page-locked host copy, refreshed by every Propagate
   int mirror_ctas_ = 24;

@@ -30,6 +30,7 @@ namespace ngst {
 namespace {
 
 using namespace tiles;
+constexpr int kMaxFinal = 64;  // final elements of one tent listed in shared memory (compact state)
 
 template <int D, int P, int FO>
 struct Cfg {
@@ -101,9 +102,16 @@ __device__ __forceinline__ void eval_part(int part, const double* xi, F&& f) {
   }
 }
 
-template <int D, int P, int FO>
+// CS = 1 (compact state): the tents read and write a second, internal state that holds every
+// row at the QS points of the compact degree-2P rule instead of the Q points of the order-2P rule. A row written by a
+// tent is a polynomial of degree <= P on its element, so the compact samples carry the same information, and for any
+// row g the bottom-face integrals against degree-<=P test functions agree: sum_q w_q phi(x_q) g_q = sum_r v_r phi(y_r) (M g)_r
+// with M the transfer through the degree-P polynomials (rule_transfer_matrix; applied once by SetInitial). The public
+// Q-point rows are written only by the LAST tent of the slab that contains the element (f.te_final).
+template <int D, int P, int FO, int CS>
 __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a, FastArgs f) {
   using C = Cfg<D, P, FO>;
+  static_assert(!CS || (C::QS > 0 && C::rhsFirst), "compact state needs the compact degree-2P rule");
   constexpr int d1 = C::d1, N = C::N, NT = C::NT, NP = C::NP, G = C::G, Q = C::Q, QT = C::QT, ZS = C::ZS, LDA = C::LDA;
   constexpr int NACC = C::NACC, FE = C::FE, FF = C::FF, npoly = C::npoly, npm1 = C::npm1;
   extern __shared__ double sm[];
@@ -158,6 +166,11 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
     // accumulators are not live yet, the partial sums of all N functions fit in registers. The state rows are loaded at the
     // top of an iteration and consumed after the coordinate setup (a register prefetch one chunk ahead costs spills).
     constexpr int NC = FO ? d1 : d1 + 1;
+    constexpr int QR = CS ? (C::QS > 0 ? C::QS : 1) : Q;             // points per element of the rule the state lives on
+    const double* __restrict__ const lamR = CS ? f.lam_stab : a.lam;
+    const double* __restrict__ const wR = CS ? f.w_stab : a.w;
+    const double* __restrict__ const stR = CS ? f.cstate : a.wavefront;
+    const int nptr = nel * QR;
     // H = 2 (larger bases): a warp evaluates one half of the functions (groups 2h, 2h + 1) on every second chunk, which
     // keeps the partial sums and the live monomials within the 168-register budget of three CTAs per SM
     constexpr int H = (NP > 32) ? 2 : 1;
@@ -167,25 +180,25 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
     double bp[NB];
 #pragma unroll
     for (int i = 0; i < NB; i++) bp[i] = 0.0;
-    for (int c0 = cs * kChunk; c0 < npts; c0 += NS * kChunk) {
+    for (int c0 = cs * kChunk; c0 < nptr; c0 += NS * kChunk) {
       const int idx = c0 + lane;
-      const bool valid = idx < npts;
-      const int idc = valid ? idx : npts - 1;
-      const int te = te0 + idc / Q, q = idc % Q;
+      const bool valid = idx < nptr;
+      const int idc = valid ? idx : nptr - 1;
+      const int te = te0 + idc / QR, q = idc % QR;
       double gcur[NC];
       {
-        const double* __restrict__ wf = a.wavefront + (size_t)a.te_el[te] * (NC * Q) + q;
+        const double* __restrict__ wf = stR + (size_t)a.te_el[te] * (NC * QR) + q;
 #pragma unroll
-        for (int cc = 0; cc < NC; cc++) gcur[cc] = __ldcg(wf + cc * Q);  // L2: rows written by other SMs
-        if (c0 + NS * kChunk < npts) {  // next chunk of this warp: HBM -> L2 now (costs no registers)
-          const int idn = min(idx + NS * kChunk, npts - 1);
-          const double* __restrict__ wn = a.wavefront + (size_t)a.te_el[te0 + idn / Q] * (NC * Q) + idn % Q;
+        for (int cc = 0; cc < NC; cc++) gcur[cc] = __ldcg(wf + cc * QR);  // L2: rows written by other SMs
+        if (c0 + NS * kChunk < nptr) {  // next chunk of this warp: HBM -> L2 now (costs no registers)
+          const int idn = min(idx + NS * kChunk, nptr - 1);
+          const double* __restrict__ wn = stR + (size_t)a.te_el[te0 + idn / QR] * (NC * QR) + idn % QR;
 #pragma unroll
-          for (int cc = 0; cc < NC; cc++) asm volatile("prefetch.global.L2 [%0];" ::"l"(wn + cc * Q));
+          for (int cc = 0; cc < NC; cc++) asm volatile("prefetch.global.L2 [%0];" ::"l"(wn + cc * QR));
         }
       }
       const double* __restrict__ rec = f.fe + (size_t)te * FE;
-      const double* __restrict__ lm = a.lam + q * d1;
+      const double* __restrict__ lm = lamR + q * d1;
       double xi[d1];
 #pragma unroll
       for (int u = 0; u < d1; u++) xi[u] = 0.0;
@@ -199,7 +212,7 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
       const double area = rec[fast_fe_bot(D)];
       const double* __restrict__ nn = rec + fast_fe_bot(D) + 2;
       const double s = rec[fast_fe_sc(D)], sc = rec[fast_fe_sc(D) + 1], ic2 = rec[fast_fe_sc(D) + 2];
-      const double om = valid ? a.w[q] * area : 0.0;
+      const double om = valid ? wR[q] * area : 0.0;
       const double gt = gcur[(FO ? 0 : 1) + D];
       double rho[d1];
       double ndg = 0.0;
@@ -569,10 +582,10 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
   __syncthreads();
   for (int t = tid; t < d1 * npm1; t += kThreads) cmd[t] = cm[f.dmap[t]] * f.dfac[t];
   __syncthreads();
-  for (int idx = tid; idx < npts; idx += kThreads) {
-    const int te = te0 + idx / Q, q = idx % Q;
+  // value and gradient of the solution at point q (barycentric coordinates lm) of the top face of tent-element te -> row
+  // `row` with `QW` points per component
+  auto eval_point = [&](int te, const double* __restrict__ lm, double* __restrict__ row, int QW, int q) {
     const double* __restrict__ rec = f.fe + (size_t)te * FE;
-    const double* __restrict__ lm = a.lam + q * d1;
     double xi[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
     for (int kk = 0; kk < d1; kk++) {
@@ -616,11 +629,44 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
       asm volatile("" ::: "memory");  // keeps the coefficient loads of later e0 slices from being hoisted (register pressure)
     }
     const double s = rec[fast_fe_sc(D)], sc = rec[fast_fe_sc(D) + 1];
-    double* __restrict__ wf = a.wavefront + (size_t)a.te_el[te] * ((FO ? d1 : d1 + 1) * Q);
-    if (!FO) wf[q] = val;
+    if (!FO) row[q] = val;
 #pragma unroll
-    for (int u = 0; u < D; u++) wf[((FO ? 0 : 1) + u) * Q + q] = s * dv[u];
-    wf[((FO ? 0 : 1) + D) * Q + q] = sc * dv[D];
+    for (int u = 0; u < D; u++) row[((FO ? 0 : 1) + u) * QW + q] = s * dv[u];
+    row[((FO ? 0 : 1) + D) * QW + q] = sc * dv[D];
+  };
+  constexpr int NCW = FO ? d1 : d1 + 1;
+  if (CS) {
+    // compact rows of every element of the tent (what later tents read) ...
+    constexpr int QC = C::QS > 0 ? C::QS : 1;
+    const int nptc = nel * QC;
+    for (int idx = tid; idx < nptc; idx += kThreads) {
+      const int te = te0 + idx / QC, q = idx % QC;
+      eval_point(te, f.lam_stab + q * d1, f.cstate + (size_t)a.te_el[te] * (NCW * QC), QC, q);
+    }
+    // ... and the public rows (order-2P points) of the elements this tent is the last one of the slab to contain
+    __shared__ int s_fin[kMaxFinal], s_nfin;
+    if (tid == 0) s_nfin = 0;
+    __syncthreads();
+    for (int e = tid; e < nel; e += kThreads)
+      if (f.te_final[te0 + e]) s_fin[atomicAdd(&s_nfin, 1) % kMaxFinal] = e;
+    __syncthreads();
+    const int nfin = s_nfin;
+    if (nfin <= kMaxFinal) {
+      for (int idx = tid; idx < nfin * Q; idx += kThreads) {
+        const int te = te0 + s_fin[idx / Q], q = idx % Q;
+        eval_point(te, a.lam + q * d1, a.wavefront + (size_t)a.te_el[te] * (NCW * Q), Q, q);
+      }
+    } else {  // more final elements than the list holds (never with vertex patches of simplicial meshes): scan the flags
+      for (int idx = tid; idx < npts; idx += kThreads) {
+        const int te = te0 + idx / Q, q = idx % Q;
+        if (f.te_final[te]) eval_point(te, a.lam + q * d1, a.wavefront + (size_t)a.te_el[te] * (NCW * Q), Q, q);
+      }
+    }
+  } else {
+    for (int idx = tid; idx < npts; idx += kThreads) {
+      const int te = te0 + idx / Q, q = idx % Q;
+      eval_point(te, a.lam + q * d1, a.wavefront + (size_t)a.te_el[te] * (NCW * Q), Q, q);
+    }
   }
   if (a.ticket) {
     __threadfence();  // this thread's state rows are visible device-wide before the successors are released
@@ -629,11 +675,12 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
   }
 }
 
-template <int D, int P, int FO>
+template <int D, int P, int FO, int CS>
 cudaError_t launch_cfg(const TentKernelArgs& a, const FastArgs& f, cudaStream_t stream) {
   using C = Cfg<D, P, FO>;
   if (a.Q != C::Q || f.Qt != C::QT || a.N != C::N || a.npoly != C::npoly) return cudaErrorInvalidValue;
-  if (C::splitStab && f.Qs != C::QS) return cudaErrorInvalidValue;
+  if ((C::splitStab || CS) && f.Qs != C::QS) return cudaErrorInvalidValue;
+  if (CS && (!f.cstate || !f.te_final || !f.w_stab)) return cudaErrorInvalidValue;
   const size_t smem = sizeof(double) * C::nsmem;
   // the attribute is per device: one flag per device ordinal, not per process (a process may hold solvers on several GPUs)
   static bool configured[64] = {};
@@ -641,12 +688,23 @@ cudaError_t launch_cfg(const TentKernelArgs& a, const FastArgs& f, cudaStream_t 
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   if (dev < 0 || dev >= 64 || !configured[dev]) {
-    e = cudaFuncSetAttribute(tent_kernel_fast<D, P, FO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    e = cudaFuncSetAttribute(tent_kernel_fast<D, P, FO, CS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     if (dev >= 0 && dev < 64) configured[dev] = true;
   }
-  tent_kernel_fast<D, P, FO><<<a.ntents, kThreads, smem, stream>>>(a, f);
+  tent_kernel_fast<D, P, FO, CS><<<a.ntents, kThreads, smem, stream>>>(a, f);
   return cudaGetLastError();
+}
+
+// compact state only where the compact degree-2P rule exists and is smaller than the order-2P rule
+template <int D, int P, int FO>
+cudaError_t launch_any(const TentKernelArgs& a, const FastArgs& f, cudaStream_t stream) {
+  if constexpr (Cfg<D, P, FO>::QS > 0 && Cfg<D, P, FO>::QS < Cfg<D, P, FO>::Q && Cfg<D, P, FO>::rhsFirst) {
+    if (f.cstate) return launch_cfg<D, P, FO, 1>(a, f, stream);
+  } else {
+    if (f.cstate) return cudaErrorInvalidValue;
+  }
+  return launch_cfg<D, P, FO, 0>(a, f, stream);
 }
 
 template <int D, int P, int FO>
@@ -655,6 +713,20 @@ constexpr size_t smem_cfg() { return sizeof(double) * Cfg<D, P, FO>::nsmem; }
 }  // namespace
 
 #define NGST_FAST_CONFIGS(X) X(3, 4) X(3, 3) X(3, 2) X(2, 4) X(2, 5) X(2, 3) X(2, 6)
+
+// points of the compact state rule of (D, order, fosystem), 0 where the variant has no compact-state form
+int tent_fast_compact_points(int D, int order, int fosystem) {
+#define X(d, p)                                                                                              \
+  if (D == d && order == p) {                                                                                \
+    using C0 = Cfg<d, p, 0>;                                                                                 \
+    using C1 = Cfg<d, p, 1>;                                                                                 \
+    if (fosystem) return (C1::QS > 0 && C1::QS < C1::Q && C1::rhsFirst) ? C1::QS : 0;                        \
+    return (C0::QS > 0 && C0::QS < C0::Q && C0::rhsFirst) ? C0::QS : 0;                                      \
+  }
+  NGST_FAST_CONFIGS(X)
+#undef X
+  return 0;
+}
 
 bool tent_fast_available(int D, int order) {
 #define X(d, p) if (D == d && order == p) return true;
@@ -673,7 +745,7 @@ size_t tent_fast_smem_bytes(int D, int order, int fosystem) {
 cudaError_t launch_tent_fast(int D, int order, int fosystem, const TentKernelArgs& a, const FastArgs& f,
                              cudaStream_t stream) {
   if (a.ntents <= 0) return cudaSuccess;
-#define X(d, p) if (D == d && order == p) return fosystem ? launch_cfg<d, p, 1>(a, f, stream) : launch_cfg<d, p, 0>(a, f, stream);
+#define X(d, p) if (D == d && order == p) return fosystem ? launch_any<d, p, 1>(a, f, stream) : launch_any<d, p, 0>(a, f, stream);
   NGST_FAST_CONFIGS(X)
 #undef X
   return cudaErrorInvalidValue;

@@ -42,7 +42,13 @@ struct FastArgs {
   // compact rule exact to degree 2p for the bottom-face stabilisation Gram (second-order form), when the table has one
   const double* lam_stab;   // Qs * (D+1)
   const double* sqrtw_stab; // Qs
+  const double* w_stab;     // Qs
   int Qs;
+  // compact state (tent_fast.cu, CS = 1): nel * ncomp * Qs, row = [comp][point of the compact rule]; nullptr = the tents
+  // read and write the public order-2p rows. te_final[te] != 0: this tent is the last one of the slab (or of the
+  // requested levels) to contain the element -> it also writes the public row.
+  double* cstate;
+  const unsigned char* te_final;
   // column-compressed basis matrix (monomial j -> functions), for sol -> monomial coefficients
   const int* cptr;      // npoly + 1
   const int* crow;      // nnz
@@ -53,6 +59,7 @@ struct FastArgs {
 };
 
 bool tent_fast_available(int D, int order);
+int tent_fast_compact_points(int D, int order, int fosystem);
 size_t tent_fast_smem_bytes(int D, int order, int fosystem);
 cudaError_t launch_tent_fast(int D, int order, int fosystem, const TentKernelArgs& a, const FastArgs& f,
                              cudaStream_t stream);

@@ -46,6 +46,13 @@ PartitionPlan make_partition_plan(const SimplexMesh& m, const TentSlab& slab, co
     }
   }
 
+  p.final_level.assign(p.loc2glob.size(), -1);
+  for (int t = 0; t < slab.ntents; t++)
+    for (int j = slab.els.off[t]; j < slab.els.off[t + 1]; j++) {
+      const int le = p.glob2loc[slab.els.val[j]];
+      if (le >= 0) p.final_level[le] = std::max(p.final_level[le], slab.level[t]);
+    }
+
   // exchange lists, level by level
   std::vector<std::vector<int>> snd(nranks), rcv(nranks);
   p.send_off.assign(1, 0);

@@ -19,6 +19,7 @@ struct PartitionPlan {
   std::vector<int> loc2glob;         // local element -> global element, ascending
   std::vector<int> glob2loc;         // global element -> local element or -1
   std::vector<unsigned char> owned;  // per local element: counted by this rank in reductions
+  std::vector<int> final_level;      // per local element: level of the last tent of the GLOBAL slab that contains it, -1 if none
   // rows exchanged after level l with peer q: [off[l*nranks+q], off[l*nranks+q+1]) into *_el (LOCAL element ids,
   // ordered by global element id on both sides)
   std::vector<int> send_off, send_el;

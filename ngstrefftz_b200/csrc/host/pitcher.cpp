@@ -378,6 +378,61 @@ double TentSlab::MaxSlope() const {
   return s;
 }
 
+namespace {
+// What follows the greedy loop (and an import): dependency table, top-front slopes, level sets.
+void finalize_slab(TentSlab& S, const Pitcher& P, const std::vector<int>& dep_src, const std::vector<int>& dep_dst) {
+  const SimplexMesh& m = *S.mesh;
+  const int D = m.D, nv = m.nv;
+  // dependency graph, tents.cpp:313-321
+  // (stable counting sort by source tent: every row keeps the order in which its dependents were appended)
+  S.dag.off.assign(S.ntents + 1, 0);
+  for (int s : dep_src) S.dag.off[s + 1]++;
+  for (int i = 0; i < S.ntents; i++) S.dag.off[i + 1] += S.dag.off[i];
+  S.dag.val.resize(dep_src.size());
+  {
+    std::vector<int> pos(S.dag.off.begin(), S.dag.off.end() - 1);
+    for (size_t k = 0; k < dep_src.size(); k++) S.dag.val[pos[dep_src[k]]++] = dep_dst[k];
+  }
+
+  // slope of the top front per tent, tents.cpp:323-356
+  S.maxslope.assign(S.ntents, 0.0);
+#pragma omp parallel
+  {
+    // front height of the patch vertices of the current tent (every S.vertex of a patch element is the tent S.vertex or one of S.nbv)
+    std::vector<double> vt(nv, 0.0);
+#pragma omp for schedule(static)
+    for (int i = 0; i < S.ntents; i++) {
+      vt[S.vertex[i]] = S.ttop[i];
+      for (int q = S.nbv.off[i]; q < S.nbv.off[i + 1]; q++) vt[S.nbv.val[q]] = S.nbtime[q];
+      double ms = 0.0;
+      for (int j = S.els.off[i]; j < S.els.off[i + 1]; j++) {
+        const int el = S.els.val[j];
+        const int* ev = m.elverts(el);
+        const double* g = P.grads(el);
+        double gp[3] = {0, 0, 0};
+        for (int d = 0; d < D; d++)
+          for (int k = 0; k <= D; k++) gp[d] += g[k * D + d] * vt[ev[k]];
+        const double nrm = norm(gp, D);
+        if (nrm > ms) ms = nrm;
+      }
+      S.maxslope[i] = ms;
+    }
+  }
+
+  // S.level sets (BSP schedule replacing RunParallelDependency, paralleldepend.hpp:20-131)
+  int nl = 0;
+  for (int i = 0; i < S.ntents; i++) nl = std::max(nl, S.level[i] + 1);
+  S.level_off.assign(nl + 1, 0);
+  for (int i = 0; i < S.ntents; i++) S.level_off[S.level[i] + 1]++;
+  for (int l = 0; l < nl; l++) S.level_off[l + 1] += S.level_off[l];
+  S.level_tents.resize(S.ntents);
+  {
+    std::vector<int> pos(S.level_off.begin(), S.level_off.end() - 1);
+    for (int i = 0; i < S.ntents; i++) S.level_tents[pos[S.level[i]]++] = i;
+  }
+}
+}  // namespace
+
 bool TentSlab::PitchTents(double adt, bool calc_local_ct, double global_ct) {
   generation++;
   if (!mesh) throw std::runtime_error("TentSlab: no mesh");
@@ -515,55 +570,133 @@ bool TentSlab::PitchTents(double adt, bool calc_local_ct, double global_ct) {
 
   if (!slab_complete) std::printf("Error: the algorithm could not pitch the whole slab\n");
 
-  // dependency graph, tents.cpp:313-321
-  // (stable counting sort by source tent: every row keeps the order in which its dependents were appended)
-  dag.off.assign(ntents + 1, 0);
-  for (int s : dep_src) dag.off[s + 1]++;
-  for (int i = 0; i < ntents; i++) dag.off[i + 1] += dag.off[i];
-  dag.val.resize(dep_src.size());
-  {
-    std::vector<int> pos(dag.off.begin(), dag.off.end() - 1);
-    for (size_t k = 0; k < dep_src.size(); k++) dag.val[pos[dep_src[k]]++] = dep_dst[k];
-  }
-
-  // slope of the top front per tent, tents.cpp:323-356
-  maxslope.assign(ntents, 0.0);
-#pragma omp parallel
-  {
-    // front height of the patch vertices of the current tent (every vertex of a patch element is the tent vertex or one of nbv)
-    std::vector<double> vt(nv, 0.0);
-#pragma omp for schedule(static)
-    for (int i = 0; i < ntents; i++) {
-      vt[vertex[i]] = ttop[i];
-      for (int q = nbv.off[i]; q < nbv.off[i + 1]; q++) vt[nbv.val[q]] = nbtime[q];
-      double ms = 0.0;
-      for (int j = els.off[i]; j < els.off[i + 1]; j++) {
-        const int el = els.val[j];
-        const int* ev = m.elverts(el);
-        const double* g = P.grads(el);
-        double gp[3] = {0, 0, 0};
-        for (int d = 0; d < D; d++)
-          for (int k = 0; k <= D; k++) gp[d] += g[k * D + d] * vt[ev[k]];
-        const double nrm = norm(gp, D);
-        if (nrm > ms) ms = nrm;
-      }
-      maxslope[i] = ms;
-    }
-  }
-
-  // level sets (BSP schedule replacing RunParallelDependency, paralleldepend.hpp:20-131)
-  int nl = 0;
-  for (int i = 0; i < ntents; i++) nl = std::max(nl, level[i] + 1);
-  level_off.assign(nl + 1, 0);
-  for (int i = 0; i < ntents; i++) level_off[level[i] + 1]++;
-  for (int l = 0; l < nl; l++) level_off[l + 1] += level_off[l];
-  level_tents.resize(ntents);
-  {
-    std::vector<int> pos(level_off.begin(), level_off.end() - 1);
-    for (int i = 0; i < ntents; i++) level_tents[pos[level[i]]++] = i;
-  }
+  finalize_slab(*this, P, dep_src, dep_dst);
   pitched = slab_complete;
   return pitched;
+}
+
+// A slab from tents pitched elsewhere -- the fields python_tents.cpp:119-128 exposes of every Tent of a real
+// TentPitchedSlab (vertex, tbot, ttop, nbv, nbtime, els, level, internal_facets), flattened. The tents are taken as they
+// are (ids, order inside the lists, times); what the solver needs beyond them is derived here exactly as after pitching:
+// dependency table (tents.cpp:206, 313-321), top-front slopes, level sets. The lists are checked for consistency with the
+// mesh and for the property the level-parallel schedule rests on: tents that share an element have increasing levels
+// in tent order.
+void TentSlab::ImportTents(int n, double adt, const int* vertex_, const int* level_, const double* tbot_,
+                           const double* ttop_, const int* nb_off, const int* nbv_, const double* nbtime_,
+                           const int* el_off, const int* els_, const int* facet_off, const int* facets_) {
+  if (!mesh) throw std::runtime_error("TentSlab: no mesh");
+  const SimplexMesh& m = *mesh;
+  const int D = m.D, nv = m.nv;
+  auto bad = [](const std::string& what) { throw std::invalid_argument("import tents: " + what); };
+  if (n < 1 || !(adt > 0)) bad("need at least one tent and a positive slab height");
+  if (!vertex_ || !tbot_ || !ttop_ || !nb_off || !nbv_ || !nbtime_ || !el_off || !els_) bad("null array");
+  if ((facet_off == nullptr) != (facets_ == nullptr)) bad("facet_off and facets go together");
+  if (nb_off[0] != 0 || el_off[0] != 0 || (facet_off && facet_off[0] != 0)) bad("offset arrays must start at 0");
+  const double tol = 1e-12 * adt;
+  std::vector<char> mark(nv, 0);
+  for (int t = 0; t < n; t++) {
+    const int v = vertex_[t];
+    if (v < 0 || v >= nv) bad("tent vertex out of range");
+    if (nb_off[t + 1] < nb_off[t] || el_off[t + 1] <= el_off[t] || (facet_off && facet_off[t + 1] < facet_off[t]))
+      bad("offset arrays must be non-decreasing (and every tent needs an element)");
+    if (!(ttop_[t] > tbot_[t]) || tbot_[t] < -tol || ttop_[t] > adt + tol) bad("tent times outside [0, dt] or ttop <= tbot");
+    mark[v] = 1;
+    for (int q = nb_off[t]; q < nb_off[t + 1]; q++) {
+      if (nbv_[q] < 0 || nbv_[q] >= nv) bad("neighbour vertex out of range");
+      if (!(nbtime_[q] >= tbot_[t] - tol) && !(nbtime_[q] <= ttop_[t] + tol)) bad("neighbour time is not a number");
+      mark[nbv_[q]] = 1;
+    }
+    for (int j = el_off[t]; j < el_off[t + 1]; j++) {
+      const int el = els_[j];
+      if (el < 0 || el >= m.nel) bad("element out of range");
+      const int* ev = m.elverts(el);
+      bool has = false;
+      for (int k = 0; k <= D; k++) {
+        has = has || ev[k] == v;
+        if (!mark[ev[k]]) bad("an element of a tent has a vertex that is neither the tent vertex nor one of its neighbours");
+      }
+      if (!has) bad("an element of a tent does not contain the tent vertex");
+    }
+    if (facet_off)
+      for (int j = facet_off[t]; j < facet_off[t + 1]; j++)
+        if (facets_[j] < 0 || facets_[j] >= (D == 1 ? nv : m.nfacets)) bad("facet out of range");
+    mark[v] = 0;
+    for (int q = nb_off[t]; q < nb_off[t + 1]; q++) mark[nbv_[q]] = 0;
+  }
+
+  // levels and dependencies as the greedy loop assigns them (tents.cpp:199-217), replayed over the given tent order
+  std::vector<int> vertices_level(nv, 0), latest_tent(nv, -1), dep_src, dep_dst, lev_new(n, 0);
+  for (int t = 0; t < n; t++) {
+    const int v = vertex_[t];
+    const int lev = level_ ? level_[t] : vertices_level[v];
+    if (lev < 0) bad("negative level");
+    lev_new[t] = lev;
+    for (int q = nb_off[t]; q < nb_off[t + 1]; q++) {
+      const int nb = nbv_[q];
+      vertices_level[nb] = std::max(vertices_level[nb], lev + 1);
+      if (latest_tent[nb] != -1) { dep_src.push_back(latest_tent[nb]); dep_dst.push_back(t); }
+    }
+    latest_tent[v] = t;
+    vertices_level[v] = std::max(vertices_level[v], lev) + 1;
+  }
+  {
+    std::vector<int> last(m.nel, -1);
+    for (int t = 0; t < n; t++)
+      for (int j = el_off[t]; j < el_off[t + 1]; j++) {
+        int& l = last[els_[j]];
+        if (l >= lev_new[t]) bad("two tents that share an element do not have increasing levels in tent order");
+        l = lev_new[t];
+      }
+  }
+
+  // everything checked: replace the slab's tents
+  generation++;
+  dt = adt;
+  pitched = false;
+  ntents = n;
+  vertex.assign(vertex_, vertex_ + n);
+  level.swap(lev_new);
+  tbot.assign(tbot_, tbot_ + n);
+  ttop.assign(ttop_, ttop_ + n);
+  nbv.off.assign(nb_off, nb_off + n + 1);
+  nbv.val.assign(nbv_, nbv_ + nb_off[n]);
+  nbtime.assign(nbtime_, nbtime_ + nb_off[n]);
+  els.off.assign(el_off, el_off + n + 1);
+  els.val.assign(els_, els_ + el_off[n]);
+  nlayers = 0;
+  for (int t = 0; t < n; t++) nlayers = std::max(nlayers, level[t]);
+
+  if (facet_off) {
+    facets.off.assign(facet_off, facet_off + n + 1);
+    facets.val.assign(facets_, facets_ + facet_off[n]);
+  } else {
+    // internal facets of the vertex patch as the pitcher lists them (tents.cpp:219-247)
+    facets.off.assign(1, 0);
+    facets.val.clear();
+    for (int t = 0; t < n; t++) {
+      const int vi = vertex[t];
+      if (D == 1) facets.val.push_back(vi);
+      else if (D == 2)
+        for (int i = 0; i < m.v2e.size(vi); i++) facets.val.push_back(m.v2e.row(vi)[i]);
+      else {
+        const size_t b = facets.val.size();
+        for (int i = 0; i < m.v2el.size(vi); i++) {
+          const int el = m.v2el.row(vi)[i];
+          for (int k = 0; k < 4; k++) {
+            const int f = m.el2facet[(size_t)el * 4 + k];
+            const int* fv = &m.facet2v[(size_t)f * 3];
+            if ((fv[0] == vi || fv[1] == vi || fv[2] == vi) && std::find(facets.val.begin() + b, facets.val.end(), f) == facets.val.end())
+              facets.val.push_back(f);
+          }
+        }
+      }
+      facets.off.push_back((int)facets.val.size());
+    }
+  }
+  Pitcher P(m, method);
+  P.CacheGradients();
+  finalize_slab(*this, P, dep_src, dep_dst);
+  pitched = true;
 }
 
 }  // namespace ngst

@@ -44,6 +44,13 @@ struct TentSlab {
 
   // returns false when the front could not reach dt (tents.cpp:265-288)
   bool PitchTents(double dt, bool local_ct, double global_ct);
+
+  // Tents pitched elsewhere (the Tent fields of python_tents.cpp:119-128, flattened; *_off have n + 1 entries). level and
+  // facet_off / facets may be null: levels are then replayed as the greedy loop assigns them, internal facets taken from
+  // the mesh. Throws std::invalid_argument on lists that are inconsistent with the mesh or not level-schedulable.
+  void ImportTents(int n, double dt, const int* vertex, const int* level, const double* tbot, const double* ttop,
+                   const int* nb_off, const int* nbv, const double* nbtime, const int* el_off, const int* els,
+                   const int* facet_off, const int* facets);
 };
 
 }  // namespace ngst

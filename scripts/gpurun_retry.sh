@@ -1,0 +1,10 @@
+#!/bin/bash
+# Builder-side helper: retries a gpurun call while the pod answers busy (exit 3). usage: gpurun_retry.sh <log> <gpurun args...>
+LOG=$1; shift
+for i in $(seq 1 12); do
+  /usr/local/graft/bin/gpurun "$@" > "$LOG" 2>&1
+  rc=$?
+  if [ $rc -ne 3 ]; then exit $rc; fi
+  sleep 150
+done
+exit 3
