@@ -189,6 +189,19 @@ int ngst_twave_set_kernel_mode(ngst_twave* t, int mode);
  * ngst_twave_compact_state: 1 when the next Propagate will use it. */
 int ngst_twave_set_compact_state(ngst_twave* t, int on);
 int ngst_twave_compact_state(const ngst_twave* t);
+/* Factor cache (no reference counterpart; default on where the compact state is in use). The matrix of a tent depends on
+ * the tent's geometry and the wavespeed only -- not on the state, the boundary datum or the time -- and a slab is
+ * propagated many times (docs/notebooks/twavetents.ipynb: one TentSlab, a loop of Propagate calls). The reference
+ * re-assembles and re-inverts it in every Propagate (src/twavetents.cpp:119-164, 64-70). Here the first Propagate forms
+ * the inverse of every tent matrix (as the reference's Solve does) and keeps it in HBM (8 N (N rounded up to 8) bytes per
+ * tent: 24.6 kB at D = 3, p = 4); every later Propagate builds the right-hand sides (src/twavetents.cpp:230-267, 373-433),
+ * multiplies by the stored inverses and evaluates (src/twavetents.cpp:541-590). Results are those of inverse-then-multiply,
+ * i.e. the reference's own arithmetic. on == 0: assemble and solve in every Propagate (the memory is kept until the solver
+ * is destroyed). If the memory cannot be allocated the solver silently keeps assembling.
+ * ngst_twave_factor_cache returns 0 = not in use, 1 = the next Propagate builds the cache, 2 = the next Propagate applies it;
+ * *bytes (may be NULL) = device memory held by the cache. */
+int ngst_twave_set_factor_cache(ngst_twave* t, int on);
+int ngst_twave_factor_cache(const ngst_twave* t, long long* bytes);
 int ngst_twave_ntents_fast(const ngst_twave* t);
 /* device time of the last Propagate in ms (CUDA events on the solver's stream) and kernel launches in it */
 double ngst_twave_last_ms(const ngst_twave* t);

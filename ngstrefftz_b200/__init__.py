@@ -679,6 +679,17 @@ class TWaveTents(TrefftzTents):
     def compact_state(self):
         return bool(lib.ngst_twave_compact_state(self._h))
 
+    def set_factor_cache(self, on=True):
+        """Keep the inverse of every tent matrix in HBM after the first Propagate (default) or assemble and solve in every
+        Propagate (ngst_twave_set_factor_cache)."""
+        check(lib.ngst_twave_set_factor_cache(self._h, int(bool(on))))
+
+    def factor_cache(self):
+        """(state, bytes): state 0 = not in use, 1 = next Propagate builds it, 2 = next Propagate applies it."""
+        b = C.c_longlong(0)
+        st = lib.ngst_twave_factor_cache(self._h, C.byref(b))
+        return int(st), int(b.value)
+
     def ntents_fast(self):
         return lib.ngst_twave_ntents_fast(self._h)
 

@@ -89,6 +89,8 @@ _SIGS = {
     "ngst_twave_ntents_fast": (C.c_int, [c_vp]),
     "ngst_twave_set_compact_state": (C.c_int, [c_vp, C.c_int]),
     "ngst_twave_compact_state": (C.c_int, [c_vp]),
+    "ngst_twave_set_factor_cache": (C.c_int, [c_vp, C.c_int]),
+    "ngst_twave_factor_cache": (C.c_int, [c_vp, c_llp]),
     "ngst_twave_last_ms": (C.c_double, [c_vp]),
     "ngst_twave_last_launches": (C.c_int, [c_vp]),
     "ngst_twave_get_wavefront": (C.c_int, [c_vp, c_dp]),

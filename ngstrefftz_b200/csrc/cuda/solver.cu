@@ -388,6 +388,7 @@ Solver::~Solver() {
   if (d_tmp_a_) cudaFree(d_tmp_a_);
   if (d_tmp_b_) cudaFree(d_tmp_b_);
   if (d_cstate_) cudaFree(d_cstate_);
+  for (double* p : d_ainv_) if (p) cudaFree(p);
   if (h_flags_) cudaFreeHost(h_flags_);
   if (d_sendbuf_) cudaFree(d_sendbuf_);
   if (d_recvbuf_) cudaFree(d_recvbuf_);
@@ -676,6 +677,26 @@ void Solver::Propagate(int level_limit) {
     fa.cstate = d_cstate_;
     fa.te_final = FinalFlags(partial ? level_limit : -1);
   }
+  // factor cache: first full Propagate of this system stores the inverses (MODE 1), later ones apply them (MODE 2)
+  fa.ainv = nullptr;
+  fa.mode = 0;
+  const int fo = fosystem_;
+  if (compact && factor_cache_enabled_ && !cache_failed_ && (ainv_valid_[fo] || !partial)) {
+    if (!d_ainv_[fo]) {
+      const size_t bytes = sizeof(double) * tent_fast_inverse_doubles(mesh_.D, order_, fo) * (size_t)std::max(staged_.ntents, 1);
+      if (cudaMalloc(&d_ainv_[fo], bytes) != cudaSuccess) {
+        cudaGetLastError();  // not enough memory for the cache: keep assembling in every Propagate
+        d_ainv_[fo] = nullptr;
+        cache_failed_ = true;
+      } else {
+        ainv_bytes_[fo] = bytes;
+      }
+    }
+    if (d_ainv_[fo]) {
+      fa.ainv = d_ainv_[fo];
+      fa.mode = ainv_valid_[fo] ? 2 : 1;
+    }
+  }
   int launches = 0;
   CU(cudaEventRecord(ev0_, stream_));
   if (bnd_family_ >= 0 && staged_.nbnd_values > 0) {
@@ -805,6 +826,7 @@ void Solver::Propagate(int level_limit) {
                              "the dependency-driven launch (scheduling failure, not a numerical one); the state is invalid");
     throw std::domain_error("Propagate: singular local system in " + std::to_string(sing) + " pivot step(s)");
   }
+  if (fa.mode == 1) ainv_valid_[fo] = true;  // (a singular system has thrown above: the inverses are then not trusted)
   if (!compact) cstate_valid_ = false;   // the public rows moved on without the compact copy
   if (!partial) timeshift_ += slab_.dt;  // twavetents.cpp:173
 }

@@ -96,6 +96,13 @@ class Solver {
   // the state on the compact degree-2p rule that the tents read and write; off = the tents work on the public rows (A/B).
   void set_compact_state(bool on) { compact_enabled_ = on; }
   bool compact_state_active() const { return UseCompact(); }
+  // Factor cache (tent_fast.cu MODE 1 / 2; default on, needs the compact state): the inverse of every tent matrix is formed
+  // by the first Propagate and stored in HBM (NP x N doubles per tent); later Propagates of the same slab geometry only
+  // build right-hand sides, apply the stored inverses and evaluate. off: assemble and solve in every Propagate.
+  void set_factor_cache(bool on) { factor_cache_enabled_ = on; }
+  // 0 = not in use, 1 = the next Propagate assembles, inverts and stores, 2 = the next Propagate applies stored inverses
+  int factor_cache_state() const { return !(UseCompact() && factor_cache_enabled_ && !cache_failed_) ? 0 : (ainv_valid_[fosystem_] ? 2 : 1); }
+  size_t factor_cache_bytes() const { return ainv_bytes_[0] + ainv_bytes_[1]; }
   double last_ms() const { return last_ms_; }
   int last_launches() const { return last_launches_; }
 
@@ -197,6 +204,10 @@ class Solver {
   // multi-GPU: per (level, peer) the exchanged rows whose element becomes final in that level (public rows follow)
   std::vector<int> sendf_off_, recvf_off_;
   int *d_sendf_el_ = nullptr, *d_recvf_el_ = nullptr;
+  bool factor_cache_enabled_ = true, cache_failed_ = false;
+  double* d_ainv_[2] = {nullptr, nullptr};  // [fosystem]
+  size_t ainv_bytes_[2] = {0, 0};
+  bool ainv_valid_[2] = {false, false};
   bool UseCompact() const { return cs_points_ > 0 && compact_enabled_ && !force_generic_; }
   void ProjectCompact();
   const unsigned char* FinalFlags(int level_limit);

@@ -22,6 +22,7 @@
 #include "basis_eval_gen.cuh"
 #include "dmma_tiles.cuh"
 #include "tent_solve.cuh"
+#include "tma_bulk.cuh"
 #include "tent_fast.cuh"
 #include "tent_kernel.cuh"
 
@@ -108,13 +109,20 @@ __device__ __forceinline__ void eval_part(int part, const double* xi, F&& f) {
 // row g the bottom-face integrals against degree-<=P test functions agree: sum_q w_q phi(x_q) g_q = sum_r v_r phi(y_r) (M g)_r
 // with M the transfer through the degree-P polynomials (rule_transfer_matrix; applied once by SetInitial). The public
 // Q-point rows are written only by the LAST tent of the slab that contains the element (f.te_final).
-template <int D, int P, int FO, int CS>
-__global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a, FastArgs f) {
+//
+// MODE (factor cache): the tent matrix A depends on the geometry of the tent only, not on the
+// state, and a slab is propagated many times (the reference re-assembles and re-inverts A on every Propagate,
+// src/twavetents.cpp:119-164). MODE 0 assembles and solves. MODE 1 assembles, forms A^-1 (as the reference does) and
+// stores it in HBM (f.ainv, transposed), then applies it. MODE 2 skips the assembly: right-hand side, sol = A^-1 b with
+// the stored inverse (fetched by one bulk asynchronous copy behind the right-hand-side pass), evaluation.
+template <int D, int P, int FO, int CS, int MODE>
+__global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(TentKernelArgs a, FastArgs f) {
   using C = Cfg<D, P, FO>;
   static_assert(!CS || (C::QS > 0 && C::rhsFirst), "compact state needs the compact degree-2P rule");
+  static_assert(MODE == 0 || CS, "the factor cache is built on the compact-state variant");
   constexpr int d1 = C::d1, N = C::N, NT = C::NT, NP = C::NP, G = C::G, Q = C::Q, QT = C::QT, ZS = C::ZS, LDA = C::LDA;
   constexpr int NACC = C::NACC, FE = C::FE, FF = C::FF, npoly = C::npoly, npm1 = C::npm1;
-  extern __shared__ double sm[];
+  extern __shared__ __align__(16) double sm[];
   double* const A = sm + C::oA;
   double* const bv = sm + C::oB;
   double* const Z = sm + C::oZ;
@@ -157,6 +165,21 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
   const int tf0 = a.tf_off[tent], nfc = a.tf_off[tent + 1] - tf0;
   const int npts = nel * Q;
   const int nptt = nel * QT;
+  // stored inverse of this tent (MODE 1 writes, MODE 2 reads): N columns of NP doubles, behind the NS * NP partial sums of
+  // the right-hand-side pass in the (otherwise unused) operand buffer
+  constexpr int kInvOff = 4 * NP;
+  static_assert(MODE == 0 || kInvOff + NP * N <= NP * ZS, "the stored inverse must fit in the operand buffer");
+  double* const invS = Z + kInvOff;
+  [[maybe_unused]] double* const invG = (MODE != 0) ? f.ainv + (size_t)tent * (NP * N) : nullptr;
+  __shared__ __align__(8) unsigned long long s_bar;
+  if constexpr (MODE == 2) {
+    if (tid == 0) tma::mbar_init(&s_bar, 1);
+    __syncthreads();
+    if (tid == 0) {
+      tma::mbar_expect(&s_bar, NP * N * 8);
+      tma::bulk_load(invS, invG, NP * N * 8, &s_bar);
+    }
+  }
 
   if (C::rhsFirst) {
     // ---------------------------------------------------------------- bottom faces: right-hand side  (twavetents.cpp:209-267)
@@ -301,13 +324,14 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
     }
     __syncthreads();
   }
+  double bpart[G];
+#pragma unroll
+  for (int j = 0; j < G; j++) bpart[j] = 0.0;
+  if constexpr (MODE != 2) {  // ============================ assembly of the tent matrix (skipped when its inverse is stored)
   for (int i = tid; i < NP * ZS; i += kThreads) Z[i] = 0.0;  // rows of the padding functions stay zero
   double acc[NACC][2];
 #pragma unroll
   for (int i = 0; i < NACC; i++) acc[i][0] = acc[i][1] = 0.0;
-  double bpart[G];
-#pragma unroll
-  for (int j = 0; j < G; j++) bpart[j] = 0.0;
   __syncthreads();
 
   // ------------------------------------------------------------------ top faces: A += B W B^T  (twavetents.cpp:270-313)
@@ -553,6 +577,7 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
       default: flush_full<NT, NACC, 3>(acc, A, LDA, g, k); break;
     }
   }
+  }  // ======================================================= MODE != 2
 
   // ------------------------------------------------------------------ right-hand side
   if (C::rhsFirst) {
@@ -569,8 +594,30 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
   __syncthreads();
   // ------------------------------------------------------------------ Solve (64-70 forms the inverse with LAPACK)
   // Interior tents (no boundary face) have a symmetric positive definite matrix (Z Z^T + stabilisation): no pivoting.
-  gauss_jordan_solve<N, NP, kThreads>(A, LDA, bv, nfc == 0, a.singular);
-  __syncthreads();
+  if constexpr (MODE == 0) {
+    gauss_jordan_solve<N, NP, kThreads>(A, LDA, bv, nfc == 0, a.singular);
+    __syncthreads();
+  } else {
+    const double* inv;
+    if constexpr (MODE == 1) {
+      gauss_jordan_invert<N, NP, kThreads>(A, LDA, nfc == 0, a.singular, invG);
+      __syncthreads();  // the inverse this CTA has just written is visible to all of its threads
+      inv = invG;
+    } else {
+      tma::mbar_wait(&s_bar, 0);
+      inv = invS;
+    }
+    // sol = A^-1 b. Thread (h, i) sums the columns j = h, h + 2, .. of row i (identical arithmetic in MODE 1 and 2)
+    const int i = tid & 63, h = tid >> 6;
+    double part = 0.0;
+    if (i < N)
+      for (int j = h; j < N; j += 2) part = fma(inv[(size_t)j * NP + i], bv[j], part);
+    __syncthreads();
+    if (h == 1 && i < N) cm[i] = part;   // cm is free until the evaluation
+    __syncthreads();
+    if (h == 0 && i < N) bv[i] = part + cm[i];
+    __syncthreads();
+  }
 
   // ------------------------------------------------------------------ CalcTentElEval (541-590) in the monomial basis
   // u = sum_i sol_i phi_i = sum_j cm_j xi^alpha_j with cm = M^T sol; derivative coefficients in the degree <= P-1 basis.
@@ -675,24 +722,25 @@ __global__ void __launch_bounds__(kThreads, 3) tent_kernel_fast(TentKernelArgs a
   }
 }
 
-template <int D, int P, int FO, int CS>
+template <int D, int P, int FO, int CS, int MODE>
 cudaError_t launch_cfg(const TentKernelArgs& a, const FastArgs& f, cudaStream_t stream) {
   using C = Cfg<D, P, FO>;
   if (a.Q != C::Q || f.Qt != C::QT || a.N != C::N || a.npoly != C::npoly) return cudaErrorInvalidValue;
   if ((C::splitStab || CS) && f.Qs != C::QS) return cudaErrorInvalidValue;
   if (CS && (!f.cstate || !f.te_final || !f.w_stab)) return cudaErrorInvalidValue;
+  if (MODE != 0 && !f.ainv) return cudaErrorInvalidValue;
   const size_t smem = sizeof(double) * C::nsmem;
   // the attribute is per device: one flag per device ordinal, not per process (a process may hold solvers on several GPUs)
-  static bool configured[64] = {};
+  static bool configured[64] = {};  // (one flag set per template instance)
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   if (dev < 0 || dev >= 64 || !configured[dev]) {
-    e = cudaFuncSetAttribute(tent_kernel_fast<D, P, FO, CS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    e = cudaFuncSetAttribute(tent_kernel_fast<D, P, FO, CS, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     if (dev >= 0 && dev < 64) configured[dev] = true;
   }
-  tent_kernel_fast<D, P, FO, CS><<<a.ntents, kThreads, smem, stream>>>(a, f);
+  tent_kernel_fast<D, P, FO, CS, MODE><<<a.ntents, kThreads, smem, stream>>>(a, f);
   return cudaGetLastError();
 }
 
@@ -700,11 +748,16 @@ cudaError_t launch_cfg(const TentKernelArgs& a, const FastArgs& f, cudaStream_t 
 template <int D, int P, int FO>
 cudaError_t launch_any(const TentKernelArgs& a, const FastArgs& f, cudaStream_t stream) {
   if constexpr (Cfg<D, P, FO>::QS > 0 && Cfg<D, P, FO>::QS < Cfg<D, P, FO>::Q && Cfg<D, P, FO>::rhsFirst) {
-    if (f.cstate) return launch_cfg<D, P, FO, 1>(a, f, stream);
+    if (f.cstate) {
+      if (f.mode == 1) return launch_cfg<D, P, FO, 1, 1>(a, f, stream);
+      if (f.mode == 2) return launch_cfg<D, P, FO, 1, 2>(a, f, stream);
+      return launch_cfg<D, P, FO, 1, 0>(a, f, stream);
+    }
   } else {
     if (f.cstate) return cudaErrorInvalidValue;
   }
-  return launch_cfg<D, P, FO, 0>(a, f, stream);
+  if (f.mode != 0) return cudaErrorInvalidValue;  // the factor cache needs the compact state
+  return launch_cfg<D, P, FO, 0, 0>(a, f, stream);
 }
 
 template <int D, int P, int FO>
@@ -723,6 +776,15 @@ int tent_fast_compact_points(int D, int order, int fosystem) {
     if (fosystem) return (C1::QS > 0 && C1::QS < C1::Q && C1::rhsFirst) ? C1::QS : 0;                        \
     return (C0::QS > 0 && C0::QS < C0::Q && C0::rhsFirst) ? C0::QS : 0;                                      \
   }
+  NGST_FAST_CONFIGS(X)
+#undef X
+  return 0;
+}
+
+// doubles per tent of the stored inverse (NP x N), 0 without a fast variant
+size_t tent_fast_inverse_doubles(int D, int order, int fosystem) {
+#define X(d, p) \
+  if (D == d && order == p) return fosystem ? (size_t)Cfg<d, p, 1>::NP * Cfg<d, p, 1>::N : (size_t)Cfg<d, p, 0>::NP * Cfg<d, p, 0>::N;
   NGST_FAST_CONFIGS(X)
 #undef X
   return 0;

@@ -49,6 +49,10 @@ struct FastArgs {
   // requested levels) to contain the element -> it also writes the public row.
   double* cstate;
   const unsigned char* te_final;
+  // factor cache (tent_fast.cu, MODE): 0 = assemble and solve, 1 = assemble, invert, store in ainv, apply, 2 = apply the
+  // stored inverse. ainv: per staged tent NP x N doubles, the inverse transposed (column j of A^-1 at [j * NP, j * NP + N)).
+  double* ainv;
+  int mode;
   // column-compressed basis matrix (monomial j -> functions), for sol -> monomial coefficients
   const int* cptr;      // npoly + 1
   const int* crow;      // nnz
@@ -60,6 +64,7 @@ struct FastArgs {
 
 bool tent_fast_available(int D, int order);
 int tent_fast_compact_points(int D, int order, int fosystem);
+size_t tent_fast_inverse_doubles(int D, int order, int fosystem);
 size_t tent_fast_smem_bytes(int D, int order, int fosystem);
 cudaError_t launch_tent_fast(int D, int order, int fosystem, const TentKernelArgs& a, const FastArgs& f,
                              cudaStream_t stream);

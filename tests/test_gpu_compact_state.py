@@ -115,3 +115,91 @@ def test_material_interfaces_switch_the_compact_state_off(built):
     tw = ng.TWave(3, ts, c)
     tw.SetInitial(standing(2))
     assert not tw.compact_state()
+
+
+# ---------------------------------------------------------------------------------------------- factor cache (MODE 1 / 2)
+@pytest.mark.parametrize("name", ["3d_p4", "3d_p4_neumann", "3d_p4_fo", "2d_p4"])
+def test_factor_cache_matches_assembly_every_step_and_oracle(built, name):
+    """The first Propagate stores the inverse of every tent matrix, later ones apply it (tent_fast.cu MODE 1 / 2): same
+    result as assembling and solving in every Propagate up to cond * eps, the oracle's (inverse-then-multiply, as the
+    reference) to 1e-10, and a slab repeated from the same data is bitwise the same whether it built or applied the cache."""
+    mk, order, dt, init, bnd, neu = CASES[name]
+
+    def mesh():
+        m = mk()
+        if neu:
+            m.SetBoundaryNames("neumann")
+        return m
+
+    D = mesh().dim
+    nslabs = 3
+    ts = ng.TentSlab(mesh(), "edge")
+    ts.SetMaxWavespeed(1.0)
+    assert ts.PitchTents(dt, True, 2 / 3)
+    out = {}
+    for cache in (True, False):
+        tw = ng.TWave(order, ts, 1.0)
+        tw.set_factor_cache(cache)
+        tw.SetInitial(init(D))
+        tw.SetBoundaryCF(bnd(D))
+        states = [tw.factor_cache()[0]]
+        for _ in range(nslabs):
+            tw.Propagate()
+            states.append(tw.factor_cache()[0])
+        out[cache] = tw.GetWavefront()
+        if cache:
+            assert states == [1, 2, 2, 2] and tw.factor_cache()[1] > 0
+            # the same first slab again, now applying the stored inverses: bitwise what the building pass produced
+            tw.reset_time()
+            tw.SetInitial(init(D))
+            tw.Propagate()
+            again = tw.GetWavefront()
+            tw2 = ng.TWave(order, ts, 1.0)
+            tw2.SetInitial(init(D))
+            tw2.SetBoundaryCF(bnd(D))
+            tw2.Propagate()
+            assert np.array_equal(again, tw2.GetWavefront())
+        else:
+            assert states == [0, 0, 0, 0]
+    d = np.abs(out[True] - out[False]).max() / np.abs(out[False]).max()
+    print(f"{name}: cached inverse vs solve every step {d:.3e}")
+    assert d <= 5e-11, d
+    o = Oracle(mesh())
+    assert o.pitch(dt, True, 2 / 3, 1.0)
+    o.setup(order, 1.0)
+    o.set_initial(init(D))
+    o.set_boundary_cf(bnd(D))
+    for _ in range(nslabs):
+        o.propagate()
+    ref = o.wavefront()
+    rel = np.abs(out[True] - ref).max() / np.abs(ref).max()
+    print(f"{name}: cached inverse vs oracle {rel:.3e}")
+    assert rel <= 1e-10, rel
+
+
+def test_factor_cache_follows_the_system(built):
+    """First- and second-order input have different bases: each keeps its own stored inverses."""
+    f = standing(3)
+    mesh = ng.UnitCubeMesh(3)
+    ts = ng.TentSlab(mesh, "edge")
+    ts.SetMaxWavespeed(1.0)
+    assert ts.PitchTents(0.2, True, 2 / 3)
+    tw = ng.TWave(4, ts, 1.0)
+    tw.SetBoundaryCF(dirichlet(f, 3))
+    tw.SetInitial(f)
+    tw.Propagate()
+    assert tw.factor_cache()[0] == 2
+    tw.SetInitial(first_order(f))
+    assert tw.factor_cache()[0] == 1
+    tw.Propagate()
+    tw.SetInitial(f)
+    assert tw.factor_cache()[0] == 2
+    tw.reset_time()
+    tw.Propagate()
+    ref = ng.TWave(4, ts, 1.0)
+    ref.set_factor_cache(False)
+    ref.SetInitial(f)
+    ref.SetBoundaryCF(dirichlet(f, 3))
+    ref.Propagate()
+    a, b = tw.GetWavefront(), ref.GetWavefront()
+    assert np.abs(a - b).max() <= 5e-11 * np.abs(b).max()
