@@ -216,6 +216,14 @@ int oracle_propagate(void* hp, int nthreads, int ntents_limit) {
   h->tw->singular = 0;
   return s ? -2 : 0;
 }
+// largest 1-norm condition number of a tent system met since the last call (reset != 0 clears it)
+double oracle_max_cond(void* hp, int reset) {
+  auto* tw = ((OracleHandle*)hp)->tw.get();
+  if (!tw) return 0.0;
+  const double c = tw->max_cond;
+  if (reset) tw->max_cond = 0.0;
+  return c;
+}
 // bench.py's CPU baseline: the listed tents only, dependencies ignored (timing; see PropagateSample)
 int oracle_propagate_sample(void* hp, int nthreads, const int* tents, int n) {
   auto* h = (OracleHandle*)hp;

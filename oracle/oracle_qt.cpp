@@ -229,7 +229,7 @@ struct QTWaveTents : TWaveTents {
             elmat[(size_t)i * n + j] += s;
           }
       }
-    if (!CalcInverseLapack(elmat.data(), n)) {
+    if (!InvertTracked(elmat.data(), n)) {
 #pragma omp atomic
       singular++;
     }

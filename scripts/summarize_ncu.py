@@ -16,7 +16,11 @@ tag = sys.argv[1]
 out = os.path.join(ROOT, "profiles")
 os.makedirs(out, exist_ok=True)
 
-KEYS = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
+KEYS = ["gpu__time_duration.sum", "sm__pipe_shared_cycles_active.avg.pct_of_peak_sustained_elapsed",
+        "sm__pipe_tensor_subpipe_dmma_cycles_active.avg.pct_of_peak_sustained_elapsed",
+        "sm__inst_executed_pipe_tensor_subpipe_dmma.sum", "sm__sass_thread_inst_executed_op_dfma_pred_on.sum",
+        "sm__sass_thread_inst_executed_op_dmul_pred_on.sum", "sm__sass_thread_inst_executed_op_dadd_pred_on.sum",
+        "sm__cycles_elapsed.avg", "sm__cycles_elapsed.avg.per_second", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
         "launch__shared_mem_per_block_dynamic", "launch__occupancy_limit_shared_mem", "launch__occupancy_limit_registers",
         "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__issue_active.avg.pct_of_peak_sustained_active",
         "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active",
@@ -74,4 +78,55 @@ if os.path.exists(rep):
     with open(os.path.join(out, "traffic.json"), "w") as f:
         json.dump({"tag": tag, "dram_bytes_per_launch": sum(tr) / len(tr), "dram_bytes_per_tent": sum(tr) / sum(grids),
                    "captured_launches": len(tr), "grid_sizes": grids}, f)
+        f.write("\n")
     print(open(os.path.join(out, f"{tag}_tent_kernel_full.txt")).read())
+
+    # ---- executed FP64 work per tent-element (roofline numerator of bench.py): the captured launches are levels of the
+    # benched slab (28^3 cells x 6 tets, order 4, dt = 0.05); a level is identified by its tent count = grid size
+    def col(name):
+        i = hdr.index(name)
+        return [float(r[i].replace(",", "")) for r in data]
+
+    try:
+        sys.path.insert(0, ROOT)
+        import numpy as np
+        import ngstrefftz_b200 as ng
+        cells = int(os.environ.get("NGST_PROFILE_CELLS", "28"))
+        mesh = ng.StructuredMesh([cells] * 3, [0.0] * 3, [1.0] * 3)
+        ts = ng.TentSlab(mesh, "edge")
+        ts.SetMaxWavespeed(1.0)
+        assert ts.PitchTents(0.05, True, 2 / 3)
+        e = ts.export()
+        nels = np.diff(e["el_off"])
+        per_level = {}
+        for l in range(int(e["level"].max()) + 1):
+            m = e["level"] == l
+            per_level.setdefault(int(m.sum()), []).append(int(nels[m].sum()))
+        te = []
+        for g in grids:
+            assert g in per_level and len(per_level[g]) == 1, f"grid size {g} does not identify one level"
+            te.append(per_level[g][0])
+        dmma = col("sm__inst_executed_pipe_tensor_subpipe_dmma.sum")
+        dfma = col("sm__sass_thread_inst_executed_op_dfma_pred_on.sum")
+        dmul = col("sm__sass_thread_inst_executed_op_dmul_pred_on.sum")
+        dadd = col("sm__sass_thread_inst_executed_op_dadd_pred_on.sum")
+        kname = data[0][hdr.index("Kernel Name")]
+        rec = {"tag": tag, "kernel": "tent_kernel_fast" if "tent_kernel_fast" in kname else kname, "kernel_instance": kname,
+               "D": 3, "order": 4, "workload": f"bench.py --cells {cells} --level-launches, mid-slab levels",
+               "formula": "DMMA warp instructions x 512 + 2 x DFMA + DMUL + DADD thread instructions (pred on), per tent-element",
+               "captured_grid_sizes": grids, "captured_tent_elements": te,
+               "dmma_flops_per_tent_element": 512.0 * sum(dmma) / sum(te),
+               "dfma_flops_per_tent_element": (2.0 * sum(dfma) + sum(dmul) + sum(dadd)) / sum(te),
+               "dram_bytes_per_tent_element": sum(tr) / sum(te),
+               "pipe_shared_pct": col("sm__pipe_shared_cycles_active.avg.pct_of_peak_sustained_elapsed"),
+               "dmma_pipe_pct": col("sm__pipe_tensor_subpipe_dmma_cycles_active.avg.pct_of_peak_sustained_elapsed"),
+               "fp64_pipe_pct": col("sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_elapsed"),
+               "duration_ms_under_ncu": col("gpu__time_duration.sum")}
+        rec["flops_per_tent_element"] = rec["dmma_flops_per_tent_element"] + rec["dfma_flops_per_tent_element"]
+        name = os.environ.get("NGST_EXECUTED_JSON", "executed_flops.json")
+        with open(os.path.join(out, name), "w") as f:
+            json.dump(rec, f, indent=1)
+            f.write("\n")
+        print(json.dumps(rec, indent=1))
+    except Exception as ex:  # the text summaries above stand on their own
+        print("executed_flops.json not written:", repr(ex))

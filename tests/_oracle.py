@@ -54,6 +54,8 @@ def _load():
     lib.oracle_boundary_points.argtypes = [C.c_void_p, c_dp, c_ip]
     lib.oracle_set_boundary_values.argtypes = [C.c_void_p, c_dp, C.c_longlong]
     lib.oracle_propagate.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    lib.oracle_max_cond.restype = C.c_double
+    lib.oracle_max_cond.argtypes = [C.c_void_p, C.c_int]
     lib.oracle_propagate_sample.argtypes = [C.c_void_p, C.c_int, c_ip, C.c_int]
     lib.oracle_get_wavefront.argtypes = [C.c_void_p, c_dp]
     lib.oracle_set_phase_timing.argtypes = [C.c_void_p, C.c_int]
@@ -333,6 +335,10 @@ class Oracle:
 
     def nbasis(self):
         return lib.oracle_nbasis(self.h)
+
+    def max_cond(self, reset=True):
+        """Largest 1-norm condition number of a tent system since the last reset (plain Trefftz path)."""
+        return lib.oracle_max_cond(self.h, int(reset))
 
     def max_adiam(self):
         return lib.oracle_max_adiam(self.h)

@@ -84,7 +84,8 @@ def test_propagate_device_data_vs_oracle(name, neu, fo):
     for _ in range(nslabs):
         tw2.Propagate()
     wf2 = tw2.GetWavefront()
-    assert np.abs(wf - wf2).max() <= 1e-12 * np.abs(wf2).max()
+    # (device and host evaluate sin / cos / powers with different last bits; both runs then go through the same kernels)
+    assert np.abs(wf - wf2).max() <= 1e-11 * np.abs(wf2).max()
 
 
 def test_polynomial_is_reproduced_exactly():

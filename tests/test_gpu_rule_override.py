@@ -1,10 +1,6 @@
 """Device side of the rule override (ngst_rule_override): with a permuted rule installed, the solver agrees with the
 oracle run on the same permuted rule, and its state is the default-rule state with the columns permuted.
-
-Written after round 1's GPU budget was spent: NOT yet run on a B200, therefore opt-in (NGST_TEST_RULE_OVERRIDE=1) so that
-an untested test cannot turn the GPU suite red; the host side of the feature is covered by tests/test_rule_override.py."""
-import os
-
+(First run on a B200 in round 2, profiles/r04a_pytest_gpu.txt; the host side is covered by tests/test_rule_override.py.)"""
 import numpy as np
 import pytest
 
@@ -12,8 +8,7 @@ import ngstrefftz_b200 as ng
 from _cases import dirichlet, standing
 from _oracle import Oracle
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("NGST_TEST_RULE_OVERRIDE") != "1", reason="opt-in: not yet run on a B200")]
+pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("D,mk,order,dt", [(1, lambda: ng.SegMesh(16, 0, 1), 4, 0.3), (2, lambda: ng.UnitSquareMesh(4), 4, 0.3),
