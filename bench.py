@@ -48,6 +48,10 @@ def parse():
     ap.add_argument("--no-parity-check", action="store_true",
                     help="N>1: skip the bitwise comparison of the partitioned run with a single-GPU run on rank 0")
     ap.add_argument("--mirror-ctas", type=int, default=0, help="copy CTAs of the output mirror (0 = library default)")
+    ap.add_argument("--no-factor-cache", action="store_true",
+                    help="assemble and solve every tent system in every Propagate (no stored inverses): the headline becomes the "
+                         "cold figure that is otherwise reported beside it as `assembly_every_step`")
+    ap.add_argument("--no-compact-state", action="store_true", help="tents read / write the public order-2p rows (A/B)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-mirror", action="store_true", help="e2e arm: explicit get_wavefront copy instead of the output mirror")
@@ -276,6 +280,10 @@ def run_ours(args):
             tw.set_kernel_mode(3)
         if args.level_launches:
             tw.set_kernel_mode(2)
+    if args.no_compact_state:
+        tw.set_compact_state(False)
+    if args.no_factor_cache:
+        tw.set_factor_cache(False)
     e = ts.export()
     ntents_global = ts.GetNTents()
     mine = tw.owned_tents() if world > 1 else np.arange(ntents_global)
@@ -298,7 +306,7 @@ def run_ours(args):
     nsteps_total = args.warmup + args.steps
     bvals = []
     h = ts.GetSlabHeight()
-    for i in range(2 * nsteps_total + 2):
+    for i in range(2 * nsteps_total + 3):
         bvals.append(tw.sample_boundary(i * h))
 
     def barrier():
@@ -324,6 +332,25 @@ def run_ours(args):
     clocks = clk.stop()
     dev_s = float(np.sum(dev_ms)) * 1e-3
     energy = tw.Energy()
+    cache_state, cache_bytes = tw.factor_cache()
+    kernel_variant = ("apply" if cache_state == 2 else "assemble") if tw.kernel_name() == "tent_kernel_fast" else "other"
+
+    # ---------------- the same steps with the factor cache off: every tent system assembled and solved in every Propagate
+    # (what the reference does, src/twavetents.cpp:119-164) -- reported beside the headline as `assembly_every_step`
+    cold = None
+    if cache_state == 2:
+        tw.set_factor_cache(False)
+        for _ in range(1):
+            tw.propagate_with_values(bvals[step]); step += 1
+        barrier()
+        cold_ms, cold_launches = [], 0
+        for _ in range(args.steps):
+            tw.propagate_with_values(bvals[step]); step += 1
+            cold_ms.append(tw.last_ms())
+            cold_launches += tw.last_launches()
+        barrier()
+        cold = {"sec": float(np.sum(cold_ms)) * 1e-3, "launches": cold_launches}
+        tw.set_factor_cache(True)
 
     # ---------------- e2e arm: the plugin call sequence with HOST buffers inside the timed region
     e2e = None
@@ -485,7 +512,8 @@ def run_ours(args):
     # ---------------- reduce over ranks (max time, sum units)
     ntents_local = len(mine)
     stats = torch.tensor([dev_s, wall_s, e2e["sec"] if e2e else 0.0, float(ntents_local), flops_step, bytes_step,
-                          float(launches), float(nels.sum())], dtype=torch.float64, device="cuda")
+                          float(launches), float(nels.sum()), cold["sec"] if cold else 0.0], dtype=torch.float64,
+                         device="cuda")
     if world > 1:
         mx = stats.clone()
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
@@ -534,41 +562,63 @@ def run_ours(args):
     check(lib.ngst_compact_rule(D, 2 * order, _capi.C.byref(n_rule), None, None))
     Qs = n_rule.value   # stabilisation Gram: compact rule exact to degree 2p where the table has one
     dmma_model = (Qt * (D + 1) / 4.0 + (0 if tw.fosystem else Qs / 4.0)) * (nt_tiles * (nt_tiles + 1) / 2) * 512.0
-    exe, exe_src, traffic, ncu = None, None, None, None
-    try:
-        with open(os.path.join(ROOT, "profiles", "executed_flops.json")) as fh:
-            rec = json.load(fh)
-        if rec.get("kernel") == tw.kernel_name() and rec.get("D") == D and rec.get("order") == order:
-            exe = rec["flops_per_tent_element"]
-            exe_src = f"ncu counters, {rec.get('tag')}: {rec.get('formula')}"
-            traffic = rec.get("dram_bytes_per_tent_element")
-            ncu = {k: rec.get(k) for k in ("pipe_shared_pct", "dmma_pipe_pct", "fp64_pipe_pct", "dmma_flops_per_tent_element",
-                                           "dfma_flops_per_tent_element", "captured_grid_sizes", "tag")}
-    except (OSError, ValueError, KeyError):
-        exe = None
-    if exe is None:
-        exe, exe_src = dmma_model, "model: DMMA tiles only (no ncu capture of this kernel variant under profiles/)"
-    exe_tf = exe * te_rank0 / dev_sec0 * 1e-12
-    te_per_launch = te_rank0 / launches_rank0
-    roofline = {
-        "bound": "tensor", "unit": "TFLOP/s", "achieved": exe_tf, "peak": fp64_peak, "frac": exe_tf / fp64_peak,
-        "kernel": tw.kernel_name(),
-        "pipe": "FP64: DMMA m8n8k4 (tensor path) and DFMA/DMUL/DADD share one datapath per SM (sm__pipe_shared)",
-        "achieved_definition": "EXECUTED FP64 flops per tent-element x tent-elements of the timed steps / CUDA-event time",
-        "executed_flops_per_tent_element": exe, "executed_source": exe_src,
-        "executed_dmma_model_flops_per_tent_element": dmma_model,
-        "peak_source": f"measured live on this GPU (ngst_device_fp64_peak): DFMA {dfma.value:.2f} / DMMA m8n8k4 {dmma.value:.2f} "
-                       f"TFLOP/s, interleaved 4:1 {mixed.value:.2f}; MEASURED_PEAKS.json holds no FP64 figure",
-        "traffic": None if traffic is None else traffic * te_per_launch,
-        "algorithmic_bytes_per_launch": bytes_step * args.steps / launches_rank0,
-        "ncu": ncu, "launches_per_step": launches / max(args.steps, 1),
-        # SURVEY 8.4's count (order-2p rule everywhere, full N x N Grams) over the same time: how much faster the kernel is
-        # than executing the reference's algorithm at the FP64 peak would be -- the gain of symmetry and compact rules
-        "algorithmic": {"flops_per_tent_element": f_el, "achieved": ach_tf, "unit": "TFLOP/s",
-                        "algorithmic_speedup": ach_tf / fp64_peak},
-        "hbm": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
-                "peak_source": hbm_src, "bytes_per_tent_element": b_el},
-    }
+    # algorithmic bytes of the apply variant: it also streams the stored inverse of every tent (8 N NP bytes)
+    inv_bytes_step = float(len(mine)) * 8.0 * N * ((N + 7) // 8 * 8)
+
+    def roofline_of(variant, dev_sec, nlaunch):
+        """variant: 'assemble' (every tent system assembled and solved: DMMA Grams + evaluation) or 'apply' (factor cache:
+        right-hand side, stored inverse, evaluation -- no tensor-path work)."""
+        exe, exe_src, traffic, ncu = None, None, None, None
+        fname = "executed_flops.json" if variant == "assemble" else "executed_flops_apply.json"
+        try:
+            with open(os.path.join(ROOT, "profiles", fname)) as fh:
+                rec = json.load(fh)
+            if rec.get("kernel") == tw.kernel_name() and rec.get("D") == D and rec.get("order") == order:
+                exe = rec["flops_per_tent_element"]
+                exe_src = f"ncu counters, profiles/{fname} ({rec.get('tag')}): {rec.get('formula')}"
+                traffic = rec.get("dram_bytes_per_tent_element")
+                ncu = {k: rec.get(k) for k in ("pipe_shared_pct", "dmma_pipe_pct", "fp64_pipe_pct", "dmma_flops_per_tent_element",
+                                               "dfma_flops_per_tent_element", "captured_grid_sizes", "tag")}
+        except (OSError, ValueError, KeyError):
+            exe = None
+        if exe is None and variant == "assemble":
+            exe, exe_src = dmma_model, "model: DMMA tiles only (no ncu capture of this kernel variant under profiles/)"
+        nlaunch = max(nlaunch, 1)
+        te_per_launch = te_rank0 / nlaunch
+        exe_tf = None if exe is None else exe * te_rank0 / dev_sec * 1e-12
+        alg_bytes = bytes_step + (inv_bytes_step if variant == "apply" else 0.0)
+        gbs = alg_bytes * args.steps / dev_sec * 1e-9
+        alg_tf = flops_rank0 / dev_sec * 1e-12
+        return {
+            "bound": "tensor", "unit": "TFLOP/s", "achieved": exe_tf, "peak": fp64_peak,
+            "frac": None if exe_tf is None else exe_tf / fp64_peak, "kernel": tw.kernel_name(), "variant": variant,
+            "pipe": "FP64: DMMA m8n8k4 (tensor path) and DFMA/DMUL/DADD share one datapath per SM (sm__pipe_shared)",
+            "achieved_definition": "EXECUTED FP64 flops per tent-element (ncu counters) x tent-elements of the timed steps / "
+                                   "CUDA-event time",
+            "executed_flops_per_tent_element": exe, "executed_source": exe_src,
+            "peak_source": f"measured live on this GPU (ngst_device_fp64_peak): DFMA {dfma.value:.2f} / DMMA m8n8k4 "
+                           f"{dmma.value:.2f} TFLOP/s, interleaved 4:1 {mixed.value:.2f}; MEASURED_PEAKS.json holds no FP64 figure",
+            "traffic": None if traffic is None else traffic * te_per_launch,
+            "algorithmic_bytes_per_launch": alg_bytes * args.steps / nlaunch,
+            "ncu": ncu, "launches_per_step": nlaunch / max(args.steps, 1),
+            # SURVEY 8.4's count (order-2p rule everywhere, full N x N Grams, LU) over the same time: how much faster this is
+            # than executing the reference's algorithm at the FP64 peak would be
+            "algorithmic": {"flops_per_tent_element": f_el, "achieved": alg_tf, "unit": "TFLOP/s",
+                            "algorithmic_speedup": alg_tf / fp64_peak},
+            "hbm": {"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak,
+                    "peak_source": hbm_src, "bytes_per_tent_element": b_el,
+                    "stored_inverse_bytes_per_tent": 8 * N * ((N + 7) // 8 * 8) if variant == "apply" else 0},
+        }
+
+    roofline = roofline_of(kernel_variant if kernel_variant != "other" else "assemble", dev_sec0, launches)
+    assembly_every_step = None
+    if cold:
+        cold_s = mx[8]
+        assembly_every_step = {"value": tents_step * args.steps / cold_s, "unit": "tents/s",
+                               "ms_per_step": 1e3 * cold_s / args.steps,
+                               "what": "factor cache off: every tent system assembled (DMMA Grams) and solved in every "
+                                       "Propagate, as the reference does",
+                               "roofline": roofline_of("assemble", cold["sec"], cold["launches"])}
 
     line = {
         "metric": METRIC, "value": value, "unit": "tents/s", "n_gpus": world, "steps": args.steps,
@@ -582,7 +632,12 @@ def run_ours(args):
                    "parallelism": (f"spatial partition {grid[0]}x{grid[1]}x{grid[2]} ({args.partition} vertex ownership), per-level halo exchange "
                                    f"{'after' if args.no_overlap else 'overlapped with'} the interior tents") if world > 1 else "single GPU",
                    "l2": f"state {wf0.nbytes * world / 1e6:.0f} MB per slab > 126 MB L2 (no flush needed)",
-                   "pitch_s": pitch_s},
+                   "pitch_s": pitch_s,
+                   "compact_state": bool(tw.compact_state()),
+                   "factor_cache": ("on: steady state of a time loop -- the inverse of every tent matrix was formed by the first "
+                                    "Propagate of this slab geometry (warm-up) and is applied by the timed ones; "
+                                    "`assembly_every_step` is the same measurement with the cache off") if cache_state == 2 else "off",
+                   "factor_cache_bytes": int(cache_bytes)},
         "wall_ms_per_step": 1e3 * wall_s / args.steps,
         "gpu_launches": int(sm[6]),
         "clocks": clocks,
@@ -597,6 +652,8 @@ def run_ours(args):
                                 "streamed into the host buffer during propagate (ngst_twave_set_output_mirror; checked bitwise "
                                 "against ngst_twave_get_wavefront before timing)") if e2e.get("mirror") else
                                "ngst_twave_set_initial + set_boundary_values + propagate + get_wavefront on pinned host buffers"}
+    if assembly_every_step:
+        line["assembly_every_step"] = assembly_every_step
     if device_data:
         line["device_data"] = device_data
     if parity is not None:
