@@ -213,7 +213,8 @@ int ngst_twave_get_wavefront(ngst_twave* t, double* out);
  * during ngst_twave_propagate as soon as the last tent that contains its element has run, over PCIe while the remaining
  * tents are solved; when ngst_twave_propagate returns it holds exactly what ngst_twave_get_wavefront would copy. The
  * buffer must stay valid until the mirror is switched off (host == NULL), ngst_twave_set_initial changes the row length,
- * or the solver is destroyed. Call after ngst_twave_set_initial. Single-GPU solvers only. */
+ * or the solver is destroyed. Call after ngst_twave_set_initial. Partitioned solvers mirror their local rows (owned and ghost),
+ * a ghost row after the halo exchange of the level that completes it. */
 int ngst_twave_set_output_mirror(ngst_twave* t, double* host);
 /* number of copy CTAs the output mirror keeps in flight (default 24, the best of 12 / 24 / 48 measured on B200) */
 int ngst_twave_set_mirror_ctas(ngst_twave* t, int ctas);

@@ -348,19 +348,17 @@ Solver::Solver(const TentSlab& slab, int order, const std::vector<double>& c_el,
 
   // ---- compact state (tent_fast.cu, CS = 1): which tent is the last one of the slab to contain each element
   compact_possible_ = fast_ && !qt_ && slab_.ntents > 0 && gen_off_.back() == 0;
-  if (compact_possible_) {
-    if (plan_) {
-      el_final_level_ = plan_->final_level;
-    } else {
-      el_final_level_.assign(nel_, -1);
-      for (int t = 0; t < staged_.ntents; t++)
-        for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++) {
-          int& l = el_final_level_[staged_.te_el[te]];
-          l = std::max(l, slab_.level[t]);
-        }
-    }
-    d_te_final_ = const_cast<unsigned char*>(FinalFlags(-1));
+  if (plan_) {
+    el_final_level_ = plan_->final_level;  // of the GLOBAL slab: the last tent of a ghost element may run on another rank
+  } else {
+    el_final_level_.assign(nel_, -1);
+    for (int t = 0; t < staged_.ntents; t++)
+      for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++) {
+        int& l = el_final_level_[staged_.te_el[te]];
+        l = std::max(l, slab_.level[t]);
+      }
   }
+  if (compact_possible_) d_te_final_ = const_cast<unsigned char*>(FinalFlags(-1));
 
   // element quadrature weights |detJ| * w (GetWeight, twavetents.cpp:793,818,843)
   {
@@ -777,7 +775,11 @@ void Solver::Propagate(int level_limit) {
     const int fh = overlap ? fast_nhalo_[l] : 0, gh = overlap ? gen_nhalo_[l] : 0;
     if (overlap) {
       CU(cudaStreamWaitEvent(stream_halo_, ev_int_, 0));
-      if (l > 0) CU(cudaStreamWaitEvent(stream_, ev_halo_, 0));
+      if (l > 0) {
+        CU(cudaStreamWaitEvent(stream_, ev_halo_, 0));
+        // level l-1 is complete on both streams now (interior tents, halo tents, exchange): its final rows can go out
+        if (mirror_dev_) MirrorRows(l - 1, l - 1, launches);
+      }
       TentKernelArgs h = args_;
       h.tents = d_level_fast_ + fast_off_[l];
       h.ntents = fh;
@@ -803,9 +805,12 @@ void Solver::Propagate(int level_limit) {
     }
     if (overlap) CU(cudaEventRecord(ev_int_, stream_));
     else if (comm_) launches += ExchangeLevel(l, stream_);
-    if (mirror_dev_) MirrorRows(l, l, launches);
+    if (mirror_dev_ && !overlap) MirrorRows(l, l, launches);
   }
-  if (overlap) CU(cudaStreamWaitEvent(stream_, ev_halo_, 0));
+  if (overlap) {
+    CU(cudaStreamWaitEvent(stream_, ev_halo_, 0));
+    if (mirror_dev_ && nlev > 0 && !force_generic_ && !qt_ && !dag) MirrorRows(nlev - 1, nlev - 1, launches);
+  }
   if (mirror_dev_) {  // the slab is done when the last rows have reached the host buffer
     CU(cudaEventRecord(ev_mirror_, stream_mirror_));
     CU(cudaStreamWaitEvent(stream_, ev_mirror_, 0));
@@ -895,7 +900,6 @@ void Solver::SetOutputMirror(double* host) {
   CU(cudaSetDevice(device_));
   ReleaseMirror();
   if (!host) return;
-  if (plan_) throw std::invalid_argument("SetOutputMirror: partitioned (multi-GPU) solvers are not supported");
   if (!have_initial_) throw std::logic_error("SetOutputMirror: SetInitial has not been called (row length unknown)");
   const size_t bytes = (size_t)nel_ * ncomp_ * rule_.nip * sizeof(double);
   cudaPointerAttributes attr{};
@@ -926,14 +930,10 @@ void Solver::SetOutputMirror(double* host) {
     CU(cudaEventCreateWithFlags(&ev_mirror_, cudaEventDisableTiming));
   }
   if (!d_final_rows_) {
-    // level of the last tent that contains each element (the tents of one level touch disjoint elements)
+    // level of the last tent that contains each element (the tents of one level touch disjoint elements); partitioned
+    // solvers: of the global slab -- a ghost row is final once the exchange of that level has delivered it
     const int nlev = (int)slab_.level_off.size() - 1;
-    std::vector<int> last(nel_, -1);
-    for (int t = 0; t < staged_.ntents; t++)
-      for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++) {
-        int& l = last[staged_.te_el[te]];
-        l = std::max(l, slab_.level[t]);
-      }
+    const std::vector<int>& last = el_final_level_;
     final_off_.assign(nlev + 2, 0);
     for (int el = 0; el < nel_; el++) final_off_[last[el] + 2]++;
     for (int i = 0; i < nlev + 1; i++) final_off_[i + 1] += final_off_[i];

@@ -70,7 +70,7 @@ class Solver {
   void GetWavefront(double* out);
   // Output mirror (cuda/mirror.cu): `host` (nel x ncomp*nip doubles; page-locked here if it is not already) receives every
   // state row as soon as it is final during Propagate, overlapped with the remaining tents; when Propagate returns it
-  // holds what GetWavefront would copy. nullptr switches the mirror off. Single-GPU solvers only.
+  // holds what GetWavefront would copy (partitioned solvers: their local rows). nullptr switches the mirror off.
   void SetOutputMirror(double* host);
   double Energy(const double* wf);
   double Error(const double* wf, const double* ref, bool l2only);

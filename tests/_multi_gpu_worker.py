@@ -42,13 +42,27 @@ def main():
     tw.SetInitial(f)
     tw.SetBoundaryCF(dirichlet(f, D))
     e0 = tw.Energy()
+    # output mirror of a partitioned solver: local rows (owned and ghost) streamed to the host during Propagate
+    mirror = np.full((tw.nel, tw.ncomp * tw.nip), np.nan)
+    tw.SetOutputMirror(mirror)
     for _ in range(nslabs):
         tw.Propagate()
     wf = tw.GetWavefront()
+    mirror_ok = bool(np.array_equal(mirror, wf))
+    tw.SetOutputMirror(None)
     en = tw.Energy()
     err = tw.Error(wf, tw.MakeWavefront(f, nslabs * dt))
+    # the same slabs from data sampled on the device (what bench.py's parity_check runs)
+    data = ng.StandingWave(D, 1.0)
+    tw.reset_time()
+    tw.SetInitial(data)
+    tw.SetBoundaryCF(data)
+    for _ in range(nslabs):
+        tw.Propagate()
+    wf_dev = tw.GetWavefront()
     np.savez(os.path.join(outdir, f"rank{rank}.npz"), wf=wf, loc2glob=tw.loc2glob, owned=tw.owned, energy0=e0, energy=en,
-             error=err, own_tents=tw.owned_tents(), launches=tw.last_launches(), ms=tw.last_ms())
+             error=err, own_tents=tw.owned_tents(), launches=tw.last_launches(), ms=tw.last_ms(), mirror_ok=mirror_ok,
+             wf_dev=wf_dev, compact=tw.compact_state(), cache=tw.factor_cache()[0])
     dist.barrier()
     dist.destroy_process_group()
     print("MULTI_OK", rank)

@@ -61,11 +61,21 @@ def test_partitioned_matches_single_gpu(built, case, world, how):
     ref = tw.GetWavefront()
     en = tw.Energy()
     err = tw.Error(ref, tw.MakeWavefront(f, nslabs * dt))
+    data = ng.StandingWave(D, 1.0)
+    tw.reset_time()
+    tw.SetInitial(data)
+    tw.SetBoundaryCF(data)
+    for _ in range(nslabs):
+        tw.Propagate()
+    ref_dev = tw.GetWavefront()
     covered = np.zeros(mesh.ne, dtype=int)
     own = []
     for k, d in enumerate(ranks):
         # every local row (owned or ghost) is current after the last level's exchange
         assert np.array_equal(d["wf"], ref[d["loc2glob"]]), f"rank {k}: state differs from the single-GPU run"
+        assert bool(d["mirror_ok"]), f"rank {k}: output mirror differs from GetWavefront"
+        assert np.array_equal(d["wf_dev"], ref_dev[d["loc2glob"]]), f"rank {k}: device-sampled run differs"
+        assert bool(d["compact"]) == tw.compact_state() and int(d["cache"]) == tw.factor_cache()[0]
         np.add.at(covered, d["loc2glob"][d["owned"] == 1], 1)
         own.append(d["own_tents"])
         assert abs(float(d["energy0"]) - e0) <= 1e-13 * e0
