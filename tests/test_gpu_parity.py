@@ -341,4 +341,7 @@ def test_pointwise_wavespeed_in_error_plain_trefftz(built):
     wf = tw.GetWavefront()
     err = tw.Error(wf, tw.MakeWavefront(f, 1.0))
     assert repr(err).startswith("0.01"), err
-    assert abs(err - o.error(o.wavefront(), o.make_wavefront(f, 1.0))) <= forced_tol(o, "plain Trefftz, c = x + 1") * err
+    # Error is the norm of a difference of nearly equal states: it moves by up to tol * |state| in absolute terms
+    ref = o.wavefront()
+    scale = math.sqrt(2 * o.energy(ref))
+    assert abs(err - o.error(ref, o.make_wavefront(f, 1.0))) <= 10 * forced_tol(o, "plain Trefftz, c = x + 1") * scale
