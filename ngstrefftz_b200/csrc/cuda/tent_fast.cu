@@ -73,6 +73,27 @@ struct Cfg {
   static constexpr int nsmem = oRHS + (rhsFirst ? NP : 0);
   static_assert(2 * kBS <= ZS, "boundary operands must fit in the Z buffer");
   static_assert(NT >= 2 && (NT * NT + 3) / 4 <= NACC, "accumulator budget");
+
+  // ---- compact state rows staged in shared memory by bulk asynchronous copies (right-hand-side pass)
+  static constexpr int NCS = FO ? d1 : d1 + 1;                       // state components
+  static constexpr int ROWLEN = NCS * (QS > 0 ? QS : 1);             // doubles per compact row
+  static constexpr bool stageRows = QS > 0 && ROWLEN % 2 == 0;       // bulk copies move multiples of 16 bytes
+  // MODE 0 / 1: the operand buffer Z is free during the pass: rows behind the partial sums
+  static constexpr int oRows01 = 4 * NP;
+  static constexpr int capRows01 = (NP * ZS - oRows01) / ROWLEN < 32 ? (NP * ZS - oRows01) / ROWLEN : 32;
+  // MODE 2 (apply): no operand buffer, no matrix. [partial sums | stored inverse | rows | b | cm | cmd | rhs], sized
+  // so that three CTAs fit in the 227 KB of an SM
+  static constexpr int oInv2 = 4 * NP;
+  static constexpr int oRows2 = oInv2 + NP * N;
+  static constexpr int tail2 = (NP + 2) + (npoly + 2) + (d1 * npm1 + 2) + NP;
+  static constexpr int budget2 = 74 * 1024 / 8;
+  static constexpr int capRows2raw = (budget2 - oRows2 - tail2) / ROWLEN;
+  static constexpr int capRows2 = capRows2raw > 32 ? 32 : (capRows2raw < 1 ? 1 : capRows2raw);
+  static constexpr int oB2 = (oRows2 + capRows2 * ROWLEN + 1) / 2 * 2;
+  static constexpr int oCM2 = (oB2 + NP + 1) / 2 * 2;
+  static constexpr int oCMD2 = oCM2 + npoly;
+  static constexpr int oRHS2 = (oCMD2 + d1 * npm1 + 1) / 2 * 2;
+  static constexpr int nsmem2 = oRHS2 + NP;
 };
 
 // group dispatch: warp w evaluates the functions i with i % 4 == w
@@ -124,10 +145,15 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
   constexpr int NACC = C::NACC, FE = C::FE, FF = C::FF, npoly = C::npoly, npm1 = C::npm1;
   extern __shared__ __align__(16) double sm[];
   double* const A = sm + C::oA;
-  double* const bv = sm + C::oB;
+  double* const bv = sm + (MODE == 2 ? C::oB2 : C::oB);
   double* const Z = sm + C::oZ;
-  double* const cm = sm + C::oCM;
-  double* const cmd = sm + C::oCMD;
+  double* const cm = sm + (MODE == 2 ? C::oCM2 : C::oCM);
+  double* const cmd = sm + (MODE == 2 ? C::oCMD2 : C::oCMD);
+  double* const rhsS = sm + (MODE == 2 ? C::oRHS2 : C::oRHS);
+  // compact rows of the tent's elements, fetched by bulk asynchronous copies (cp.async.bulk) ahead of the right-hand-side pass
+  constexpr bool STG = CS && C::stageRows;
+  constexpr int kRowCap = STG ? (MODE == 2 ? C::capRows2 : C::capRows01) : (1 << 30);
+  double* const rowsS = sm + (MODE == 2 ? C::oRows2 : C::oRows01);
 
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const int g = lane >> 2, k = lane & 3;  // DMMA fragment coordinates
@@ -167,14 +193,17 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
   const int nptt = nel * QT;
   // stored inverse of this tent (MODE 1 writes, MODE 2 reads): N columns of NP doubles, behind the NS * NP partial sums of
   // the right-hand-side pass in the (otherwise unused) operand buffer
-  constexpr int kInvOff = 4 * NP;
-  static_assert(MODE == 0 || kInvOff + NP * N <= NP * ZS, "the stored inverse must fit in the operand buffer");
-  double* const invS = Z + kInvOff;
+  double* const invS = sm + C::oInv2;
   [[maybe_unused]] double* const invG = (MODE != 0) ? f.ainv + (size_t)tent * (NP * N) : nullptr;
-  __shared__ __align__(8) unsigned long long s_bar;
-  if constexpr (MODE == 2) {
-    if (tid == 0) tma::mbar_init(&s_bar, 1);
+  __shared__ __align__(8) unsigned long long s_bar, s_bar_rows;
+  if constexpr (MODE == 2 || STG) {
+    if (tid == 0) {
+      tma::mbar_init(&s_bar, 1);
+      tma::mbar_init(&s_bar_rows, 1);
+    }
     __syncthreads();
+  }
+  if constexpr (MODE == 2) {
     if (tid == 0) {
       tma::mbar_expect(&s_bar, NP * N * 8);
       tma::bulk_load(invS, invG, NP * N * 8, &s_bar);
@@ -193,7 +222,6 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
     const double* __restrict__ const lamR = CS ? f.lam_stab : a.lam;
     const double* __restrict__ const wR = CS ? f.w_stab : a.w;
     const double* __restrict__ const stR = CS ? f.cstate : a.wavefront;
-    const int nptr = nel * QR;
     // H = 2 (larger bases): a warp evaluates one half of the functions (groups 2h, 2h + 1) on every second chunk, which
     // keeps the partial sums and the live monomials within the 168-register budget of three CTAs per SM
     constexpr int H = (NP > 32) ? 2 : 1;
@@ -203,18 +231,40 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
     double bp[NB];
 #pragma unroll
     for (int i = 0; i < NB; i++) bp[i] = 0.0;
-    for (int c0 = cs * kChunk; c0 < nptr; c0 += NS * kChunk) {
+    // STG: the elements of the tent in batches of kRowCap rows (one batch for all but the largest vertex patches): warp 0
+    // issues one bulk copy per row, everybody waits on the mbarrier, then the rows are read from shared memory
+    for (int b0 = 0; b0 < nel; b0 += kRowCap) {
+    const int nb = STG ? min(kRowCap, nel - b0) : nel;
+    if constexpr (STG) {
+      constexpr unsigned kRowBytes = C::ROWLEN * 8;
+      if (w == 0) {
+        if (lane == 0) tma::mbar_expect(&s_bar_rows, nb * kRowBytes);
+        __syncwarp();
+        for (int e = lane; e < nb; e += 32) {
+          if (a.ticket) tma::fence_proxy_async();  // rows written by other CTAs of this launch (dependency-driven order)
+          tma::bulk_load(rowsS + e * C::ROWLEN, f.cstate + (size_t)a.te_el[te0 + b0 + e] * C::ROWLEN, kRowBytes, &s_bar_rows);
+        }
+      }
+      tma::mbar_wait(&s_bar_rows, (b0 / kRowCap) & 1);
+    }
+    const int nptb = nb * QR;
+    for (int c0 = cs * kChunk; c0 < nptb; c0 += NS * kChunk) {
       const int idx = c0 + lane;
-      const bool valid = idx < nptr;
-      const int idc = valid ? idx : nptr - 1;
-      const int te = te0 + idc / QR, q = idc % QR;
+      const bool valid = idx < nptb;
+      const int idc = valid ? idx : nptb - 1;
+      const int eb = idc / QR, q = idc % QR;
+      const int te = te0 + b0 + eb;
       double gcur[NC];
-      {
+      if constexpr (STG) {
+        const double* __restrict__ r = rowsS + eb * C::ROWLEN + q;
+#pragma unroll
+        for (int cc = 0; cc < NC; cc++) gcur[cc] = r[cc * QR];
+      } else {
         const double* __restrict__ wf = stR + (size_t)a.te_el[te] * (NC * QR) + q;
 #pragma unroll
         for (int cc = 0; cc < NC; cc++) gcur[cc] = __ldcg(wf + cc * QR);  // L2: rows written by other SMs
-        if (c0 + NS * kChunk < nptr) {  // next chunk of this warp: HBM -> L2 now (costs no registers)
-          const int idn = min(idx + NS * kChunk, nptr - 1);
+        if (c0 + NS * kChunk < nptb) {  // next chunk of this warp: HBM -> L2 now (costs no registers)
+          const int idn = min(idx + NS * kChunk, nptb - 1);
           const double* __restrict__ wn = stR + (size_t)a.te_el[te0 + idn / QR] * (NC * QR) + idn % QR;
 #pragma unroll
           for (int cc = 0; cc < NC; cc++) asm volatile("prefetch.global.L2 [%0];" ::"l"(wn + cc * QR));
@@ -256,6 +306,8 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
         bp[H == 1 ? i : ((i >> 2) * 2 + (i & 1))] += r;   // H == 2: function i = 4 m + 2 part + b -> slot 2 m + b
       };
       eval_part<D, P, FO, H>(part, xi, fn);
+    }
+    if (STG && b0 + kRowCap < nel) __syncthreads();  // everybody is done with the staged rows before the next batch lands
     }
     // boundary faces, right-hand side only (CalcTentBndEl, 404-433 / 380-403): b += om g (alpha gamma p + nn) (Dirichlet),
     // b += om (n.g) (beta nn + p) (Neumann); the datum is sampled at the points of the order-2P rule (twavetents.cpp:373-374)
@@ -320,7 +372,7 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
       double v = 0.0;
 #pragma unroll
       for (int c = 0; c < NS; c++) v += Z[c * NP + i];
-      sm[C::oRHS + i] = v;
+      rhsS[i] = v;
     }
     __syncthreads();
   }
@@ -581,7 +633,7 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
 
   // ------------------------------------------------------------------ right-hand side
   if (C::rhsFirst) {
-    for (int i = tid; i < NP; i += kThreads) bv[i] = sm[C::oRHS + i];
+    for (int i = tid; i < NP; i += kThreads) bv[i] = rhsS[i];
   } else {
 #pragma unroll
     for (int j = 0; j < G; j++) {
@@ -729,7 +781,7 @@ cudaError_t launch_cfg(const TentKernelArgs& a, const FastArgs& f, cudaStream_t 
   if ((C::splitStab || CS) && f.Qs != C::QS) return cudaErrorInvalidValue;
   if (CS && (!f.cstate || !f.te_final || !f.w_stab)) return cudaErrorInvalidValue;
   if (MODE != 0 && !f.ainv) return cudaErrorInvalidValue;
-  const size_t smem = sizeof(double) * C::nsmem;
+  const size_t smem = sizeof(double) * (MODE == 2 ? C::nsmem2 : C::nsmem);
   // the attribute is per device: one flag per device ordinal, not per process (a process may hold solvers on several GPUs)
   static bool configured[64] = {};  // (one flag set per template instance)
   int dev = 0;
