@@ -250,7 +250,7 @@ def bind_to_gpu_numa(local):
         with open(f"/sys/bus/pci/devices/{addr}/numa_node") as fh:
             node = int(fh.read().strip())
         if node < 0:
-            return None
+            return {"node": node, "note": "the platform reports no NUMA affinity for this GPU"}
         with open(f"/sys/devices/system/node/node{node}/cpulist") as fh:
             cpus = set()
             for part in fh.read().strip().split(","):
@@ -260,9 +260,9 @@ def bind_to_gpu_numa(local):
         if cpus:
             os.sched_setaffinity(0, cpus)
             return {"node": node, "cpus": len(cpus)}
-    except Exception:
-        pass
-    return None
+        return {"node": node, "note": "no allowed CPU on that node"}
+    except Exception as ex:
+        return {"error": repr(ex)[:200]}
 
 
 # ------------------------------------------------------------------------------------------------ our arm

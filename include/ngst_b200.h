@@ -118,6 +118,11 @@ int ngst_partition_plan(const ngst_slab* s, const int* vertex_owner, int nranks,
                         int* loc2glob, int* owned, int* send_off, int* send_el, int* recv_off, int* recv_el);
 int ngst_twave_create_partitioned(const ngst_slab* s, int order, const double* c_el, const double* c_vertex, int device,
                                   const int* vertex_owner, int nranks, int rank, ngst_twave** out);
+/* the quasi-Trefftz solver (ngst_qtwave_create) on this rank's part of the partition; the Taylor tables stay global
+ * (one row per mesh vertex) */
+int ngst_qtwave_create_partitioned(const ngst_slab* s, int order, const double* c_el, const double* c_vertex, int device,
+                                   int cdeg, const double* ccoef, const double* aa_taylor, const double* bb_taylor,
+                                   const int* vertex_owner, int nranks, int rank, ngst_twave** out);
 /* NCCL bootstrap: one rank creates the 128-byte id, the caller distributes it (MPI / torch.distributed broadcast), every
  * rank calls ngst_twave_comm_init. Afterwards Propagate exchanges the updated ghost rows after every tent level with
  * grouped ncclSend/ncclRecv, and Energy / Error / L2Error return the all-reduced global value. */

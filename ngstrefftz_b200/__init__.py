@@ -468,15 +468,23 @@ class TWaveTents(TrefftzTents):
             # TWave(order, tps, wavespeedcf, BBcf) -> QTWaveTents (src/twavetents.cpp:1201-1216)
             if not isinstance(wavespeedcf, PolynomialCF):
                 raise TypeError("quasi-Trefftz: the wavespeed must be a ngstrefftz_b200.PolynomialCF (polynomial in x)")
-            if partition is not None:
-                raise NotImplementedError("quasi-Trefftz: multi-GPU partition is not supported yet")
             if not isinstance(BBcf, PolynomialCF):
                 BBcf = PolynomialCF.constant(mesh.dim, float(BBcf))
             aa = f64(wavespeedcf.taylor_inverse_square(mesh.points, max(self.order - 2, 0)))
             bb = f64(BBcf.taylor(mesh.points, self.order - 1))
             cc = f64(wavespeedcf.coef_array())
-            check(lib.ngst_qtwave_create(tps._h, self.order, dptr(c_el), dptr(c_vertex), int(device), wavespeedcf.deg,
-                                         dptr(cc), dptr(aa), dptr(bb), C.byref(self._h)))
+            if partition is None:
+                check(lib.ngst_qtwave_create(tps._h, self.order, dptr(c_el), dptr(c_vertex), int(device), wavespeedcf.deg,
+                                             dptr(cc), dptr(aa), dptr(bb), C.byref(self._h)))
+            else:
+                rank, nranks, owner = partition
+                owner = brick_vertex_owner(mesh, owner) if isinstance(owner, tuple) else i32(owner)
+                if len(owner) != mesh.nv:
+                    raise ValueError("partition: need one owner per mesh vertex")
+                check(lib.ngst_qtwave_create_partitioned(tps._h, self.order, dptr(c_el), dptr(c_vertex), int(device),
+                                                         wavespeedcf.deg, dptr(cc), dptr(aa), dptr(bb), iptr(owner),
+                                                         int(nranks), int(rank), C.byref(self._h)))
+                self.partition = (int(rank), int(nranks), owner)
         elif partition is None:
             check(lib.ngst_twave_create(tps._h, self.order, dptr(c_el), dptr(c_vertex), int(device), C.byref(self._h)))
         else:

@@ -63,6 +63,8 @@ _SIGS = {
     "ngst_twave_create_partitioned": (C.c_int, [c_vp, C.c_int, c_dp, c_dp, C.c_int, c_ip, C.c_int, C.c_int,
                                                 C.POINTER(c_vp)]),
     "ngst_qtwave_create": (C.c_int, [c_vp, C.c_int, c_dp, c_dp, C.c_int, C.c_int, c_dp, c_dp, c_dp, C.POINTER(c_vp)]),
+    "ngst_qtwave_create_partitioned": (C.c_int, [c_vp, C.c_int, c_dp, c_dp, C.c_int, C.c_int, c_dp, c_dp, c_dp, c_ip, C.c_int,
+                                                 C.c_int, C.POINTER(c_vp)]),
     "ngst_twave_set_wavespeed_poly": (C.c_int, [c_vp, C.c_int, c_dp]),
     "ngst_comm_unique_id": (C.c_int, [c_vp]),
     "ngst_twave_comm_init": (C.c_int, [c_vp, c_vp]),

@@ -273,25 +273,53 @@ int ngst_twave_create_partitioned(const ngst_slab* s, int order, const double* c
   });
 }
 
+namespace {
+QtHostData make_qt_data(const SimplexMesh& m, int order, int cdeg, const double* ccoef, const double* aa_taylor,
+                        const double* bb_taylor) {
+  need(ccoef, "ccoef"); need(aa_taylor, "aa_taylor"); need(bb_taylor, "bb_taylor");
+  if (order < 2 || cdeg < 0 || cdeg > 8) throw std::invalid_argument("ngst_qtwave_create: order >= 2 and 0 <= cdeg <= 8 required");
+  QtHostData q;
+  q.cdeg = cdeg;
+  q.ccoef.assign(ccoef, ccoef + monomial_exponents(m.D, cdeg).size() / m.D);
+  const size_t nA = monomial_exponents(m.D, order - 2).size() / m.D, nB = monomial_exponents(m.D, order - 1).size() / m.D;
+  q.aa.assign(aa_taylor, aa_taylor + (size_t)m.nv * nA);
+  q.bb.assign(bb_taylor, bb_taylor + (size_t)m.nv * nB);
+  return q;
+}
+}  // namespace
+
 int ngst_qtwave_create(const ngst_slab* s, int order, const double* c_el, const double* c_vertex, int device, int cdeg,
                        const double* ccoef, const double* aa_taylor, const double* bb_taylor, ngst_twave** out) {
   return guarded([&] {
-    need(s, "slab"); need(out, "out"); need(c_el, "c_el"); need(ccoef, "ccoef"); need(aa_taylor, "aa_taylor");
-    need(bb_taylor, "bb_taylor");
+    need(s, "slab"); need(out, "out"); need(c_el, "c_el");
     const SimplexMesh& m = *s->s.mesh;
-    if (order < 2 || cdeg < 0 || cdeg > 8) throw std::invalid_argument("ngst_qtwave_create: order >= 2 and 0 <= cdeg <= 8 required");
+    const QtHostData q = make_qt_data(m, order, cdeg, ccoef, aa_taylor, bb_taylor);
     std::vector<double> ce(c_el, c_el + m.nel), cv;
     if (c_vertex) cv.assign(c_vertex, c_vertex + m.nv);
-    QtHostData q;
-    q.cdeg = cdeg;
-    q.ccoef.assign(ccoef, ccoef + monomial_exponents(m.D, cdeg).size() / m.D);
-    const size_t nA = monomial_exponents(m.D, order - 2).size() / m.D, nB = monomial_exponents(m.D, order - 1).size() / m.D;
-    q.aa.assign(aa_taylor, aa_taylor + (size_t)m.nv * nA);
-    q.bb.assign(bb_taylor, bb_taylor + (size_t)m.nv * nB);
     auto h = std::make_unique<ngst_twave>();
     h->slab = s;
     h->slab_generation = s->s.generation;
     h->solver = std::make_unique<Solver>(s->s, order, ce, cv, device, nullptr, &q);
+    *out = h.release();
+  });
+}
+
+int ngst_qtwave_create_partitioned(const ngst_slab* s, int order, const double* c_el, const double* c_vertex, int device,
+                                   int cdeg, const double* ccoef, const double* aa_taylor, const double* bb_taylor,
+                                   const int* vertex_owner, int nranks, int rank, ngst_twave** out) {
+  return guarded([&] {
+    need(s, "slab"); need(out, "out"); need(c_el, "c_el"); need(vertex_owner, "vertex_owner");
+    const SimplexMesh& m = *s->s.mesh;
+    const QtHostData q = make_qt_data(m, order, cdeg, ccoef, aa_taylor, bb_taylor);
+    std::vector<double> ce(c_el, c_el + m.nel), cv;
+    if (c_vertex) cv.assign(c_vertex, c_vertex + m.nv);
+    const std::vector<int> vo(vertex_owner, vertex_owner + m.nv);
+    auto h = std::make_unique<ngst_twave>();
+    h->slab = s;
+    h->slab_generation = s->s.generation;
+    h->plan = std::make_unique<PartitionPlan>(make_partition_plan(m, s->s, vo, nranks, rank));
+    h->sub = std::make_unique<TentSlab>(restrict_slab(s->s, h->plan->own_tents));
+    h->solver = std::make_unique<Solver>(*h->sub, order, ce, cv, device, h->plan.get(), &q);
     *out = h.release();
   });
 }
