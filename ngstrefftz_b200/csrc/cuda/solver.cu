@@ -495,7 +495,8 @@ void Solver::ProjectCompact() {
     d_transfer_ = Upload(rule_transfer_matrix(rule_, rs, order_));
     transfer_points_ = cs_points_;
   }
-  CU(launch_project_rows(nel_, Q, cs_points_, 0, ncomp_, ncomp_ * Q, d_transfer_, d_wavefront_, d_cstate_, stream_));
+  // (nel * ncomp) contiguous rows of Q doubles times the transposed transfer matrix: a GEMM on the FP64 tensor path
+  CU(launch_transfer_rows((long long)nel_ * ncomp_, Q, cs_points_, d_transfer_, d_wavefront_, d_cstate_, stream_));
   cstate_valid_ = true;
 }
 
@@ -743,7 +744,10 @@ void Solver::Propagate(int level_limit) {
   // Measured on B200 (profiles/r01o): with ~2700 tents per level (config 4) the single launch is 3 % slower than one launch
   // per level (waiting CTAs hold SM slots and poll), with small levels it removes the launch gaps and tails.
   const bool small_levels = slab_.ntents < 2 * 444 * nlev;
-  const bool dag = dag_ && (dag_mode_ == 2 || (dag_mode_ == 1 && small_levels)) && !force_generic_ && !comm_ && !partial;
+  // (r04d, B200: with stored inverses a tent is 6x cheaper and the single launch wins at config 4 as well, 11.74 vs 12.17 ms;
+  // not with an output mirror, whose copies overlap the per-level launches)
+  const bool cheap_tents = fa.mode == 2 && !mirror_dev_;
+  const bool dag = dag_ && (dag_mode_ == 2 || (dag_mode_ == 1 && (small_levels || cheap_tents))) && !force_generic_ && !comm_ && !partial;
   if (dag) {
     CU(cudaMemcpyAsync(d_remaining_, d_indeg_, sizeof(int) * slab_.ntents, cudaMemcpyDeviceToDevice, stream_));
     CU(cudaMemsetAsync(d_ticket_, 0, sizeof(int), stream_));

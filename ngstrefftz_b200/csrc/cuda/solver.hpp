@@ -228,6 +228,8 @@ size_t tent_generic_smem_bytes(int D, const TentKernelArgs& a);
 cudaError_t launch_tent_generic(int D, const TentKernelArgs& a, int threads, size_t smem, cudaStream_t stream);
 cudaError_t launch_project_rows(int nel, int Q, int ndof, int comp0, int ncomp_used, int rowlen, const double* P,
                                 const double* wf, double* out, cudaStream_t stream);
+cudaError_t launch_transfer_rows(long long nrows, int Q, int ndof, const double* P, const double* in, double* out,
+                                 cudaStream_t stream);
 cudaError_t launch_mirror_rows(const int* rows, int nrows, int rowlen, const double* wf, double* host_alias, int ctas,
                                cudaStream_t stream);
 cudaError_t launch_element_reduce(int mode, int D, int nel, int Q, int ncomp, int fosystem, const double* elw,
