@@ -58,6 +58,8 @@ def parse():
     ap.add_argument("--no-device-data", action="store_true", help="skip the informational device-sampled-data arm")
     ap.add_argument("--partition", default="balanced", choices=["balanced", "brick"],
                     help="N>1: cost-balanced recursive bisection (default) or plain brick cut of the bounding box")
+    ap.add_argument("--no-peer-exchange", action="store_true",
+                    help="N>1: halo tents + grouped ncclSend/ncclRecv per level instead of the exchange inside the tent kernel")
     ap.add_argument("--no-overlap", action="store_true", help="N>1: exchange after each level instead of overlapped")
     ap.add_argument("--level-launches", action="store_true",
                     help="N=1: always one launch per tent level (profiling; default: automatic, see DESIGN.md section 4.5)")
@@ -303,6 +305,8 @@ def run_ours(args):
         tw = ng.TWave(order, ts, 1.0, device=local, partition=(rank, world, owner))
         if args.no_overlap:
             tw.set_kernel_mode(2)
+        if args.no_peer_exchange:
+            tw.set_peer_exchange(False)
     else:
         tw = ng.TWave(order, ts, 1.0, device=local)
         if args.mirror_ctas:
@@ -665,6 +669,8 @@ def run_ours(args):
                                    f"{'after' if args.no_overlap else 'overlapped with'} the interior tents") if world > 1 else "single GPU",
                    "l2": f"state {wf0.nbytes * world / 1e6:.0f} MB per slab > 126 MB L2 (no flush needed)",
                    "pitch_s": pitch_s,
+                   "exchange": (tw.peer_exchange()[1] if tw.peer_exchange()[0] else "per-level NCCL send/recv ("
+                                + tw.peer_exchange()[1] + ")") if world > 1 else None,
                    "numa_binding_rank0": numa,
                    "compact_state": bool(tw.compact_state()),
                    "factor_cache": ("on: steady state of a time loop -- the inverse of every tent matrix was formed by the first "

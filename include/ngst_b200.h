@@ -128,6 +128,15 @@ int ngst_qtwave_create_partitioned(const ngst_slab* s, int order, const double* 
  * grouped ncclSend/ncclRecv, and Energy / Error / L2Error return the all-reduced global value. */
 int ngst_comm_unique_id(void* out128);
 int ngst_twave_comm_init(ngst_twave* t, const void* id128);
+/* Peer-to-peer exchange (default where ngst_twave_comm_init could set it up on EVERY rank: compact state in use, CUDA IPC
+ * mappings of the other ranks' state buffers over NVLink). Propagate is then ONE dependency-driven launch per slab on every
+ * rank: a tent waits for its predecessors on any rank (hazard counters), pushes the rows it writes into the buffers of the
+ * other ranks that hold the element and releases its successors elsewhere with system-scope atomics -- compute and exchange
+ * in one kernel, no per-level synchronisation between the GPUs; one stream-ordered NCCL barrier per slab. on == 0 (or kernel
+ * mode 2): halo tents + grouped ncclSend/ncclRecv per level. ngst_twave_peer_exchange returns 1 when the next Propagate will
+ * use it and copies a short reason / description into note (may be NULL). */
+int ngst_twave_set_peer_exchange(ngst_twave* t, int on);
+int ngst_twave_peer_exchange(const ngst_twave* t, char* note, int note_len);
 /* own_tents: info[7] global tent ids; loc2glob / owned: info[6] entries; NULL skips */
 int ngst_twave_partition(const ngst_twave* t, int* own_tents, int* loc2glob, int* owned);
 /* info[8] = D, order, nbasis (LocalDofs), nip, ncomp, fosystem, nel (local), ntents (of this rank) */

@@ -687,6 +687,16 @@ class TWaveTents(TrefftzTents):
     def compact_state(self):
         return bool(lib.ngst_twave_compact_state(self._h))
 
+    def set_peer_exchange(self, on=True):
+        """Multi-GPU: exchange inside the tent kernel over peer memory (default where available) or per level with NCCL."""
+        check(lib.ngst_twave_set_peer_exchange(self._h, int(bool(on))))
+
+    def peer_exchange(self):
+        """(active, note)"""
+        buf = C.create_string_buffer(256)
+        on = lib.ngst_twave_peer_exchange(self._h, buf, 256)
+        return bool(on), buf.value.decode()
+
     def set_factor_cache(self, on=True):
         """Keep the inverse of every tent matrix in HBM after the first Propagate (default) or assemble and solve in every
         Propagate (ngst_twave_set_factor_cache)."""

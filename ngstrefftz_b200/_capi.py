@@ -68,6 +68,8 @@ _SIGS = {
     "ngst_twave_set_wavespeed_poly": (C.c_int, [c_vp, C.c_int, c_dp]),
     "ngst_comm_unique_id": (C.c_int, [c_vp]),
     "ngst_twave_comm_init": (C.c_int, [c_vp, c_vp]),
+    "ngst_twave_set_peer_exchange": (C.c_int, [c_vp, C.c_int]),
+    "ngst_twave_peer_exchange": (C.c_int, [c_vp, C.c_char_p, C.c_int]),
     "ngst_twave_partition": (C.c_int, [c_vp, c_ip, c_ip, c_ip]),
     "ngst_twave_info": (C.c_int, [c_vp, c_ip]),
     "ngst_twave_quadrature": (C.c_int, [c_vp, c_dp, c_dp]),

@@ -460,6 +460,18 @@ int ngst_twave_factor_cache(const ngst_twave* t, long long* bytes) {
   return t ? t->solver->factor_cache_state() : 0;
 }
 
+int ngst_twave_set_peer_exchange(ngst_twave* t, int on) {
+  return guarded([&] { need(t, "solver"); t->solver->set_peer_exchange(on != 0); });
+}
+int ngst_twave_peer_exchange(const ngst_twave* t, char* note, int note_len) {
+  if (!t) return 0;
+  if (note && note_len > 0) {
+    std::strncpy(note, t->solver->peer_exchange_note().c_str(), (size_t)note_len - 1);
+    note[note_len - 1] = 0;
+  }
+  return t->solver->peer_exchange_active() ? 1 : 0;
+}
+
 int ngst_twave_set_mirror_ctas(ngst_twave* t, int ctas) {
   return guarded([&] {
     need(t, "solver");

@@ -27,6 +27,7 @@ struct NcclApi {
   ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
 };
 
@@ -50,6 +51,7 @@ NcclApi& api() {
   sym(lib, "ncclSend", a.Send);
   sym(lib, "ncclRecv", a.Recv);
   sym(lib, "ncclAllReduce", a.AllReduce);
+  sym(lib, "ncclAllGather", a.AllGather);
   sym(lib, "ncclGetErrorString", a.GetErrorString);
   a.lib = lib;
   return a;
@@ -119,6 +121,14 @@ void HaloComm::Exchange(double* wf, int rowlen, const int* d_send_rows, const in
   if (nr > 0) unpack_rows_kernel<<<nr, 128, 0, stream>>>(wf, d_recv_rows, rowlen, d_recvbuf);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) throw std::runtime_error(std::string("CUDA: halo pack/unpack: ") + cudaGetErrorString(e));
+}
+
+void HaloComm::AllGatherBytes(const void* d_in, void* d_out, size_t bytes, cudaStream_t stream) {
+  NC(api().AllGather(d_in, d_out, bytes, ncclChar, static_cast<ncclComm_t>(comm_), stream));
+}
+
+void HaloComm::Barrier(double* d_scalar, cudaStream_t stream) {
+  NC(api().AllReduce(d_scalar, d_scalar, 1, ncclDouble, ncclSum, static_cast<ncclComm_t>(comm_), stream));
 }
 
 double HaloComm::AllReduceSum(double local, double* d_scalar, cudaStream_t stream) {

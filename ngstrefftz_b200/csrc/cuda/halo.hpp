@@ -22,6 +22,10 @@ class HaloComm {
   // peer after peer; buffers hold (sum of counts) * rowlen doubles. Everything is enqueued on `stream`.
   void Exchange(double* wf, int rowlen, const int* d_send_rows, const int* send_cnt, const int* d_recv_rows,
                 const int* recv_cnt, double* d_sendbuf, double* d_recvbuf, cudaStream_t stream);
+  // every rank contributes `bytes` bytes (device buffer) and receives all contributions in rank order (device buffer)
+  void AllGatherBytes(const void* d_in, void* d_out, size_t bytes, cudaStream_t stream);
+  // stream-ordered barrier: completes on `stream` once every rank has reached it on its stream (no host synchronisation)
+  void Barrier(double* d_scalar, cudaStream_t stream);
   // FP64 sum over ranks of one scalar (Energy / Error); blocks until the result is on the host
   double AllReduceSum(double local, double* d_scalar, cudaStream_t stream);
 

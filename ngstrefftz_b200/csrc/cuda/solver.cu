@@ -1,8 +1,11 @@
 #include "solver.hpp"
 #include "sample.hpp"
 
+#include <dlfcn.h>
+
 #include <algorithm>
 #include <cmath>
+#include <cstring>
 #include <stdexcept>
 
 namespace ngst {
@@ -387,6 +390,7 @@ Solver::~Solver() {
   if (d_tmp_b_) cudaFree(d_tmp_b_);
   if (d_cstate_) cudaFree(d_cstate_);
   for (double* p : d_ainv_) if (p) cudaFree(p);
+  for (void* b : ipc_opened_) cudaIpcCloseMemHandle(b);
   if (h_flags_) cudaFreeHost(h_flags_);
   if (d_sendbuf_) cudaFree(d_sendbuf_);
   if (d_recvbuf_) cudaFree(d_recvbuf_);
@@ -516,14 +520,25 @@ void Solver::SetInitial(const double* wf, int ncomp) {
     if (d_tmp_a_) { CU(cudaFree(d_tmp_a_)); d_tmp_a_ = nullptr; }
     if (d_tmp_b_) { CU(cudaFree(d_tmp_b_)); d_tmp_b_ = nullptr; }
   }
-  if (d_wavefront_ && wavefront_bytes_ != bytes) { CU(cudaFree(d_wavefront_)); d_wavefront_ = nullptr; }
-  if (!d_wavefront_) { CU(cudaMalloc(&d_wavefront_, bytes)); wavefront_bytes_ = bytes; }
+  if (state_capacity_ > 0) {
+    // peer-to-peer exchange: the buffers were allocated once for the largest system and are mapped by the other ranks
+    if (bytes > state_capacity_) throw std::logic_error("SetInitial: state larger than the buffer shared with the other ranks");
+    wavefront_bytes_ = bytes;
+  } else {
+    if (d_wavefront_ && wavefront_bytes_ != bytes) { CU(cudaFree(d_wavefront_)); d_wavefront_ = nullptr; }
+    if (!d_wavefront_) { CU(cudaMalloc(&d_wavefront_, bytes)); wavefront_bytes_ = bytes; }
+  }
   cs_points_ = compact_possible_ ? tent_fast_compact_points(D, order_, fosystem_) : 0;
   cstate_valid_ = false;
   if (cs_points_ > 0) {
     const size_t cb = (size_t)nel_ * ncomp * cs_points_ * sizeof(double);
-    if (d_cstate_ && cstate_bytes_ != cb) { CU(cudaFree(d_cstate_)); d_cstate_ = nullptr; }
-    if (!d_cstate_) { CU(cudaMalloc(&d_cstate_, cb)); cstate_bytes_ = cb; }
+    if (cstate_capacity_ > 0) {
+      if (cb > cstate_capacity_) throw std::logic_error("SetInitial: compact state larger than the buffer shared with the other ranks");
+      cstate_bytes_ = cb;
+    } else {
+      if (d_cstate_ && cstate_bytes_ != cb) { CU(cudaFree(d_cstate_)); d_cstate_ = nullptr; }
+      if (!d_cstate_) { CU(cudaMalloc(&d_cstate_, cb)); cstate_bytes_ = cb; }
+    }
   }
   if (wf) {
     CU(cudaMemcpyAsync(d_wavefront_, wf, bytes, cudaMemcpyHostToDevice, stream_));
@@ -679,6 +694,7 @@ void Solver::Propagate(int level_limit) {
   // factor cache: first full Propagate of this system stores the inverses (MODE 1), later ones apply them (MODE 2)
   fa.ainv = nullptr;
   fa.mode = 0;
+  fa.p2p = nullptr;
   const int fo = fosystem_;
   if (compact && factor_cache_enabled_ && !cache_failed_ && (ainv_valid_[fo] || !partial)) {
     if (!d_ainv_[fo]) {
@@ -762,7 +778,29 @@ void Solver::Propagate(int level_limit) {
     launches++;
     if (mirror_dev_) MirrorRows(0, nlev - 1, launches);  // single launch per slab: nothing to overlap with
   }
-  const bool overlap = comm_ && !force_generic_ && !qt_ && overlap_;
+  // multi-GPU, peer-to-peer: ONE dependency-driven launch per slab on every rank. Tents wait on hazard counters that tents of
+  // other ranks decrement with system-scope atomics after pushing their rows into this rank's buffers (tent_fast.cu).
+  const bool p2p = comm_ && p2p_ready_ && p2p_enabled_ && compact && overlap_ && !force_generic_ && !qt_ && !partial;
+  if (p2p) {
+    TentKernelArgs a = args_;
+    a.tents = d_level_fast_;
+    a.ntents = fast_off_.back();
+    a.ticket = d_ticket_;
+    a.remaining = d_remaining_;
+    a.succ_off = d_p2p_lsucc_off_;
+    a.succ = d_p2p_lsucc_;
+    fa.p2p = d_p2p_;
+    CU(launch_tent_fast(mesh_.D, order_, fosystem_, a, fa, stream_));
+    launches++;
+    // arm the counters for the next slab, then wait for everybody: when the barrier completes on this stream every rank has
+    // finished its tents (all pushes into this rank's buffers have landed) and nobody starts the next slab before all
+    // counters are armed
+    CU(cudaMemcpyAsync(d_remaining_, d_p2p_indeg_, sizeof(int) * slab_.ntents, cudaMemcpyDeviceToDevice, stream_));
+    CU(cudaMemsetAsync(d_ticket_, 0, sizeof(int), stream_));
+    comm_->Barrier(d_barrier_, stream_);
+    if (mirror_dev_) MirrorRows(0, nlev - 1, launches);
+  }
+  const bool overlap = comm_ && !force_generic_ && !qt_ && overlap_ && !p2p;
   if (overlap && !stream_halo_) {
     int lo = 0, hi = 0;
     CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
@@ -771,7 +809,7 @@ void Solver::Propagate(int level_limit) {
     CU(cudaEventCreateWithFlags(&ev_int_, cudaEventDisableTiming));
   }
   if (overlap) CU(cudaEventRecord(ev_int_, stream_));
-  for (int l = 0; l < nlev && !force_generic_ && !qt_ && !dag; l++) {
+  for (int l = 0; l < nlev && !force_generic_ && !qt_ && !dag && !p2p; l++) {
     // level l: [halo tents | interior tents] of the fast and of the generic list. Single GPU: one launch per list.
     // Multi-GPU: halo tents + exchange on the high-priority stream, interior tents concurrently on the main stream;
     // level l+1 starts when both are done (tents of a level touch disjoint rows, received rows belong to no local tent
@@ -813,7 +851,7 @@ void Solver::Propagate(int level_limit) {
   }
   if (overlap) {
     CU(cudaStreamWaitEvent(stream_, ev_halo_, 0));
-    if (mirror_dev_ && nlev > 0 && !force_generic_ && !qt_ && !dag) MirrorRows(nlev - 1, nlev - 1, launches);
+    if (mirror_dev_ && nlev > 0 && !force_generic_ && !qt_ && !dag && !p2p) MirrorRows(nlev - 1, nlev - 1, launches);
   }
   if (mirror_dev_) {  // the slab is done when the last rows have reached the host buffer
     CU(cudaEventRecord(ev_mirror_, stream_mirror_));
@@ -1080,7 +1118,134 @@ void Solver::InitComm(const void* id128) {
     }
     CU(cudaMalloc(&d_scalar_, sizeof(double)));
     allocs_.push_back(d_scalar_);
+    InitP2P();
   }
+}
+
+namespace {
+// offset of a device pointer inside its allocation: an IPC handle maps the allocation, not the pointer
+size_t offset_in_allocation(const void* p) {
+  using Fn = int (*)(unsigned long long*, size_t*, unsigned long long);
+  static Fn fn = [] {
+    void* lib = dlopen("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL);
+    return lib ? reinterpret_cast<Fn>(dlsym(lib, "cuMemGetAddressRange_v2")) : nullptr;
+  }();
+  unsigned long long base = 0;
+  size_t size = 0;
+  if (!fn || fn(&base, &size, (unsigned long long)p) != 0) return 0;
+  return (size_t)((unsigned long long)p - base);
+}
+struct P2PMsg {
+  int ok;
+  int pad;
+  cudaIpcMemHandle_t handle[3];
+  unsigned long long offset[3];
+};
+}  // namespace
+
+// Collective over the ranks of the partition (called from InitComm). Sets p2p_ready_ only if EVERY rank could set it up.
+void Solver::InitP2P() {
+  p2p_ready_ = false;
+  const int nr = plan_->nranks, me = plan_->rank, D = mesh_.D, Q = rule_.nip;
+  if (nr < 2) return;
+  const int qs = tent_fast_compact_points(D, order_, 0);
+  bool ok = compact_possible_ && qs > 0 && nr <= kMaxPeers && !have_initial_;
+  P2PMsg mine{};
+  const int nown = slab_.ntents;
+  try {
+    if (ok) {
+      // state buffers once, for the second-order system (the larger one): their IPC mappings stay valid
+      state_capacity_ = (size_t)nel_ * (D + 2) * Q * sizeof(double);
+      cstate_capacity_ = (size_t)nel_ * (D + 2) * qs * sizeof(double);
+      CU(cudaMalloc(&d_wavefront_, state_capacity_));
+      CU(cudaMalloc(&d_cstate_, cstate_capacity_));
+      CU(cudaMemset(d_wavefront_, 0, state_capacity_));
+      CU(cudaMemset(d_cstate_, 0, cstate_capacity_));
+      if (!d_remaining_) {
+        CU(cudaMalloc(&d_remaining_, sizeof(int) * std::max(nown, 1)));
+        allocs_.push_back(d_remaining_);
+        CU(cudaMalloc(&d_ticket_, sizeof(int)));
+        allocs_.push_back(d_ticket_);
+      }
+      void* ptrs[3] = {d_cstate_, d_wavefront_, d_remaining_};
+      for (int k = 0; k < 3; k++) {
+        CU(cudaIpcGetMemHandle(&mine.handle[k], ptrs[k]));
+        mine.offset[k] = offset_in_allocation(ptrs[k]);
+      }
+    }
+  } catch (const std::exception& e) {
+    p2p_note_ = e.what();
+    cudaGetLastError();
+    ok = false;
+  }
+  mine.ok = ok ? 1 : 0;
+  // agreement and handle exchange in one all-gather
+  std::vector<P2PMsg> all(nr);
+  {
+    P2PMsg *d_in = nullptr, *d_out = nullptr;
+    CU(cudaMalloc(&d_in, sizeof(P2PMsg)));
+    CU(cudaMalloc(&d_out, sizeof(P2PMsg) * nr));
+    CU(cudaMemcpyAsync(d_in, &mine, sizeof(P2PMsg), cudaMemcpyHostToDevice, stream_));
+    comm_->AllGatherBytes(d_in, d_out, sizeof(P2PMsg), stream_);
+    CU(cudaMemcpyAsync(all.data(), d_out, sizeof(P2PMsg) * nr, cudaMemcpyDeviceToHost, stream_));
+    CU(cudaStreamSynchronize(stream_));
+    CU(cudaFree(d_in));
+    CU(cudaFree(d_out));
+  }
+  bool all_ok = true;
+  for (const P2PMsg& m : all) all_ok = all_ok && m.ok;
+  int failed = 0;
+  if (all_ok) {
+    for (int q = 0; q < nr && !failed; q++) {
+      void* ptrs[3] = {d_cstate_, d_wavefront_, d_remaining_};
+      if (q != me)
+        for (int k = 0; k < 3; k++) {
+          void* base = nullptr;
+          if (cudaIpcOpenMemHandle(&base, all[q].handle[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+            p2p_note_ = std::string("cudaIpcOpenMemHandle: ") + cudaGetErrorString(cudaGetLastError());
+            failed = 1;
+            break;
+          }
+          ipc_opened_.push_back(base);
+          ptrs[k] = static_cast<char*>(base) + all[q].offset[k];
+        }
+      p2p_host_.cstate[q] = static_cast<double*>(ptrs[0]);
+      p2p_host_.wavefront[q] = static_cast<double*>(ptrs[1]);
+      p2p_host_.remaining[q] = static_cast<int*>(ptrs[2]);
+    }
+  }
+  // second agreement: every rank could open every handle
+  const double nfail = comm_->AllReduceSum(all_ok ? (double)failed : 1.0, d_scalar_, stream_);
+  if (nfail != 0.0) {
+    for (void* b : ipc_opened_) cudaIpcCloseMemHandle(b);
+    ipc_opened_.clear();
+    if (p2p_note_.empty()) p2p_note_ = all_ok ? "another rank could not map the peer buffers" : "not every rank can use the compact state";
+    // keep the fixed-capacity buffers (harmless); the per-level NCCL exchange is used
+    return;
+  }
+  const PartitionPlan& p = *plan_;
+  p2p_host_.push_off = Upload(p.p2p_push_off);
+  p2p_host_.push_peer = Upload(p.p2p_push_peer);
+  p2p_host_.push_el = Upload(p.p2p_push_el);
+  p2p_host_.rsucc_off = Upload(p.p2p_rsucc_off);
+  p2p_host_.rsucc_peer = Upload(p.p2p_rsucc_peer);
+  p2p_host_.rsucc_tent = Upload(p.p2p_rsucc_tent);
+  CU(cudaMalloc(&d_p2p_, sizeof(P2PArgs)));
+  allocs_.push_back(d_p2p_);
+  CU(cudaMemcpy(d_p2p_, &p2p_host_, sizeof(P2PArgs), cudaMemcpyHostToDevice));
+  d_p2p_indeg_ = Upload(p.p2p_indeg);
+  d_p2p_lsucc_off_ = Upload(p.p2p_lsucc_off);
+  d_p2p_lsucc_ = Upload(p.p2p_lsucc);
+  CU(cudaMalloc(&d_barrier_, sizeof(double)));
+  allocs_.push_back(d_barrier_);
+  CU(cudaMemset(d_barrier_, 0, sizeof(double)));
+  // counters armed for the first slab, then nobody starts before everybody is armed
+  CU(cudaMemcpyAsync(d_remaining_, d_p2p_indeg_, sizeof(int) * nown, cudaMemcpyDeviceToDevice, stream_));
+  CU(cudaMemsetAsync(d_ticket_, 0, sizeof(int), stream_));
+  comm_->Barrier(d_barrier_, stream_);
+  CU(cudaStreamSynchronize(stream_));
+  p2p_ready_ = true;
+  p2p_note_ = "peer-to-peer exchange inside the tent kernel";
 }
 
 double Solver::Energy(const double* wf) {

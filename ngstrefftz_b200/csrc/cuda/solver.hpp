@@ -100,6 +100,10 @@ class Solver {
   // by the first Propagate and stored in HBM (NP x N doubles per tent); later Propagates of the same slab geometry only
   // build right-hand sides, apply the stored inverses and evaluate. off: assemble and solve in every Propagate.
   void set_factor_cache(bool on) { factor_cache_enabled_ = on; }
+  // multi-GPU: exchange inside the tent kernel over peer memory (default where it could be set up) or per level with NCCL
+  void set_peer_exchange(bool on) { p2p_enabled_ = on; }
+  bool peer_exchange_active() const { return p2p_ready_ && p2p_enabled_ && UseCompact() && !qt_; }
+  const std::string& peer_exchange_note() const { return p2p_note_; }
   // 0 = not in use, 1 = the next Propagate assembles, inverts and stores, 2 = the next Propagate applies stored inverses
   int factor_cache_state() const { return !(UseCompact() && factor_cache_enabled_ && !cache_failed_) ? 0 : (ainv_valid_[fosystem_] ? 2 : 1); }
   size_t factor_cache_bytes() const { return ainv_bytes_[0] + ainv_bytes_[1]; }
@@ -204,6 +208,19 @@ class Solver {
   // multi-GPU: per (level, peer) the exchanged rows whose element becomes final in that level (public rows follow)
   std::vector<int> sendf_off_, recvf_off_;
   int *d_sendf_el_ = nullptr, *d_recvf_el_ = nullptr;
+  // ---- peer-to-peer exchange inside the tent kernel (multi-GPU): one dependency-driven launch per slab on every rank; tents
+  // push the rows they write into the other holders' buffers (CUDA IPC mappings over NVLink) and release their successors
+  // on other ranks with system-scope atomics. Falls back to the per-level NCCL exchange when it cannot be set up.
+  bool p2p_enabled_ = true, p2p_ready_ = false;
+  P2PArgs p2p_host_{};
+  P2PArgs* d_p2p_ = nullptr;
+  std::vector<void*> ipc_opened_;
+  int* d_p2p_indeg_ = nullptr;
+  int *d_p2p_lsucc_off_ = nullptr, *d_p2p_lsucc_ = nullptr;
+  double* d_barrier_ = nullptr;
+  size_t state_capacity_ = 0, cstate_capacity_ = 0;  // p2p: buffers allocated once for the largest system (IPC handles stay valid)
+  void InitP2P();
+  std::string p2p_note_;
   bool factor_cache_enabled_ = true, cache_failed_ = false;
   double* d_ainv_[2] = {nullptr, nullptr};  // [fosystem]
   size_t ainv_bytes_[2] = {0, 0};

@@ -174,7 +174,8 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
         // not a singular system), skips its work and still releases its successors so that the launch drains quickly
         if (++spins > (1ll << 26)) { atomicAdd(a.stuck, 1); stuck = 1; break; }
       }
-      __threadfence();
+      if (f.p2p) __threadfence_system();  // rows and counters may have been written by another GPU
+      else __threadfence();
       s_tent = t;
       s_stuck = stuck;
     }
@@ -182,6 +183,9 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
     tent = s_tent;
     if (s_stuck) {
       for (int s = a.succ_off[tent] + tid; s < a.succ_off[tent + 1]; s += kThreads) atomicSub(a.remaining + a.succ[s], 1);
+      if (f.p2p)
+        for (int s = f.p2p->rsucc_off[tent] + tid; s < f.p2p->rsucc_off[tent + 1]; s += kThreads)
+          atomicSub_system(f.p2p->remaining[f.p2p->rsucc_peer[s]] + f.p2p->rsucc_tent[s], 1);
       return;
     }
   } else {
@@ -768,9 +772,41 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
     }
   }
   if (a.ticket) {
-    __threadfence();  // this thread's state rows are visible device-wide before the successors are released
-    __syncthreads();
-    for (int s = a.succ_off[tent] + tid; s < a.succ_off[tent + 1]; s += kThreads) atomicSub(a.remaining + a.succ[s], 1);
+    if (CS && f.p2p) {
+      // multi-GPU: the rows this tent has just written also go to the other ranks that hold the element -- stores to
+      // their buffers over NVLink -- before its successors, here or there, are released
+      __syncthreads();
+      const P2PArgs& pp = *f.p2p;
+      constexpr int RL = C::ROWLEN, RP = NCW * Q;
+      for (int e = 0; e < nel; e++) {
+        const int te = te0 + e;
+        const int k0 = pp.push_off[te], k1 = pp.push_off[te + 1];
+        if (k0 == k1) continue;
+        const size_t el = (size_t)a.te_el[te];
+        const bool fin = f.te_final[te] != 0;
+        for (int k = k0; k < k1; k++) {
+          const int q = pp.push_peer[k];
+          const size_t pel = (size_t)pp.push_el[k];
+          double* __restrict__ dst = pp.cstate[q] + pel * RL;
+          const double* __restrict__ src = f.cstate + el * RL;
+          for (int i = tid; i < RL; i += kThreads) dst[i] = __ldcg(src + i);
+          if (fin) {
+            double* __restrict__ dw = pp.wavefront[q] + pel * RP;
+            const double* __restrict__ sw = a.wavefront + el * RP;
+            for (int i = tid; i < RP; i += kThreads) dw[i] = __ldcg(sw + i);
+          }
+        }
+      }
+      __threadfence_system();
+      __syncthreads();
+      for (int s = a.succ_off[tent] + tid; s < a.succ_off[tent + 1]; s += kThreads) atomicSub(a.remaining + a.succ[s], 1);
+      for (int s = pp.rsucc_off[tent] + tid; s < pp.rsucc_off[tent + 1]; s += kThreads)
+        atomicSub_system(pp.remaining[pp.rsucc_peer[s]] + pp.rsucc_tent[s], 1);
+    } else {
+      __threadfence();  // this thread's state rows are visible device-wide before the successors are released
+      __syncthreads();
+      for (int s = a.succ_off[tent] + tid; s < a.succ_off[tent + 1]; s += kThreads) atomicSub(a.remaining + a.succ[s], 1);
+    }
   }
 }
 

@@ -31,6 +31,22 @@ constexpr int fast_ff_n(int D) { return fast_ff_e(D) + D * (D + 1); }
 constexpr int fast_ff_misc(int D) { return fast_ff_n(D) + D; }
 constexpr int fast_ff_stride(int D) { return (fast_ff_misc(D) + 5 + 3) / 4 * 4; }
 
+// Peer-to-peer exchange inside the tent kernel (multi-GPU, dependency-driven single launch; device-resident table):
+// the state buffers and hazard counters of every rank of the box, mapped into this process (CUDA IPC over NVLink), the
+// holders of every tent-element of this rank and the successors of its tents on other ranks (host/partition.hpp).
+constexpr int kMaxPeers = 16;
+struct P2PArgs {
+  double* cstate[kMaxPeers];     // compact state of rank q (this rank's own buffer at its own index)
+  double* wavefront[kMaxPeers];  // public rows of rank q
+  int* remaining[kMaxPeers];     // hazard counters of rank q's tents
+  const int* push_off;           // nte + 1
+  const int* push_peer;
+  const int* push_el;
+  const int* rsucc_off;          // ntents + 1
+  const int* rsucc_peer;
+  const int* rsucc_tent;
+};
+
 struct FastArgs {
   const double* fe;     // nte * fast_fe_stride(D)
   const double* ff;     // ntf * fast_ff_stride(D)
@@ -53,6 +69,7 @@ struct FastArgs {
   // stored inverse. ainv: per staged tent NP x N doubles, the inverse transposed (column j of A^-1 at [j * NP, j * NP + N)).
   double* ainv;
   int mode;
+  const P2PArgs* p2p;   // nullptr: single GPU, or the per-level NCCL exchange
   // column-compressed basis matrix (monomial j -> functions), for sol -> monomial coefficients
   const int* cptr;      // npoly + 1
   const int* crow;      // nnz

@@ -86,6 +86,65 @@ PartitionPlan make_partition_plan(const SimplexMesh& m, const TentSlab& slab, co
       p.recv_off.push_back((int)p.recv_el.size());
     }
   }
+  // ---- cross-rank hazards and push lists
+  {
+    std::vector<int> towner(slab.ntents), tindex(slab.ntents), cnt(nranks, 0);
+    for (int t = 0; t < slab.ntents; t++) {
+      towner[t] = vowner[slab.vertex[t]];
+      tindex[t] = cnt[towner[t]]++;
+    }
+    const int nown = (int)p.own_tents.size();
+    p.p2p_indeg.assign(nown, 0);
+    std::vector<std::vector<int>> lsucc(nown), rsucc(nown);
+    std::vector<int> last(m.nel, -1), preds;
+    for (int t = 0; t < slab.ntents; t++) {
+      preds.clear();
+      for (int j = slab.els.off[t]; j < slab.els.off[t + 1]; j++) {
+        const int e = slab.els.val[j];
+        if (last[e] >= 0) preds.push_back(last[e]);
+        last[e] = t;
+      }
+      std::sort(preds.begin(), preds.end());
+      preds.erase(std::unique(preds.begin(), preds.end()), preds.end());
+      if (towner[t] == rank) p.p2p_indeg[tindex[t]] = (int)preds.size();
+      for (int q : preds) {
+        if (slab.level[q] >= slab.level[t]) throw std::invalid_argument("partition: tent levels do not respect the element hazards");
+        if (towner[q] != rank) continue;
+        (towner[t] == rank ? lsucc : rsucc)[tindex[q]].push_back(t);
+      }
+    }
+    p.p2p_lsucc_off.assign(1, 0);
+    p.p2p_rsucc_off.assign(1, 0);
+    for (int i = 0; i < nown; i++) {
+      for (int t : lsucc[i]) p.p2p_lsucc.push_back(tindex[t]);
+      for (int t : rsucc[i]) { p.p2p_rsucc_peer.push_back(towner[t]); p.p2p_rsucc_tent.push_back(tindex[t]); }
+      p.p2p_lsucc_off.push_back((int)p.p2p_lsucc.size());
+      p.p2p_rsucc_off.push_back((int)p.p2p_rsucc_peer.size());
+    }
+    // local element numbering of every rank: ascending global element among the elements with a vertex it owns
+    std::vector<int> nloc(nranks, 0);
+    std::vector<int> holders_off(m.nel + 1, 0), holders, holder_loc;
+    for (int e = 0; e < m.nel; e++) {
+      const int* ev = m.elverts(e);
+      for (int k = 0; k < d1; k++) {
+        const int q = vowner[ev[k]];
+        bool seen = false;
+        for (int kk = 0; kk < k; kk++) seen = seen || vowner[ev[kk]] == q;
+        if (seen) continue;
+        holders.push_back(q);
+        holder_loc.push_back(nloc[q]++);
+      }
+      holders_off[e + 1] = (int)holders.size();
+    }
+    p.p2p_push_off.assign(1, 0);
+    for (int t : p.own_tents)
+      for (int j = slab.els.off[t]; j < slab.els.off[t + 1]; j++) {
+        const int e = slab.els.val[j];
+        for (int h = holders_off[e]; h < holders_off[e + 1]; h++)
+          if (holders[h] != rank) { p.p2p_push_peer.push_back(holders[h]); p.p2p_push_el.push_back(holder_loc[h]); }
+        p.p2p_push_off.push_back((int)p.p2p_push_peer.size());
+      }
+  }
   return p;
 }
 

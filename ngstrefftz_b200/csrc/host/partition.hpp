@@ -25,6 +25,16 @@ struct PartitionPlan {
   std::vector<int> send_off, send_el;
   std::vector<int> recv_off, recv_el;
   int max_rows_per_level() const;    // max over levels of max(total send rows, total recv rows)
+
+  // ---- dependency-driven execution across ranks (peer-to-peer exchange inside the tent kernel, solver.cu): the hazards of
+  // the GLOBAL slab -- tent t waits for the last earlier tent, on whatever rank, that touched each of its elements.
+  // Own tents are numbered in own_tents order on every rank.
+  std::vector<int> p2p_indeg;                         // per own tent: distinct predecessor tents
+  std::vector<int> p2p_lsucc_off, p2p_lsucc;          // successors on this rank (own-tent index)
+  std::vector<int> p2p_rsucc_off, p2p_rsucc_peer, p2p_rsucc_tent;  // successors elsewhere: (rank, its own-tent index)
+  // per own tent-element, in the order of the restricted slab's element lists: the OTHER ranks that hold the element,
+  // with the element's local index there (where this tent's rows are pushed to)
+  std::vector<int> p2p_push_off, p2p_push_peer, p2p_push_el;
 };
 
 // vowner[v] in [0, nranks). Throws std::invalid_argument on malformed input.

@@ -54,10 +54,14 @@ def main():
     assert ts.PitchTents(dt, True, 2 / 3)
     # argv[3]: "brick" (default) or "balanced" vertex ownership; argv[4]: kernel mode (2 = exchange not overlapped)
     how = sys.argv[3] if len(sys.argv) > 3 else "brick"
+    nccl_only = how.endswith("-nccl")   # per-level NCCL exchange instead of the peer-to-peer exchange inside the kernel
+    how = how.replace("-nccl", "")
     owner = ng.balanced_vertex_owner(ts, grids[world]) if how == "balanced" else grids[world]
     tw, init, bnd, f = make_solver(case, mesh, ts, order, device=local, partition=(rank, world, owner))
     if len(sys.argv) > 4:
         tw.set_kernel_mode(int(sys.argv[4]))
+    if nccl_only:
+        tw.set_peer_exchange(False)
     tw.SetInitial(init)
     tw.SetBoundaryCF(bnd)
     e0 = tw.Energy()
@@ -83,7 +87,8 @@ def main():
         wf_dev = tw.GetWavefront()
     np.savez(os.path.join(outdir, f"rank{rank}.npz"), wf=wf, loc2glob=tw.loc2glob, owned=tw.owned, energy0=e0, energy=en,
              error=err, own_tents=tw.owned_tents(), launches=tw.last_launches(), ms=tw.last_ms(), mirror_ok=mirror_ok,
-             wf_dev=wf_dev, compact=tw.compact_state(), cache=tw.factor_cache()[0])
+             wf_dev=wf_dev, compact=tw.compact_state(), cache=tw.factor_cache()[0], p2p=tw.peer_exchange()[0],
+             p2p_note=tw.peer_exchange()[1])
     dist.barrier()
     dist.destroy_process_group()
     print("MULTI_OK", rank)

@@ -31,7 +31,7 @@ def _free_port():
 
 
 @pytest.mark.parametrize("case,world,how", [("cube_p4", 2, "brick"), ("square_p4", 2, "brick"), ("cube_p3", 2, "balanced"),
-                                            ("cube_p4", 2, "balanced"), ("cube_p4", 2, "brick-nooverlap"),
+                                            ("cube_p4", 2, "balanced"), ("cube_p4", 2, "brick-nooverlap"), ("cube_p4", 2, "balanced-nccl"),
                                             ("qt_square_p4", 2, "brick"), ("qt_square_p2", 2, "brick"),
                                             ("cube_p4", 4, "balanced"), ("cube_p3", 8, "brick"), ("cube_p4", 8, "balanced")])
 def test_partitioned_matches_single_gpu(built, case, world, how):
@@ -70,6 +70,7 @@ def test_partitioned_matches_single_gpu(built, case, world, how):
         for _ in range(nslabs):
             tw.Propagate()
         ref_dev = tw.GetWavefront()
+    print(case, world, how, "peer exchange:", [(bool(d["p2p"]), str(d["p2p_note"])) for d in ranks][:1])
     covered = np.zeros(mesh.ne, dtype=int)
     own = []
     for k, d in enumerate(ranks):
