@@ -116,6 +116,13 @@ int ngst_twave_set_wavespeed_poly(ngst_twave* t, int cdeg, const double* ccoef);
  * element ids; owned[i] = 1 when this rank counts local element i in Energy/Error. */
 int ngst_partition_plan(const ngst_slab* s, const int* vertex_owner, int nranks, int rank, int* counts, int* own_tents,
                         int* loc2glob, int* owned, int* send_off, int* send_el, int* recv_off, int* recv_el);
+/* The cross-rank hazard graph and push lists of the peer-to-peer exchange (host only; tests): counts[5] = own tents, local
+ * successor entries, remote successor entries, push entries, own tent-elements; indeg per own tent (predecessors on any
+ * rank); successors on this rank (own-tent index) and on other ranks (rank, its own-tent index); per own tent-element the
+ * other ranks holding the element with its local index there. Arrays may be NULL. */
+int ngst_partition_p2p(const ngst_slab* s, const int* vertex_owner, int nranks, int rank, long long* counts, int* indeg,
+                       int* lsucc_off, int* lsucc, int* rsucc_off, int* rsucc_peer, int* rsucc_tent, int* push_off,
+                       int* push_peer, int* push_el);
 int ngst_twave_create_partitioned(const ngst_slab* s, int order, const double* c_el, const double* c_vertex, int device,
                                   const int* vertex_owner, int nranks, int rank, ngst_twave** out);
 /* the quasi-Trefftz solver (ngst_qtwave_create) on this rank's part of the partition; the Taylor tables stay global

@@ -920,6 +920,22 @@ def partition_plan(tps, owner, nranks, rank):
     return out
 
 
+def partition_p2p(tps, owner, nranks, rank):
+    """Host-only view of a rank's cross-rank hazard graph and push lists (ngst_partition_p2p): dict of numpy arrays."""
+    owner = i32(owner)
+    counts = np.zeros(5, dtype=np.int64)
+    cp = counts.ctypes.data_as(_capi.c_llp)
+    check(lib.ngst_partition_p2p(tps._h, iptr(owner), nranks, rank, cp, None, None, None, None, None, None, None, None, None))
+    nown, nl, nr, npush, nte = (int(x) for x in counts)
+    out = {"indeg": np.zeros(nown, np.int32), "lsucc_off": np.zeros(nown + 1, np.int32), "lsucc": np.zeros(nl, np.int32),
+           "rsucc_off": np.zeros(nown + 1, np.int32), "rsucc_peer": np.zeros(nr, np.int32), "rsucc_tent": np.zeros(nr, np.int32),
+           "push_off": np.zeros(nte + 1, np.int32), "push_peer": np.zeros(npush, np.int32), "push_el": np.zeros(npush, np.int32)}
+    check(lib.ngst_partition_p2p(tps._h, iptr(owner), nranks, rank, cp, iptr(out["indeg"]), iptr(out["lsucc_off"]),
+                                 iptr(out["lsucc"]), iptr(out["rsucc_off"]), iptr(out["rsucc_peer"]), iptr(out["rsucc_tent"]),
+                                 iptr(out["push_off"]), iptr(out["push_peer"]), iptr(out["push_el"])))
+    return out
+
+
 def TWave(order, tps, wavespeedcf, BBcf=None, device=0, partition=None, comm_id=None):
     """Factory of src/twavetents.cpp:1194-1228. partition / comm_id: multi-GPU (see TWaveTents)."""
     return TWaveTents(order, tps, wavespeedcf, device=device, partition=partition, comm_id=comm_id, BBcf=BBcf)

@@ -60,6 +60,7 @@ _SIGS = {
     "ngst_slab_destroy": (None, [c_vp]),
     "ngst_twave_create": (C.c_int, [c_vp, C.c_int, c_dp, c_dp, C.c_int, C.POINTER(c_vp)]),
     "ngst_partition_plan": (C.c_int, [c_vp, c_ip, C.c_int, C.c_int, c_ip, c_ip, c_ip, c_ip, c_ip, c_ip, c_ip, c_ip]),
+    "ngst_partition_p2p": (C.c_int, [c_vp, c_ip, C.c_int, C.c_int, c_llp, c_ip, c_ip, c_ip, c_ip, c_ip, c_ip, c_ip, c_ip, c_ip]),
     "ngst_twave_create_partitioned": (C.c_int, [c_vp, C.c_int, c_dp, c_dp, C.c_int, c_ip, C.c_int, C.c_int,
                                                 C.POINTER(c_vp)]),
     "ngst_qtwave_create": (C.c_int, [c_vp, C.c_int, c_dp, c_dp, C.c_int, C.c_int, c_dp, c_dp, c_dp, C.POINTER(c_vp)]),

@@ -255,6 +255,26 @@ int ngst_partition_plan(const ngst_slab* s, const int* vertex_owner, int nranks,
   });
 }
 
+int ngst_partition_p2p(const ngst_slab* s, const int* vertex_owner, int nranks, int rank, long long* counts, int* indeg,
+                       int* lsucc_off, int* lsucc, int* rsucc_off, int* rsucc_peer, int* rsucc_tent, int* push_off,
+                       int* push_peer, int* push_el) {
+  return guarded([&] {
+    need(s, "slab"); need(vertex_owner, "vertex_owner"); need(counts, "counts");
+    const SimplexMesh& m = *s->s.mesh;
+    const std::vector<int> vo(vertex_owner, vertex_owner + m.nv);
+    const PartitionPlan p = make_partition_plan(m, s->s, vo, nranks, rank);
+    counts[0] = (long long)p.own_tents.size();
+    counts[1] = (long long)p.p2p_lsucc.size();
+    counts[2] = (long long)p.p2p_rsucc_peer.size();
+    counts[3] = (long long)p.p2p_push_peer.size();
+    counts[4] = (long long)p.p2p_push_off.size() - 1;
+    copy_out(indeg, p.p2p_indeg);
+    copy_out(lsucc_off, p.p2p_lsucc_off); copy_out(lsucc, p.p2p_lsucc);
+    copy_out(rsucc_off, p.p2p_rsucc_off); copy_out(rsucc_peer, p.p2p_rsucc_peer); copy_out(rsucc_tent, p.p2p_rsucc_tent);
+    copy_out(push_off, p.p2p_push_off); copy_out(push_peer, p.p2p_push_peer); copy_out(push_el, p.p2p_push_el);
+  });
+}
+
 int ngst_twave_create_partitioned(const ngst_slab* s, int order, const double* c_el, const double* c_vertex, int device,
                                   const int* vertex_owner, int nranks, int rank, ngst_twave** out) {
   return guarded([&] {

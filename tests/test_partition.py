@@ -112,3 +112,62 @@ def test_halo_exchange_two_ranks_gloo(built, case):
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o
         assert "HALO_OK" in o, o
+
+
+# ---------------------------------------------------------------------------------------------- peer-to-peer exchange plan
+@pytest.mark.parametrize("D,world,grid", [(2, 2, (2, 1)), (2, 4, (2, 2)), (3, 2, (2, 1, 1)), (3, 8, (2, 2, 2)), (1, 2, (2,))])
+def test_peer_exchange_plan_replays_the_slab(built, D, world, grid):
+    """The cross-rank hazard graph and push lists the tent kernel uses for the peer-to-peer exchange (ngst_partition_p2p),
+    replayed on the host with one row per (rank, local element): every rank runs its tents in level order, a tent may only
+    run when its counter is zero and every row it reads carries the version the serial order prescribes, pushes reach
+    exactly the other holders of an element, and the counters drain."""
+    mesh = {1: lambda: ng.SegMesh(24, 0, 1), 2: lambda: ng.UnitSquareMesh(6), 3: lambda: ng.UnitCubeMesh(4)}[D]()
+    ts = ng.TentSlab(mesh, "edge")
+    ts.SetMaxWavespeed(1.0)
+    assert ts.PitchTents(0.2, True, 2 / 3)
+    e = ts.export()
+    owner = ng.brick_vertex_owner(mesh, grid)
+    plans = [ng.partition_plan(ts, owner, world, r) for r in range(world)]
+    p2p = [ng.partition_p2p(ts, owner, world, r) for r in range(world)]
+    nt = ts.GetNTents()
+    # serial reference: version of an element's row = id of the last tent that wrote it
+    version = -np.ones(mesh.ne, dtype=np.int64)
+    want_read = {}
+    for t in range(nt):
+        els = e["els"][e["el_off"][t]:e["el_off"][t + 1]]
+        want_read[t] = version[els].copy()
+        version[els] = t
+    rows = [-np.ones(len(pl["loc2glob"]), dtype=np.int64) for pl in plans]          # per rank: version held per local row
+    g2l = [{int(g): i for i, g in enumerate(pl["loc2glob"])} for pl in plans]
+    remaining = [pp["indeg"].copy() for pp in p2p]
+    te0 = [np.concatenate([[0], np.cumsum([e["el_off"][t + 1] - e["el_off"][t] for t in pl["own_tents"]])]) for pl in plans]
+    # interleave the ranks level by level (any interleaving that respects the counters must do)
+    order = sorted(((int(e["level"][t]), r, i) for r, pl in enumerate(plans) for i, t in enumerate(pl["own_tents"])))
+    done = 0
+    for lev, r, i in order:
+        t = int(plans[r]["own_tents"][i])
+        assert remaining[r][i] == 0, f"tent {t} on rank {r} would start before its predecessors are done"
+        els = e["els"][e["el_off"][t]:e["el_off"][t + 1]]
+        loc = [g2l[r][int(g)] for g in els]
+        assert np.array_equal(rows[r][loc], want_read[t]), f"tent {t} on rank {r} reads a stale row"
+        rows[r][loc] = t
+        pp = p2p[r]
+        for k, g in enumerate(els):
+            te = te0[r][i] + k
+            peers = pp["push_peer"][pp["push_off"][te]:pp["push_off"][te + 1]]
+            pels = pp["push_el"][pp["push_off"][te]:pp["push_off"][te + 1]]
+            holders = sorted(q for q in range(world) if q != r and int(g) in g2l[q])
+            assert sorted(peers.tolist()) == holders
+            for q, pel in zip(peers, pels):
+                assert plans[q]["loc2glob"][pel] == g
+                rows[q][pel] = t
+        for s in pp["lsucc"][pp["lsucc_off"][i]:pp["lsucc_off"][i + 1]]:
+            remaining[r][s] -= 1
+        for q, s in zip(pp["rsucc_peer"][pp["rsucc_off"][i]:pp["rsucc_off"][i + 1]],
+                        pp["rsucc_tent"][pp["rsucc_off"][i]:pp["rsucc_off"][i + 1]]):
+            assert q != r
+            remaining[q][s] -= 1
+        done += 1
+    assert done == nt and all((x == 0).all() for x in remaining)
+    for r in range(world):  # every rank ends with the final version of all its rows
+        assert np.array_equal(rows[r], version[plans[r]["loc2glob"]])
