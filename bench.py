@@ -55,6 +55,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-mirror", action="store_true", help="e2e arm: explicit get_wavefront copy instead of the output mirror")
+    ap.add_argument("--no-streamed-input", action="store_true",
+                    help="e2e arm: blocking ngst_twave_set_initial instead of ngst_twave_set_initial_streamed")
     ap.add_argument("--no-device-data", action="store_true", help="skip the informational device-sampled-data arm")
     ap.add_argument("--partition", default="balanced", choices=["balanced", "brick"],
                     help="N>1: cost-balanced recursive bisection (default) or plain brick cut of the bounding box")
@@ -406,18 +408,31 @@ def run_ours(args):
         # (partitioned solvers: the rank's local rows).
         use_mirror = not args.no_mirror
 
-        def e2e_step(mirror=None):
+        use_stream = not args.no_streamed_input
+
+        def e2e_step(mirror=None, stream=None):
             mirror = use_mirror if mirror is None else mirror
+            stream = use_stream if stream is None else stream
             tw.reset_time()
-            check(lib.ngst_twave_set_initial(tw._h, in_ptr, ncomp))               # H2D: state rows
+            if stream:   # H2D of the state rows in first-use order, overlapped with the first tent levels
+                check(lib.ngst_twave_set_initial_streamed(tw._h, in_ptr, ncomp))
+            else:
+                check(lib.ngst_twave_set_initial(tw._h, in_ptr, ncomp))           # H2D: state rows
             check(lib.ngst_twave_set_boundary_values(tw._h, b_ptr, nb))            # H2D: boundary samples
             check(lib.ngst_twave_propagate(tw._h))                                 # (+ D2H of final rows with the mirror)
             if not mirror:
                 check(lib.ngst_twave_get_wavefront(tw._h, out_ptr))                # D2H: state rows
 
-        if use_mirror:
-            e2e_step(False)                      # reference result through the explicit copy
+        if use_mirror or use_stream:
+            e2e_step(False, False)               # reference result: blocking copy in, explicit copy out
             want = pin_out.numpy().copy()
+            if use_stream:
+                pin_out.zero_()
+                e2e_step(False, True)
+                if not np.array_equal(pin_out.numpy(), want):
+                    print("bench.py: streamed input differs from ngst_twave_set_initial; timing the blocking copy", file=sys.stderr)
+                    use_stream = False
+        if use_mirror:
             pin_out.zero_()
             check(lib.ngst_twave_set_output_mirror(tw._h, out_ptr))
             e2e_step(True)
@@ -436,7 +451,7 @@ def run_ours(args):
             e2e_step()
         barrier()
         e2e_s = time.perf_counter() - t0
-        e2e = {"sec": e2e_s, "h2d": int(nbytes + nb * 8), "d2h": int(nbytes), "mirror": use_mirror}
+        e2e = {"sec": e2e_s, "h2d": int(nbytes + nb * 8), "d2h": int(nbytes), "mirror": use_mirror, "stream": use_stream}
         if use_mirror:
             check(lib.ngst_twave_set_output_mirror(tw._h, None))
 
@@ -687,7 +702,9 @@ def run_ours(args):
         line["e2e"] = {"value": tents_step * args.steps / e2e_s, "unit": "tents/s",
                        "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"],
                        "ms_per_step": 1e3 * e2e_s / args.steps,
-                       "path": ("ngst_twave_set_initial + set_boundary_values + propagate on pinned host buffers, result rows "
+                       "streamed_input": bool(e2e.get("stream")),
+                       "path": (("ngst_twave_set_initial_streamed" if e2e.get("stream") else "ngst_twave_set_initial") +
+                                " + set_boundary_values + propagate on pinned host buffers, result rows "
                                 "streamed into the host buffer during propagate (ngst_twave_set_output_mirror; checked bitwise "
                                 "against ngst_twave_get_wavefront before timing)") if e2e.get("mirror") else
                                "ngst_twave_set_initial + set_boundary_values + propagate + get_wavefront on pinned host buffers"}

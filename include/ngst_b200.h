@@ -154,6 +154,13 @@ int ngst_twave_quadrature(const ngst_twave* t, double* x, double* weight);
 /* SetInitial src/twavetents.hpp:195-204: wf is nel x (ncomp*nip), row = [comp][q]; ncomp == D+2 second-order
  * input (u, grad u, dt u), ncomp == D+1 first-order input (switches to fosystem, nbasis-1). Host pointer. */
 int ngst_twave_set_initial(ngst_twave* t, const double* wf, int ncomp);
+/* Streamed form of ngst_twave_set_initial (no reference counterpart): returns at once; the device fetches the rows of `wf`
+ * over PCIe in the order in which the tent levels first need them (half of the rows of a slab are first read by level 0,
+ * the rest level by level), transfers each batch to the compact state, and every level of the NEXT ngst_twave_propagate
+ * waits for its own rows only, so that most of the host-to-device copy overlaps the tents. `wf` must be page-locked
+ * (pageable memory is page-locked and mapped by the call) and must stay unchanged until that propagate has returned;
+ * any other call that reads the state waits for the whole input first. */
+int ngst_twave_set_initial_streamed(ngst_twave* t, const double* wf, int ncomp);
 /* Boundary datum (SetBoundaryCF src/twavetents.hpp:206-209, evaluated at src/twavetents.cpp:373-407):
  * number of sample points and their (x, t_local) coordinates, npoints*(D+1); the datum must be evaluated at
  * (x, t_local + timeshift). values: for each boundary face in the same order nip Dirichlet values (dt u) or

@@ -589,6 +589,17 @@ class TWaveTents(TrefftzTents):
         check(lib.ngst_twave_set_initial(self._h, dptr(wf), ncomp))
         self._refresh()
 
+    def SetInitialStreamed(self, wf):
+        """SetInitial from a host array whose rows the device fetches in first-use order while the first tent levels of the
+        next Propagate run (ngst_twave_set_initial_streamed). `wf` (C-contiguous float64, nel x ncomp*nip) must stay
+        unchanged until that Propagate has returned; the solver keeps a reference."""
+        if not (isinstance(wf, np.ndarray) and wf.dtype == np.float64 and wf.flags.c_contiguous and wf.ndim == 2
+                and wf.shape[0] == self.nel and wf.shape[1] % self.nip == 0):
+            raise ValueError("SetInitialStreamed: need a C-contiguous float64 array of nel x (ncomp*nip) entries")
+        self._streamed = wf
+        check(lib.ngst_twave_set_initial_streamed(self._h, dptr(wf), wf.shape[1] // self.nip))
+        self._refresh()
+
     def SetBoundaryCF(self, bddatum):
         """An AnalyticData datum is sampled on the device by every Propagate (Dirichlet faces take d_t u, Neumann faces
         grad u); any other callable is evaluated on the host per slab as before."""

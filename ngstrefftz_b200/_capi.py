@@ -75,6 +75,7 @@ _SIGS = {
     "ngst_twave_info": (C.c_int, [c_vp, c_ip]),
     "ngst_twave_quadrature": (C.c_int, [c_vp, c_dp, c_dp]),
     "ngst_twave_set_initial": (C.c_int, [c_vp, c_dp, C.c_int]),
+    "ngst_twave_set_initial_streamed": (C.c_int, [c_vp, c_dp, C.c_int]),
     "ngst_twave_boundary_npoints": (C.c_longlong, [c_vp]),
     "ngst_twave_boundary_nvalues": (C.c_longlong, [c_vp]),
     "ngst_twave_boundary_points": (C.c_int, [c_vp, c_dp, c_ip]),

@@ -393,6 +393,10 @@ int ngst_twave_set_initial(ngst_twave* t, const double* wf, int ncomp) {
 long long ngst_twave_boundary_npoints(const ngst_twave* t) { return t ? t->solver->staged().nbnd_points : 0; }
 long long ngst_twave_boundary_nvalues(const ngst_twave* t) { return t ? t->solver->staged().nbnd_values : 0; }
 
+int ngst_twave_set_initial_streamed(ngst_twave* t, const double* wf, int ncomp) {
+  return guarded([&] { need(t, "solver"); need(wf, "wf"); t->solver->SetInitialStreamed(wf, ncomp); });
+}
+
 int ngst_twave_boundary_points(const ngst_twave* t, double* xt, int* kind_per_point) {
   return guarded([&] {
     need(t, "solver");

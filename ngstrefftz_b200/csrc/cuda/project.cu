@@ -24,7 +24,8 @@ constexpr int kElems = 8;
 // NT = n-tiles of 8 columns; K = Q rounded up to 4 (zero padded).
 template <int NT>
 __global__ void __launch_bounds__(128) transfer_rows_dmma_kernel(long long nrows, int Q, int ndof, const double* __restrict__ P,
-                                                                 const double* __restrict__ in, double* __restrict__ out) {
+                                                                 const double* __restrict__ in, double* __restrict__ out,
+                                                                 const int* __restrict__ groups, int per_group) {
   extern __shared__ double sm[];
   const int KP = (Q + 3) / 4 * 4;          // padded inner dimension
   const int LD = KP + ((4 - KP % 16) + 16) % 16;  // row stride == 4 (mod 16) doubles
@@ -39,8 +40,17 @@ __global__ void __launch_bounds__(128) transfer_rows_dmma_kernel(long long nrows
   __syncthreads();
   for (long long r0 = (long long)blockIdx.x * 32; r0 < nrows; r0 += (long long)gridDim.x * 32) {
     const int nr = (int)min((long long)32, nrows - r0);
-    // 32 consecutive rows are one contiguous block of nr * Q doubles
-    for (int i = tid; i < nr * Q; i += 128) Vs[(i / Q) * LD + i % Q] = in[r0 * Q + i];
+    if (groups == nullptr) {
+      // 32 consecutive rows are one contiguous block of nr * Q doubles
+      for (int i = tid; i < nr * Q; i += 128) Vs[(i / Q) * LD + i % Q] = in[r0 * Q + i];
+    } else {
+      // row r of the pass is row (r % per_group) of the group groups[r / per_group] (an element's component rows)
+      for (int i = tid; i < nr * Q; i += 128) {
+        const long long r = r0 + i / Q;
+        const long long gr = (long long)groups[r / per_group] * per_group + r % per_group;
+        Vs[(i / Q) * LD + i % Q] = in[gr * Q + i % Q];
+      }
+    }
     __syncthreads();
     double acc[NT][2];
 #pragma unroll
@@ -54,7 +64,9 @@ __global__ void __launch_bounds__(128) transfer_rows_dmma_kernel(long long nrows
     }
     const int r = 8 * w + g;
     if (r < nr) {
-      double* __restrict__ o = out + (r0 + r) * ndof;
+      const long long rr = r0 + r;
+      const long long orow = groups ? (long long)groups[rr / per_group] * per_group + rr % per_group : rr;
+      double* __restrict__ o = out + orow * ndof;
 #pragma unroll
       for (int t = 0; t < NT; t++) {
         const int n = 8 * t + 2 * k;
@@ -113,8 +125,10 @@ cudaError_t launch_project_rows(int nel, int Q, int ndof, int comp0, int ncomp_u
 }
 
 // out[row][n] = sum_q P[n][q] in[row][q] for nrows contiguous rows of Q doubles (ndof <= 64)
+// groups != nullptr: only the rows of the listed groups (ngroups groups of per_group consecutive rows each; in / out are
+// indexed by the group's own number) -- the streamed input transfers the rows of the elements it has just fetched
 cudaError_t launch_transfer_rows(long long nrows, int Q, int ndof, const double* P, const double* in, double* out,
-                                 cudaStream_t stream) {
+                                 cudaStream_t stream, const int* groups, int per_group) {
   if (nrows <= 0) return cudaSuccess;
   const int NT = (ndof + 7) / 8;
   if (NT < 1 || NT > 8) return cudaErrorInvalidValue;
@@ -131,7 +145,7 @@ cudaError_t launch_transfer_rows(long long nrows, int Q, int ndof, const double*
   case nt:                                                                                                                \
     e = cudaFuncSetAttribute(transfer_rows_dmma_kernel<nt>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);      \
     if (e != cudaSuccess) return e;                                                                                       \
-    transfer_rows_dmma_kernel<nt><<<grid, 128, smem, stream>>>(nrows, Q, ndof, P, in, out);                               \
+    transfer_rows_dmma_kernel<nt><<<grid, 128, smem, stream>>>(nrows, Q, ndof, P, in, out, groups, per_group);            \
     break;
   switch (NT) {
     NGST_TR(1) NGST_TR(2) NGST_TR(3) NGST_TR(4) NGST_TR(5) NGST_TR(6) NGST_TR(7) NGST_TR(8)

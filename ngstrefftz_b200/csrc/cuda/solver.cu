@@ -381,6 +381,10 @@ Solver::~Solver() {
   if (d_wavefront_) cudaFree(d_wavefront_);
   if (d_bnd_) cudaFree(d_bnd_);
   ReleaseMirror();
+  ReleaseLoadBuffer();
+  if (stream_load_) { cudaStreamSynchronize(stream_load_); cudaStreamDestroy(stream_load_); }
+  if (ev_load_start_) cudaEventDestroy(ev_load_start_);
+  for (cudaEvent_t e : ev_load_) cudaEventDestroy(e);
   if (stream_mirror_) cudaStreamDestroy(stream_mirror_);
   if (ev_level_) cudaEventDestroy(ev_level_);
   if (ev_mirror_) cudaEventDestroy(ev_mirror_);
@@ -511,6 +515,10 @@ void Solver::SetInitial(const double* wf, int ncomp) {
   if (qt_ && ncomp == D + 1)  // checked before any member changes: a failed call leaves the solver as it was
     throw std::invalid_argument("SetInitial: the quasi-Trefftz solver takes second-order initial data (D+2 components)");
   CU(cudaSetDevice(device_));
+  if (load_pending_) {  // a streamed input nobody consumed: its fetches still write into the buffers
+    CU(cudaStreamSynchronize(stream_load_));
+    load_pending_ = false;
+  }
   fosystem_ = (ncomp == D + 1) ? 1 : 0;  // twavetents.hpp:198-203
   ncomp_ = ncomp;
   basis_ = fosystem_ ? basis_fo_ : basis_so_;
@@ -586,6 +594,92 @@ void Solver::SetInitial(const double* wf, int ncomp) {
     throw std::invalid_argument("TWave: local system too large for shared memory (order / number of wavespeed regions per tent)");
   const int tiles = (a.Npad / 4) * (a.Npad / 4);
   threads_ = tiles > 128 ? 256 : (tiles > 32 ? 128 : 64);
+}
+
+void Solver::ReleaseLoadBuffer() {
+  if (load_host_ && load_registered_) {
+    cudaSetDevice(device_);
+    if (stream_load_) cudaStreamSynchronize(stream_load_);
+    cudaHostUnregister(const_cast<double*>(load_host_));
+  }
+  load_host_ = nullptr;
+  load_registered_ = false;
+}
+
+void Solver::FinishLoad() {
+  if (!load_pending_) return;
+  CU(cudaStreamWaitEvent(stream_, ev_load_.back(), 0));
+  load_pending_ = false;
+}
+
+void Solver::SetInitialStreamed(const double* wf, int ncomp) {
+  if (!wf) throw std::invalid_argument("SetInitialStreamed: null buffer");
+  FinishLoad();
+  SetInitial(nullptr, ncomp);  // validates, allocates, configures the kernels
+  const int nlev = (int)slab_.level_off.size() - 1;
+  const size_t bytes = (size_t)nel_ * ncomp_ * rule_.nip * sizeof(double);
+  if (wf != load_host_) {
+    ReleaseLoadBuffer();
+    cudaPointerAttributes attr{};
+    if (cudaPointerGetAttributes(&attr, wf) != cudaSuccess) {
+      cudaGetLastError();
+      attr.type = cudaMemoryTypeUnregistered;
+    }
+    if (attr.type == cudaMemoryTypeUnregistered) {
+      CU(cudaHostRegister(const_cast<double*>(wf), bytes, cudaHostRegisterMapped));
+      load_registered_ = true;
+    } else if (attr.type != cudaMemoryTypeHost) {
+      throw std::invalid_argument("SetInitialStreamed: the buffer must be host memory");
+    }
+    load_host_ = wf;
+  }
+  void* alias = nullptr;
+  CU(cudaHostGetDevicePointer(&alias, const_cast<double*>(wf), 0));
+  if (!stream_load_) {
+    int lo = 0, hi = 0;
+    CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CU(cudaStreamCreateWithPriority(&stream_load_, cudaStreamNonBlocking, hi));
+    CU(cudaEventCreateWithFlags(&ev_load_start_, cudaEventDisableTiming));
+    ev_load_.resize(nlev + 1);
+    for (cudaEvent_t& e : ev_load_) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    // level of the FIRST tent that contains each element (partitioned solvers: of this rank's tents -- rows only other
+    // ranks' tents touch are ghosts that nobody here reads before they are overwritten, they go last)
+    std::vector<int> first(nel_, nlev);
+    for (int t = 0; t < staged_.ntents; t++)
+      for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++) {
+        const int el = plan_ ? plan_->glob2loc[staged_.te_el[te]] : staged_.te_el[te];
+        first[el] = std::min(first[el], slab_.level[t]);
+      }
+    firstuse_off_.assign(nlev + 2, 0);
+    for (int el = 0; el < nel_; el++) firstuse_off_[first[el] + 1]++;
+    for (int i = 0; i <= nlev; i++) firstuse_off_[i + 1] += firstuse_off_[i];
+    std::vector<int> rows(nel_), pos(firstuse_off_.begin(), firstuse_off_.end() - 1);
+    for (int el = 0; el < nel_; el++) rows[pos[first[el]]++] = el;
+    d_firstuse_rows_ = Upload(rows);
+  }
+  const bool compact = cs_points_ > 0 && compact_enabled_;
+  if (compact && transfer_points_ != cs_points_) {
+    const SimplexRule rs = make_compact_rule(mesh_.D, 2 * order_);
+    d_transfer_ = Upload(rule_transfer_matrix(rule_, rs, order_));
+    transfer_points_ = cs_points_;
+  }
+  // everything the solver's stream still has to do with the old state comes first
+  CU(cudaEventRecord(ev_load_start_, stream_));
+  CU(cudaStreamWaitEvent(stream_load_, ev_load_start_, 0));
+  const int rowlen = ncomp_ * rule_.nip;
+  for (int b = 0; b <= nlev; b++) {
+    const int r0 = firstuse_off_[b], nr = firstuse_off_[b + 1] - r0;
+    if (nr > 0) {
+      // 32 CTAs x 16 KB in flight keep PCIe busy; each takes the place of one tent CTA while it waits for the bus
+      CU(launch_fetch_rows(d_firstuse_rows_ + r0, nr, rowlen, static_cast<const double*>(alias), d_wavefront_, 32, stream_load_));
+      if (compact)
+        CU(launch_transfer_rows((long long)nr * ncomp_, rule_.nip, cs_points_, d_transfer_, d_wavefront_, d_cstate_, stream_load_,
+                                d_firstuse_rows_ + r0, ncomp_));
+    }
+    CU(cudaEventRecord(ev_load_[b], stream_load_));
+  }
+  cstate_valid_ = compact;  // (in stream order: every consumer waits for the bucket events)
+  load_pending_ = true;
 }
 
 namespace {
@@ -681,6 +775,11 @@ void Solver::Propagate(int level_limit) {
   const bool partial = level_limit >= 0 && level_limit < nlev_all;
   const int nlev = partial ? level_limit : nlev_all;
   if (partial && plan_) throw std::logic_error("Propagate: partial slabs (propagate_levels) are for single-GPU solvers");
+  // streamed input (SetInitialStreamed): with one launch per level each level only waits for the rows it is the first to
+  // read; every other scheme waits for the whole input
+  const bool peer_ready = comm_ && p2p_ready_ && p2p_enabled_ && overlap_;
+  const bool stream_levels = load_pending_ && !qt_ && !force_generic_ && !partial && !peer_ready;
+  if (load_pending_ && !stream_levels) FinishLoad();
   // compact state: the fast kernel reads / writes d_cstate_ and writes the public rows of final elements only
   const bool compact = UseCompact() && !qt_;
   FastArgs fa = fargs_;
@@ -720,7 +819,7 @@ void Solver::Propagate(int level_limit) {
                               args_.tf_verts, args_.tf_data, args_.lam, kNeumann, d_bnd_, stream_));
     launches++;
   }
-  if (mirror_dev_) MirrorRows(-1, -1, launches);  // rows no tent touches are final from the start
+  if (mirror_dev_ && !stream_levels) MirrorRows(-1, -1, launches);  // rows no tent touches are final from the start
   for (int l = 0; l < nlev && qt_; l++) {
     // quasi-Trefftz: fast monomial-space DMMA kernel where a variant exists (second-order form, causal top faces),
     // generic kernel otherwise
@@ -762,8 +861,10 @@ void Solver::Propagate(int level_limit) {
   const bool small_levels = slab_.ntents < 2 * 444 * nlev;
   // (r04d, B200: with stored inverses a tent is 6x cheaper and the single launch wins at config 4 as well, 11.74 vs 12.17 ms;
   // not with an output mirror, whose copies overlap the per-level launches)
-  const bool cheap_tents = fa.mode == 2 && !mirror_dev_;
-  const bool dag = dag_ && (dag_mode_ == 2 || (dag_mode_ == 1 && (small_levels || cheap_tents))) && !force_generic_ && !comm_ && !partial;
+  const bool cheap_tents = fa.mode == 2 && !mirror_dev_ && !stream_levels;
+  const bool dag = dag_ && (dag_mode_ == 2 || (dag_mode_ == 1 && (small_levels || cheap_tents))) && !force_generic_ && !comm_ && !partial &&
+                   !(stream_levels && dag_mode_ != 2);
+  if (dag && load_pending_) FinishLoad();
   if (dag) {
     CU(cudaMemcpyAsync(d_remaining_, d_indeg_, sizeof(int) * slab_.ntents, cudaMemcpyDeviceToDevice, stream_));
     CU(cudaMemsetAsync(d_ticket_, 0, sizeof(int), stream_));
@@ -790,6 +891,8 @@ void Solver::Propagate(int level_limit) {
     a.succ_off = d_p2p_lsucc_off_;
     a.succ = d_p2p_lsucc_;
     fa.p2p = d_p2p_;
+    // nobody's tents push into a buffer that its owner is still filling (SetInitial, sampling, the compact transfer)
+    comm_->Barrier(d_barrier_, stream_);
     CU(launch_tent_fast(mesh_.D, order_, fosystem_, a, fa, stream_));
     launches++;
     // arm the counters for the next slab, then wait for everybody: when the barrier completes on this stream every rank has
@@ -815,6 +918,10 @@ void Solver::Propagate(int level_limit) {
     // level l+1 starts when both are done (tents of a level touch disjoint rows, received rows belong to no local tent
     // of the level).
     const int fh = overlap ? fast_nhalo_[l] : 0, gh = overlap ? gen_nhalo_[l] : 0;
+    if (load_pending_) {  // the rows this level is the first to read have landed (earlier buckets: in stream order)
+      CU(cudaStreamWaitEvent(stream_, ev_load_[l], 0));
+      if (overlap) CU(cudaStreamWaitEvent(stream_halo_, ev_load_[l], 0));
+    }
     if (overlap) {
       CU(cudaStreamWaitEvent(stream_halo_, ev_int_, 0));
       if (l > 0) {
@@ -852,6 +959,10 @@ void Solver::Propagate(int level_limit) {
   if (overlap) {
     CU(cudaStreamWaitEvent(stream_, ev_halo_, 0));
     if (mirror_dev_ && nlev > 0 && !force_generic_ && !qt_ && !dag && !p2p) MirrorRows(nlev - 1, nlev - 1, launches);
+  }
+  if (load_pending_) {  // rows no tent of this rank reads: the input is complete when they have landed
+    FinishLoad();
+    if (mirror_dev_) MirrorRows(-1, -1, launches);
   }
   if (mirror_dev_) {  // the slab is done when the last rows have reached the host buffer
     CU(cudaEventRecord(ev_mirror_, stream_mirror_));
@@ -999,6 +1110,7 @@ void Solver::MirrorRows(int first_level, int last_level, int& launches) {
 void Solver::GetWavefront(double* out) {
   if (!have_initial_) throw std::logic_error("GetWavefront: SetInitial has not been called");
   CU(cudaSetDevice(device_));
+  FinishLoad();
   const size_t bytes = (size_t)nel_ * ncomp_ * rule_.nip * sizeof(double);
   CU(cudaMemcpyAsync(out, d_wavefront_, bytes, cudaMemcpyDeviceToHost, stream_));
   CU(cudaStreamSynchronize(stream_));
@@ -1024,6 +1136,7 @@ double Solver::ReduceElements(const double* a, const double* b, int mode) {
 void Solver::GetWave(int* sizes, double* coef, double* psi_at_points, double* mono_coef, int* expo) {
   if (!have_initial_) throw std::logic_error("GetWave: SetInitial has not been called");
   CU(cudaSetDevice(device_));
+  FinishLoad();
   const int D = mesh_.D, Q = rule_.nip;
   const int deg = fosystem_ ? order_ - 1 : order_;
   const int comps = fosystem_ ? D + 1 : 1;
@@ -1251,6 +1364,7 @@ void Solver::InitP2P() {
 double Solver::Energy(const double* wf) {
   if (!have_initial_) throw std::logic_error("Energy: SetInitial has not been called");
   CU(cudaSetDevice(device_));
+  FinishLoad();
   const size_t bytes = (size_t)nel_ * ncomp_ * rule_.nip * sizeof(double);
   const double* src = d_wavefront_;
   if (wf) {
@@ -1279,6 +1393,7 @@ double Solver::ErrorAnalytic(int family, const double* params, int nparams, doub
   check_family(mesh_.D, family, params, nparams);
   if (l2only && fosystem_) throw std::invalid_argument("L2Error: the first-order state has no u component");
   CU(cudaSetDevice(device_));
+  FinishLoad();
   const size_t bytes = (size_t)nel_ * ncomp_ * rule_.nip * sizeof(double);
   if (!d_tmp_b_) CU(cudaMalloc(&d_tmp_b_, bytes));
   double* d_p = UploadParams(params, nparams, &d_tmp_params_);

@@ -58,6 +58,10 @@ class Solver {
 
   void Quadrature(double* x, double* weight) const;
   void SetInitial(const double* wf, int ncomp);
+  // Streamed input: as SetInitial, but returns at once; the rows are fetched from `wf` (page-locked by the call if it is
+  // pageable; must stay unchanged until the next Propagate has returned) by the device in the order in which the tent levels
+  // first need them, and every level of that Propagate only waits for its own rows.
+  void SetInitialStreamed(const double* wf, int ncomp);
   void SetBoundaryValues(const double* values, long long n);
   // Analytic data sampled on the device (cuda/sample.hpp): SetInitial / MakeWavefront
   // (twavetents.cpp:734-764) and the boundary datum, re-sampled by every Propagate at t_local + timeshift
@@ -192,6 +196,17 @@ class Solver {
   int proj_deg_ = -1, proj_ndof_ = 0;
   std::vector<double> proj_psi_, proj_mono_;
   std::vector<int> proj_expo_;
+  // ---- streamed input (SetInitialStreamed)
+  const double* load_host_ = nullptr;   // caller's buffer, registered by us if load_registered_
+  bool load_registered_ = false;
+  bool load_pending_ = false;           // fetches are enqueued on stream_load_; ev_load_[b] = bucket b has landed
+  int* d_firstuse_rows_ = nullptr;      // local elements ordered by the level of the first tent that contains them
+  std::vector<int> firstuse_off_;       // nlev + 2 offsets: bucket l = first used in level l, bucket nlev = never used
+  cudaStream_t stream_load_ = nullptr;
+  cudaEvent_t ev_load_start_ = nullptr;
+  std::vector<cudaEvent_t> ev_load_;
+  void FinishLoad();                    // the whole input has landed before the solver's stream goes on
+  void ReleaseLoadBuffer();
   // ---- compact state
   bool compact_enabled_ = true;
   bool compact_possible_ = false;     // every tent of the slab runs on the fast kernel
@@ -246,7 +261,9 @@ cudaError_t launch_tent_generic(int D, const TentKernelArgs& a, int threads, siz
 cudaError_t launch_project_rows(int nel, int Q, int ndof, int comp0, int ncomp_used, int rowlen, const double* P,
                                 const double* wf, double* out, cudaStream_t stream);
 cudaError_t launch_transfer_rows(long long nrows, int Q, int ndof, const double* P, const double* in, double* out,
-                                 cudaStream_t stream);
+                                 cudaStream_t stream, const int* groups = nullptr, int per_group = 1);
+cudaError_t launch_fetch_rows(const int* rows, int nrows, int rowlen, const double* host_alias, double* wf, int ctas,
+                              cudaStream_t stream);
 cudaError_t launch_mirror_rows(const int* rows, int nrows, int rowlen, const double* wf, double* host_alias, int ctas,
                                cudaStream_t stream);
 cudaError_t launch_element_reduce(int mode, int D, int nel, int Q, int ncomp, int fosystem, const double* elw,

@@ -772,9 +772,12 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
     }
   }
   if (a.ticket) {
-    if (CS && f.p2p) {
+    bool remote = false;
+    if (CS && f.p2p) remote = f.p2p->push_off[te0 + nel] > f.p2p->push_off[te0] || f.p2p->rsucc_off[tent + 1] > f.p2p->rsucc_off[tent];
+    if (CS && remote) {
       // multi-GPU: the rows this tent has just written also go to the other ranks that hold the element -- stores to
-      // their buffers over NVLink -- before its successors, here or there, are released
+      // their buffers over NVLink -- before its successors, here or there, are released (interior tents, which neither
+      // push nor have successors elsewhere, take the cheaper device-scope path below)
       __syncthreads();
       const P2PArgs& pp = *f.p2p;
       constexpr int RL = C::ROWLEN, RP = NCW * Q;
