@@ -395,6 +395,7 @@ Solver::~Solver() {
   if (d_cstate_) cudaFree(d_cstate_);
   for (double* p : d_ainv_) if (p) cudaFree(p);
   for (void* b : ipc_opened_) cudaIpcCloseMemHandle(b);
+  for (double* p : d_ginv_) if (p) cudaFree(p);
   if (h_flags_) cudaFreeHost(h_flags_);
   if (d_sendbuf_) cudaFree(d_sendbuf_);
   if (d_recvbuf_) cudaFree(d_recvbuf_);
@@ -811,6 +812,33 @@ void Solver::Propagate(int level_limit) {
       fa.mode = ainv_valid_[fo] ? 2 : 1;
     }
   }
+  // factor cache of the generic kernel (small systems): inverses formed by the first full Propagate, applied afterwards
+  args_.ginv = nullptr;
+  args_.gmode = 0;
+  size_t gen_smem = smem_;
+  if (GenericCachePossible() && (ginv_valid_[fosystem_] || !partial)) {
+    const int fo = fosystem_;
+    const size_t nmax = (size_t)args_.max_ndom * args_.Npad;
+    if (!d_ginv_[fo]) {
+      const size_t bytes = sizeof(double) * nmax * nmax * (size_t)std::max(staged_.ntents, 1);
+      if (cudaMalloc(&d_ginv_[fo], bytes) != cudaSuccess) {
+        cudaGetLastError();
+        d_ginv_[fo] = nullptr;
+        ginv_failed_ = true;
+      } else {
+        ginv_bytes_[fo] = bytes;
+      }
+    }
+    if (d_ginv_[fo]) {
+      args_.ginv = d_ginv_[fo];
+      args_.gmode = ginv_valid_[fo] ? 2 : 1;
+      if (args_.gmode == 1) {
+        TentKernelArgs probe = args_;
+        gen_smem = tent_generic_smem_bytes(mesh_.D, probe);
+        if (gen_smem > 200 * 1024) { args_.ginv = nullptr; args_.gmode = 0; gen_smem = smem_; }
+      }
+    }
+  }
   int launches = 0;
   CU(cudaEventRecord(ev0_, stream_));
   if (bnd_family_ >= 0 && staged_.nbnd_values > 0) {
@@ -850,7 +878,7 @@ void Solver::Propagate(int level_limit) {
     a.tents = d_level_all_ + slab_.level_off[l];
     a.ntents = slab_.level_off[l + 1] - slab_.level_off[l];
     if (a.ntents > 0) {
-      CU(launch_tent_generic(mesh_.D, a, threads_, smem_, stream_));
+      CU(launch_tent_generic(mesh_.D, a, threads_, gen_smem, stream_));
       launches++;
     }
     if (comm_) launches += ExchangeLevel(l, stream_);
@@ -935,7 +963,7 @@ void Solver::Propagate(int level_limit) {
       if (h.ntents > 0) { CU(launch_tent_fast(mesh_.D, order_, fosystem_, h, fa, stream_halo_)); launches++; }
       h.tents = d_level_tents_ + gen_off_[l];
       h.ntents = gh;
-      if (h.ntents > 0) { CU(launch_tent_generic(mesh_.D, h, threads_, smem_, stream_halo_)); launches++; }
+      if (h.ntents > 0) { CU(launch_tent_generic(mesh_.D, h, threads_, gen_smem, stream_halo_)); launches++; }
       launches += ExchangeLevel(l, stream_halo_);
       CU(cudaEventRecord(ev_halo_, stream_halo_));
     }
@@ -949,7 +977,7 @@ void Solver::Propagate(int level_limit) {
     a.tents = d_level_tents_ + gen_off_[l] + gh;
     a.ntents = gen_off_[l + 1] - gen_off_[l] - gh;
     if (a.ntents > 0) {
-      CU(launch_tent_generic(mesh_.D, a, threads_, smem_, stream_));
+      CU(launch_tent_generic(mesh_.D, a, threads_, gen_smem, stream_));
       launches++;
     }
     if (overlap) CU(cudaEventRecord(ev_int_, stream_));
@@ -985,6 +1013,7 @@ void Solver::Propagate(int level_limit) {
     throw std::domain_error("Propagate: singular local system in " + std::to_string(sing) + " pivot step(s)");
   }
   if (fa.mode == 1) ainv_valid_[fo] = true;  // (a singular system has thrown above: the inverses are then not trusted)
+  if (args_.gmode == 1) ginv_valid_[fosystem_] = true;
   if (!compact) cstate_valid_ = false;   // the public rows moved on without the compact copy
   if (!partial) timeshift_ += slab_.dt;  // twavetents.cpp:173
 }
@@ -1331,6 +1360,7 @@ void Solver::InitP2P() {
   const double nfail = comm_->AllReduceSum(all_ok ? (double)failed : 1.0, d_scalar_, stream_);
   if (nfail != 0.0) {
     for (void* b : ipc_opened_) cudaIpcCloseMemHandle(b);
+  for (double* p : d_ginv_) if (p) cudaFree(p);
     ipc_opened_.clear();
     if (p2p_note_.empty()) p2p_note_ = all_ok ? "another rank could not map the peer buffers" : "not every rank can use the compact state";
     // keep the fixed-capacity buffers (harmless); the per-level NCCL exchange is used

@@ -109,8 +109,18 @@ class Solver {
   bool peer_exchange_active() const { return p2p_ready_ && p2p_enabled_ && UseCompact() && !qt_; }
   const std::string& peer_exchange_note() const { return p2p_note_; }
   // 0 = not in use, 1 = the next Propagate assembles, inverts and stores, 2 = the next Propagate applies stored inverses
-  int factor_cache_state() const { return !(UseCompact() && factor_cache_enabled_ && !cache_failed_) ? 0 : (ainv_valid_[fosystem_] ? 2 : 1); }
-  size_t factor_cache_bytes() const { return ainv_bytes_[0] + ainv_bytes_[1]; }
+  int factor_cache_state() const {
+    if (UseCompact() && factor_cache_enabled_ && !cache_failed_) return ainv_valid_[fosystem_] ? 2 : 1;
+    if (GenericCachePossible()) return ginv_valid_[fosystem_] ? 2 : 1;
+    return 0;
+  }
+  size_t factor_cache_bytes() const { return ainv_bytes_[0] + ainv_bytes_[1] + ginv_bytes_[0] + ginv_bytes_[1]; }
+  // the generic kernel keeps inverses of systems up to 32 unknowns (D = 1 up to order 7 with two wavespeed regions), when
+  // every tent of the solver runs on it
+  bool GenericCachePossible() const {
+    return factor_cache_enabled_ && !ginv_failed_ && !qt_ && have_initial_ && (force_generic_ || !fast_) &&
+           args_.max_ndom * args_.Npad <= 32 && threads_ >= args_.max_ndom * args_.Npad;
+  }
   double last_ms() const { return last_ms_; }
   int last_launches() const { return last_launches_; }
 
@@ -236,6 +246,11 @@ class Solver {
   size_t state_capacity_ = 0, cstate_capacity_ = 0;  // p2p: buffers allocated once for the largest system (IPC handles stay valid)
   void InitP2P();
   std::string p2p_note_;
+  // factor cache of the generic kernel (small systems only: 1-D, low orders, material-interface tents of such solvers)
+  double* d_ginv_[2] = {nullptr, nullptr};  // [fosystem]
+  size_t ginv_bytes_[2] = {0, 0};
+  bool ginv_valid_[2] = {false, false}, ginv_failed_ = false;
+  size_t smem_build_ = 0;                   // shared memory of the generic kernel while it forms the inverses
   bool factor_cache_enabled_ = true, cache_failed_ = false;
   double* d_ainv_[2] = {nullptr, nullptr};  // [fosystem]
   size_t ainv_bytes_[2] = {0, 0};

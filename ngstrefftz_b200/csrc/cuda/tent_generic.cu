@@ -15,7 +15,7 @@ namespace ngst {
 namespace {
 
 struct Smem {
-  double *A, *b, *E0, *E1, *Y, *rr, *pw, *mono, *pt;
+  double *A, *b, *E0, *E1, *Y, *rr, *pw, *mono, *pt, *Inv;
 };
 
 template <int D>
@@ -33,6 +33,7 @@ __device__ __forceinline__ Smem carve(double* base, const TentKernelArgs& a) {
   s.pw = s.rr + nv * a.Qc;
   s.mono = s.pw + a.Qc * d1 * (a.order + 1);
   s.pt = s.mono + a.Qc * nv * a.npoly;
+  s.Inv = s.pt + a.Qc * d1;  // (max_ndom * Npad)^2 doubles, only when the factor cache is being built (gmode 1)
   return s;
 }
 
@@ -145,19 +146,23 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
   const int n = nd * Np;
   const int fo = a.fosystem;
   const int vlo_val = fo ? 1 : 0;
+  // factor cache: the tent matrix does not depend on the state. apply = only right-hand side, stored inverse, evaluation
+  const bool apply = a.gmode == 2;
 
   double ctr[d1];
 #pragma unroll
   for (int d = 0; d < d1; d++) ctr[d] = a.center[(size_t)tent * d1 + d];
   const double sc = a.scale[tent];
 
-  for (int idx = tid; idx < n * n; idx += nth) s.A[idx] = 0.0;
+  if (!apply)
+    for (int idx = tid; idx < n * n; idx += nth) s.A[idx] = 0.0;
   for (int idx = tid; idx < n; idx += nth) s.b[idx] = 0.0;
   __syncthreads();
 
   // ------------------------------------------------------------------ time-like faces
   for (int tf = a.tf_off[tent]; tf < a.tf_off[tent + 1]; tf++) {
     const int kind = a.tf_kind[tf];
+    if (apply && kind == 2) continue;  // material interfaces contribute to the matrix only
     const double* V = a.tf_verts + (size_t)tf * d1 * d1;
     double nrm[D];
 #pragma unroll
@@ -197,7 +202,7 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
         }
         __syncthreads();
         double* Asub = s.A + (size_t)(din * Np) * n + din * Np;
-        gram(Asub, n, s.E0, s.Y, 1 + D, 2 + D, nq, Qc, Np);
+        if (!apply) gram(Asub, n, s.E0, s.Y, 1 + D, 2 + D, nq, Qc, Np);
         gemv(s.b + din * Np, s.E0, s.rr, 1, nv, nq, Qc, Np, N);
         __syncthreads();
       } else if (kind == 1) {  // Neumann, twavetents.cpp:380-403
@@ -225,7 +230,7 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
         }
         __syncthreads();
         double* Asub = s.A + (size_t)(din * Np) * n + din * Np;
-        gram(Asub, n, s.E0, s.Y, 1, nv, nq, Qc, Np);
+        if (!apply) gram(Asub, n, s.E0, s.Y, 1, nv, nq, Qc, Np);
         gemv(s.b + din * Np, s.E0, s.rr, 1, nv, nq, Qc, Np, N);
         __syncthreads();
       } else {  // material interface, twavetents.cpp:436-539
@@ -273,7 +278,7 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
     }
     for (int q0 = 0; q0 < Q; q0 += Qc) {
       const int nq = min(Qc, Q - q0);
-      for (int side = 0; side < 2; side++) {
+      for (int side = 0; side < (apply ? 1 : 2); side++) {  // top faces contribute to the matrix only
         const double* tau = (side == 0 ? a.te_tbot : a.te_ttop) + (size_t)te * d1;
         const double* nn = geo + side * (d1 + 1);
         const double area = nn[d1];
@@ -301,14 +306,14 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
             s.rr[(1 + D) * Qc + q] = -rt;
             if (!fo) s.rr[q] = om * wf[q0 + q];
           }
-          if (!fo)
+          if (!fo && !apply)
             for (int idx = tid; idx < nq * Np; idx += nth) {
               const int q = idx / Np;
               s.Y[idx] = a.w[q0 + q] * area * s.E0[idx];
             }
           __syncthreads();
           gemv(bsub, s.E0, s.rr, vlo_val, nv, nq, Qc, Np, N);
-          if (!fo) gram(Asub, n, s.E0, s.Y, 0, 1, nq, Qc, Np);
+          if (!fo && !apply) gram(Asub, n, s.E0, s.Y, 0, 1, nq, Qc, Np);
           __syncthreads();
         } else {
           eval_basis<D>(a, s, nq, ctr, sc, c, 1, s.E0);
@@ -333,12 +338,14 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
     }
   }
 
-  // ------------------------------------------------------------------ Solve (LU with partial pivoting)
+  // ------------------------------------------------------------------ Solve
+  __shared__ int piv_row;
+  __shared__ double piv_inv;
+  if (a.gmode == 0) {
+  // LU with partial pivoting
   for (int g = 0; g < nd; g++)
     for (int i = N + tid; i < Np; i += nth) s.A[(size_t)(g * Np + i) * n + g * Np + i] = 1.0;
   __syncthreads();
-  __shared__ int piv_row;
-  __shared__ double piv_inv;
   for (int k = 0; k < n; k++) {
     if (tid < 32) {
       double best = -1.0;
@@ -394,6 +401,73 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
     __syncthreads();
   }
 
+  } else {
+    // factor cache. The inverse is kept transposed: invT[j * n + i] = (A^-1)[i][j] (consecutive threads read consecutive
+    // doubles in the product). Stride n = nd * Npad of THIS tent inside its slot of (max_ndom * Npad)^2 doubles.
+    double* const invT = a.ginv + (size_t)tent * ((size_t)a.max_ndom * Np) * ((size_t)a.max_ndom * Np);
+    if (a.gmode == 1) {
+      // Gauss-Jordan with partial pivoting on [A | I] (the reference forms the inverse as well, twavetents.cpp:64-70)
+      for (int g = 0; g < nd; g++)
+        for (int i = N + tid; i < Np; i += nth) s.A[(size_t)(g * Np + i) * n + g * Np + i] = 1.0;
+      for (int idx = tid; idx < n * n; idx += nth) s.Inv[idx] = (idx / n == idx % n) ? 1.0 : 0.0;
+      __syncthreads();
+      for (int k = 0; k < n; k++) {
+        if (tid < 32) {
+          double best = -1.0;
+          int brow = k;
+          for (int r = k + tid; r < n; r += 32) {
+            const double v = fabs(s.A[(size_t)r * n + k]);
+            if (v > best) { best = v; brow = r; }
+          }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            const double ob = __shfl_down_sync(0xffffffffu, best, o);
+            const int orow = __shfl_down_sync(0xffffffffu, brow, o);
+            if (ob > best || (ob == best && orow < brow)) { best = ob; brow = orow; }
+          }
+          if (tid == 0) {
+            piv_row = brow;
+            if (!(best > 0.0) || !isfinite(best)) { atomicAdd(a.singular, 1); piv_inv = 0.0; }
+            else piv_inv = 1.0 / s.A[(size_t)brow * n + k];
+          }
+        }
+        __syncthreads();
+        const int p = piv_row;
+        const double pinv = piv_inv;
+        // swap rows k and p and scale the pivot row, in A and in the inverse
+        for (int cidx = tid; cidx < 2 * n; cidx += nth) {
+          double* M = cidx < n ? s.A : s.Inv;
+          const int cc = cidx < n ? cidx : cidx - n;
+          const double vk = M[(size_t)k * n + cc], vp = M[(size_t)p * n + cc];
+          M[(size_t)p * n + cc] = vk;
+          M[(size_t)k * n + cc] = vp * pinv;
+        }
+        __syncthreads();
+        // eliminate column k from every other row (the multipliers are read before anybody overwrites column k)
+        for (int idx = tid; idx < n * 2 * n; idx += nth) {
+          const int r = idx / (2 * n), cidx = idx % (2 * n);
+          if (r == k) continue;
+          const double m = s.A[(size_t)r * n + k];
+          if (cidx < n) { if (cidx != k) s.A[(size_t)r * n + cidx] -= m * s.A[(size_t)k * n + cidx]; }
+          else s.Inv[(size_t)r * n + cidx - n] -= m * s.Inv[(size_t)k * n + cidx - n];
+        }
+        __syncthreads();
+        for (int r = tid; r < n; r += nth)
+          if (r != k) s.A[(size_t)r * n + k] = 0.0;
+        __syncthreads();
+      }
+      for (int idx = tid; idx < n * n; idx += nth) invT[(size_t)(idx % n) * n + idx / n] = s.Inv[idx];
+      __syncthreads();  // this CTA's stores are visible to its own threads
+    }
+    // sol = A^-1 b (identical arithmetic when building and when applying the cache)
+    double acc = 0.0;
+    if (tid < n)
+      for (int j = 0; j < n; j++) acc = fma(__ldcg(invT + (size_t)j * n + tid), s.b[j], acc);
+    __syncthreads();
+    if (tid < n) s.b[tid] = acc;
+    __syncthreads();
+  }
+
   // ------------------------------------------------------------------ CalcTentElEval
   const int lane = tid & 31, wid = tid >> 5, nw = nth >> 5;
   for (int te = a.te_off[tent]; te < a.te_off[tent + 1]; te++) {
@@ -445,6 +519,7 @@ size_t tent_generic_smem_bytes(int D, const TentKernelArgs& a) {
   const size_t esz = (size_t)nv * a.Qc * a.Npad;
   size_t doubles = nmax * nmax + nmax + 3 * esz + (size_t)nv * a.Qc + (size_t)a.Qc * d1 * (a.order + 1) +
                    (size_t)a.Qc * nv * a.npoly + (size_t)a.Qc * d1;
+  if (a.gmode == 1) doubles += nmax * nmax;  // [A | I] while the inverses are formed
   return doubles * sizeof(double);
 }
 

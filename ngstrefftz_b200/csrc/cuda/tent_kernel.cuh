@@ -43,6 +43,11 @@ struct TentKernelArgs {
   int max_ndom;
   int* singular;           // incremented when a zero pivot is met
   int* stuck;              // incremented when a tent of the dependency-driven launch gives up waiting (its writes are skipped)
+  // ---- factor cache of the generic kernel (tent_generic.cu): gmode 0 = assemble and solve, 1 = assemble, invert
+  // (Gauss-Jordan on [A | I] in shared memory), store the inverse in ginv and apply it, 2 = right-hand side + stored inverse +
+  // evaluation. ginv: per staged tent (max_ndom * Npad)^2 doubles, the inverse transposed.
+  double* ginv;
+  int gmode;
   // ---- dependency-driven scheduling (tent_fast.cu, single GPU): one launch per slab; CTAs draw tents from `tents` in
   // order through `ticket` and wait until remaining[tent] (unfinished predecessors) is zero; a finished tent decrements
   // the counters of its successors. ticket == nullptr: `tents` is one level, CTA b solves tents[b].

@@ -1,0 +1,79 @@
+"""Factor cache of the generic kernel (tent_generic.cu gmode 1 / 2): solvers whose tents all run on the generic kernel with
+systems of up to 32 unknowns -- 1-D meshes, incl. the material-interface (macro-element) tents of BASELINE configs[1] --
+keep the inverse of every tent matrix after the first Propagate and afterwards only build right-hand sides, apply the
+stored inverse and evaluate."""
+import numpy as np
+import pytest
+
+import ngstrefftz_b200 as ng
+from _cases import dirichlet, first_order, gaussian_1d, neumann, standing
+from _oracle import Oracle
+from test_gpu_parity import forced_tol
+
+pytestmark = pytest.mark.gpu
+
+
+def pc(x):
+    return np.where((np.floor(x[:, 0] * 4).astype(int) % 2) == 0, 1.0, 2.0)
+
+
+CASES = {
+    "1d_p4": (lambda: ng.SegMesh(32, 0, 1), 4, 1.0, 0.3, standing(1), dirichlet(standing(1), 1), False),
+    "1d_p6_piecewise": (lambda: ng.SegMesh(64, 0, 1), 6, pc, 0.2, gaussian_1d, lambda x, t: 0 * t, False),
+    "1d_p4_neumann": (lambda: ng.SegMesh(24, 0, 1), 4, 1.0, 0.3, standing(1), neumann(standing(1), 1), True),
+    "1d_p5_fo": (lambda: ng.SegMesh(24, 0, 1), 5, 1.0, 0.3, first_order(standing(1)), dirichlet(standing(1), 1), False),
+}
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_generic_factor_cache(built, name):
+    mk, order, c, dt, init, bnd, neu = CASES[name]
+
+    def mesh():
+        m = mk()
+        if neu:
+            m.SetBoundaryNames("neumann")
+        return m
+
+    nslabs = 3
+    m0 = mesh()
+    ts = ng.TentSlab(m0, "edge")
+    ts.SetMaxWavespeed(c)
+    assert ts.PitchTents(dt, True, 2 / 3)
+    out = {}
+    for cache in (True, False):
+        tw = ng.TWave(order, ts, c)
+        tw.set_factor_cache(cache)
+        tw.SetInitial(init)
+        tw.SetBoundaryCF(bnd)
+        assert tw.kernel_name() == "tent_kernel_generic"
+        states = [tw.factor_cache()[0]]
+        for _ in range(nslabs):
+            tw.Propagate()
+            states.append(tw.factor_cache()[0])
+        out[cache] = tw.GetWavefront()
+        assert states == ([1, 2, 2, 2] if cache else [0, 0, 0, 0])
+        if cache:
+            assert tw.factor_cache()[1] > 0
+            tw.reset_time()
+            tw.SetInitial(init)
+            tw.Propagate()           # applies the stored inverses
+            again = tw.GetWavefront()
+            tw2 = ng.TWave(order, ts, c)
+            tw2.SetInitial(init)
+            tw2.SetBoundaryCF(bnd)
+            tw2.Propagate()          # builds them
+            assert np.array_equal(again, tw2.GetWavefront())
+    o = Oracle(mesh())
+    assert o.pitch(dt, True, 2 / 3, c(o.centroids) if callable(c) else c)
+    o.setup(order, c)
+    o.set_initial(init)
+    o.set_boundary_cf(bnd)
+    for _ in range(nslabs):
+        o.propagate()
+    ref = o.wavefront()
+    tol = forced_tol(o, name)
+    d = np.abs(out[True] - out[False]).max() / np.abs(out[False]).max()
+    rel = np.abs(out[True] - ref).max() / np.abs(ref).max()
+    print(f"{name}: stored inverse vs LU every step {d:.3e}, vs oracle {rel:.3e} (tolerance {tol:.1e})")
+    assert d <= tol and rel <= tol
