@@ -246,6 +246,8 @@ int ngst_twave_get_wavefront(ngst_twave* t, double* out);
 int ngst_twave_set_output_mirror(ngst_twave* t, double* host);
 /* number of copy CTAs the output mirror keeps in flight (default 24, the best of 12 / 24 / 48 measured on B200) */
 int ngst_twave_set_mirror_ctas(ngst_twave* t, int ctas);
+/* number of CTAs that fetch the rows of a streamed input (ngst_twave_set_initial_streamed) over PCIe (default 32) */
+int ngst_twave_set_fetch_ctas(ngst_twave* t, int ctas);
 /* GetWave src/__init__.py:7-43 (per-element L2 projection of the quadrature-point state, IntegrationPointFunction
  * src/specialcoefficientfunction.cpp:48-172): second-order state -> u onto polynomials of degree p (1 component),
  * first-order state -> (grad u, d_t u) onto degree p-1 (D+1 components). The basis is orthonormal on the reference

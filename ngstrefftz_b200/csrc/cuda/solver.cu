@@ -672,7 +672,7 @@ void Solver::SetInitialStreamed(const double* wf, int ncomp) {
     const int r0 = firstuse_off_[b], nr = firstuse_off_[b + 1] - r0;
     if (nr > 0) {
       // 32 CTAs x 16 KB in flight keep PCIe busy; each takes the place of one tent CTA while it waits for the bus
-      CU(launch_fetch_rows(d_firstuse_rows_ + r0, nr, rowlen, static_cast<const double*>(alias), d_wavefront_, 32, stream_load_));
+      CU(launch_fetch_rows(d_firstuse_rows_ + r0, nr, rowlen, static_cast<const double*>(alias), d_wavefront_, fetch_ctas_, stream_load_));
       if (compact)
         CU(launch_transfer_rows((long long)nr * ncomp_, rule_.nip, cs_points_, d_transfer_, d_wavefront_, d_cstate_, stream_load_,
                                 d_firstuse_rows_ + r0, ncomp_));

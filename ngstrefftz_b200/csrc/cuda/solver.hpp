@@ -96,6 +96,7 @@ class Solver {
   // single launch forced (default: only for slabs with small levels, where launches and level tails dominate)
   void set_kernel_mode(int mode) { force_generic_ = mode == 1; overlap_ = mode != 2; dag_mode_ = mode == 2 ? 0 : (mode == 3 ? 2 : 1); }
   void set_mirror_ctas(int n) { mirror_ctas_ = n; }
+  void set_fetch_ctas(int n) { fetch_ctas_ = n; }
   // Compact state (tent_fast.cu, CS = 1; default on): slabs whose tents all run on the fast kernel keep an internal copy of
   // the state on the compact degree-2p rule that the tents read and write; off = the tents work on the public rows (A/B).
   void set_compact_state(bool on) { compact_enabled_ = on; }
@@ -261,6 +262,7 @@ class Solver {
   int* d_singular_ = nullptr;      // device words: [0] singular pivot steps, [1] dependency time-outs
   int* h_flags_ = nullptr;         // their page-locked host copy, refreshed by every Propagate
   int mirror_ctas_ = 24;
+  int fetch_ctas_ = 32;            // CTAs of the streamed input
   int* d_rowptr_[2] = {nullptr, nullptr};  // [fosystem]
   int* d_col_[2] = {nullptr, nullptr};
   double* d_val_[2] = {nullptr, nullptr};

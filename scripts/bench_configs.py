@@ -75,7 +75,8 @@ def run_config(idx, slabs=2, scale=1.0):
         tw.Propagate()
         ms.append(tw.last_ms())
         en.append(tw.Energy())
-    best = min(ms)
+    best = min(ms)  # with the factor cache: a slab that applies the stored inverses (ms[0] forms them)
+    cache_state, cache_bytes = tw.factor_cache()
     ex = ts.export()
     ndof = int(tw.nbasis) * int(ts.GetNTents())
     out = {
@@ -84,6 +85,7 @@ def run_config(idx, slabs=2, scale=1.0):
         "nbasis": int(tw.nbasis), "nip": int(tw.nip), "kernel": tw.kernel_name(), "launches": int(tw.last_launches()),
         "pitch_s": t_pitch, "stage_s": t_stage, "ms_per_slab": ms, "tents_per_s": ts.GetNTents() / (best * 1e-3),
         "dof_updates_per_s_single_domain": ndof / (best * 1e-3), "energy": en,
+        "factor_cache": {"state": cache_state, "bytes": cache_bytes, "ms_first_slab": ms[0]},
     }
     if exact is not None:
         wf = tw.GetWavefront()
