@@ -56,7 +56,7 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-mirror", action="store_true", help="e2e arm: explicit get_wavefront copy instead of the output mirror")
     ap.add_argument("--no-streamed-input", action="store_true",
-                    help="e2e arm: blocking ngst_twave_set_initial instead of ngst_twave_set_initial_streamed")
+                    help="e2e arm: blocking ngst_twave_set_initial instead of ngst_twave_set_initial_streamed (spatial sweep)")
     ap.add_argument("--no-device-data", action="store_true", help="skip the informational device-sampled-data arm")
     ap.add_argument("--partition", default="balanced", choices=["balanced", "brick"],
                     help="N>1: cost-balanced recursive bisection (default) or plain brick cut of the bounding box")
@@ -414,11 +414,14 @@ def run_ours(args):
             mirror = use_mirror if mirror is None else mirror
             stream = use_stream if stream is None else stream
             tw.reset_time()
-            if stream:   # H2D of the state rows in first-use order, overlapped with the first tent levels
+            if stream:
+                # boundary samples first (blocking H2D), then the state rows: the copy engine delivers them in chunks while
+                # propagate sweeps through the slab behind the copies (and, with the mirror, copies finished chunks out)
+                check(lib.ngst_twave_set_boundary_values(tw._h, b_ptr, nb))
                 check(lib.ngst_twave_set_initial_streamed(tw._h, in_ptr, ncomp))
             else:
                 check(lib.ngst_twave_set_initial(tw._h, in_ptr, ncomp))           # H2D: state rows
-            check(lib.ngst_twave_set_boundary_values(tw._h, b_ptr, nb))            # H2D: boundary samples
+                check(lib.ngst_twave_set_boundary_values(tw._h, b_ptr, nb))        # H2D: boundary samples
             check(lib.ngst_twave_propagate(tw._h))                                 # (+ D2H of final rows with the mirror)
             if not mirror:
                 check(lib.ngst_twave_get_wavefront(tw._h, out_ptr))                # D2H: state rows

@@ -154,12 +154,15 @@ int ngst_twave_quadrature(const ngst_twave* t, double* x, double* weight);
 /* SetInitial src/twavetents.hpp:195-204: wf is nel x (ncomp*nip), row = [comp][q]; ncomp == D+2 second-order
  * input (u, grad u, dt u), ncomp == D+1 first-order input (switches to fosystem, nbasis-1). Host pointer. */
 int ngst_twave_set_initial(ngst_twave* t, const double* wf, int ncomp);
-/* Streamed form of ngst_twave_set_initial (no reference counterpart): returns at once; the device fetches the rows of `wf`
- * over PCIe in the order in which the tent levels first need them (half of the rows of a slab are first read by level 0,
- * the rest level by level), transfers each batch to the compact state, and every level of the NEXT ngst_twave_propagate
- * waits for its own rows only, so that most of the host-to-device copy overlaps the tents. `wf` must be page-locked
- * (pageable memory is page-locked and mapped by the call) and must stay unchanged until that propagate has returned;
- * any other call that reads the state waits for the whole input first. */
+/* Streamed form of ngst_twave_set_initial (no reference counterpart): returns at once. The copy engine delivers `wf` in
+ * chunks of consecutive elements (~16 MB) while the NEXT ngst_twave_propagate runs as a spatial sweep: one dependency-driven
+ * launch whose tents are ticketed in the order in which their dependency cones are complete -- a tent waits for its
+ * predecessors and for the chunk of rows it is the first to read, whose compact form it builds on the fly. With an output
+ * mirror (ngst_twave_set_output_mirror) the same propagate copies every chunk out as soon as the last tent of its elements
+ * is done, so that host-to-device copy, tents and device-to-host copy overlap along the sweep. `wf` must be page-locked
+ * (pageable memory is page-locked by the call) and stay unchanged until that propagate has returned; any other call that
+ * reads the state waits for the whole input first. Single GPU, every tent on the fast kernel with the compact state;
+ * otherwise the call is ngst_twave_set_initial. The result is bitwise that of ngst_twave_set_initial + propagate. */
 int ngst_twave_set_initial_streamed(ngst_twave* t, const double* wf, int ncomp);
 /* Boundary datum (SetBoundaryCF src/twavetents.hpp:206-209, evaluated at src/twavetents.cpp:373-407):
  * number of sample points and their (x, t_local) coordinates, npoints*(D+1); the datum must be evaluated at
@@ -246,8 +249,6 @@ int ngst_twave_get_wavefront(ngst_twave* t, double* out);
 int ngst_twave_set_output_mirror(ngst_twave* t, double* host);
 /* number of copy CTAs the output mirror keeps in flight (default 24, the best of 12 / 24 / 48 measured on B200) */
 int ngst_twave_set_mirror_ctas(ngst_twave* t, int ctas);
-/* number of CTAs that fetch the rows of a streamed input (ngst_twave_set_initial_streamed) over PCIe (default 32) */
-int ngst_twave_set_fetch_ctas(ngst_twave* t, int ctas);
 /* GetWave src/__init__.py:7-43 (per-element L2 projection of the quadrature-point state, IntegrationPointFunction
  * src/specialcoefficientfunction.cpp:48-172): second-order state -> u onto polynomials of degree p (1 component),
  * first-order state -> (grad u, d_t u) onto degree p-1 (D+1 components). The basis is orthonormal on the reference

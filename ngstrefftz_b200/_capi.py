@@ -85,7 +85,6 @@ _SIGS = {
     "ngst_twave_set_boundary_analytic": (C.c_int, [c_vp, C.c_int, c_dp, C.c_int]),
     "ngst_twave_set_output_mirror": (C.c_int, [c_vp, c_dp]),
     "ngst_twave_set_mirror_ctas": (C.c_int, [c_vp, C.c_int]),
-    "ngst_twave_set_fetch_ctas": (C.c_int, [c_vp, C.c_int]),
     "ngst_twave_error_analytic": (C.c_int, [c_vp, C.c_int, c_dp, C.c_int, C.c_double, C.c_int, C.POINTER(C.c_double)]),
     "ngst_twave_propagate": (C.c_int, [c_vp]),
     "ngst_twave_propagate_levels": (C.c_int, [c_vp, C.c_int]),

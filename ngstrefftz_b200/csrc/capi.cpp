@@ -496,14 +496,6 @@ int ngst_twave_peer_exchange(const ngst_twave* t, char* note, int note_len) {
   return t->solver->peer_exchange_active() ? 1 : 0;
 }
 
-int ngst_twave_set_fetch_ctas(ngst_twave* t, int ctas) {
-  return guarded([&] {
-    need(t, "solver");
-    if (ctas < 1 || ctas > 4096) throw std::invalid_argument("ngst_twave_set_fetch_ctas: ctas must be in 1..4096");
-    t->solver->set_fetch_ctas(ctas);
-  });
-}
-
 int ngst_twave_set_mirror_ctas(ngst_twave* t, int ctas) {
   return guarded([&] {
     need(t, "solver");

@@ -42,42 +42,7 @@ __global__ void __launch_bounds__(kMirrorThreads) mirror_rows_kernel(const int* 
   }
 }
 
-// The reverse direction (streamed input, solver.cu SetInitialStreamed): rows of the caller's mapped, page-locked buffer are
-// fetched over PCIe in the order in which the tents first need them.
-__global__ void __launch_bounds__(kMirrorThreads) fetch_rows_kernel(const int* __restrict__ rows, int nrows, int rowlen,
-                                                                    const double* __restrict__ host,
-                                                                    double* __restrict__ wf) {
-  const long long total = (long long)nrows * rowlen;
-  constexpr int kTile = kMirrorThreads * kMirrorUnroll;
-  for (long long base = (long long)blockIdx.x * kTile; base < total; base += (long long)gridDim.x * kTile) {
-    double v[kMirrorUnroll];
-    size_t off[kMirrorUnroll];
-#pragma unroll
-    for (int u = 0; u < kMirrorUnroll; u++) {
-      const long long idx = base + u * kMirrorThreads + threadIdx.x;
-      if (idx < total) {
-        const int r = (int)(idx / rowlen);
-        off[u] = (size_t)rows[r] * rowlen + (size_t)(idx - (long long)r * rowlen);
-        v[u] = __ldcs(host + off[u]);  // host memory, read once
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < kMirrorUnroll; u++) {
-      const long long idx = base + u * kMirrorThreads + threadIdx.x;
-      if (idx < total) wf[off[u]] = v[u];
-    }
-  }
-}
 }  // namespace
-
-cudaError_t launch_fetch_rows(const int* rows, int nrows, int rowlen, const double* host_alias, double* wf, int ctas,
-                              cudaStream_t stream) {
-  if (nrows <= 0) return cudaSuccess;
-  const long long tiles = ((long long)nrows * rowlen + kMirrorThreads * kMirrorUnroll - 1) / (kMirrorThreads * kMirrorUnroll);
-  const int grid = (int)(tiles < ctas ? tiles : ctas);
-  fetch_rows_kernel<<<grid, kMirrorThreads, 0, stream>>>(rows, nrows, rowlen, host_alias, wf);
-  return cudaGetLastError();
-}
 
 // ctas: how many CTAs stream rows out concurrently (each takes the place of one tent CTA while it runs)
 cudaError_t launch_mirror_rows(const int* rows, int nrows, int rowlen, const double* wf, double* host_alias, int ctas,

@@ -382,9 +382,10 @@ Solver::~Solver() {
   if (d_bnd_) cudaFree(d_bnd_);
   ReleaseMirror();
   ReleaseLoadBuffer();
-  if (stream_load_) { cudaStreamSynchronize(stream_load_); cudaStreamDestroy(stream_load_); }
-  if (ev_load_start_) cudaEventDestroy(ev_load_start_);
-  for (cudaEvent_t e : ev_load_) cudaEventDestroy(e);
+  for (cudaStream_t st : {stream_in_, stream_out_})
+    if (st) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
+  for (cudaEvent_t e : {ev_in_start_, ev_in_done_, ev_out_start_, ev_out_done_})
+    if (e) cudaEventDestroy(e);
   if (stream_mirror_) cudaStreamDestroy(stream_mirror_);
   if (ev_level_) cudaEventDestroy(ev_level_);
   if (ev_mirror_) cudaEventDestroy(ev_mirror_);
@@ -504,8 +505,9 @@ void Solver::ProjectCompact() {
     d_transfer_ = Upload(rule_transfer_matrix(rule_, rs, order_));
     transfer_points_ = cs_points_;
   }
-  // (nel * ncomp) contiguous rows of Q doubles times the transposed transfer matrix: a GEMM on the FP64 tensor path
-  CU(launch_transfer_rows((long long)nel_ * ncomp_, Q, cs_points_, d_transfer_, d_wavefront_, d_cstate_, stream_));
+  // (sums over the points in ascending order, as the tents of a spatial sweep do for the rows they are the first to read:
+  // both routes give the same bits)
+  CU(launch_project_rows(nel_, Q, cs_points_, 0, ncomp_, ncomp_ * Q, d_transfer_, d_wavefront_, d_cstate_, stream_));
   cstate_valid_ = true;
 }
 
@@ -516,8 +518,8 @@ void Solver::SetInitial(const double* wf, int ncomp) {
   if (qt_ && ncomp == D + 1)  // checked before any member changes: a failed call leaves the solver as it was
     throw std::invalid_argument("SetInitial: the quasi-Trefftz solver takes second-order initial data (D+2 components)");
   CU(cudaSetDevice(device_));
-  if (load_pending_) {  // a streamed input nobody consumed: its fetches still write into the buffers
-    CU(cudaStreamSynchronize(stream_load_));
+  if (load_pending_) {  // a streamed input nobody consumed: its copies still write into the buffers
+    CU(cudaStreamSynchronize(stream_in_));
     load_pending_ = false;
   }
   fosystem_ = (ncomp == D + 1) ? 1 : 0;  // twavetents.hpp:198-203
@@ -597,10 +599,33 @@ void Solver::SetInitial(const double* wf, int ncomp) {
   threads_ = tiles > 128 ? 256 : (tiles > 32 ? 128 : 64);
 }
 
+namespace {
+// stream memory operations of the driver API (no SM involved: they run on the front end of a stream)
+struct StreamMemOps {
+  using WriteFn = int (*)(cudaStream_t, unsigned long long, unsigned int, unsigned int);
+  using WaitFn = int (*)(cudaStream_t, unsigned long long, unsigned int, unsigned int);
+  WriteFn write = nullptr;
+  WaitFn wait = nullptr;
+  StreamMemOps() {
+    void* lib = dlopen("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) return;
+    write = reinterpret_cast<WriteFn>(dlsym(lib, "cuStreamWriteValue32_v2"));
+    wait = reinterpret_cast<WaitFn>(dlsym(lib, "cuStreamWaitValue32_v2"));
+    if (!write) write = reinterpret_cast<WriteFn>(dlsym(lib, "cuStreamWriteValue32"));
+    if (!wait) wait = reinterpret_cast<WaitFn>(dlsym(lib, "cuStreamWaitValue32"));
+  }
+  bool ok() const { return write && wait; }
+};
+StreamMemOps& memops() {
+  static StreamMemOps m;
+  return m;
+}
+}  // namespace
+
 void Solver::ReleaseLoadBuffer() {
   if (load_host_ && load_registered_) {
     cudaSetDevice(device_);
-    if (stream_load_) cudaStreamSynchronize(stream_load_);
+    if (stream_in_) cudaStreamSynchronize(stream_in_);
     cudaHostUnregister(const_cast<double*>(load_host_));
   }
   load_host_ = nullptr;
@@ -609,16 +634,78 @@ void Solver::ReleaseLoadBuffer() {
 
 void Solver::FinishLoad() {
   if (!load_pending_) return;
-  CU(cudaStreamWaitEvent(stream_, ev_load_.back(), 0));
+  CU(cudaStreamWaitEvent(stream_, ev_in_done_, 0));
   load_pending_ = false;
+}
+
+// Sweep tables (once per solver): chunks of consecutive elements, the ticket order, first-touch flags, per-chunk counts
+void Solver::BuildSweep() {
+  sweep_built_ = true;
+  sweep_possible_ = false;
+  if (!dag_ || !compact_possible_ || plan_ || !memops().ok()) return;
+  const int nt = staged_.ntents, Q = rule_.nip;
+  const size_t rowbytes = (size_t)(mesh_.D + 2) * Q * sizeof(double);
+  sweep_chunk_elems_ = (int)std::max<size_t>(256, (16u << 20) / rowbytes);  // ~16 MB per chunk
+  sweep_nchunks_ = (nel_ + sweep_chunk_elems_ - 1) / sweep_chunk_elems_;
+  std::vector<int> need(nt, 0), ready(nt, 0), ready_of_last(nel_, -1);
+  std::vector<unsigned char> first(std::max(staged_.nte, 1), 0), touched(nel_, 0);
+  for (int t = 0; t < nt; t++) {  // pitching order: predecessors first
+    int nd = 0, rd = 0;
+    for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++) {
+      const int el = staged_.te_el[te];
+      nd = std::max(nd, el / sweep_chunk_elems_);
+      rd = std::max(rd, ready_of_last[el]);
+      if (!touched[el]) { touched[el] = 1; first[te] = 1; }
+    }
+    need[t] = nd;
+    ready[t] = std::max(nd, rd);
+    for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++) ready_of_last[staged_.te_el[te]] = ready[t];
+  }
+  std::vector<int> order(nt);
+  for (int t = 0; t < nt; t++) order[t] = t;
+  // every predecessor has a smaller or equal `ready` and a smaller level: it draws an earlier ticket (no deadlock)
+  std::stable_sort(order.begin(), order.end(), [&](int x, int y) {
+    if (ready[x] != ready[y]) return ready[x] < ready[y];
+    return slab_.level[x] < slab_.level[y];
+  });
+  chunk_left_init_.assign(sweep_nchunks_, 0);
+  std::vector<int> untouched;
+  for (int el = 0; el < nel_; el++) {
+    if (touched[el]) chunk_left_init_[el / sweep_chunk_elems_]++;
+    else untouched.push_back(el);
+  }
+  sweep_untouched_ = (int)untouched.size();
+  d_sweep_tents_ = Upload(order);
+  d_tent_chunk_ = Upload(need);
+  d_te_first_ = Upload(first);
+  d_chunk_left_init_ = Upload(chunk_left_init_);
+  d_untouched_ = Upload(untouched);
+  CU(cudaMalloc(&d_chunk_loaded_, sizeof(int) * sweep_nchunks_));
+  allocs_.push_back(d_chunk_loaded_);
+  CU(cudaMalloc(&d_chunk_left_, sizeof(int) * sweep_nchunks_));
+  allocs_.push_back(d_chunk_left_);
+  int lo = 0, hi = 0;
+  CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+  CU(cudaStreamCreateWithPriority(&stream_in_, cudaStreamNonBlocking, hi));
+  CU(cudaStreamCreateWithPriority(&stream_out_, cudaStreamNonBlocking, hi));
+  for (cudaEvent_t* e : {&ev_in_start_, &ev_in_done_, &ev_out_start_, &ev_out_done_})
+    CU(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+  sweep_possible_ = true;
 }
 
 void Solver::SetInitialStreamed(const double* wf, int ncomp) {
   if (!wf) throw std::invalid_argument("SetInitialStreamed: null buffer");
-  FinishLoad();
-  SetInitial(nullptr, ncomp);  // validates, allocates, configures the kernels
-  const int nlev = (int)slab_.level_off.size() - 1;
-  const size_t bytes = (size_t)nel_ * ncomp_ * rule_.nip * sizeof(double);
+  CU(cudaSetDevice(device_));
+  if (!sweep_built_) BuildSweep();
+  const bool can = sweep_possible_ && compact_enabled_ && !force_generic_ &&
+                   tent_fast_stages_rows(mesh_.D, order_, ncomp == mesh_.D + 1 ? 1 : 0);
+  if (!can) {  // no sweep for this solver: the plain, blocking path
+    SetInitial(wf, ncomp);
+    return;
+  }
+  SetInitial(nullptr, ncomp);  // validates, allocates, configures the kernels (waits for an input nobody consumed)
+  const size_t rowlen = (size_t)ncomp_ * rule_.nip;
+  const size_t bytes = (size_t)nel_ * rowlen * sizeof(double);
   if (wf != load_host_) {
     ReleaseLoadBuffer();
     cudaPointerAttributes attr{};
@@ -627,59 +714,30 @@ void Solver::SetInitialStreamed(const double* wf, int ncomp) {
       attr.type = cudaMemoryTypeUnregistered;
     }
     if (attr.type == cudaMemoryTypeUnregistered) {
-      CU(cudaHostRegister(const_cast<double*>(wf), bytes, cudaHostRegisterMapped));
+      CU(cudaHostRegister(const_cast<double*>(wf), bytes, cudaHostRegisterDefault));  // asynchronous copies need page-locked memory
       load_registered_ = true;
     } else if (attr.type != cudaMemoryTypeHost) {
       throw std::invalid_argument("SetInitialStreamed: the buffer must be host memory");
     }
     load_host_ = wf;
   }
-  void* alias = nullptr;
-  CU(cudaHostGetDevicePointer(&alias, const_cast<double*>(wf), 0));
-  if (!stream_load_) {
-    int lo = 0, hi = 0;
-    CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-    CU(cudaStreamCreateWithPriority(&stream_load_, cudaStreamNonBlocking, hi));
-    CU(cudaEventCreateWithFlags(&ev_load_start_, cudaEventDisableTiming));
-    ev_load_.resize(nlev + 1);
-    for (cudaEvent_t& e : ev_load_) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    // level of the FIRST tent that contains each element (partitioned solvers: of this rank's tents -- rows only other
-    // ranks' tents touch are ghosts that nobody here reads before they are overwritten, they go last)
-    std::vector<int> first(nel_, nlev);
-    for (int t = 0; t < staged_.ntents; t++)
-      for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++) {
-        const int el = plan_ ? plan_->glob2loc[staged_.te_el[te]] : staged_.te_el[te];
-        first[el] = std::min(first[el], slab_.level[t]);
-      }
-    firstuse_off_.assign(nlev + 2, 0);
-    for (int el = 0; el < nel_; el++) firstuse_off_[first[el] + 1]++;
-    for (int i = 0; i <= nlev; i++) firstuse_off_[i + 1] += firstuse_off_[i];
-    std::vector<int> rows(nel_), pos(firstuse_off_.begin(), firstuse_off_.end() - 1);
-    for (int el = 0; el < nel_; el++) rows[pos[first[el]]++] = el;
-    d_firstuse_rows_ = Upload(rows);
-  }
-  const bool compact = cs_points_ > 0 && compact_enabled_;
-  if (compact && transfer_points_ != cs_points_) {
+  if (transfer_points_ != cs_points_) {
     const SimplexRule rs = make_compact_rule(mesh_.D, 2 * order_);
     d_transfer_ = Upload(rule_transfer_matrix(rule_, rs, order_));
     transfer_points_ = cs_points_;
   }
-  // everything the solver's stream still has to do with the old state comes first
-  CU(cudaEventRecord(ev_load_start_, stream_));
-  CU(cudaStreamWaitEvent(stream_load_, ev_load_start_, 0));
-  const int rowlen = ncomp_ * rule_.nip;
-  for (int b = 0; b <= nlev; b++) {
-    const int r0 = firstuse_off_[b], nr = firstuse_off_[b + 1] - r0;
-    if (nr > 0) {
-      // 32 CTAs x 16 KB in flight keep PCIe busy; each takes the place of one tent CTA while it waits for the bus
-      CU(launch_fetch_rows(d_firstuse_rows_ + r0, nr, rowlen, static_cast<const double*>(alias), d_wavefront_, fetch_ctas_, stream_load_));
-      if (compact)
-        CU(launch_transfer_rows((long long)nr * ncomp_, rule_.nip, cs_points_, d_transfer_, d_wavefront_, d_cstate_, stream_load_,
-                                d_firstuse_rows_ + r0, ncomp_));
-    }
-    CU(cudaEventRecord(ev_load_[b], stream_load_));
+  // flags down in the order of the solver's stream (behind whatever still uses the old state), then the chunk copies
+  CU(cudaMemsetAsync(d_chunk_loaded_, 0, sizeof(int) * sweep_nchunks_, stream_));
+  CU(cudaEventRecord(ev_in_start_, stream_));
+  CU(cudaStreamWaitEvent(stream_in_, ev_in_start_, 0));
+  for (int c = 0; c < sweep_nchunks_; c++) {
+    const size_t e0 = (size_t)c * sweep_chunk_elems_, ne = std::min<size_t>(sweep_chunk_elems_, nel_ - e0);
+    CU(cudaMemcpyAsync(d_wavefront_ + e0 * rowlen, wf + e0 * rowlen, ne * rowlen * sizeof(double), cudaMemcpyHostToDevice, stream_in_));
+    if (memops().write(stream_in_, (unsigned long long)(d_chunk_loaded_ + c), 1u, 0u) != 0)
+      throw CudaFailure("CUDA: cuStreamWriteValue32 failed");
   }
-  cstate_valid_ = compact;  // (in stream order: every consumer waits for the bucket events)
+  CU(cudaEventRecord(ev_in_done_, stream_in_));
+  cstate_valid_ = false;  // the tents of the sweep build the compact rows of everything they touch
   load_pending_ = true;
 }
 
@@ -776,18 +834,18 @@ void Solver::Propagate(int level_limit) {
   const bool partial = level_limit >= 0 && level_limit < nlev_all;
   const int nlev = partial ? level_limit : nlev_all;
   if (partial && plan_) throw std::logic_error("Propagate: partial slabs (propagate_levels) are for single-GPU solvers");
-  // streamed input (SetInitialStreamed): with one launch per level each level only waits for the rows it is the first to
-  // read; every other scheme waits for the whole input
-  const bool peer_ready = comm_ && p2p_ready_ && p2p_enabled_ && overlap_;
-  const bool stream_levels = load_pending_ && !qt_ && !force_generic_ && !partial && !peer_ready;
-  if (load_pending_ && !stream_levels) FinishLoad();
+  // streamed input (SetInitialStreamed): the spatial sweep below consumes the chunks as they land; anything else waits
+  // for the whole input
+  const bool sweep = load_pending_ && sweep_possible_ && compact_enabled_ && cs_points_ > 0 && !qt_ && !force_generic_ && !partial &&
+                     !comm_ && dag_mode_ != 0;
+  if (load_pending_ && !sweep) FinishLoad();
   // compact state: the fast kernel reads / writes d_cstate_ and writes the public rows of final elements only
   const bool compact = UseCompact() && !qt_;
   FastArgs fa = fargs_;
   fa.cstate = nullptr;
   fa.te_final = nullptr;
   if (compact) {
-    if (!cstate_valid_) ProjectCompact();
+    if (!cstate_valid_ && !load_pending_) ProjectCompact();
     fa.cstate = d_cstate_;
     fa.te_final = FinalFlags(partial ? level_limit : -1);
   }
@@ -795,6 +853,12 @@ void Solver::Propagate(int level_limit) {
   fa.ainv = nullptr;
   fa.mode = 0;
   fa.p2p = nullptr;
+  fa.tent_chunk = nullptr;
+  fa.chunk_loaded = nullptr;
+  fa.te_first = nullptr;
+  fa.transfer = nullptr;
+  fa.chunk_left = nullptr;
+  fa.chunk_elems = 1;
   const int fo = fosystem_;
   if (compact && factor_cache_enabled_ && !cache_failed_ && (ainv_valid_[fo] || !partial)) {
     if (!d_ainv_[fo]) {
@@ -847,7 +911,7 @@ void Solver::Propagate(int level_limit) {
                               args_.tf_verts, args_.tf_data, args_.lam, kNeumann, d_bnd_, stream_));
     launches++;
   }
-  if (mirror_dev_ && !stream_levels) MirrorRows(-1, -1, launches);  // rows no tent touches are final from the start
+  if (mirror_dev_ && !sweep) MirrorRows(-1, -1, launches);  // rows no tent touches are final from the start
   for (int l = 0; l < nlev && qt_; l++) {
     // quasi-Trefftz: fast monomial-space DMMA kernel where a variant exists (second-order form, causal top faces),
     // generic kernel otherwise
@@ -889,10 +953,57 @@ void Solver::Propagate(int level_limit) {
   const bool small_levels = slab_.ntents < 2 * 444 * nlev;
   // (r04d, B200: with stored inverses a tent is 6x cheaper and the single launch wins at config 4 as well, 11.74 vs 12.17 ms;
   // not with an output mirror, whose copies overlap the per-level launches)
-  const bool cheap_tents = fa.mode == 2 && !mirror_dev_ && !stream_levels;
+  const bool cheap_tents = fa.mode == 2 && !mirror_dev_;
   const bool dag = dag_ && (dag_mode_ == 2 || (dag_mode_ == 1 && (small_levels || cheap_tents))) && !force_generic_ && !comm_ && !partial &&
-                   !(stream_levels && dag_mode_ != 2);
-  if (dag && load_pending_) FinishLoad();
+                   !sweep;
+  if (sweep) {
+    // ---- spatial sweep: ONE dependency-driven launch whose tents are ticketed in the order in which their dependency cones
+    // are complete. A tent waits for its predecessors (hazard counters) and for the chunk of public rows it is the first
+    // to read (flag written by the copy engine's stream behind the chunk's copy); the first tent to touch an element builds
+    // its compact row on the fly. With an output mirror the last tent of an element counts its chunk down and the copy
+    // engine takes every finished chunk out (stream wait on the counter) while the sweep goes on.
+    const size_t rowlen = (size_t)ncomp_ * rule_.nip;
+    CU(cudaMemcpyAsync(d_remaining_, d_indeg_, sizeof(int) * slab_.ntents, cudaMemcpyDeviceToDevice, stream_));
+    CU(cudaMemsetAsync(d_ticket_, 0, sizeof(int), stream_));
+    const bool out = mirror_host_ != nullptr;
+    if (out) {
+      CU(cudaMemcpyAsync(d_chunk_left_, d_chunk_left_init_, sizeof(int) * sweep_nchunks_, cudaMemcpyDeviceToDevice, stream_));
+      CU(cudaEventRecord(ev_out_start_, stream_));
+      CU(cudaStreamWaitEvent(stream_out_, ev_out_start_, 0));
+    }
+    TentKernelArgs a = args_;
+    a.tents = d_sweep_tents_;
+    a.ntents = slab_.ntents;
+    a.ticket = d_ticket_;
+    a.remaining = d_remaining_;
+    a.succ_off = d_succ_off_;
+    a.succ = d_succ_;
+    fa.tent_chunk = d_tent_chunk_;
+    fa.chunk_loaded = d_chunk_loaded_;
+    fa.te_first = d_te_first_;
+    fa.transfer = d_transfer_;
+    fa.chunk_left = out ? d_chunk_left_ : nullptr;
+    fa.chunk_elems = sweep_chunk_elems_;
+    CU(launch_tent_fast(mesh_.D, order_, fosystem_, a, fa, stream_));
+    launches++;
+    if (out) {
+      for (int c = 0; c < sweep_nchunks_; c++) {
+        const size_t e0 = (size_t)c * sweep_chunk_elems_, ne = std::min<size_t>(sweep_chunk_elems_, nel_ - e0);
+        if (chunk_left_init_[c] == 0) CU(cudaStreamWaitEvent(stream_out_, ev_in_done_, 0));  // nobody touches it: plain copy of the input
+        else if (memops().wait(stream_out_, (unsigned long long)(d_chunk_left_ + c), 0u, 1u /* EQ */) != 0)
+          throw CudaFailure("CUDA: cuStreamWaitValue32 failed");
+        CU(cudaMemcpyAsync(mirror_host_ + e0 * rowlen, d_wavefront_ + e0 * rowlen, ne * rowlen * sizeof(double), cudaMemcpyDeviceToHost, stream_out_));
+      }
+      CU(cudaEventRecord(ev_out_done_, stream_out_));
+      CU(cudaStreamWaitEvent(stream_, ev_out_done_, 0));
+    }
+    CU(cudaStreamWaitEvent(stream_, ev_in_done_, 0));  // (chunks no tent reads)
+    load_pending_ = false;
+    if (sweep_untouched_ > 0)  // elements no tent touches: their compact rows by the ordinary transfer
+      CU(launch_project_rows(sweep_untouched_, rule_.nip, cs_points_, 0, ncomp_, ncomp_ * rule_.nip, d_transfer_, d_wavefront_, d_cstate_,
+                             stream_, d_untouched_));
+    cstate_valid_ = true;
+  }
   if (dag) {
     CU(cudaMemcpyAsync(d_remaining_, d_indeg_, sizeof(int) * slab_.ntents, cudaMemcpyDeviceToDevice, stream_));
     CU(cudaMemsetAsync(d_ticket_, 0, sizeof(int), stream_));
@@ -940,16 +1051,12 @@ void Solver::Propagate(int level_limit) {
     CU(cudaEventCreateWithFlags(&ev_int_, cudaEventDisableTiming));
   }
   if (overlap) CU(cudaEventRecord(ev_int_, stream_));
-  for (int l = 0; l < nlev && !force_generic_ && !qt_ && !dag && !p2p; l++) {
+  for (int l = 0; l < nlev && !force_generic_ && !qt_ && !dag && !p2p && !sweep; l++) {
     // level l: [halo tents | interior tents] of the fast and of the generic list. Single GPU: one launch per list.
     // Multi-GPU: halo tents + exchange on the high-priority stream, interior tents concurrently on the main stream;
     // level l+1 starts when both are done (tents of a level touch disjoint rows, received rows belong to no local tent
     // of the level).
     const int fh = overlap ? fast_nhalo_[l] : 0, gh = overlap ? gen_nhalo_[l] : 0;
-    if (load_pending_) {  // the rows this level is the first to read have landed (earlier buckets: in stream order)
-      CU(cudaStreamWaitEvent(stream_, ev_load_[l], 0));
-      if (overlap) CU(cudaStreamWaitEvent(stream_halo_, ev_load_[l], 0));
-    }
     if (overlap) {
       CU(cudaStreamWaitEvent(stream_halo_, ev_int_, 0));
       if (l > 0) {
@@ -987,10 +1094,6 @@ void Solver::Propagate(int level_limit) {
   if (overlap) {
     CU(cudaStreamWaitEvent(stream_, ev_halo_, 0));
     if (mirror_dev_ && nlev > 0 && !force_generic_ && !qt_ && !dag && !p2p) MirrorRows(nlev - 1, nlev - 1, launches);
-  }
-  if (load_pending_) {  // rows no tent of this rank reads: the input is complete when they have landed
-    FinishLoad();
-    if (mirror_dev_) MirrorRows(-1, -1, launches);
   }
   if (mirror_dev_) {  // the slab is done when the last rows have reached the host buffer
     CU(cudaEventRecord(ev_mirror_, stream_mirror_));

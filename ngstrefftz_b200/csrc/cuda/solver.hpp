@@ -58,10 +58,12 @@ class Solver {
 
   void Quadrature(double* x, double* weight) const;
   void SetInitial(const double* wf, int ncomp);
-  // Streamed input: as SetInitial, but returns at once; the rows are fetched from `wf` (page-locked by the call if it is
-  // pageable; must stay unchanged until the next Propagate has returned) by the device in the order in which the tent levels
-  // first need them, and every level of that Propagate only waits for its own rows.
+  // Streamed input: as SetInitial, but returns at once: the copy engine delivers `wf` (page-locked by the call if it is
+  // pageable; must stay unchanged until the next Propagate has returned) in chunks of consecutive elements while that
+  // Propagate runs its tents in the order in which their dependency cones are complete (and, with an output mirror, copies
+  // finished chunks out at the other end). Falls back to SetInitial where the sweep does not apply.
   void SetInitialStreamed(const double* wf, int ncomp);
+  bool sweep_active() const { return load_pending_ && sweep_built_; }
   void SetBoundaryValues(const double* values, long long n);
   // Analytic data sampled on the device (cuda/sample.hpp): SetInitial / MakeWavefront
   // (twavetents.cpp:734-764) and the boundary datum, re-sampled by every Propagate at t_local + timeshift
@@ -96,7 +98,6 @@ class Solver {
   // single launch forced (default: only for slabs with small levels, where launches and level tails dominate)
   void set_kernel_mode(int mode) { force_generic_ = mode == 1; overlap_ = mode != 2; dag_mode_ = mode == 2 ? 0 : (mode == 3 ? 2 : 1); }
   void set_mirror_ctas(int n) { mirror_ctas_ = n; }
-  void set_fetch_ctas(int n) { fetch_ctas_ = n; }
   // Compact state (tent_fast.cu, CS = 1; default on): slabs whose tents all run on the fast kernel keep an internal copy of
   // the state on the compact degree-2p rule that the tents read and write; off = the tents work on the public rows (A/B).
   void set_compact_state(bool on) { compact_enabled_ = on; }
@@ -207,15 +208,25 @@ class Solver {
   int proj_deg_ = -1, proj_ndof_ = 0;
   std::vector<double> proj_psi_, proj_mono_;
   std::vector<int> proj_expo_;
-  // ---- streamed input (SetInitialStreamed)
-  const double* load_host_ = nullptr;   // caller's buffer, registered by us if load_registered_
+  // ---- spatial sweep: streamed input and output (SetInitialStreamed; single GPU, every tent on the fast kernel, compact
+  // state). The copy engine delivers the public rows in chunks of consecutive elements and takes finished chunks out while
+  // ONE dependency-driven launch runs the tents in the order in which their dependency cones are complete.
+  const double* load_host_ = nullptr;   // caller's input buffer, page-locked by us if load_registered_
   bool load_registered_ = false;
-  bool load_pending_ = false;           // fetches are enqueued on stream_load_; ev_load_[b] = bucket b has landed
-  int* d_firstuse_rows_ = nullptr;      // local elements ordered by the level of the first tent that contains them
-  std::vector<int> firstuse_off_;       // nlev + 2 offsets: bucket l = first used in level l, bucket nlev = never used
-  cudaStream_t stream_load_ = nullptr;
-  cudaEvent_t ev_load_start_ = nullptr;
-  std::vector<cudaEvent_t> ev_load_;
+  bool load_pending_ = false;           // chunk copies are enqueued on stream_in_; ev_in_done_ = all have landed
+  bool sweep_built_ = false, sweep_possible_ = false;
+  int sweep_nchunks_ = 0, sweep_chunk_elems_ = 0, sweep_untouched_ = 0;
+  int* d_sweep_tents_ = nullptr;        // tents ordered by (last chunk their cone needs, level)
+  int* d_tent_chunk_ = nullptr;         // per tent: last chunk its own elements lie in
+  int* d_chunk_loaded_ = nullptr;       // per chunk: set by a stream memory operation behind the chunk's copy
+  int* d_chunk_left_ = nullptr;         // per chunk: touched elements not yet final (armed from d_chunk_left_init_)
+  int* d_chunk_left_init_ = nullptr;
+  std::vector<int> chunk_left_init_;
+  unsigned char* d_te_first_ = nullptr; // per tent-element: first tent of the slab to touch the element
+  int* d_untouched_ = nullptr;          // elements no tent touches (their compact rows are transferred separately)
+  cudaStream_t stream_in_ = nullptr, stream_out_ = nullptr;
+  cudaEvent_t ev_in_start_ = nullptr, ev_in_done_ = nullptr, ev_out_start_ = nullptr, ev_out_done_ = nullptr;
+  void BuildSweep();
   void FinishLoad();                    // the whole input has landed before the solver's stream goes on
   void ReleaseLoadBuffer();
   // ---- compact state
@@ -262,7 +273,6 @@ class Solver {
   int* d_singular_ = nullptr;      // device words: [0] singular pivot steps, [1] dependency time-outs
   int* h_flags_ = nullptr;         // their page-locked host copy, refreshed by every Propagate
   int mirror_ctas_ = 24;
-  int fetch_ctas_ = 32;            // CTAs of the streamed input
   int* d_rowptr_[2] = {nullptr, nullptr};  // [fosystem]
   int* d_col_[2] = {nullptr, nullptr};
   double* d_val_[2] = {nullptr, nullptr};
@@ -276,11 +286,7 @@ class Solver {
 size_t tent_generic_smem_bytes(int D, const TentKernelArgs& a);
 cudaError_t launch_tent_generic(int D, const TentKernelArgs& a, int threads, size_t smem, cudaStream_t stream);
 cudaError_t launch_project_rows(int nel, int Q, int ndof, int comp0, int ncomp_used, int rowlen, const double* P,
-                                const double* wf, double* out, cudaStream_t stream);
-cudaError_t launch_transfer_rows(long long nrows, int Q, int ndof, const double* P, const double* in, double* out,
-                                 cudaStream_t stream, const int* groups = nullptr, int per_group = 1);
-cudaError_t launch_fetch_rows(const int* rows, int nrows, int rowlen, const double* host_alias, double* wf, int ctas,
-                              cudaStream_t stream);
+                                const double* wf, double* out, cudaStream_t stream, const int* elems = nullptr);
 cudaError_t launch_mirror_rows(const int* rows, int nrows, int rowlen, const double* wf, double* host_alias, int ctas,
                                cudaStream_t stream);
 cudaError_t launch_element_reduce(int mode, int D, int nel, int Q, int ncomp, int fosystem, const double* elw,

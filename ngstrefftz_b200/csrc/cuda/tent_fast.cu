@@ -174,6 +174,14 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
         // not a singular system), skips its work and still releases its successors so that the launch drains quickly
         if (++spins > (1ll << 26)) { atomicAdd(a.stuck, 1); stuck = 1; break; }
       }
+      if (CS && f.tent_chunk && !stuck) {
+        // streamed input: the public rows this tent projects from have been delivered by the copy engine
+        volatile const int* ld = f.chunk_loaded + f.tent_chunk[t];
+        while (*ld == 0) {
+          __nanosleep(256);
+          if (++spins > (1ll << 26)) { atomicAdd(a.stuck, 1); stuck = 1; break; }
+        }
+      }
       if (f.p2p) __threadfence_system();  // rows and counters may have been written by another GPU
       else __threadfence();
       s_tent = t;
@@ -241,13 +249,38 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
     const int nb = STG ? min(kRowCap, nel - b0) : nel;
     if constexpr (STG) {
       constexpr unsigned kRowBytes = C::ROWLEN * 8;
+      const unsigned char* __restrict__ first = f.te_first;  // streamed input: rows without a compact copy yet
       if (w == 0) {
-        if (lane == 0) tma::mbar_expect(&s_bar_rows, nb * kRowBytes);
+        int nload = 0;
+        for (int e = lane; e < nb; e += 32) nload += !(first && first[te0 + b0 + e]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) nload += __shfl_xor_sync(0xffffffffu, nload, o);
+        if (lane == 0) tma::mbar_expect(&s_bar_rows, nload * kRowBytes);
         __syncwarp();
         for (int e = lane; e < nb; e += 32) {
+          if (first && first[te0 + b0 + e]) continue;
           if (a.ticket) tma::fence_proxy_async();  // rows written by other CTAs of this launch (dependency-driven order)
           tma::bulk_load(rowsS + e * C::ROWLEN, f.cstate + (size_t)a.te_el[te0 + b0 + e] * C::ROWLEN, kRowBytes, &s_bar_rows);
         }
+      }
+      if (first) {
+        // compact row = transfer (Qs x Q) times the public row, component by component (what SetInitial's GEMM does for the
+        // whole state; here only for the rows this tent is the first to read, straight from the delivered chunk)
+        bool any = false;
+        for (int e = 0; e < nb; e++) {
+          if (!first[te0 + b0 + e]) continue;
+          any = true;
+          const double* __restrict__ pub = a.wavefront + (size_t)a.te_el[te0 + b0 + e] * (NC * Q);
+          for (int idx = tid; idx < C::ROWLEN; idx += kThreads) {
+            const int cc = idx / QR, kq = idx % QR;
+            const double* __restrict__ m = f.transfer + (size_t)kq * Q;
+            const double* __restrict__ g = pub + cc * Q;
+            double acc = 0.0;
+            for (int q = 0; q < Q; q++) acc = fma(__ldg(m + q), __ldcg(g + q), acc);
+            rowsS[e * C::ROWLEN + idx] = acc;
+          }
+        }
+        if (any) __syncthreads();
       }
       tma::mbar_wait(&s_bar_rows, (b0 / kRowCap) & 1);
     }
@@ -765,6 +798,14 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
         if (f.te_final[te]) eval_point(te, a.lam + q * d1, a.wavefront + (size_t)a.te_el[te] * (NCW * Q), Q, q);
       }
     }
+    if (f.chunk_left) {
+      // streamed output: one element less to finish in its chunk; the copy engine takes a chunk out as soon as its count
+      // is zero (stream wait on the counter), so the rows must be visible system-wide first
+      __threadfence_system();
+      __syncthreads();
+      for (int e = tid; e < nel; e += kThreads)
+        if (f.te_final[te0 + e]) atomicSub(f.chunk_left + a.te_el[te0 + e] / f.chunk_elems, 1);
+    }
   } else {
     for (int idx = tid; idx < npts; idx += kThreads) {
       const int te = te0 + idx / Q, q = idx % Q;
@@ -870,6 +911,15 @@ int tent_fast_compact_points(int D, int order, int fosystem) {
   NGST_FAST_CONFIGS(X)
 #undef X
   return 0;
+}
+
+// whether the variant stages its compact rows through shared memory with bulk copies (needed by the spatial sweep)
+bool tent_fast_stages_rows(int D, int order, int fosystem) {
+#define X(d, p) \
+  if (D == d && order == p) return fosystem ? (Cfg<d, p, 1>::stageRows && Cfg<d, p, 1>::QS < Cfg<d, p, 1>::Q) : (Cfg<d, p, 0>::stageRows && Cfg<d, p, 0>::QS < Cfg<d, p, 0>::Q);
+  NGST_FAST_CONFIGS(X)
+#undef X
+  return false;
 }
 
 // doubles per tent of the stored inverse (NP x N), 0 without a fast variant

@@ -70,6 +70,16 @@ struct FastArgs {
   double* ainv;
   int mode;
   const P2PArgs* p2p;   // nullptr: single GPU, or the per-level NCCL exchange
+  // ---- spatial sweep (streamed input and output, single GPU, dependency-driven launch; solver.cu SetInitialStreamed):
+  // the copy engine delivers the public rows in chunks of consecutive elements while the kernel runs; tents are ticketed
+  // in the order in which their dependency cones are complete.
+  const int* tent_chunk;          // per tent: the last input chunk it (not its ancestors) reads; nullptr = no streamed input
+  const int* chunk_loaded;        // per chunk: non-zero once it has landed (written by a stream memory operation)
+  const unsigned char* te_first;  // per tent-element: first tent of the slab to touch the element -> its compact row does not
+                                  // exist yet and is projected here from the public row (transfer: Qs x Q, row-major)
+  const double* transfer;
+  int* chunk_left;                // per chunk: touched elements whose public row is not final yet (output side); nullptr = off
+  int chunk_elems;                // elements per chunk
   // column-compressed basis matrix (monomial j -> functions), for sol -> monomial coefficients
   const int* cptr;      // npoly + 1
   const int* crow;      // nnz
@@ -82,6 +92,7 @@ struct FastArgs {
 bool tent_fast_available(int D, int order);
 int tent_fast_compact_points(int D, int order, int fosystem);
 size_t tent_fast_inverse_doubles(int D, int order, int fosystem);
+bool tent_fast_stages_rows(int D, int order, int fosystem);
 size_t tent_fast_smem_bytes(int D, int order, int fosystem);
 cudaError_t launch_tent_fast(int D, int order, int fosystem, const TentKernelArgs& a, const FastArgs& f,
                              cudaStream_t stream);

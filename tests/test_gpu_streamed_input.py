@@ -1,6 +1,8 @@
-"""Streamed input (ngst_twave_set_initial_streamed): the device fetches the rows of the caller's host buffer in the order in
-which the tent levels first need them while the first levels run. Whatever the launch scheme, the result must be bitwise
-what SetInitial + Propagate gives."""
+"""Streamed input (ngst_twave_set_initial_streamed): the copy engine delivers the caller's host buffer in chunks of
+consecutive elements while Propagate runs as a spatial sweep -- one dependency-driven launch, tents ticketed in the order
+in which their dependency cones are complete, compact rows of first-touched elements built on the fly, finished chunks
+copied out when an output mirror is set. Whatever the launch scheme (the sweep, or the fallbacks that wait for the whole
+input), the result must be bitwise what SetInitial + Propagate gives."""
 import numpy as np
 import pytest
 
