@@ -647,27 +647,32 @@ void Solver::BuildSweep() {
   const size_t rowbytes = (size_t)(mesh_.D + 2) * Q * sizeof(double);
   sweep_chunk_elems_ = (int)std::max<size_t>(256, (16u << 20) / rowbytes);  // ~16 MB per chunk
   sweep_nchunks_ = (nel_ + sweep_chunk_elems_ - 1) / sweep_chunk_elems_;
-  std::vector<int> need(nt, 0), ready(nt, 0), ready_of_last(nel_, -1);
+  // Ticket order = estimated earliest start of every tent: it can start when the chunk it reads has landed (chunk c after
+  // (c + 1) chunk copies at the measured PCIe rate) and when the last earlier tent of each of its elements is done (a tent
+  // takes about 1.6 us per element when it applies a stored inverse). Predecessors have strictly smaller estimates, so
+  // they draw earlier tickets (no deadlock), and CTAs pick up tents along the diagonal front of the sweep -- chunk after
+  // chunk in space, level after level in time -- instead of finishing one chunk's 42 levels before touching the next.
+  const double chunk_s = (double)sweep_chunk_elems_ * rowbytes / 53e9, el_s = 1.6e-6;
+  std::vector<int> need(nt, 0);
+  std::vector<double> est(nt, 0.0), done_of_last(nel_, 0.0);
   std::vector<unsigned char> first(std::max(staged_.nte, 1), 0), touched(nel_, 0);
   for (int t = 0; t < nt; t++) {  // pitching order: predecessors first
-    int nd = 0, rd = 0;
+    int nd = 0;
+    double st = 0.0;
     for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++) {
       const int el = staged_.te_el[te];
       nd = std::max(nd, el / sweep_chunk_elems_);
-      rd = std::max(rd, ready_of_last[el]);
+      st = std::max(st, done_of_last[el]);
       if (!touched[el]) { touched[el] = 1; first[te] = 1; }
     }
     need[t] = nd;
-    ready[t] = std::max(nd, rd);
-    for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++) ready_of_last[staged_.te_el[te]] = ready[t];
+    est[t] = std::max(st, (nd + 1) * chunk_s);
+    const double fin = est[t] + el_s * (staged_.te_off[t + 1] - staged_.te_off[t]);
+    for (int te = staged_.te_off[t]; te < staged_.te_off[t + 1]; te++) done_of_last[staged_.te_el[te]] = fin;
   }
   std::vector<int> order(nt);
   for (int t = 0; t < nt; t++) order[t] = t;
-  // every predecessor has a smaller or equal `ready` and a smaller level: it draws an earlier ticket (no deadlock)
-  std::stable_sort(order.begin(), order.end(), [&](int x, int y) {
-    if (ready[x] != ready[y]) return ready[x] < ready[y];
-    return slab_.level[x] < slab_.level[y];
-  });
+  std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return est[x] < est[y]; });
   chunk_left_init_.assign(sweep_nchunks_, 0);
   std::vector<int> untouched;
   for (int el = 0; el < nel_; el++) {
