@@ -55,8 +55,11 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-mirror", action="store_true", help="e2e arm: explicit get_wavefront copy instead of the output mirror")
-    ap.add_argument("--no-streamed-input", action="store_true",
-                    help="e2e arm: blocking ngst_twave_set_initial instead of ngst_twave_set_initial_streamed (spatial sweep)")
+    ap.add_argument("--streamed-input", action="store_true",
+                    help="sequential e2e arm: ngst_twave_set_initial_streamed (spatial sweep) instead of the blocking set_initial")
+    ap.add_argument("--no-pipelined-e2e", action="store_true",
+                    help="headline e2e = the sequential call sequence instead of pipelined steps (prefetched input, asynchronous output)")
+    ap.add_argument("--no-sequential-mirror", action="store_true", help="sequential e2e arm: explicit get_wavefront instead of the mirror")
     ap.add_argument("--no-device-data", action="store_true", help="skip the informational device-sampled-data arm")
     ap.add_argument("--partition", default="balanced", choices=["balanced", "brick"],
                     help="N>1: cost-balanced recursive bisection (default) or plain brick cut of the bounding box")
@@ -403,20 +406,18 @@ def run_ours(args):
         b_ptr = _capi.C.cast(b0.data_ptr(), _capi.c_dp) if b0 is not None else None
         nb = 0 if b0 is None else b0.numel()
 
-        # The result rows reach the host buffer through the output mirror (ngst_twave_set_output_mirror): each row is
-        # written to pin_out during Propagate as soon as it is final, so most of the D2H overlaps the remaining tents
-        # (partitioned solvers: the rank's local rows).
-        use_mirror = not args.no_mirror
-
-        use_stream = not args.no_streamed_input
+        # Sequential form: set_initial, set_boundary_values, propagate, then the result through the output mirror
+        # (ngst_twave_set_output_mirror) or an explicit get_wavefront -- every call blocks, the copies of a step cannot overlap
+        # its own tents much (all rows are needed by the first levels, most rows are final only in the last ones).
+        use_mirror = not args.no_mirror and not args.no_sequential_mirror
+        use_stream = args.streamed_input
 
         def e2e_step(mirror=None, stream=None):
             mirror = use_mirror if mirror is None else mirror
             stream = use_stream if stream is None else stream
             tw.reset_time()
             if stream:
-                # boundary samples first (blocking H2D), then the state rows: the copy engine delivers them in chunks while
-                # propagate sweeps through the slab behind the copies (and, with the mirror, copies finished chunks out)
+                # spatial sweep (opt-in, measured slower than the blocking copy on this workload: DESIGN.md)
                 check(lib.ngst_twave_set_boundary_values(tw._h, b_ptr, nb))
                 check(lib.ngst_twave_set_initial_streamed(tw._h, in_ptr, ncomp))
             else:
@@ -426,15 +427,30 @@ def run_ours(args):
             if not mirror:
                 check(lib.ngst_twave_get_wavefront(tw._h, out_ptr))                # D2H: state rows
 
-        if use_mirror or use_stream:
-            e2e_step(False, False)               # reference result: blocking copy in, explicit copy out
-            want = pin_out.numpy().copy()
-            if use_stream:
-                pin_out.zero_()
-                e2e_step(False, True)
-                if not np.array_equal(pin_out.numpy(), want):
-                    print("bench.py: streamed input differs from ngst_twave_set_initial; timing the blocking copy", file=sys.stderr)
-                    use_stream = False
+        # Pipelined form (headline): consecutive steps are independent problems, so the NEXT step's input is prefetched
+        # (H2D on the input stream, copy engine) while this step's tents run, and this step's result leaves through an
+        # asynchronous copy (D2H on the output stream) while the next step's input arrives -- PCIe is full duplex. Every step
+        # still moves its own 794 MB in and 659 MB out inside the timed region; the first input and the last output are not
+        # overlapped with anything and are part of the measured time.
+        def e2e_pipelined(nsteps):
+            check(lib.ngst_twave_prefetch_input(tw._h, in_ptr, ncomp, b_ptr, nb))
+            for k in range(nsteps):
+                tw.reset_time()
+                check(lib.ngst_twave_use_prefetched(tw._h))
+                if k + 1 < nsteps:
+                    check(lib.ngst_twave_prefetch_input(tw._h, in_ptr, ncomp, b_ptr, nb))
+                check(lib.ngst_twave_propagate(tw._h))
+                check(lib.ngst_twave_get_wavefront_async(tw._h, out_ptr))
+            check(lib.ngst_twave_wait_output(tw._h))
+
+        e2e_step(False, False)               # reference result: blocking copy in, explicit copy out
+        want = pin_out.numpy().copy()
+        if use_stream:
+            pin_out.zero_()
+            e2e_step(False, True)
+            if not np.array_equal(pin_out.numpy(), want):
+                print("bench.py: streamed input differs from ngst_twave_set_initial; timing the blocking copy", file=sys.stderr)
+                use_stream = False
         if use_mirror:
             pin_out.zero_()
             check(lib.ngst_twave_set_output_mirror(tw._h, out_ptr))
@@ -445,7 +461,6 @@ def run_ours(args):
                       file=sys.stderr)
                 check(lib.ngst_twave_set_output_mirror(tw._h, None))
                 use_mirror = False
-            del want
         for _ in range(args.warmup):
             e2e_step()
         barrier()
@@ -453,10 +468,25 @@ def run_ours(args):
         for _ in range(args.steps):
             e2e_step()
         barrier()
-        e2e_s = time.perf_counter() - t0
-        e2e = {"sec": e2e_s, "h2d": int(nbytes + nb * 8), "d2h": int(nbytes), "mirror": use_mirror, "stream": use_stream}
+        seq_s = time.perf_counter() - t0
         if use_mirror:
             check(lib.ngst_twave_set_output_mirror(tw._h, None))
+        e2e = {"sec": seq_s, "h2d": int(nbytes + nb * 8), "d2h": int(nbytes), "mirror": use_mirror, "stream": use_stream,
+               "pipelined": False, "seq_sec": seq_s}
+        if not args.no_pipelined_e2e:
+            pin_out.zero_()
+            e2e_pipelined(2)
+            if np.array_equal(pin_out.numpy(), want):
+                e2e_pipelined(max(args.warmup, 1))
+                barrier()
+                t0 = time.perf_counter()
+                e2e_pipelined(args.steps)
+                barrier()
+                e2e["sec"] = time.perf_counter() - t0
+                e2e["pipelined"] = True
+            else:
+                print("bench.py: pipelined steps differ from the sequential result; reporting the sequential figure", file=sys.stderr)
+        del want
 
     # ---------------- informational: the same call sequence with initial and boundary data sampled ON THE DEVICE
     # (ngst_twave_*_analytic): no H2D of samples, same D2H. Not the e2e figure (that one copies
@@ -566,8 +596,8 @@ def run_ours(args):
     # ---------------- reduce over ranks (max time, sum units)
     ntents_local = len(mine)
     stats = torch.tensor([dev_s, wall_s, e2e["sec"] if e2e else 0.0, float(ntents_local), flops_step, bytes_step,
-                          float(launches), float(nels.sum()), cold["sec"] if cold else 0.0], dtype=torch.float64,
-                         device="cuda")
+                          float(launches), float(nels.sum()), cold["sec"] if cold else 0.0,
+                          e2e["seq_sec"] if e2e else 0.0], dtype=torch.float64, device="cuda")
     if world > 1:
         mx = stats.clone()
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
@@ -581,6 +611,7 @@ def run_ours(args):
             dist.destroy_process_group()
         return
     dev_s, wall_s, e2e_s = mx[0], mx[1], mx[2]
+    seq_s_max = mx[9]
     tents_step = sm[3]
     value = tents_step * args.steps / dev_s
 
@@ -702,15 +733,23 @@ def run_ours(args):
         "energy_after": energy,
     }
     if e2e:
+        seq_path = (("ngst_twave_set_initial_streamed" if e2e.get("stream") else "ngst_twave_set_initial") +
+                    " + set_boundary_values + propagate" +
+                    (" with the result rows streamed into the host buffer during propagate (ngst_twave_set_output_mirror)"
+                     if e2e.get("mirror") else " + get_wavefront") + ", every call blocking, pinned host buffers")
+        seq = {"value": tents_step * args.steps / seq_s_max, "unit": "tents/s", "ms_per_step": 1e3 * seq_s_max / args.steps,
+               "path": seq_path}
         line["e2e"] = {"value": tents_step * args.steps / e2e_s, "unit": "tents/s",
                        "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"],
-                       "ms_per_step": 1e3 * e2e_s / args.steps,
-                       "streamed_input": bool(e2e.get("stream")),
-                       "path": (("ngst_twave_set_initial_streamed" if e2e.get("stream") else "ngst_twave_set_initial") +
-                                " + set_boundary_values + propagate on pinned host buffers, result rows "
-                                "streamed into the host buffer during propagate (ngst_twave_set_output_mirror; checked bitwise "
-                                "against ngst_twave_get_wavefront before timing)") if e2e.get("mirror") else
-                               "ngst_twave_set_initial + set_boundary_values + propagate + get_wavefront on pinned host buffers"}
+                       "ms_per_step": 1e3 * e2e_s / args.steps, "pipelined": bool(e2e.get("pipelined")),
+                       "path": ("independent steps pipelined over the copy engines through the C ABI, pinned host buffers: per step "
+                                "ngst_twave_use_prefetched (input staged by the previous step's ngst_twave_prefetch_input: H2D of "
+                                "state rows + boundary samples on the input stream, compact transfer) + ngst_twave_prefetch_input of the "
+                                "next step + ngst_twave_propagate + ngst_twave_get_wavefront_async (device snapshot, D2H on the output "
+                                "stream); ngst_twave_wait_output after the last step; the unoverlapped first input and last output are "
+                                "inside the timed region; result checked bitwise against the sequential calls before timing")
+                               if e2e.get("pipelined") else seq_path,
+                       "sequential": seq}
     if assembly_every_step:
         line["assembly_every_step"] = assembly_every_step
     if device_data:

@@ -189,6 +189,18 @@ int ngst_twave_set_boundary_analytic(ngst_twave* t, int family, const double* pa
  * the analytic data sampled on the device at `time`: no wavefront crosses PCIe. */
 int ngst_twave_error_analytic(ngst_twave* t, int family, const double* params, int nparams, double time, int l2only,
                               double* out);
+/* Pipelining of independent steps over the copy engines (no reference counterpart; double buffering as in any input
+ * pipeline). ngst_twave_prefetch_input returns at once: the NEXT step's initial rows (wf, nel x ncomp*nip) and boundary
+ * samples (bnd_values, n as ngst_twave_set_boundary_values, or NULL) are copied host-to-device into staging buffers and
+ * transferred to the compact state on an input stream while the current step computes; both host buffers must be page-locked
+ * and stay unchanged until ngst_twave_use_prefetched has been called. ngst_twave_use_prefetched = ngst_twave_set_initial
+ * (+ ngst_twave_set_boundary_values) from the staged data, device to device. ngst_twave_get_wavefront_async snapshots the
+ * state on the device and copies it to `out` (page-locked) on an output stream while the next step's input arrives and its
+ * tents run (PCIe is full duplex); ngst_twave_wait_output blocks until the last such copy has landed. */
+int ngst_twave_prefetch_input(ngst_twave* t, const double* wf, int ncomp, const double* bnd_values, long long nbnd);
+int ngst_twave_use_prefetched(ngst_twave* t);
+int ngst_twave_get_wavefront_async(ngst_twave* t, double* out);
+int ngst_twave_wait_output(ngst_twave* t);
 /* Propagate src/twavetents.cpp:72-175: one slab, timeshift += slab height. Fails with NGST_ERR_STATE when the slab was
  * re-pitched after the solver was created (the device tables are staged once; the reference re-reads its slab on every
  * call): create a new solver for the new tents. */

@@ -600,6 +600,27 @@ class TWaveTents(TrefftzTents):
         check(lib.ngst_twave_set_initial_streamed(self._h, dptr(wf), wf.shape[1] // self.nip))
         self._refresh()
 
+    def PrefetchInput(self, wf, bnd_values=None):
+        """Start copying the NEXT step's initial rows (and pre-sampled boundary values) to the device while the current step
+        runs; UsePrefetched() then makes them the state. Arrays must be page-locked (e.g. torch pinned tensors' .numpy())
+        and stay unchanged until UsePrefetched() has been called."""
+        self._prefetched = (wf, bnd_values)
+        n = 0 if bnd_values is None else len(bnd_values)
+        check(lib.ngst_twave_prefetch_input(self._h, dptr(wf), wf.shape[1] // self.nip, dptr(bnd_values), n))
+
+    def UsePrefetched(self):
+        check(lib.ngst_twave_use_prefetched(self._h))
+        self._bnd_dirty = True
+        self._refresh()
+
+    def GetWavefrontAsync(self, out):
+        """Copy of the state into the page-locked array `out`, asynchronously; WaitOutput() blocks until it has landed."""
+        self._async_out = out
+        check(lib.ngst_twave_get_wavefront_async(self._h, dptr(out)))
+
+    def WaitOutput(self):
+        check(lib.ngst_twave_wait_output(self._h))
+
     def SetBoundaryCF(self, bddatum):
         """An AnalyticData datum is sampled on the device by every Propagate (Dirichlet faces take d_t u, Neumann faces
         grad u); any other callable is evaluated on the host per slab as before."""

@@ -76,6 +76,10 @@ _SIGS = {
     "ngst_twave_quadrature": (C.c_int, [c_vp, c_dp, c_dp]),
     "ngst_twave_set_initial": (C.c_int, [c_vp, c_dp, C.c_int]),
     "ngst_twave_set_initial_streamed": (C.c_int, [c_vp, c_dp, C.c_int]),
+    "ngst_twave_prefetch_input": (C.c_int, [c_vp, c_dp, C.c_int, c_dp, C.c_longlong]),
+    "ngst_twave_use_prefetched": (C.c_int, [c_vp]),
+    "ngst_twave_get_wavefront_async": (C.c_int, [c_vp, c_dp]),
+    "ngst_twave_wait_output": (C.c_int, [c_vp]),
     "ngst_twave_boundary_npoints": (C.c_longlong, [c_vp]),
     "ngst_twave_boundary_nvalues": (C.c_longlong, [c_vp]),
     "ngst_twave_boundary_points": (C.c_int, [c_vp, c_dp, c_ip]),

@@ -397,6 +397,19 @@ int ngst_twave_set_initial_streamed(ngst_twave* t, const double* wf, int ncomp) 
   return guarded([&] { need(t, "solver"); need(wf, "wf"); t->solver->SetInitialStreamed(wf, ncomp); });
 }
 
+int ngst_twave_prefetch_input(ngst_twave* t, const double* wf, int ncomp, const double* bnd_values, long long nbnd) {
+  return guarded([&] { need(t, "solver"); need(wf, "wf"); t->solver->PrefetchInput(wf, ncomp, bnd_values, nbnd); });
+}
+int ngst_twave_use_prefetched(ngst_twave* t) {
+  return guarded([&] { need_current(t); t->solver->UsePrefetched(); });
+}
+int ngst_twave_get_wavefront_async(ngst_twave* t, double* out) {
+  return guarded([&] { need(t, "solver"); need(out, "out"); t->solver->GetWavefrontAsync(out); });
+}
+int ngst_twave_wait_output(ngst_twave* t) {
+  return guarded([&] { need(t, "solver"); t->solver->WaitOutput(); });
+}
+
 int ngst_twave_boundary_points(const ngst_twave* t, double* xt, int* kind_per_point) {
   return guarded([&] {
     need(t, "solver");

@@ -384,8 +384,10 @@ Solver::~Solver() {
   ReleaseLoadBuffer();
   for (cudaStream_t st : {stream_in_, stream_out_})
     if (st) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
-  for (cudaEvent_t e : {ev_in_start_, ev_in_done_, ev_out_start_, ev_out_done_})
+  for (cudaEvent_t e : {ev_in_start_, ev_in_done_, ev_out_start_, ev_out_done_, ev_stage_, ev_snap_, ev_copied_, ev_used_})
     if (e) cudaEventDestroy(e);
+  for (double* p : {d_stage_wf_, d_stage_cs_, d_stage_bnd_, d_snap_})
+    if (p) cudaFree(p);
   if (stream_mirror_) cudaStreamDestroy(stream_mirror_);
   if (ev_level_) cudaEventDestroy(ev_level_);
   if (ev_mirror_) cudaEventDestroy(ev_mirror_);
@@ -689,12 +691,7 @@ void Solver::BuildSweep() {
   allocs_.push_back(d_chunk_loaded_);
   CU(cudaMalloc(&d_chunk_left_, sizeof(int) * sweep_nchunks_));
   allocs_.push_back(d_chunk_left_);
-  int lo = 0, hi = 0;
-  CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-  CU(cudaStreamCreateWithPriority(&stream_in_, cudaStreamNonBlocking, hi));
-  CU(cudaStreamCreateWithPriority(&stream_out_, cudaStreamNonBlocking, hi));
-  for (cudaEvent_t* e : {&ev_in_start_, &ev_in_done_, &ev_out_start_, &ev_out_done_})
-    CU(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+  EnsurePipeStreams();
   sweep_possible_ = true;
 }
 
@@ -744,6 +741,123 @@ void Solver::SetInitialStreamed(const double* wf, int ncomp) {
   CU(cudaEventRecord(ev_in_done_, stream_in_));
   cstate_valid_ = false;  // the tents of the sweep build the compact rows of everything they touch
   load_pending_ = true;
+}
+
+void Solver::EnsurePipeStreams() {
+  if (!stream_in_) {
+    int lo = 0, hi = 0;
+    CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CU(cudaStreamCreateWithPriority(&stream_in_, cudaStreamNonBlocking, hi));
+    CU(cudaStreamCreateWithPriority(&stream_out_, cudaStreamNonBlocking, hi));
+    for (cudaEvent_t* e : {&ev_in_start_, &ev_in_done_, &ev_out_start_, &ev_out_done_})
+      CU(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+  }
+  if (!ev_stage_)
+    for (cudaEvent_t* e : {&ev_stage_, &ev_snap_, &ev_copied_, &ev_used_}) CU(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+}
+
+// The next step's input, fetched while the current step computes: H2D copies on the input stream (copy engine), then the
+// transfer to the compact state on the same stream.
+void Solver::PrefetchInput(const double* wf, int ncomp, const double* bnd_values, long long nbnd) {
+  const int D = mesh_.D, Q = rule_.nip;
+  if (!wf) throw std::invalid_argument("PrefetchInput: null buffer");
+  if (ncomp != D + 2 && ncomp != D + 1) throw std::invalid_argument("PrefetchInput: initial data must have D+2 or D+1 components");
+  if (qt_ && ncomp == D + 1) throw std::invalid_argument("PrefetchInput: the quasi-Trefftz solver takes second-order initial data");
+  if (bnd_values && nbnd != staged_.nbnd_values) throw std::invalid_argument("PrefetchInput: wrong number of boundary values");
+  CU(cudaSetDevice(device_));
+  EnsurePipeStreams();
+  const size_t bytes = (size_t)nel_ * ncomp * Q * sizeof(double);
+  if (stage_wf_bytes_ < bytes) {
+    CU(cudaStreamSynchronize(stream_in_));
+    if (d_stage_wf_) CU(cudaFree(d_stage_wf_));
+    CU(cudaMalloc(&d_stage_wf_, bytes));
+    stage_wf_bytes_ = bytes;
+  }
+  const int fo = ncomp == D + 1 ? 1 : 0;
+  const int cs = (compact_possible_ && compact_enabled_) ? tent_fast_compact_points(D, order_, fo) : 0;
+  const size_t cbytes = (size_t)nel_ * ncomp * cs * sizeof(double);
+  if (cs > 0 && stage_cs_bytes_ < cbytes) {
+    CU(cudaStreamSynchronize(stream_in_));
+    if (d_stage_cs_) CU(cudaFree(d_stage_cs_));
+    CU(cudaMalloc(&d_stage_cs_, cbytes));
+    stage_cs_bytes_ = cbytes;
+  }
+  if (bnd_values && nbnd > 0 && !d_stage_bnd_) CU(cudaMalloc(&d_stage_bnd_, sizeof(double) * nbnd));
+  if (cs > 0 && transfer_points_ != cs) {
+    const SimplexRule rs = make_compact_rule(D, 2 * order_);
+    d_transfer_ = Upload(rule_transfer_matrix(rule_, rs, order_));
+    transfer_points_ = cs;
+  }
+  // the staging buffers are free once the previous prefetch has been taken over
+  CU(cudaStreamWaitEvent(stream_in_, ev_used_, 0));
+  if (bnd_values && nbnd > 0)
+    CU(cudaMemcpyAsync(d_stage_bnd_, bnd_values, sizeof(double) * nbnd, cudaMemcpyHostToDevice, stream_in_));
+  // in chunks, so that the transfer of a chunk runs behind the copy of the next one
+  const size_t rowlen = (size_t)ncomp * Q;
+  const int chunk = (int)std::max<size_t>(256, (16u << 20) / (rowlen * sizeof(double)));
+  for (int e0 = 0; e0 < nel_; e0 += chunk) {
+    const int ne = std::min(chunk, nel_ - e0);
+    CU(cudaMemcpyAsync(d_stage_wf_ + (size_t)e0 * rowlen, wf + (size_t)e0 * rowlen, (size_t)ne * rowlen * sizeof(double),
+                       cudaMemcpyHostToDevice, stream_in_));
+    if (cs > 0)
+      CU(launch_project_rows(ne, Q, cs, 0, ncomp, ncomp * Q, d_transfer_, d_stage_wf_ + (size_t)e0 * rowlen,
+                             d_stage_cs_ + (size_t)e0 * ncomp * cs, stream_in_));
+  }
+  CU(cudaEventRecord(ev_stage_, stream_in_));
+  stage_ncomp_ = ncomp;
+  stage_has_bnd_ = bnd_values && nbnd > 0;
+  stage_valid_ = true;
+}
+
+// SetInitial (+ SetBoundaryValues) from the prefetched input: device-to-device copies on the solver's stream
+void Solver::UsePrefetched() {
+  if (!stage_valid_) throw std::logic_error("UsePrefetched: nothing has been prefetched");
+  SetInitial(nullptr, stage_ncomp_);  // validates, allocates, configures
+  const size_t bytes = (size_t)nel_ * ncomp_ * rule_.nip * sizeof(double);
+  CU(cudaStreamWaitEvent(stream_, ev_stage_, 0));
+  CU(cudaMemcpyAsync(d_wavefront_, d_stage_wf_, bytes, cudaMemcpyDeviceToDevice, stream_));
+  if (cs_points_ > 0 && compact_enabled_) {
+    CU(cudaMemcpyAsync(d_cstate_, d_stage_cs_, (size_t)nel_ * ncomp_ * cs_points_ * sizeof(double), cudaMemcpyDeviceToDevice, stream_));
+    cstate_valid_ = true;
+  }
+  if (stage_has_bnd_) {
+    bnd_family_ = -1;
+    if (!d_bnd_) CU(cudaMalloc(&d_bnd_, sizeof(double) * staged_.nbnd_values));
+    CU(cudaMemcpyAsync(d_bnd_, d_stage_bnd_, sizeof(double) * staged_.nbnd_values, cudaMemcpyDeviceToDevice, stream_));
+    args_.bnd_data = d_bnd_;
+  }
+  CU(cudaEventRecord(ev_used_, stream_));
+  stage_valid_ = false;
+}
+
+void Solver::GetWavefrontAsync(double* out) {
+  if (!have_initial_) throw std::logic_error("GetWavefrontAsync: SetInitial has not been called");
+  if (!out) throw std::invalid_argument("GetWavefrontAsync: null buffer");
+  CU(cudaSetDevice(device_));
+  FinishLoad();
+  EnsurePipeStreams();
+  const size_t bytes = (size_t)nel_ * ncomp_ * rule_.nip * sizeof(double);
+  if (snap_bytes_ < bytes) {
+    CU(cudaStreamSynchronize(stream_out_));
+    if (d_snap_) CU(cudaFree(d_snap_));
+    CU(cudaMalloc(&d_snap_, bytes));
+    snap_bytes_ = bytes;
+  }
+  // snapshot on the device (the state may be overwritten by the next step at once), then the copy engine takes it out
+  if (out_pending_) CU(cudaStreamWaitEvent(stream_, ev_copied_, 0));  // the previous snapshot has left
+  CU(cudaMemcpyAsync(d_snap_, d_wavefront_, bytes, cudaMemcpyDeviceToDevice, stream_));
+  CU(cudaEventRecord(ev_snap_, stream_));
+  CU(cudaStreamWaitEvent(stream_out_, ev_snap_, 0));
+  CU(cudaMemcpyAsync(out, d_snap_, bytes, cudaMemcpyDeviceToHost, stream_out_));
+  CU(cudaEventRecord(ev_copied_, stream_out_));
+  out_pending_ = true;
+}
+
+void Solver::WaitOutput() {
+  if (!out_pending_) return;
+  CU(cudaSetDevice(device_));
+  CU(cudaEventSynchronize(ev_copied_));
+  out_pending_ = false;
 }
 
 namespace {

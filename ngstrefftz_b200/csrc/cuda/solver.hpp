@@ -64,6 +64,14 @@ class Solver {
   // finished chunks out at the other end). Falls back to SetInitial where the sweep does not apply.
   void SetInitialStreamed(const double* wf, int ncomp);
   bool sweep_active() const { return load_pending_ && sweep_built_; }
+  // Pipelining of independent steps (double buffering, copy engines): PrefetchInput copies the NEXT step's initial rows and
+  // boundary samples into staging buffers on the input stream (and transfers them to the compact state there) while the
+  // current step computes; UsePrefetched makes them the state with device-to-device copies. GetWavefrontAsync snapshots the
+  // result on the device and copies it to `out` (page-locked) on the output stream; WaitOutput blocks until it has landed.
+  void PrefetchInput(const double* wf, int ncomp, const double* bnd_values, long long nbnd);
+  void UsePrefetched();
+  void GetWavefrontAsync(double* out);
+  void WaitOutput();
   void SetBoundaryValues(const double* values, long long n);
   // Analytic data sampled on the device (cuda/sample.hpp): SetInitial / MakeWavefront
   // (twavetents.cpp:734-764) and the boundary datum, re-sampled by every Propagate at t_local + timeshift
@@ -226,6 +234,12 @@ class Solver {
   int* d_untouched_ = nullptr;          // elements no tent touches (their compact rows are transferred separately)
   cudaStream_t stream_in_ = nullptr, stream_out_ = nullptr;
   cudaEvent_t ev_in_start_ = nullptr, ev_in_done_ = nullptr, ev_out_start_ = nullptr, ev_out_done_ = nullptr;
+  double *d_stage_wf_ = nullptr, *d_stage_cs_ = nullptr, *d_stage_bnd_ = nullptr, *d_snap_ = nullptr;
+  size_t stage_wf_bytes_ = 0, stage_cs_bytes_ = 0, snap_bytes_ = 0;
+  int stage_ncomp_ = 0;
+  bool stage_valid_ = false, stage_has_bnd_ = false, out_pending_ = false;
+  cudaEvent_t ev_stage_ = nullptr, ev_snap_ = nullptr, ev_copied_ = nullptr, ev_used_ = nullptr;
+  void EnsurePipeStreams();
   void BuildSweep();
   void FinishLoad();                    // the whole input has landed before the solver's stream goes on
   void ReleaseLoadBuffer();
