@@ -291,6 +291,13 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
       const int idc = valid ? idx : nptb - 1;
       const int eb = idc / QR, q = idc % QR;
       const int te = te0 + b0 + eb;
+      if (c0 + NS * kChunk < nptb && lane < 6) {
+        // geometry records of the (at most two) elements of this warp's NEXT chunk: into L1 now, so that the loads at the top
+        // of the next iteration do not wait for L2 (288 B = three 128-byte lines per record; costs no registers)
+        const int first_pt = c0 + NS * kChunk + (lane < 3 ? 0 : kChunk - 1);
+        const int ten = te0 + b0 + min(first_pt, nptb - 1) / QR;
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(f.fe + (size_t)ten * FE + (lane % 3) * 16));
+      }
       double gcur[NC];
       if constexpr (STG) {
         const double* __restrict__ r = rowsS + eb * C::ROWLEN + q;
