@@ -808,10 +808,15 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
     if (f.chunk_left) {
       // streamed output: one element less to finish in its chunk; the copy engine takes a chunk out as soon as its count
       // is zero (stream wait on the counter), so the rows must be visible system-wide first
-      __threadfence_system();
+      // (one fence for the CTA: the barrier orders every thread's stores before thread 0's fence, which is cumulative --
+      // the pattern of a cooperative-groups grid barrier)
       __syncthreads();
-      for (int e = tid; e < nel; e += kThreads)
-        if (f.te_final[te0 + e]) atomicSub(f.chunk_left + a.te_el[te0 + e] / f.chunk_elems, 1);
+      if (w == 0) {
+        if (lane == 0) __threadfence_system();
+        __syncwarp();
+        for (int e = lane; e < nel; e += 32)
+          if (f.te_final[te0 + e]) atomicSub(f.chunk_left + a.te_el[te0 + e] / f.chunk_elems, 1);
+      }
     }
   } else {
     for (int idx = tid; idx < npts; idx += kThreads) {
@@ -848,15 +853,23 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
           }
         }
       }
-      __threadfence_system();
       __syncthreads();
-      for (int s = a.succ_off[tent] + tid; s < a.succ_off[tent + 1]; s += kThreads) atomicSub(a.remaining + a.succ[s], 1);
-      for (int s = pp.rsucc_off[tent] + tid; s < pp.rsucc_off[tent + 1]; s += kThreads)
-        atomicSub_system(pp.remaining[pp.rsucc_peer[s]] + pp.rsucc_tent[s], 1);
+      if (w == 0) {  // one system-scope fence for the CTA (cumulative over the barrier), then the releases
+        if (lane == 0) __threadfence_system();
+        __syncwarp();
+        for (int s = a.succ_off[tent] + lane; s < a.succ_off[tent + 1]; s += 32) atomicSub(a.remaining + a.succ[s], 1);
+        for (int s = pp.rsucc_off[tent] + lane; s < pp.rsucc_off[tent + 1]; s += 32)
+          atomicSub_system(pp.remaining[pp.rsucc_peer[s]] + pp.rsucc_tent[s], 1);
+      }
     } else {
-      __threadfence();  // this thread's state rows are visible device-wide before the successors are released
+      // the state rows of every thread are visible device-wide before the successors are released: barrier, then ONE
+      // fence (cumulative), then the releases by the same warp
       __syncthreads();
-      for (int s = a.succ_off[tent] + tid; s < a.succ_off[tent + 1]; s += kThreads) atomicSub(a.remaining + a.succ[s], 1);
+      if (w == 0) {
+        if (lane == 0) __threadfence();
+        __syncwarp();
+        for (int s = a.succ_off[tent] + lane; s < a.succ_off[tent + 1]; s += 32) atomicSub(a.remaining + a.succ[s], 1);
+      }
     }
   }
 }
