@@ -714,8 +714,11 @@ def run_ours(args):
                                f"c=1, standing wave, Dirichlet, dt={args.dt}, edge pitching local_ct global_ct=2/3",
                    "tets": int(np.prod(cells) * 6), "order": order, "nbasis": N, "nip": Q,
                    "slab_tents": int(ntents_global), "levels": ts.GetNLayers(), "tent_elements": int(sm[7]),
-                   "parallelism": (f"spatial partition {grid[0]}x{grid[1]}x{grid[2]} ({args.partition} vertex ownership), per-level halo exchange "
-                                   f"{'after' if args.no_overlap else 'overlapped with'} the interior tents") if world > 1 else "single GPU",
+                   "parallelism": (f"spatial partition {grid[0]}x{grid[1]}x{grid[2]} ({args.partition} vertex ownership), " +
+                                   ("interface rows exchanged inside the tent kernel over NVLink peer memory, one launch per slab"
+                                    if tw.peer_exchange()[0] else
+                                    f"per-level NCCL halo exchange {'after' if args.no_overlap else 'overlapped with'} the interior tents"))
+                                  if world > 1 else "single GPU",
                    "l2": f"state {wf0.nbytes * world / 1e6:.0f} MB per slab > 126 MB L2 (no flush needed)",
                    "pitch_s": pitch_s,
                    "exchange": (tw.peer_exchange()[1] if tw.peer_exchange()[0] else "per-level NCCL send/recv ("
