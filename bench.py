@@ -65,6 +65,7 @@ def parse():
                     help="N>1: cost-balanced recursive bisection (default) or plain brick cut of the bounding box")
     ap.add_argument("--no-peer-exchange", action="store_true",
                     help="N>1: halo tents + grouped ncclSend/ncclRecv per level instead of the exchange inside the tent kernel")
+    ap.add_argument("--halo-first", action="store_true", help="N>1, peer-to-peer exchange: ticket the halo tents of a level first (A/B)")
     ap.add_argument("--no-overlap", action="store_true", help="N>1: exchange after each level instead of overlapped")
     ap.add_argument("--level-launches", action="store_true",
                     help="N=1: always one launch per tent level (profiling; default: automatic, see DESIGN.md section 4.5)")
@@ -312,6 +313,8 @@ def run_ours(args):
             tw.set_kernel_mode(2)
         if args.no_peer_exchange:
             tw.set_peer_exchange(False)
+        elif args.halo_first:
+            tw.set_peer_exchange(2)
     else:
         tw = ng.TWave(order, ts, 1.0, device=local)
         if args.mirror_ctas:

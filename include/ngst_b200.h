@@ -140,8 +140,9 @@ int ngst_twave_comm_init(ngst_twave* t, const void* id128);
  * rank: a tent waits for its predecessors on any rank (hazard counters), pushes the rows it writes into the buffers of the
  * other ranks that hold the element and releases its successors elsewhere with system-scope atomics -- compute and exchange
  * in one kernel, no per-level synchronisation between the GPUs; one stream-ordered NCCL barrier per slab. on == 0 (or kernel
- * mode 2): halo tents + grouped ncclSend/ncclRecv per level. ngst_twave_peer_exchange returns 1 when the next Propagate will
- * use it and copies a short reason / description into note (may be NULL). */
+ * mode 2): halo tents + grouped ncclSend/ncclRecv per level. on == 2: as 1, but the halo tents of a level are ticketed before
+ * all its interior tents instead of behind the first third of them (A/B). ngst_twave_peer_exchange returns 1 when the next
+ * Propagate will use it and copies a short reason / description into note (may be NULL). */
 int ngst_twave_set_peer_exchange(ngst_twave* t, int on);
 int ngst_twave_peer_exchange(const ngst_twave* t, char* note, int note_len);
 /* own_tents: info[7] global tent ids; loc2glob / owned: info[6] entries; NULL skips */

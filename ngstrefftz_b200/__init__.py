@@ -721,7 +721,7 @@ class TWaveTents(TrefftzTents):
 
     def set_peer_exchange(self, on=True):
         """Multi-GPU: exchange inside the tent kernel over peer memory (default where available) or per level with NCCL."""
-        check(lib.ngst_twave_set_peer_exchange(self._h, int(bool(on))))
+        check(lib.ngst_twave_set_peer_exchange(self._h, int(on)))  # 2 = halo tents of a level first (A/B)
 
     def peer_exchange(self):
         """(active, note)"""

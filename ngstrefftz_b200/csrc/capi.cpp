@@ -498,7 +498,7 @@ int ngst_twave_factor_cache(const ngst_twave* t, long long* bytes) {
 }
 
 int ngst_twave_set_peer_exchange(ngst_twave* t, int on) {
-  return guarded([&] { need(t, "solver"); t->solver->set_peer_exchange(on != 0); });
+  return guarded([&] { need(t, "solver"); t->solver->set_peer_exchange(on != 0, on == 2); });
 }
 int ngst_twave_peer_exchange(const ngst_twave* t, char* note, int note_len) {
   if (!t) return 0;

@@ -115,7 +115,7 @@ class Solver {
   // build right-hand sides, apply the stored inverses and evaluate. off: assemble and solve in every Propagate.
   void set_factor_cache(bool on) { factor_cache_enabled_ = on; }
   // multi-GPU: exchange inside the tent kernel over peer memory (default where it could be set up) or per level with NCCL
-  void set_peer_exchange(bool on) { p2p_enabled_ = on; }
+  void set_peer_exchange(bool on, bool halo_first = false) { p2p_enabled_ = on; p2p_halo_first_ = halo_first; }
   bool peer_exchange_active() const { return p2p_ready_ && p2p_enabled_ && UseCompact() && !qt_; }
   const std::string& peer_exchange_note() const { return p2p_note_; }
   // 0 = not in use, 1 = the next Propagate assembles, inverts and stores, 2 = the next Propagate applies stored inverses
@@ -262,7 +262,9 @@ class Solver {
   // ---- peer-to-peer exchange inside the tent kernel (multi-GPU): one dependency-driven launch per slab on every rank; tents
   // push the rows they write into the other holders' buffers (CUDA IPC mappings over NVLink) and release their successors
   // on other ranks with system-scope atomics. Falls back to the per-level NCCL exchange when it cannot be set up.
-  bool p2p_enabled_ = true, p2p_ready_ = false;
+  bool p2p_enabled_ = true, p2p_ready_ = false, p2p_halo_first_ = false;
+  std::vector<int> p2p_order_;   // ticket order of the peer-to-peer launch: level by level, halo tents behind a third of the interior ones
+  int* d_p2p_tents_ = nullptr;
   P2PArgs p2p_host_{};
   P2PArgs* d_p2p_ = nullptr;
   std::vector<void*> ipc_opened_;
