@@ -58,6 +58,15 @@ int ngst_slab_create(const ngst_mesh* m, int method, ngst_slab** out);
 int ngst_slab_set_max_wavespeed(ngst_slab* s, const double* c, int n);
 /* PitchTents python_tents.cpp:44-65 -> tents.cpp:78-359. *ok = 0 when the slab could not be completed. */
 int ngst_slab_pitch(ngst_slab* s, double dt, int local_ct, double global_ct, int* ok);
+/* Level-synchronous pitcher (no reference counterpart; same front-advancing rules and pole heights, tents.cpp:796-813, but a
+ * pick rule that depends on the state alone: the ready vertex of minimal (level, vertex number) instead of "first vertex of
+ * minimal level in the ready list", tents.cpp:431-443, whose order is a history of the whole run). All ready vertices of the
+ * minimal level are handled as one phase -- the lexicographically first maximal independent set of them is pitched, in
+ * parallel -- so the cost is a few passes over the mesh per level instead of a serial loop over the tents, and the result does
+ * not depend on how the work is split. The tents DIFFER from the reference's (on the tested meshes: fewer tents, fewer
+ * levels); they are bit-identical to the CPU oracle's serial loop with the same rule. Use ngst_slab_pitch where the
+ * reference's tent order is wanted. */
+int ngst_slab_pitch_level_sync(ngst_slab* s, double dt, int local_ct, double global_ct, int* ok);
 /* A slab from tents pitched elsewhere, e.g. by the reference's own ngstents (what TWave(order, tps, ...) is handed,
  * src/twavetents.cpp:1194-1228): the Tent fields of python_tents.cpp:119-128 -- vertex, level, tbot, ttop, nbv, nbtime,
  * els, internal_facets -- flattened with CSR offsets (*_off: ntents+1 entries), in the slab's tent order. They are taken

@@ -173,11 +173,14 @@ class TentSlab:
             c = f64(np.atleast_1d(wavespeed)).reshape(-1)
         check(lib.ngst_slab_set_max_wavespeed(self._h, dptr(c), len(c)))
 
-    def PitchTents(self, dt, local_ct=False, global_ct=1.0):
+    def PitchTents(self, dt, local_ct=False, global_ct=1.0, level_sync=False):
+        """python_tents.cpp:44-65. level_sync=True (extension): the level-synchronous parallel pitcher with the pick rule
+        "minimal (level, vertex number)" -- other tents than the reference's order (ngst_slab_pitch_level_sync)."""
         ok = C.c_int(0)
         self._export = None
         try:
-            check(lib.ngst_slab_pitch(self._h, float(dt), int(bool(local_ct)), float(global_ct), C.byref(ok)))
+            fn = lib.ngst_slab_pitch_level_sync if level_sync else lib.ngst_slab_pitch
+            check(fn(self._h, float(dt), int(bool(local_ct)), float(global_ct), C.byref(ok)))
         except NgstError as e:
             if e.code == -2:
                 raise RuntimeError("Wavespeed has not been set!") from e

@@ -49,6 +49,7 @@ _SIGS = {
     "ngst_slab_pitch": (C.c_int, [c_vp, C.c_double, C.c_int, C.c_double, c_ip]),
     "ngst_slab_import_tents": (C.c_int, [c_vp, C.c_int, C.c_double, c_ip, c_ip, c_dp, c_dp, c_ip, c_ip, c_dp, c_ip, c_ip,
                                          c_ip, c_ip]),
+    "ngst_slab_pitch_level_sync": (C.c_int, [c_vp, C.c_double, C.c_int, C.c_double, c_ip]),
     "ngst_slab_ntents": (C.c_int, [c_vp]),
     "ngst_slab_nlayers": (C.c_int, [c_vp]),
     "ngst_slab_height": (C.c_double, [c_vp]),

@@ -168,6 +168,13 @@ int ngst_slab_pitch(ngst_slab* s, double dt, int local_ct, double global_ct, int
   });
 }
 
+int ngst_slab_pitch_level_sync(ngst_slab* s, double dt, int local_ct, double global_ct, int* ok) {
+  return guarded([&] {
+    need(s, "slab"); need(ok, "ok");
+    *ok = s->s.PitchTentsLevelSync(dt, local_ct != 0, global_ct) ? 1 : 0;
+  });
+}
+
 int ngst_slab_import_tents(ngst_slab* s, int ntents, double dt, const int* vertex, const int* level, const double* tbot,
                            const double* ttop, const int* nb_off, const int* nbv, const double* nbtime, const int* el_off,
                            const int* els, const int* facet_off, const int* facets) {

@@ -575,6 +575,160 @@ bool TentSlab::PitchTents(double adt, bool calc_local_ct, double global_ct) {
   return pitched;
 }
 
+// Level-synchronous pitcher (no reference counterpart). The reference picks "the first vertex of minimal level in the ready
+// LIST" (tents.cpp:431-443); the order of that list is a history of the whole run, so its tents can only be reproduced by the
+// serial loop above. This pitcher uses a rule that depends on the state alone -- the ready vertex of minimal (level, vertex
+// number) -- and is therefore independent of how the work is split: all ready vertices of the minimal level L form one
+// phase; pitching them in ascending order, skipping those a smaller-numbered neighbour has just lifted above L, selects the
+// lexicographically first maximal independent set of the phase, whose tents do not interact. Selection is a cheap serial
+// scan; the tents of a phase, their tables and the pole heights of the neighbourhood are computed in parallel. Other, on
+// the tested meshes fewer, tents and levels than the reference's order; bit-identical to the oracle's SERIAL loop with the
+// same rule (tests/test_pitcher.py).
+bool TentSlab::PitchTentsLevelSync(double adt, bool calc_local_ct, double global_ct) {
+  generation++;
+  if (!mesh) throw std::runtime_error("TentSlab: no mesh");
+  if (cmax_el.empty()) throw std::logic_error("Wavespeed has not been set!");
+  const SimplexMesh& m = *mesh;
+  if ((int)cmax_el.size() != m.nel) throw std::runtime_error("TentSlab: wavespeed array size mismatch");
+  if (method != kEdgeGrad && method != kVolGrad) return false;
+  const int D = m.D, nv = m.nv;
+  dt = adt;
+  pitched = false;
+  nlayers = 0;
+  ntents = 0;
+  vertex.clear(); level.clear(); tbot.clear(); ttop.clear(); maxslope.clear();
+  nbv = Csr(); els = Csr(); facets = Csr(); dag = Csr();
+  nbv.off = {0}; els.off = {0}; facets.off = {0};
+  nbtime.clear();
+  Pitcher P(m, method);
+  P.CacheGradients();
+  P.InitializeMeshData(cmax_el, calc_local_ct, global_ct);
+  std::vector<double> tau(nv, 0.0);
+  P.vertex_refdt.assign(nv, std::numeric_limits<double>::max());
+#pragma omp parallel for schedule(static)
+  for (int i = 0; i < nv; i++) P.vertex_refdt[i] = P.GetPoleHeight(i, tau);
+  std::vector<double> ktilde = P.vertex_refdt;
+  std::vector<int> latest_tent(nv, -1), vlevel(nv, 0), dep_src, dep_dst;
+  std::vector<char> complete(nv, 0), blocked(nv, 0), touched(nv, 0);
+  const double num_tol = std::numeric_limits<double>::epsilon() * dt;
+  // internal facets per vertex (D = 3), as in PitchTents
+  Csr v2f;
+  if (D == 3) {
+    v2f.off.assign(nv + 1, 0);
+    std::vector<std::vector<int>> rows(nv);
+#pragma omp parallel for schedule(dynamic, 256)
+    for (int vi = 0; vi < nv; vi++) {
+      std::vector<int>& r = rows[vi];
+      for (int i = 0; i < m.v2el.size(vi); i++) {
+        const int el = m.v2el.row(vi)[i];
+        for (int k = 0; k < 4; k++) {
+          const int f = m.el2facet[(size_t)el * 4 + k];
+          const int* fv = &m.facet2v[(size_t)f * 3];
+          if ((fv[0] == vi || fv[1] == vi || fv[2] == vi) && std::find(r.begin(), r.end(), f) == r.end()) r.push_back(f);
+        }
+      }
+    }
+    for (int vi = 0; vi < nv; vi++) v2f.off[vi + 1] = v2f.off[vi] + (int)rows[vi].size();
+    v2f.val.resize(v2f.off[nv]);
+    for (int vi = 0; vi < nv; vi++) std::copy(rows[vi].begin(), rows[vi].end(), v2f.val.begin() + v2f.off[vi]);
+  }
+  auto nfacets_of = [&](int vi) { return D == 1 ? 1 : (D == 2 ? m.v2e.size(vi) : v2f.size(vi)); };
+
+  std::vector<int> phase, sel, nbs;
+  bool slab_complete = false;
+  while (!slab_complete) {
+    // ---- the phase: ready vertices of minimal level (ready set from the state; advance factor halved up to 5 times)
+    phase.clear();
+    int L = 0;
+    double af = 0.5;
+    for (int ia = 0; ia < 5 && phase.empty(); ia++, af /= 2) {
+      int minlevel = std::numeric_limits<int>::max();
+#pragma omp parallel for reduction(min : minlevel) schedule(static)
+      for (int iv = 0; iv < nv; iv++)
+        if (!complete[iv] && ktilde[iv] > af * P.vertex_refdt[iv]) minlevel = std::min(minlevel, vlevel[iv]);
+      if (minlevel == std::numeric_limits<int>::max()) continue;
+      for (int iv = 0; iv < nv; iv++)
+        if (!complete[iv] && ktilde[iv] > af * P.vertex_refdt[iv] && vlevel[iv] == minlevel) phase.push_back(iv);
+      L = minlevel;
+    }
+    if (phase.empty()) break;
+    nlayers = std::max(nlayers, L);
+    // ---- lexicographically first maximal independent set of the phase
+    sel.clear();
+    for (int v : phase) {
+      if (blocked[v]) continue;
+      sel.push_back(v);
+      for (int i = 0; i < m.v2v.size(v); i++) blocked[m.v2v.row(v)[i]] = 1;
+    }
+    for (int v : sel)
+      for (int i = 0; i < m.v2v.size(v); i++) blocked[m.v2v.row(v)[i]] = 0;
+    // ---- tables of the new tents: offsets first, then the rows in parallel
+    const int n0 = ntents, ns = (int)sel.size();
+    vertex.resize(n0 + ns); level.resize(n0 + ns); tbot.resize(n0 + ns); ttop.resize(n0 + ns);
+    nbv.off.resize(n0 + ns + 1); els.off.resize(n0 + ns + 1); facets.off.resize(n0 + ns + 1);
+    for (int i = 0; i < ns; i++) {
+      const int v = sel[i];
+      nbv.off[n0 + i + 1] = nbv.off[n0 + i] + m.v2v.size(v);
+      els.off[n0 + i + 1] = els.off[n0 + i] + m.v2el.size(v);
+      facets.off[n0 + i + 1] = facets.off[n0 + i] + nfacets_of(v);
+    }
+    nbv.val.resize(nbv.off[n0 + ns]); nbtime.resize(nbv.off[n0 + ns]);
+    els.val.resize(els.off[n0 + ns]); facets.val.resize(facets.off[n0 + ns]);
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < ns; i++) {
+      const int v = sel[i], t = n0 + i;
+      vertex[t] = v;
+      level[t] = L;
+      tbot[t] = tau[v];
+      const double new_ttop = tau[v] + ktilde[v];
+      ttop[t] = (dt - new_ttop > num_tol) ? new_ttop : dt;
+      for (int k = 0; k < m.v2v.size(v); k++) {   // neighbours are not in the set: their heights are those before the phase
+        nbv.val[nbv.off[t] + k] = m.v2v.row(v)[k];
+        nbtime[nbv.off[t] + k] = tau[m.v2v.row(v)[k]];
+      }
+      for (int k = 0; k < m.v2el.size(v); k++) els.val[els.off[t] + k] = m.v2el.row(v)[k];
+      int* fo = &facets.val[facets.off[t]];
+      if (D == 1) fo[0] = v;
+      else if (D == 2) std::copy(m.v2e.row(v), m.v2e.row(v) + m.v2e.size(v), fo);
+      else std::copy(v2f.row(v), v2f.row(v) + v2f.size(v), fo);
+    }
+    // ---- state: dependencies (in tent and neighbour order, as the serial loop appends them), levels, front
+    nbs.clear();
+    for (int i = 0; i < ns; i++) {
+      const int v = sel[i], t = n0 + i;
+      for (int k = 0; k < m.v2v.size(v); k++) {
+        const int nb = m.v2v.row(v)[k];
+        if (vlevel[nb] < L + 1) vlevel[nb] = L + 1;
+        if (latest_tent[nb] != -1) { dep_src.push_back(latest_tent[nb]); dep_dst.push_back(t); }
+        if (!touched[nb]) { touched[nb] = 1; nbs.push_back(nb); }
+      }
+    }
+    for (int i = 0; i < ns; i++) {
+      const int v = sel[i], t = n0 + i;
+      latest_tent[v] = t;
+      vlevel[v] = L + 1;
+      if (!(dt - (tau[v] + ktilde[v]) > num_tol)) complete[v] = 1;
+      tau[v] = ttop[t];
+      ktilde[v] = 0;
+    }
+    const int nn = (int)nbs.size();
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < nn; i++) {
+      const int nb = nbs[i];
+      if (!complete[nb]) ktilde[nb] = P.GetPoleHeight(nb, tau);
+    }
+    for (int nb : nbs) touched[nb] = 0;
+    ntents = n0 + ns;
+    slab_complete = true;
+    for (int i = 0; i < nv; i++)
+      if (!complete[i]) { slab_complete = false; break; }
+  }
+  if (!slab_complete) std::printf("Error: the algorithm could not pitch the whole slab\n");
+  finalize_slab(*this, P, dep_src, dep_dst);
+  pitched = slab_complete;
+  return pitched;
+}
+
 // A slab from tents pitched elsewhere -- the fields python_tents.cpp:119-128 exposes of every Tent of a real
 // TentPitchedSlab (vertex, tbot, ttop, nbv, nbtime, els, level, internal_facets), flattened. The tents are taken as they
 // are (ids, order inside the lists, times); what the solver needs beyond them is derived here exactly as after pitching:

@@ -45,6 +45,10 @@ struct TentSlab {
   // returns false when the front could not reach dt (tents.cpp:265-288)
   bool PitchTents(double dt, bool local_ct, double global_ct);
 
+  // Level-synchronous pitcher with the partition-independent pick rule "ready vertex of minimal (level, vertex number)"
+  // (no reference counterpart; other tents than the reference's order). Parallel over the tents of a level.
+  bool PitchTentsLevelSync(double dt, bool local_ct, double global_ct);
+
   // Tents pitched elsewhere (the Tent fields of python_tents.cpp:119-128, flattened; *_off have n + 1 entries). level and
   // facet_off / facets may be null: levels are then replayed as the greedy loop assigns them, internal facets taken from
   // the mesh. Throws std::invalid_argument on lists that are inconsistent with the mesh or not level-schedulable.

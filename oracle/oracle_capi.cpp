@@ -52,6 +52,14 @@ int oracle_pitch(void* hp, int method, const double* cmax_el, double dt, int loc
   int rc = guarded([&] { ok = PitchTents(h->slab, h->ma, method, c, dt, local_ct != 0, global_ct) ? 1 : 0; });
   return rc ? rc : ok;
 }
+// the same with the partition-independent pick rule of the product's level-synchronous pitcher (rule 1)
+int oracle_pitch_rule(void* hp, int method, const double* cmax_el, double dt, int local_ct, double global_ct, int rule) {
+  auto* h = (OracleHandle*)hp;
+  std::vector<double> c(cmax_el, cmax_el + h->ma.nel);
+  int ok = 0;
+  int rc = guarded([&] { ok = PitchTents(h->slab, h->ma, method, c, dt, local_ct != 0, global_ct, rule) ? 1 : 0; });
+  return rc ? rc : ok;
+}
 int oracle_ntents(void* hp) { return (int)((OracleHandle*)hp)->slab.tents.size(); }
 int oracle_nlayers(void* hp) { return ((OracleHandle*)hp)->slab.GetNLayers(); }
 void oracle_sizes(void* hp, long long* sz) {

@@ -47,6 +47,6 @@ struct OSlab {
 };
 
 bool PitchTents(OSlab& slab, const OMesh& ma, int method, const std::vector<double>& cmax_el, double dt,
-                bool calc_local_ct, double global_ct);
+                bool calc_local_ct, double global_ct, int rule = 0);
 
 }  // namespace oracle

@@ -301,8 +301,11 @@ struct TentSlabPitcher {
 
 }  // namespace
 
+// rule 0: the reference's pick rule (first vertex of minimal level in the ready list, tents.cpp:431-443).
+// rule 1: the partition-independent rule of the product's level-synchronous pitcher (no reference counterpart): the ready
+// vertex of minimal (level, vertex number); the ready set is recomputed from the state whenever a level is exhausted.
 bool PitchTents(OSlab& slab, const OMesh& ma, int method, const std::vector<double>& cmax_el, double dt,
-                bool calc_local_ct, double global_ct) {
+                bool calc_local_ct, double global_ct, int rule) {
   const int DIM = ma.D;
   slab.ma = &ma;
   slab.tents.clear();
@@ -326,19 +329,46 @@ bool PitchTents(OSlab& slab, const OMesh& ma, int method, const std::vector<doub
   const double num_tol = std::numeric_limits<double>::epsilon() * dt;
   std::vector<OTent>& tents = slab.tents;
 
+  // rule 1: the vertices of the current phase (ready at its start, minimal level), ascending, and the position in it
+  std::vector<int> phase;
+  size_t phase_pos = 0;
+  int phase_level = 0;
   while (!slab_complete) {
-    const bool found_vertices =
-        pitcher.GetReadyVertices(adv_factor, reset_adv_factor, ktilde, complete_vertices, vertex_ready, ready_vertices);
-    if (!found_vertices) break;
-    while (ready_vertices.Size()) {
-      // PickNextVertexForPitching
-      int minlevel = std::numeric_limits<int>::max(), posmin = -1;
-      for (size_t i = 0; i < ready_vertices.Size(); i++)
-        if (vertices_level[ready_vertices[i]] < minlevel) { minlevel = vertices_level[ready_vertices[i]]; posmin = (int)i; }
-      slab.nlayers = std::max(minlevel, slab.nlayers);
-      const int vi = ready_vertices[posmin];
-      ready_vertices.DeleteElement(posmin);
-      vertex_ready[vi] = 0;
+    if (rule == 0) {
+      const bool found_vertices =
+          pitcher.GetReadyVertices(adv_factor, reset_adv_factor, ktilde, complete_vertices, vertex_ready, ready_vertices);
+      if (!found_vertices) break;
+    } else {
+      // ready set from the state: advance larger than adv_factor * reference height, the factor halved up to 5 times
+      phase.clear();
+      phase_pos = 0;
+      double af = 0.5;
+      for (int ia = 0; ia < 5 && phase.empty(); ia++, af /= 2) {
+        int minlevel = std::numeric_limits<int>::max();
+        for (int iv = 0; iv < ma.nv; iv++)
+          if (!complete_vertices[iv] && ktilde[iv] > af * pitcher.vertex_refdt[iv]) minlevel = std::min(minlevel, vertices_level[iv]);
+        for (int iv = 0; iv < ma.nv; iv++)
+          if (!complete_vertices[iv] && ktilde[iv] > af * pitcher.vertex_refdt[iv] && vertices_level[iv] == minlevel) phase.push_back(iv);
+        phase_level = minlevel;
+      }
+      if (phase.empty()) break;
+    }
+    while (rule == 0 ? ready_vertices.Size() > 0 : phase_pos < phase.size()) {
+      int vi;
+      if (rule == 0) {
+        // PickNextVertexForPitching
+        int minlevel = std::numeric_limits<int>::max(), posmin = -1;
+        for (size_t i = 0; i < ready_vertices.Size(); i++)
+          if (vertices_level[ready_vertices[i]] < minlevel) { minlevel = vertices_level[ready_vertices[i]]; posmin = (int)i; }
+        slab.nlayers = std::max(minlevel, slab.nlayers);
+        vi = ready_vertices[posmin];
+        ready_vertices.DeleteElement(posmin);
+        vertex_ready[vi] = 0;
+      } else {
+        vi = phase[phase_pos++];
+        if (vertices_level[vi] != phase_level) continue;  // a neighbour with a smaller number was pitched in this phase
+        slab.nlayers = std::max(phase_level, slab.nlayers);
+      }
 
       OTent tent;
       tent.vertex = vi;
@@ -372,7 +402,12 @@ bool PitchTents(OSlab& slab, const OMesh& ma, int method, const std::vector<doub
               }
           }
       tent.els = ma.v2el[vi];
-      pitcher.UpdateNeighbours(vi, adv_factor, tau, complete_vertices, ktilde, vertex_ready, ready_vertices);
+      if (rule == 0) {
+        pitcher.UpdateNeighbours(vi, adv_factor, tau, complete_vertices, ktilde, vertex_ready, ready_vertices);
+      } else {
+        for (int nb : ma.v2v[vi])
+          if (!complete_vertices[nb]) ktilde[nb] = pitcher.GetPoleHeight(nb, tau);
+      }
       tents.push_back(std::move(tent));
     }
     slab_complete = true;

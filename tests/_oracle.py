@@ -37,6 +37,7 @@ def _load():
     lib.oracle_destroy.argtypes = [C.c_void_p]
     lib.oracle_last_error.restype = C.c_char_p
     lib.oracle_pitch.argtypes = [C.c_void_p, C.c_int, c_dp, C.c_double, C.c_int, C.c_double]
+    lib.oracle_pitch_rule.argtypes = [C.c_void_p, C.c_int, c_dp, C.c_double, C.c_int, C.c_double, C.c_int]
     lib.oracle_ntents.argtypes = [C.c_void_p]
     lib.oracle_nlayers.argtypes = [C.c_void_p]
     lib.oracle_sizes.argtypes = [C.c_void_p, C.POINTER(C.c_longlong)]
@@ -133,9 +134,10 @@ class Oracle:
             lib.oracle_destroy(self.h)
             self.h = None
 
-    def pitch(self, dt, local_ct=False, global_ct=1.0, cmax=1.0, method="edge"):
+    def pitch(self, dt, local_ct=False, global_ct=1.0, cmax=1.0, method="edge", rule=0):
+        """rule 0: the reference's pick rule; rule 1: minimal (level, vertex number) -- the level-synchronous pitcher's."""
         c = np.ascontiguousarray(np.broadcast_to(np.asarray(cmax, dtype=np.float64), (self.nel,)))
-        rc = lib.oracle_pitch(self.h, 2 if method == "edge" else 1, _dp(c), float(dt), int(local_ct), float(global_ct))
+        rc = lib.oracle_pitch_rule(self.h, 2 if method == "edge" else 1, _dp(c), float(dt), int(local_ct), float(global_ct), int(rule))
         if rc < 0:
             raise RuntimeError(lib.oracle_last_error().decode())
         return bool(rc)

@@ -114,3 +114,37 @@ def test_tent_fields_and_tentdata1d(built):
     assert len(t0.nbv) == len(t0.nbtime) and len(t0.els) in (1, 2)
     with pytest.raises(IndexError):
         ts.GetTent(ts.GetNTents())
+
+
+# ---------------------------------------------------------------------------------------------- level-synchronous pitcher
+@pytest.mark.parametrize("D,mk,dt", [(1, lambda: ng.SegMesh(24, 0, 1), 0.5), (2, lambda: ng.UnitSquareMesh(7), 0.3),
+                                      (3, lambda: ng.UnitCubeMesh(4), 0.2), (3, lambda: ng.StructuredMesh([4, 2, 3], [0, 0, 0], [1, 0.6, 1.3]), 0.15)])
+@pytest.mark.parametrize("local_ct", [True, False])
+def test_level_sync_pitcher_equals_serial_loop_with_the_same_rule(built, D, mk, dt, local_ct):
+    """ngst_slab_pitch_level_sync picks the ready vertex of minimal (level, vertex number) and handles the ready vertices of
+    a level as one parallel phase; the oracle runs the SERIAL greedy loop with that pick rule. Every table must be bitwise
+    equal; the slab must be complete and causal; the level sets must be conflict-free."""
+    mesh = mk()
+    ts = ng.TentSlab(mesh, "edge")
+    ts.SetMaxWavespeed(1.0)
+    assert ts.PitchTents(dt, local_ct, 2 / 3, level_sync=True)
+    o = Oracle(mesh)
+    assert o.pitch(dt, local_ct, 2 / 3, 1.0, rule=1)
+    e, eo = ts.export(), o.export()
+    assert [k for k in eo if not np.array_equal(e[k], eo[k])] == []
+    assert ts.GetNLayers() == o.nlayers()
+    # complete: the last tent of every vertex reaches the slab height; causal: slopes below 1 / c
+    top = np.zeros(mesh.nv)
+    np.maximum.at(top, e["vertex"], e["ttop"])
+    assert np.all(top == dt)
+    if local_ct:  # (without the local constant the edge algorithm does not guarantee causality in 3-D, whatever the pick rule)
+        assert ts.MaxSlope() <= 1.0 + 1e-12
+    # tents of one level share no element
+    for l in range(int(e["level"].max()) + 1):
+        els = np.concatenate([e["els"][e["el_off"][t]:e["el_off"][t + 1]] for t in np.flatnonzero(e["level"] == l)])
+        assert len(els) == len(np.unique(els))
+    # other tents than the reference's pick rule (that is the point), not more of them on these meshes
+    ref = ng.TentSlab(mesh, "edge")
+    ref.SetMaxWavespeed(1.0)
+    assert ref.PitchTents(dt, local_ct, 2 / 3)
+    assert ts.GetNLayers() <= ref.GetNLayers()
