@@ -345,3 +345,29 @@ def test_pointwise_wavespeed_in_error_plain_trefftz(built):
     ref = o.wavefront()
     scale = math.sqrt(2 * o.energy(ref))
     assert abs(err - o.error(ref, o.make_wavefront(f, 1.0))) <= 10 * forced_tol(o, "plain Trefftz, c = x + 1") * scale
+
+
+@pytest.mark.parametrize("D,mk,order,dt", [(2, lambda: ng.UnitSquareMesh(5), 4, 0.3), (3, lambda: ng.UnitCubeMesh(4), 4, 0.2)])
+def test_parity_on_level_sync_tents(built, D, mk, order, dt):
+    """The solver on the tents of the level-synchronous pitcher (ngst_slab_pitch_level_sync, pick rule "minimal (level, vertex
+    number)") against the oracle on ITS serial loop with the same rule: tables bitwise, wavefront to 1e-10."""
+    f = standing(D)
+    mesh = mk()
+    ts = ng.TentSlab(mesh, "edge")
+    ts.SetMaxWavespeed(1.0)
+    assert ts.PitchTents(dt, True, 2 / 3, level_sync=True)
+    o = Oracle(mesh)
+    assert o.pitch(dt, True, 2 / 3, 1.0, rule=1)
+    e1, e2 = ts.export(), o.export()
+    for k in e2:
+        assert np.array_equal(e1[k], e2[k]), f"tent table {k} differs"
+    tw = ng.TWave(order, ts, 1.0)
+    tw.SetInitial(f)
+    tw.SetBoundaryCF(dirichlet(f, D))
+    o.setup(order, 1.0)
+    o.set_initial(f)
+    o.set_boundary_cf(dirichlet(f, D))
+    for _ in range(2):
+        tw.Propagate()
+        o.propagate()
+    check(tw, o)
