@@ -306,6 +306,16 @@ def run_ours(args):
     t0 = time.perf_counter()
     assert ts.PitchTents(args.dt, True, 2 / 3)
     pitch_s = time.perf_counter() - t0
+    # informational: the level-synchronous pitcher (partition-independent pick rule, other tents) on the same mesh
+    pitch_ls = None
+    if rank == 0:
+        ts2 = ng.TentSlab(mesh, "edge")
+        ts2.SetMaxWavespeed(1.0)
+        t0 = time.perf_counter()
+        ok2 = ts2.PitchTents(args.dt, True, 2 / 3, level_sync=True)
+        pitch_ls = {"s": time.perf_counter() - t0, "tents": ts2.GetNTents(), "levels": ts2.GetNLayers(), "ok": bool(ok2),
+                    "omp_threads": os.environ.get("OMP_NUM_THREADS", "all")}
+        del ts2
     if world > 1:
         owner = ng.balanced_vertex_owner(ts, grid) if args.partition == "balanced" else ng.brick_vertex_owner(mesh, grid)
         tw = ng.TWave(order, ts, 1.0, device=local, partition=(rank, world, owner))
@@ -736,7 +746,7 @@ def run_ours(args):
                                     f"per-level NCCL halo exchange {'after' if args.no_overlap else 'overlapped with'} the interior tents"))
                                   if world > 1 else "single GPU",
                    "l2": f"state {wf0.nbytes * world / 1e6:.0f} MB per slab > 126 MB L2 (no flush needed)",
-                   "pitch_s": pitch_s,
+                   "pitch_s": pitch_s, "pitch_level_sync": pitch_ls,
                    "exchange": (tw.peer_exchange()[1] if tw.peer_exchange()[0] else "per-level NCCL send/recv ("
                                 + tw.peer_exchange()[1] + ")") if world > 1 else None,
                    "numa_binding_rank0": numa,
