@@ -51,6 +51,8 @@ def parse():
     ap.add_argument("--no-factor-cache", action="store_true",
                     help="assemble and solve every tent system in every Propagate (no stored inverses): the headline becomes the "
                          "cold figure that is otherwise reported beside it as `assembly_every_step`")
+    ap.add_argument("--apply-four-ctas", action="store_true",
+                    help="factor cache: apply kernel variant with 128 registers / 55 KB shared memory, four CTAs per SM (A/B)")
     ap.add_argument("--no-compact-state", action="store_true", help="tents read / write the public order-2p rows (A/B)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -337,6 +339,8 @@ def run_ours(args):
         tw.set_compact_state(False)
     if args.no_factor_cache:
         tw.set_factor_cache(False)
+    elif args.apply_four_ctas:
+        tw.set_factor_cache(2)
     e = ts.export()
     ntents_global = ts.GetNTents()
     mine = tw.owned_tents() if world > 1 else np.arange(ntents_global)
@@ -413,7 +417,7 @@ def run_ours(args):
             cold_launches += tw.last_launches()
         barrier()
         cold = {"sec": float(np.sum(cold_ms)) * 1e-3, "launches": cold_launches}
-        tw.set_factor_cache(True)
+        tw.set_factor_cache(2 if args.apply_four_ctas else True)
 
     # ---------------- e2e arm: the plugin call sequence with HOST buffers inside the timed region
     e2e = None

@@ -735,7 +735,7 @@ class TWaveTents(TrefftzTents):
     def set_factor_cache(self, on=True):
         """Keep the inverse of every tent matrix in HBM after the first Propagate (default) or assemble and solve in every
         Propagate (ngst_twave_set_factor_cache)."""
-        check(lib.ngst_twave_set_factor_cache(self._h, int(bool(on))))
+        check(lib.ngst_twave_set_factor_cache(self._h, int(on)))  # 2 = apply variant with four CTAs per SM (A/B)
 
     def factor_cache(self):
         """(state, bytes): state 0 = not in use, 1 = next Propagate builds it, 2 = next Propagate applies it."""

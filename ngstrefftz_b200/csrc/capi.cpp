@@ -497,7 +497,7 @@ int ngst_twave_set_compact_state(ngst_twave* t, int on) {
 int ngst_twave_compact_state(const ngst_twave* t) { return t && t->solver->compact_state_active() ? 1 : 0; }
 
 int ngst_twave_set_factor_cache(ngst_twave* t, int on) {
-  return guarded([&] { need(t, "solver"); t->solver->set_factor_cache(on != 0); });
+  return guarded([&] { need(t, "solver"); t->solver->set_factor_cache(on != 0, on == 2); });
 }
 int ngst_twave_factor_cache(const ngst_twave* t, long long* bytes) {
   if (bytes) *bytes = t ? (long long)t->solver->factor_cache_bytes() : 0;

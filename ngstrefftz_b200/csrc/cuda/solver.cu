@@ -1002,7 +1002,7 @@ void Solver::Propagate(int level_limit) {
     }
     if (d_ainv_[fo]) {
       fa.ainv = d_ainv_[fo];
-      fa.mode = ainv_valid_[fo] ? 2 : 1;
+      fa.mode = ainv_valid_[fo] ? (apply_four_ctas_ ? 3 : 2) : 1;
     }
   }
   // factor cache of the generic kernel (small systems): inverses formed by the first full Propagate, applied afterwards
@@ -1082,7 +1082,7 @@ void Solver::Propagate(int level_limit) {
   const bool small_levels = slab_.ntents < 2 * 444 * nlev;
   // (r04d, B200: with stored inverses a tent is 6x cheaper and the single launch wins at config 4 as well, 11.74 vs 12.17 ms;
   // not with an output mirror, whose copies overlap the per-level launches)
-  const bool cheap_tents = fa.mode == 2 && !mirror_dev_;
+  const bool cheap_tents = fa.mode >= 2 && !mirror_dev_;
   const bool dag = dag_ && (dag_mode_ == 2 || (dag_mode_ == 1 && (small_levels || cheap_tents))) && !force_generic_ && !comm_ && !partial &&
                    !sweep;
   if (sweep) {

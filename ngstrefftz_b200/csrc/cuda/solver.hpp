@@ -113,7 +113,7 @@ class Solver {
   // Factor cache (tent_fast.cu MODE 1 / 2; default on, needs the compact state): the inverse of every tent matrix is formed
   // by the first Propagate and stored in HBM (NP x N doubles per tent); later Propagates of the same slab geometry only
   // build right-hand sides, apply the stored inverses and evaluate. off: assemble and solve in every Propagate.
-  void set_factor_cache(bool on) { factor_cache_enabled_ = on; }
+  void set_factor_cache(bool on, bool four_ctas = false) { factor_cache_enabled_ = on; apply_four_ctas_ = four_ctas; }
   // multi-GPU: exchange inside the tent kernel over peer memory (default where it could be set up) or per level with NCCL
   void set_peer_exchange(bool on, bool halo_first = false) { p2p_enabled_ = on; p2p_halo_first_ = halo_first; }
   bool peer_exchange_active() const { return p2p_ready_ && p2p_enabled_ && UseCompact() && !qt_; }
@@ -280,6 +280,7 @@ class Solver {
   bool ginv_valid_[2] = {false, false}, ginv_failed_ = false;
   size_t smem_build_ = 0;                   // shared memory of the generic kernel while it forms the inverses
   bool factor_cache_enabled_ = true, cache_failed_ = false;
+  bool apply_four_ctas_ = false;   // apply variant with 128 registers / 55 KB: four CTAs per SM, inverse read from L2 (A/B)
   double* d_ainv_[2] = {nullptr, nullptr};  // [fosystem]
   size_t ainv_bytes_[2] = {0, 0};
   bool ainv_valid_[2] = {false, false};

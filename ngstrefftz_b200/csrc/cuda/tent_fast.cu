@@ -94,6 +94,17 @@ struct Cfg {
   static constexpr int oCMD2 = oCM2 + npoly;
   static constexpr int oRHS2 = (oCMD2 + d1 * npm1 + 1) / 2 * 2;
   static constexpr int nsmem2 = oRHS2 + NP;
+  // MODE 3 (apply, four CTAs per SM): the stored inverse is read from L2 by the product instead of being staged:
+  // [partial sums | rows | b | cm | cmd | rhs] within 55 KB
+  static constexpr int oRows3 = 4 * NP;
+  static constexpr int budget3 = 55 * 1024 / 8;
+  static constexpr int capRows3raw = (budget3 - oRows3 - tail2) / ROWLEN;
+  static constexpr int capRows3 = capRows3raw > 32 ? 32 : (capRows3raw < 1 ? 1 : capRows3raw);
+  static constexpr int oB3 = (oRows3 + capRows3 * ROWLEN + 1) / 2 * 2;
+  static constexpr int oCM3 = (oB3 + NP + 1) / 2 * 2;
+  static constexpr int oCMD3 = oCM3 + npoly;
+  static constexpr int oRHS3 = (oCMD3 + d1 * npm1 + 1) / 2 * 2;
+  static constexpr int nsmem3 = oRHS3 + NP;
 };
 
 // group dispatch: warp w evaluates the functions i with i % 4 == w
@@ -137,7 +148,7 @@ __device__ __forceinline__ void eval_part(int part, const double* xi, F&& f) {
 // stores it in HBM (f.ainv, transposed), then applies it. MODE 2 skips the assembly: right-hand side, sol = A^-1 b with
 // the stored inverse (fetched by one bulk asynchronous copy behind the right-hand-side pass), evaluation.
 template <int D, int P, int FO, int CS, int MODE>
-__global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(TentKernelArgs a, FastArgs f) {
+__global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : (MODE == 3 ? 4 : 3)) tent_kernel_fast(TentKernelArgs a, FastArgs f) {
   using C = Cfg<D, P, FO>;
   static_assert(!CS || (C::QS > 0 && C::rhsFirst), "compact state needs the compact degree-2P rule");
   static_assert(MODE == 0 || CS, "the factor cache is built on the compact-state variant");
@@ -145,15 +156,16 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
   constexpr int NACC = C::NACC, FE = C::FE, FF = C::FF, npoly = C::npoly, npm1 = C::npm1;
   extern __shared__ __align__(16) double sm[];
   double* const A = sm + C::oA;
-  double* const bv = sm + (MODE == 2 ? C::oB2 : C::oB);
+  constexpr bool APPLY = MODE >= 2;  // MODE 3: as 2 with 128 registers, 55 KB of shared memory, four CTAs per SM
+  double* const bv = sm + (MODE == 2 ? C::oB2 : (MODE == 3 ? C::oB3 : C::oB));
   double* const Z = sm + C::oZ;
-  double* const cm = sm + (MODE == 2 ? C::oCM2 : C::oCM);
-  double* const cmd = sm + (MODE == 2 ? C::oCMD2 : C::oCMD);
-  double* const rhsS = sm + (MODE == 2 ? C::oRHS2 : C::oRHS);
+  double* const cm = sm + (MODE == 2 ? C::oCM2 : (MODE == 3 ? C::oCM3 : C::oCM));
+  double* const cmd = sm + (MODE == 2 ? C::oCMD2 : (MODE == 3 ? C::oCMD3 : C::oCMD));
+  double* const rhsS = sm + (MODE == 2 ? C::oRHS2 : (MODE == 3 ? C::oRHS3 : C::oRHS));
   // compact rows of the tent's elements, fetched by bulk asynchronous copies (cp.async.bulk) ahead of the right-hand-side pass
   constexpr bool STG = CS && C::stageRows;
-  constexpr int kRowCap = STG ? (MODE == 2 ? C::capRows2 : C::capRows01) : (1 << 30);
-  double* const rowsS = sm + (MODE == 2 ? C::oRows2 : C::oRows01);
+  constexpr int kRowCap = STG ? (MODE == 2 ? C::capRows2 : (MODE == 3 ? C::capRows3 : C::capRows01)) : (1 << 30);
+  double* const rowsS = sm + (MODE == 2 ? C::oRows2 : (MODE == 3 ? C::oRows3 : C::oRows01));
 
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const int g = lane >> 2, k = lane & 3;  // DMMA fragment coordinates
@@ -208,7 +220,7 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
   double* const invS = sm + C::oInv2;
   [[maybe_unused]] double* const invG = (MODE != 0) ? f.ainv + (size_t)tent * (NP * N) : nullptr;
   __shared__ __align__(8) unsigned long long s_bar, s_bar_rows;
-  if constexpr (MODE == 2 || STG) {
+  if constexpr (APPLY || STG) {
     if (tid == 0) {
       tma::mbar_init(&s_bar, 1);
       tma::mbar_init(&s_bar_rows, 1);
@@ -220,6 +232,9 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
       tma::mbar_expect(&s_bar, NP * N * 8);
       tma::bulk_load(invS, invG, NP * N * 8, &s_bar);
     }
+  }
+  if constexpr (MODE == 3) {  // the stored inverse towards L2 now; the product reads it from there after the first pass
+    for (int i = tid * 16; i < NP * N; i += kThreads * 16) asm volatile("prefetch.global.L2 [%0];" ::"l"(invG + i));
   }
 
   if (C::rhsFirst) {
@@ -423,7 +438,7 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
   double bpart[G];
 #pragma unroll
   for (int j = 0; j < G; j++) bpart[j] = 0.0;
-  if constexpr (MODE != 2) {  // ============================ assembly of the tent matrix (skipped when its inverse is stored)
+  if constexpr (!APPLY) {  // ============================ assembly of the tent matrix (skipped when its inverse is stored)
   for (int i = tid; i < NP * ZS; i += kThreads) Z[i] = 0.0;  // rows of the padding functions stay zero
   double acc[NACC][2];
 #pragma unroll
@@ -699,6 +714,8 @@ __global__ void __launch_bounds__(kThreads, MODE == 1 ? 2 : 3) tent_kernel_fast(
       gauss_jordan_invert<N, NP, kThreads>(A, LDA, nfc == 0, a.singular, invG);
       __syncthreads();  // the inverse this CTA has just written is visible to all of its threads
       inv = invG;
+    } else if constexpr (MODE == 3) {
+      inv = invG;
     } else {
       tma::mbar_wait(&s_bar, 0);
       inv = invS;
@@ -881,7 +898,7 @@ cudaError_t launch_cfg(const TentKernelArgs& a, const FastArgs& f, cudaStream_t 
   if ((C::splitStab || CS) && f.Qs != C::QS) return cudaErrorInvalidValue;
   if (CS && (!f.cstate || !f.te_final || !f.w_stab)) return cudaErrorInvalidValue;
   if (MODE != 0 && !f.ainv) return cudaErrorInvalidValue;
-  const size_t smem = sizeof(double) * (MODE == 2 ? C::nsmem2 : C::nsmem);
+  const size_t smem = sizeof(double) * (MODE == 2 ? C::nsmem2 : (MODE == 3 ? C::nsmem3 : C::nsmem));
   // the attribute is per device: one flag per device ordinal, not per process (a process may hold solvers on several GPUs)
   static bool configured[64] = {};  // (one flag set per template instance)
   int dev = 0;
@@ -903,6 +920,7 @@ cudaError_t launch_any(const TentKernelArgs& a, const FastArgs& f, cudaStream_t 
     if (f.cstate) {
       if (f.mode == 1) return launch_cfg<D, P, FO, 1, 1>(a, f, stream);
       if (f.mode == 2) return launch_cfg<D, P, FO, 1, 2>(a, f, stream);
+      if (f.mode == 3) return launch_cfg<D, P, FO, 1, 3>(a, f, stream);
       return launch_cfg<D, P, FO, 1, 0>(a, f, stream);
     }
   } else {

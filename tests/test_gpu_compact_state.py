@@ -203,3 +203,23 @@ def test_factor_cache_follows_the_system(built):
     ref.Propagate()
     a, b = tw.GetWavefront(), ref.GetWavefront()
     assert np.abs(a - b).max() <= 5e-11 * np.abs(b).max()
+
+
+def test_apply_variant_with_four_ctas_is_bitwise_the_default_one(built):
+    """set_factor_cache(2): the apply kernel compiled for 128 registers / 55 KB (four CTAs per SM), reading the stored inverse
+    from L2 instead of staging it in shared memory -- same arithmetic, same bits."""
+    f = standing(3)
+    mesh = ng.UnitCubeMesh(5)
+    ts = ng.TentSlab(mesh, "edge")
+    ts.SetMaxWavespeed(1.0)
+    assert ts.PitchTents(0.1, True, 2 / 3)
+    out = []
+    for variant in (True, 2):
+        tw = ng.TWave(4, ts, 1.0)
+        tw.set_factor_cache(variant)
+        tw.SetInitial(f)
+        tw.SetBoundaryCF(dirichlet(f, 3))
+        for _ in range(3):
+            tw.Propagate()
+        out.append(tw.GetWavefront())
+    assert np.array_equal(out[0], out[1])
