@@ -280,6 +280,16 @@ int ngst_twave_set_mirror_ctas(ngst_twave* t, int ctas);
 int ngst_twave_get_wave(ngst_twave* t, int* sizes, double* coef, double* psi_at_points, double* mono_coef, int* expo);
 /* Energy / Error / L2Error src/twavetents.cpp:766-847 on host wavefronts (nel x ncomp*nip) */
 int ngst_twave_energy(ngst_twave* t, const double* wf, double* out);
+/* Energy of the RESIDENT state (what ngst_twave_energy(t, NULL, out) returns, same summation order, same bits) for
+ * callers that must not allocate: no counterpart in the reference. The
+ * per-element partial sums and the result slot live in a file-scope `static __device__` array of the library
+ * (ngst_twave_energy_noalloc_max_elements() = 262 144 elements, 2 MB held by every GPU that loads the library until
+ * exit); the call does no cudaMalloc / cudaFree and no host allocation: two kernel launches, one 8-byte copy into *out
+ * and a stream synchronisation on the solver's stream. Single-GPU solvers only; more elements than the maximum ->
+ * NGST_ERR_ARG (use ngst_twave_energy). All calls on a GPU share the array -- it keeps the last call's contents, none of
+ * which is read by the next call -- so calls that overlap on the GPU (two solvers from two host threads) race. */
+int ngst_twave_energy_resident_noalloc(ngst_twave* t, double* out);
+int ngst_twave_energy_noalloc_max_elements(void);
 int ngst_twave_error(ngst_twave* t, const double* wf, const double* wf_ref, double* out);
 int ngst_twave_l2error(ngst_twave* t, const double* wf, const double* wf_ref, double* out);
 /* MaxAdiam src/twavetents.cpp:906-914 */

@@ -831,6 +831,13 @@ class TWaveTents(TrefftzTents):
         check(lib.ngst_twave_energy(self._h, dptr(wf), C.byref(out)))
         return out.value
 
+    def EnergyNoAlloc(self):
+        """Energy of the resident state through ngst_twave_energy_resident_noalloc: static device scratch, no allocation
+        (no counterpart in the reference; at most ngst_twave_energy_noalloc_max_elements() elements, single-GPU solvers)."""
+        out = C.c_double(0)
+        check(lib.ngst_twave_energy_resident_noalloc(self._h, C.byref(out)))
+        return out.value
+
     def MaxAdiam(self):
         out = C.c_double(0)
         check(lib.ngst_twave_max_adiam(self._h, C.byref(out)))

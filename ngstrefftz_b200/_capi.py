@@ -107,6 +107,8 @@ _SIGS = {
     "ngst_twave_get_wavefront": (C.c_int, [c_vp, c_dp]),
     "ngst_twave_get_wave": (C.c_int, [c_vp, c_ip, c_dp, c_dp, c_dp, c_ip]),
     "ngst_twave_energy": (C.c_int, [c_vp, c_dp, c_dp]),
+    "ngst_twave_energy_resident_noalloc": (C.c_int, [c_vp, c_dp]),
+    "ngst_twave_energy_noalloc_max_elements": (C.c_int, []),
     "ngst_twave_error": (C.c_int, [c_vp, c_dp, c_dp, c_dp]),
     "ngst_twave_l2error": (C.c_int, [c_vp, c_dp, c_dp, c_dp]),
     "ngst_twave_max_adiam": (C.c_int, [c_vp, c_dp]),

@@ -528,6 +528,12 @@ int ngst_twave_energy(ngst_twave* t, const double* wf, double* out) {
   return guarded([&] { need(t, "solver"); need(out, "out"); *out = t->solver->Energy(wf); });
 }
 
+int ngst_twave_energy_resident_noalloc(ngst_twave* t, double* out) {
+  return guarded([&] { need(t, "solver"); need(out, "out"); t->solver->EnergyResidentNoAlloc(out); });
+}
+
+int ngst_twave_energy_noalloc_max_elements(void) { return ngst::static_reduce_max_elements(); }
+
 int ngst_twave_error(ngst_twave* t, const double* wf, const double* wf_ref, double* out) {
   return guarded([&] {
     need(t, "solver"); need(wf, "wf"); need(wf_ref, "wf_ref"); need(out, "out");

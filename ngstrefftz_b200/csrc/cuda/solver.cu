@@ -1637,6 +1637,17 @@ double Solver::Energy(const double* wf) {
   return ReduceElements(src, nullptr, 0);
 }
 
+void Solver::EnergyResidentNoAlloc(double* out) {
+  if (!have_initial_) throw std::logic_error("Energy: SetInitial has not been called");
+  if (plan_) throw std::logic_error("ngst_twave_energy_resident_noalloc: single-GPU solvers only (a partitioned solver sums over ranks)");
+  if (nel_ > static_reduce_max_elements())
+    throw std::invalid_argument("ngst_twave_energy_resident_noalloc: " + std::to_string(nel_) + " elements exceed the static scratch of " +
+                                std::to_string(static_reduce_max_elements()) + " elements; use ngst_twave_energy");
+  CU(cudaSetDevice(device_));
+  FinishLoad();
+  CU(launch_energy_static(mesh_.D, nel_, rule_.nip, ncomp_, fosystem_, d_elw_, args_.c_el, d_cpoint_, d_wavefront_, out, stream_));
+}
+
 double Solver::Error(const double* wf, const double* ref, bool l2only) {
   if (!have_initial_) throw std::logic_error("Error: SetInitial has not been called");
   CU(cudaSetDevice(device_));

@@ -87,6 +87,9 @@ class Solver {
   // holds what GetWavefront would copy (partitioned solvers: their local rows). nullptr switches the mirror off.
   void SetOutputMirror(double* host);
   double Energy(const double* wf);
+  // Energy of the resident state without cudaMalloc / cudaFree / host allocation (scratch: static device array in
+  // reduce.cu, shared by all calls on a GPU). Single-GPU solvers with at most static_reduce_max_elements() elements.
+  void EnergyResidentNoAlloc(double* out);
   double Error(const double* wf, const double* ref, bool l2only);
   double MaxAdiam() const;
   // GetWave (src/__init__.py:7-43): L2 projection of the state onto polynomials, element by element. Second-order state:
@@ -309,6 +312,10 @@ cudaError_t launch_mirror_rows(const int* rows, int nrows, int rowlen, const dou
 cudaError_t launch_element_reduce(int mode, int D, int nel, int Q, int ncomp, int fosystem, const double* elw,
                                   const double* c_el, const double* c_point, const double* a, const double* b,
                                   double* out, cudaStream_t stream);
+// Energy with scratch and result slot in a file-scope device array (reduce.cu): no allocation; nel <= static_reduce_max_elements()
+int static_reduce_max_elements();
+cudaError_t launch_energy_static(int D, int nel, int Q, int ncomp, int fosystem, const double* elw, const double* c_el,
+                                 const double* c_point, const double* a, double* host_out, cudaStream_t stream);
 
 // fp64_peak.cu: which 0 = DFMA pipe, 1 = DMMA (mma.sync m8n8k4 f64); TFLOP/s on the current device
 cudaError_t measure_fp64_peak(int which, int reps, double* tflops);
