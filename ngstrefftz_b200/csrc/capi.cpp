@@ -497,7 +497,13 @@ int ngst_twave_set_compact_state(ngst_twave* t, int on) {
 int ngst_twave_compact_state(const ngst_twave* t) { return t && t->solver->compact_state_active() ? 1 : 0; }
 
 int ngst_twave_set_factor_cache(ngst_twave* t, int on) {
-  return guarded([&] { need(t, "solver"); t->solver->set_factor_cache(on != 0, on == 2); });
+  return guarded([&] {
+    need(t, "solver");
+    if (on < 0 || on > 5) throw std::invalid_argument("ngst_twave_set_factor_cache: on must be 0..5");
+    // generic kernel, stored inverses: 3 = a warp per tent (1-D: lanes-as-functions kernel), 4 = a CTA per tent, 5 = the CTA code on a warp
+    if (on >= 3) t->solver->set_generic_warp_apply(on == 3 ? 2 : (on == 5 ? 1 : 0));
+    else t->solver->set_factor_cache(on != 0, on == 2);
+  });
 }
 int ngst_twave_factor_cache(const ngst_twave* t, long long* bytes) {
   if (bytes) *bytes = t ? (long long)t->solver->factor_cache_bytes() : 0;

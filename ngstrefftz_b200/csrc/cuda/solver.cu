@@ -1008,6 +1008,7 @@ void Solver::Propagate(int level_limit) {
   // factor cache of the generic kernel (small systems): inverses formed by the first full Propagate, applied afterwards
   args_.ginv = nullptr;
   args_.gmode = 0;
+  args_.gwarp = 0;
   size_t gen_smem = smem_;
   if (GenericCachePossible() && (ginv_valid_[fosystem_] || !partial)) {
     const int fo = fosystem_;
@@ -1025,6 +1026,7 @@ void Solver::Propagate(int level_limit) {
     if (d_ginv_[fo]) {
       args_.ginv = d_ginv_[fo];
       args_.gmode = ginv_valid_[fo] ? 2 : 1;
+      args_.gwarp = args_.gmode == 2 ? GenericWarpApply() : 0;
       if (args_.gmode == 1) {
         TentKernelArgs probe = args_;
         gen_smem = tent_generic_smem_bytes(mesh_.D, probe);
@@ -1635,6 +1637,17 @@ double Solver::Energy(const double* wf) {
     src = d_tmp_a_;
   }
   return ReduceElements(src, nullptr, 0);
+}
+
+// the next Propagate applies stored inverses of the generic kernel with one warp per tent
+int Solver::GenericWarpApply() const {
+  if (!generic_warp_apply_ || !GenericCachePossible() || !ginv_valid_[fosystem_] || !d_ginv_[fosystem_]) return 0;
+  if (generic_warp_apply_ == 2 && mesh_.D == 1 && tent_small1d_supported(args_)) {
+    int nnz = 0;
+    for (int i = 0; i < basis_.nbasis; i++) nnz = std::max(nnz, basis_.rowptr[i + 1] - basis_.rowptr[i]);
+    if (nnz <= 8) return 2;
+  }
+  return tent_generic_warp_smem_bytes(mesh_.D, args_) <= 100 * 1024 ? 1 : 0;
 }
 
 void Solver::EnergyResidentNoAlloc(double* out) {

@@ -101,7 +101,7 @@ class Solver {
 
   double timeshift() const { return timeshift_; }
   void set_timeshift(double t) { timeshift_ = t; }
-  const char* kernel_name() const { return qt_ ? ((qtfast_ && !force_generic_ && !fosystem_) ? "tent_kernel_qt_fast" : "tent_kernel_qt") : ((fast_ && !force_generic_) ? "tent_kernel_fast" : "tent_kernel_generic"); }
+  const char* kernel_name() const { if (!qt_ && !(fast_ && !force_generic_) && GenericWarpApply()) return GenericWarpApply() == 2 ? "tent_kernel_small1d" : "tent_kernel_generic_warp"; return qt_ ? ((qtfast_ && !force_generic_ && !fosystem_) ? "tent_kernel_qt_fast" : "tent_kernel_qt") : ((fast_ && !force_generic_) ? "tent_kernel_fast" : "tent_kernel_generic"); }
   int ntents_fast() const { return (fast_ || qtfast_) ? fast_off_.back() : 0; }
   // 0 = automatic routing (fast kernel where possible), 1 = every tent on the generic DFMA kernel (A/B evidence)
   // 0: fast kernel where available (default), 1: generic kernel everywhere, 2: fast kernel with one launch per level
@@ -117,6 +117,10 @@ class Solver {
   // by the first Propagate and stored in HBM (NP x N doubles per tent); later Propagates of the same slab geometry only
   // build right-hand sides, apply the stored inverses and evaluate. off: assemble and solve in every Propagate.
   void set_factor_cache(bool on, bool four_ctas = false) { factor_cache_enabled_ = on; apply_four_ctas_ = four_ctas; }
+  // generic kernel, stored inverses: one warp per tent (tent_kernel_generic<D, true>) instead of one CTA
+  // (0 = CTA per tent, 1 = the CTA code on a warp, 2 = automatic: the 1-D lanes-as-functions kernel where it applies)
+  void set_generic_warp_apply(int mode) { generic_warp_apply_ = mode; }
+  int GenericWarpApply() const;   // 0 = CTA, 1 = tent_kernel_generic<D, true>, 2 = tent_kernel_small1d
   // multi-GPU: exchange inside the tent kernel over peer memory (default where it could be set up) or per level with NCCL
   void set_peer_exchange(bool on, bool halo_first = false) { p2p_enabled_ = on; p2p_halo_first_ = halo_first; }
   bool peer_exchange_active() const { return p2p_ready_ && p2p_enabled_ && UseCompact() && !qt_; }
@@ -283,6 +287,7 @@ class Solver {
   bool ginv_valid_[2] = {false, false}, ginv_failed_ = false;
   size_t smem_build_ = 0;                   // shared memory of the generic kernel while it forms the inverses
   bool factor_cache_enabled_ = true, cache_failed_ = false;
+  int generic_warp_apply_ = 0;  // stored inverses of the generic kernel applied by one warp per tent (set_generic_warp_apply)
   bool apply_four_ctas_ = false;   // apply variant with 128 registers / 55 KB: four CTAs per SM, inverse read from L2 (A/B)
   double* d_ainv_[2] = {nullptr, nullptr};  // [fosystem]
   size_t ainv_bytes_[2] = {0, 0};
@@ -304,6 +309,8 @@ class Solver {
 
 // kernels (tent_generic.cu, reduce.cu)
 size_t tent_generic_smem_bytes(int D, const TentKernelArgs& a);
+bool tent_small1d_supported(const TentKernelArgs& a);   // sizes tent_kernel_small1d (gwarp 2) is compiled for
+size_t tent_generic_warp_smem_bytes(int D, const TentKernelArgs& a);  // per CTA of the warp-per-tent variant (gmode 2, gwarp)
 cudaError_t launch_tent_generic(int D, const TentKernelArgs& a, int threads, size_t smem, cudaStream_t stream);
 cudaError_t launch_project_rows(int nel, int Q, int ndof, int comp0, int ncomp_used, int rowlen, const double* P,
                                 const double* wf, double* out, cudaStream_t stream, const int* elems = nullptr);

@@ -6,11 +6,25 @@
 //   CalcTentElEval (541-590), with the basis evaluation of ScalarMappedElement<D+1>::CalcShape /
 //   CalcDShape (src/scalarmappedfe.cpp:437-674) done on the fly in shared memory.
 // Shared-memory operand layout: E[(v*Qc + q)*Npad + i], v = 0 value, v = 1+d derivative in direction d.
+//
+// WARP = true (apply mode of the factor cache only, gmode 2): one WARP per tent instead of one CTA -- the same statements
+// in the same order, executed by the 32 lanes of a warp with __syncwarp() in place of __syncthreads() and a private slice
+// of shared memory without the matrix and Gram operands. Systems of the cache have at most 32 unknowns (1-D tents,
+// BASELINE configs[1]): a CTA per tent leaves most of its threads idle and pays a block-wide barrier per step.
 #include <cuda_runtime.h>
 
 #include "tent_kernel.cuh"
 
 namespace ngst {
+
+constexpr int kGenericWarpsPerCta = 4;
+
+// doubles of shared memory one warp of the warp-per-tent variant owns: [b | E0 | rr | pw | mono | pt], rounded up to even
+__host__ __device__ inline size_t generic_warp_doubles(int D, const TentKernelArgs& a) {
+  const size_t d1 = D + 1, nv = D + 2, Qc = a.Qc;
+  const size_t n = (size_t)a.max_ndom * a.Npad + nv * Qc * a.Npad + nv * Qc + Qc * d1 * (a.order + 1) + Qc * nv * a.npoly + Qc * d1;
+  return (n + 1) / 2 * 2;
+}
 
 namespace {
 
@@ -18,12 +32,28 @@ struct Smem {
   double *A, *b, *E0, *E1, *Y, *rr, *pw, *mono, *pt, *Inv;
 };
 
-template <int D>
+template <bool WARP>
+__device__ __forceinline__ void gsync() {
+  if constexpr (WARP) __syncwarp();
+  else __syncthreads();
+}
+
+template <int D, bool WARP>
 __device__ __forceinline__ Smem carve(double* base, const TentKernelArgs& a) {
   constexpr int d1 = D + 1, nv = D + 2;
   const int nmax = a.max_ndom * a.Npad;
   const int esz = nv * a.Qc * a.Npad;
   Smem s;
+  if constexpr (WARP) {  // apply only: [b | E0 | rr | pw | mono | pt] (generic_warp_doubles)
+    s.A = nullptr; s.E1 = nullptr; s.Y = nullptr; s.Inv = nullptr;
+    s.b = base;
+    s.E0 = s.b + nmax;
+    s.rr = s.E0 + esz;
+    s.pw = s.rr + nv * a.Qc;
+    s.mono = s.pw + a.Qc * d1 * (a.order + 1);
+    s.pt = s.mono + a.Qc * nv * a.npoly;
+    return s;
+  }
   s.A = base;
   s.b = s.A + (size_t)nmax * nmax;
   s.E0 = s.b + nmax;
@@ -38,11 +68,11 @@ __device__ __forceinline__ Smem carve(double* base, const TentKernelArgs& a) {
 }
 
 // Evaluate the scaled Trefftz basis (variants vlo..D+1) at the nq points in s.pt into E.
-template <int D>
+template <int D, bool WARP>
 __device__ void eval_basis(const TentKernelArgs& a, const Smem& s, int nq, const double* ctr, double sc, double c,
                            int vlo, double* E) {
   constexpr int d1 = D + 1, nv = D + 2;
-  const int tid = threadIdx.x, nth = blockDim.x;
+  const int tid = WARP ? (threadIdx.x & 31) : threadIdx.x, nth = WARP ? 32 : blockDim.x;
   const int P1 = a.order + 1, npoly = a.npoly, Np = a.Npad, N = a.N, Qc = a.Qc;
   for (int idx = tid; idx < nq * d1; idx += nth) {
     const int q = idx / d1, d = idx % d1;
@@ -53,7 +83,7 @@ __device__ void eval_basis(const TentKernelArgs& a, const Smem& s, int nq, const
     p[0] = 1.0;
     for (int k = 1; k < P1; k++) { v *= xi; p[k] = v; }
   }
-  __syncthreads();
+  gsync<WARP>();
   for (int idx = tid; idx < nq * npoly; idx += nth) {
     const int q = idx / npoly, ii = idx % npoly;
     const int* e = a.expo + ii * d1;
@@ -76,7 +106,7 @@ __device__ void eval_basis(const TentKernelArgs& a, const Smem& s, int nq, const
       mq[(1 + d) * npoly + ii] = der;
     }
   }
-  __syncthreads();
+  gsync<WARP>();
   const int tot = (nv - vlo) * nq * Np;
   for (int idx = tid; idx < tot; idx += nth) {
     const int i = idx % Np;
@@ -90,7 +120,7 @@ __device__ void eval_basis(const TentKernelArgs& a, const Smem& s, int nq, const
     }
     E[(size_t)(v * Qc + q) * Np + i] = val;
   }
-  __syncthreads();
+  gsync<WARP>();
 }
 
 // Asub[i][j] += sum_{v in [v0,v1), q < nq} L[(v*Qc+q)*Np + i] * R[(v*Qc+q)*Np + j], 4x4 register tiles.
@@ -125,8 +155,10 @@ __device__ void gram(double* Asub, int lda, const double* L, const double* R, in
 }
 
 // bsub[i] += sum_{v in [v0,v1), q<nq} E[(v*Qc+q)*Np + i] * rr[v*Qc+q]
+template <bool WARP>
 __device__ void gemv(double* bsub, const double* E, const double* rr, int v0, int v1, int nq, int Qc, int Np, int N) {
-  for (int i = threadIdx.x; i < N; i += blockDim.x) {
+  const int tid = WARP ? (threadIdx.x & 31) : threadIdx.x, nth = WARP ? 32 : blockDim.x;
+  for (int i = tid; i < N; i += nth) {
     double acc = 0.0;
     for (int v = v0; v < v1; v++)
       for (int q = 0; q < nq; q++) acc = fma(E[(size_t)(v * Qc + q) * Np + i], rr[v * Qc + q], acc);
@@ -134,20 +166,24 @@ __device__ void gemv(double* bsub, const double* E, const double* rr, int v0, in
   }
 }
 
-template <int D>
+template <int D, bool WARP>
 __global__ void tent_kernel_generic(TentKernelArgs a) {
   constexpr int d1 = D + 1, nv = D + 2;
   extern __shared__ double smem_raw[];
-  const Smem s = carve<D>(smem_raw, a);
-  const int tid = threadIdx.x, nth = blockDim.x;
-  const int tent = a.tents[blockIdx.x];
+  const int tid = WARP ? (threadIdx.x & 31) : threadIdx.x, nth = WARP ? 32 : blockDim.x;
+  // WARP: warp k of CTA b takes entry b * (warps per CTA) + k of the launch's tent list; surplus warps leave at once
+  // (no block-wide barrier anywhere on this path)
+  const int slot = WARP ? blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5) : blockIdx.x;
+  if (WARP && slot >= a.ntents) return;
+  const Smem s = carve<D, WARP>(smem_raw + (WARP ? (size_t)(threadIdx.x >> 5) * generic_warp_doubles(D, a) : 0), a);
+  const int tent = a.tents[slot];
   const int nd = a.ndom[tent];
   const int N = a.N, Np = a.Npad, Qc = a.Qc, Q = a.Q;
   const int n = nd * Np;
   const int fo = a.fosystem;
   const int vlo_val = fo ? 1 : 0;
   // factor cache: the tent matrix does not depend on the state. apply = only right-hand side, stored inverse, evaluation
-  const bool apply = a.gmode == 2;
+  const bool apply = WARP || a.gmode == 2;
 
   double ctr[d1];
 #pragma unroll
@@ -157,7 +193,7 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
   if (!apply)
     for (int idx = tid; idx < n * n; idx += nth) s.A[idx] = 0.0;
   for (int idx = tid; idx < n; idx += nth) s.b[idx] = 0.0;
-  __syncthreads();
+  gsync<WARP>();
 
   // ------------------------------------------------------------------ time-like faces
   for (int tf = a.tf_off[tent]; tf < a.tf_off[tent + 1]; tf++) {
@@ -178,9 +214,9 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
         for (int m = 0; m < D; m++) x += (V[(m + 1) * d1 + r] - V[r]) * a.lam[(size_t)(q0 + q) * d1 + m];
         s.pt[q * d1 + r] = x;
       }
-      __syncthreads();
-      eval_basis<D>(a, s, nq, ctr, sc, c0, 1, s.E0);
-      if (kind == 2) eval_basis<D>(a, s, nq, ctr, sc, c1, 1, s.E1);
+      gsync<WARP>();
+      eval_basis<D, WARP>(a, s, nq, ctr, sc, c0, 1, s.E0);
+      if (kind == 2) eval_basis<D, WARP>(a, s, nq, ctr, sc, c1, 1, s.E1);
 
       if (kind == 0) {  // Dirichlet, twavetents.cpp:404-433
         const double alpha = 0.5, gam = 1.0 / (c0 * c0);
@@ -200,11 +236,11 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
 #pragma unroll
           for (int d = 0; d < D; d++) s.rr[(1 + d) * Qc + q] = nrm[d] * om * g;
         }
-        __syncthreads();
+        gsync<WARP>();
         double* Asub = s.A + (size_t)(din * Np) * n + din * Np;
         if (!apply) gram(Asub, n, s.E0, s.Y, 1 + D, 2 + D, nq, Qc, Np);
-        gemv(s.b + din * Np, s.E0, s.rr, 1, nv, nq, Qc, Np, N);
-        __syncthreads();
+        gemv<WARP>(s.b + din * Np, s.E0, s.rr, 1, nv, nq, Qc, Np, N);
+        gsync<WARP>();
       } else if (kind == 1) {  // Neumann, twavetents.cpp:380-403
         const double beta = 0.5;
         const long long off = a.tf_data[tf];
@@ -228,12 +264,12 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
           for (int d = 0; d < D; d++) s.rr[(1 + d) * Qc + q] = -nrm[d] * beta * gn * om;
           s.rr[(1 + D) * Qc + q] = -gn * om;
         }
-        __syncthreads();
+        gsync<WARP>();
         double* Asub = s.A + (size_t)(din * Np) * n + din * Np;
         if (!apply) gram(Asub, n, s.E0, s.Y, 1, nv, nq, Qc, Np);
-        gemv(s.b + din * Np, s.E0, s.rr, 1, nv, nq, Qc, Np, N);
-        __syncthreads();
-      } else {  // material interface, twavetents.cpp:436-539
+        gemv<WARP>(s.b + din * Np, s.E0, s.rr, 1, nv, nq, Qc, Np, N);
+        gsync<WARP>();
+      } else if (!WARP) {  // material interface, twavetents.cpp:436-539 (matrix only: never reached when applying)
         for (int el = 0; el < 4; el++) {
           const double* Lm = (el / 2 == 0) ? s.E0 : s.E1;
           const double* Rm = (el % 2 == 0) ? s.E0 : s.E1;
@@ -250,11 +286,11 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
             }
             s.Y[(size_t)((1 + D) * Qc + q) * Np + j] = yt;
           }
-          __syncthreads();
+          gsync<WARP>();
           const int in = (el / 2 == 0) ? din : dout;
           const int out = (el % 2 == 0) ? din : dout;
           gram(s.A + (size_t)(in * Np) * n + out * Np, n, Lm, s.Y, 1, nv, nq, Qc, Np);
-          __syncthreads();
+          gsync<WARP>();
         }
       }
     }
@@ -290,9 +326,9 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
           else { for (int k = 0; k < d1; k++) x += lm[k] * tau[k]; }
           s.pt[q * d1 + r] = x;
         }
-        __syncthreads();
+        gsync<WARP>();
         if (side == 0) {
-          eval_basis<D>(a, s, nq, ctr, sc, c, vlo_val, s.E0);
+          eval_basis<D, WARP>(a, s, nq, ctr, sc, c, vlo_val, s.E0);
           for (int q = tid; q < nq; q += nth) {
             const double om = a.w[q0 + q] * area;
             const double gt = wf[(size_t)((!fo) + D) * Q + q0 + q];
@@ -311,12 +347,12 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
               const int q = idx / Np;
               s.Y[idx] = a.w[q0 + q] * area * s.E0[idx];
             }
-          __syncthreads();
-          gemv(bsub, s.E0, s.rr, vlo_val, nv, nq, Qc, Np, N);
+          gsync<WARP>();
+          gemv<WARP>(bsub, s.E0, s.rr, vlo_val, nv, nq, Qc, Np, N);
           if (!fo && !apply) gram(Asub, n, s.E0, s.Y, 0, 1, nq, Qc, Np);
-          __syncthreads();
+          gsync<WARP>();
         } else {
-          eval_basis<D>(a, s, nq, ctr, sc, c, 1, s.E0);
+          eval_basis<D, WARP>(a, s, nq, ctr, sc, c, 1, s.E0);
           for (int idx = tid; idx < nq * Np; idx += nth) {
             const int q = idx / Np, j = idx % Np;
             const double om = a.w[q0 + q] * area;
@@ -330,9 +366,9 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
             }
             s.Y[(size_t)((1 + D) * Qc + q) * Np + j] = yt;
           }
-          __syncthreads();
+          gsync<WARP>();
           gram(Asub, n, s.E0, s.Y, 1, nv, nq, Qc, Np);
-          __syncthreads();
+          gsync<WARP>();
         }
       }
     }
@@ -341,11 +377,11 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
   // ------------------------------------------------------------------ Solve
   __shared__ int piv_row;
   __shared__ double piv_inv;
-  if (a.gmode == 0) {
+  if (!WARP && a.gmode == 0) {
   // LU with partial pivoting
   for (int g = 0; g < nd; g++)
     for (int i = N + tid; i < Np; i += nth) s.A[(size_t)(g * Np + i) * n + g * Np + i] = 1.0;
-  __syncthreads();
+  gsync<WARP>();
   for (int k = 0; k < n; k++) {
     if (tid < 32) {
       double best = -1.0;
@@ -366,7 +402,7 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
         else piv_inv = 1.0 / s.A[(size_t)brow * n + k];
       }
     }
-    __syncthreads();
+    gsync<WARP>();
     const int p = piv_row;
     if (p != k) {
       for (int cidx = tid; cidx <= n; cidx += nth) {
@@ -378,7 +414,7 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
           const double t0 = s.b[k]; s.b[k] = s.b[p]; s.b[p] = t0;
         }
       }
-      __syncthreads();
+      gsync<WARP>();
     }
     const double pinv = piv_inv;
     const int nr = n - k - 1, nc = n - k;  // columns k+1..n-1 and the right-hand side
@@ -388,29 +424,29 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
       if (cc < nc - 1) s.A[(size_t)r * n + k + 1 + cc] -= m * s.A[(size_t)k * n + k + 1 + cc];
       else s.b[r] -= m * s.b[k];
     }
-    __syncthreads();
+    gsync<WARP>();
   }
   for (int k = n - 1; k >= 0; k--) {
     if (tid == 0) {
       const double d = s.A[(size_t)k * n + k];
       s.b[k] = (d != 0.0) ? s.b[k] / d : 0.0;
     }
-    __syncthreads();
+    gsync<WARP>();
     const double xk = s.b[k];
     for (int r = tid; r < k; r += nth) s.b[r] -= s.A[(size_t)r * n + k] * xk;
-    __syncthreads();
+    gsync<WARP>();
   }
 
   } else {
     // factor cache. The inverse is kept transposed: invT[j * n + i] = (A^-1)[i][j] (consecutive threads read consecutive
     // doubles in the product). Stride n = nd * Npad of THIS tent inside its slot of (max_ndom * Npad)^2 doubles.
     double* const invT = a.ginv + (size_t)tent * ((size_t)a.max_ndom * Np) * ((size_t)a.max_ndom * Np);
-    if (a.gmode == 1) {
+    if (!WARP && a.gmode == 1) {
       // Gauss-Jordan with partial pivoting on [A | I] (the reference forms the inverse as well, twavetents.cpp:64-70)
       for (int g = 0; g < nd; g++)
         for (int i = N + tid; i < Np; i += nth) s.A[(size_t)(g * Np + i) * n + g * Np + i] = 1.0;
       for (int idx = tid; idx < n * n; idx += nth) s.Inv[idx] = (idx / n == idx % n) ? 1.0 : 0.0;
-      __syncthreads();
+      gsync<WARP>();
       for (int k = 0; k < n; k++) {
         if (tid < 32) {
           double best = -1.0;
@@ -431,7 +467,7 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
             else piv_inv = 1.0 / s.A[(size_t)brow * n + k];
           }
         }
-        __syncthreads();
+        gsync<WARP>();
         const int p = piv_row;
         const double pinv = piv_inv;
         // swap rows k and p and scale the pivot row, in A and in the inverse
@@ -442,7 +478,7 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
           M[(size_t)p * n + cc] = vk;
           M[(size_t)k * n + cc] = vp * pinv;
         }
-        __syncthreads();
+        gsync<WARP>();
         // eliminate column k from every other row (the multipliers are read before anybody overwrites column k)
         for (int idx = tid; idx < n * 2 * n; idx += nth) {
           const int r = idx / (2 * n), cidx = idx % (2 * n);
@@ -451,21 +487,21 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
           if (cidx < n) { if (cidx != k) s.A[(size_t)r * n + cidx] -= m * s.A[(size_t)k * n + cidx]; }
           else s.Inv[(size_t)r * n + cidx - n] -= m * s.Inv[(size_t)k * n + cidx - n];
         }
-        __syncthreads();
+        gsync<WARP>();
         for (int r = tid; r < n; r += nth)
           if (r != k) s.A[(size_t)r * n + k] = 0.0;
-        __syncthreads();
+        gsync<WARP>();
       }
       for (int idx = tid; idx < n * n; idx += nth) invT[(size_t)(idx % n) * n + idx / n] = s.Inv[idx];
-      __syncthreads();  // this CTA's stores are visible to its own threads
+      gsync<WARP>();  // this CTA's stores are visible to its own threads
     }
     // sol = A^-1 b (identical arithmetic when building and when applying the cache)
     double acc = 0.0;
     if (tid < n)
       for (int j = 0; j < n; j++) acc = fma(__ldcg(invT + (size_t)j * n + tid), s.b[j], acc);
-    __syncthreads();
+    gsync<WARP>();
     if (tid < n) s.b[tid] = acc;
-    __syncthreads();
+    gsync<WARP>();
   }
 
   // ------------------------------------------------------------------ CalcTentElEval
@@ -494,8 +530,8 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
         else { for (int k = 0; k < d1; k++) x += lm[k] * tau[k]; }
         s.pt[q * d1 + r] = x;
       }
-      __syncthreads();
-      eval_basis<D>(a, s, nq, ctr, sc, c, vlo_val, s.E0);
+      gsync<WARP>();
+      eval_basis<D, WARP>(a, s, nq, ctr, sc, c, vlo_val, s.E0);
       const int nk = (nv - vlo_val) * nq;
       for (int kk = wid; kk < nk; kk += nw) {
         const int v = vlo_val + kk / nq, q = kk % nq;
@@ -506,12 +542,305 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
         for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
         if (lane == 0) wf[(size_t)(v - fo) * Q + q0 + q] = acc;
       }
-      __syncthreads();
+      gsync<WARP>();
     }
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// gwarp == 2: 1-D tents with stored inverses, one warp per tent, lanes = basis functions (BASELINE configs[1]).
+// The variant above runs the CTA code on a warp and is bound by its index arithmetic (a division per operand entry) and
+// by the monomial tables it fills for every function. Here lane i of a half-warp owns basis function i of one element
+// of the tent (N <= 16; the two elements of a 1-D tent side by side in the two half-warps): it keeps its CSR row in
+// registers, evaluates its own function and derivatives at the Q points of a face from the power tables of that face
+// (Q x 2 x (p+1) doubles per half-warp in shared memory) and accumulates its own entry of the right-hand side; the
+// product with the stored inverse is one row per lane; the evaluation is a 16-lane shuffle tree per output value.
+// Every floating-point expression and every summation order is the generic kernel's (the same statements on the same
+// operands; the shuffle tree of the evaluation is the 32-lane tree with its upper half known to be zero), so the result
+// is bitwise the CTA variant's (tests/test_gpu_generic_cache.py).
+constexpr int kSmallQ = 8, kSmallP1 = 8, kSmallNnz = 8;
+constexpr int kSmallHalfDoubles = 2 * kSmallQ * kSmallP1 + 3 * kSmallQ;   // px | pt | rr
+constexpr int kSmallWarpDoubles = 32 + 2 * kSmallHalfDoubles;             // b | half 0 | half 1
+
+struct LaneRow {
+  double cv[kSmallNnz];
+  int ca[kSmallNnz], cb[kSmallNnz];
+  int nnz;
+};
+
+// value, d/dx, d/dt of the lane's basis function at a point given by its power tables (eval_basis for one (q, i))
+__device__ __forceinline__ void lane_basis(const LaneRow& r, const double* __restrict__ px, const double* __restrict__ pt,
+                                           double sx, double st, double& e0, double& e1, double& e2) {
+  double v0 = 0.0, v1 = 0.0, v2 = 0.0;
+#pragma unroll
+  for (int j = 0; j < kSmallNnz; j++) {
+    if (j < r.nnz) {
+      const int ea = r.ca[j], eb = r.cb[j];
+      double f[2];
+      double full = 1.0;
+      f[0] = px[ea]; full *= f[0];
+      f[1] = pt[eb]; full *= f[1];
+      double dx = 0.0;
+      if (ea > 0) { dx = (double)ea * px[ea - 1]; dx *= f[1]; }
+      double dt = 0.0;
+      if (eb > 0) { dt = (double)eb * pt[eb - 1]; dt *= f[0]; }
+      v0 += r.cv[j] * full;
+      v1 += r.cv[j] * dx;
+      v2 += r.cv[j] * dt;
+    }
+  }
+  v1 *= sx;
+  v2 *= st;
+  e0 = v0; e1 = v1; e2 = v2;
+}
+
+__global__ void __launch_bounds__(32 * kGenericWarpsPerCta) tent_kernel_small1d(TentKernelArgs a) {
+  constexpr int D = 1, d1 = 2, nv = 3;
+  __shared__ double S_all[kGenericWarpsPerCta][kSmallWarpDoubles];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int slot = blockIdx.x * kGenericWarpsPerCta + wid;
+  if (slot >= a.ntents) return;   // whole warps; no block-wide barrier in this kernel
+  const unsigned full_mask = 0xffffffffu;
+  const int tent = a.tents[slot];
+  const int half = lane >> 4, i = lane & 15;
+  double* const b = S_all[wid];
+  double* const px = b + 32 + half * kSmallHalfDoubles;   // [q][k]
+  double* const ptw = px + kSmallQ * kSmallP1;             // [q][k]
+  double* const rr = ptw + kSmallQ * kSmallP1;             // [v][q]
+  const int N = a.N, Np = a.Npad, Q = a.Q, P1 = a.order + 1;
+  const int fo = a.fosystem, vlo = fo ? 1 : 0;
+  const int nd = a.ndom[tent];
+  const int n = nd * Np;
+  const double ctr[d1] = {a.center[(size_t)tent * d1], a.center[(size_t)tent * d1 + 1]};
+  const double sc = a.scale[tent];
+
+  LaneRow row;
+  row.nnz = 0;
+  if (i < N) {
+    const int r0 = a.rowptr[i];
+    row.nnz = a.rowptr[i + 1] - r0;
+#pragma unroll
+    for (int j = 0; j < kSmallNnz; j++) {
+      row.cv[j] = 0.0; row.ca[j] = 0; row.cb[j] = 0;
+      if (j < row.nnz) {
+        row.cv[j] = a.val[r0 + j];
+        const int c = a.col[r0 + j];
+        row.ca[j] = a.expo[c * d1];
+        row.cb[j] = a.expo[c * d1 + 1];
+      }
+    }
+  }
+  b[lane] = 0.0;
+  __syncwarp();
+
+  // power tables of point (x, t) for the lane's q: p[k] = xi^k by repeated multiplication (eval_basis, first loop)
+  auto powers = [&](int q, double x, double t, double c) {
+#pragma unroll
+    for (int d = 0; d < d1; d++) {
+      const double scale = (d == D) ? sc * c : sc;
+      const double xi = ((d == 0 ? x : t) - ctr[d]) * scale;
+      double* p = (d == 0 ? px : ptw) + q * kSmallP1;
+      double v = 1.0;
+      p[0] = 1.0;
+      for (int k = 1; k < P1; k++) { v *= xi; p[k] = v; }
+    }
+  };
+  // acc = sum_{v in [v0, 3), q < Q} E[v][q] rr[v][q] for the lane's function, v outer, q inner (gemv)
+  auto rhs_entry = [&](int v0, double c) {
+    double E[nv][kSmallQ];
+#pragma unroll
+    for (int q = 0; q < kSmallQ; q++) {
+      E[0][q] = E[1][q] = E[2][q] = 0.0;
+      if (q < Q) lane_basis(row, px + q * kSmallP1, ptw + q * kSmallP1, sc, sc * c, E[0][q], E[1][q], E[2][q]);
+    }
+    double acc = 0.0;
+#pragma unroll
+    for (int v = 0; v < nv; v++) {
+      if (v < v0) continue;
+#pragma unroll
+      for (int q = 0; q < kSmallQ; q++)
+        if (q < Q) acc = fma(E[v][q], rr[v * kSmallQ + q], acc);
+    }
+    return acc;
+  };
+
+  // ------------------------------------------------------------------ boundary faces (right-hand side only), half-warp 0
+  for (int tf = a.tf_off[tent]; tf < a.tf_off[tent + 1]; tf++) {
+    const int kind = a.tf_kind[tf];
+    if (kind == 2) continue;  // material interfaces contribute to the matrix only
+    const double* V = a.tf_verts + (size_t)tf * d1 * d1;
+    double nrm[D];
+    nrm[0] = a.tf_n[(size_t)tf * D];
+    const double area = a.tf_area[tf];
+    const int din = a.tf_dom[2 * tf];
+    const double c0 = a.tf_c[2 * tf];
+    if (half == 0 && i < Q) {
+      const int q = i;
+      double xt[d1];
+#pragma unroll
+      for (int r = 0; r < d1; r++) {
+        double x = V[r];
+        for (int m = 0; m < D; m++) x += (V[(m + 1) * d1 + r] - V[r]) * a.lam[(size_t)q * d1 + m];
+        xt[r] = x;
+      }
+      powers(q, xt[0], xt[1], c0);
+      const long long off = a.tf_data[tf];
+      const double om = a.w[q] * area;
+      if (kind == 0) {  // Dirichlet, twavetents.cpp:404-433
+        const double alpha = 0.5, gam = 1.0 / (c0 * c0);
+        const double g = a.bnd_data ? a.bnd_data[off + q] : 0.0;
+        rr[(1 + D) * kSmallQ + q] = om * alpha * gam * g;
+#pragma unroll
+        for (int d = 0; d < D; d++) rr[(1 + d) * kSmallQ + q] = nrm[d] * om * g;
+      } else {  // Neumann, twavetents.cpp:380-403
+        const double beta = 0.5;
+        double gn = 0.0;
+#pragma unroll
+        for (int r = 0; r < D; r++) gn += -nrm[r] * (a.bnd_data ? a.bnd_data[off + (long long)r * Q + q] : 0.0);
+#pragma unroll
+        for (int d = 0; d < D; d++) rr[(1 + d) * kSmallQ + q] = -nrm[d] * beta * gn * om;
+        rr[(1 + D) * kSmallQ + q] = -gn * om;
+      }
+    }
+    __syncwarp();
+    if (half == 0 && i < N) {
+      const double acc = rhs_entry(1, c0);
+      b[din * Np + i] += acc;
+    }
+    __syncwarp();
+  }
+
+  // ------------------------------------------------------------------ bottom faces: right-hand side (CalcTentEl, 209-267)
+  const int te0 = a.te_off[tent], te1 = a.te_off[tent + 1];
+  for (int tp = te0; tp < te1; tp += 2) {
+    const int te = tp + half;
+    const bool have = te < te1;
+    int dom = 0;
+    double c = 1.0;
+    if (have) {
+      const int el = a.te_el[te];
+      dom = a.te_dom[te];
+      c = a.c_el[el];
+      if (i < Q) {
+        const int q = i;
+        const double* geo = a.te_geo + (size_t)te * 2 * (d1 + 1);
+        const double* wf = a.wavefront + (size_t)el * a.ncomp * Q;
+        const double* tau = a.te_tbot + (size_t)te * d1;
+        const double* nn = geo;
+        const double area = nn[d1];
+        double P[d1][D];
+#pragma unroll
+        for (int k = 0; k < d1; k++) {
+          const int vk = a.el2v[(size_t)el * d1 + k];
+          P[k][0] = a.pts[(size_t)vk * D];
+        }
+        const double* lm = a.lam + (size_t)q * d1;
+        double xt[d1];
+#pragma unroll
+        for (int r = 0; r < d1; r++) {
+          double x = 0.0;
+          if (r < D) { for (int k = 0; k < d1; k++) x += lm[k] * P[k][r]; }
+          else { for (int k = 0; k < d1; k++) x += lm[k] * tau[k]; }
+          xt[r] = x;
+        }
+        powers(q, xt[0], xt[1], c);
+        const double om = a.w[q] * area;
+        const double gt = wf[(size_t)((!fo) + D) * Q + q];
+        double rt = nn[D] / (c * c) * om * gt;
+#pragma unroll
+        for (int d = 0; d < D; d++) {
+          const double gx = wf[(size_t)((!fo) + d) * Q + q];
+          rr[(1 + d) * kSmallQ + q] = -(nn[D] * om * gx - nn[d] * om * gt);
+          rt -= nn[d] * om * gx;
+        }
+        rr[(1 + D) * kSmallQ + q] = -rt;
+        if (!fo) rr[q] = om * wf[q];
+      }
+    }
+    __syncwarp();
+    double acc = 0.0;
+    if (have && i < N) acc = rhs_entry(vlo, c);
+    // b += acc in the order of the tent's elements
+    if (half == 0 && i < N) b[dom * Np + i] += acc;
+    __syncwarp();
+    if (half == 1 && have && i < N) b[dom * Np + i] += acc;
+    __syncwarp();
+  }
+
+  // ------------------------------------------------------------------ sol = A^-1 b, one row per lane
+  {
+    const double* const invT = a.ginv + (size_t)tent * ((size_t)a.max_ndom * Np) * ((size_t)a.max_ndom * Np);
+    double acc = 0.0;
+    if (lane < n)
+      for (int j = 0; j < n; j++) acc = fma(__ldcg(invT + (size_t)j * n + lane), b[j], acc);
+    __syncwarp();
+    if (lane < n) b[lane] = acc;
+    __syncwarp();
+  }
+
+  // ------------------------------------------------------------------ CalcTentElEval (541-590) at the top faces
+  for (int tp = te0; tp < te1; tp += 2) {
+    const int te = tp + half;
+    const bool have = te < te1;
+    int dom = 0, el = 0;
+    double c = 1.0;
+    if (have) {
+      el = a.te_el[te];
+      dom = a.te_dom[te];
+      c = a.c_el[el];
+      if (i < Q) {
+        const int q = i;
+        const double* tau = a.te_ttop + (size_t)te * d1;
+        double P[d1][D];
+#pragma unroll
+        for (int k = 0; k < d1; k++) {
+          const int vk = a.el2v[(size_t)el * d1 + k];
+          P[k][0] = a.pts[(size_t)vk * D];
+        }
+        const double* lm = a.lam + (size_t)q * d1;
+        double xt[d1];
+#pragma unroll
+        for (int r = 0; r < d1; r++) {
+          double x = 0.0;
+          if (r < D) { for (int k = 0; k < d1; k++) x += lm[k] * P[k][r]; }
+          else { for (int k = 0; k < d1; k++) x += lm[k] * tau[k]; }
+          xt[r] = x;
+        }
+        powers(q, xt[0], xt[1], c);
+      }
+    }
+    __syncwarp();
+    const double sol = (have && i < N) ? b[dom * Np + i] : 0.0;
+    double* wf = a.wavefront + (size_t)el * a.ncomp * Q;
+    for (int q = 0; q < Q; q++) {
+      double e[nv] = {0.0, 0.0, 0.0};
+      if (have && i < N) lane_basis(row, px + q * kSmallP1, ptw + q * kSmallP1, sc, sc * c, e[0], e[1], e[2]);
+#pragma unroll
+      for (int v = 0; v < nv; v++) {
+        if (v < vlo) continue;
+        double acc = 0.0;
+        if (have && i < N) acc = fma(e[v], sol, acc);
+        acc += 0.0;   // the step o = 16 of the 32-lane tree of the generic kernel: lanes 16.. hold zero (N <= 16)
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) acc += __shfl_down_sync(full_mask, acc, o, 16);
+        if (have && i == 0) wf[(size_t)(v - fo) * Q + q] = acc;
+      }
+    }
+    __syncwarp();
+  }
+}
+
 }  // namespace
+
+// sizes the 1-D lanes-as-functions kernel is compiled for (the CSR rows are checked by the solver: at most 8 entries)
+bool tent_small1d_supported(const TentKernelArgs& a) {
+  return a.Npad <= 16 && a.Q <= kSmallQ && a.Qc >= a.Q && a.order + 1 <= kSmallP1 && a.max_ndom * a.Npad <= 32;
+}
+
+size_t tent_generic_warp_smem_bytes(int D, const TentKernelArgs& a) {
+  return (size_t)kGenericWarpsPerCta * generic_warp_doubles(D, a) * sizeof(double);
+}
 
 size_t tent_generic_smem_bytes(int D, const TentKernelArgs& a) {
   const int d1 = D + 1, nv = D + 2;
@@ -523,24 +852,50 @@ size_t tent_generic_smem_bytes(int D, const TentKernelArgs& a) {
   return doubles * sizeof(double);
 }
 
+namespace {
+template <int D>
+cudaError_t launch_warp(const TentKernelArgs& a, cudaStream_t stream) {
+  const size_t smem = tent_generic_warp_smem_bytes(D, a);
+  cudaError_t err = cudaFuncSetAttribute(tent_kernel_generic<D, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (err != cudaSuccess) return err;
+  const int ctas = (a.ntents + kGenericWarpsPerCta - 1) / kGenericWarpsPerCta;
+  tent_kernel_generic<D, true><<<ctas, 32 * kGenericWarpsPerCta, smem, stream>>>(a);
+  return cudaGetLastError();
+}
+}  // namespace
+
 cudaError_t launch_tent_generic(int D, const TentKernelArgs& a, int threads, size_t smem, cudaStream_t stream) {
   if (a.ntents <= 0) return cudaSuccess;
   cudaError_t err;
+  if (a.gmode == 2 && a.gwarp == 2) {  // stored inverses, 1-D: one warp per tent, lanes = basis functions
+    if (D != 1 || !tent_small1d_supported(a)) return cudaErrorInvalidValue;
+    const int ctas = (a.ntents + kGenericWarpsPerCta - 1) / kGenericWarpsPerCta;
+    tent_kernel_small1d<<<ctas, 32 * kGenericWarpsPerCta, 0, stream>>>(a);
+    return cudaGetLastError();
+  }
+  if (a.gmode == 2 && a.gwarp) {  // stored inverses, one warp per tent
+    switch (D) {
+      case 1: return launch_warp<1>(a, stream);
+      case 2: return launch_warp<2>(a, stream);
+      case 3: return launch_warp<3>(a, stream);
+      default: return cudaErrorInvalidValue;
+    }
+  }
   switch (D) {
     case 1:
-      err = cudaFuncSetAttribute(tent_kernel_generic<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      err = cudaFuncSetAttribute(tent_kernel_generic<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (err != cudaSuccess) return err;
-      tent_kernel_generic<1><<<a.ntents, threads, smem, stream>>>(a);
+      tent_kernel_generic<1, false><<<a.ntents, threads, smem, stream>>>(a);
       break;
     case 2:
-      err = cudaFuncSetAttribute(tent_kernel_generic<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      err = cudaFuncSetAttribute(tent_kernel_generic<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (err != cudaSuccess) return err;
-      tent_kernel_generic<2><<<a.ntents, threads, smem, stream>>>(a);
+      tent_kernel_generic<2, false><<<a.ntents, threads, smem, stream>>>(a);
       break;
     case 3:
-      err = cudaFuncSetAttribute(tent_kernel_generic<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      err = cudaFuncSetAttribute(tent_kernel_generic<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (err != cudaSuccess) return err;
-      tent_kernel_generic<3><<<a.ntents, threads, smem, stream>>>(a);
+      tent_kernel_generic<3, false><<<a.ntents, threads, smem, stream>>>(a);
       break;
     default:
       return cudaErrorInvalidValue;

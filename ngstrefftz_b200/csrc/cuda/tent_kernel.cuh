@@ -48,6 +48,7 @@ struct TentKernelArgs {
   // evaluation. ginv: per staged tent (max_ndom * Npad)^2 doubles, the inverse transposed.
   double* ginv;
   int gmode;
+  int gwarp;  // gmode 2 only: one warp per tent (tent_kernel_generic<D, true>) instead of one CTA
   // ---- dependency-driven scheduling (tent_fast.cu, single GPU): one launch per slab; CTAs draw tents from `tents` in
   // order through `ticket` and wait until remaining[tent] (unfinished predecessors) is zero; a finished tent decrements
   // the counters of its successors. ticket == nullptr: `tents` is one level, CTA b solves tents[b].

@@ -22,7 +22,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 
-def run_config(idx, slabs=2, scale=1.0):
+def run_config(idx, slabs=2, scale=1.0, generic_apply=None):
     import ngstrefftz_b200 as ng
     from _cases import dirichlet, gaussian_1d, standing
 
@@ -67,6 +67,8 @@ def run_config(idx, slabs=2, scale=1.0):
     t0 = time.perf_counter()
     tw = ng.TWave(order, ts, cw, BBcf=1) if qt else ng.TWave(order, ts, cw)
     t_stage = time.perf_counter() - t0
+    if generic_apply is not None:   # stored inverses of the generic kernel applied by a warp / a CTA per tent (A/B)
+        tw.set_factor_cache({"warp": 3, "cta": 4, "warp-generic": 5}[generic_apply])
     tw.SetInitial(init)
     tw.SetBoundaryCF(bnd)
     e0 = tw.Energy()
@@ -86,6 +88,8 @@ def run_config(idx, slabs=2, scale=1.0):
         "pitch_s": t_pitch, "stage_s": t_stage, "ms_per_slab": ms, "tents_per_s": ts.GetNTents() / (best * 1e-3),
         "dof_updates_per_s_single_domain": ndof / (best * 1e-3), "energy": en,
         "factor_cache": {"state": cache_state, "bytes": cache_bytes, "ms_first_slab": ms[0]},
+        "wavefront_sum_xor": [int(np.frombuffer(tw.GetWavefront().tobytes(), dtype=np.uint64).sum(dtype=np.uint64)),
+                              int(np.bitwise_xor.reduce(np.frombuffer(tw.GetWavefront().tobytes(), dtype=np.uint64)))],
     }
     if exact is not None:
         wf = tw.GetWavefront()
@@ -99,9 +103,10 @@ def main():
     ap.add_argument("--config", type=int, nargs="*", default=[0, 1, 2, 3])
     ap.add_argument("--slabs", type=int, default=2)
     ap.add_argument("--scale", type=float, default=1.0)
+    ap.add_argument("--generic-apply", choices=["warp", "cta", "warp-generic"], default=None)
     a = ap.parse_args()
     for idx in a.config:
-        print(json.dumps(run_config(idx, a.slabs, a.scale)), flush=True)
+        print(json.dumps(run_config(idx, a.slabs, a.scale, a.generic_apply)), flush=True)
 
 
 if __name__ == "__main__":

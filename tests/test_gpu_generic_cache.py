@@ -77,3 +77,36 @@ def test_generic_factor_cache(built, name):
     rel = np.abs(out[True] - ref).max() / np.abs(ref).max()
     print(f"{name}: stored inverse vs LU every step {d:.3e}, vs oracle {rel:.3e} (tolerance {tol:.1e})")
     assert d <= tol and rel <= tol
+
+
+WARP_CASES = dict(CASES)
+# levels of several hundred tents (several CTAs of four warps, a partly filled last one), material-interface tents among them
+WARP_CASES["1d_p6_piecewise_1000"] = (lambda: ng.SegMesh(1000, 0, 1), 6, lambda x: np.where((np.floor(x[:, 0] * 10).astype(int) % 2) == 0, 1.0, 2.0),
+                                      0.01, gaussian_1d, lambda x, t: 0 * t, False)
+
+
+@pytest.mark.parametrize("name", list(WARP_CASES))
+def test_warp_per_tent_apply_is_bitwise_the_cta_one(built, name):
+    """set_factor_cache(3 / 5): the stored inverses of the generic kernel applied by one WARP per tent -- 3: in 1-D the
+    lanes-as-functions kernel tent_kernel_small1d, 5: tent_kernel_generic<D, true>, the statements of the CTA variant executed by
+    32 lanes with warp-level barriers. Same arithmetic in the same order: same bits as the CTA variant (4)."""
+    mk, order, c, dt, init, bnd, neu = WARP_CASES[name]
+    m = mk()
+    if neu:
+        m.SetBoundaryNames("neumann")
+    ts = ng.TentSlab(m, "edge")
+    ts.SetMaxWavespeed(c)
+    assert ts.PitchTents(dt, True, 2 / 3)
+    out, names = [], []
+    for variant in (4, 3, 5):
+        tw = ng.TWave(order, ts, c)
+        tw.set_factor_cache(variant)
+        tw.SetInitial(init)
+        tw.SetBoundaryCF(bnd)
+        for _ in range(3):
+            tw.Propagate()
+        names.append(tw.kernel_name())
+        out.append(tw.GetWavefront())
+    assert names == ["tent_kernel_generic", "tent_kernel_small1d", "tent_kernel_generic_warp"], names
+    assert np.isfinite(out[0]).all() and np.array_equal(out[0], out[1]) and np.array_equal(out[0], out[2])
+
