@@ -575,6 +575,8 @@ void Solver::SetInitial(const double* wf, int ncomp) {
   a.col = d_col_[fosystem_];
   a.val = d_val_[fosystem_];
   a.N = basis_.nbasis;
+  a.gnnz = 0;
+  for (int i = 0; i + 1 < (int)basis_.rowptr.size(); i++) a.gnnz = std::max(a.gnnz, basis_.rowptr[i + 1] - basis_.rowptr[i]);
   a.Npad = (a.N + 3) / 4 * 4;
   a.ncomp = ncomp_;
   a.fosystem = fosystem_;
@@ -1642,11 +1644,7 @@ double Solver::Energy(const double* wf) {
 // the next Propagate applies stored inverses of the generic kernel with one warp per tent
 int Solver::GenericWarpApply() const {
   if (!generic_warp_apply_ || !GenericCachePossible() || !ginv_valid_[fosystem_] || !d_ginv_[fosystem_]) return 0;
-  if (generic_warp_apply_ == 2 && mesh_.D == 1 && tent_small1d_supported(args_)) {
-    int nnz = 0;
-    for (int i = 0; i < basis_.nbasis; i++) nnz = std::max(nnz, basis_.rowptr[i + 1] - basis_.rowptr[i]);
-    if (nnz <= 8) return 2;
-  }
+  if (generic_warp_apply_ == 2 && mesh_.D == 1 && tent_small1d_supported(args_)) return 2;
   return tent_generic_warp_smem_bytes(mesh_.D, args_) <= 100 * 1024 ? 1 : 0;
 }
 

@@ -559,32 +559,41 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
 // Every floating-point expression and every summation order is the generic kernel's (the same statements on the same
 // operands; the shuffle tree of the evaluation is the 32-lane tree with its upper half known to be zero), so the result
 // is bitwise the CTA variant's (tests/test_gpu_generic_cache.py).
-constexpr int kSmallQ = 8, kSmallP1 = 8, kSmallNnz = 8;
-constexpr int kSmallHalfDoubles = 2 * kSmallQ * kSmallP1 + 3 * kSmallQ;   // px | pt | rr
-constexpr int kSmallWarpDoubles = 32 + 2 * kSmallHalfDoubles;             // b | half 0 | half 1
+constexpr int kSmallQ = 8, kSmallP1 = 8;
+constexpr int kSmallTab = kSmallQ * kSmallP1;
+constexpr int kSmallHalfDoubles = 4 * kSmallTab + 3 * kSmallQ;   // px | pt | dpx | dpt | rr
+constexpr int kSmallWarpDoubles = 32 + 2 * kSmallHalfDoubles;    // b | half 0 | half 1
 
+template <int NNZ>
 struct LaneRow {
-  double cv[kSmallNnz];
-  int ca[kSmallNnz], cb[kSmallNnz];
+  double cv[NNZ];
+  int ea[NNZ], eb[NNZ];
   int nnz;
 };
 
-// value, d/dx, d/dt of the lane's basis function at a point given by its power tables (eval_basis for one (q, i))
-__device__ __forceinline__ void lane_basis(const LaneRow& r, const double* __restrict__ px, const double* __restrict__ pt,
-                                           double sx, double st, double& e0, double& e1, double& e2) {
+// value, d/dx, d/dt of the lane's basis function at point q of the half-warp's face: eval_basis for one (q, i) with the
+// monomials formed on the fly. tab: px[q][k] = xi_x^k, pt[q][k] = xi_t^k, dpx[q][k] = (double)k * px[q][k-1], dpt likewise
+// (the first factor of the generic kernel's derivative, formed once per point instead of once per function).
+template <int NNZ>
+__device__ __forceinline__ void lane_basis(const LaneRow<NNZ>& r, const double* __restrict__ tab, int q, double sx, double st,
+                                           double& e0, double& e1, double& e2) {
+  const double* __restrict__ px = tab + q * kSmallP1;
+  const double* __restrict__ pt = px + kSmallTab;
+  const double* __restrict__ dpx = pt + kSmallTab;
+  const double* __restrict__ dpt = dpx + kSmallTab;
   double v0 = 0.0, v1 = 0.0, v2 = 0.0;
 #pragma unroll
-  for (int j = 0; j < kSmallNnz; j++) {
+  for (int j = 0; j < NNZ; j++) {
     if (j < r.nnz) {
-      const int ea = r.ca[j], eb = r.cb[j];
+      const int ea = r.ea[j], eb = r.eb[j];
       double f[2];
       double full = 1.0;
       f[0] = px[ea]; full *= f[0];
       f[1] = pt[eb]; full *= f[1];
       double dx = 0.0;
-      if (ea > 0) { dx = (double)ea * px[ea - 1]; dx *= f[1]; }
+      if (ea > 0) { dx = dpx[ea]; dx *= f[1]; }
       double dt = 0.0;
-      if (eb > 0) { dt = (double)eb * pt[eb - 1]; dt *= f[0]; }
+      if (eb > 0) { dt = dpt[eb]; dt *= f[0]; }
       v0 += r.cv[j] * full;
       v1 += r.cv[j] * dx;
       v2 += r.cv[j] * dt;
@@ -595,7 +604,8 @@ __device__ __forceinline__ void lane_basis(const LaneRow& r, const double* __res
   e0 = v0; e1 = v1; e2 = v2;
 }
 
-__global__ void __launch_bounds__(32 * kGenericWarpsPerCta) tent_kernel_small1d(TentKernelArgs a) {
+template <int NNZ>
+__global__ void __launch_bounds__(32 * kGenericWarpsPerCta, 4) tent_kernel_small1d(TentKernelArgs a) {
   constexpr int D = 1, d1 = 2, nv = 3;
   __shared__ double S_all[kGenericWarpsPerCta][kSmallWarpDoubles];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -605,54 +615,67 @@ __global__ void __launch_bounds__(32 * kGenericWarpsPerCta) tent_kernel_small1d(
   const int tent = a.tents[slot];
   const int half = lane >> 4, i = lane & 15;
   double* const b = S_all[wid];
-  double* const px = b + 32 + half * kSmallHalfDoubles;   // [q][k]
-  double* const ptw = px + kSmallQ * kSmallP1;             // [q][k]
-  double* const rr = ptw + kSmallQ * kSmallP1;             // [v][q]
+  double* const tab = b + 32 + half * kSmallHalfDoubles;   // px | pt | dpx | dpt, each [q][k]
+  double* const rr = tab + 4 * kSmallTab;                  // [v][q]
   const int N = a.N, Np = a.Npad, Q = a.Q, P1 = a.order + 1;
   const int fo = a.fosystem, vlo = fo ? 1 : 0;
   const int nd = a.ndom[tent];
   const int n = nd * Np;
   const double ctr[d1] = {a.center[(size_t)tent * d1], a.center[(size_t)tent * d1 + 1]};
   const double sc = a.scale[tent];
+  // the tent's stored inverse towards L2 now (rows of n doubles, 128 bytes per prefetch): it is read after the right-hand side
+  const double* const invT = a.ginv + (size_t)tent * ((size_t)a.max_ndom * Np) * ((size_t)a.max_ndom * Np);
+  if (lane < n) {
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(invT + (size_t)lane * n));
+    if (n > 16) asm volatile("prefetch.global.L2 [%0];" ::"l"(invT + (size_t)lane * n + 16));
+  }
 
-  LaneRow row;
+  LaneRow<NNZ> row;
   row.nnz = 0;
+#pragma unroll
+  for (int j = 0; j < NNZ; j++) { row.cv[j] = 0.0; row.ea[j] = 0; row.eb[j] = 0; }
   if (i < N) {
     const int r0 = a.rowptr[i];
     row.nnz = a.rowptr[i + 1] - r0;
 #pragma unroll
-    for (int j = 0; j < kSmallNnz; j++) {
-      row.cv[j] = 0.0; row.ca[j] = 0; row.cb[j] = 0;
+    for (int j = 0; j < NNZ; j++) {
       if (j < row.nnz) {
         row.cv[j] = a.val[r0 + j];
         const int c = a.col[r0 + j];
-        row.ca[j] = a.expo[c * d1];
-        row.cb[j] = a.expo[c * d1 + 1];
+        row.ea[j] = a.expo[c * d1];
+        row.eb[j] = a.expo[c * d1 + 1];
       }
     }
   }
   b[lane] = 0.0;
   __syncwarp();
 
-  // power tables of point (x, t) for the lane's q: p[k] = xi^k by repeated multiplication (eval_basis, first loop)
+  // tables of point (x, t) for the lane's q: p[k] = xi^k by repeated multiplication (eval_basis, first loop), dp[k] = k p[k-1]
   auto powers = [&](int q, double x, double t, double c) {
 #pragma unroll
     for (int d = 0; d < d1; d++) {
       const double scale = (d == D) ? sc * c : sc;
       const double xi = ((d == 0 ? x : t) - ctr[d]) * scale;
-      double* p = (d == 0 ? px : ptw) + q * kSmallP1;
+      double* p = tab + d * kSmallTab + q * kSmallP1;
+      double* dp = p + 2 * kSmallTab;
       double v = 1.0;
       p[0] = 1.0;
-      for (int k = 1; k < P1; k++) { v *= xi; p[k] = v; }
+      dp[0] = 0.0;
+      for (int k = 1; k < P1; k++) {
+        dp[k] = (double)k * v;
+        v *= xi;
+        p[k] = v;
+      }
     }
   };
   // acc = sum_{v in [v0, 3), q < Q} E[v][q] rr[v][q] for the lane's function, v outer, q inner (gemv)
   auto rhs_entry = [&](int v0, double c) {
     double E[nv][kSmallQ];
+    const double st = sc * c;
 #pragma unroll
     for (int q = 0; q < kSmallQ; q++) {
       E[0][q] = E[1][q] = E[2][q] = 0.0;
-      if (q < Q) lane_basis(row, px + q * kSmallP1, ptw + q * kSmallP1, sc, sc * c, E[0][q], E[1][q], E[2][q]);
+      if (q < Q) lane_basis<NNZ>(row, tab, q, sc, st, E[0][q], E[1][q], E[2][q]);
     }
     double acc = 0.0;
 #pragma unroll
@@ -770,10 +793,17 @@ __global__ void __launch_bounds__(32 * kGenericWarpsPerCta) tent_kernel_small1d(
 
   // ------------------------------------------------------------------ sol = A^-1 b, one row per lane
   {
-    const double* const invT = a.ginv + (size_t)tent * ((size_t)a.max_ndom * Np) * ((size_t)a.max_ndom * Np);
     double acc = 0.0;
-    if (lane < n)
-      for (int j = 0; j < n; j++) acc = fma(__ldcg(invT + (size_t)j * n + lane), b[j], acc);
+#pragma unroll
+    for (int j0 = 0; j0 < 32; j0 += 16) {
+      if (j0 >= n) break;
+      double col[16];   // sixteen independent loads in flight, then the chain in the order of the generic kernel
+#pragma unroll
+      for (int j = 0; j < 16; j++) col[j] = (lane < n && j0 + j < n) ? __ldcg(invT + (size_t)(j0 + j) * n + lane) : 0.0;
+#pragma unroll
+      for (int j = 0; j < 16; j++)
+        if (j0 + j < n) acc = fma(col[j], b[j0 + j], acc);
+    }
     __syncwarp();
     if (lane < n) b[lane] = acc;
     __syncwarp();
@@ -815,7 +845,7 @@ __global__ void __launch_bounds__(32 * kGenericWarpsPerCta) tent_kernel_small1d(
     double* wf = a.wavefront + (size_t)el * a.ncomp * Q;
     for (int q = 0; q < Q; q++) {
       double e[nv] = {0.0, 0.0, 0.0};
-      if (have && i < N) lane_basis(row, px + q * kSmallP1, ptw + q * kSmallP1, sc, sc * c, e[0], e[1], e[2]);
+      if (have && i < N) lane_basis<NNZ>(row, tab, q, sc, sc * c, e[0], e[1], e[2]);
 #pragma unroll
       for (int v = 0; v < nv; v++) {
         if (v < vlo) continue;
@@ -833,9 +863,9 @@ __global__ void __launch_bounds__(32 * kGenericWarpsPerCta) tent_kernel_small1d(
 
 }  // namespace
 
-// sizes the 1-D lanes-as-functions kernel is compiled for (the CSR rows are checked by the solver: at most 8 entries)
+// sizes the 1-D lanes-as-functions kernel is compiled for (gnnz: longest CSR row of the basis, set by the solver)
 bool tent_small1d_supported(const TentKernelArgs& a) {
-  return a.Npad <= 16 && a.Q <= kSmallQ && a.Qc >= a.Q && a.order + 1 <= kSmallP1 && a.max_ndom * a.Npad <= 32;
+  return a.gnnz >= 1 && a.gnnz <= 8 && a.Npad <= 16 && a.Q <= kSmallQ && a.Qc >= a.Q && a.order + 1 <= kSmallP1 && a.max_ndom * a.Npad <= 32;
 }
 
 size_t tent_generic_warp_smem_bytes(int D, const TentKernelArgs& a) {
@@ -870,7 +900,8 @@ cudaError_t launch_tent_generic(int D, const TentKernelArgs& a, int threads, siz
   if (a.gmode == 2 && a.gwarp == 2) {  // stored inverses, 1-D: one warp per tent, lanes = basis functions
     if (D != 1 || !tent_small1d_supported(a)) return cudaErrorInvalidValue;
     const int ctas = (a.ntents + kGenericWarpsPerCta - 1) / kGenericWarpsPerCta;
-    tent_kernel_small1d<<<ctas, 32 * kGenericWarpsPerCta, 0, stream>>>(a);
+    if (a.gnnz <= 4) tent_kernel_small1d<4><<<ctas, 32 * kGenericWarpsPerCta, 0, stream>>>(a);
+    else tent_kernel_small1d<8><<<ctas, 32 * kGenericWarpsPerCta, 0, stream>>>(a);
     return cudaGetLastError();
   }
   if (a.gmode == 2 && a.gwarp) {  // stored inverses, one warp per tent

@@ -48,7 +48,8 @@ struct TentKernelArgs {
   // evaluation. ginv: per staged tent (max_ndom * Npad)^2 doubles, the inverse transposed.
   double* ginv;
   int gmode;
-  int gwarp;  // gmode 2 only: one warp per tent (tent_kernel_generic<D, true>) instead of one CTA
+  int gwarp;  // gmode 2 only: 1 = one warp per tent (tent_kernel_generic<D, true>), 2 = tent_kernel_small1d (D = 1), 0 = one CTA
+  int gnnz;   // longest row of the CSR basis (tent_kernel_small1d keeps a lane's row in registers)
   // ---- dependency-driven scheduling (tent_fast.cu, single GPU): one launch per slab; CTAs draw tents from `tents` in
   // order through `ticket` and wait until remaining[tent] (unfinished predecessors) is zero; a finished tent decrements
   // the counters of its successors. ticket == nullptr: `tents` is one level, CTA b solves tents[b].
