@@ -560,54 +560,57 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
 // operands; the shuffle tree of the evaluation is the 32-lane tree with its upper half known to be zero), so the result
 // is bitwise the CTA variant's (tests/test_gpu_generic_cache.py).
 constexpr int kSmallQ = 8, kSmallP1 = 8;
-constexpr int kSmallTab = kSmallQ * kSmallP1;
-constexpr int kSmallHalfDoubles = 4 * kSmallTab + 3 * kSmallQ;   // px | pt | dpx | dpt | rr
+// Tables of (xi^k, k xi^(k-1)) pairs, laid out [k][q] with an odd row length: the lanes that fill them (one point q each,
+// the same k) store consecutive 16-byte words, and the lanes that read them (the same q, different k) hit different banks
+// (k * 9 * 16 bytes apart). r05l: with [q][k] rows of 128 bytes the stores were 7- to 14-way bank conflicts and the L1 data
+// pipe was the busiest unit of the kernel (73 % of its peak).
+constexpr int kSmallQS = 9;
+constexpr int kSmallTab = kSmallP1 * kSmallQS;                   // pairs per direction
+constexpr int kSmallHalfDoubles = 4 * kSmallTab + 3 * kSmallQ;   // (px, dpx) pairs | (pt, dpt) pairs | rr
 constexpr int kSmallWarpDoubles = 32 + 2 * kSmallHalfDoubles;    // b | half 0 | half 1
 
-template <int NNZ>
+constexpr int kSmallNnz = 4;   // a 1-D wave polynomial of degree <= 7 has at most four monomials
 struct LaneRow {
-  double cv[NNZ];
-  int ea[NNZ], eb[NNZ];
-  int nnz;
+  double cv[kSmallNnz];   // zero in unused slots (exponents 0): such a slot adds 0.0 * 1.0 to the sums below
+  int ea[kSmallNnz], eb[kSmallNnz];   // exponents of x and t times the table row length
 };
 
 // value, d/dx, d/dt of the lane's basis function at point q of the half-warp's face: eval_basis for one (q, i) with the
 // monomials formed on the fly. tab: px[q][k] = xi_x^k, pt[q][k] = xi_t^k, dpx[q][k] = (double)k * px[q][k-1], dpt likewise
 // (the first factor of the generic kernel's derivative, formed once per point instead of once per function).
-template <int NNZ>
-__device__ __forceinline__ void lane_basis(const LaneRow<NNZ>& r, const double* __restrict__ tab, int q, double sx, double st,
+__device__ __forceinline__ void lane_basis(const LaneRow& r, const double* __restrict__ tab, int q, double sx, double st,
                                            double& e0, double& e1, double& e2) {
-  const double* __restrict__ px = tab + q * kSmallP1;
-  const double* __restrict__ pt = px + kSmallTab;
-  const double* __restrict__ dpx = pt + kSmallTab;
-  const double* __restrict__ dpt = dpx + kSmallTab;
+  // (power, derivative factor) pairs: one 16-byte shared-memory load per direction and monomial
+  const double2* __restrict__ px = reinterpret_cast<const double2*>(tab) + q;
+  const double2* __restrict__ pt = px + kSmallTab;
   double v0 = 0.0, v1 = 0.0, v2 = 0.0;
+  // No branches: an exponent 0 reads dp[0] = 0.0, so the derivative is (+-0.0) where the generic kernel has 0.0, and an
+  // unused slot contributes 0.0 * 1.0. Adding a zero of either sign leaves the sums unchanged (they start at +0.0 and can
+  // never be -0.0), so the values are bitwise the generic kernel's.
 #pragma unroll
-  for (int j = 0; j < NNZ; j++) {
-    if (j < r.nnz) {
-      const int ea = r.ea[j], eb = r.eb[j];
-      double f[2];
-      double full = 1.0;
-      f[0] = px[ea]; full *= f[0];
-      f[1] = pt[eb]; full *= f[1];
-      double dx = 0.0;
-      if (ea > 0) { dx = dpx[ea]; dx *= f[1]; }
-      double dt = 0.0;
-      if (eb > 0) { dt = dpt[eb]; dt *= f[0]; }
-      v0 += r.cv[j] * full;
-      v1 += r.cv[j] * dx;
-      v2 += r.cv[j] * dt;
-    }
+  for (int j = 0; j < kSmallNnz; j++) {
+    const double2 xa = px[r.ea[j]], tb = pt[r.eb[j]];
+    double f[2];
+    double full = 1.0;
+    f[0] = xa.x; full *= f[0];
+    f[1] = tb.x; full *= f[1];
+    double dx = xa.y;
+    dx *= f[1];
+    double dt = tb.y;
+    dt *= f[0];
+    v0 += r.cv[j] * full;
+    v1 += r.cv[j] * dx;
+    v2 += r.cv[j] * dt;
   }
   v1 *= sx;
   v2 *= st;
   e0 = v0; e1 = v1; e2 = v2;
 }
 
-template <int NNZ>
-__global__ void __launch_bounds__(32 * kGenericWarpsPerCta, 4) tent_kernel_small1d(TentKernelArgs a) {
+template <int P>   // order; Q = P + 1 points per face, P + 1 powers per direction
+__global__ void __launch_bounds__(32 * kGenericWarpsPerCta, 5) tent_kernel_small1d(TentKernelArgs a) {
   constexpr int D = 1, d1 = 2, nv = 3;
-  __shared__ double S_all[kGenericWarpsPerCta][kSmallWarpDoubles];
+  __shared__ __align__(16) double S_all[kGenericWarpsPerCta][kSmallWarpDoubles];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int slot = blockIdx.x * kGenericWarpsPerCta + wid;
   if (slot >= a.ntents) return;   // whole warps; no block-wide barrier in this kernel
@@ -615,9 +618,10 @@ __global__ void __launch_bounds__(32 * kGenericWarpsPerCta, 4) tent_kernel_small
   const int tent = a.tents[slot];
   const int half = lane >> 4, i = lane & 15;
   double* const b = S_all[wid];
-  double* const tab = b + 32 + half * kSmallHalfDoubles;   // px | pt | dpx | dpt, each [q][k]
+  double* const tab = b + 32 + half * kSmallHalfDoubles;   // (px, dpx)[q][k] | (pt, dpt)[q][k]
   double* const rr = tab + 4 * kSmallTab;                  // [v][q]
-  const int N = a.N, Np = a.Npad, Q = a.Q, P1 = a.order + 1;
+  constexpr int Q = P + 1, P1 = P + 1;
+  const int N = a.N, Np = a.Npad;
   const int fo = a.fosystem, vlo = fo ? 1 : 0;
   const int nd = a.ndom[tent];
   const int n = nd * Np;
@@ -630,20 +634,19 @@ __global__ void __launch_bounds__(32 * kGenericWarpsPerCta, 4) tent_kernel_small
     if (n > 16) asm volatile("prefetch.global.L2 [%0];" ::"l"(invT + (size_t)lane * n + 16));
   }
 
-  LaneRow<NNZ> row;
-  row.nnz = 0;
+  LaneRow row;
 #pragma unroll
-  for (int j = 0; j < NNZ; j++) { row.cv[j] = 0.0; row.ea[j] = 0; row.eb[j] = 0; }
+  for (int j = 0; j < kSmallNnz; j++) { row.cv[j] = 0.0; row.ea[j] = 0; row.eb[j] = 0; }
   if (i < N) {
     const int r0 = a.rowptr[i];
-    row.nnz = a.rowptr[i + 1] - r0;
+    const int nnz = a.rowptr[i + 1] - r0;
 #pragma unroll
-    for (int j = 0; j < NNZ; j++) {
-      if (j < row.nnz) {
+    for (int j = 0; j < kSmallNnz; j++) {
+      if (j < nnz) {
         row.cv[j] = a.val[r0 + j];
         const int c = a.col[r0 + j];
-        row.ea[j] = a.expo[c * d1];
-        row.eb[j] = a.expo[c * d1 + 1];
+        row.ea[j] = a.expo[c * d1] * kSmallQS;       // table offsets (rows of kSmallQS pairs)
+        row.eb[j] = a.expo[c * d1 + 1] * kSmallQS;
       }
     }
   }
@@ -656,34 +659,29 @@ __global__ void __launch_bounds__(32 * kGenericWarpsPerCta, 4) tent_kernel_small
     for (int d = 0; d < d1; d++) {
       const double scale = (d == D) ? sc * c : sc;
       const double xi = ((d == 0 ? x : t) - ctr[d]) * scale;
-      double* p = tab + d * kSmallTab + q * kSmallP1;
-      double* dp = p + 2 * kSmallTab;
+      double2* p = reinterpret_cast<double2*>(tab) + d * kSmallTab + q;   // (xi^k, k xi^(k-1)) at [k][q]
       double v = 1.0;
-      p[0] = 1.0;
-      dp[0] = 0.0;
+      p[0] = make_double2(1.0, 0.0);
+#pragma unroll
       for (int k = 1; k < P1; k++) {
-        dp[k] = (double)k * v;
+        const double dk = (double)k * v;
         v *= xi;
-        p[k] = v;
+        p[k * kSmallQS] = make_double2(v, dk);
       }
     }
   };
   // acc = sum_{v in [v0, 3), q < Q} E[v][q] rr[v][q] for the lane's function, v outer, q inner (gemv)
   auto rhs_entry = [&](int v0, double c) {
-    double E[nv][kSmallQ];
+    double E[nv][Q];
     const double st = sc * c;
 #pragma unroll
-    for (int q = 0; q < kSmallQ; q++) {
-      E[0][q] = E[1][q] = E[2][q] = 0.0;
-      if (q < Q) lane_basis<NNZ>(row, tab, q, sc, st, E[0][q], E[1][q], E[2][q]);
-    }
+    for (int q = 0; q < Q; q++) lane_basis(row, tab, q, sc, st, E[0][q], E[1][q], E[2][q]);
     double acc = 0.0;
 #pragma unroll
     for (int v = 0; v < nv; v++) {
       if (v < v0) continue;
 #pragma unroll
-      for (int q = 0; q < kSmallQ; q++)
-        if (q < Q) acc = fma(E[v][q], rr[v * kSmallQ + q], acc);
+      for (int q = 0; q < Q; q++) acc = fma(E[v][q], rr[v * kSmallQ + q], acc);
     }
     return acc;
   };
@@ -843,14 +841,14 @@ __global__ void __launch_bounds__(32 * kGenericWarpsPerCta, 4) tent_kernel_small
     __syncwarp();
     const double sol = (have && i < N) ? b[dom * Np + i] : 0.0;
     double* wf = a.wavefront + (size_t)el * a.ncomp * Q;
+#pragma unroll
     for (int q = 0; q < Q; q++) {
-      double e[nv] = {0.0, 0.0, 0.0};
-      if (have && i < N) lane_basis<NNZ>(row, tab, q, sc, sc * c, e[0], e[1], e[2]);
+      double e[nv];
+      lane_basis(row, tab, q, sc, sc * c, e[0], e[1], e[2]);   // lanes >= N: zero row; halves without an element: not written
 #pragma unroll
       for (int v = 0; v < nv; v++) {
         if (v < vlo) continue;
-        double acc = 0.0;
-        if (have && i < N) acc = fma(e[v], sol, acc);
+        double acc = fma(e[v], sol, 0.0);
         acc += 0.0;   // the step o = 16 of the 32-lane tree of the generic kernel: lanes 16.. hold zero (N <= 16)
 #pragma unroll
         for (int o = 8; o > 0; o >>= 1) acc += __shfl_down_sync(full_mask, acc, o, 16);
@@ -865,7 +863,8 @@ __global__ void __launch_bounds__(32 * kGenericWarpsPerCta, 4) tent_kernel_small
 
 // sizes the 1-D lanes-as-functions kernel is compiled for (gnnz: longest CSR row of the basis, set by the solver)
 bool tent_small1d_supported(const TentKernelArgs& a) {
-  return a.gnnz >= 1 && a.gnnz <= 8 && a.Npad <= 16 && a.Q <= kSmallQ && a.Qc >= a.Q && a.order + 1 <= kSmallP1 && a.max_ndom * a.Npad <= 32;
+  return a.gnnz >= 1 && a.gnnz <= kSmallNnz && a.Npad <= 16 && a.order >= 1 && a.order <= 7 && a.Q == a.order + 1 && a.Qc >= a.Q &&
+         a.max_ndom * a.Npad <= 32;
 }
 
 size_t tent_generic_warp_smem_bytes(int D, const TentKernelArgs& a) {
@@ -900,8 +899,15 @@ cudaError_t launch_tent_generic(int D, const TentKernelArgs& a, int threads, siz
   if (a.gmode == 2 && a.gwarp == 2) {  // stored inverses, 1-D: one warp per tent, lanes = basis functions
     if (D != 1 || !tent_small1d_supported(a)) return cudaErrorInvalidValue;
     const int ctas = (a.ntents + kGenericWarpsPerCta - 1) / kGenericWarpsPerCta;
-    if (a.gnnz <= 4) tent_kernel_small1d<4><<<ctas, 32 * kGenericWarpsPerCta, 0, stream>>>(a);
-    else tent_kernel_small1d<8><<<ctas, 32 * kGenericWarpsPerCta, 0, stream>>>(a);
+    switch (a.order) {
+      case 1: tent_kernel_small1d<1><<<ctas, 32 * kGenericWarpsPerCta, 0, stream>>>(a); break;
+      case 2: tent_kernel_small1d<2><<<ctas, 32 * kGenericWarpsPerCta, 0, stream>>>(a); break;
+      case 3: tent_kernel_small1d<3><<<ctas, 32 * kGenericWarpsPerCta, 0, stream>>>(a); break;
+      case 4: tent_kernel_small1d<4><<<ctas, 32 * kGenericWarpsPerCta, 0, stream>>>(a); break;
+      case 5: tent_kernel_small1d<5><<<ctas, 32 * kGenericWarpsPerCta, 0, stream>>>(a); break;
+      case 6: tent_kernel_small1d<6><<<ctas, 32 * kGenericWarpsPerCta, 0, stream>>>(a); break;
+      default: tent_kernel_small1d<7><<<ctas, 32 * kGenericWarpsPerCta, 0, stream>>>(a); break;
+    }
     return cudaGetLastError();
   }
   if (a.gmode == 2 && a.gwarp) {  // stored inverses, one warp per tent
