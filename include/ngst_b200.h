@@ -252,7 +252,11 @@ int ngst_twave_compact_state(const ngst_twave* t);
  * i.e. the reference's own arithmetic. on == 0: assemble and solve in every Propagate (the memory is kept until the solver
  * is destroyed). If the memory cannot be allocated the solver silently keeps assembling.
  * ngst_twave_factor_cache returns 0 = not in use, 1 = the next Propagate builds the cache, 2 = the next Propagate applies it;
- * *bytes (may be NULL) = device memory held by the cache. */
+ * *bytes (may be NULL) = device memory held by the cache.
+ * Values of `on` above 1 select how stored inverses are applied and leave the cache switch alone: 2 = fast kernel compiled for four
+ * CTAs per SM (A/B; measured slower); generic kernel (systems of up to 32 unknowns, e.g. all 1-D tents): 3 = automatic (default:
+ * one warp per tent with lanes as basis functions, tent_kernel_small1d, for D = 1 and order <= 7; one CTA per tent otherwise),
+ * 4 = one CTA per tent, 5 = the CTA code executed by one warp per tent (A/B). All variants give the same bits. */
 int ngst_twave_set_factor_cache(ngst_twave* t, int on);
 int ngst_twave_factor_cache(const ngst_twave* t, long long* bytes);
 int ngst_twave_ntents_fast(const ngst_twave* t);

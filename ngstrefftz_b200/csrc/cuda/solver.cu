@@ -1644,7 +1644,7 @@ double Solver::Energy(const double* wf) {
 // the next Propagate applies stored inverses of the generic kernel with one warp per tent
 int Solver::GenericWarpApply() const {
   if (!generic_warp_apply_ || !GenericCachePossible() || !ginv_valid_[fosystem_] || !d_ginv_[fosystem_]) return 0;
-  if (generic_warp_apply_ == 2 && mesh_.D == 1 && tent_small1d_supported(args_)) return 2;
+  if (generic_warp_apply_ == 2) return (mesh_.D == 1 && tent_small1d_supported(args_)) ? 2 : 0;
   return tent_generic_warp_smem_bytes(mesh_.D, args_) <= 100 * 1024 ? 1 : 0;
 }
 

@@ -118,7 +118,8 @@ class Solver {
   // build right-hand sides, apply the stored inverses and evaluate. off: assemble and solve in every Propagate.
   void set_factor_cache(bool on, bool four_ctas = false) { factor_cache_enabled_ = on; apply_four_ctas_ = four_ctas; }
   // generic kernel, stored inverses: one warp per tent (tent_kernel_generic<D, true>) instead of one CTA
-  // (0 = CTA per tent, 1 = the CTA code on a warp, 2 = automatic: the 1-D lanes-as-functions kernel where it applies)
+  // (0 = CTA per tent, 1 = the CTA code on a warp (A/B), 2 = automatic, the default: the 1-D lanes-as-functions kernel
+  // tent_kernel_small1d where it applies -- D = 1, order <= 7 --, a CTA per tent otherwise)
   void set_generic_warp_apply(int mode) { generic_warp_apply_ = mode; }
   int GenericWarpApply() const;   // 0 = CTA, 1 = tent_kernel_generic<D, true>, 2 = tent_kernel_small1d
   // multi-GPU: exchange inside the tent kernel over peer memory (default where it could be set up) or per level with NCCL
@@ -287,7 +288,7 @@ class Solver {
   bool ginv_valid_[2] = {false, false}, ginv_failed_ = false;
   size_t smem_build_ = 0;                   // shared memory of the generic kernel while it forms the inverses
   bool factor_cache_enabled_ = true, cache_failed_ = false;
-  int generic_warp_apply_ = 0;  // stored inverses of the generic kernel applied by one warp per tent (set_generic_warp_apply)
+  int generic_warp_apply_ = 2;  // stored inverses of the generic kernel applied by one warp per tent (set_generic_warp_apply)
   bool apply_four_ctas_ = false;   // apply variant with 128 registers / 55 KB: four CTAs per SM, inverse read from L2 (A/B)
   double* d_ainv_[2] = {nullptr, nullptr};  // [fosystem]
   size_t ainv_bytes_[2] = {0, 0};

@@ -608,7 +608,7 @@ __device__ __forceinline__ void lane_basis(const LaneRow& r, const double* __res
 }
 
 template <int P>   // order; Q = P + 1 points per face, P + 1 powers per direction
-__global__ void __launch_bounds__(32 * kGenericWarpsPerCta, 5) tent_kernel_small1d(TentKernelArgs a) {
+__global__ void __launch_bounds__(32 * kGenericWarpsPerCta, 6) tent_kernel_small1d(TentKernelArgs a) {
   constexpr int D = 1, d1 = 2, nv = 3;
   __shared__ __align__(16) double S_all[kGenericWarpsPerCta][kSmallWarpDoubles];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;

@@ -85,11 +85,18 @@ WARP_CASES["1d_p6_piecewise_1000"] = (lambda: ng.SegMesh(1000, 0, 1), 6, lambda 
                                       0.01, gaussian_1d, lambda x, t: 0 * t, False)
 
 
+# outside the 1-D kernel's range the default stays the CTA variant; the CTA code on a warp (5) is bitwise the same there too
+WARP_CASES["2d_p2"] = (lambda: ng.UnitSquareMesh(5), 2, 1.0, 0.2, standing(2), dirichlet(standing(2), 2), False)
+WARP_CASES["3d_p1"] = (lambda: ng.UnitCubeMesh(3), 1, 1.0, 0.2, standing(3), dirichlet(standing(3), 3), False)
+WARP_CASES["1d_p8"] = (lambda: ng.SegMesh(24, 0, 1), 8, 1.0, 0.3, standing(1), dirichlet(standing(1), 1), False)
+
+
 @pytest.mark.parametrize("name", list(WARP_CASES))
 def test_warp_per_tent_apply_is_bitwise_the_cta_one(built, name):
-    """set_factor_cache(3 / 5): the stored inverses of the generic kernel applied by one WARP per tent -- 3: in 1-D the
-    lanes-as-functions kernel tent_kernel_small1d, 5: tent_kernel_generic<D, true>, the statements of the CTA variant executed by
-    32 lanes with warp-level barriers. Same arithmetic in the same order: same bits as the CTA variant (4)."""
+    """The stored inverses of the generic kernel applied by one WARP per tent -- set_factor_cache(3), the default: in 1-D up
+    to order 7 the lanes-as-functions kernel tent_kernel_small1d (a CTA per tent elsewhere); 5: tent_kernel_generic<D, true>, the
+    statements of the CTA variant executed by 32 lanes with warp-level barriers. Same arithmetic in the same order: same bits as
+    the CTA variant (4)."""
     mk, order, c, dt, init, bnd, neu = WARP_CASES[name]
     m = mk()
     if neu:
@@ -107,6 +114,13 @@ def test_warp_per_tent_apply_is_bitwise_the_cta_one(built, name):
             tw.Propagate()
         names.append(tw.kernel_name())
         out.append(tw.GetWavefront())
-    assert names == ["tent_kernel_generic", "tent_kernel_small1d", "tent_kernel_generic_warp"], names
+    auto = "tent_kernel_small1d" if (m.dim == 1 and order <= 7) else "tent_kernel_generic"
+    assert names == ["tent_kernel_generic", auto, "tent_kernel_generic_warp"], names
+    dflt = ng.TWave(order, ts, c)   # no selection: the automatic choice
+    dflt.SetInitial(init)
+    dflt.SetBoundaryCF(bnd)
+    for _ in range(3):
+        dflt.Propagate()
+    assert dflt.kernel_name() == auto and np.array_equal(dflt.GetWavefront(), out[0])
     assert np.isfinite(out[0]).all() and np.array_equal(out[0], out[1]) and np.array_equal(out[0], out[2])
 
