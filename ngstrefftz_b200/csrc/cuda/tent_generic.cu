@@ -841,19 +841,58 @@ __global__ void __launch_bounds__(32 * kGenericWarpsPerCta, 6) tent_kernel_small
     __syncwarp();
     const double sol = (have && i < N) ? b[dom * Np + i] : 0.0;
     double* wf = a.wavefront + (size_t)el * a.ncomp * Q;
+    // t[v * Q + q] = this lane's term of output (v, q); lanes >= N hold a zero row, halves without an element garbage
+    // that never leaves the half-warp and is not written
+    double t[24];
+#pragma unroll
+    for (int k = 3 * Q; k < 24; k++) t[k] = 0.0;
 #pragma unroll
     for (int q = 0; q < Q; q++) {
       double e[nv];
-      lane_basis(row, tab, q, sc, sc * c, e[0], e[1], e[2]);   // lanes >= N: zero row; halves without an element: not written
+      lane_basis(row, tab, q, sc, sc * c, e[0], e[1], e[2]);
 #pragma unroll
       for (int v = 0; v < nv; v++) {
-        if (v < vlo) continue;
         double acc = fma(e[v], sol, 0.0);
         acc += 0.0;   // the step o = 16 of the 32-lane tree of the generic kernel: lanes 16.. hold zero (N <= 16)
-#pragma unroll
-        for (int o = 8; o > 0; o >>= 1) acc += __shfl_down_sync(full_mask, acc, o, 16);
-        if (have && i == 0) wf[(size_t)(v - fo) * Q + q] = acc;
+        t[v * Q + q] = acc;
       }
+    }
+    // The 16-lane tree (partners 8, 4, 2, 1 apart) for all outputs at once: at every level a lane keeps one half of its
+    // values and hands the other half to its partner, so 12 + 6 + 3 + 2 exchanges replace 4 per output. Each output still
+    // is ((t_c + t_c+8) + (t_c+4 + t_c+12)) + ..., i.e. the pairs and the order of the generic kernel's shuffle tree (an
+    // addition with swapped operands gives the same bits).
+#pragma unroll
+    for (int k = 0; k < 12; k++) {
+      const bool up = (i & 8) != 0;
+      const double recv = __shfl_xor_sync(full_mask, up ? t[k] : t[k + 12], 8, 16);
+      t[k] = (up ? t[k + 12] : t[k]) + recv;
+    }
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+      const bool up = (i & 4) != 0;
+      const double recv = __shfl_xor_sync(full_mask, up ? t[k] : t[k + 6], 4, 16);
+      t[k] = (up ? t[k + 6] : t[k]) + recv;
+    }
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      const bool up = (i & 2) != 0;
+      const double recv = __shfl_xor_sync(full_mask, up ? t[k] : t[k + 3], 2, 16);
+      t[k] = (up ? t[k + 3] : t[k]) + recv;
+    }
+    t[3] = 0.0;
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+      const bool up = (i & 1) != 0;
+      const double recv = __shfl_xor_sync(full_mask, up ? t[k] : t[k + 2], 1, 16);
+      t[k] = (up ? t[k + 2] : t[k]) + recv;
+    }
+    // lane i now holds outputs base + 0 (and base + 1 on even lanes)
+    const int base = ((i & 8) ? 12 : 0) + ((i & 4) ? 6 : 0) + ((i & 2) ? 3 : 0) + ((i & 1) ? 2 : 0);
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+      const int idx = base + k;
+      const int v = idx / Q, q = idx % Q;
+      if (have && idx < 3 * Q && (k == 0 || !(i & 1)) && v >= vlo) wf[(size_t)(v - fo) * Q + q] = t[k];
     }
     __syncwarp();
   }
