@@ -392,8 +392,9 @@ Solver::~Solver() {
   if (d_bnd_) cudaFree(d_bnd_);
   ReleaseMirror();
   ReleaseLoadBuffer();
-  for (cudaStream_t st : {stream_in_, stream_out_})
+  for (cudaStream_t st : {stream_in_, stream_out_, stream_proj_})
     if (st) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
+  for (cudaEvent_t e : ev_chunk_) cudaEventDestroy(e);
   for (cudaEvent_t e : {ev_in_start_, ev_in_done_, ev_out_start_, ev_out_done_, ev_stage_, ev_snap_, ev_copied_, ev_used_})
     if (e) cudaEventDestroy(e);
   for (double* p : {d_stage_wf_, d_stage_cs_, d_stage_bnd_, d_snap_})
@@ -761,6 +762,7 @@ void Solver::EnsurePipeStreams() {
     CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
     CU(cudaStreamCreateWithPriority(&stream_in_, cudaStreamNonBlocking, hi));
     CU(cudaStreamCreateWithPriority(&stream_out_, cudaStreamNonBlocking, hi));
+    CU(cudaStreamCreateWithPriority(&stream_proj_, cudaStreamNonBlocking, hi));
     for (cudaEvent_t* e : {&ev_in_start_, &ev_in_done_, &ev_out_start_, &ev_out_done_})
       CU(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
   }
@@ -768,8 +770,9 @@ void Solver::EnsurePipeStreams() {
     for (cudaEvent_t* e : {&ev_stage_, &ev_snap_, &ev_copied_, &ev_used_}) CU(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
 }
 
-// The next step's input, fetched while the current step computes: H2D copies on the input stream (copy engine), then the
-// transfer to the compact state on the same stream.
+// The next step's input, fetched while the current step computes: H2D copies back to back on the input stream (copy
+// engine); the transfer of each chunk to the compact state runs on a second stream behind that chunk's event, so the copy
+// engine never waits for a kernel (r04m had both in one stream: every transfer kernel stalled the next chunk's copy).
 void Solver::PrefetchInput(const double* wf, int ncomp, const double* bnd_values, long long nbnd) {
   const int D = mesh_.D, Q = rule_.nip;
   if (!wf) throw std::invalid_argument("PrefetchInput: null buffer");
@@ -781,6 +784,7 @@ void Solver::PrefetchInput(const double* wf, int ncomp, const double* bnd_values
   const size_t bytes = (size_t)nel_ * ncomp * Q * sizeof(double);
   if (stage_wf_bytes_ < bytes) {
     CU(cudaStreamSynchronize(stream_in_));
+    CU(cudaStreamSynchronize(stream_proj_));
     if (d_stage_wf_) CU(cudaFree(d_stage_wf_));
     CU(cudaMalloc(&d_stage_wf_, bytes));
     stage_wf_bytes_ = bytes;
@@ -790,6 +794,7 @@ void Solver::PrefetchInput(const double* wf, int ncomp, const double* bnd_values
   const size_t cbytes = (size_t)nel_ * ncomp * cs * sizeof(double);
   if (cs > 0 && stage_cs_bytes_ < cbytes) {
     CU(cudaStreamSynchronize(stream_in_));
+    CU(cudaStreamSynchronize(stream_proj_));
     if (d_stage_cs_) CU(cudaFree(d_stage_cs_));
     CU(cudaMalloc(&d_stage_cs_, cbytes));
     stage_cs_bytes_ = cbytes;
@@ -807,15 +812,30 @@ void Solver::PrefetchInput(const double* wf, int ncomp, const double* bnd_values
   // in chunks, so that the transfer of a chunk runs behind the copy of the next one
   const size_t rowlen = (size_t)ncomp * Q;
   const int chunk = (int)std::max<size_t>(256, (16u << 20) / (rowlen * sizeof(double)));
-  for (int e0 = 0; e0 < nel_; e0 += chunk) {
+  const int nchunks = (nel_ + chunk - 1) / chunk;
+  while (cs > 0 && (int)ev_chunk_.size() < nchunks) {
+    cudaEvent_t e;
+    CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    ev_chunk_.push_back(e);
+  }
+  for (int c = 0, e0 = 0; e0 < nel_; e0 += chunk, c++) {
     const int ne = std::min(chunk, nel_ - e0);
     CU(cudaMemcpyAsync(d_stage_wf_ + (size_t)e0 * rowlen, wf + (size_t)e0 * rowlen, (size_t)ne * rowlen * sizeof(double),
                        cudaMemcpyHostToDevice, stream_in_));
-    if (cs > 0)
+    if (cs > 0) {
+      CU(cudaEventRecord(ev_chunk_[c], stream_in_));
+      CU(cudaStreamWaitEvent(stream_proj_, ev_chunk_[c], 0));
       CU(launch_project_rows(ne, Q, cs, 0, ncomp, ncomp * Q, d_transfer_, d_stage_wf_ + (size_t)e0 * rowlen,
-                             d_stage_cs_ + (size_t)e0 * ncomp * cs, stream_in_));
+                             d_stage_cs_ + (size_t)e0 * ncomp * cs, stream_proj_));
+    }
   }
-  CU(cudaEventRecord(ev_stage_, stream_in_));
+  if (cs > 0) {  // staged = every copy has landed (the boundary samples included) and every chunk is transferred
+    CU(cudaEventRecord(ev_stage_, stream_in_));
+    CU(cudaStreamWaitEvent(stream_proj_, ev_stage_, 0));
+    CU(cudaEventRecord(ev_stage_, stream_proj_));
+  } else {
+    CU(cudaEventRecord(ev_stage_, stream_in_));
+  }
   stage_ncomp_ = ncomp;
   stage_has_bnd_ = bnd_values && nbnd > 0;
   stage_valid_ = true;

@@ -241,6 +241,8 @@ class Solver {
   unsigned char* d_te_first_ = nullptr; // per tent-element: first tent of the slab to touch the element
   int* d_untouched_ = nullptr;          // elements no tent touches (their compact rows are transferred separately)
   cudaStream_t stream_in_ = nullptr, stream_out_ = nullptr;
+  cudaStream_t stream_proj_ = nullptr;          // compact transfer of prefetched chunks: keeps kernels out of the copy stream
+  std::vector<cudaEvent_t> ev_chunk_;           // chunk c of the prefetched input has landed
   cudaEvent_t ev_in_start_ = nullptr, ev_in_done_ = nullptr, ev_out_start_ = nullptr, ev_out_done_ = nullptr;
   double *d_stage_wf_ = nullptr, *d_stage_cs_ = nullptr, *d_stage_bnd_ = nullptr, *d_snap_ = nullptr;
   size_t stage_wf_bytes_ = 0, stage_cs_bytes_ = 0, snap_bytes_ = 0;
