@@ -36,7 +36,10 @@ WEAK_GRIDS = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=None,
+                    help="timed steps (default 10; 3 for --impl reference, whose step is seconds of CPU work). A step takes "
+                         "12-40 ms here; 10 steps amortise the unoverlapped first input / last output of the pipelined e2e arm "
+                         "and give the clock sampler several samples")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cells", type=int, default=28, help="cells per side of the per-GPU brick")
@@ -73,7 +76,10 @@ def parse():
                     help="N=1: always one launch per tent level (profiling; default: automatic, see DESIGN.md section 4.5)")
     ap.add_argument("--single-launch", action="store_true",
                     help="N=1: dependency-driven single launch per slab instead of one launch per tent level (A/B)")
-    return ap.parse_args()
+    args = ap.parse_args()
+    if args.steps is None:
+        args.steps = 3 if args.impl == "reference" else 10
+    return args
 
 
 def workload(args, ngpus):
