@@ -554,11 +554,13 @@ __global__ void tent_kernel_generic(TentKernelArgs a) {
 // by the monomial tables it fills for every function. Here lane i of a half-warp owns basis function i of one element
 // of the tent (N <= 16; the two elements of a 1-D tent side by side in the two half-warps): it keeps its CSR row in
 // registers, evaluates its own function and derivatives at the Q points of a face from the power tables of that face
-// (Q x 2 x (p+1) doubles per half-warp in shared memory) and accumulates its own entry of the right-hand side; the
-// product with the stored inverse is one row per lane; the evaluation is a 16-lane shuffle tree per output value.
+// (pairs (xi^k, k xi^(k-1)) per point and direction in shared memory, filled by the half-warp's point lanes) and
+// accumulates its own entry of the right-hand side; the product with the stored inverse is one row per lane; the
+// evaluation reduces the 3 Q outputs of an element in one transposed 16-lane shuffle tree.
 // Every floating-point expression and every summation order is the generic kernel's (the same statements on the same
 // operands; the shuffle tree of the evaluation is the 32-lane tree with its upper half known to be zero), so the result
-// is bitwise the CTA variant's (tests/test_gpu_generic_cache.py).
+// is bitwise the CTA variant's (tests/test_gpu_generic_cache.py; DESIGN.md section 4.2 has the measurements that led
+// from the first version, 8.3 ms per slab of BASELINE configs[1], to 3.6 ms).
 constexpr int kSmallQ = 8, kSmallP1 = 8;
 // Tables of (xi^k, k xi^(k-1)) pairs, laid out [k][q] with an odd row length: the lanes that fill them (one point q each,
 // the same k) store consecutive 16-byte words, and the lanes that read them (the same q, different k) hit different banks
