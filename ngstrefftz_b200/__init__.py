@@ -642,10 +642,13 @@ class TWaveTents(TrefftzTents):
             xt = np.zeros((npts, self.D + 1))
             kind = np.zeros(npts, dtype=np.int32)
             check(lib.ngst_twave_boundary_points(self._h, dptr(xt), iptr(kind)))
-            self._bnd_pts = (xt, kind)
-        xt, kind = self._bnd_pts
+            # the space coordinates do not change from slab to slab: one read-only copy, so that a datum may keep
+            # what depends on x alone between calls (tests/_cases.py does)
+            x = np.ascontiguousarray(xt[:, :self.D])
+            x.flags.writeable = False
+            self._bnd_pts = (xt, kind, x)
+        xt, kind, x = self._bnd_pts
         t = xt[:, self.D] + (lib.ngst_twave_timeshift(self._h) if timeshift is None else float(timeshift))
-        x = np.ascontiguousarray(xt[:, :self.D])
         cf = self._bddatum
         Q, D = self.nip, self.D
         fk = kind.reshape(-1, Q)[:, 0]  # kind per boundary face

@@ -22,6 +22,24 @@ def standing(D, c=1.0):
         out.append(prod * np.cos(pi * t * c * sq) * c)
         return np.stack(out, axis=1)
 
+    kept = {}
+
+    def spatial_product(x):
+        # prod_d sin(pi x_d); kept between calls for a READ-ONLY array (the boundary points a solver hands out for every
+        # slab: same object, cannot change), recomputed otherwise
+        if not x.flags.writeable and kept.get("x") is x:
+            return kept["prod"]
+        prod = np.prod([np.sin(pi * x[:, d]) for d in range(D)], axis=0)
+        if not x.flags.writeable:
+            kept["x"], kept["prod"] = x, prod
+        return prod
+
+    def dt_u(x, t):
+        """Column D + 1 of f(x, t) alone (the Dirichlet datum): same expression, same bits, a fifth of the work."""
+        t = np.broadcast_to(np.asarray(t, dtype=float), (x.shape[0],))
+        return spatial_product(x) * np.cos(pi * t * c * sq) * c
+
+    f.dt_u = dt_u
     return f
 
 
@@ -59,6 +77,9 @@ def first_order(f):
 
 
 def dirichlet(f, D):
+    dt_u = getattr(f, "dt_u", None)   # data that can evaluate d_t u alone (bench.py samples 17 M boundary points per slab)
+    if dt_u is not None:
+        return lambda x, t: dt_u(x, t)
     return lambda x, t: f(x, t)[:, D + 1]
 
 
