@@ -22,6 +22,25 @@ def test_standing_matches_cases(D, c):
 
 
 @pytest.mark.parametrize("D", [1, 2, 3])
+def test_dirichlet_datum_of_the_standing_wave_is_the_full_evaluation(D):
+    """dirichlet(standing) evaluates d_t u alone and keeps its spatial factor for a read-only point array (what a solver
+    hands out for every slab): bitwise the column of the full evaluation, also when the times change between calls."""
+    from _cases import dirichlet
+    f = standing(D, 1.3)
+    bd = dirichlet(f, D)
+    x, t = pts(D, n=500)
+    assert np.array_equal(bd(x, t), f(x, t)[:, D + 1])
+    xr = x.copy()
+    xr.flags.writeable = False
+    for shift in (0.0, 0.25, 0.5):
+        assert np.array_equal(bd(xr, t + shift), f(x, t + shift)[:, D + 1])
+    x2 = np.ascontiguousarray(x[::-1])   # another array: nothing kept from the first one is used
+    x2.flags.writeable = False
+    assert np.array_equal(bd(x2, t), f(x2, t)[:, D + 1])
+    assert np.array_equal(bd(xr, 0.3), f(x, 0.3)[:, D + 1])
+
+
+@pytest.mark.parametrize("D", [1, 2, 3])
 def test_polynomial_matches_cases(D):
     x, t = pts(D)
     c = 1.2
