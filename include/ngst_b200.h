@@ -255,8 +255,9 @@ int ngst_twave_compact_state(const ngst_twave* t);
  * *bytes (may be NULL) = device memory held by the cache.
  * Values of `on` above 1 select how stored inverses are applied and leave the cache switch alone: 2 = fast kernel compiled for four
  * CTAs per SM (A/B; measured slower); generic kernel (systems of up to 32 unknowns, e.g. all 1-D tents): 3 = automatic (default:
- * one warp per tent with lanes as basis functions, tent_kernel_small1d, for D = 1 and order <= 7; one CTA per tent otherwise),
- * 4 = one CTA per tent, 5 = the CTA code executed by one warp per tent (A/B). All variants give the same bits. */
+ * one warp per tent with lanes as basis functions, tent_kernel_small1d, for D = 1 and orders 4..6; one CTA per tent otherwise),
+ * 4 = one CTA per tent, 5 = the CTA code executed by one warp per tent (A/B), 6 = tent_kernel_small1d at every order it is
+ * compiled for (1..7; orders 1..3 and 7 have not been run on a GPU yet, hence not automatic). All variants give the same bits. */
 int ngst_twave_set_factor_cache(ngst_twave* t, int on);
 int ngst_twave_factor_cache(const ngst_twave* t, long long* bytes);
 int ngst_twave_ntents_fast(const ngst_twave* t);

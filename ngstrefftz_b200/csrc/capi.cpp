@@ -499,10 +499,10 @@ int ngst_twave_compact_state(const ngst_twave* t) { return t && t->solver->compa
 int ngst_twave_set_factor_cache(ngst_twave* t, int on) {
   return guarded([&] {
     need(t, "solver");
-    if (on < 0 || on > 5) throw std::invalid_argument("ngst_twave_set_factor_cache: on must be 0..5");
-    // generic kernel, stored inverses: 3 = automatic (default: the 1-D warp-per-tent kernel where it applies), 4 = a CTA per
-    // tent, 5 = the CTA code executed by a warp per tent (A/B)
-    if (on >= 3) t->solver->set_generic_warp_apply(on == 3 ? 2 : (on == 5 ? 1 : 0));
+    if (on < 0 || on > 6) throw std::invalid_argument("ngst_twave_set_factor_cache: on must be 0..6");
+    // generic kernel, stored inverses: 3 = automatic (default: the 1-D warp-per-tent kernel at orders 4..6), 4 = a CTA per
+    // tent, 5 = the CTA code executed by a warp per tent (A/B), 6 = the 1-D warp-per-tent kernel at every order it is compiled for
+    if (on >= 3) t->solver->set_generic_warp_apply(on == 3 ? 2 : (on == 5 ? 1 : (on == 6 ? 3 : 0)));
     else t->solver->set_factor_cache(on != 0, on == 2);
   });
 }

@@ -1664,7 +1664,11 @@ double Solver::Energy(const double* wf) {
 // the next Propagate applies stored inverses of the generic kernel with one warp per tent
 int Solver::GenericWarpApply() const {
   if (!generic_warp_apply_ || !GenericCachePossible() || !ginv_valid_[fosystem_] || !d_ginv_[fosystem_]) return 0;
-  if (generic_warp_apply_ == 2) return (mesh_.D == 1 && tent_small1d_supported(args_)) ? 2 : 0;
+  // automatic: the orders the 1-D kernel has been run and compared bitwise at on a B200 (tests/test_gpu_generic_cache.py);
+  // 3 = wherever it is compiled (orders 1..7)
+  if (generic_warp_apply_ == 2)
+    return (mesh_.D == 1 && order_ >= 4 && order_ <= 6 && tent_small1d_supported(args_)) ? 2 : 0;
+  if (generic_warp_apply_ == 3) return (mesh_.D == 1 && tent_small1d_supported(args_)) ? 2 : 0;
   return tent_generic_warp_smem_bytes(mesh_.D, args_) <= 100 * 1024 ? 1 : 0;
 }
 

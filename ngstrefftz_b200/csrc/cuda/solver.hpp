@@ -119,7 +119,8 @@ class Solver {
   void set_factor_cache(bool on, bool four_ctas = false) { factor_cache_enabled_ = on; apply_four_ctas_ = four_ctas; }
   // generic kernel, stored inverses: one warp per tent (tent_kernel_generic<D, true>) instead of one CTA
   // (0 = CTA per tent, 1 = the CTA code on a warp (A/B), 2 = automatic, the default: the 1-D lanes-as-functions kernel
-  // tent_kernel_small1d where it applies -- D = 1, order <= 7 --, a CTA per tent otherwise)
+  // tent_kernel_small1d at D = 1, orders 4..6 -- the ones run on a B200 --, a CTA per tent otherwise, 3 = that kernel at
+  // every order it is compiled for, 1..7)
   void set_generic_warp_apply(int mode) { generic_warp_apply_ = mode; }
   int GenericWarpApply() const;   // 0 = CTA, 1 = tent_kernel_generic<D, true>, 2 = tent_kernel_small1d
   // multi-GPU: exchange inside the tent kernel over peer memory (default where it could be set up) or per level with NCCL

@@ -93,8 +93,8 @@ WARP_CASES["1d_p8"] = (lambda: ng.SegMesh(24, 0, 1), 8, 1.0, 0.3, standing(1), d
 
 @pytest.mark.parametrize("name", list(WARP_CASES))
 def test_warp_per_tent_apply_is_bitwise_the_cta_one(built, name):
-    """The stored inverses of the generic kernel applied by one WARP per tent -- set_factor_cache(3), the default: in 1-D up
-    to order 7 the lanes-as-functions kernel tent_kernel_small1d (a CTA per tent elsewhere); 5: tent_kernel_generic<D, true>, the
+    """The stored inverses of the generic kernel applied by one WARP per tent -- set_factor_cache(3), the default: in 1-D at
+    orders 4-6 the lanes-as-functions kernel tent_kernel_small1d (a CTA per tent elsewhere); 5: tent_kernel_generic<D, true>, the
     statements of the CTA variant executed by 32 lanes with warp-level barriers. Same arithmetic in the same order: same bits as
     the CTA variant (4)."""
     mk, order, c, dt, init, bnd, neu = WARP_CASES[name]
@@ -114,7 +114,7 @@ def test_warp_per_tent_apply_is_bitwise_the_cta_one(built, name):
             tw.Propagate()
         names.append(tw.kernel_name())
         out.append(tw.GetWavefront())
-    auto = "tent_kernel_small1d" if (m.dim == 1 and order <= 7) else "tent_kernel_generic"
+    auto = "tent_kernel_small1d" if (m.dim == 1 and 4 <= order <= 6) else "tent_kernel_generic"
     assert names == ["tent_kernel_generic", auto, "tent_kernel_generic_warp"], names
     dflt = ng.TWave(order, ts, c)   # no selection: the automatic choice
     dflt.SetInitial(init)
