@@ -738,7 +738,8 @@ class TWaveTents(TrefftzTents):
     def set_factor_cache(self, on=True):
         """Keep the inverse of every tent matrix in HBM after the first Propagate (default) or assemble and solve in every
         Propagate (ngst_twave_set_factor_cache)."""
-        check(lib.ngst_twave_set_factor_cache(self._h, int(on)))  # 2 = apply variant with four CTAs per SM (A/B)
+        # 2..6 select among bitwise-equivalent apply kernels (A/B runs), see include/ngst_b200.h
+        check(lib.ngst_twave_set_factor_cache(self._h, int(on)))
 
     def factor_cache(self):
         """(state, bytes): state 0 = not in use, 1 = next Propagate builds it, 2 = next Propagate applies it."""
